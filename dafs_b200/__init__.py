@@ -1,0 +1,22 @@
+"""dafs_b200 -- B200-native (sm_100a) engines for the DAFS hot path.
+
+The product is ``libdafs_cuda.so`` (C ABI in ``include/dafs_cuda.h``) plus the
+C++ adapters in ``dafs_b200/host`` that plug it behind the reference's
+``Align::Model`` / ``Fold::Model`` interfaces.  This Python package is only the
+thin ctypes binding the tests and ``bench.py`` drive it through; there is no
+CPU fallback anywhere: if the library or a GPU is missing, calls raise.
+"""
+from .capi import (  # noqa: F401
+    DafsCudaError,
+    CsrBatch,
+    PairHmmPlan,
+    all_pairs,
+    device_count,
+    init,
+    lib,
+    library_path,
+    pairhmm_all,
+    pairhmm_pairs,
+    pairhmm_tables,
+)
+from .synth import fasta_read, homolog_family, random_rna, splitmix64  # noqa: F401

@@ -1,0 +1,115 @@
+// Lifecycle + error plumbing of libdafs_cuda, and a small cache of pinned host
+// buffers so repeated calls do not pay cudaHostAlloc every time.
+#include "common.cuh"
+
+#include <map>
+#include <mutex>
+#include <vector>
+
+namespace dafs {
+
+std::string& last_error() {
+  static thread_local std::string e;
+  return e;
+}
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  last_error() = buf;
+  return code;
+}
+
+namespace {
+std::mutex g_pin_mu;
+std::multimap<size_t, void*> g_pin_free;   // capacity -> buffer
+std::map<void*, size_t> g_pin_cap;
+size_t g_pin_cached = 0;
+const size_t kPinCacheLimit = size_t(6) << 30;
+}  // namespace
+
+void* pinned_alloc(size_t bytes) {
+  if (bytes == 0) bytes = 1;
+  {
+    std::lock_guard<std::mutex> g(g_pin_mu);
+    auto it = g_pin_free.lower_bound(bytes);
+    if (it != g_pin_free.end() && it->first <= 2 * bytes + (1 << 20)) {
+      void* p = it->second;
+      g_pin_cached -= it->first;
+      g_pin_free.erase(it);
+      return p;
+    }
+  }
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> g(g_pin_mu);
+  g_pin_cap[p] = bytes;
+  return p;
+}
+
+void pinned_free(void* p) {
+  if (!p) return;
+  std::lock_guard<std::mutex> g(g_pin_mu);
+  const size_t cap = g_pin_cap[p];
+  if (g_pin_cached + cap <= kPinCacheLimit) {
+    g_pin_free.emplace(cap, p);
+    g_pin_cached += cap;
+  } else {
+    g_pin_cap.erase(p);
+    cudaFreeHost(p);
+  }
+}
+
+void pinned_trim() {
+  std::lock_guard<std::mutex> g(g_pin_mu);
+  for (auto& kv : g_pin_free) { g_pin_cap.erase(kv.second); cudaFreeHost(kv.second); }
+  g_pin_free.clear();
+  g_pin_cached = 0;
+}
+
+}  // namespace dafs
+
+extern "C" {
+
+const char* dafs_cuda_last_error(void) { return dafs::last_error().c_str(); }
+
+int dafs_cuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int dafs_cuda_init(int ngpu) {
+  const int n = dafs_cuda_device_count();
+  if (n <= 0) return dafs::fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)");
+  if (ngpu < 0 || ngpu > n) return dafs::fail(DAFS_CUDA_ENODEV, "requested %d GPUs, %d visible", ngpu, n);
+  const int use = ngpu == 0 ? n : ngpu;
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (int d = 0; d < use; ++d) {
+    cudaDeviceProp p;
+    DAFS_CUDA_TRY(cudaGetDeviceProperties(&p, d));
+    if (p.major != 10)
+      return dafs::fail(DAFS_CUDA_ENODEV, "device %d is sm_%d%d; this library is built for sm_100a only", d, p.major, p.minor);
+    DAFS_CUDA_TRY(cudaSetDevice(d));
+    DAFS_CUDA_TRY(cudaFree(0));
+  }
+  cudaSetDevice(cur);
+  return DAFS_CUDA_OK;
+}
+
+void dafs_cuda_shutdown(void) { dafs::pinned_trim(); }
+
+void dafs_cuda_free_batch(dafs_csr_batch* b) {
+  if (!b) return;
+  dafs::pinned_free((void*)b->owner_);
+  *b = dafs_csr_batch{};
+}
+
+}  // extern "C"

@@ -1,0 +1,51 @@
+// Shared host/device helpers for libdafs_cuda (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/dafs_cuda.h"
+
+namespace dafs {
+
+// Thread-local last-error text behind dafs_cuda_last_error().
+std::string& last_error();
+int fail(int code, const char* fmt, ...);
+
+#define DAFS_CUDA_TRY(expr)                                                        \
+  do {                                                                             \
+    cudaError_t e_ = (expr);                                                       \
+    if (e_ != cudaSuccess)                                                         \
+      return ::dafs::fail(e_ == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM       \
+                                                          : DAFS_CUDA_ECUDA,       \
+                          "%s:%d: %s -> %s", __FILE__, __LINE__, #expr,            \
+                          cudaGetErrorString(e_));                                 \
+  } while (0)
+
+// Cached pinned host memory (cudaHostAlloc is slow; results are fetched into it).
+void* pinned_alloc(size_t bytes);
+void pinned_free(void* p);
+void pinned_trim();
+
+// Symbol classes of the ProbCons alphabet "ACGUTN" (probconsRNA/Defaults.h:28,
+// wrapper.cpp:158-170).  U and T rows of the reference's tables are identical,
+// so they share class 3; 4 = N; 5 = every other byte (1e-10 / 1e-5 emissions).
+// Class 6 is internal padding: log-emission LOG_ZERO, used for columns past the
+// end of a sequence so that padded DP cells can never win a log-sum.
+enum { kClsN = 4, kClsOther = 5, kClsPad = 6, kNumCls = 7 };
+
+inline uint8_t symbol_class(unsigned char c) {
+  switch (c) {
+    case 'A': case 'a': return 0;
+    case 'C': case 'c': return 1;
+    case 'G': case 'g': return 2;
+    case 'U': case 'u': case 'T': case 't': return 3;
+    case 'N': case 'n': return kClsN;
+    default: return kClsOther;
+  }
+}
+
+}  // namespace dafs

@@ -1,0 +1,493 @@
+// Host side of (1): plan management, launch, CSR assembly and the C-ABI entry
+// points declared in include/dafs_cuda.h.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+#include <thread>
+#include <vector>
+
+#include "common.cuh"
+#include "pairhmm_post.cuh"
+
+namespace dafs {
+
+// ---- model tables: ProbabilisticModel ctor (ProbabilisticModel.h:55-88) over
+// the defaults of probconsRNA/Defaults.h:19-39 --------------------------------
+static const float kInit[3] = {0.9588437676f, 0.0205782652f, 0.0205782652f};
+static const float kGapOpen = 0.0190259293f, kGapExtend = 0.3269913495f;
+static const float kEmitSingle[5] = {0.2270790040f, 0.2422080040f, 0.2839320004f, 0.2464679927f,
+                                     0.0003124650f};   // A C G U/T N
+static const float kEmitPairs[5][5] = {
+    {0.1487240046f, 0.0184142999f, 0.0361397006f, 0.0238473993f, 0.0000375308f},
+    {0.0184142999f, 0.1583919972f, 0.0275536999f, 0.0389291011f, 0.0000815823f},
+    {0.0361397006f, 0.0275536999f, 0.1979320049f, 0.0244289003f, 0.0000824765f},
+    {0.0238473993f, 0.0389291011f, 0.0244289003f, 0.1557479948f, 0.0000743985f},
+    {0.0000375308f, 0.0000815823f, 0.0000824765f, 0.0000743985f, 0.0000263252f}};
+
+static void build_tables(PairHmmTables& t) {
+  float tm[3][3] = {{0.f}};
+  tm[0][0] = 1;
+  tm[0][1] = kGapOpen; tm[0][2] = kGapOpen;
+  tm[0][0] -= (kGapOpen + kGapOpen);
+  tm[1][1] = kGapExtend; tm[2][2] = kGapExtend;
+  tm[1][0] = 1 - kGapExtend; tm[2][0] = 1 - kGapExtend;
+  for (int i = 0; i < 3; ++i) {
+    t.init[i] = logf(kInit[i]);
+    for (int j = 0; j < 3; ++j) t.trans[i * 3 + j] = logf(tm[i][j]);   // log 0 = -inf, never read
+  }
+  for (int a = 0; a < 8; ++a) {
+    t.ins[a] = a < 5 ? logf(kEmitSingle[a]) : a == kClsOther ? logf((float)1e-5) : DAFS_LOG_ZERO;
+    for (int b = 0; b < 8; ++b) {
+      float v;
+      if (a < 5 && b < 5) v = logf(kEmitPairs[a][b]);
+      else if (a <= kClsOther && b <= kClsOther) v = logf((float)1e-10);
+      else v = DAFS_LOG_ZERO;
+      t.match[a * 8 + b] = v;
+    }
+  }
+}
+
+static const PairHmmTables& host_tables() {
+  static PairHmmTables t;
+  static bool built = false;
+  if (!built) { build_tables(t); built = true; }
+  return t;
+}
+
+// keep-threshold prefilter: x <= xcut implies EXP(x) <= th (EXP's pieces are
+// within ~1.1e-4 of exp on [-16,0]), so such cells are never kept.
+static float compute_xcut(float th) {
+  if (th < 0.f) return -INFINITY;
+  if (th < 5.2e-4f) return -16.0f;
+  return logf(th) - 0.5f;
+}
+
+// ---- small helper kernels ---------------------------------------------------
+// Exclusive scan of per-pair nnz -> nz_off[npairs+1]; one block.
+__global__ void scan_nnz_kernel(const int32_t* __restrict__ nnz, int n, int64_t* __restrict__ off) {
+  __shared__ long long part[1024];
+  const int t = threadIdx.x, T = blockDim.x;
+  const int per = (n + T - 1) / T;
+  const int b = min(n, t * per), e = min(n, b + per);
+  long long s = 0;
+  for (int k = b; k < e; ++k) s += nnz[k];
+  part[t] = s;
+  __syncthreads();
+  if (t == 0) {
+    long long run = 0;
+    for (int k = 0; k < T; ++k) { const long long v = part[k]; part[k] = run; run += v; }
+    off[n] = run;
+  }
+  __syncthreads();
+  long long run = part[t];
+  for (int k = b; k < e; ++k) { off[k] = run; run += nnz[k]; }
+}
+
+// Pool (completion order) -> pair order.  One warp per pair.
+__global__ void gather_csr_kernel(int npairs, const int64_t* __restrict__ pool_off,
+                                  const int32_t* __restrict__ nnz, const int64_t* __restrict__ nz_off,
+                                  const uint32_t* __restrict__ pcol, const float* __restrict__ pval,
+                                  uint32_t* __restrict__ col, float* __restrict__ val) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  for (int p = blockIdx.x * wpb + (threadIdx.x >> 5); p < npairs; p += gridDim.x * wpb) {
+    const int64_t src = pool_off[p], dst = nz_off[p];
+    const int n = nnz[p];
+    for (int k = lane; k < n; k += 32) { col[dst + k] = pcol[src + k]; val[dst + k] = pval[src + k]; }
+  }
+}
+
+}  // namespace dafs
+
+// ---- plan -------------------------------------------------------------------
+struct dafs_pairhmm_plan {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int nseq = 0, npairs = 0;
+  float th = 0, xcut = 0;
+  int C = 0, grid = 0;
+  int64_t total_rows = 0;          // sum over pairs of (L1+1)
+  std::vector<int64_t> row_off;    // host copy, [npairs+1]
+  // device
+  uint8_t* d_seq = nullptr; int64_t* d_seq_off = nullptr; int32_t* d_seq_len = nullptr;
+  int2* d_pairs = nullptr; int32_t* d_order = nullptr;
+  float* d_planes = nullptr; int64_t plane_stride = 0;
+  float4* d_bnd = nullptr; int64_t bnd_stride = 0;
+  int* d_queue = nullptr; unsigned long long* d_pool_count = nullptr;
+  int64_t* d_row_off = nullptr; int32_t* d_row_ptr = nullptr;
+  uint32_t* d_pool_col = nullptr; float* d_pool_val = nullptr; int64_t pool_cap = 0;
+  int64_t* d_pair_pool_off = nullptr; int32_t* d_pair_nnz = nullptr; float* d_pair_total = nullptr;
+  int64_t* d_nz_off = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
+  bool launched = false;
+  int64_t nnz = -1;
+  float last_ms = 0;
+};
+
+namespace dafs {
+
+static const int kWarps = 4;     // warps per CTA
+static const int kMinBlocks = 4; // CTAs per SM the kernel is compiled for (<=128 regs)
+
+static void free_plan_buffers(dafs_pairhmm_plan* p) {
+  cudaFree(p->d_seq); cudaFree(p->d_seq_off); cudaFree(p->d_seq_len); cudaFree(p->d_pairs);
+  cudaFree(p->d_order); cudaFree(p->d_planes); cudaFree(p->d_bnd); cudaFree(p->d_queue);
+  cudaFree(p->d_pool_count); cudaFree(p->d_row_off); cudaFree(p->d_row_ptr);
+  cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_pair_pool_off);
+  cudaFree(p->d_pair_nnz); cudaFree(p->d_pair_total); cudaFree(p->d_nz_off);
+  cudaFree(p->d_col); cudaFree(p->d_val);
+  if (p->ev0) cudaEventDestroy(p->ev0);
+  if (p->ev1) cudaEventDestroy(p->ev1);
+  if (p->stream) cudaStreamDestroy(p->stream);
+}
+
+static int alloc_pool(dafs_pairhmm_plan* p, int64_t cap) {
+  cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_col); cudaFree(p->d_val);
+  p->d_pool_col = nullptr; p->d_pool_val = nullptr; p->d_col = nullptr; p->d_val = nullptr;
+  cap = std::max<int64_t>(cap, 32);
+  DAFS_CUDA_TRY(cudaMalloc(&p->d_pool_col, cap * sizeof(uint32_t)));
+  DAFS_CUDA_TRY(cudaMalloc(&p->d_pool_val, cap * sizeof(float)));
+  DAFS_CUDA_TRY(cudaMalloc(&p->d_col, cap * sizeof(uint32_t)));
+  DAFS_CUDA_TRY(cudaMalloc(&p->d_val, cap * sizeof(float)));
+  p->pool_cap = cap;
+  return DAFS_CUDA_OK;
+}
+
+// Columns per lane: minimise the padded DP width over the instantiated widths,
+// larger C (fewer stripes) on ties.
+static const int kColsPerLane[] = {2, 3, 4, 5, 6, 8, 10, 12};
+static int choose_cols(int max_l2) {
+  int best = 12; int64_t best_w = INT64_MAX;
+  for (int c : kColsPerLane) {
+    const int sw = 32 * c;
+    const int64_t w = (int64_t)((max_l2 + 1 + sw - 1) / sw) * sw;
+    if (w <= best_w) { best_w = w; best = c; }
+  }
+  return best;
+}
+
+template <int C>
+static cudaError_t launch_pairhmm(const PairHmmArgs& a, int grid, cudaStream_t st) {
+  pairhmm_kernel<C, kWarps, kMinBlocks><<<grid, kWarps * 32, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+static int launch_all(dafs_pairhmm_plan* p) {
+  PairHmmArgs a;
+  a.seq = p->d_seq; a.seq_off = p->d_seq_off; a.seq_len = p->d_seq_len;
+  a.pairs = p->d_pairs; a.order = p->d_order; a.npairs = p->npairs;
+  a.th = p->th; a.xcut = p->xcut;
+  a.planes = p->d_planes; a.plane_stride = p->plane_stride;
+  a.bnd = p->d_bnd; a.bnd_stride = p->bnd_stride;
+  a.queue = p->d_queue;
+  a.row_off = p->d_row_off; a.row_ptr = p->d_row_ptr;
+  a.pool_count = p->d_pool_count; a.pool_col = p->d_pool_col; a.pool_val = p->d_pool_val;
+  a.pool_cap = p->pool_cap;
+  a.pair_pool_off = p->d_pair_pool_off; a.pair_nnz = p->d_pair_nnz; a.pair_total = p->d_pair_total;
+  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
+  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_pool_count, 0, sizeof(unsigned long long), p->stream));
+  DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
+  cudaError_t e;
+  switch (p->C) {
+    case 2: e = launch_pairhmm<2>(a, p->grid, p->stream); break;
+    case 3: e = launch_pairhmm<3>(a, p->grid, p->stream); break;
+    case 4: e = launch_pairhmm<4>(a, p->grid, p->stream); break;
+    case 5: e = launch_pairhmm<5>(a, p->grid, p->stream); break;
+    case 6: e = launch_pairhmm<6>(a, p->grid, p->stream); break;
+    case 8: e = launch_pairhmm<8>(a, p->grid, p->stream); break;
+    case 10: e = launch_pairhmm<10>(a, p->grid, p->stream); break;
+    default: e = launch_pairhmm<12>(a, p->grid, p->stream); break;
+  }
+  DAFS_CUDA_TRY(e);
+  scan_nnz_kernel<<<1, 1024, 0, p->stream>>>(p->d_pair_nnz, p->npairs, p->d_nz_off);
+  DAFS_CUDA_TRY(cudaGetLastError());
+  const int gblocks = std::min(p->npairs / 8 + 1, 148 * 8);
+  gather_csr_kernel<<<gblocks, 256, 0, p->stream>>>(p->npairs, p->d_pair_pool_off, p->d_pair_nnz,
+                                                    p->d_nz_off, p->d_pool_col, p->d_pool_val,
+                                                    p->d_col, p->d_val);
+  DAFS_CUDA_TRY(cudaGetLastError());
+  DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
+  p->launched = true;
+  p->nnz = -1;
+  return DAFS_CUDA_OK;
+}
+
+}  // namespace dafs
+
+// ---- C ABI -------------------------------------------------------------------
+using dafs::fail;
+
+extern "C" int dafs_cuda_pairhmm_tables(float* out54) {
+  if (!out54) return fail(DAFS_CUDA_EINVAL, "out54 is NULL");
+  const dafs::PairHmmTables& t = dafs::host_tables();
+  int k = 0;
+  for (int i = 0; i < 3; ++i) out54[k++] = t.init[i];
+  for (int i = 0; i < 9; ++i) out54[k++] = t.trans[i];
+  for (int a = 0; a < 6; ++a) out54[k++] = t.ins[a];
+  for (int a = 0; a < 6; ++a)
+    for (int b = 0; b < 6; ++b) out54[k++] = t.match[a * 8 + b];
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, const int* len,
+                                             int64_t npairs, const int32_t* pi, const int32_t* pj,
+                                             float th, dafs_pairhmm_plan** out) {
+  using namespace dafs;
+  if (!out) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  *out = nullptr;
+  if (nseq < 0 || npairs < 0 || npairs > INT32_MAX / 2) return fail(DAFS_CUDA_EINVAL, "bad nseq/npairs");
+  if ((nseq > 0 && (!seq || !len)) || (npairs > 0 && (!pi || !pj))) return fail(DAFS_CUDA_EINVAL, "NULL input array");
+  if (std::isnan(th)) return fail(DAFS_CUDA_EINVAL, "threshold is NaN");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    cudaGetLastError();
+    return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)");
+  }
+  for (int i = 0; i < nseq; ++i)
+    if (len[i] < 1 || !seq[i]) return fail(DAFS_CUDA_EINVAL, "sequence %d is empty (the reference reads seq[1] unconditionally, ProbabilisticModel.h:123)", i);
+  for (int64_t k = 0; k < npairs; ++k)
+    if (pi[k] < 0 || pi[k] >= nseq || pj[k] < 0 || pj[k] >= nseq) return fail(DAFS_CUDA_EINVAL, "pair %lld out of range", (long long)k);
+
+  dafs_pairhmm_plan* p = new dafs_pairhmm_plan();
+  auto bail = [&](int rc) { free_plan_buffers(p); delete p; return rc; };
+#define PLAN_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return bail(fail(e_ == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM : DAFS_CUDA_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_))); } while (0)
+  PLAN_TRY(cudaGetDevice(&p->device));
+  p->nseq = nseq; p->npairs = (int)npairs; p->th = th; p->xcut = compute_xcut(th);
+  PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  PLAN_TRY(cudaEventCreate(&p->ev0));
+  PLAN_TRY(cudaEventCreate(&p->ev1));
+  static bool tables_up[64] = {false};
+  if (!tables_up[p->device & 63]) {
+    PLAN_TRY(cudaMemcpyToSymbol(c_tab, &host_tables(), sizeof(PairHmmTables)));
+    tables_up[p->device & 63] = true;
+  }
+
+  // encode sequences
+  std::vector<int64_t> seq_off(nseq + 1, 0);
+  for (int i = 0; i < nseq; ++i) seq_off[i + 1] = seq_off[i] + len[i];
+  std::vector<uint8_t> enc(std::max<int64_t>(seq_off[nseq], 1));
+  for (int i = 0; i < nseq; ++i)
+    for (int k = 0; k < len[i]; ++k) enc[seq_off[i] + k] = symbol_class((unsigned char)seq[i][k]);
+
+  // pair list, cost order (longest first), row offsets, geometry
+  std::vector<int2> pairs(std::max<int64_t>(npairs, 1));
+  std::vector<int32_t> order(std::max<int64_t>(npairs, 1));
+  p->row_off.assign(npairs + 1, 0);
+  int max_l1 = 1, max_l2 = 1;
+  int64_t est_nnz = 0;
+  for (int64_t k = 0; k < npairs; ++k) {
+    pairs[k] = make_int2(pi[k], pj[k]);
+    order[k] = (int32_t)k;
+    const int l1 = len[pi[k]], l2 = len[pj[k]];
+    p->row_off[k + 1] = p->row_off[k] + l1 + 1;
+    max_l1 = std::max(max_l1, l1); max_l2 = std::max(max_l2, l2);
+    est_nnz += (int64_t)l1 * std::min(l2, 10) + 64;
+  }
+  p->total_rows = p->row_off[npairs];
+  std::stable_sort(order.begin(), order.begin() + npairs, [&](int32_t a, int32_t b) {
+    return (int64_t)len[pi[a]] * len[pj[a]] > (int64_t)len[pi[b]] * len[pj[b]];
+  });
+  p->C = choose_cols(max_l2);
+  const int sw = 32 * p->C;
+  const int64_t pw = (int64_t)((max_l2 + 1 + sw - 1) / sw) * sw;
+  p->plane_stride = (int64_t)(max_l1 + 1) * pw;
+  p->bnd_stride = max_l1 + 1;
+  cudaDeviceProp prop;
+  PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
+  const int max_grid = prop.multiProcessorCount * kMinBlocks;
+  p->grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_grid, (npairs + kWarps - 1) / kWarps));
+  const int64_t slots = (int64_t)p->grid * kWarps;
+
+  PLAN_TRY(cudaMalloc(&p->d_seq, enc.size()));
+  PLAN_TRY(cudaMalloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * std::max(nseq, 1)));
+  PLAN_TRY(cudaMalloc(&p->d_pairs, sizeof(int2) * pairs.size()));
+  PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * order.size()));
+  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * p->plane_stride * slots));
+  PLAN_TRY(cudaMalloc(&p->d_bnd, sizeof(float4) * p->bnd_stride * 2 * slots));
+  PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
+  PLAN_TRY(cudaMalloc(&p->d_pool_count, sizeof(unsigned long long)));
+  PLAN_TRY(cudaMalloc(&p->d_row_off, sizeof(int64_t) * (npairs + 1)));
+  PLAN_TRY(cudaMalloc(&p->d_row_ptr, sizeof(int32_t) * std::max<int64_t>(p->total_rows, 1)));
+  PLAN_TRY(cudaMalloc(&p->d_pair_pool_off, sizeof(int64_t) * pairs.size()));
+  PLAN_TRY(cudaMalloc(&p->d_pair_nnz, sizeof(int32_t) * pairs.size()));
+  PLAN_TRY(cudaMalloc(&p->d_pair_total, sizeof(float) * pairs.size()));
+  PLAN_TRY(cudaMalloc(&p->d_nz_off, sizeof(int64_t) * (npairs + 1)));
+  { const int rc = alloc_pool(p, est_nnz); if (rc) return bail(rc); }
+  PLAN_TRY(cudaMemcpyAsync(p->d_seq, enc.data(), enc.size(), cudaMemcpyHostToDevice, p->stream));
+  PLAN_TRY(cudaMemcpyAsync(p->d_seq_off, seq_off.data(), sizeof(int64_t) * (nseq + 1), cudaMemcpyHostToDevice, p->stream));
+  if (nseq) PLAN_TRY(cudaMemcpyAsync(p->d_seq_len, len, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, p->stream));
+  PLAN_TRY(cudaMemcpyAsync(p->d_pairs, pairs.data(), sizeof(int2) * pairs.size(), cudaMemcpyHostToDevice, p->stream));
+  PLAN_TRY(cudaMemcpyAsync(p->d_order, order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, p->stream));
+  PLAN_TRY(cudaMemcpyAsync(p->d_row_off, p->row_off.data(), sizeof(int64_t) * (npairs + 1), cudaMemcpyHostToDevice, p->stream));
+  PLAN_TRY(cudaStreamSynchronize(p->stream));   // host vectors above go out of scope
+#undef PLAN_TRY
+  *out = p;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_pairhmm_plan_run(dafs_pairhmm_plan* p) {
+  if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  if (p->npairs == 0) { p->launched = true; p->nnz = 0; return DAFS_CUDA_OK; }
+  return dafs::launch_all(p);
+}
+
+extern "C" int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* p, float* device_ms, int64_t* nnz) {
+  if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  if (p->npairs > 0 && p->nnz < 0) {
+    for (int attempt = 0;; ++attempt) {
+      DAFS_CUDA_TRY(cudaStreamSynchronize(p->stream));
+      unsigned long long count = 0;
+      DAFS_CUDA_TRY(cudaMemcpy(&count, p->d_pool_count, sizeof count, cudaMemcpyDeviceToHost));
+      if ((int64_t)count <= p->pool_cap) { p->nnz = (int64_t)count; break; }
+      // The pool was sized from a density guess; now the exact size is known.
+      if (attempt >= 2) return fail(DAFS_CUDA_ECUDA, "posterior pool overflow persists");
+      const int rc = dafs::alloc_pool(p, (int64_t)count + 1024);
+      if (rc) return rc;
+      const int rc2 = dafs::launch_all(p);
+      if (rc2) return rc2;
+    }
+    DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+  }
+  if (device_ms) *device_ms = p->last_ms;
+  if (nnz) *nnz = p->nnz;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch* out) {
+  if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  *out = dafs_csr_batch{};
+  const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+  if (rc) return rc;
+  const int64_t np = p->npairs, nnz = p->nnz, rows = p->total_rows;
+  // one pinned block: row_off | nz_off | row_ptr | col | val
+  const size_t b_row_off = sizeof(int64_t) * (np + 1), b_nz_off = sizeof(int64_t) * (np + 1);
+  const size_t b_row_ptr = sizeof(int32_t) * rows, b_col = sizeof(uint32_t) * nnz, b_val = sizeof(float) * nnz;
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t total = up(b_row_off) + up(b_nz_off) + up(b_row_ptr) + up(b_col) + up(b_val);
+  char* base = (char*)dafs::pinned_alloc(total);
+  if (!base) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %zu bytes failed", total);
+  int64_t* h_row_off = (int64_t*)base;
+  int64_t* h_nz_off = (int64_t*)(base + up(b_row_off));
+  int32_t* h_row_ptr = (int32_t*)((char*)h_nz_off + up(b_nz_off));
+  uint32_t* h_col = (uint32_t*)((char*)h_row_ptr + up(b_row_ptr));
+  float* h_val = (float*)((char*)h_col + up(b_col));
+  std::memcpy(h_row_off, p->row_off.data(), b_row_off);
+  cudaError_t e = cudaSuccess;
+  if (np > 0) {
+    e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h_row_ptr, p->d_row_ptr, b_row_ptr, cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_col, p->d_col, b_col, cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_val, p->d_val, b_val, cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  } else {
+    h_nz_off[0] = 0;
+  }
+  if (e != cudaSuccess) {
+    dafs::pinned_free(base);
+    return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
+  }
+  out->n_units = np; out->nnz = nnz;
+  out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
+  out->col = h_col; out->val = h_val; out->owner_ = base;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* p) {
+  if (!p) return;
+  cudaSetDevice(p->device);
+  if (p->stream) cudaStreamSynchronize(p->stream);
+  dafs::free_plan_buffers(p);
+  delete p;
+}
+
+extern "C" int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const int* len,
+                                       int64_t npairs, const int32_t* pi, const int32_t* pj,
+                                       float th, dafs_csr_batch* out) {
+  if (!out) return fail(DAFS_CUDA_EINVAL, "out is NULL");
+  *out = dafs_csr_batch{};
+  dafs_pairhmm_plan* p = nullptr;
+  int rc = dafs_cuda_pairhmm_plan_create(nseq, seq, len, npairs, pi, pj, th, &p);
+  if (rc) return rc;
+  rc = dafs_cuda_pairhmm_plan_run(p);
+  if (!rc) rc = dafs_cuda_pairhmm_plan_fetch(p, out);
+  dafs_cuda_pairhmm_plan_destroy(p);
+  return rc;
+}
+
+// All i<j pairs, row-major (src/align.cpp:41-51).  With ngpu > 1 the pair list
+// is dealt round-robin over the devices of this process (pairs arrive cost
+// sorted inside each plan), one host thread per device, and the per-device
+// batches are merged on the host in pair order.
+extern "C" int dafs_cuda_pairhmm_all(int nseq, const char* const* seq, const int* len, float th,
+                                     int ngpu, dafs_csr_batch* out) {
+  if (!out) return fail(DAFS_CUDA_EINVAL, "out is NULL");
+  *out = dafs_csr_batch{};
+  if (nseq < 0) return fail(DAFS_CUDA_EINVAL, "nseq < 0");
+  const int64_t npairs = (int64_t)nseq * (nseq - 1) / 2;
+  std::vector<int32_t> pi(std::max<int64_t>(npairs, 1)), pj(std::max<int64_t>(npairs, 1));
+  int64_t k = 0;
+  for (int i = 0; i < nseq; ++i)
+    for (int j = i + 1; j < nseq; ++j) { pi[k] = i; pj[k] = j; ++k; }
+  const int ndev = dafs_cuda_device_count();
+  if (ndev <= 0) return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)");
+  if (ngpu > ndev) return fail(DAFS_CUDA_ENODEV, "requested %d GPUs, %d visible", ngpu, ndev);
+  if (ngpu <= 1 || npairs < 2 * ngpu)
+    return dafs_cuda_pairhmm_pairs(nseq, seq, len, npairs, pi.data(), pj.data(), th, out);
+
+  std::vector<std::vector<int32_t>> spi(ngpu), spj(ngpu);
+  std::vector<std::vector<int64_t>> sidx(ngpu);
+  for (int64_t q = 0; q < npairs; ++q) {
+    const int d = (int)(q % ngpu);
+    spi[d].push_back(pi[q]); spj[d].push_back(pj[q]); sidx[d].push_back(q);
+  }
+  std::vector<dafs_csr_batch> part(ngpu);
+  std::vector<int> rc(ngpu, 0);
+  std::vector<std::string> err(ngpu);
+  std::vector<std::thread> workers;
+  for (int d = 0; d < ngpu; ++d)
+    workers.emplace_back([&, d]() {
+      if (cudaSetDevice(d) != cudaSuccess) { rc[d] = DAFS_CUDA_ECUDA; err[d] = "cudaSetDevice failed"; return; }
+      rc[d] = dafs_cuda_pairhmm_pairs(nseq, seq, len, (int64_t)spi[d].size(), spi[d].data(),
+                                      spj[d].data(), th, &part[d]);
+      if (rc[d]) err[d] = dafs::last_error();
+    });
+  for (auto& w : workers) w.join();
+  for (int d = 0; d < ngpu; ++d)
+    if (rc[d]) {
+      for (auto& b : part) dafs_cuda_free_batch(&b);
+      return fail(rc[d], "device %d: %s", d, err[d].c_str());
+    }
+  // merge
+  int64_t nnz = 0, rows = 0;
+  for (int64_t q = 0; q < npairs; ++q) rows += len[pi[q]] + 1;
+  for (auto& b : part) nnz += b.nnz;
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t b_off = sizeof(int64_t) * (npairs + 1);
+  const size_t total = 2 * up(b_off) + up(sizeof(int32_t) * rows) + up(sizeof(uint32_t) * nnz) + up(sizeof(float) * nnz);
+  char* base = (char*)dafs::pinned_alloc(total);
+  if (!base) { for (auto& b : part) dafs_cuda_free_batch(&b); return fail(DAFS_CUDA_ENOMEM, "pinned allocation failed"); }
+  int64_t* row_off = (int64_t*)base;
+  int64_t* nz_off = (int64_t*)(base + up(b_off));
+  int32_t* row_ptr = (int32_t*)((char*)nz_off + up(b_off));
+  uint32_t* col = (uint32_t*)((char*)row_ptr + up(sizeof(int32_t) * rows));
+  float* val = (float*)((char*)col + up(sizeof(uint32_t) * nnz));
+  row_off[0] = 0; nz_off[0] = 0;
+  for (int64_t q = 0; q < npairs; ++q) {
+    const int d = (int)(q % ngpu); const int64_t u = q / ngpu;
+    const dafs_csr_batch& b = part[d];
+    const int64_t nr = b.row_off[u + 1] - b.row_off[u], nz = b.nz_off[u + 1] - b.nz_off[u];
+    std::memcpy(row_ptr + row_off[q], b.row_ptr + b.row_off[u], sizeof(int32_t) * nr);
+    std::memcpy(col + nz_off[q], b.col + b.nz_off[u], sizeof(uint32_t) * nz);
+    std::memcpy(val + nz_off[q], b.val + b.nz_off[u], sizeof(float) * nz);
+    row_off[q + 1] = row_off[q] + nr; nz_off[q + 1] = nz_off[q] + nz;
+  }
+  for (auto& b : part) dafs_cuda_free_batch(&b);
+  out->n_units = npairs; out->nnz = nnz; out->row_off = row_off; out->row_ptr = row_ptr;
+  out->nz_off = nz_off; out->col = col; out->val = val; out->owner_ = base;
+  return DAFS_CUDA_OK;
+}

@@ -1,0 +1,144 @@
+// K1/K2: batched ProbCons pair-HMM forward / backward / posterior for sm_100a.
+//
+// Reference: ProbabilisticModel::ComputeForwardMatrix / ComputeBackwardMatrix /
+// ComputeTotalProbability / ComputePosteriorMatrix
+// (src/probconsRNA/ProbabilisticModel.h:105-179, :197-259, :337-365, :374-403),
+// the >= th / > th sparsification of wrapper.cpp:125-128 and align.cpp:69-78.
+//
+// Mapping (no tensor cores: nothing here is a contraction).  One warp owns one
+// sequence pair at a time and pulls pairs from an atomic queue (persistent
+// grid).  The DP matrix is cut into column stripes of 32*C columns; inside a
+// stripe lane t owns C consecutive columns whose three state values of the
+// previous row stay in registers, and the rows run through the lanes as a
+// skewed pipeline: at step s lane t works on row s-t and hands its last column
+// to lane t+1 with warp shuffles.  There is no block-level barrier anywhere in
+// the DP.  The forward match plane F_M (the only O(L1*L2) intermediate) goes to
+// a per-warp slot in HBM, the backward sweep overwrites it with F_M+B_M, and a
+// coalesced sweep of that slot produces the thresholded CSR rows.
+#pragma once
+#include <cstdint>
+
+#include "pairhmm_math.cuh"
+
+namespace dafs {
+
+struct PairHmmTables {   // log-space, symbol classes A C G U/T N other pad
+  float init[3];         // ProbabilisticModel.h:76
+  float trans[9];        // [from*3+to], :77-78
+  float ins[8];          // :83-84   (class 6 = pad = LOG_ZERO)
+  float match[64];       // [c1*8+c2], :85-86
+};
+
+struct PairHmmArgs {
+  const uint8_t* seq;        // concatenated symbol classes
+  const int64_t* seq_off;    // [nseq]
+  const int32_t* seq_len;    // [nseq]
+  const int2* pairs;         // [npairs] (row sequence, column sequence)
+  const int32_t* order;      // [npairs] queue position -> pair index (longest first)
+  int npairs;
+  float th;                  // keep p > th
+  float xcut;                // cells with F+B-total <= xcut cannot exceed th
+  float* planes;             // per-warp-slot F_M / F_M+B_M plane
+  int64_t plane_stride;      // floats per slot
+  float4* bnd;               // per-warp-slot stripe-boundary columns (2 buffers)
+  int64_t bnd_stride;        // float4 per buffer
+  int* queue;                // work counter
+  // outputs
+  const int64_t* row_off;    // [npairs+1]
+  int32_t* row_ptr;          // concatenated per-pair row_ptr blocks
+  unsigned long long* pool_count;
+  uint32_t* pool_col;
+  float* pool_val;
+  int64_t pool_cap;
+  int64_t* pair_pool_off;    // [npairs] where the pair's entries start in the pool
+  int32_t* pair_nnz;         // [npairs]
+  float* pair_total;         // [npairs] total log-probability (diagnostic)
+};
+
+__constant__ PairHmmTables c_tab;
+
+// Per-block shared tables, replicated once per lane (index*32 + lane) so that a
+// warp whose lanes look up different symbols never has a bank conflict.
+struct PairHmmSmem {
+  float match[64 * 32];
+  float ins[8 * 32];
+};
+
+template <int C>
+struct StripeCols {       // per-lane constants of the current stripe
+  int mofs[C];            // class(column j)*32 + lane : offset into smem.match row
+  float ins[C];           // log insert emission of column j
+};
+
+// ---------------------------------------------------------------------------
+// Forward sweep over one stripe.  Returns (through fend) F_k(L1, L2) when the
+// stripe contains column L2.
+template <int C>
+__device__ __forceinline__ void forward_stripe(
+    const PairHmmSmem& sm, const uint8_t* __restrict__ s1, int L1, int L2, int stripe,
+    int nstripes, int lane, const StripeCols<C>& sc, float* __restrict__ plane, int PW,
+    const float4* __restrict__ bnd_in, float4* __restrict__ bnd_out, float (&fend)[3]) {
+  const float T00 = c_tab.trans[0], T01 = c_tab.trans[1], T02 = c_tab.trans[2];
+  const float T10 = c_tab.trans[3], T11 = c_tab.trans[4];
+  const float T20 = c_tab.trans[6], T22 = c_tab.trans[8];
+  const int j0 = stripe * 32 * C + lane * C;
+  const bool origin = (stripe == 0 && lane == 0);   // owns cells (0,0),(0,1),(1,0),(1,1)
+
+  float pM[C], pX[C], pY[C];                        // F(i-1, j0+c)
+#pragma unroll
+  for (int c = 0; c < C; ++c) pM[c] = pX[c] = pY[c] = DAFS_LOG_ZERO;
+  float dM = DAFS_LOG_ZERO, dX = DAFS_LOG_ZERO, dY = DAFS_LOG_ZERO;   // F(i-1, j0-1)
+  float oM = DAFS_LOG_ZERO, oX = DAFS_LOG_ZERO, oY = DAFS_LOG_ZERO;   // my last column, last step
+  // Lane t works on row s-t at step s.  Row 0 has no symbol; any finite class
+  // works there because every term it feeds is LOG_ZERO-absorbed.
+  int cls_next = kClsOther;                         // class of seq1 for the next step's row
+  const int nsteps = L1 + 1 + 31;
+  for (int step = 0; step < nsteps; ++step) {
+    float lM = __shfl_up_sync(0xffffffffu, oM, 1);
+    float lX = __shfl_up_sync(0xffffffffu, oX, 1);
+    float lY = __shfl_up_sync(0xffffffffu, oY, 1);
+    const int i = step - lane;
+    const int cls1 = cls_next;
+    if (i + 1 >= 1 && i + 1 <= L1) cls_next = s1[i];          // prefetch symbol of row i+1
+    if (i < 0 || i > L1) continue;
+    if (lane == 0) {
+      if (stripe > 0) { const float4 b = bnd_in[i]; lM = b.x; lX = b.y; lY = b.z; }
+      else { lM = lX = lY = DAFS_LOG_ZERO; }
+    }
+    const float insRow = sm.ins[cls1 * 32 + lane];
+    const float* mrow = sm.match + cls1 * 8 * 32;
+    float leftM = lM, leftY = lY;
+    float gM = dM, gX = dX, gY = dY;                           // diagonal F(i-1, j-1)
+    float* prow = plane + (int64_t)i * PW + j0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      // ProbabilisticModel.h:151-156
+      float nM = pairhmm_lse(pairhmm_lse(__fadd_rn(gM, T00), __fadd_rn(gX, T10)), __fadd_rn(gY, T20));
+      nM = __fadd_rn(nM, mrow[sc.mofs[c]]);
+      // :157-162
+      float nX = __fadd_rn(insRow, pairhmm_lse(__fadd_rn(pM[c], T01), __fadd_rn(pX[c], T11)));
+      // :163-168
+      float nY = __fadd_rn(sc.ins[c], pairhmm_lse(__fadd_rn(leftM, T02), __fadd_rn(leftY, T22)));
+      if (c < 2 && origin && i <= 1) {
+        // seeds, ProbabilisticModel.h:123-131; (0,0) and the other states stay LOG_ZERO (:150)
+        nM = (i == 1 && c == 1) ? __fadd_rn(c_tab.init[0], mrow[sc.mofs[1]]) : DAFS_LOG_ZERO;
+        nX = (i == 1 && c == 0) ? __fadd_rn(c_tab.init[1], insRow) : DAFS_LOG_ZERO;
+        nY = (i == 0 && c == 1) ? __fadd_rn(c_tab.init[2], sc.ins[1]) : DAFS_LOG_ZERO;
+      }
+      gM = pM[c]; gX = pX[c]; gY = pY[c];
+      pM[c] = nM; pX[c] = nX; pY[c] = nY;
+      leftM = nM; leftY = nY;
+      prow[c] = nM;
+    }
+    dM = lM; dX = lX; dY = lY;
+    oM = pM[C - 1]; oX = pX[C - 1]; oY = pY[C - 1];
+    if (lane == 31 && stripe + 1 < nstripes) bnd_out[i] = make_float4(oM, oX, oY, 0.f);
+    if (i == L1) {
+#pragma unroll
+      for (int c = 0; c < C; ++c)
+        if (j0 + c == L2) { fend[0] = pM[c]; fend[1] = pX[c]; fend[2] = pY[c]; }
+    }
+  }
+}
+
+}  // namespace dafs

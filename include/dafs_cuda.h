@@ -1,0 +1,111 @@
+/* libdafs_cuda -- C ABI of the B200-native DAFS hot path.
+ *
+ * Drop-in boundary for satoken/dafs (reference paths are relative to its tree):
+ *   (1) all-pairs ProbCons pair-HMM matching posteriors
+ *         replaces Align::Model::calculate(fa, mp)        src/align.cpp:35-52
+ *         and ProbCons::calculate(seq1, seq2, mp)         src/align.cpp:60-79
+ *   (2) Boltzmann/McCaskill base-pairing probabilities
+ *         replaces Fold::Model::calculate(fa, bp)         src/fold.cpp:60-68
+ *         and RNAfold::calculate(seq, bp)                 src/fold.cpp:78-116
+ *   (3) the dual-decomposition solver and its two decoders
+ *         replaces DAFS::solve_by_dd                      src/dafs.cpp:1006-1295
+ *         SparseNussinov::decode                          src/nussinov.cpp:207-392
+ *         SparseNeedlemanWunsch::initialize/decode        src/needleman_wunsch.cpp:198-422
+ *
+ * Plain C types only.  Every entry point returns 0 on success or a negative
+ * DAFS_CUDA_E* code; dafs_cuda_last_error() gives the message (thread-local).
+ * No exception crosses this boundary.  There is no CPU fallback: without a
+ * usable CUDA device every compute entry point fails with DAFS_CUDA_ENODEV.
+ */
+#ifndef DAFS_CUDA_H_
+#define DAFS_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DAFS_CUDA_OK 0
+#define DAFS_CUDA_EINVAL (-1)   /* bad argument                               */
+#define DAFS_CUDA_ENODEV (-2)   /* no CUDA device / device index out of range */
+#define DAFS_CUDA_ECUDA (-3)    /* CUDA runtime error                         */
+#define DAFS_CUDA_ENOMEM (-4)   /* host or device allocation failed           */
+#define DAFS_CUDA_ENOTSUP (-5)  /* not supported (like the reference's throws) */
+
+/* ---- lifecycle (no reference equivalent; errors there are C++ throws caught
+ *      in main, src/dafs.cpp:1898-1909) -------------------------------------- */
+int dafs_cuda_init(int ngpu /* 0 = all visible */);
+void dafs_cuda_shutdown(void);
+const char* dafs_cuda_last_error(void);
+int dafs_cuda_device_count(void);
+
+/* ---- sparse results ------------------------------------------------------
+ * A batch of row-sparse matrices, one per unit (a sequence pair for (1), a
+ * sequence for (2)), in the order the units were given.  It carries exactly
+ * what the reference keeps in MP / BP = vector<vector<pair<uint,float>>>
+ * (src/typedefs.h:39-41): for unit u and row r the kept entries are
+ *   k in [ row_ptr[row_off[u] + r], row_ptr[row_off[u] + r + 1] )  (+ nz_off[u])
+ * with col[] ascending inside a row (src/dafs.cpp:533-544 relies on that) and
+ * val[] strictly greater than the threshold.  All arrays are owned by the
+ * library (pinned host memory) until dafs_cuda_free_batch().                */
+typedef struct dafs_csr_batch {
+  int64_t n_units;
+  int64_t nnz;            /* total kept entries                                   */
+  const int64_t* row_off; /* [n_units+1] start of unit u's row_ptr block           */
+  const int32_t* row_ptr; /* per unit: rows+1 entries, relative to nz_off[u]       */
+  const int64_t* nz_off;  /* [n_units+1] start of unit u's entries in col/val      */
+  const uint32_t* col;    /* [nnz] 0-based column                                  */
+  const float* val;       /* [nnz]                                                 */
+  void* owner_;           /* private                                               */
+} dafs_csr_batch;
+
+void dafs_cuda_free_batch(dafs_csr_batch* b);
+
+/* ---- (1) pair-HMM posteriors ---------------------------------------------
+ * seq[i] are the raw sequence bytes (no terminator needed), len[i] >= 1.
+ * Alphabet handling equals the reference's (case-insensitive ACGUTN, anything
+ * else = its "unknown" emission, probconsRNA/wrapper.cpp:134-171).
+ * th is Align::Model::threshold() (-u, default 0.01).                       */
+
+/* All i<j pairs in row-major order: unit index = pair rank in
+ *   for i in [0,nseq) for j in (i,nseq)            (src/align.cpp:41-51).
+ * ngpu: 0/1 = current device only; k>1 = shard pairs over devices 0..k-1 of
+ * this process and merge on the host.                                       */
+int dafs_cuda_pairhmm_all(int nseq, const char* const* seq, const int* len, float th,
+                          int ngpu, dafs_csr_batch* out);
+
+/* An explicit list of (pi[k], pj[k]) pairs; rows come from seq[pi], columns
+ * from seq[pj].  This is what one rank calls when pairs are sharded across
+ * processes (one process per GPU).                                          */
+int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const int* len,
+                            int64_t npairs, const int32_t* pi, const int32_t* pj,
+                            float th, dafs_csr_batch* out);
+
+/* Split-phase form of the same call, for callers that keep inputs resident in
+ * HBM (and for timing the device part alone):
+ *   create  = encode + H2D of sequences and pair list, workspace allocation
+ *   run     = all kernels, asynchronous on the plan's stream; no host copies
+ *   sync    = wait; optionally reports the device time of the last run (ms,
+ *             CUDA events on the plan's stream)
+ *   fetch   = D2H of the CSR result into a batch (implies sync)
+ * A plan belongs to the device that was current at create.                  */
+typedef struct dafs_pairhmm_plan dafs_pairhmm_plan;
+int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, const int* len,
+                                  int64_t npairs, const int32_t* pi, const int32_t* pj,
+                                  float th, dafs_pairhmm_plan** plan);
+int dafs_cuda_pairhmm_plan_run(dafs_pairhmm_plan* plan);
+int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* plan, float* device_ms, int64_t* nnz);
+int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* plan, dafs_csr_batch* out);
+void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* plan);
+
+/* Log-space model tables the kernels use (3 init, 9 trans, 6 insert, 36 match;
+ * symbol classes A C G U/T N other) -- exported so tests can pin them against
+ * the reference's ProbabilisticModel constructor (ProbabilisticModel.h:55-88). */
+int dafs_cuda_pairhmm_tables(float* out54);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAFS_CUDA_H_ */

@@ -1,0 +1,186 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into, or called from, the product.
+//
+// C shim over the *unmodified* reference translation units of satoken/dafs,
+// compiled where they lie under /root/reference (see oracle/Makefile; output
+// goes to oracle/_ref/libdafs_ref.so).  It exposes, with plain pointers:
+//   * ProbCons::calculate                    (src/align.cpp:60-79)
+//   * calculate_similarity_score             (src/dafs.cpp:713-764, lifted)
+//   * SparseNussinov::decode  (both)         (src/nussinov.cpp:207-392)
+//   * SparseNeedlemanWunsch::initialize/decode (src/needleman_wunsch.cpp:198-422)
+//   * DAFS::solve_by_dd                      (src/dafs.cpp:1006-1295, lifted)
+// The two "lifted" pieces are cut out of dafs.cpp by the Makefile with awk at
+// build time into oracle/_ref/*.inc (dafs.cpp itself needs ViennaRNA, which is
+// not on this box) and #included below; no reference source is stored here.
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "align.h"
+#include "fold.h"
+#include "needleman_wunsch.h"
+#include "nussinov.h"
+#include "typedefs.h"
+
+// fold.cpp needs ViennaRNA, so the three statics it defines (fold.cpp:56-58)
+// are re-stated here for the linker.
+const uint Fold::Decoder::n_support_brackets = 4 + 26;
+const char* Fold::Decoder::left_brackets = "([{<ABCDEFGHIJKLMNOPQRSTUVWXYZ";
+const char* Fold::Decoder::right_brackets = ")]}>abcdefghijklmnopqrstuvwxyz";
+
+#define FOREACH(i, v) for (auto i = std::begin(v); i != std::end(v); ++i)
+#define CUTOFF 0.01
+#define SPARSE_UPDATE
+
+namespace spdlog {
+template <class... A> inline void debug(const char*, A&&...) {}
+template <class... A> inline void info(const char*, A&&...) {}
+}  // namespace spdlog
+
+namespace {
+int g_last_iters = 0;
+unsigned g_last_violated = 0;
+}
+
+// Stub with exactly the members DAFS::solve_by_dd touches (dafs.cpp:126-152).
+class DAFS {
+ public:
+  typedef std::pair<std::pair<uint, uint>, std::pair<uint, uint>> CBP;
+  uint t_max_;
+  float th_a_;
+  VF th_s_;
+  float w_;
+  float eta0_;
+  std::unique_ptr<Align::Decoder> a_decoder_;
+  std::unique_ptr<Fold::Decoder> s_decoder_;
+  uint verbose_ = 0;
+  void output_verbose(const VU&, const VU&, const VU&, const ALN&, const ALN&) const {}
+  float solve_by_dd(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z,
+                    const ALN& aln1, const ALN& aln2) const;
+};
+
+// The lifted body logs "Step: {}, Violated: {}" through spdlog::info at its
+// end; capture those two values for the trajectory tests.
+#define info(fmt, t, v) info_capture(t, v)
+namespace spdlog {
+inline void info_capture(uint t, uint v) { g_last_iters = (int)t; g_last_violated = v; }
+}
+#include "_ref/solve_by_dd.inc"
+#undef info
+
+#include "_ref/similarity.inc"
+
+static VVF to_vvf(const float* a, int r, int c) {
+  VVF m(r, VF(c));
+  for (int i = 0; i < r; ++i) std::copy(a + (size_t)i * c, a + (size_t)(i + 1) * c, m[i].begin());
+  return m;
+}
+
+extern "C" {
+
+// Dense L1 x L2 posterior (0-based, zero where not kept) exactly as
+// ProbCons::calculate would fill MP: entries strictly > th.
+int ref_probcons_pair(const char* s1, const char* s2, float th, float* dense, float* sim) {
+  static ProbCons* model = nullptr;
+  static float model_th = -1;
+  if (!model || model_th != th) { delete model; model = new ProbCons(th); model_th = th; }
+  std::string a(s1), b(s2);
+  MP mp;
+  model->calculate(a, b, mp);
+  const size_t L1 = a.size(), L2 = b.size();
+  int nnz = 0;
+  if (dense) std::fill(dense, dense + L1 * L2, 0.0f);
+  for (size_t i = 0; i < L1; ++i)
+    for (auto& e : mp[i]) { if (dense) dense[i * L2 + e.first] = e.second; ++nnz; }
+  if (sim) *sim = calculate_similarity_score(mp, L1, L2);
+  return nnz;
+}
+
+float ref_nussinov_dd(int L, float th, float w, const float* p, const float* q, unsigned* ss) {
+  SparseNussinov dec(th);
+  VU out;
+  float s = dec.decode(w, to_vvf(p, L, L), to_vvf(q, L, L), out);
+  std::copy(out.begin(), out.end(), ss);
+  return s;
+}
+
+float ref_nussinov_plain(int L, float th, const float* p, unsigned* ss) {
+  SparseNussinov dec(th);
+  VU out;
+  std::string str;
+  float s = dec.decode(to_vvf(p, L, L), out, str);
+  std::copy(out.begin(), out.end(), ss);
+  return s;
+}
+
+// q == NULL selects the plain overload (needleman_wunsch.cpp:340).
+float ref_nw(int L1, int L2, float th, const float* p, const float* q, unsigned* al) {
+  SparseNeedlemanWunsch dec(th);
+  VVF P = to_vvf(p, L1, L2);
+  dec.initialize(P);
+  VU out;
+  float s = q ? dec.decode(P, to_vvf(q, L1, L2), out) : dec.decode(P, out);
+  std::copy(out.begin(), out.end(), al);
+  return s;
+}
+
+float ref_dd_solve(int L1, int L2, int N1, int N2, const float* p_x, const float* p_y,
+                   const float* p_z, float w, float th_s, float th_a, float eta0, int t_max,
+                   unsigned* x, unsigned* y, unsigned* z, int* iters, unsigned* violated) {
+  DAFS d;
+  d.t_max_ = t_max; d.th_a_ = th_a; d.th_s_ = VF(1, th_s); d.w_ = w; d.eta0_ = eta0;
+  d.a_decoder_.reset(new SparseNeedlemanWunsch(th_a));
+  d.s_decoder_.reset(new SparseNussinov(th_s));
+  ALN a1(N1), a2(N2);
+  VU vx, vy, vz;
+  float s = d.solve_by_dd(vx, vy, vz, to_vvf(p_x, L1, L1), to_vvf(p_y, L2, L2),
+                          to_vvf(p_z, L1, L2), a1, a2);
+  std::copy(vx.begin(), vx.end(), x);
+  std::copy(vy.begin(), vy.end(), y);
+  std::copy(vz.begin(), vz.end(), z);
+  *iters = g_last_iters; *violated = g_last_violated;
+  return s;
+}
+
+}  // extern "C"
+
+// All-pairs fan-out over the reference's own ProbCons::calculate for the timed
+// CPU baseline ("kind": "reference").  The reference itself is single-threaded
+// (align.cpp:41-51); threads here only run independent pairs side by side, one
+// ProbCons object per thread.  first/count select a bounded sample of pairs in
+// row-major i<j order.
+#include <atomic>
+#include <thread>
+extern "C" int ref_probcons_all(int nseq, const char* const* seq, float th, long first,
+                                long count, int nthreads, int* nnz_out) {
+  std::vector<std::string> s(seq, seq + nseq);
+  std::atomic<long> next(0);
+  // ProbCons' constructor rewrites file-scope tables (wrapper.cpp:134-171), so
+  // the per-thread objects are built here, one after another, before any runs.
+  const int nt = nthreads < 1 ? 1 : nthreads;
+  std::vector<std::unique_ptr<ProbCons>> models;
+  for (int k = 0; k < nt; ++k) models.emplace_back(new ProbCons(th));
+  auto work = [&](int tid) {
+    ProbCons& model = *models[tid];
+    for (;;) {
+      long k = next.fetch_add(1);
+      if (k >= count) break;
+      long rem = first + k; int a = 0;
+      while (rem >= nseq - 1 - a) { rem -= nseq - 1 - a; a++; }
+      MP mp;
+      model.calculate(s[a], s[a + 1 + rem], mp);
+      int nnz = 0;
+      for (auto& r : mp) nnz += (int)r.size();
+      if (nnz_out) nnz_out[k] = nnz;
+    }
+  };
+  if (nt == 1) { work(0); return 0; }
+  std::vector<std::thread> th_;
+  for (int k = 0; k < nt; ++k) th_.emplace_back(work, k);
+  for (auto& t : th_) t.join();
+  return 0;
+}
