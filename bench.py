@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- pair-posteriors/sec of the all-pairs ProbCons pair-HMM stage on
+BASELINE.json's config C4 (synthetic random RNA, N=256, L=300, 32 640 pairs).
+
+  python bench.py --gpus N --steps K --warmup W          (ours; torchrun for N>1)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+                  (the reference's own ProbCons::calculate on the host cores)
+
+A "step" is one pass of the hot path over the whole pair list.  `value` is
+pairs/s with inputs resident in HBM (device time, CUDA events); `e2e` is the same
+metric through the C ABI with host buffers (H2D of the inputs, all kernels, the
+cross-rank NCCL all-gather of the CSR payload for N>1, D2H of the result)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NSEQ, LEN, CONFIG_ID, TH = 256, 300, 4, 0.01
+# Algorithmic FP32 work per DP cell (DESIGN.md "pair-HMM roofline"): one LSE =
+# 1 sub + 6 (cubic, unfused) + 1 add = 8; forward 4 LSE + 10 adds = 42; backward
+# 4 LSE + 12 adds = 44 (the reference's three other LOG_PLUS_EQUALS per cell hit
+# the LOG_ZERO shortcut and do no arithmetic); posterior 2 adds.
+FLOP_PER_CELL = 88
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12    # FMA peak at clocks.max.sm
+
+
+def workload():
+    import dafs_b200
+    seqs = dafs_b200.random_rna(NSEQ, LEN, config_id=CONFIG_ID)
+    pi, pj = dafs_b200.all_pairs(NSEQ)
+    return seqs, pi, pj
+
+
+def shard(npairs, rank, world):
+    """Pairs dealt round-robin to ranks: equal cell counts, no data-path collective."""
+    return np.arange(rank, npairs, world, dtype=np.int64)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(mx)) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the reference's own ProbCons::calculate (oracle/_ref, compiled from
+# /root/reference unmodified) or, if that library is absent, the C restatement.
+def cpu_engine():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_util as ou
+    import ctypes as C
+    if ou.have_ref():
+        L = ou.ref()
+
+        def run(seqs, first, count, threads):
+            arr = (C.c_char_p * len(seqs))(*seqs)
+            L.ref_probcons_all(len(seqs), arr, TH, first, count, threads, None)
+        return "reference", run
+    L = ou.oracle()
+
+    def run(seqs, first, count, threads):
+        arr = (C.c_char_p * len(seqs))(*seqs)
+        lens = (C.c_int * len(seqs))(*[len(s) for s in seqs])
+        L.oracle_pairhmm_all(len(seqs), arr, lens, TH, first, count, threads, None)
+    return "port", run
+
+
+def time_cpu(seqs, npairs, target_s, steps=1, warmup=0):
+    """pairs/s of the CPU arm on a bounded sample of the same pair list."""
+    kind, run = cpu_engine()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    probe = max(cores * 2, 8)
+    t0 = time.perf_counter(); run(seqs, 0, probe, cores); t_probe = time.perf_counter() - t0
+    rate = probe / max(t_probe, 1e-6)
+    count = int(min(npairs, max(probe, rate * target_s)))
+    for _ in range(warmup):
+        run(seqs, 0, min(count, probe), cores)
+    times = []
+    for k in range(steps):
+        first = (k * count) % max(1, npairs - count + 1)
+        t0 = time.perf_counter(); run(seqs, first, count, cores); times.append(time.perf_counter() - t0)
+    dt = sum(times) / len(times)
+    return {"value": count / dt, "unit": "pairs/s", "cores": cores, "kind": kind,
+            "sample": "%d of %d pairs of the same N=%d L=%d list per step, %d host threads" % (count, npairs, NSEQ, LEN, cores)}, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    seqs, pi, pj = workload()
+    per_step = max(5.0, min(30.0, 150.0 / max(1, args.steps + args.warmup)))
+    cb, dt = time_cpu(seqs, len(pi), per_step, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": "pair-posteriors/sec", "value": cb["value"], "unit": "pairs/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config_dict(args.gpus),
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def config_dict(ngpu):
+    return {"workload": "C4: synthetic random RNA N=%d L=%d, all %d i<j pairs, ProbCons pair-HMM posteriors th=%g" % (
+                NSEQ, LEN, NSEQ * (NSEQ - 1) // 2, TH),
+            "nseq": NSEQ, "seq_len": LEN, "pairs": NSEQ * (NSEQ - 1) // 2, "threshold": TH,
+            "parallelism": "pairs sharded round-robin over %d GPU(s), no data-path collective; CSR all-gather only in e2e" % ngpu,
+            "l2": "per-step working set (per-warp F_M planes, ~0.9 GB) exceeds the 126 MB L2; no flush needed"}
+
+
+# ---------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import dafs_b200
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libdafs_cuda has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    seqs, pi, pj = workload()
+    mine = shard(len(pi), rank, world)
+    mpi, mpj = pi[mine], pj[mine]
+    K, W = args.steps, max(args.warmup, 3)
+
+    # ---- value: inputs resident in HBM, device time --------------------------
+    plan = dafs_b200.PairHmmPlan(seqs, mpi, mpj, TH)
+    for _ in range(W):
+        plan.run(); plan.sync()
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    dev_ms, kern_ms = [], []
+    t0 = time.perf_counter()
+    for _ in range(K):
+        plan.run()
+        ms, nnz = plan.sync()
+        dev_ms.append(ms); kern_ms.append(plan.info()["last_kernel_ms"])
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3 / K
+    clocks = sampler.stop()
+    info = plan.info()
+    step_ms = max_over_ranks(sum(dev_ms) / K)
+    kernel_ms = sum(kern_ms) / K
+    nnz_total = nnz
+    if world > 1:
+        t = torch.tensor([nnz], dtype=torch.int64, device=dev); dist.all_reduce(t); nnz_total = int(t.item())
+    plan.close()
+
+    # ---- e2e: host buffers in, host CSR out on rank 0 --------------------------
+    h2d = NSEQ * LEN + 8 * (NSEQ + 1) + 4 * NSEQ + (8 + 4 + 8) * len(mine) + 8
+    e2e_times, d2h = [], 0
+    pinned = {}
+    for it in range(W + K):
+        barrier()
+        t0 = time.perf_counter()
+        p2 = dafs_b200.PairHmmPlan(seqs, mpi, mpj, TH)       # encode + H2D + workspace
+        p2.run()
+        if world == 1:
+            with p2.fetch() as b:                              # D2H into pinned host memory
+                d2h = b.row_ptr.nbytes + b.nz_off.nbytes + b.col.nbytes + b.val.nbytes
+                checksum = int(b.nnz)
+        else:
+            _, n_mine = p2.sync()
+            rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
+            sizes = torch.tensor([n_mine, rows_mine, len(mine)], dtype=torch.int64, device=dev)
+            all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(all_sizes, sizes)
+            mx = all_sizes.view(world, 3).max(dim=0).values.tolist()
+            col = torch.empty(mx[0], dtype=torch.int32, device=dev)
+            val = torch.empty(mx[0], dtype=torch.float32, device=dev)
+            rp = torch.empty(mx[1], dtype=torch.int32, device=dev)
+            nzo = torch.empty(mx[2] + 1, dtype=torch.int64, device=dev)
+            p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), mx[0])
+            g = [torch.empty(world * x.numel(), dtype=x.dtype, device=dev) for x in (col, val, rp, nzo)]
+            for dst, src in zip(g, (col, val, rp, nzo)):
+                dist.all_gather_into_tensor(dst, src)          # NCCL over NVLink
+            if rank == 0:
+                d2h = 0
+                for k, x in enumerate(g):
+                    if k not in pinned or pinned[k].numel() < x.numel():
+                        pinned[k] = torch.empty(x.numel(), dtype=x.dtype, pin_memory=True)
+                    pinned[k][:x.numel()].copy_(x, non_blocking=True)
+                    d2h += x.numel() * x.element_size()
+                torch.cuda.synchronize()
+                checksum = int(all_sizes.view(world, 3)[:, 0].sum().item())
+        p2.close()
+        barrier()
+        if it >= W:
+            e2e_times.append(time.perf_counter() - t0)
+    e2e_s = max_over_ranks(sum(e2e_times) / len(e2e_times))
+    d2h_max = int(max_over_ranks(float(d2h)))
+
+    if rank == 0:
+        npairs = len(pi)
+        cells = (LEN + 1) * (LEN + 1)
+        flop_launch = len(mine) * cells * FLOP_PER_CELL
+        achieved = flop_launch / (kernel_ms * 1e-3) / 1e12
+        peaks = measured_peaks()
+        alg_bytes = len(mine) * (2 * LEN + 4 * (LEN + 1)) + 8 * (nnz_total // world)
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "pairhmm_traffic.json"))).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        line = {
+            "metric": "pair-posteriors/sec", "value": npairs / (step_ms * 1e-3), "unit": "pairs/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms, "wall_ms_per_step": wall_ms,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config_dict(world), "clocks": clocks,
+            "e2e": {"value": npairs / e2e_s, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": d2h_max, "ms_per_step": e2e_s * 1e3},
+            "gpu_launches": info["launches_per_run"] * K,
+            "nnz": nnz_total,
+            "kernel": {"name": "pairhmm_kernel<C=%d>" % info["cols_per_lane"], "grid": info["grid"],
+                       "block": info["warps_per_cta"] * 32, "avg_ms": kernel_ms,
+                       "workspace_bytes": info["workspace_bytes"]},
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": FP32_NOMINAL_TFLOPS, "unit": "TFLOP/s",
+                         "frac": achieved / FP32_NOMINAL_TFLOPS, "traffic": traffic,
+                         "note": "FP32 CUDA-core bound (no tensor-core or HBM roofline applies); peak = nominal FMA "
+                                 "peak 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry); "
+                                 "bit-exact parity forbids FMA, so the reachable ceiling is peak/2; "
+                                 "achieved = %d algorithmic flop/cell x cells per launch / kernel time" % FLOP_PER_CELL},
+            "roofline_hbm": {"bound": "hbm", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
+                             "peak": (peaks or {}).get("hbm_gbs", 6650.0), "unit": "GB/s",
+                             "peak_source": "measured" if peaks else "fallback",
+                             "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / (peaks or {}).get("hbm_gbs", 6650.0),
+                             "traffic": traffic},
+        }
+        if world == 1 and not args.no_cpu:
+            cb, _ = time_cpu(seqs, npairs, 12.0)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

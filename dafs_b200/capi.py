@@ -30,6 +30,12 @@ class _CsrBatch(C.Structure):
     ]
 
 
+class _PairHmmInfo(C.Structure):
+    _fields_ = [("cols_per_lane", C.c_int), ("grid", C.c_int), ("warps_per_cta", C.c_int),
+                ("launches_per_run", C.c_int), ("workspace_bytes", C.c_int64),
+                ("last_total_ms", C.c_float), ("last_kernel_ms", C.c_float)]
+
+
 _lib = None
 
 
@@ -51,6 +57,9 @@ def lib():
         L.dafs_cuda_pairhmm_plan_sync.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64)]
         L.dafs_cuda_pairhmm_plan_fetch.argtypes = [C.c_void_p, C.POINTER(_CsrBatch)]
         L.dafs_cuda_pairhmm_plan_destroy.argtypes = [C.c_void_p]
+        L.dafs_cuda_pairhmm_plan_export.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_int64]
+        L.dafs_cuda_pairhmm_plan_info.argtypes = [C.c_void_p, C.POINTER(_PairHmmInfo)]
         L.dafs_cuda_pairhmm_plan_destroy.restype = None
         L.dafs_cuda_pairhmm_pairs.argtypes = [
             C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_int64,
@@ -189,6 +198,16 @@ class PairHmmPlan:
         nnz = C.c_int64()
         _check(lib().dafs_cuda_pairhmm_plan_sync(self._h, C.byref(ms), C.byref(nnz)))
         return float(ms.value), int(nnz.value)
+
+    def info(self):
+        i = _PairHmmInfo()
+        _check(lib().dafs_cuda_pairhmm_plan_info(self._h, C.byref(i)))
+        return {k: getattr(i, k) for k, _ in _PairHmmInfo._fields_}
+
+    def export(self, d_row_ptr, d_nz_off, d_col, d_val, cap_nnz):
+        """Raw device pointers (ints) of caller-owned buffers on this plan's device."""
+        _check(lib().dafs_cuda_pairhmm_plan_export(self._h, d_row_ptr, d_nz_off, d_col, d_val,
+                                                   int(cap_nnz)))
 
     def fetch(self):
         raw = _CsrBatch()

@@ -104,7 +104,7 @@ __global__ void gather_csr_kernel(int npairs, const int64_t* __restrict__ pool_o
 struct dafs_pairhmm_plan {
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
   int nseq = 0, npairs = 0;
   float th = 0, xcut = 0;
   int C = 0, grid = 0;
@@ -122,7 +122,7 @@ struct dafs_pairhmm_plan {
   int64_t* d_nz_off = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
   bool launched = false;
   int64_t nnz = -1;
-  float last_ms = 0;
+  float last_ms = 0, last_kernel_ms = 0;
 };
 
 namespace dafs {
@@ -139,6 +139,8 @@ static void free_plan_buffers(dafs_pairhmm_plan* p) {
   cudaFree(p->d_col); cudaFree(p->d_val);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
+  if (p->evk0) cudaEventDestroy(p->evk0);
+  if (p->evk1) cudaEventDestroy(p->evk1);
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 
@@ -188,6 +190,7 @@ static int launch_all(dafs_pairhmm_plan* p) {
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_pool_count, 0, sizeof(unsigned long long), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
+  DAFS_CUDA_TRY(cudaEventRecord(p->evk0, p->stream));
   cudaError_t e;
   switch (p->C) {
     case 2: e = launch_pairhmm<2>(a, p->grid, p->stream); break;
@@ -200,6 +203,7 @@ static int launch_all(dafs_pairhmm_plan* p) {
     default: e = launch_pairhmm<12>(a, p->grid, p->stream); break;
   }
   DAFS_CUDA_TRY(e);
+  DAFS_CUDA_TRY(cudaEventRecord(p->evk1, p->stream));
   scan_nnz_kernel<<<1, 1024, 0, p->stream>>>(p->d_pair_nnz, p->npairs, p->d_nz_off);
   DAFS_CUDA_TRY(cudaGetLastError());
   const int gblocks = std::min(p->npairs / 8 + 1, 148 * 8);
@@ -257,6 +261,8 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
   PLAN_TRY(cudaEventCreate(&p->ev0));
   PLAN_TRY(cudaEventCreate(&p->ev1));
+  PLAN_TRY(cudaEventCreate(&p->evk0));
+  PLAN_TRY(cudaEventCreate(&p->evk1));
   static bool tables_up[64] = {false};
   if (!tables_up[p->device & 63]) {
     PLAN_TRY(cudaMemcpyToSymbol(c_tab, &host_tables(), sizeof(PairHmmTables)));
@@ -352,9 +358,19 @@ extern "C" int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* p, float* device_m
       if (rc2) return rc2;
     }
     DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_kernel_ms, p->evk0, p->evk1));
   }
   if (device_ms) *device_ms = p->last_ms;
   if (nnz) *nnz = p->nnz;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* p, dafs_pairhmm_info* info) {
+  if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  info->cols_per_lane = p->C; info->grid = p->grid; info->warps_per_cta = dafs::kWarps;
+  info->workspace_bytes = (int64_t)sizeof(float) * p->plane_stride * p->grid * dafs::kWarps;
+  info->last_total_ms = p->last_ms; info->last_kernel_ms = p->last_kernel_ms;
+  info->launches_per_run = 3;
   return DAFS_CUDA_OK;
 }
 
@@ -394,6 +410,24 @@ extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch
   out->n_units = np; out->nnz = nnz;
   out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
   out->col = h_col; out->val = h_val; out->owner_ = base;
+  return DAFS_CUDA_OK;
+}
+
+// Device-to-device copy of the pair-ordered CSR into caller-owned device
+// buffers (e.g. tensors of the process that will run an NCCL all-gather on them).
+extern "C" int dafs_cuda_pairhmm_plan_export(dafs_pairhmm_plan* p, int32_t* d_row_ptr,
+                                             int64_t* d_nz_off, uint32_t* d_col, float* d_val,
+                                             int64_t cap_nnz) {
+  if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+  if (rc) return rc;
+  if (p->nnz > cap_nnz) return fail(DAFS_CUDA_EINVAL, "export buffers hold %lld entries, result has %lld", (long long)cap_nnz, (long long)p->nnz);
+  if (p->npairs == 0) return DAFS_CUDA_OK;
+  if (d_row_ptr) DAFS_CUDA_TRY(cudaMemcpyAsync(d_row_ptr, p->d_row_ptr, sizeof(int32_t) * p->total_rows, cudaMemcpyDeviceToDevice, p->stream));
+  if (d_nz_off) DAFS_CUDA_TRY(cudaMemcpyAsync(d_nz_off, p->d_nz_off, sizeof(int64_t) * (p->npairs + 1), cudaMemcpyDeviceToDevice, p->stream));
+  if (d_col && p->nnz) DAFS_CUDA_TRY(cudaMemcpyAsync(d_col, p->d_col, sizeof(uint32_t) * p->nnz, cudaMemcpyDeviceToDevice, p->stream));
+  if (d_val && p->nnz) DAFS_CUDA_TRY(cudaMemcpyAsync(d_val, p->d_val, sizeof(float) * p->nnz, cudaMemcpyDeviceToDevice, p->stream));
+  DAFS_CUDA_TRY(cudaStreamSynchronize(p->stream));
   return DAFS_CUDA_OK;
 }
 

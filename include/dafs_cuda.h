@@ -100,6 +100,26 @@ int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* plan, float* device_ms, int64
 int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* plan, dafs_csr_batch* out);
 void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* plan);
 
+/* Device-resident hand-over: copies the pair-ordered CSR (row_ptr blocks,
+ * nz_off[npairs+1], col, val) into caller-owned DEVICE buffers, e.g. the
+ * tensors a rank feeds to an NCCL all-gather.  cap_nnz = capacity of d_col/d_val
+ * in entries; any pointer may be NULL to skip that array.  Implies sync.     */
+int dafs_cuda_pairhmm_plan_export(dafs_pairhmm_plan* plan, int32_t* d_row_ptr,
+                                  int64_t* d_nz_off, uint32_t* d_col, float* d_val,
+                                  int64_t cap_nnz);
+
+/* Geometry and timings of a plan (for benchmarks and profiles). */
+typedef struct dafs_pairhmm_info {
+  int cols_per_lane;        /* C: DP columns each lane keeps in registers          */
+  int grid;                 /* persistent CTAs                                     */
+  int warps_per_cta;
+  int launches_per_run;     /* kernels one run() launches                          */
+  int64_t workspace_bytes;  /* per-warp F_M planes in HBM                          */
+  float last_total_ms;      /* device time of the last run, all kernels            */
+  float last_kernel_ms;     /* ... of the forward/backward/posterior kernel alone  */
+} dafs_pairhmm_info;
+int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* plan, dafs_pairhmm_info* info);
+
 /* Log-space model tables the kernels use (3 init, 9 trans, 6 insert, 36 match;
  * symbol classes A C G U/T N other) -- exported so tests can pin them against
  * the reference's ProbabilisticModel constructor (ProbabilisticModel.h:55-88). */
