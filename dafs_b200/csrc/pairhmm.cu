@@ -310,7 +310,7 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * std::max(nseq, 1)));
   PLAN_TRY(cudaMalloc(&p->d_pairs, sizeof(int2) * pairs.size()));
   PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * order.size()));
-  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * p->plane_stride * slots));
+  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * 2 * p->plane_stride * slots));
   PLAN_TRY(cudaMalloc(&p->d_bnd, sizeof(float4) * p->bnd_stride * 2 * slots));
   PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
   PLAN_TRY(cudaMalloc(&p->d_pool_count, sizeof(unsigned long long)));
@@ -368,7 +368,7 @@ extern "C" int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* p, float* device_m
 extern "C" int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* p, dafs_pairhmm_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   info->cols_per_lane = p->C; info->grid = p->grid; info->warps_per_cta = dafs::kWarps;
-  info->workspace_bytes = (int64_t)sizeof(float) * p->plane_stride * p->grid * dafs::kWarps;
+  info->workspace_bytes = (int64_t)sizeof(float) * 2 * p->plane_stride * p->grid * dafs::kWarps;
   info->last_total_ms = p->last_ms; info->last_kernel_ms = p->last_kernel_ms;
   info->launches_per_run = 3;
   return DAFS_CUDA_OK;

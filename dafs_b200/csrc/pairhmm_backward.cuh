@@ -1,5 +1,5 @@
-// Backward sweep of one column stripe (ProbabilisticModel.h:197-259), fused with
-// S = F_M + B_M (the argument of the posterior, :393-398) written over F_M.
+// Backward sweep of one column stripe (ProbabilisticModel.h:197-259); B_M goes to
+// its own plane so the DP loop issues no global loads.
 // Mirror image of forward_stripe: lane 31 starts, rows run L1..0, each lane walks
 // its columns right to left and hands its first column to lane t-1.
 #pragma once
@@ -51,7 +51,7 @@ __device__ __forceinline__ void backward_stripe(
     const float* mrow = sm.match + cls1 * 8 * 32;
     float rightY = rY;                               // B_Y(i, j+1)
     float gM = dM;                                   // B_M(i+1, j+1)
-    float* prow = plane + (int64_t)i * PW + j0;
+    float* prow = plane + (int64_t)i * PW + j0;            // B_M plane
     const int seed = (i == L1) ? (L2 - j0) : -1;     // column slot of cell (L1, L2)
 #pragma unroll
     for (int c = C - 1; c >= 0; --c) {
@@ -61,14 +61,14 @@ __device__ __forceinline__ void backward_stripe(
       const float bxi = __fadd_rn(pX[c], insRow);
       // :244-249
       const float byi = __fadd_rn(rightY, sc.ins[c]);
-      float nM = pairhmm_lse(pairhmm_lse(__fadd_rn(pxy, T00), __fadd_rn(bxi, T01)), __fadd_rn(byi, T02));
-      float nX = pairhmm_lse(__fadd_rn(pxy, T10), __fadd_rn(bxi, T11));
-      float nY = pairhmm_lse(__fadd_rn(pxy, T20), __fadd_rn(byi, T22));
+      float nM = pairhmm_lse(sm.lut, pairhmm_lse(sm.lut, __fadd_rn(pxy, T00), __fadd_rn(bxi, T01)), __fadd_rn(byi, T02));
+      float nX = pairhmm_lse(sm.lut, __fadd_rn(pxy, T10), __fadd_rn(bxi, T11));
+      float nY = pairhmm_lse(sm.lut, __fadd_rn(pxy, T20), __fadd_rn(byi, T22));
       if (c == seed) { nM = c_tab.init[0]; nX = c_tab.init[1]; nY = c_tab.init[2]; }   // :213-214
       gM = pM[c];
       pM[c] = nM; pX[c] = nX; pY[c] = nY;
       rightY = nY;
-      prow[c] = __fadd_rn(prow[c], nM);              // forward[ij] + backward[ij], :396
+      prow[c] = nM;
     }
     dM = rM;
     oM = pM[0]; oY = pY[0];

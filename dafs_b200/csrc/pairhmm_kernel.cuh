@@ -38,8 +38,8 @@ struct PairHmmArgs {
   int npairs;
   float th;                  // keep p > th
   float xcut;                // cells with F+B-total <= xcut cannot exceed th
-  float* planes;             // per-warp-slot F_M / F_M+B_M plane
-  int64_t plane_stride;      // floats per slot
+  float* planes;             // per-warp-slot planes: F_M then B_M
+  int64_t plane_stride;      // floats per plane (a slot holds two)
   float4* bnd;               // per-warp-slot stripe-boundary columns (2 buffers)
   int64_t bnd_stride;        // float4 per buffer
   int* queue;                // work counter
@@ -60,6 +60,7 @@ __constant__ PairHmmTables c_tab;
 // Per-block shared tables, replicated once per lane (index*32 + lane) so that a
 // warp whose lanes look up different symbols never has a bank conflict.
 struct PairHmmSmem {
+  float4 lut[4];            // LOOKUP coefficient rows {c3,c2,c1,c0}
   float match[64 * 32];
   float ins[8 * 32];
 };
@@ -113,12 +114,12 @@ __device__ __forceinline__ void forward_stripe(
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       // ProbabilisticModel.h:151-156
-      float nM = pairhmm_lse(pairhmm_lse(__fadd_rn(gM, T00), __fadd_rn(gX, T10)), __fadd_rn(gY, T20));
+      float nM = pairhmm_lse(sm.lut, pairhmm_lse(sm.lut, __fadd_rn(gM, T00), __fadd_rn(gX, T10)), __fadd_rn(gY, T20));
       nM = __fadd_rn(nM, mrow[sc.mofs[c]]);
       // :157-162
-      float nX = __fadd_rn(insRow, pairhmm_lse(__fadd_rn(pM[c], T01), __fadd_rn(pX[c], T11)));
+      float nX = __fadd_rn(insRow, pairhmm_lse(sm.lut, __fadd_rn(pM[c], T01), __fadd_rn(pX[c], T11)));
       // :163-168
-      float nY = __fadd_rn(sc.ins[c], pairhmm_lse(__fadd_rn(leftM, T02), __fadd_rn(leftY, T22)));
+      float nY = __fadd_rn(sc.ins[c], pairhmm_lse(sm.lut, __fadd_rn(leftM, T02), __fadd_rn(leftY, T22)));
       if (c < 2 && origin && i <= 1) {
         // seeds, ProbabilisticModel.h:123-131; (0,0) and the other states stay LOG_ZERO (:150)
         nM = (i == 1 && c == 1) ? __fadd_rn(c_tab.init[0], mrow[sc.mofs[1]]) : DAFS_LOG_ZERO;

@@ -12,16 +12,22 @@ namespace dafs {
 #define DAFS_LOG_ZERO (-2e20f)
 
 // LOOKUP(d) = log(1 + e^-d)-ish on [0, 7.5): four cubic pieces, Horner form,
-// float literals (ScoreType.h:187-198).
-__device__ __forceinline__ float pairhmm_lookup(float d) {
-  const bool p1 = d <= 1.00f, p2 = d <= 2.50f, p3 = d <= 4.50f;
-  const float c3 = p1 ? -0.009350833524763f : p2 ? -0.014532321752540f : p3 ? -0.004605031767994f : -0.000458661602210f;
-  const float c2 = p1 ? 0.130659527668286f : p2 ? 0.139942324101744f : p3 ? 0.063427417320019f : 0.009695946122598f;
-  const float c1 = p1 ? 0.498799810682272f : p2 ? 0.495635523139337f : p3 ? 0.695956496475118f : 0.930734667215156f;
-  const float c0 = p1 ? 0.693203116424741f : p2 ? 0.692140569840976f : p3 ? 0.514272634594009f : 0.168037164329057f;
-  float r = __fadd_rn(__fmul_rn(c3, d), c2);
-  r = __fadd_rn(__fmul_rn(r, d), c1);
-  r = __fadd_rn(__fmul_rn(r, d), c0);
+// float literals (ScoreType.h:187-198).  The four coefficient rows live in
+// shared memory as float4 {c3,c2,c1,c0}; a lane picks its row with three
+// compares and fetches it with one LDS.128 (rows sit in disjoint banks, equal
+// rows broadcast: conflict-free) instead of twelve register selects.
+#define DAFS_LOOKUP_ROWS                                                                   \
+  {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f},      \
+  {-0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f},      \
+  {-0.004605031767994f, 0.063427417320019f, 0.695956496475118f, 0.514272634594009f},      \
+  {-0.000458661602210f, 0.009695946122598f, 0.930734667215156f, 0.168037164329057f}
+
+__device__ __forceinline__ float pairhmm_lookup(const float4* __restrict__ tab, float d) {
+  const int row = (d > 4.50f) ? 3 : (d > 2.50f) ? 2 : (d > 1.00f) ? 1 : 0;
+  const float4 k = tab[row];
+  float r = __fadd_rn(__fmul_rn(k.x, d), k.y);
+  r = __fadd_rn(__fmul_rn(r, d), k.z);
+  r = __fadd_rn(__fmul_rn(r, d), k.w);
   return r;
 }
 
@@ -31,10 +37,10 @@ __device__ __forceinline__ float pairhmm_lookup(float d) {
 // or hi == LOG_ZERO too (then LOOKUP(0)+LOG_ZERO rounds to LOG_ZERO, the same
 // answer).  The same holds for the even more negative values that padded DP
 // cells carry, so "zero" never leaks into a finite cell.
-__device__ __forceinline__ float pairhmm_lse(float x, float y) {
+__device__ __forceinline__ float pairhmm_lse(const float4* __restrict__ tab, float x, float y) {
   const float hi = fmaxf(x, y), lo = fminf(x, y);
   const float d = __fsub_rn(hi, lo);
-  const float r = __fadd_rn(pairhmm_lookup(d), lo);
+  const float r = __fadd_rn(pairhmm_lookup(tab, d), lo);
   return d >= 7.5f ? hi : r;
 }
 
