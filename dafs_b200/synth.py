@@ -56,3 +56,49 @@ def fasta_read(path):
             elif line and seqs:
                 seqs[-1] += line
     return names, [s.encode("ascii") for s in seqs]
+
+
+def synthetic_bpp(length, family_seed=0, member=0, noise=0.5):
+    """A base-pairing-probability-like matrix (dense float32 L x L, only i<j set,
+    every kept value > 0.01 like RNAfold::calculate leaves them, fold.cpp:108-114)
+    for tests and benchmarks of the DD stage: stems shared by a family plus
+    member-specific jitter and low-probability noise pairs.  Stand-in for real
+    McCaskill output wherever a test wants many problems cheaply."""
+    L = int(length)
+    p = np.zeros((L, L), np.float32)
+    if L < 8:
+        return p
+    fam = splitmix64(0xB99000 + 7919 * family_seed, 4 * (L // 8 + 2))
+    mem = splitmix64(0xB99000 + 7919 * family_seed + 104729 * (member + 1), 8 * L)
+    u = lambda r: float(r >> np.uint64(11)) / float(1 << 53)   # noqa: E731
+    rowsum = np.zeros(L)
+    m = 0
+    for s in range(L // 8 + 1):
+        a = int(fam[4 * s] % np.uint64(L))
+        span = 5 + int(fam[4 * s + 1] % np.uint64(max(1, L - 5)))
+        b = a + span
+        n = 3 + int(fam[4 * s + 2] % np.uint64(6))
+        base = 0.15 + 0.8 * u(fam[4 * s + 3])
+        if u(mem[m]) < 0.15:      # this member lost the stem
+            m += 1
+            continue
+        m += 1
+        for t in range(n):
+            i, j = a + t, b - t
+            if j >= L or j - i < 4:
+                break
+            v = base * (0.6 + 0.4 * u(mem[m % len(mem)])); m += 1
+            v = min(v, 1.0 - rowsum[i], 1.0 - rowsum[j])
+            if v > 0.011 and p[i, j] == 0:
+                p[i, j] = np.float32(v); rowsum[i] += v; rowsum[j] += v
+    nn = int(noise * L)
+    for t in range(nn):
+        i = int(mem[m % len(mem)] % np.uint64(L)); m += 1
+        j = i + 4 + int(mem[m % len(mem)] % np.uint64(L)); m += 1
+        if j >= L or p[i, j] != 0:
+            continue
+        v = 0.011 + 0.3 * u(mem[m % len(mem)]) ** 2; m += 1
+        v = min(v, 1.0 - rowsum[i], 1.0 - rowsum[j])
+        if v > 0.011:
+            p[i, j] = np.float32(v); rowsum[i] += v; rowsum[j] += v
+    return p

@@ -74,3 +74,124 @@ def ref_pair_dense(s1, s2, th=0.01):
     sim = C.c_float()
     ref().ref_probcons_pair(s1, s2, th, d.ctypes.data, C.addressof(sim))
     return d, float(sim.value)
+
+
+# ---- dual decomposition: decoders and solve_by_dd -----------------------------
+NOPAIR = 0xFFFFFFFF
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+
+
+def oracle_nussinov(p, q=None, th=0.2, w=1.0):
+    """SparseNussinov::decode restated (q None = the plain overload)."""
+    L = oracle()
+    L.oracle_nussinov.restype = C.c_float
+    L.oracle_nussinov.argtypes = [C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    p = _f32(p); q = None if q is None else _f32(q)
+    ss = np.zeros(p.shape[0], np.uint32)
+    s = L.oracle_nussinov(p.shape[0], th, w, _fp(p), _fp(q), _fp(ss))
+    return np.float32(s), ss
+
+
+def ref_nussinov(p, q=None, th=0.2, w=1.0):
+    L = ref()
+    p = _f32(p); ss = np.zeros(p.shape[0], np.uint32)
+    if q is None:
+        L.ref_nussinov_plain.restype = C.c_float
+        L.ref_nussinov_plain.argtypes = [C.c_int, C.c_float, C.c_void_p, C.c_void_p]
+        s = L.ref_nussinov_plain(p.shape[0], th, _fp(p), _fp(ss))
+    else:
+        q = _f32(q)
+        L.ref_nussinov_dd.restype = C.c_float
+        L.ref_nussinov_dd.argtypes = [C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        s = L.ref_nussinov_dd(p.shape[0], th, w, _fp(p), _fp(q), _fp(ss))
+    return np.float32(s), ss
+
+
+def oracle_nw(p, q=None, th=0.01):
+    """initialize + decode; returns (score, al, env[(L1+1),2], bad)."""
+    L = oracle()
+    L.oracle_nw_envelope.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
+    L.oracle_nw_decode.restype = C.c_float
+    L.oracle_nw_decode.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.POINTER(C.c_int)]
+    p = _f32(p); q = None if q is None else _f32(q)
+    L1, L2 = p.shape
+    env = np.zeros((L1 + 1, 2), np.uint32)
+    L.oracle_nw_envelope(L1, L2, th, _fp(p), _fp(env))
+    al = np.zeros(L1, np.uint32)
+    bad = C.c_int(0)
+    s = L.oracle_nw_decode(L1, L2, th, _fp(p), _fp(q), _fp(env), _fp(al), C.byref(bad))
+    return np.float32(s), al, env, bad.value
+
+
+def ref_nw(p, q=None, th=0.01):
+    L = ref()
+    L.ref_nw.restype = C.c_float
+    L.ref_nw.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    p = _f32(p); q = None if q is None else _f32(q)
+    al = np.zeros(p.shape[0], np.uint32)
+    s = L.ref_nw(p.shape[0], p.shape[1], th, _fp(p), _fp(q), _fp(al))
+    return np.float32(s), al
+
+
+def oracle_dd(p_x, p_y, p_z, n1=1, n2=1, w=4.0, th_s=0.2, th_a=0.01, eta0=0.5, t_max=600,
+              min_th_s=None, trace=False):
+    L = oracle()
+    L.oracle_dd_solve.restype = C.c_float
+    L.oracle_dd_solve.argtypes = [C.c_int] * 4 + [C.c_void_p] * 3 + [C.c_float] * 5 + [C.c_int] + \
+        [C.c_void_p] * 3 + [C.POINTER(C.c_int), C.POINTER(C.c_uint), C.POINTER(C.c_int64), C.c_void_p, C.c_int]
+    p_x, p_y, p_z = _f32(p_x), _f32(p_y), _f32(p_z)
+    L1, L2 = p_z.shape
+    x = np.zeros(L1, np.uint32); y = np.zeros(L2, np.uint32); z = np.zeros(L1, np.uint32)
+    it, vi, nc = C.c_int(0), C.c_uint(0), C.c_int64(0)
+    tr = np.zeros((max(t_max, 1), 3), np.float32) if trace else None
+    s = L.oracle_dd_solve(L1, L2, n1, n2, _fp(p_x), _fp(p_y), _fp(p_z), w, th_s,
+                          th_s if min_th_s is None else min_th_s, th_a, eta0, t_max,
+                          _fp(x), _fp(y), _fp(z), C.byref(it), C.byref(vi), C.byref(nc),
+                          _fp(tr), max(t_max, 1) if trace else 0)
+    out = {"score": np.float32(s), "x": x, "y": y, "z": z, "iters": it.value, "violated": vi.value,
+           "ncbp": nc.value}
+    if trace:
+        out["trace"] = tr[:min(it.value + 1, t_max)]
+    return out
+
+
+def ref_dd(p_x, p_y, p_z, n1=1, n2=1, w=4.0, th_s=0.2, th_a=0.01, eta0=0.5, t_max=600):
+    L = ref()
+    L.ref_dd_solve.restype = C.c_float
+    L.ref_dd_solve.argtypes = [C.c_int] * 4 + [C.c_void_p] * 3 + [C.c_float] * 4 + [C.c_int] + \
+        [C.c_void_p] * 3 + [C.POINTER(C.c_int), C.POINTER(C.c_uint)]
+    p_x, p_y, p_z = _f32(p_x), _f32(p_y), _f32(p_z)
+    L1, L2 = p_z.shape
+    x = np.zeros(L1, np.uint32); y = np.zeros(L2, np.uint32); z = np.zeros(L1, np.uint32)
+    it, vi = C.c_int(0), C.c_uint(0)
+    s = L.ref_dd_solve(L1, L2, n1, n2, _fp(p_x), _fp(p_y), _fp(p_z), w, th_s, th_a, eta0, t_max,
+                       _fp(x), _fp(y), _fp(z), C.byref(it), C.byref(vi))
+    return {"score": np.float32(s), "x": x, "y": y, "z": z, "iters": it.value, "violated": vi.value}
+
+
+def dd_problem(length, family=0, a=0, b=1, l2=None, mutation=0.2, th=0.01, mix=False):
+    """One 2-leaf DD problem as align_alignments builds it (dafs.cpp:913-940) with
+    PCT and alifold off: p_x, p_y = BPP of the two sequences (synthetic_bpp), p_z =
+    their ProbCons posterior (restated oracle), all dense."""
+    from dafs_b200.synth import homolog_family, synthetic_bpp
+    seqs = homolog_family(max(a, b) + 1, length, config_id=70 + family, mutation=mutation)
+    sa, sb = seqs[a], seqs[b]
+    if l2 is not None:
+        sb = sb[:l2]
+    p_x = synthetic_bpp(len(sa), family, a)
+    p_y = synthetic_bpp(length, family, b)[:len(sb), :len(sb)].copy()
+    if mix:   # conflicting stems from two other families: slow, often non-converging DD
+        p_x = np.maximum(p_x, synthetic_bpp(len(sa), family + 2, 0))
+        p_y = np.maximum(p_y, synthetic_bpp(length, family + 1, 1)[:len(sb), :len(sb)])
+    p_z = oracle_pair_dense(sa, sb, th)
+    return p_x, np.ascontiguousarray(p_y), p_z
