@@ -19,4 +19,5 @@ from .capi import (  # noqa: F401
     pairhmm_pairs,
     pairhmm_tables,
 )
-from .synth import fasta_read, homolog_family, random_rna, splitmix64  # noqa: F401
+from .capi_dd import DDPlan, dd_solve_batch, nussinov_decode, nw_decode  # noqa: F401
+from .synth import fasta_read, homolog_family, random_rna, splitmix64, synthetic_bpp  # noqa: F401

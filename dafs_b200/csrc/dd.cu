@@ -1,0 +1,687 @@
+// Host side of (3): per-problem setup (consensus-base-pair enumeration, sparse
+// multiplier index sets, NW envelope), scratch layout, launch, and the C-ABI
+// entry points declared in include/dafs_cuda.h.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "common.cuh"
+#include "dd_kernel.cuh"
+
+namespace dafs {
+
+static const double kCutoff = 0.01;       // CUTOFF, src/dafs.cpp:65 (a double literal)
+static const int kMaxL = 16384;
+
+// Host image of one problem.  "cst" is uploaded once, "state" exists only on
+// the device (multipliers, results); offsets are bytes into those two buffers.
+struct NusHost {
+  int L = 0, n = 0;
+  float w = 0;
+  size_t col_ptr, row_ptr, row_ent, ent_ij, ent_p, ent_flag;   // cst
+  size_t ent_q;                                                // state
+  size_t out;                                                  // res
+  int max_col = 0;
+};
+struct ProbHost {
+  NusHost sx, sy;
+  int L1 = 0, L2 = 0, nz = 0, ncbp = 0, t_max = 0;
+  float th_s = 0, th_a = 0, eta0 = 0;
+  size_t pz, env, cz_ptr, cz_col, cz_cell, cbp;                // cst
+  size_t qz;                                                   // state
+  size_t z_out, result, trace;                                 // res
+  std::vector<char> cst;                                       // this problem's constant block
+  size_t state_bytes = 0, res_bytes = 0;
+  size_t cst_base = 0, state_base = 0, res_base = 0;                         // position in the plan's buffers
+};
+
+static size_t up16(size_t x) { return (x + 15) & ~size_t(15); }
+
+template <class T>
+static size_t put(std::vector<char>& buf, const T* data, size_t n) {
+  const size_t off = up16(buf.size());
+  buf.resize(off + sizeof(T) * n);
+  if (n) std::memcpy(buf.data() + off, data, sizeof(T) * n);
+  return off;
+}
+
+struct Ent { int i, j; float p; uint8_t flag; };
+
+// Entries of one structure: decoder candidates (w*(p-th) > 0 with q = 0, span
+// > 2: src/nussinov.cpp:234-237) plus the projection c_x of the CBPs
+// (src/dafs.cpp:1037).  Nothing else can ever get a non-zero multiplier:
+// q changes only for c_x entries and for decoded pairs (dafs.cpp:1121-1150),
+// and a decoded pair had s > 0.
+static void build_nus(NusHost& H, std::vector<char>& cst, size_t& state, size_t& res, int L, const float* p, float w,
+                      float th, const std::vector<std::pair<int, int>>& proj /* sorted unique (i,j) */) {
+  std::vector<Ent> ents;
+  size_t pc = 0;
+  for (int i = 0; i < L; ++i)
+    for (int j = i + 1; j < L; ++j) {
+      const float pij = p[(size_t)i * L + j];
+      bool inproj = false;
+      while (pc < proj.size() && (proj[pc].first < i || (proj[pc].first == i && proj[pc].second < j))) ++pc;
+      if (pc < proj.size() && proj[pc].first == i && proj[pc].second == j) inproj = true;
+      const bool span = (j - i > 2);
+      const float s0 = w * (pij - th);
+      const bool cand = span && (s0 > 0.0f);
+      if (cand || inproj) ents.push_back({i, j, pij, (uint8_t)((inproj ? 1 : 0) | (span ? 2 : 0))});
+    }
+  // column order: ascending j, descending i
+  std::sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.j != b.j ? a.j < b.j : a.i > b.i; });
+  const int n = (int)ents.size();
+  std::vector<int> col_ptr(L + 1, 0), row_ptr(L + 1, 0), row_ent(n);
+  std::vector<uint32_t> ij(n);
+  std::vector<float> pv(n);
+  std::vector<uint8_t> fl(n);
+  for (int e = 0; e < n; ++e) {
+    col_ptr[ents[e].j + 1]++; row_ptr[ents[e].i + 1]++;
+    ij[e] = (uint32_t)ents[e].i | ((uint32_t)ents[e].j << 16);
+    pv[e] = ents[e].p; fl[e] = ents[e].flag;
+  }
+  int max_col = 0;
+  for (int k = 0; k < L; ++k) {
+    max_col = std::max(max_col, col_ptr[k + 1]);
+    col_ptr[k + 1] += col_ptr[k]; row_ptr[k + 1] += row_ptr[k];
+  }
+  {
+    std::vector<int> fill(row_ptr.begin(), row_ptr.end() - 1);
+    // entries arrive in ascending j, so each row list comes out ascending in j
+    for (int e = 0; e < n; ++e) row_ent[fill[ents[e].i]++] = e;
+  }
+  H.L = L; H.n = n; H.w = w; H.max_col = max_col;
+  H.col_ptr = put(cst, col_ptr.data(), col_ptr.size());
+  H.row_ptr = put(cst, row_ptr.data(), row_ptr.size());
+  H.row_ent = put(cst, row_ent.data(), row_ent.size());
+  H.ent_ij = put(cst, ij.data(), ij.size());
+  H.ent_p = put(cst, pv.data(), pv.size());
+  H.ent_flag = put(cst, fl.data(), fl.size());
+  H.ent_q = up16(state); state = H.ent_q + sizeof(float) * n;
+  H.out = up16(res); res = H.out + sizeof(uint32_t) * L;
+}
+
+// entry id of (i, j) in a structure built by build_nus (must exist)
+static int find_ent(const std::vector<char>& cst, const NusHost& H, int i, int j) {
+  const int* row_ptr = reinterpret_cast<const int*>(cst.data() + H.row_ptr);
+  const int* row_ent = reinterpret_cast<const int*>(cst.data() + H.row_ent);
+  const uint32_t* ij = reinterpret_cast<const uint32_t*>(cst.data() + H.ent_ij);
+  int lo = row_ptr[i], hi = row_ptr[i + 1];
+  while (lo < hi) {
+    const int mid = (lo + hi) / 2;
+    const int jj = (int)(ij[row_ent[mid]] >> 16);
+    if (jj < j) lo = mid + 1; else hi = mid;
+  }
+  return row_ent[lo];
+}
+
+// SparseNeedlemanWunsch::initialize, src/needleman_wunsch.cpp:198-253
+static void build_envelope(int L1, int L2, float th, const float* p, std::vector<uint2>& env) {
+  env.assign(L1 + 1, make_uint2(0, 0));
+  for (int i = 1; i <= L1; ++i) {
+    const float* row = p + (size_t)(i - 1) * L2;
+    for (int k = 1; k != L2 + 1; ++k)
+      if (row[k - 1] - th >= 0.0) {
+        env[i - 1].x = std::min(env[i - 1].x, (unsigned)(k - 1));
+        env[i].x = (unsigned)k;
+        break;
+      }
+    if (env[i].x == 0) { env[i] = env[i - 1]; continue; }
+    for (int k = L2; k != 0; --k)
+      if (row[k - 1] - th >= 0.0) {
+        env[i - 1].y = std::max(env[i - 1].y, (unsigned)(k - 1));
+        env[i].y = (unsigned)k;
+        break;
+      }
+  }
+  env[L1].y = (unsigned)L2;
+  { unsigned v = (unsigned)L2; for (int i = L1; i != 0; --i) env[i].x = v = std::min(v, env[i].x); }
+  { unsigned v = 0; for (int i = 0; i != L1 + 1; ++i) env[i].y = v = std::max(v, env[i].y); }
+  for (int i = 1; i != L1 + 1; ++i)
+    if (env[i - 1].y < env[i].x) env[i].x = env[i - 1].y;
+}
+
+struct Cbp { int i, j, k, l; };
+
+// src/dafs.cpp:1016-1061, walking only the entries that pass the CUTOFF gates
+// (same lexicographic (i, j, k, l) order as the reference's four nested loops).
+static void enumerate_cbp(const dafs_dd_problem& q, std::vector<Cbp>& cbp) {
+  const int L1 = q.L1, L2 = q.L2;
+  std::vector<int> xptr(L1 + 1, 0), yptr(L2 + 1, 0), zptr(L1 + 1, 0);
+  std::vector<int> xcol, ycol, zcol;
+  for (int i = 0; i < L1; ++i) {
+    for (int j = i + 1; j < L1; ++j) if (q.p_x[(size_t)i * L1 + j] > kCutoff) xcol.push_back(j);
+    xptr[i + 1] = (int)xcol.size();
+    for (int k = 0; k < L2; ++k) if (q.p_z[(size_t)i * L2 + k] > kCutoff) zcol.push_back(k);
+    zptr[i + 1] = (int)zcol.size();
+  }
+  for (int k = 0; k < L2; ++k) {
+    for (int l = k + 1; l < L2; ++l) if (q.p_y[(size_t)k * L2 + l] > kCutoff) ycol.push_back(l);
+    yptr[k + 1] = (int)ycol.size();
+  }
+  const unsigned N1 = (unsigned)q.N1, N2 = (unsigned)q.N2;
+  for (int i = 0; i + 1 < L1; ++i)
+    for (int a = xptr[i]; a < xptr[i + 1]; ++a) {
+      const int j = xcol[a];
+      const float pxv = q.p_x[(size_t)i * L1 + j];
+      for (int b = zptr[i]; b < zptr[i + 1]; ++b) {
+        const int k = zcol[b];
+        if (k + 1 >= L2) continue;
+        const float pz1 = q.p_z[(size_t)i * L2 + k];
+        for (int c = yptr[k]; c < yptr[k + 1]; ++c) {
+          const int l = ycol[c];
+          const float pz2 = q.p_z[(size_t)j * L2 + l];
+          if (!(pz2 > kCutoff)) continue;
+          const float p = (N1 * pxv + N2 * q.p_y[(size_t)k * L2 + l]) / (N1 + N2);     // :1030
+          const float qq = (pz1 + pz2) / 2;                                            // :1031
+          if (p - q.min_th_s > 0.0 && q.w * (p - q.min_th_s) + (qq - q.th_a) > 0.0)    // :1032
+            cbp.push_back({i, j, k, l});
+        }
+      }
+    }
+}
+
+static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H) {
+  const int L1 = q.L1, L2 = q.L2;
+  H.L1 = L1; H.L2 = L2; H.t_max = q.t_max; H.th_s = q.th_s; H.th_a = q.th_a; H.eta0 = q.eta0;
+  std::vector<Cbp> cbp;
+  enumerate_cbp(q, cbp);
+  H.ncbp = (int)cbp.size();
+  std::vector<std::pair<int, int>> cx, cy, cz;
+  cx.reserve(cbp.size()); cy.reserve(cbp.size()); cz.reserve(2 * cbp.size());
+  for (const Cbp& c : cbp) {
+    cx.emplace_back(c.i, c.j); cy.emplace_back(c.k, c.l);
+    cz.emplace_back(c.i, c.k); cz.emplace_back(c.j, c.l);
+  }
+  auto uniq = [](std::vector<std::pair<int, int>>& v) {
+    std::sort(v.begin(), v.end());
+    v.erase(std::unique(v.begin(), v.end()), v.end());
+  };
+  uniq(cx); uniq(cy); uniq(cz);
+  const unsigned N1 = (unsigned)q.N1, N2 = (unsigned)q.N2;
+  const float wx = q.w * 2 * N1 / (N1 + N2), wy = q.w * 2 * N2 / (N1 + N2);   // dafs.cpp:1091-1092
+  size_t state = 0, res = 0;
+  build_nus(H.sx, H.cst, state, res, L1, q.p_x, wx, q.th_s, cx);
+  build_nus(H.sy, H.cst, state, res, L2, q.p_y, wy, q.th_s, cy);
+  // z
+  H.pz = put(H.cst, q.p_z, (size_t)L1 * L2);
+  std::vector<uint2> env;
+  build_envelope(L1, L2, q.th_a, q.p_z, env);
+  H.env = put(H.cst, env.data(), env.size());
+  H.nz = (int)cz.size();
+  std::vector<int> cz_ptr(L1 + 1, 0), cz_col(cz.size()), cz_cell(cz.size());
+  for (size_t e = 0; e < cz.size(); ++e) {
+    cz_ptr[cz[e].first + 1]++;
+    cz_col[e] = cz[e].second;
+    cz_cell[e] = cz[e].first * L2 + cz[e].second;
+  }
+  for (int i = 0; i < L1; ++i) cz_ptr[i + 1] += cz_ptr[i];
+  H.cz_ptr = put(H.cst, cz_ptr.data(), cz_ptr.size());
+  H.cz_col = put(H.cst, cz_col.data(), cz_col.size());
+  H.cz_cell = put(H.cst, cz_cell.data(), cz_cell.size());
+  std::vector<int4> cb(cbp.size());
+  auto zid = [&](int i, int k) {
+    return (int)(std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin());
+  };
+  for (size_t u = 0; u < cbp.size(); ++u)
+    cb[u] = make_int4(find_ent(H.cst, H.sx, cbp[u].i, cbp[u].j), find_ent(H.cst, H.sy, cbp[u].k, cbp[u].l),
+                      zid(cbp[u].i, cbp[u].k), zid(cbp[u].j, cbp[u].l));
+  H.cbp = put(H.cst, cb.data(), cb.size());
+  H.cst.resize(up16(H.cst.size()));
+  H.qz = up16(state); state = H.qz + sizeof(float) * (size_t)L1 * L2;
+  H.z_out = up16(res); res = H.z_out + sizeof(uint32_t) * L1;
+  H.result = up16(res); res = H.result + 16;
+  H.trace = up16(res);
+  if (want_trace) res = H.trace + sizeof(float) * 3 * (size_t)std::max(q.t_max, 0);
+  H.state_bytes = up16(state);
+  H.res_bytes = up16(res);
+  return DAFS_CUDA_OK;
+}
+
+}  // namespace dafs
+
+// ---- plan ---------------------------------------------------------------------
+struct dafs_dd_plan {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int nprob = 0;
+  bool want_trace = false;
+  std::vector<dafs::ProbHost> host;       // offsets (cst blocks are released after upload)
+  char* d_cst = nullptr; size_t cst_bytes = 0;
+  char* d_state = nullptr; size_t state_bytes = 0;
+  char* d_res = nullptr; size_t res_bytes = 0;
+  dafs::DDProblem* d_prob = nullptr;
+  int32_t* d_order = nullptr;
+  int* d_queue = nullptr;
+  char* d_ws = nullptr;
+  dafs::DDLayout lay{};
+  int C = 0, grid = 0, smem = 0, ctas_per_sm = 0;
+  int64_t total_cbp = 0, total_entries = 0;
+  bool launched = false;
+  float last_ms = 0;
+};
+
+namespace dafs {
+
+static const int kDDCols[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16};
+
+template <int C>
+static cudaError_t dd_launch(const DDArgs& a, int grid, int smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(dd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  dd_kernel<C><<<grid, 96, smem, st>>>(a);
+  return cudaGetLastError();
+}
+template <int C>
+static cudaError_t dd_occupancy(int smem, int* blocks) {
+  cudaError_t e = cudaFuncSetAttribute(dd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, dd_kernel<C>, 96, smem);
+}
+#define DD_DISPATCH(C, CALL)                                                   \
+  switch (C) {                                                                 \
+    case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break;    \
+    case 4: CALL(4); break; case 5: CALL(5); break; case 6: CALL(6); break;    \
+    case 8: CALL(8); break; case 10: CALL(10); break; case 12: CALL(12); break; \
+    default: CALL(16); break;                                                  \
+  }
+
+static void free_dd_plan(dafs_dd_plan* p) {
+  cudaFree(p->d_cst); cudaFree(p->d_state); cudaFree(p->d_res); cudaFree(p->d_prob); cudaFree(p->d_order);
+  cudaFree(p->d_queue); cudaFree(p->d_ws);
+  if (p->ev0) cudaEventDestroy(p->ev0);
+  if (p->ev1) cudaEventDestroy(p->ev1);
+  if (p->stream) cudaStreamDestroy(p->stream);
+}
+
+// Scratch layout from the batch maxima: items go to shared memory in priority
+// order (enum order in dd_kernel.cuh) while they fit, the rest to the per-CTA
+// global workspace.
+static void plan_layout(dafs_dd_plan* p, int maxL1, int maxL2, int maxnx, int maxny, int maxnz,
+                        int maxncbp, int maxcol, size_t smem_budget, size_t* ws_bytes) {
+  DDLayout& lay = p->lay;
+  const int SW = 32 * p->C;
+  lay.nstripes = (maxL2 + 1 + SW - 1) / SW;
+  lay.lp1 = (maxL1 + 2) & ~1;
+  lay.lp2 = (maxL2 + 2) & ~1;
+  lay.tr16 = (maxcol > 250) ? 1u : 0u;
+  const size_t trb = lay.tr16 ? 2 : 1;
+  size_t sz[DD_NITEMS];
+  sz[DD_ES_X] = 4 * (size_t)maxnx; sz[DD_ES_Y] = 4 * (size_t)maxny;
+  sz[DD_ROW_X] = 4 * (size_t)32 * lay.lp1; sz[DD_ROW_Y] = 4 * (size_t)32 * lay.lp2;
+  sz[DD_BROW_X] = 4 * (size_t)lay.lp1; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2;
+  sz[DD_TRZ] = 4 * (size_t)(maxL1 + 1) * lay.nstripes * 32;
+  sz[DD_TR_X] = trb * ((size_t)maxL1 * (maxL1 - 1) / 2 + 1);
+  sz[DD_TR_Y] = trb * ((size_t)maxL2 * (maxL2 - 1) / 2 + 1);
+  sz[DD_SS_X] = 4 * (size_t)maxL1; sz[DD_SS_Y] = 4 * (size_t)maxL2; sz[DD_ZRES] = 4 * (size_t)maxL1;
+  sz[DD_STK_X] = 4 * (size_t)(maxL1 / 2 + 4); sz[DD_STK_Y] = 4 * (size_t)(maxL2 / 2 + 4);
+  sz[DD_TAL_X] = 4 * (size_t)maxnx; sz[DD_TAL_Y] = 4 * (size_t)maxny; sz[DD_TAL_Z] = 4 * (size_t)maxnz;
+  sz[DD_SW] = 4 * (size_t)maxncbp;
+  sz[DD_BND] = 8 * (size_t)(maxL1 + 1);
+  size_t s_off = 0, g_off = 0;
+  lay.in_smem = 0;
+  for (int k = 0; k < DD_NITEMS; ++k) {
+    const size_t b = up16(std::max<size_t>(sz[k], 16));
+    if (s_off + b <= smem_budget) { lay.off[k] = (uint32_t)s_off; s_off += b; lay.in_smem |= 1u << k; }
+    else { lay.off[k] = (uint32_t)g_off; g_off += b; }
+  }
+  p->smem = (int)s_off;
+  *ws_bytes = up16(g_off) + 256;
+}
+
+static void fill_nus(DDNus& D, const NusHost& H, char* cst, char* state, char* res) {
+  D.L = H.L; D.n = H.n; D.w = H.w;
+  D.col_ptr = reinterpret_cast<const int*>(cst + H.col_ptr);
+  D.row_ptr = reinterpret_cast<const int*>(cst + H.row_ptr);
+  D.row_ent = reinterpret_cast<const int*>(cst + H.row_ent);
+  D.ent_ij = reinterpret_cast<const uint32_t*>(cst + H.ent_ij);
+  D.ent_p = reinterpret_cast<const float*>(cst + H.ent_p);
+  D.ent_flag = reinterpret_cast<const uint8_t*>(cst + H.ent_flag);
+  D.ent_q = reinterpret_cast<float*>(state + H.ent_q);
+  D.out = reinterpret_cast<uint32_t*>(res + H.out);
+}
+
+}  // namespace dafs
+
+using dafs::fail;
+
+extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
+                                        dafs_dd_plan** out) {
+  using namespace dafs;
+  if (!out) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  *out = nullptr;
+  if (nprob < 0 || (nprob > 0 && !prob)) return fail(DAFS_CUDA_EINVAL, "bad nprob / prob");
+  for (int k = 0; k < nprob; ++k) {
+    const dafs_dd_problem& q = prob[k];
+    if (q.L1 < 1 || q.L2 < 1 || q.L1 > kMaxL || q.L2 > kMaxL)
+      return fail(DAFS_CUDA_EINVAL, "problem %d: L1=%d L2=%d outside [1, %d]", k, q.L1, q.L2, kMaxL);
+    if (!q.p_x || !q.p_y || !q.p_z) return fail(DAFS_CUDA_EINVAL, "problem %d: NULL matrix", k);
+    if (q.N1 < 1 || q.N2 < 1 || q.t_max < 0) return fail(DAFS_CUDA_EINVAL, "problem %d: bad N1/N2/t_max", k);
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    cudaGetLastError();
+    return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)");
+  }
+  dafs_dd_plan* p = new dafs_dd_plan();
+  auto bail = [&](int rc) { free_dd_plan(p); delete p; return rc; };
+#define PLAN_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return bail(fail(e_ == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM : DAFS_CUDA_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_))); } while (0)
+  PLAN_TRY(cudaGetDevice(&p->device));
+  p->nprob = nprob; p->want_trace = want_trace != 0;
+  PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  PLAN_TRY(cudaEventCreate(&p->ev0));
+  PLAN_TRY(cudaEventCreate(&p->ev1));
+  PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
+  if (nprob == 0) { *out = p; return DAFS_CUDA_OK; }
+
+  // per-problem setup on the host cores (independent problems)
+  p->host.resize(nprob);
+  {
+    std::atomic<int> next(0);
+    const int nt = (int)std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)nprob));
+    auto work = [&]() { for (;;) { const int k = next.fetch_add(1); if (k >= nprob) break; build_problem(prob[k], p->want_trace, p->host[k]); } };
+    if (nt == 1) work();
+    else { std::vector<std::thread> th; for (int k = 0; k < nt; ++k) th.emplace_back(work); for (auto& t : th) t.join(); }
+  }
+  int maxL1 = 1, maxL2 = 1, maxnx = 1, maxny = 1, maxnz = 1, maxncbp = 1, maxcol = 0;
+  size_t cst = 0, state = 0, res = 0;
+  for (auto& H : p->host) {
+    H.res_base = res; res += H.res_bytes;
+    H.cst_base = cst; cst += up16(H.cst.size()) + 240; cst = (cst + 255) & ~size_t(255);
+    H.state_base = state; state += H.state_bytes; state = (state + 255) & ~size_t(255);
+    maxL1 = std::max(maxL1, H.L1); maxL2 = std::max(maxL2, H.L2);
+    maxnx = std::max(maxnx, H.sx.n); maxny = std::max(maxny, H.sy.n);
+    maxnz = std::max(maxnz, H.nz); maxncbp = std::max(maxncbp, H.ncbp);
+    maxcol = std::max(maxcol, std::max(H.sx.max_col, H.sy.max_col));
+    p->total_cbp += H.ncbp; p->total_entries += H.sx.n + H.sy.n;
+  }
+  p->cst_bytes = cst; p->state_bytes = state; p->res_bytes = res;
+  PLAN_TRY(cudaMalloc(&p->d_cst, std::max<size_t>(cst, 256)));
+  PLAN_TRY(cudaMalloc(&p->d_state, std::max<size_t>(state, 256)));
+  PLAN_TRY(cudaMalloc(&p->d_res, std::max<size_t>(res, 256)));
+  PLAN_TRY(cudaMalloc(&p->d_prob, sizeof(DDProblem) * nprob));
+  PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * nprob));
+  {
+    // one pinned staging buffer -> one H2D copy
+    char* stage = (char*)pinned_alloc(std::max<size_t>(cst, 256));
+    if (!stage) return bail(fail(DAFS_CUDA_ENOMEM, "pinned staging of %zu bytes failed", cst));
+    for (auto& H : p->host) { std::memcpy(stage + H.cst_base, H.cst.data(), H.cst.size()); std::vector<char>().swap(H.cst); }
+    cudaError_t e = cudaMemcpyAsync(p->d_cst, stage, cst, cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    pinned_free(stage);
+    PLAN_TRY(e);
+  }
+  std::vector<DDProblem> dp(nprob);
+  std::vector<int32_t> order(nprob);
+  for (int k = 0; k < nprob; ++k) {
+    const ProbHost& H = p->host[k];
+    char* c = p->d_cst + H.cst_base; char* s = p->d_state + H.state_base; char* r = p->d_res + H.res_base;
+    DDProblem& D = dp[k];
+    fill_nus(D.sx, H.sx, c, s, r); fill_nus(D.sy, H.sy, c, s, r);
+    D.L1 = H.L1; D.L2 = H.L2; D.nz = H.nz; D.ncbp = H.ncbp; D.t_max = H.t_max;
+    D.th_s = H.th_s; D.th_a = H.th_a; D.eta0 = H.eta0;
+    D.pz = reinterpret_cast<const float*>(c + H.pz);
+    D.qz = reinterpret_cast<float*>(s + H.qz);
+    D.env = reinterpret_cast<const uint2*>(c + H.env);
+    D.cz_ptr = reinterpret_cast<const int*>(c + H.cz_ptr);
+    D.cz_col = reinterpret_cast<const int*>(c + H.cz_col);
+    D.cz_cell = reinterpret_cast<const int*>(c + H.cz_cell);
+    D.cbp = reinterpret_cast<const int4*>(c + H.cbp);
+    D.z_out = reinterpret_cast<uint32_t*>(r + H.z_out);
+    D.result = reinterpret_cast<float*>(r + H.result);
+    D.trace = p->want_trace ? reinterpret_cast<float*>(r + H.trace) : nullptr;
+    order[k] = k;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+    const ProbHost &A = p->host[a], &B = p->host[b];
+    return (int64_t)A.t_max * ((int64_t)A.L1 * A.L1 + (int64_t)A.L2 * A.L2 + (int64_t)A.L1 * A.L2) >
+           (int64_t)B.t_max * ((int64_t)B.L1 * B.L1 + (int64_t)B.L2 * B.L2 + (int64_t)B.L1 * B.L2);
+  });
+  PLAN_TRY(cudaMemcpy(p->d_prob, dp.data(), sizeof(DDProblem) * nprob, cudaMemcpyHostToDevice));
+  PLAN_TRY(cudaMemcpy(p->d_order, order.data(), sizeof(int32_t) * nprob, cudaMemcpyHostToDevice));
+
+  // geometry
+  const int need = (maxL2 + 1 + 31) / 32;
+  p->C = 16;
+  for (int c : kDDCols) if (c >= need) { p->C = c; break; }
+  cudaDeviceProp prop;
+  PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
+  const size_t budget = (size_t)prop.sharedMemPerBlockOptin - 2048;
+  size_t ws_per = 0;
+  plan_layout(p, maxL1, maxL2, maxnx, maxny, maxnz, maxncbp, maxcol, budget, &ws_per);
+  int blocks = 0;
+#define OCC(CC) PLAN_TRY(dd_occupancy<CC>(p->smem, &blocks))
+  DD_DISPATCH(p->C, OCC)
+#undef OCC
+  if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
+  p->ctas_per_sm = blocks;
+  p->grid = std::max(1, std::min(nprob, prop.multiProcessorCount * blocks));
+  p->lay.ws_stride = ws_per;
+  PLAN_TRY(cudaMalloc(&p->d_ws, ws_per * p->grid));
+  p->lay.ws = p->d_ws;
+#undef PLAN_TRY
+  *out = p;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
+  using namespace dafs;
+  if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  p->launched = true;
+  if (p->nprob == 0) return DAFS_CUDA_OK;
+  DDArgs a;
+  a.prob = p->d_prob; a.order = p->d_order; a.nprob = p->nprob; a.queue = p->d_queue; a.lay = p->lay;
+  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
+  DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
+  cudaError_t e = cudaSuccess;
+#define RUN(CC) e = dd_launch<CC>(a, p->grid, p->smem, p->stream)
+  DD_DISPATCH(p->C, RUN)
+#undef RUN
+  DAFS_CUDA_TRY(e);
+  DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_dd_plan_sync(dafs_dd_plan* p, float* device_ms) {
+  if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  DAFS_CUDA_TRY(cudaStreamSynchronize(p->stream));
+  if (p->nprob > 0) DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+  if (device_ms) *device_ms = p->last_ms;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
+  using namespace dafs;
+  if (!p || (p->nprob > 0 && !res)) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  const int rc = dafs_cuda_dd_plan_sync(p, nullptr);
+  if (rc) return rc;
+  if (p->nprob == 0) return DAFS_CUDA_OK;
+  // x, y, z, result and trace of all problems are one contiguous device block.
+  char* stage = (char*)pinned_alloc(std::max<size_t>(p->res_bytes, 256));
+  if (!stage) return fail(DAFS_CUDA_ENOMEM, "pinned staging of %zu bytes failed", p->res_bytes);
+  cudaError_t e = cudaMemcpyAsync(stage, p->d_res, p->res_bytes, cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (e != cudaSuccess) { pinned_free(stage); return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e)); }
+  for (int k = 0; k < p->nprob; ++k) {
+    const ProbHost& H = p->host[k];
+    const char* s = stage + H.res_base;
+    dafs_dd_result& r = res[k];
+    if (r.x) std::memcpy(r.x, s + H.sx.out, sizeof(uint32_t) * H.L1);
+    if (r.y) std::memcpy(r.y, s + H.sy.out, sizeof(uint32_t) * H.L2);
+    if (r.z) std::memcpy(r.z, s + H.z_out, sizeof(uint32_t) * H.L1);
+    const float* rf = reinterpret_cast<const float*>(s + H.result);
+    r.score = rf[0];
+    r.iters = reinterpret_cast<const int*>(rf)[1];
+    r.violated = reinterpret_cast<const unsigned*>(rf)[2];
+    r.status = reinterpret_cast<const int*>(rf)[3];
+    r.ncbp = H.ncbp;
+    if (r.trace && p->want_trace)
+      std::memcpy(r.trace, s + H.trace, sizeof(float) * 3 * (size_t)std::min(H.t_max, r.iters + 1));
+  }
+  pinned_free(stage);
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_dd_plan_info(dafs_dd_plan* p, dafs_dd_info* info) {
+  if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  info->grid = p->grid; info->block = 96; info->cols_per_lane = p->C; info->smem_bytes = p->smem;
+  info->ctas_per_sm = p->ctas_per_sm; info->items_in_smem = p->lay.in_smem;
+  info->workspace_bytes = (int64_t)p->lay.ws_stride * p->grid;
+  info->arena_bytes = (int64_t)(p->cst_bytes + p->state_bytes + p->res_bytes);
+  info->total_cbp = p->total_cbp; info->total_entries = p->total_entries; info->last_ms = p->last_ms;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" void dafs_cuda_dd_plan_destroy(dafs_dd_plan* p) {
+  if (!p) return;
+  cudaSetDevice(p->device);
+  if (p->stream) cudaStreamSynchronize(p->stream);
+  dafs::free_dd_plan(p);
+  delete p;
+}
+
+extern "C" int dafs_cuda_dd_solve_batch(int nprob, const dafs_dd_problem* prob, dafs_dd_result* res) {
+  dafs_dd_plan* p = nullptr;
+  int rc = dafs_cuda_dd_plan_create(nprob, prob, 0, &p);
+  if (rc) return rc;
+  rc = dafs_cuda_dd_plan_run(p);
+  if (!rc) rc = dafs_cuda_dd_plan_fetch(p, res);
+  dafs_cuda_dd_plan_destroy(p);
+  return rc;
+}
+
+// ---- single decodes ------------------------------------------------------------
+namespace dafs {
+
+__global__ void __launch_bounds__(32) nussinov_single_kernel(const DDNus S, const NusScratch sc, float th,
+                                                             float* score) {
+  const float v = nussinov_warp(S, sc, th, threadIdx.x);
+  if (threadIdx.x == 0) *score = v;
+  for (int i = threadIdx.x; i < S.L; i += 32) S.out[i] = sc.ss[i];
+}
+
+template <int C>
+__global__ void __launch_bounds__(32) nw_single_kernel(const DDProblem P, uint32_t* trz, float* bnd, int* bad) {
+  const float v = nw_warp<C>(P, trz, bnd, P.z_out, threadIdx.x, bad);
+  if (threadIdx.x == 0) P.result[0] = v;
+}
+
+struct DevBuf {   // one cudaMalloc, carved
+  char* base = nullptr; size_t size = 0, used = 0;
+  ~DevBuf() { cudaFree(base); }
+  template <class T> T* take(size_t n) { used = up16(used); T* p = reinterpret_cast<T*>(base + used); used += sizeof(T) * std::max<size_t>(n, 1); return p; }
+};
+
+}  // namespace dafs
+
+extern "C" int dafs_cuda_nussinov_decode(int L, float th, float w, const float* p, const float* q,
+                                         uint32_t* ss, float* score) {
+  using namespace dafs;
+  if (L < 1 || L > kMaxL || !p || !ss) return fail(DAFS_CUDA_EINVAL, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
+  if (!q) w = 1.0f;   // plain overload: s = p - th == 1*(p - th) - 0 exactly
+  // candidates: s > 0, span > 2 (nussinov.cpp:234-237); nothing else is ever read
+  struct E { int i, j; float p, q; };
+  std::vector<E> ents;
+  for (int i = 0; i < L; ++i)
+    for (int j = i + 3; j < L; ++j) {
+      const float pv = p[(size_t)i * L + j], qv = q ? q[(size_t)i * L + j] : 0.0f;
+      const float s = w * (pv - th) - qv;
+      if (s > 0.0) ents.push_back({i, j, pv, qv});
+    }
+  std::sort(ents.begin(), ents.end(), [](const E& a, const E& b) { return a.j != b.j ? a.j < b.j : a.i > b.i; });
+  const int n = (int)ents.size();
+  std::vector<int> col_ptr(L + 1, 0), row_ptr(L + 1, 0), row_ent(std::max(n, 1));
+  std::vector<uint32_t> ij(std::max(n, 1));
+  std::vector<float> pv(std::max(n, 1)), qv(std::max(n, 1));
+  std::vector<uint8_t> fl(std::max(n, 1), 2);
+  for (int e = 0; e < n; ++e) {
+    col_ptr[ents[e].j + 1]++; row_ptr[ents[e].i + 1]++;
+    ij[e] = (uint32_t)ents[e].i | ((uint32_t)ents[e].j << 16); pv[e] = ents[e].p; qv[e] = ents[e].q;
+  }
+  int maxcol = 0;
+  for (int k = 0; k < L; ++k) { maxcol = std::max(maxcol, col_ptr[k + 1]); col_ptr[k + 1] += col_ptr[k]; row_ptr[k + 1] += row_ptr[k]; }
+  { std::vector<int> fill(row_ptr.begin(), row_ptr.end() - 1); for (int e = 0; e < n; ++e) row_ent[fill[ents[e].i]++] = e; }
+  const bool tr16 = maxcol > 250;
+  const int lp = (L + 2) & ~1;
+  const size_t ntr = (size_t)L * (L - 1) / 2 + 1;
+  DevBuf B;
+  B.size = 64 * 16 + 4 * (size_t)(2 * (L + 1) + 6 * (size_t)std::max(n, 1) + 33 * (size_t)lp + 2 * L + L / 2 + 8) + (tr16 ? 2 : 1) * ntr + 64;
+  DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
+  DDNus S; NusScratch sc;
+  int* d_col = B.take<int>(L + 1); int* d_row = B.take<int>(L + 1); int* d_re = B.take<int>(n);
+  uint32_t* d_ij = B.take<uint32_t>(n); float* d_p = B.take<float>(n); float* d_q = B.take<float>(n);
+  uint8_t* d_fl = B.take<uint8_t>(n);
+  sc.es = B.take<float>(n); sc.row = B.take<float>(32 * (size_t)lp); sc.brow = B.take<float>(lp);
+  sc.ss = B.take<uint32_t>(L); sc.stk = B.take<uint32_t>(L / 2 + 4);
+  uint32_t* d_out = B.take<uint32_t>(L); float* d_score = B.take<float>(1);
+  sc.tr = tr16 ? (void*)B.take<uint16_t>(ntr) : (void*)B.take<uint8_t>(ntr);
+  sc.lp = lp; sc.tr16 = tr16;
+  S.L = L; S.n = n; S.col_ptr = d_col; S.row_ptr = d_row; S.row_ent = d_re; S.ent_ij = d_ij; S.ent_p = d_p;
+  S.ent_flag = d_fl; S.ent_q = d_q; S.w = w; S.out = d_out;
+  DAFS_CUDA_TRY(cudaMemcpy(d_col, col_ptr.data(), sizeof(int) * (L + 1), cudaMemcpyHostToDevice));
+  DAFS_CUDA_TRY(cudaMemcpy(d_row, row_ptr.data(), sizeof(int) * (L + 1), cudaMemcpyHostToDevice));
+  if (n) {
+    DAFS_CUDA_TRY(cudaMemcpy(d_re, row_ent.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_ij, ij.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_p, pv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_q, qv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_fl, fl.data(), n, cudaMemcpyHostToDevice));
+  }
+  nussinov_single_kernel<<<1, 32>>>(S, sc, th, d_score);
+  DAFS_CUDA_TRY(cudaGetLastError());
+  DAFS_CUDA_TRY(cudaMemcpy(ss, d_out, sizeof(uint32_t) * L, cudaMemcpyDeviceToHost));
+  float sv = 0;
+  DAFS_CUDA_TRY(cudaMemcpy(&sv, d_score, sizeof(float), cudaMemcpyDeviceToHost));
+  if (score) *score = sv;
+  return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, const float* q, uint32_t* al,
+                                   float* score) {
+  using namespace dafs;
+  if (L1 < 1 || L2 < 1 || L1 > kMaxL || L2 > kMaxL || !p || !al) return fail(DAFS_CUDA_EINVAL, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
+  std::vector<uint2> env;
+  build_envelope(L1, L2, th, p, env);
+  const int need = (L2 + 1 + 31) / 32;
+  int C = 16;
+  for (int c : kDDCols) if (c >= need) { C = c; break; }
+  const int nstripes = (L2 + 1 + 32 * C - 1) / (32 * C);
+  const size_t cells = (size_t)L1 * L2;
+  DevBuf B;
+  B.size = 16 * 16 + 4 * (2 * cells + 2 * (size_t)(L1 + 1) + (size_t)(L1 + 1) * nstripes * 32 + 2 * (size_t)(L1 + 1) + L1 + 8) + 64;
+  DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
+  DDProblem P{};
+  float* d_p = B.take<float>(cells); float* d_q = B.take<float>(cells);
+  uint2* d_env = B.take<uint2>(L1 + 1);
+  uint32_t* trz = B.take<uint32_t>((size_t)(L1 + 1) * nstripes * 32);
+  float* bnd = B.take<float>(2 * (size_t)(L1 + 1));
+  uint32_t* d_al = B.take<uint32_t>(L1); float* d_res = B.take<float>(4); int* d_bad = B.take<int>(1);
+  DAFS_CUDA_TRY(cudaMemcpy(d_p, p, sizeof(float) * cells, cudaMemcpyHostToDevice));
+  if (q) DAFS_CUDA_TRY(cudaMemcpy(d_q, q, sizeof(float) * cells, cudaMemcpyHostToDevice));
+  else DAFS_CUDA_TRY(cudaMemset(d_q, 0, sizeof(float) * cells));   // v + 0.0f == v
+  DAFS_CUDA_TRY(cudaMemcpy(d_env, env.data(), sizeof(uint2) * (L1 + 1), cudaMemcpyHostToDevice));
+  DAFS_CUDA_TRY(cudaMemset(d_bad, 0, sizeof(int)));
+  P.L1 = L1; P.L2 = L2; P.th_a = th; P.pz = d_p; P.qz = d_q; P.env = d_env; P.z_out = d_al; P.result = d_res;
+  cudaError_t e = cudaSuccess;
+#define RUN(CC) { nw_single_kernel<CC><<<1, 32>>>(P, trz, bnd, d_bad); e = cudaGetLastError(); }
+  DD_DISPATCH(C, RUN)
+#undef RUN
+  DAFS_CUDA_TRY(e);
+  DAFS_CUDA_TRY(cudaMemcpy(al, d_al, sizeof(uint32_t) * L1, cudaMemcpyDeviceToHost));
+  float sv = 0; int bad = 0;
+  DAFS_CUDA_TRY(cudaMemcpy(&sv, d_res, sizeof(float), cudaMemcpyDeviceToHost));
+  DAFS_CUDA_TRY(cudaMemcpy(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+  if (score) *score = sv;
+  if (bad) return fail(DAFS_CUDA_ECUDA, "NW traceback met an unfilled cell (the reference does not terminate on this input)");
+  return DAFS_CUDA_OK;
+}

@@ -125,6 +125,77 @@ int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* plan, dafs_pairhmm_info* info
  * the reference's ProbabilisticModel constructor (ProbabilisticModel.h:55-88). */
 int dafs_cuda_pairhmm_tables(float* out54);
 
+/* ---- (3) dual decomposition ------------------------------------------------
+ * One problem = one call of DAFS::solve_by_dd(x, y, z, p_x, p_y, p_z, aln1, aln2)
+ * (src/dafs.cpp:1006): dense row-major probability matrices exactly as the
+ * reference passes them (VVF), N1 = aln1.size(), N2 = aln2.size() (:1013-1014),
+ * and the members it reads: w = w_, th_s = th_s_[0] (the threshold of
+ * s_decoder_, :1759), min_th_s = min(th_s_) (:1018), th_a = th_a_, eta0 = eta0_,
+ * t_max = t_max_ (-m).  Requires 1 <= L1, L2 <= 16384.                      */
+typedef struct dafs_dd_problem {
+  int32_t L1, L2, N1, N2;
+  const float* p_x;   /* [L1*L1], only i<j read */
+  const float* p_y;   /* [L2*L2]                */
+  const float* p_z;   /* [L1*L2]                */
+  float w, th_s, min_th_s, th_a, eta0;
+  int32_t t_max;
+} dafs_dd_problem;
+
+/* x, y, z are caller-allocated (L1, L2, L1 entries; 0xffffffff = "-1u", no
+ * partner), trace may be NULL or hold 3*t_max floats {L, eta, violated} per
+ * iteration (what -v 2 logs, src/dafs.cpp:1273).  score is solve_by_dd's return
+ * value, iters / violated what it logs at :1292.  status != 0: the NW traceback
+ * met an unfilled cell (the reference would not terminate there).           */
+typedef struct dafs_dd_result {
+  uint32_t* x;
+  uint32_t* y;
+  uint32_t* z;
+  float* trace;
+  float score;
+  int32_t iters;
+  uint32_t violated;
+  int32_t status;
+  int64_t ncbp;       /* consensus-base-pair candidates enumerated (:1016-1045) */
+} dafs_dd_result;
+
+/* All problems in one launch, each running its whole <= t_max iteration loop on
+ * the device (no host round trip between iterations).                       */
+int dafs_cuda_dd_solve_batch(int nprob, const dafs_dd_problem* prob, dafs_dd_result* res);
+
+/* Split-phase form (inputs resident in HBM; run() is repeatable):
+ *   create = CBP enumeration (:1016-1061) + NW envelope (needleman_wunsch.cpp:
+ *            198-253) + H2D;   run = reset multipliers + the DD kernel;
+ *   sync   = wait, device ms;  fetch = D2H of x, y, z, score, iters, violated. */
+typedef struct dafs_dd_plan dafs_dd_plan;
+int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
+                             dafs_dd_plan** plan);
+int dafs_cuda_dd_plan_run(dafs_dd_plan* plan);
+int dafs_cuda_dd_plan_sync(dafs_dd_plan* plan, float* device_ms);
+int dafs_cuda_dd_plan_fetch(dafs_dd_plan* plan, dafs_dd_result* res);
+void dafs_cuda_dd_plan_destroy(dafs_dd_plan* plan);
+
+typedef struct dafs_dd_info {
+  int grid, block, cols_per_lane;  /* persistent CTAs, threads, NW columns per lane */
+  int smem_bytes;                  /* dynamic shared memory per CTA                 */
+  int ctas_per_sm;
+  unsigned items_in_smem;          /* bit per scratch array (dd_kernel.cuh)         */
+  int64_t workspace_bytes;         /* per-CTA global scratch, all CTAs              */
+  int64_t arena_bytes;             /* per-problem device data                       */
+  int64_t total_cbp, total_entries;
+  float last_ms;
+} dafs_dd_info;
+int dafs_cuda_dd_plan_info(dafs_dd_plan* plan, dafs_dd_info* info);
+
+/* Single decodes, for the reference's other call sites of the two decoders
+ * (src/dafs.cpp:923, :1867, :1870) and for bit-exactness tests.
+ * Nussinov: p, q are [L*L]; q == NULL selects the plain overload
+ * (src/nussinov.cpp:300-392: s = p - th).  NW: p, q are [L1*L2]; includes
+ * initialize() (src/needleman_wunsch.cpp:198-253); q == NULL = plain overload. */
+int dafs_cuda_nussinov_decode(int L, float th, float w, const float* p, const float* q,
+                              uint32_t* ss, float* score);
+int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, const float* q, uint32_t* al,
+                        float* score);
+
 #ifdef __cplusplus
 }
 #endif

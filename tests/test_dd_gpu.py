@@ -1,0 +1,170 @@
+"""GPU parity tests of (3): the device decoders and the on-device DD loop against
+the oracle (oracle/dd_oracle.c, pinned to the reference) -- bit-exact scores,
+identical x / y / z, identical iteration counts -- and against the golden
+fixtures generated from the reference's own solve_by_dd."""
+import json
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+from dafs_b200.synth import synthetic_bpp
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def dafs():
+    import dafs_b200
+    dafs_b200.init(1)
+    return dafs_b200
+
+
+def rand_q(shape, seed, density=0.05, scale=0.5, signed=True):
+    r = np.random.default_rng(seed)
+    q = (r.random(shape) < density) * (r.random(shape) - (0.5 if signed else 0.0)) * scale
+    return q.astype(np.float32)
+
+
+def bits(x):
+    return int(np.float32(x).view(np.uint32))
+
+
+@pytest.mark.parametrize("L,seed", [(1, 0), (2, 1), (3, 2), (4, 3), (5, 4), (17, 5), (33, 9), (64, 10), (65, 11),
+                                    (73, 6), (150, 7), (301, 8), (700, 12)])
+def test_nussinov_decode_bit_exact(dafs, L, seed):
+    p = synthetic_bpp(L, seed, 0)
+    q = rand_q((L, L), seed)
+    for w in (4.0, 2.6666667):
+        so, sso = ou.oracle_nussinov(p, q, 0.2, w)
+        sg, ssg = dafs.nussinov_decode(p, q, 0.2, w)
+        assert bits(so) == bits(sg)
+        assert np.array_equal(sso, ssg)
+    so, sso = ou.oracle_nussinov(p, None, 0.15)
+    sg, ssg = dafs.nussinov_decode(p, None, 0.15)
+    assert bits(so) == bits(sg) and np.array_equal(sso, ssg)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_nussinov_dense_ties(dafs, seed):
+    """Quantised dense p: many equal sums, so the tie-break order is what is tested;
+    the last seeds give columns with > 250 candidates (16-bit traceback codes)."""
+    r = np.random.default_rng(100 + seed)
+    L = 40 + 7 * seed if seed < 4 else 600
+    dens = 0.3 if seed < 4 else 0.6
+    p = (np.round(r.random((L, L)) * 8) / 8 * (r.random((L, L)) < dens)).astype(np.float32)
+    q = (np.round(r.random((L, L)) * 4) / 8 * (r.random((L, L)) < 0.2)).astype(np.float32)
+    so, sso = ou.oracle_nussinov(p, q, 0.25, 1.0)
+    sg, ssg = dafs.nussinov_decode(p, q, 0.25, 1.0)
+    assert bits(so) == bits(sg) and np.array_equal(sso, ssg)
+
+
+@pytest.mark.parametrize("L1,L2,seed", [(1, 1, 0), (1, 9, 1), (9, 1, 2), (31, 32, 7), (40, 40, 3), (73, 80, 4),
+                                        (150, 120, 5), (300, 300, 6), (100, 600, 8), (600, 100, 9)])
+def test_nw_decode_bit_exact(dafs, L1, L2, seed):
+    _, _, p = ou.dd_problem(max(L1, L2), family=seed)
+    p = np.ascontiguousarray(p[:L1, :L2])
+    q = rand_q((L1, L2), seed, signed=False)
+    for qq in (q, None):
+        so, alo, _, bad = ou.oracle_nw(p, qq, 0.01)
+        sg, alg = dafs.nw_decode(p, qq, 0.01)
+        assert bad == 0
+        assert bits(so) == bits(sg) and np.array_equal(alo, alg)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_nw_sparse_envelope(dafs, seed):
+    r = np.random.default_rng(seed)
+    L1, L2 = 30 + seed, 45 - seed
+    p = ((r.random((L1, L2)) < 0.04) * r.random((L1, L2))).astype(np.float32)
+    so, alo, _, bad = ou.oracle_nw(p, None, 0.3)
+    sg, alg = dafs.nw_decode(p, None, 0.3)
+    assert bad == 0 and bits(so) == bits(sg) and np.array_equal(alo, alg)
+
+
+def check_dd(g, o, compare_xyz=True):
+    assert bits(g["score"]) == bits(o["score"])
+    assert g["iters"] == o["iters"] and g["violated"] == o["violated"] and g["ncbp"] == o["ncbp"]
+    assert g["status"] == 0
+    for k in "xyz":
+        if compare_xyz:
+            assert np.array_equal(g[k], o[k])
+        else:   # -m 0: the reference never decodes, x / y / z stay empty vectors
+            assert (g[k] == 0xFFFFFFFF).all()
+
+
+SPECS = [(30, 0, None, 1, 1, 600, 0.2, False), (73, 1, None, 1, 1, 600, 0.2, False),
+         (73, 2, None, 3, 2, 600, 0.2, False), (120, 3, 97, 1, 4, 600, 0.2, False),
+         (73, 1, None, 1, 1, 600, 0.75, True), (150, 4, None, 1, 1, 600, 0.6, True),
+         (150, 5, None, 2, 1, 600, 0.75, True), (300, 5, None, 1, 1, 200, 0.75, True),
+         (8, 6, None, 1, 1, 50, 0.2, False), (2, 7, None, 1, 1, 5, 0.2, False), (1, 8, None, 1, 1, 5, 0.2, False)]
+
+
+def test_dd_batch_vs_oracle_with_trace(dafs):
+    """One mixed batch (different sizes, weights, t_max) through the plan API; every
+    iteration's (L, eta, violated) must equal the oracle's -- the -v 2 trajectory."""
+    probs, want = [], []
+    for L, fam, l2, n1, n2, tm, mut, mix in SPECS:
+        p_x, p_y, p_z = ou.dd_problem(L, family=fam, l2=l2, mutation=mut, mix=mix)
+        probs.append(dict(p_x=p_x, p_y=p_y, p_z=p_z, n1=n1, n2=n2, t_max=tm))
+        want.append(ou.oracle_dd(p_x, p_y, p_z, n1, n2, t_max=tm, trace=True))
+    with dafs.DDPlan(probs, trace=True) as plan:
+        for rep in range(2):                 # run() is repeatable: multipliers are reset on the device
+            plan.run()
+            got = plan.fetch()
+            for g, o in zip(got, want):
+                check_dd(g, o)
+                assert np.array_equal(g["trace"].view(np.uint32), o["trace"].view(np.uint32))
+
+
+def test_dd_solve_batch_one_shot(dafs):
+    p_x, p_y, p_z = ou.dd_problem(73, family=1, mutation=0.75, mix=True)
+    g = dafs.dd_solve_batch([dict(p_x=p_x, p_y=p_y, p_z=p_z)])[0]
+    check_dd(g, ou.oracle_dd(p_x, p_y, p_z))
+
+
+def test_dd_options(dafs):
+    """Non-default -w, -t, -u, --eta, -m and th_s vector minimum."""
+    p_x, p_y, p_z = ou.dd_problem(100, family=11, mutation=0.6, mix=True)
+    for kw in (dict(w=2.0, th_s=0.3, th_a=0.05, eta0=0.25, t_max=77),
+               dict(w=8.0, th_s=0.5, min_th_s=0.1, th_a=0.01, eta0=1.0, t_max=40),
+               dict(t_max=0), dict(t_max=1)):
+        g = dafs.dd_solve_batch([dict(p_x=p_x, p_y=p_y, p_z=p_z, **kw)])[0]
+        okw = dict(kw); okw.setdefault("t_max", 600)
+        check_dd(g, ou.oracle_dd(p_x, p_y, p_z, 1, 1, **okw), compare_xyz=okw["t_max"] > 0)
+
+
+def test_dd_empty_cbp_nan_path(dafs):
+    p_x, p_y, p_z = ou.dd_problem(40, family=9)
+    p_z[:] = 0
+    g = dafs.dd_solve_batch([dict(p_x=p_x, p_y=p_y, p_z=p_z, t_max=20)])[0]
+    o = ou.oracle_dd(p_x, p_y, p_z, t_max=20)
+    assert o["ncbp"] == 0
+    check_dd(g, o)
+
+
+def test_dd_reference_golden(dafs):
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "dd_golden.json")))["cases"]
+    probs = []
+    for c in gold:
+        p_x, p_y, p_z = ou.dd_problem(c["L"], family=c["family"], l2=c["l2"], mutation=c["mutation"], mix=c["mix"])
+        probs.append(dict(p_x=p_x, p_y=p_y, p_z=p_z, n1=c["n1"], n2=c["n2"], t_max=c["t_max"]))
+    for g, c in zip(dafs.dd_solve_batch(probs), gold):
+        assert bits(g["score"]) == c["score_bits"], c["name"]
+        assert g["iters"] == c["iters"] and g["violated"] == c["violated"], c["name"]
+        for k in "xyz":
+            assert zlib.crc32(g[k].tobytes()) == c["crc_" + k], c["name"]
+
+
+def test_dd_large_falls_back_to_global_scratch(dafs):
+    """L = 900: row buffers and traceback arrays no longer fit in shared memory."""
+    p_x, p_y, p_z = ou.dd_problem(900, family=13, mutation=0.3)
+    with dafs.DDPlan([dict(p_x=p_x, p_y=p_y, p_z=p_z, t_max=12)]) as plan:
+        plan.run()
+        g = plan.fetch()[0]
+        info = plan.info()
+    assert info["workspace_bytes"] > 0
+    check_dd(g, ou.oracle_dd(p_x, p_y, p_z, t_max=12))
