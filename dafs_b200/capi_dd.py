@@ -20,7 +20,8 @@ class _DDProblem(C.Structure):
 
 class _DDResult(C.Structure):
     _fields_ = [("x", _UP), ("y", _UP), ("z", _UP), ("trace", _FP), ("score", C.c_float),
-                ("iters", C.c_int32), ("violated", C.c_uint32), ("status", C.c_int32), ("ncbp", C.c_int64)]
+                ("iters", C.c_int32), ("violated", C.c_uint32), ("status", C.c_int32), ("ncbp", C.c_int64),
+                ("cycles", C.c_float * 8)]
 
 
 class _DDInfo(C.Structure):
@@ -100,7 +101,8 @@ class DDBatch:
         for k, (x, y, z, tr) in enumerate(outs):
             r = res[k]
             d = {"score": np.float32(r.score), "x": x, "y": y, "z": z, "iters": int(r.iters),
-                 "violated": int(r.violated), "status": int(r.status), "ncbp": int(r.ncbp)}
+                 "violated": int(r.violated), "status": int(r.status), "ncbp": int(r.ncbp),
+                 "cycles": np.array(r.cycles[:], dtype=np.float64)}
             if tr is not None:
                 d["trace"] = tr[:min(int(r.iters) + 1, len(tr))]
             out.append(d)

@@ -16,26 +16,21 @@ namespace dafs {
 static const double kCutoff = 0.01;       // CUTOFF, src/dafs.cpp:65 (a double literal)
 static const int kMaxL = 16384;
 
-// Host image of one problem.  "cst" is uploaded once, "state" exists only on
-// the device (multipliers, results); offsets are bytes into those two buffers.
+// Host image of one problem: the position-independent constant block the kernel
+// stages into shared memory (DDHdr + sections), and where its results go.
 struct NusHost {
-  int L = 0, n = 0;
+  int L = 0, n = 0, max_col = 0;
   float w = 0;
-  size_t col_ptr, row_ptr, row_ent, ent_ij, ent_p, ent_flag;   // cst
-  size_t ent_q;                                                // state
-  size_t out;                                                  // res
-  int max_col = 0;
+  uint32_t col_ptr = 0, row_ptr = 0, row_ent = 0, ent_ij = 0, ent_p = 0, ent_flag = 0;   // offsets in the block
+  size_t out = 0;                                                                      // offset in the result buffer
 };
 struct ProbHost {
   NusHost sx, sy;
   int L1 = 0, L2 = 0, nz = 0, ncbp = 0, t_max = 0;
-  float th_s = 0, th_a = 0, eta0 = 0;
-  size_t pz, env, cz_ptr, cz_col, cz_cell, cbp;                // cst
-  size_t qz;                                                   // state
-  size_t z_out, result, trace;                                 // res
-  std::vector<char> cst;                                       // this problem's constant block
-  size_t state_bytes = 0, res_bytes = 0;
-  size_t cst_base = 0, state_base = 0, res_base = 0;                         // position in the plan's buffers
+  size_t z_out = 0, result = 0, trace = 0;                     // result buffer
+  std::vector<char> cst;                                       // the constant block
+  size_t res_bytes = 0;
+  size_t cst_base = 0, res_base = 0;                           // position in the plan's buffers
 };
 
 static size_t up16(size_t x) { return (x + 15) & ~size_t(15); }
@@ -55,7 +50,7 @@ struct Ent { int i, j; float p; uint8_t flag; };
 // (src/dafs.cpp:1037).  Nothing else can ever get a non-zero multiplier:
 // q changes only for c_x entries and for decoded pairs (dafs.cpp:1121-1150),
 // and a decoded pair had s > 0.
-static void build_nus(NusHost& H, std::vector<char>& cst, size_t& state, size_t& res, int L, const float* p, float w,
+static void build_nus(NusHost& H, std::vector<char>& cst, size_t& res, int L, const float* p, float w,
                       float th, const std::vector<std::pair<int, int>>& proj /* sorted unique (i,j) */) {
   std::vector<Ent> ents;
   size_t pc = 0;
@@ -93,13 +88,12 @@ static void build_nus(NusHost& H, std::vector<char>& cst, size_t& state, size_t&
     for (int e = 0; e < n; ++e) row_ent[fill[ents[e].i]++] = e;
   }
   H.L = L; H.n = n; H.w = w; H.max_col = max_col;
-  H.col_ptr = put(cst, col_ptr.data(), col_ptr.size());
-  H.row_ptr = put(cst, row_ptr.data(), row_ptr.size());
-  H.row_ent = put(cst, row_ent.data(), row_ent.size());
-  H.ent_ij = put(cst, ij.data(), ij.size());
-  H.ent_p = put(cst, pv.data(), pv.size());
-  H.ent_flag = put(cst, fl.data(), fl.size());
-  H.ent_q = up16(state); state = H.ent_q + sizeof(float) * n;
+  H.col_ptr = (uint32_t)put(cst, col_ptr.data(), col_ptr.size());
+  H.row_ptr = (uint32_t)put(cst, row_ptr.data(), row_ptr.size());
+  H.row_ent = (uint32_t)put(cst, row_ent.data(), row_ent.size());
+  H.ent_ij = (uint32_t)put(cst, ij.data(), ij.size());
+  H.ent_p = (uint32_t)put(cst, pv.data(), pv.size());
+  H.ent_flag = (uint32_t)put(cst, fl.data(), fl.size());
   H.out = up16(res); res = H.out + sizeof(uint32_t) * L;
 }
 
@@ -185,7 +179,7 @@ static void enumerate_cbp(const dafs_dd_problem& q, std::vector<Cbp>& cbp) {
 
 static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H) {
   const int L1 = q.L1, L2 = q.L2;
-  H.L1 = L1; H.L2 = L2; H.t_max = q.t_max; H.th_s = q.th_s; H.th_a = q.th_a; H.eta0 = q.eta0;
+  H.L1 = L1; H.L2 = L2; H.t_max = q.t_max;
   std::vector<Cbp> cbp;
   enumerate_cbp(q, cbp);
   H.ncbp = (int)cbp.size();
@@ -202,40 +196,61 @@ static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H)
   uniq(cx); uniq(cy); uniq(cz);
   const unsigned N1 = (unsigned)q.N1, N2 = (unsigned)q.N2;
   const float wx = q.w * 2 * N1 / (N1 + N2), wy = q.w * 2 * N2 / (N1 + N2);   // dafs.cpp:1091-1092
-  size_t state = 0, res = 0;
-  build_nus(H.sx, H.cst, state, res, L1, q.p_x, wx, q.th_s, cx);
-  build_nus(H.sy, H.cst, state, res, L2, q.p_y, wy, q.th_s, cy);
-  // z
-  H.pz = put(H.cst, q.p_z, (size_t)L1 * L2);
+  size_t res = 0;
+  H.cst.assign(sizeof(DDHdr), 0);
+  build_nus(H.sx, H.cst, res, L1, q.p_x, wx, q.th_s, cx);
+  build_nus(H.sy, H.cst, res, L2, q.p_y, wy, q.th_s, cy);
+  // z: cells with p_z != 0 (every other cell adds exactly 0 in needleman_wunsch.cpp:282)
+  // or in c_z (the only cells whose multiplier can leave 0), row by row, ascending k
+  std::vector<int> z_row_ptr(L1 + 1, 0);
+  std::vector<uint16_t> z_col;
+  std::vector<float> z_p;
+  std::vector<uint8_t> z_flag;
+  std::vector<int> cz_id(cz.size());
+  {
+    size_t c = 0;
+    for (int i = 0; i < L1; ++i) {
+      const float* row = q.p_z + (size_t)i * L2;
+      for (int k = 0; k < L2; ++k) {
+        const bool in_cz = (c < cz.size() && cz[c].first == i && cz[c].second == k);
+        if (row[k] != 0.0f || in_cz) {
+          if (in_cz) { cz_id[c] = (int)z_col.size(); ++c; }
+          z_col.push_back((uint16_t)k); z_p.push_back(row[k]); z_flag.push_back(in_cz ? 1 : 0);
+        }
+      }
+      z_row_ptr[i + 1] = (int)z_col.size();
+    }
+  }
+  H.nz = (int)z_col.size();
   std::vector<uint2> env;
   build_envelope(L1, L2, q.th_a, q.p_z, env);
-  H.env = put(H.cst, env.data(), env.size());
-  H.nz = (int)cz.size();
-  std::vector<int> cz_ptr(L1 + 1, 0), cz_col(cz.size()), cz_cell(cz.size());
-  for (size_t e = 0; e < cz.size(); ++e) {
-    cz_ptr[cz[e].first + 1]++;
-    cz_col[e] = cz[e].second;
-    cz_cell[e] = cz[e].first * L2 + cz[e].second;
-  }
-  for (int i = 0; i < L1; ++i) cz_ptr[i + 1] += cz_ptr[i];
-  H.cz_ptr = put(H.cst, cz_ptr.data(), cz_ptr.size());
-  H.cz_col = put(H.cst, cz_col.data(), cz_col.size());
-  H.cz_cell = put(H.cst, cz_cell.data(), cz_cell.size());
+  DDHdr h{};
+  h.z_row_ptr = (uint32_t)put(H.cst, z_row_ptr.data(), z_row_ptr.size());
+  h.z_col = (uint32_t)put(H.cst, z_col.data(), z_col.size());
+  h.z_p = (uint32_t)put(H.cst, z_p.data(), z_p.size());
+  h.z_flag = (uint32_t)put(H.cst, z_flag.data(), z_flag.size());
+  h.z_env = (uint32_t)put(H.cst, env.data(), env.size());
   std::vector<int4> cb(cbp.size());
   auto zid = [&](int i, int k) {
-    return (int)(std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin());
+    return cz_id[std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin()];
   };
   for (size_t u = 0; u < cbp.size(); ++u)
     cb[u] = make_int4(find_ent(H.cst, H.sx, cbp[u].i, cbp[u].j), find_ent(H.cst, H.sy, cbp[u].k, cbp[u].l),
                       zid(cbp[u].i, cbp[u].k), zid(cbp[u].j, cbp[u].l));
-  H.cbp = put(H.cst, cb.data(), cb.size());
+  h.cbp = (uint32_t)put(H.cst, cb.data(), cb.size());
   H.cst.resize(up16(H.cst.size()));
-  H.qz = up16(state); state = H.qz + sizeof(float) * (size_t)L1 * L2;
+  h.L1 = L1; h.L2 = L2; h.nx = H.sx.n; h.ny = H.sy.n; h.nz = H.nz; h.ncbp = H.ncbp; h.t_max = q.t_max;
+  h.bytes = (int)H.cst.size();
+  h.th_s = q.th_s; h.th_a = q.th_a; h.eta0 = q.eta0; h.wx = wx; h.wy = wy;
+  h.x_col_ptr = H.sx.col_ptr; h.x_row_ptr = H.sx.row_ptr; h.x_row_ent = H.sx.row_ent;
+  h.x_ij = H.sx.ent_ij; h.x_p = H.sx.ent_p; h.x_flag = H.sx.ent_flag;
+  h.y_col_ptr = H.sy.col_ptr; h.y_row_ptr = H.sy.row_ptr; h.y_row_ent = H.sy.row_ent;
+  h.y_ij = H.sy.ent_ij; h.y_p = H.sy.ent_p; h.y_flag = H.sy.ent_flag;
+  std::memcpy(H.cst.data(), &h, sizeof h);
   H.z_out = up16(res); res = H.z_out + sizeof(uint32_t) * L1;
-  H.result = up16(res); res = H.result + 16;
+  H.result = up16(res); res = H.result + 64;
   H.trace = up16(res);
   if (want_trace) res = H.trace + sizeof(float) * 3 * (size_t)std::max(q.t_max, 0);
-  H.state_bytes = up16(state);
   H.res_bytes = up16(res);
   return DAFS_CUDA_OK;
 }
@@ -251,14 +266,13 @@ struct dafs_dd_plan {
   bool want_trace = false;
   std::vector<dafs::ProbHost> host;       // offsets (cst blocks are released after upload)
   char* d_cst = nullptr; size_t cst_bytes = 0;
-  char* d_state = nullptr; size_t state_bytes = 0;
   char* d_res = nullptr; size_t res_bytes = 0;
-  dafs::DDProblem* d_prob = nullptr;
+  dafs::DDProbRef* d_prob = nullptr;
   int32_t* d_order = nullptr;
   int* d_queue = nullptr;
   char* d_ws = nullptr;
   dafs::DDLayout lay{};
-  int C = 0, grid = 0, smem = 0, ctas_per_sm = 0;
+  int grid = 0, smem = 0, ctas_per_sm = 0;
   int64_t total_cbp = 0, total_entries = 0;
   bool launched = false;
   float last_ms = 0;
@@ -266,61 +280,39 @@ struct dafs_dd_plan {
 
 namespace dafs {
 
-static const int kDDCols[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16};
-
-template <int C>
-static cudaError_t dd_launch(const DDArgs& a, int grid, int smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(dd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
-  dd_kernel<C><<<grid, 96, smem, st>>>(a);
-  return cudaGetLastError();
-}
-template <int C>
-static cudaError_t dd_occupancy(int smem, int* blocks) {
-  cudaError_t e = cudaFuncSetAttribute(dd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, dd_kernel<C>, 96, smem);
-}
-#define DD_DISPATCH(C, CALL)                                                   \
-  switch (C) {                                                                 \
-    case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break;    \
-    case 4: CALL(4); break; case 5: CALL(5); break; case 6: CALL(6); break;    \
-    case 8: CALL(8); break; case 10: CALL(10); break; case 12: CALL(12); break; \
-    default: CALL(16); break;                                                  \
-  }
-
 static void free_dd_plan(dafs_dd_plan* p) {
-  cudaFree(p->d_cst); cudaFree(p->d_state); cudaFree(p->d_res); cudaFree(p->d_prob); cudaFree(p->d_order);
+  cudaFree(p->d_cst); cudaFree(p->d_res); cudaFree(p->d_prob); cudaFree(p->d_order);
   cudaFree(p->d_queue); cudaFree(p->d_ws);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 
+struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nz = 1, ncbp = 1, col = 0, cst = 16; };
+
 // Scratch layout from the batch maxima: items go to shared memory in priority
 // order (enum order in dd_kernel.cuh) while they fit, the rest to the per-CTA
 // global workspace.
-static void plan_layout(dafs_dd_plan* p, int maxL1, int maxL2, int maxnx, int maxny, int maxnz,
-                        int maxncbp, int maxcol, size_t smem_budget, size_t* ws_bytes) {
-  DDLayout& lay = p->lay;
-  const int SW = 32 * p->C;
-  lay.nstripes = (maxL2 + 1 + SW - 1) / SW;
-  lay.lp1 = (maxL1 + 2) & ~1;
-  lay.lp2 = (maxL2 + 2) & ~1;
-  lay.tr16 = (maxcol > 250) ? 1u : 0u;
+static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, int* smem_bytes, size_t* ws_bytes) {
+  lay.lp1 = (m.L1 + 2) & ~1;
+  lay.lp2 = (m.L2 + 2) & ~1;
+  lay.w16 = (m.L2 + 15) / 16;
+  lay.tr16 = (m.col > 250) ? 1u : 0u;
   const size_t trb = lay.tr16 ? 2 : 1;
   size_t sz[DD_NITEMS];
-  sz[DD_ES_X] = 4 * (size_t)maxnx; sz[DD_ES_Y] = 4 * (size_t)maxny;
+  sz[DD_CST] = (size_t)m.cst;
+  sz[DD_Q_X] = 4 * (size_t)m.nx; sz[DD_Q_Y] = 4 * (size_t)m.ny; sz[DD_Q_Z] = 4 * (size_t)m.nz;
+  sz[DD_ES_X] = 4 * (size_t)m.nx; sz[DD_ES_Y] = 4 * (size_t)m.ny;
   sz[DD_ROW_X] = 4 * (size_t)32 * lay.lp1; sz[DD_ROW_Y] = 4 * (size_t)32 * lay.lp2;
   sz[DD_BROW_X] = 4 * (size_t)lay.lp1; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2;
-  sz[DD_TRZ] = 4 * (size_t)(maxL1 + 1) * lay.nstripes * 32;
-  sz[DD_TR_X] = trb * ((size_t)maxL1 * (maxL1 - 1) / 2 + 1);
-  sz[DD_TR_Y] = trb * ((size_t)maxL2 * (maxL2 - 1) / 2 + 1);
-  sz[DD_SS_X] = 4 * (size_t)maxL1; sz[DD_SS_Y] = 4 * (size_t)maxL2; sz[DD_ZRES] = 4 * (size_t)maxL1;
-  sz[DD_STK_X] = 4 * (size_t)(maxL1 / 2 + 4); sz[DD_STK_Y] = 4 * (size_t)(maxL2 / 2 + 4);
-  sz[DD_TAL_X] = 4 * (size_t)maxnx; sz[DD_TAL_Y] = 4 * (size_t)maxny; sz[DD_TAL_Z] = 4 * (size_t)maxnz;
-  sz[DD_SW] = 4 * (size_t)maxncbp;
-  sz[DD_BND] = 8 * (size_t)(maxL1 + 1);
+  sz[DD_BROW_Z] = 4 * (size_t)(m.L2 + 2);
+  sz[DD_TRZ] = 4 * (size_t)(m.L1 + 1) * lay.w16;
+  sz[DD_TR_X] = trb * ((size_t)m.L1 * (m.L1 - 1) / 2 + 1);
+  sz[DD_TR_Y] = trb * ((size_t)m.L2 * (m.L2 - 1) / 2 + 1);
+  sz[DD_SS_X] = 4 * (size_t)m.L1; sz[DD_SS_Y] = 4 * (size_t)m.L2; sz[DD_ZRES] = 4 * (size_t)m.L1;
+  sz[DD_STK_X] = 4 * (size_t)(m.L1 / 2 + 4); sz[DD_STK_Y] = 4 * (size_t)(m.L2 / 2 + 4);
+  sz[DD_TAL_X] = 4 * (size_t)m.nx; sz[DD_TAL_Y] = 4 * (size_t)m.ny; sz[DD_TAL_Z] = 4 * (size_t)m.nz;
+  sz[DD_SW] = 4 * (size_t)m.ncbp;
   size_t s_off = 0, g_off = 0;
   lay.in_smem = 0;
   for (int k = 0; k < DD_NITEMS; ++k) {
@@ -328,20 +320,8 @@ static void plan_layout(dafs_dd_plan* p, int maxL1, int maxL2, int maxnx, int ma
     if (s_off + b <= smem_budget) { lay.off[k] = (uint32_t)s_off; s_off += b; lay.in_smem |= 1u << k; }
     else { lay.off[k] = (uint32_t)g_off; g_off += b; }
   }
-  p->smem = (int)s_off;
+  *smem_bytes = (int)s_off;
   *ws_bytes = up16(g_off) + 256;
-}
-
-static void fill_nus(DDNus& D, const NusHost& H, char* cst, char* state, char* res) {
-  D.L = H.L; D.n = H.n; D.w = H.w;
-  D.col_ptr = reinterpret_cast<const int*>(cst + H.col_ptr);
-  D.row_ptr = reinterpret_cast<const int*>(cst + H.row_ptr);
-  D.row_ent = reinterpret_cast<const int*>(cst + H.row_ent);
-  D.ent_ij = reinterpret_cast<const uint32_t*>(cst + H.ent_ij);
-  D.ent_p = reinterpret_cast<const float*>(cst + H.ent_p);
-  D.ent_flag = reinterpret_cast<const uint8_t*>(cst + H.ent_flag);
-  D.ent_q = reinterpret_cast<float*>(state + H.ent_q);
-  D.out = reinterpret_cast<uint32_t*>(res + H.out);
 }
 
 }  // namespace dafs
@@ -360,6 +340,9 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
       return fail(DAFS_CUDA_EINVAL, "problem %d: L1=%d L2=%d outside [1, %d]", k, q.L1, q.L2, kMaxL);
     if (!q.p_x || !q.p_y || !q.p_z) return fail(DAFS_CUDA_EINVAL, "problem %d: NULL matrix", k);
     if (q.N1 < 1 || q.N2 < 1 || q.t_max < 0) return fail(DAFS_CUDA_EINVAL, "problem %d: bad N1/N2/t_max", k);
+    // q_z is kept only on c_z: with a negative step size the reference's
+    // max(0, q - eta*(1-t)) would also grow multipliers of every aligned cell.
+    if (q.eta0 < 0.0f) return fail(DAFS_CUDA_ENOTSUP, "problem %d: negative --eta is not supported", k);
   }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
@@ -386,23 +369,22 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     if (nt == 1) work();
     else { std::vector<std::thread> th; for (int k = 0; k < nt; ++k) th.emplace_back(work); for (auto& t : th) t.join(); }
   }
-  int maxL1 = 1, maxL2 = 1, maxnx = 1, maxny = 1, maxnz = 1, maxncbp = 1, maxcol = 0;
-  size_t cst = 0, state = 0, res = 0;
+  DDMaxima m;
+  size_t cst = 0, res = 0;
   for (auto& H : p->host) {
+    H.cst_base = cst; cst += H.cst.size(); cst = (cst + 255) & ~size_t(255);
     H.res_base = res; res += H.res_bytes;
-    H.cst_base = cst; cst += up16(H.cst.size()) + 240; cst = (cst + 255) & ~size_t(255);
-    H.state_base = state; state += H.state_bytes; state = (state + 255) & ~size_t(255);
-    maxL1 = std::max(maxL1, H.L1); maxL2 = std::max(maxL2, H.L2);
-    maxnx = std::max(maxnx, H.sx.n); maxny = std::max(maxny, H.sy.n);
-    maxnz = std::max(maxnz, H.nz); maxncbp = std::max(maxncbp, H.ncbp);
-    maxcol = std::max(maxcol, std::max(H.sx.max_col, H.sy.max_col));
-    p->total_cbp += H.ncbp; p->total_entries += H.sx.n + H.sy.n;
+    m.L1 = std::max(m.L1, H.L1); m.L2 = std::max(m.L2, H.L2);
+    m.nx = std::max(m.nx, H.sx.n); m.ny = std::max(m.ny, H.sy.n);
+    m.nz = std::max(m.nz, H.nz); m.ncbp = std::max(m.ncbp, H.ncbp);
+    m.col = std::max(m.col, std::max(H.sx.max_col, H.sy.max_col));
+    m.cst = std::max(m.cst, (int)H.cst.size());
+    p->total_cbp += H.ncbp; p->total_entries += H.sx.n + H.sy.n + H.nz;
   }
-  p->cst_bytes = cst; p->state_bytes = state; p->res_bytes = res;
+  p->cst_bytes = cst; p->res_bytes = res;
   PLAN_TRY(cudaMalloc(&p->d_cst, std::max<size_t>(cst, 256)));
-  PLAN_TRY(cudaMalloc(&p->d_state, std::max<size_t>(state, 256)));
   PLAN_TRY(cudaMalloc(&p->d_res, std::max<size_t>(res, 256)));
-  PLAN_TRY(cudaMalloc(&p->d_prob, sizeof(DDProblem) * nprob));
+  PLAN_TRY(cudaMalloc(&p->d_prob, sizeof(DDProbRef) * nprob));
   PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * nprob));
   {
     // one pinned staging buffer -> one H2D copy
@@ -414,22 +396,15 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     pinned_free(stage);
     PLAN_TRY(e);
   }
-  std::vector<DDProblem> dp(nprob);
+  std::vector<DDProbRef> dp(nprob);
   std::vector<int32_t> order(nprob);
   for (int k = 0; k < nprob; ++k) {
     const ProbHost& H = p->host[k];
-    char* c = p->d_cst + H.cst_base; char* s = p->d_state + H.state_base; char* r = p->d_res + H.res_base;
-    DDProblem& D = dp[k];
-    fill_nus(D.sx, H.sx, c, s, r); fill_nus(D.sy, H.sy, c, s, r);
-    D.L1 = H.L1; D.L2 = H.L2; D.nz = H.nz; D.ncbp = H.ncbp; D.t_max = H.t_max;
-    D.th_s = H.th_s; D.th_a = H.th_a; D.eta0 = H.eta0;
-    D.pz = reinterpret_cast<const float*>(c + H.pz);
-    D.qz = reinterpret_cast<float*>(s + H.qz);
-    D.env = reinterpret_cast<const uint2*>(c + H.env);
-    D.cz_ptr = reinterpret_cast<const int*>(c + H.cz_ptr);
-    D.cz_col = reinterpret_cast<const int*>(c + H.cz_col);
-    D.cz_cell = reinterpret_cast<const int*>(c + H.cz_cell);
-    D.cbp = reinterpret_cast<const int4*>(c + H.cbp);
+    char* r = p->d_res + H.res_base;
+    DDProbRef& D = dp[k];
+    D.cst = p->d_cst + H.cst_base;
+    D.x_out = reinterpret_cast<uint32_t*>(r + H.sx.out);
+    D.y_out = reinterpret_cast<uint32_t*>(r + H.sy.out);
     D.z_out = reinterpret_cast<uint32_t*>(r + H.z_out);
     D.result = reinterpret_cast<float*>(r + H.result);
     D.trace = p->want_trace ? reinterpret_cast<float*>(r + H.trace) : nullptr;
@@ -440,22 +415,18 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     return (int64_t)A.t_max * ((int64_t)A.L1 * A.L1 + (int64_t)A.L2 * A.L2 + (int64_t)A.L1 * A.L2) >
            (int64_t)B.t_max * ((int64_t)B.L1 * B.L1 + (int64_t)B.L2 * B.L2 + (int64_t)B.L1 * B.L2);
   });
-  PLAN_TRY(cudaMemcpy(p->d_prob, dp.data(), sizeof(DDProblem) * nprob, cudaMemcpyHostToDevice));
+  PLAN_TRY(cudaMemcpy(p->d_prob, dp.data(), sizeof(DDProbRef) * nprob, cudaMemcpyHostToDevice));
   PLAN_TRY(cudaMemcpy(p->d_order, order.data(), sizeof(int32_t) * nprob, cudaMemcpyHostToDevice));
 
   // geometry
-  const int need = (maxL2 + 1 + 31) / 32;
-  p->C = 16;
-  for (int c : kDDCols) if (c >= need) { p->C = c; break; }
   cudaDeviceProp prop;
   PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
   const size_t budget = (size_t)prop.sharedMemPerBlockOptin - 2048;
   size_t ws_per = 0;
-  plan_layout(p, maxL1, maxL2, maxnx, maxny, maxnz, maxncbp, maxcol, budget, &ws_per);
+  plan_layout(p->lay, m, budget, &p->smem, &ws_per);
+  PLAN_TRY(cudaFuncSetAttribute(dd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   int blocks = 0;
-#define OCC(CC) PLAN_TRY(dd_occupancy<CC>(p->smem, &blocks))
-  DD_DISPATCH(p->C, OCC)
-#undef OCC
+  PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel, DD_THREADS, p->smem));
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
   p->ctas_per_sm = blocks;
   p->grid = std::max(1, std::min(nprob, prop.multiProcessorCount * blocks));
@@ -477,11 +448,9 @@ extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
   a.prob = p->d_prob; a.order = p->d_order; a.nprob = p->nprob; a.queue = p->d_queue; a.lay = p->lay;
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  cudaError_t e = cudaSuccess;
-#define RUN(CC) e = dd_launch<CC>(a, p->grid, p->smem, p->stream)
-  DD_DISPATCH(p->C, RUN)
-#undef RUN
-  DAFS_CUDA_TRY(e);
+  DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+  dd_kernel<<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
+  DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
   return DAFS_CUDA_OK;
 }
@@ -521,6 +490,7 @@ extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
     r.violated = reinterpret_cast<const unsigned*>(rf)[2];
     r.status = reinterpret_cast<const int*>(rf)[3];
     r.ncbp = H.ncbp;
+    for (int c = 0; c < 8; ++c) r.cycles[c] = rf[4 + c];
     if (r.trace && p->want_trace)
       std::memcpy(r.trace, s + H.trace, sizeof(float) * 3 * (size_t)std::min(H.t_max, r.iters + 1));
   }
@@ -530,10 +500,10 @@ extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
 
 extern "C" int dafs_cuda_dd_plan_info(dafs_dd_plan* p, dafs_dd_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
-  info->grid = p->grid; info->block = 96; info->cols_per_lane = p->C; info->smem_bytes = p->smem;
+  info->grid = p->grid; info->block = DD_THREADS; info->cols_per_lane = 0; info->smem_bytes = p->smem;
   info->ctas_per_sm = p->ctas_per_sm; info->items_in_smem = p->lay.in_smem;
   info->workspace_bytes = (int64_t)p->lay.ws_stride * p->grid;
-  info->arena_bytes = (int64_t)(p->cst_bytes + p->state_bytes + p->res_bytes);
+  info->arena_bytes = (int64_t)(p->cst_bytes + p->res_bytes);
   info->total_cbp = p->total_cbp; info->total_entries = p->total_entries; info->last_ms = p->last_ms;
   return DAFS_CUDA_OK;
 }
@@ -561,15 +531,16 @@ namespace dafs {
 
 __global__ void __launch_bounds__(32) nussinov_single_kernel(const DDNus S, const NusScratch sc, float th,
                                                              float* score) {
-  const float v = nussinov_warp(S, sc, th, threadIdx.x);
+  const float v = nussinov_warp(S, sc, th, threadIdx.x, nullptr);
   if (threadIdx.x == 0) *score = v;
   for (int i = threadIdx.x; i < S.L; i += 32) S.out[i] = sc.ss[i];
 }
 
-template <int C>
-__global__ void __launch_bounds__(32) nw_single_kernel(const DDProblem P, uint32_t* trz, float* bnd, int* bad) {
-  const float v = nw_warp<C>(P, trz, bnd, P.z_out, threadIdx.x, bad);
-  if (threadIdx.x == 0) P.result[0] = v;
+__global__ void __launch_bounds__(32) nw_single_kernel(const DDAln A, const NwScratch sc, uint32_t* al, float* score,
+                                                       int* bad) {
+  const float v = nw_warp(A, sc, threadIdx.x, bad, nullptr);
+  if (threadIdx.x == 0) *score = v;
+  for (int i = threadIdx.x; i < A.L1; i += 32) al[i] = sc.zres[i];
 }
 
 struct DevBuf {   // one cudaMalloc, carved
@@ -652,34 +623,42 @@ extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, con
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
   std::vector<uint2> env;
   build_envelope(L1, L2, th, p, env);
-  const int need = (L2 + 1 + 31) / 32;
-  int C = 16;
-  for (int c : kDDCols) if (c >= need) { C = c; break; }
-  const int nstripes = (L2 + 1 + 32 * C - 1) / (32 * C);
-  const size_t cells = (size_t)L1 * L2;
+  // cells with p != 0 or q != 0; every other cell adds exactly 0 twice (:282)
+  std::vector<int> row_ptr(L1 + 1, 0);
+  std::vector<uint16_t> col;
+  std::vector<float> pv, qv;
+  for (int i = 0; i < L1; ++i) {
+    for (int k = 0; k < L2; ++k) {
+      const float a = p[(size_t)i * L2 + k], b = q ? q[(size_t)i * L2 + k] : 0.0f;
+      if (a != 0.0f || b != 0.0f) { col.push_back((uint16_t)k); pv.push_back(a); qv.push_back(b); }
+    }
+    row_ptr[i + 1] = (int)col.size();
+  }
+  const int n = (int)col.size(), w16 = (L2 + 15) / 16;
   DevBuf B;
-  B.size = 16 * 16 + 4 * (2 * cells + 2 * (size_t)(L1 + 1) + (size_t)(L1 + 1) * nstripes * 32 + 2 * (size_t)(L1 + 1) + L1 + 8) + 64;
+  B.size = 16 * 16 + 4 * ((size_t)(L1 + 1) * (3 + w16) + 3 * (size_t)std::max(n, 1) + (L2 + 2) + 2 * (size_t)L1 + 8) + 64;
   DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
-  DDProblem P{};
-  float* d_p = B.take<float>(cells); float* d_q = B.take<float>(cells);
+  DDAln A{}; NwScratch sc{};
+  int* d_rp = B.take<int>(L1 + 1); uint16_t* d_col = B.take<uint16_t>(n);
+  float* d_p = B.take<float>(n); float* d_q = B.take<float>(n);
   uint2* d_env = B.take<uint2>(L1 + 1);
-  uint32_t* trz = B.take<uint32_t>((size_t)(L1 + 1) * nstripes * 32);
-  float* bnd = B.take<float>(2 * (size_t)(L1 + 1));
-  uint32_t* d_al = B.take<uint32_t>(L1); float* d_res = B.take<float>(4); int* d_bad = B.take<int>(1);
-  DAFS_CUDA_TRY(cudaMemcpy(d_p, p, sizeof(float) * cells, cudaMemcpyHostToDevice));
-  if (q) DAFS_CUDA_TRY(cudaMemcpy(d_q, q, sizeof(float) * cells, cudaMemcpyHostToDevice));
-  else DAFS_CUDA_TRY(cudaMemset(d_q, 0, sizeof(float) * cells));   // v + 0.0f == v
+  sc.brow = B.take<float>(L2 + 2); sc.trz = B.take<uint32_t>((size_t)(L1 + 1) * w16); sc.zres = B.take<uint32_t>(L1);
+  sc.w16 = w16;
+  uint32_t* d_al = B.take<uint32_t>(L1); float* d_score = B.take<float>(1); int* d_bad = B.take<int>(1);
+  DAFS_CUDA_TRY(cudaMemcpy(d_rp, row_ptr.data(), sizeof(int) * (L1 + 1), cudaMemcpyHostToDevice));
+  if (n) {
+    DAFS_CUDA_TRY(cudaMemcpy(d_col, col.data(), sizeof(uint16_t) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_p, pv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
+    DAFS_CUDA_TRY(cudaMemcpy(d_q, qv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
+  }
   DAFS_CUDA_TRY(cudaMemcpy(d_env, env.data(), sizeof(uint2) * (L1 + 1), cudaMemcpyHostToDevice));
   DAFS_CUDA_TRY(cudaMemset(d_bad, 0, sizeof(int)));
-  P.L1 = L1; P.L2 = L2; P.th_a = th; P.pz = d_p; P.qz = d_q; P.env = d_env; P.z_out = d_al; P.result = d_res;
-  cudaError_t e = cudaSuccess;
-#define RUN(CC) { nw_single_kernel<CC><<<1, 32>>>(P, trz, bnd, d_bad); e = cudaGetLastError(); }
-  DD_DISPATCH(C, RUN)
-#undef RUN
-  DAFS_CUDA_TRY(e);
+  A.L1 = L1; A.L2 = L2; A.n = n; A.th = th; A.row_ptr = d_rp; A.col = d_col; A.p = d_p; A.q = d_q; A.env = d_env;
+  nw_single_kernel<<<1, 32>>>(A, sc, d_al, d_score, d_bad);
+  DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaMemcpy(al, d_al, sizeof(uint32_t) * L1, cudaMemcpyDeviceToHost));
   float sv = 0; int bad = 0;
-  DAFS_CUDA_TRY(cudaMemcpy(&sv, d_res, sizeof(float), cudaMemcpyDeviceToHost));
+  DAFS_CUDA_TRY(cudaMemcpy(&sv, d_score, sizeof(float), cudaMemcpyDeviceToHost));
   DAFS_CUDA_TRY(cudaMemcpy(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost));
   if (score) *score = sv;
   if (bad) return fail(DAFS_CUDA_ECUDA, "NW traceback met an unfilled cell (the reference does not terminate on this input)");

@@ -156,6 +156,8 @@ typedef struct dafs_dd_result {
   uint32_t violated;
   int32_t status;
   int64_t ncbp;       /* consensus-base-pair candidates enumerated (:1016-1045) */
+  float cycles[8];    /* SM cycles: x fill, x traceback, y fill, y traceback, z fill,
+                         z traceback, decode phase, tally+update phase             */
 } dafs_dd_result;
 
 /* All problems in one launch, each running its whole <= t_max iteration loop on
