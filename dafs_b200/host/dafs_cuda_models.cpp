@@ -1,0 +1,180 @@
+// See dafs_cuda_models.h.  Everything here is host glue between the reference's
+// std::vector types (src/typedefs.h:25-43) and the plain-C ABI of libdafs_cuda.
+#include "dafs_cuda_models.h"
+
+#include <algorithm>
+
+#include "dafs_cuda.h"
+
+namespace {
+
+[[noreturn]] void fail(const char* what) {
+  throw std::string(what) + ": " + dafs_cuda_last_error();
+}
+
+// One unit of a dafs_csr_batch -> MP / BP rows (vector<vector<pair<uint,float>>>).
+void unpack_unit(const dafs_csr_batch& b, int64_t u, std::vector<SV>& rows) {
+  const int64_t r0 = b.row_off[u], nrows = b.row_off[u + 1] - r0 - 1;
+  const int32_t* rp = b.row_ptr + r0;
+  const uint32_t* col = b.col + b.nz_off[u];
+  const float* val = b.val + b.nz_off[u];
+  rows.assign(nrows, SV());
+  for (int64_t r = 0; r < nrows; ++r) {
+    rows[r].reserve(rp[r + 1] - rp[r]);
+    for (int32_t k = rp[r]; k < rp[r + 1]; ++k) rows[r].push_back(std::make_pair(col[k], val[k]));
+  }
+}
+
+std::vector<float> flatten(const VVF& m, size_t cols) {
+  std::vector<float> f(m.size() * cols);
+  for (size_t i = 0; i < m.size(); ++i) std::copy(m[i].begin(), m[i].end(), f.begin() + i * cols);
+  return f;
+}
+
+}  // namespace
+
+// ---- Align::Model ---------------------------------------------------------------
+CudaProbCons::CudaProbCons(float th, int ngpu) : Align::Model(th), ngpu_(ngpu) {
+  if (dafs_cuda_init(ngpu) != DAFS_CUDA_OK) fail("dafs_cuda_init");
+}
+
+void CudaProbCons::calculate(const std::string& seq1, const std::string& seq2, MP& mp) {
+  const char* seq[2] = {seq1.data(), seq2.data()};
+  const int len[2] = {(int)seq1.size(), (int)seq2.size()};
+  const int32_t pi = 0, pj = 1;
+  dafs_csr_batch b;
+  if (dafs_cuda_pairhmm_pairs(2, seq, len, 1, &pi, &pj, threshold(), &b) != DAFS_CUDA_OK) fail("dafs_cuda_pairhmm_pairs");
+  unpack_unit(b, 0, mp);
+  dafs_cuda_free_batch(&b);
+}
+
+void CudaProbCons::calculate(const std::vector<Fasta>& fa, std::vector<std::vector<MP> >& mp) {
+  const uint N = fa.size();
+  std::vector<const char*> seq(N);
+  std::vector<int> len(N);
+  for (uint i = 0; i != N; ++i) { seq[i] = fa[i].seq().data(); len[i] = (int)fa[i].size(); }
+  dafs_csr_batch b;
+  if (dafs_cuda_pairhmm_all((int)N, seq.data(), len.data(), threshold(), ngpu_, &b) != DAFS_CUDA_OK) fail("dafs_cuda_pairhmm_all");
+  mp.resize(N, std::vector<MP>(N));
+  int64_t u = 0;
+  for (uint i = 0; i != N; ++i) {
+    mp[i][i].resize(fa[i].size());
+    for (uint x = 0; x != fa[i].size(); ++x) mp[i][i][x].push_back(std::make_pair(x, 1.0f));
+    for (uint j = i + 1; j != N; ++j) unpack_unit(b, u++, mp[i][j]);
+  }
+  dafs_cuda_free_batch(&b);
+}
+
+// ---- Fold::Model -----------------------------------------------------------------
+CudaBoltzmann::CudaBoltzmann(float th, int ngpu) : Fold::Model(th), ngpu_(ngpu) {
+  if (dafs_cuda_init(ngpu) != DAFS_CUDA_OK) fail("dafs_cuda_init");
+}
+
+void CudaBoltzmann::calculate(const std::string& seq, BP& bp) {
+  const char* s[1] = {seq.data()};
+  const int len[1] = {(int)seq.size()};
+  dafs_csr_batch b;
+  if (dafs_cuda_mccaskill_all(1, s, len, threshold(), ngpu_, &b) != DAFS_CUDA_OK) fail("dafs_cuda_mccaskill_all");
+  unpack_unit(b, 0, bp);
+  dafs_cuda_free_batch(&b);
+}
+
+void CudaBoltzmann::calculate(const std::string&, const std::string&, BP&) { throw "not supported"; }
+
+void CudaBoltzmann::calculate(const std::vector<Fasta>& fa, std::vector<BP>& bp) {
+  const uint N = fa.size();
+  std::vector<const char*> seq(N);
+  std::vector<int> len(N);
+  for (uint i = 0; i != N; ++i) { seq[i] = fa[i].seq().data(); len[i] = (int)fa[i].size(); }
+  dafs_csr_batch b;
+  if (dafs_cuda_mccaskill_all((int)N, seq.data(), len.data(), threshold(), ngpu_, &b) != DAFS_CUDA_OK) fail("dafs_cuda_mccaskill_all");
+  bp.resize(N);
+  for (uint i = 0; i != N; ++i) unpack_unit(b, i, bp[i]);
+  dafs_cuda_free_batch(&b);
+}
+
+// ---- decoders ----------------------------------------------------------------------
+float CudaNussinov::decode(float w, const VVF& p, const VVF& q, VU& ss) {
+  const int L = (int)p.size();
+  std::vector<float> fp = flatten(p, L), fq = flatten(q, L);
+  ss.resize(L);
+  float s = 0;
+  if (dafs_cuda_nussinov_decode(L, th_, w, fp.data(), fq.data(), ss.data(), &s) != DAFS_CUDA_OK) fail("dafs_cuda_nussinov_decode");
+  return s;
+}
+
+float CudaNussinov::decode(const VVF& p, VU& ss, std::string& str) {
+  const int L = (int)p.size();
+  std::vector<float> fp = flatten(p, L);
+  ss.resize(L);
+  float s = 0;
+  if (dafs_cuda_nussinov_decode(L, th_, 1.0f, fp.data(), nullptr, ss.data(), &s) != DAFS_CUDA_OK) fail("dafs_cuda_nussinov_decode");
+  make_brackets(ss, str);
+  return s;
+}
+
+void CudaNussinov::make_brackets(const VU& ss, std::string& str) const {   // src/nussinov.cpp:395-413
+  str.assign(ss.size(), '.');
+  for (uint i = 0; i != ss.size(); ++i)
+    if (ss[i] != -1u) { str[i] = Fold::Decoder::left_brackets[0]; str[ss[i]] = Fold::Decoder::right_brackets[0]; }
+}
+
+float CudaNeedlemanWunsch::decode(const VVF& p, const VVF& q, VU& al) const {
+  const int L1 = (int)p.size(), L2 = (int)p[0].size();
+  std::vector<float> fp = flatten(p, L2), fq = flatten(q, L2);
+  al.resize(L1);
+  float s = 0;
+  if (dafs_cuda_nw_decode(L1, L2, th_, fp.data(), fq.data(), al.data(), &s) != DAFS_CUDA_OK) fail("dafs_cuda_nw_decode");
+  return s;
+}
+
+float CudaNeedlemanWunsch::decode(const VVF& p, VU& al) const {
+  const int L1 = (int)p.size(), L2 = (int)p[0].size();
+  std::vector<float> fp = flatten(p, L2);
+  al.resize(L1);
+  float s = 0;
+  if (dafs_cuda_nw_decode(L1, L2, th_, fp.data(), nullptr, al.data(), &s) != DAFS_CUDA_OK) fail("dafs_cuda_nw_decode");
+  return s;
+}
+
+// ---- dual decomposition ---------------------------------------------------------------
+namespace dafs_cuda {
+
+void solve_by_dd_batch(const DDOptions& o, const std::vector<DDInput>& in, std::vector<DDOutput>& out) {
+  const size_t n = in.size();
+  std::vector<std::vector<float> > fx(n), fy(n), fz(n);
+  std::vector<dafs_dd_problem> prob(n);
+  std::vector<dafs_dd_result> res(n);
+  out.resize(n);
+  const float min_th_s = *std::min_element(o.th_s.begin(), o.th_s.end());   // src/dafs.cpp:1018
+  for (size_t k = 0; k < n; ++k) {
+    const int L1 = (int)in[k].p_x->size(), L2 = (int)in[k].p_y->size();
+    fx[k] = flatten(*in[k].p_x, L1); fy[k] = flatten(*in[k].p_y, L2); fz[k] = flatten(*in[k].p_z, L2);
+    dafs_dd_problem& q = prob[k];
+    q.L1 = L1; q.L2 = L2; q.N1 = (int)in[k].n1; q.N2 = (int)in[k].n2;
+    q.p_x = fx[k].data(); q.p_y = fy[k].data(); q.p_z = fz[k].data();
+    q.w = o.w; q.th_s = o.th_s[0]; q.min_th_s = min_th_s; q.th_a = o.th_a; q.eta0 = o.eta0; q.t_max = (int)o.t_max;
+    out[k].x.assign(L1, -1u); out[k].y.assign(L2, -1u); out[k].z.assign(L1, -1u);
+    res[k] = dafs_dd_result();
+    res[k].x = out[k].x.data(); res[k].y = out[k].y.data(); res[k].z = out[k].z.data();
+  }
+  if (dafs_cuda_dd_solve_batch((int)n, prob.data(), res.data()) != DAFS_CUDA_OK) fail("dafs_cuda_dd_solve_batch");
+  for (size_t k = 0; k < n; ++k) {
+    if (res[k].status != 0) throw std::string("dafs_cuda_dd_solve_batch: alignment traceback left the envelope");
+    out[k].outcome.score = res[k].score; out[k].outcome.iters = (unsigned)res[k].iters;
+    out[k].outcome.violated = res[k].violated;
+  }
+}
+
+DDOutcome solve_by_dd(const DDOptions& o, VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y,
+                      const VVF& p_z, const ALN& aln1, const ALN& aln2) {
+  std::vector<DDInput> in(1);
+  in[0].p_x = &p_x; in[0].p_y = &p_y; in[0].p_z = &p_z;
+  in[0].n1 = (unsigned)aln1.size(); in[0].n2 = (unsigned)aln2.size();                // src/dafs.cpp:1013-1014
+  std::vector<DDOutput> out;
+  solve_by_dd_batch(o, in, out);
+  x.swap(out[0].x); y.swap(out[0].y); z.swap(out[0].z);
+  return out[0].outcome;
+}
+
+}  // namespace dafs_cuda

@@ -1,0 +1,94 @@
+// C++ adapters that put libdafs_cuda behind the reference's own interfaces, so
+// the `dafs` driver (src/dafs.cpp) keeps every call site:
+//   CudaProbCons          : Align::Model    (src/align.h:37-55)   replaces ProbCons   (src/align.cpp:54-79)
+//   CudaBoltzmann         : Fold::Model     (src/fold.h:33-45)    replaces RNAfold(bl=true) (src/fold.cpp:70-116)
+//   CudaNussinov          : Fold::Decoder   (src/fold.h:47-60)    replaces SparseNussinov (src/nussinov.cpp:207-413)
+//   CudaNeedlemanWunsch   : Align::Decoder  (src/align.h:57-65)   replaces SparseNeedlemanWunsch (src/needleman_wunsch.cpp:198-422)
+//   dafs_cuda::solve_by_dd, solve_by_dd_batch                     replace DAFS::solve_by_dd (src/dafs.cpp:1006-1295)
+// This header is compiled inside the reference tree (it includes align.h and
+// fold.h from there); see INTEGRATION.md for the three-line patch of
+// DAFS::parse_options / DAFS::solve_by_dd.  Errors from the C ABI are re-thrown
+// as std::string, which main() already catches (src/dafs.cpp:1898-1909).
+#ifndef DAFS_CUDA_MODELS_H_
+#define DAFS_CUDA_MODELS_H_
+
+#include <string>
+#include <vector>
+
+#include "align.h"
+#include "fold.h"
+#include "typedefs.h"
+
+class CudaProbCons : public Align::Model {
+ public:
+  explicit CudaProbCons(float th, int ngpu = 0);
+  // one pair = a batch of one (same result as ProbCons::calculate)
+  void calculate(const std::string& seq1, const std::string& seq2, MP& mp) override;
+  // all i<j pairs in one device call; fills mp[i][i] with the identity exactly
+  // like Align::Model::calculate (src/align.cpp:35-52)
+  void calculate(const std::vector<Fasta>& fa, std::vector<std::vector<MP> >& mp) override;
+
+ private:
+  int ngpu_;
+};
+
+class CudaBoltzmann : public Fold::Model {
+ public:
+  explicit CudaBoltzmann(float th, int ngpu = 0);
+  void calculate(const std::string& seq, BP& bp) override;
+  // constrained folding (--bp-update, --ipknot) is not offered on the device:
+  // throws "not supported" like AUXFold does (src/fold.cpp:220)
+  void calculate(const std::string& seq, const std::string& str, BP& bp) override;
+  void calculate(const std::vector<Fasta>& fa, std::vector<BP>& bp) override;
+
+ private:
+  int ngpu_;
+};
+
+class CudaNussinov : public Fold::Decoder {
+ public:
+  explicit CudaNussinov(float th) : Fold::Decoder(), th_(th) {}
+  float decode(float w, const VVF& p, const VVF& q, VU& ss) override;
+  float decode(const VVF& p, VU& ss, std::string& str) override;
+  void make_brackets(const VU& ss, std::string& str) const override;
+
+ private:
+  float th_;
+};
+
+class CudaNeedlemanWunsch : public Align::Decoder {
+ public:
+  explicit CudaNeedlemanWunsch(float th) : Align::Decoder(), th_(th) {}
+  void initialize(const VVF& p) override {}   // the envelope is rebuilt inside each device call
+  float decode(const VVF& p, const VVF& q, VU& al) const override;
+  float decode(const VVF& p, VU& al) const override;
+
+ private:
+  float th_;
+};
+
+namespace dafs_cuda {
+
+struct DDOptions {        // the DAFS members solve_by_dd reads (src/dafs.cpp:126-135)
+  float w;                // w_      (-w)
+  VF th_s;                // th_s_   (-t)
+  float th_a;             // th_a_   (-u)
+  float eta0;             // eta0_   (--eta)
+  unsigned t_max;         // t_max_  (-m)
+};
+
+struct DDOutcome { float score; unsigned iters; unsigned violated; };
+
+// Drop-in body for DAFS::solve_by_dd: same arguments, same return value; iters and
+// violated are what it logs at src/dafs.cpp:1292.
+DDOutcome solve_by_dd(const DDOptions& o, VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y,
+                      const VVF& p_z, const ALN& aln1, const ALN& aln2);
+
+// Independent problems (sibling guide-tree nodes) in one device launch.
+struct DDInput { const VVF* p_x; const VVF* p_y; const VVF* p_z; unsigned n1, n2; };
+struct DDOutput { VU x, y, z; DDOutcome outcome; };
+void solve_by_dd_batch(const DDOptions& o, const std::vector<DDInput>& in, std::vector<DDOutput>& out);
+
+}  // namespace dafs_cuda
+
+#endif  // DAFS_CUDA_MODELS_H_

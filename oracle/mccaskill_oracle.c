@@ -1,0 +1,350 @@
+/* TEST INFRASTRUCTURE ONLY -- the product (libdafs_cuda) never links, loads or
+ * calls anything in oracle/.  Only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py may use it, as the checker.
+ *
+ * CPU restatement (FP64, scaled like ViennaRNA) of what RNAfold::calculate
+ * (src/fold.cpp:78-116) obtains from ViennaRNA's pf_fold + export_bppm: McCaskill
+ * inside/outside base-pairing probabilities under the "Boltzmann" model, i.e.
+ * ViennaRNA 2.4.18 defaults (pinned by the reference's Dockerfile:21: dangles = 2,
+ * special hairpins on, no lonely-pair filter, 37 C, TURN 3, MAXLOOP 30) with the
+ * BL* tables that copy_boltzmann_parameters() pokes into ViennaRNA's globals
+ * (src/boltzmann_param.c:6010-6026).
+ *
+ * PARITY UNPINNED.  ViennaRNA is a third-party dependency that is absent from
+ * /root/reference and from this box; the reference has no
+ * golden vector at this boundary.  This file restates the published algorithm
+ * (McCaskill 1990; ViennaRNA part_func.c / loop_energies.h as of 2.4.x) and is
+ * validated only by self-consistency: exhaustive structure enumeration for short
+ * sequences (oracle_mccaskill_bruteforce below) and outside/inside identities.
+ * Tables the reference leaves at ViennaRNA's Turner-2004 defaults, which are not
+ * available here, are substituted as follows and flagged in DESIGN.md:
+ *   mismatchM / mismatchExt [t][a][b] := dangle5[t][a] + dangle3[t][b]  (what
+ *       ViennaRNA's own conversion of 1.8-format parameter files does, and what
+ *       1.8 computes with dangles = 2)
+ *   mismatch1nI, mismatch23I := mismatchI           (same conversion rule)
+ *   Triloops, Hexaloops      := none                (BL* has no such tables)
+ *   lxc37 := 107.856 (only for hairpins longer than 30)
+ * pf_scale: the reference derives it from an MFE run (fold.cpp:86-95); base-pair
+ * probabilities do not depend on it, so this file estimates ln Z / L by a first
+ * inside pass in long double and needs no MFE code.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <strings.h>
+
+#define TURN 3
+#define MAXLOOP 30
+#define NBPAIRS 7
+#define INF_E 10000000
+#define K0 273.15
+#define GASCONST 1.98717
+#define LXC37 107.856
+
+typedef struct {
+  int stack[8][8], mismatchH[8][5][5], mismatchI[8][5][5], dangle5[8][5], dangle3[8][5];
+  int int11[8][8][5][5], int21[8][8][5][5][5], int22[8][8][5][5][5][5];
+  int hairpin[31], bulge[31], internal[31];
+  int ml_base, ml_closing, ml_intern, terminalAU, ninio, max_ninio;
+  int ntetra; char tetra[64][8]; int tetra_e[64];
+} energy_t;
+
+typedef struct {
+  double kT;
+  double stack[8][8], mismatchH[8][5][5], mismatchI[8][5][5], mismatchM[8][5][5], mismatchExt[8][5][5];
+  double dangle5[8][5], dangle3[8][5];
+  double int11[8][8][5][5], int21[8][8][5][5][5], int22[8][8][5][5][5][5];
+  double hairpin[31], bulge[31], internal[31], ninio[MAXLOOP + 1];
+  double ml_base, ml_closing, ml_intern, termAU, lxc;
+  double tetra[64];
+  const energy_t* E;
+} boltz_t;
+
+static energy_t g_E;
+static boltz_t g_B;
+static int g_loaded = 0;
+
+/* blob layout: tools/extract_blstar.py (order of boltzmann_param.c:5908-6026) */
+int oracle_mccaskill_load(const char* path) {
+  FILE* f = fopen(path, "rb");
+  if (!f) return -1;
+  int32_t* d = (int32_t*)malloc(sizeof(int32_t) * 32768);
+  const size_t n = fread(d, sizeof(int32_t), 32768, f);
+  fclose(f);
+  if (n < 20000 || d[0] != 0x424C5331) { free(d); return -2; }
+  size_t p = 1;
+  energy_t* E = &g_E;
+  memset(E, 0, sizeof *E);
+  for (int i = 1; i <= 7; i++) for (int j = 1; j <= 7; j++) E->stack[i][j] = d[p++];
+  for (int i = 1; i <= 7; i++) for (int a = 0; a < 5; a++) for (int b = 0; b < 5; b++) E->mismatchH[i][a][b] = d[p++];
+  for (int i = 1; i <= 7; i++) for (int a = 0; a < 5; a++) for (int b = 0; b < 5; b++) E->mismatchI[i][a][b] = d[p++];
+  for (int i = 0; i <= 7; i++) for (int a = 0; a < 5; a++) E->dangle5[i][a] = d[p++];
+  for (int i = 0; i <= 7; i++) for (int a = 0; a < 5; a++) E->dangle3[i][a] = d[p++];
+  for (int i = 1; i <= 7; i++) for (int j = 1; j <= 7; j++) for (int a = 0; a < 5; a++) for (int b = 0; b < 5; b++) E->int11[i][j][a][b] = d[p++];
+  for (int i = 1; i <= 7; i++) for (int j = 1; j <= 7; j++) for (int a = 0; a < 5; a++) for (int b = 0; b < 5; b++) for (int c = 0; c < 5; c++) E->int21[i][j][a][b][c] = d[p++];
+  for (int i = 1; i <= 7; i++) for (int j = 1; j <= 7; j++) for (int a = 1; a < 5; a++) for (int b = 1; b < 5; b++) for (int c = 1; c < 5; c++) for (int e = 1; e < 5; e++) E->int22[i][j][a][b][c][e] = d[p++];
+  for (int i = 0; i < 31; i++) E->hairpin[i] = d[p++];
+  for (int i = 0; i < 31; i++) E->bulge[i] = d[p++];
+  for (int i = 0; i < 31; i++) E->internal[i] = d[p++];
+  E->ml_base = d[p++]; E->ml_closing = d[p++]; E->ml_intern = d[p++]; E->terminalAU = d[p++];
+  E->ninio = d[p++]; E->max_ninio = d[p++];
+  E->ntetra = d[p++];
+  for (int t = 0; t < E->ntetra; t++) {
+    for (int c = 0; c < 6; c++) E->tetra[t][c] = (char)d[p++];
+    E->tetra[t][6] = 0;
+    E->tetra_e[t] = d[p++];
+  }
+  free(d);
+  /* Boltzmann factors at 37 C (ViennaRNA get_scaled_pf_parameters: at the
+   * measurement temperature every G(T) equals its 37 C value) */
+  boltz_t* B = &g_B;
+  memset(B, 0, sizeof *B);
+  B->E = E;
+  B->kT = (37.0 + K0) * GASCONST;                       /* cal/mol */
+#define BF(e) exp(-(double)(e) * 10.0 / B->kT)
+  for (int i = 0; i <= 7; i++) for (int j = 0; j <= 7; j++) B->stack[i][j] = BF(E->stack[i][j]);
+  for (int i = 0; i <= 7; i++) for (int a = 0; a < 5; a++) {
+    B->dangle5[i][a] = BF(E->dangle5[i][a]); B->dangle3[i][a] = BF(E->dangle3[i][a]);
+    for (int b = 0; b < 5; b++) {
+      B->mismatchH[i][a][b] = BF(E->mismatchH[i][a][b]);
+      B->mismatchI[i][a][b] = BF(E->mismatchI[i][a][b]);
+      /* substitution, see header */
+      const int mm = E->dangle5[i][a] + E->dangle3[i][b];
+      B->mismatchM[i][a][b] = BF(mm);
+      B->mismatchExt[i][a][b] = BF(mm);
+    }
+  }
+  for (int i = 0; i <= 7; i++) for (int j = 0; j <= 7; j++) for (int a = 0; a < 5; a++) for (int b = 0; b < 5; b++) {
+    B->int11[i][j][a][b] = BF(E->int11[i][j][a][b]);
+    for (int c = 0; c < 5; c++) {
+      B->int21[i][j][a][b][c] = BF(E->int21[i][j][a][b][c]);
+      for (int e = 0; e < 5; e++) B->int22[i][j][a][b][c][e] = BF(E->int22[i][j][a][b][c][e]);
+    }
+  }
+  for (int i = 0; i < 31; i++) {
+    B->hairpin[i] = E->hairpin[i] >= INF_E ? 0.0 : BF(E->hairpin[i]);
+    B->bulge[i] = E->bulge[i] >= INF_E ? 0.0 : BF(E->bulge[i]);
+    B->internal[i] = E->internal[i] >= INF_E ? 0.0 : BF(E->internal[i]);
+  }
+  for (int k = 0; k <= MAXLOOP; k++) {
+    const int e = k * E->ninio < E->max_ninio ? k * E->ninio : E->max_ninio;
+    B->ninio[k] = BF(e);
+  }
+  B->ml_base = BF(E->ml_base); B->ml_closing = BF(E->ml_closing); B->ml_intern = BF(E->ml_intern);
+  B->termAU = BF(E->terminalAU);
+  B->lxc = LXC37;
+  for (int t = 0; t < E->ntetra; t++) B->tetra[t] = BF(E->tetra_e[t]);
+#undef BF
+  g_loaded = 1;
+  return 0;
+}
+
+/* ViennaRNA encoding: A C G U -> 1 2 3 4 (T counts as U, case-insensitive), other 0 */
+static int enc(char c) {
+  switch (c) {
+    case 'A': case 'a': return 1;
+    case 'C': case 'c': return 2;
+    case 'G': case 'g': return 3;
+    case 'U': case 'u': case 'T': case 't': return 4;
+    default: return 0;
+  }
+}
+/* pair types CG 1, GC 2, GU 3, UG 4, AU 5, UA 6 */
+static const int k_pair[5][5] = {{0, 0, 0, 0, 0}, {0, 0, 0, 0, 5}, {0, 0, 0, 1, 0}, {0, 0, 2, 0, 3}, {0, 6, 0, 4, 0}};
+static const int k_rtype[8] = {0, 2, 1, 4, 3, 6, 5, 7};
+
+/* ---- loop weights (unscaled Boltzmann factors); S is 1-based ------------------ */
+/* exp_E_Hairpin: u unpaired, closing type, neighbours S[i+1], S[j-1]; seq6 = the
+ * six letters i..i+5 (only looked at when u == 4). */
+static double w_hairpin(const boltz_t* B, int u, int type, int si1, int sj1, const char* seq_i) {
+  double q = (u <= 30) ? B->hairpin[u] : B->hairpin[30] * exp(-(B->lxc * log(u / 30.0)) * 10.0 / B->kT);
+  if (u < 3) return q;
+  if (u == 4) {
+    for (int t = 0; t < B->E->ntetra; t++)
+      if (strncasecmp(B->E->tetra[t], seq_i, 6) == 0) {   /* sequences are upper-cased RNA in ViennaRNA */
+        if (type != 7) return B->tetra[t];
+        q *= B->tetra[t];
+        break;
+      }
+  } else if (u == 3) {
+    return (type > 2) ? q * B->termAU : q;
+  }
+  return q * B->mismatchH[type][si1][sj1];
+}
+
+/* exp_E_IntLoop: u1 unpaired 5' side, u2 3' side, type = (i,j), type2 = rtype of
+ * (k,l); si1 = S[i+1], sj1 = S[j-1], sp1 = S[k-1], sq1 = S[l+1]. */
+static double w_interior(const boltz_t* B, int u1, int u2, int type, int type2, int si1, int sj1, int sp1, int sq1) {
+  const int ul = u1 > u2 ? u1 : u2, us = u1 > u2 ? u2 : u1;
+  if (ul == 0) return B->stack[type][type2];
+  if (us == 0) {
+    double z = B->bulge[ul];
+    if (ul == 1) z *= B->stack[type][type2];
+    else { if (type > 2) z *= B->termAU; if (type2 > 2) z *= B->termAU; }
+    return z;
+  }
+  if (us == 1) {
+    if (ul == 1) return B->int11[type][type2][si1][sj1];
+    if (ul == 2) return (u1 == 1) ? B->int21[type][type2][si1][sq1][sj1] : B->int21[type2][type][sq1][si1][sp1];
+    /* 1xn: mismatch1nI := mismatchI (header) */
+    return B->internal[ul + us] * B->mismatchI[type][si1][sj1] * B->mismatchI[type2][sq1][sp1] * B->ninio[ul - us];
+  }
+  if (us == 2 && ul == 2) return B->int22[type][type2][si1][sp1][sq1][sj1];
+  /* 2x3 (mismatch23I := mismatchI) and generic */
+  return B->internal[ul + us] * B->mismatchI[type][si1][sj1] * B->mismatchI[type2][sq1][sp1] * B->ninio[ul - us];
+}
+
+/* exp_E_MLstem / exp_E_ExtLoop with dangles = 2: si1 / sj1 = the unpaired
+ * neighbours outside the stem (-1 beyond the sequence ends). */
+static double w_stem(const boltz_t* B, int type, int si1, int sj1, int multi) {
+  double e = 1.0;
+  if (si1 >= 0 && sj1 >= 0) e = multi ? B->mismatchM[type][si1][sj1] : B->mismatchExt[type][si1][sj1];
+  else if (si1 >= 0) e = B->dangle5[type][si1];
+  else if (sj1 >= 0) e = B->dangle3[type][sj1];
+  if (type > 2) e *= B->termAU;
+  if (multi) e *= B->ml_intern;
+  return e;
+}
+
+/* ---- exhaustive enumeration (short sequences) ------------------------------------
+ * Sums the Boltzmann weights of every secondary structure (hairpins >= TURN,
+ * interior loops <= MAXLOOP) by recursing over loops, independent of the DP
+ * recursions below.  P[i*n+j] (0-based, i<j) receives pair probabilities. */
+typedef struct { int n; const int* S; const char* seq; int* pt; double Z; double* acc; } bf_t;
+
+static double bf_weight(const bf_t* b) {
+  /* weight of the structure in pt[] (1-based, pt[i] = partner or 0) */
+  const boltz_t* B = &g_B;
+  const int n = b->n; const int* S = b->S; const int* pt = b->pt;
+  double w = 1.0;
+  for (int i = 1; i <= n; i++) {            /* exterior stems */
+    if (pt[i] > i) {
+      /* is (i, pt[i]) exterior?  it is if no pair encloses it */
+      int enclosed = 0;
+      for (int p = 1; p < i; p++) if (pt[p] > pt[i]) { enclosed = 1; break; }
+      if (!enclosed) {
+        const int j = pt[i];
+        w *= w_stem(B, k_pair[S[i]][S[j]], i > 1 ? S[i - 1] : -1, j < n ? S[j + 1] : -1, 0);
+      }
+    }
+  }
+  for (int i = 1; i <= n; i++) {
+    const int j = pt[i];
+    if (j <= i) continue;
+    const int type = k_pair[S[i]][S[j]];
+    /* loop closed by (i,j): collect inner stems */
+    int cnt = 0, k1 = 0, l1 = 0, unp = 0;
+    double stems = 1.0;
+    for (int p = i + 1; p < j;) {
+      if (pt[p] > p) {
+        if (cnt == 0) { k1 = p; l1 = pt[p]; }
+        stems *= w_stem(B, k_pair[S[p]][S[pt[p]]], S[p - 1], S[pt[p] + 1], 1);
+        cnt++; p = pt[p] + 1;
+      } else { unp++; p++; }
+    }
+    if (cnt == 0) w *= w_hairpin(B, j - i - 1, type, S[i + 1], S[j - 1], b->seq + i - 1);
+    else if (cnt == 1) w *= w_interior(B, k1 - i - 1, j - l1 - 1, type, k_rtype[k_pair[S[k1]][S[l1]]], S[i + 1], S[j - 1], S[k1 - 1], S[l1 + 1]);
+    else w *= B->ml_closing * w_stem(B, k_rtype[type], S[j - 1], S[i + 1], 1) * stems * pow(B->ml_base, unp);
+  }
+  return w;
+}
+
+static void bf_rec(bf_t* b, int pos) {
+  const int n = b->n;
+  while (pos <= n && b->pt[pos] != 0) pos++;
+  if (pos > n) {
+    const double w = bf_weight(b);
+    b->Z += w;
+    for (int i = 1; i <= n; i++) if (b->pt[i] > i) b->acc[(size_t)(i - 1) * n + b->pt[i] - 1] += w;
+    return;
+  }
+  /* pos unpaired */
+  b->pt[pos] = -1;
+  bf_rec(b, pos + 1);
+  b->pt[pos] = 0;
+  for (int j = pos + TURN + 1; j <= n; j++) {
+    if (b->pt[j] != 0 || !k_pair[b->S[pos]][b->S[j]]) continue;
+    /* non-crossing: positions < pos are all decided, so a decided position q in
+     * (pos, j) is the right end of a pair opened before pos -- it would cross. */
+    int ok = 1;
+    for (int q = pos + 1; q < j && ok; q++) if (b->pt[q] > 0) ok = 0;
+    if (!ok) continue;
+    b->pt[pos] = j; b->pt[j] = pos;
+    bf_rec(b, pos + 1);
+    b->pt[pos] = 0; b->pt[j] = 0;
+  }
+}
+
+/* interior loops longer than MAXLOOP are not part of ViennaRNA's ensemble */
+static int bf_loops_ok(const int* pt, int n) {
+  for (int i = 1; i <= n; i++) {
+    const int j = pt[i];
+    if (j <= i) continue;
+    int cnt = 0, unp = 0;
+    for (int p = i + 1; p < j;) { if (pt[p] > p) { cnt++; p = pt[p] + 1; } else { unp++; p++; } }
+    if (cnt == 1 && unp > MAXLOOP) return 0;
+  }
+  return 1;
+}
+
+double oracle_mccaskill_bruteforce(const char* seq, int n, double* P) {
+  if (!g_loaded || n > 24) return -1.0;
+  int* S = (int*)calloc(n + 2, sizeof(int));
+  int* pt = (int*)calloc(n + 2, sizeof(int));
+  for (int i = 1; i <= n; i++) S[i] = enc(seq[i - 1]);
+  bf_t b = {n, S, seq, pt, 0.0, P};
+  memset(P, 0, sizeof(double) * (size_t)n * n);
+  (void)bf_loops_ok;   /* n <= 24 < MAXLOOP: every loop is admissible */
+  bf_rec(&b, 1);
+  for (size_t c = 0; c < (size_t)n * n; c++) P[c] /= b.Z;
+  free(pt); free(S);
+  return b.Z;
+}
+
+/* ---- the DP, instantiated in double (what ViennaRNA computes in) and in long
+ * double (only to find a safe pf_scale without an MFE run) ----------------------- */
+static double logr_d(double x) { return log(x); }
+static long double logr_ld(long double x) { return logl(x); }
+#define REAL double
+#define FN(name) name##_d
+#include "mccaskill_dp.inc"
+#undef REAL
+#undef FN
+#define REAL long double
+#define FN(name) name##_ld
+#include "mccaskill_dp.inc"
+#undef REAL
+#undef FN
+
+/* ln Z via the long-double inside pass with ViennaRNA's default per-nucleotide
+ * scale exp(-(-185)/kT*... ) ~ 1.35 */
+double oracle_mccaskill_lnz(const char* seq, int n) {
+  if (!g_loaded) return NAN;
+  return mccaskill_ld(seq, n, exp(185.0 * 10.0 / g_B.kT / 10.0), NULL);
+}
+
+/* Dense P[n*n] (0-based, only i<j set) in FP64 with pf_scale = exp(lnZ/n), and
+ * RNAfold::calculate's read-out (fold.cpp:108-114): float(p) > th kept. */
+double oracle_mccaskill(const char* seq, int n, double* P) {
+  if (!g_loaded) return NAN;
+  const double lnz = n > 400 ? mccaskill_ld(seq, n, 1.35, NULL) : mccaskill_d(seq, n, 1.35, NULL);
+  return mccaskill_d(seq, n, exp(lnz / n), P);
+}
+
+int oracle_mccaskill_csr(const char* seq, int n, float th, int32_t* row_ptr, uint32_t* col, float* val) {
+  double* P = (double*)malloc(sizeof(double) * (size_t)n * n);
+  oracle_mccaskill(seq, n, P);
+  int nnz = 0;
+  for (int i = 0; i < n; i++) {
+    row_ptr[i] = nnz;
+    for (int j = i + 1; j < n; j++) {
+      const float p = (float)P[(size_t)i * n + j];
+      if (p > th) { col[nnz] = (uint32_t)j; val[nnz] = p; nnz++; }
+    }
+  }
+  row_ptr[n] = nnz;
+  free(P);
+  return nnz;
+}
