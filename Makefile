@@ -4,9 +4,14 @@ ARCH := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := -O3 -std=c++17 -lineinfo $(ARCH) -Xcompiler -fPIC,-O2,-pthread,-ffp-contract=off -Xptxas -v --fmad=false
 CSRC := dafs_b200/csrc
 LIB := dafs_b200/libdafs_cuda.so
-OBJS := $(CSRC)/common.o $(CSRC)/pairhmm.o $(CSRC)/dd.o
+OBJS := $(CSRC)/common.o $(CSRC)/pairhmm.o $(CSRC)/dd.o $(CSRC)/mccaskill.o
 
 all: $(LIB) oracle
+
+$(CSRC)/blstar37.inc: dafs_b200/data/blstar37.i32 tools/bin2inc.py
+	python3 tools/bin2inc.py $< $@
+
+$(CSRC)/mccaskill.o: $(CSRC)/blstar37.inc
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh) include/dafs_cuda.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $@.ptxas.log || (cat $@.ptxas.log; false)
@@ -18,6 +23,6 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -f $(OBJS) $(LIB) $(CSRC)/*.ptxas.log
+	rm -f $(OBJS) $(LIB) $(CSRC)/*.ptxas.log $(CSRC)/blstar37.inc
 	$(MAKE) -C oracle clean
 .PHONY: all oracle clean

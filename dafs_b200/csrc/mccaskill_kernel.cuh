@@ -1,0 +1,307 @@
+// K3/K4: McCaskill inside / outside base-pairing probabilities in scaled FP64,
+// one CTA per sequence (persistent grid, atomic queue), span-length diagonals
+// separated by one block barrier each.  Replaces what RNAfold::calculate
+// (src/fold.cpp:78-116) gets from ViennaRNA's pf_fold + export_bppm, including
+// its read-out: float(p) > th kept, rows i < j, ascending j (:108-114).
+//
+// Quantities (1-based, W = n_max + 2 row stride):
+//   qb(i,j)  = hairpin + sum interior + MLclose(i,j) * sum_k qm(i+1,k-1) * qm1(k,j-1)
+//   qm1(i,j) = qm1(i,j-1)*mlb + qb(i,j)*MLstem(i,j)           (ViennaRNA's rolling qqm)
+//   qm(i,j)  = sum_{k=i..j} (mlb^(k-i) + qm(i,k-1)) * qm1(k,j)
+//   qq(i,j)  = qq(i,j-1)*sc + qb(i,j)*Ext(i,j)                (ViennaRNA's rolling qq)
+//   q(i,j)   = sc^(j-i+1) + qq(i,j) + sum_{k=i..j-1} q(i,k) * qq(k+1,j)
+//   O(i,j)   = q(1,i-1)*q(j+1,n)*Ext(i,j) + sum_{interior (p,q)} O(p,q)*wI*sc^(..)
+//            + MLstem(i,j) * sum_{p<i} [ prm_l(p,j)*qm(p+1,i-1) + prml(p,j)*(mlb^(i-p-1) + qm(p+1,i-1)) ]
+//   prm_l(p,j) = prm_l(p,j+1)*mlb + OM(p,j+1),  prml(p,j) = sum_{q>j+1} OM(p,q)*qm(j+1,q-1),
+//   OM = O*MLclose*sc^2,   P(i,j) = qb*O / q(1,n).
+// Every O(span) inner sum runs over one index with a warp striding it; arrays
+// that are read along their first index are kept transposed (qm1T, qqT, qmT,
+// prmlT, prm_lT) so that all of those reads are coalesced.
+#pragma once
+#include "mccaskill_model.cuh"
+
+namespace dafs {
+
+struct McArgs {
+  const uint8_t* seq;          // nucleotide codes 0..4, concatenated
+  const int64_t* seq_off;      // [nseq]
+  const int32_t* seq_len;      // [nseq]
+  const int32_t* order;        // queue position -> sequence (longest first)
+  int nseq;
+  int W;                       // row stride of the DP arrays = max n + 2
+  float th;
+  const McTables* tab;         // in HBM; staged to shared memory by every CTA
+  double* ws;                  // per-CTA workspace: 10 arrays of W*W doubles
+  size_t ws_stride;            // doubles per CTA
+  int* queue;
+  // outputs
+  const int64_t* row_off;      // [nseq+1] start of each sequence's row_ptr block (n+1 entries)
+  int32_t* row_ptr;
+  const int64_t* pool_off;     // [nseq+1] start of each sequence's region in pool_col / pool_val
+  uint32_t* pool_col;
+  float* pool_val;
+  int32_t* seq_nnz;            // [nseq]
+  double* seq_lnz;             // [nseq] ln Z (diagnostic, = -G_ensemble/kT)
+};
+
+#define MC_THREADS 512
+#define MC_WARPS (MC_THREADS / 32)
+
+__device__ __forceinline__ double mc_warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+struct McWs {
+  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT;
+};
+
+// Inside recursion over all spans for the current scale.  Returns nothing; q(1,n) is in ws.q.
+__device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
+                          const double* mlb, const McWs& w, int warp, int lane) {
+#define IX(i, j) ((size_t)(i) * W + (j))
+  for (int i = 1 + threadIdx.x; i <= n + 1; i += MC_THREADS) w.q[IX(i, i - 1)] = 1.0;
+  __syncthreads();
+  for (int d = 0; d < n; ++d) {
+    for (int i = 1 + warp; i + d <= n; i += MC_WARPS) {
+      const int j = i + d;
+      const int si = S[i], sj = S[j];
+      const int type = mc_pair(si, sj);
+      const bool closes = (d > MC_TURN) && type != 0;
+      double vb = 0.0;          // hairpin + interior part of qb, lane-partial
+      if (closes) {
+        if (lane == 0) {
+          const int u = d - 1;
+          int s6 = 0;
+          if (u == 4) { for (int c = 0; c < 6; ++c) s6 = s6 * 5 + S[i + c]; }
+          vb = mc_hairpin(T, u, type, S[i + 1], S[j - 1], s6) * scale[u + 2];
+        }
+        const int kmax = min(i + MC_MAXLOOP + 1, j - MC_TURN - 2);
+        for (int k = i + 1; k <= kmax; ++k) {
+          const int u1 = k - i - 1;
+          const int lmin = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + u1);
+          const int l = lmin + lane;
+          if (l < j) {
+            const int t2 = mc_pair(S[k], S[l]);
+            if (t2) {
+              const double qkl = w.qb[IX(k, l)];
+              if (qkl != 0.0)
+                vb += qkl * mc_interior(T, u1, j - l - 1, type, mc_rtype(t2), S[i + 1], S[j - 1], S[k - 1], S[l + 1]) *
+                      scale[u1 + j - l + 1];
+            }
+          }
+        }
+      }
+      // the three O(d) sums share one pass over k = i+1 .. j
+      double sm = 0.0, sq = 0.0, sml = 0.0;
+      const double* qm_i = w.qm + IX(i, 0);
+      const double* qm_i1 = w.qm + IX(i + 1, 0);
+      const double* q_i = w.q + IX(i, 0);
+      const double* qm1T_j = w.qm1T + IX(j, 0);
+      const double* qm1T_j1 = w.qm1T + IX(j - 1, 0);
+      const double* qqT_j = w.qqT + IX(j, 0);
+      for (int k = i + 1 + lane; k <= j; k += 32) {
+        sm += (mlb[k - i] + qm_i[k - 1]) * qm1T_j[k];
+        sq += q_i[k - 1] * qqT_j[k];
+        if (closes && k >= i + 2 && k <= j - 1) sml += qm_i1[k - 1] * qm1T_j1[k];
+      }
+      vb = mc_warp_sum(vb); sm = mc_warp_sum(sm); sq = mc_warp_sum(sq); sml = mc_warp_sum(sml);
+      if (lane == 0) {
+        if (closes) vb += sml * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
+        w.qb[IX(i, j)] = vb;
+        const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
+        double m1 = (d > 0 ? w.qm1T[IX(j - 1, i)] : 0.0) * mlb[1];
+        double e1 = (d > 0 ? w.qqT[IX(j - 1, i)] : 0.0) * scale[1];
+        if (vb != 0.0) { m1 += vb * mc_stem(T, type, si1, sj1, true); e1 += vb * mc_stem(T, type, si1, sj1, false); }
+        w.qm1T[IX(j, i)] = m1;
+        w.qqT[IX(j, i)] = e1;
+        const double vqm = sm + m1;                   // k = i term: (mlb^0 + 0) * qm1(i,j)
+        w.qm[IX(i, j)] = vqm;
+        w.qmT[IX(j, i)] = vqm;
+        w.q[IX(i, j)] = scale[d + 1] + e1 + sq;
+      }
+    }
+    __syncthreads();
+  }
+#undef IX
+}
+
+// Outside recursion; needs the inside arrays of the same scale.
+__device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
+                           const double* mlb, const McWs& w, int warp, int lane) {
+#define IX(i, j) ((size_t)(i) * W + (j))
+  // O, OM, prmlT, prm_lT start at zero: entries that are never written (pairs
+  // that cannot form, q > n) are read as 0.
+  for (size_t c = threadIdx.x; c < (size_t)(n + 2) * W; c += MC_THREADS) {
+    w.O[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0;
+  }
+  __syncthreads();
+  for (int d = n - 1; d > MC_TURN; --d) {
+    for (int i = 1 + warp; i + d <= n; i += MC_WARPS) {
+      const int j = i + d;
+      // (a) prm_l(i,j), prml(i,j): OM of spans >= d+1 only
+      if (j + 1 <= n) {
+        double t = 0.0;
+        const double* OM_i = w.OM + IX(i, 0);
+        const double* qm_j1 = w.qm + IX(j + 1, 0);
+        for (int qx = j + 2 + lane; qx <= n; qx += 32) t += OM_i[qx] * qm_j1[qx - 1];
+        t = mc_warp_sum(t);
+        if (lane == 0) {
+          w.prmlT[IX(j, i)] = t;
+          w.prm_lT[IX(j, i)] = w.prm_lT[IX(j + 1, i)] * mlb[1] + OM_i[j + 1];
+        }
+      }
+      // (b) O(i,j)
+      const int type = mc_pair(S[i], S[j]);
+      if (!type) continue;
+      const double qbij = w.qb[IX(i, j)];
+      if (qbij == 0.0) continue;
+      const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
+      const int t2 = mc_rtype(type);
+      double o = 0.0;
+      if (lane == 0) o = w.q[IX(1, i - 1)] * w.q[IX(j + 1, n)] * mc_stem(T, type, si1, sj1, false);
+      const int pmin = max(1, i - MC_MAXLOOP - 1);
+      for (int p = i - 1; p >= pmin; --p) {
+        const int u1 = i - p - 1;
+        const int qx = j + 1 + lane;
+        if (qx <= n && qx - j - 1 + u1 <= MC_MAXLOOP) {
+          const int tp = mc_pair(S[p], S[qx]);
+          if (tp) {
+            const double opq = w.O[IX(p, qx)];
+            if (opq != 0.0)
+              o += opq * mc_interior(T, u1, qx - j - 1, tp, t2, S[p + 1], S[qx - 1], S[i - 1], S[j + 1]) *
+                   scale[u1 + qx - j + 1];
+          }
+        }
+      }
+      double t = 0.0;
+      const double* prm_l_j = w.prm_lT + IX(j, 0);
+      const double* prml_j = w.prmlT + IX(j, 0);
+      const double* qmT_i1 = w.qmT + IX(i - 1, 0);       // qm(p+1, i-1) = qmT[i-1][p+1]
+      for (int p = 1 + lane; p < i; p += 32) {
+        const double qml = (p + 1 <= i - 1) ? qmT_i1[p + 1] : 0.0;
+        t += prm_l_j[p] * qml + prml_j[p] * (mlb[i - p - 1] + qml);
+      }
+      o = mc_warp_sum(o); t = mc_warp_sum(t);
+      if (lane == 0) {
+        o += t * mc_stem(T, type, si1, sj1, true);
+        w.O[IX(i, j)] = o;
+        w.OM[IX(i, j)] = o * ((double)T.ml_closing * mc_stem(T, t2, S[j - 1], S[i + 1], true)) * scale[2];
+      }
+    }
+    __syncthreads();
+  }
+#undef IX
+}
+
+}  // namespace dafs
+
+namespace dafs {
+
+// Dynamic shared memory: McTables | scale[W+1] | mlb[W+1] | codes[W+8]
+__global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
+  extern __shared__ __align__(16) char smem[];
+  __shared__ int s_q;
+  __shared__ int s_total;
+  McTables& T = *reinterpret_cast<McTables*>(smem);
+  const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
+  double* scale = reinterpret_cast<double*>(smem + tab_bytes);
+  double* mlb = scale + (a.W + 2);
+  uint8_t* S = reinterpret_cast<uint8_t*>(mlb + (a.W + 2));
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(a.tab);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&T);
+    for (int k = tid; k < (int)(sizeof(McTables) / 4); k += MC_THREADS) dst[k] = src[k];
+  }
+  const int W = a.W;
+  McWs w;
+  {
+    double* base = a.ws + (size_t)blockIdx.x * a.ws_stride;
+    const size_t A = (size_t)W * W;
+    w.q = base; w.qb = base + A; w.qm = base + 2 * A; w.qmT = base + 3 * A; w.qm1T = base + 4 * A;
+    w.qqT = base + 5 * A; w.O = base + 6 * A; w.OM = base + 7 * A; w.prmlT = base + 8 * A; w.prm_lT = base + 9 * A;
+  }
+#define IX(i, j) ((size_t)(i) * W + (j))
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s_q = atomicAdd(a.queue, 1);
+    __syncthreads();
+    if (s_q >= a.nseq) break;
+    const int s = a.order[s_q];
+    const int n = a.seq_len[s];
+    const uint8_t* gs = a.seq + a.seq_off[s];
+    for (int k = tid; k <= n + 1; k += MC_THREADS) S[k] = (k >= 1 && k <= n) ? gs[k - 1] : (uint8_t)0;
+    // ---- scale: start from ViennaRNA's default per-nucleotide guess and move to
+    // exp(lnZ/n) when the first inside pass ends far from 1 (the reference takes
+    // its pf_scale from an MFE run instead, fold.cpp:86-95; p does not depend on it)
+    double lns = 0.30010459245;                        // ln 1.35
+    const double ln_mlbase = log((double)T.ml_base);
+    double Z = 0.0, lnZ = 0.0;
+    for (int attempt = 0; attempt < 8; ++attempt) {
+      __syncthreads();
+      for (int k = tid; k <= n + 2; k += MC_THREADS) { scale[k] = exp(-(double)k * lns); mlb[k] = exp((double)k * (ln_mlbase - lns)); }
+      __syncthreads();
+      mc_inside(T, S, n, W, scale, mlb, w, warp, lane);
+      Z = w.q[IX(1, n)];
+      if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
+      if (!(Z > 0.0)) { lns -= 0.25; continue; }
+      lnZ = log(Z) + (double)n * lns;
+      if (fabs(log(Z)) <= 150.0) break;
+      lns = lnZ / (double)n;                            // rerun with the ensemble's own scale
+    }
+    mc_outside(T, S, n, W, scale, mlb, w, warp, lane);
+    // ---- read-out: p = float(qb*O/Z) > th, rows ascending, columns ascending ----
+    int32_t* row_ptr = a.row_ptr + a.row_off[s];
+    const float th = a.th;
+    const double invZ = 1.0 / Z;
+    for (int i = 1 + warp; i <= n; i += MC_WARPS) {
+      int cnt = 0;
+      for (int jb = i + 1; jb <= n; jb += 32) {
+        const int j = jb + lane;
+        bool keep = false;
+        if (j <= n) { const float p = (float)(w.qb[IX(i, j)] * w.O[IX(i, j)] * invZ); keep = p > th; }
+        cnt += __popc(__ballot_sync(0xffffffffu, keep));
+      }
+      if (lane == 0) row_ptr[i] = cnt;                  // count of row i-1 (0-based), scanned below
+    }
+    __syncthreads();
+    if (warp == 0) {                                    // exclusive scan over rows by one warp
+      int run = 0;
+      for (int b = 1; b <= n; b += 32) {
+        const int i = b + lane;
+        const int c = i <= n ? row_ptr[i] : 0;
+        int x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (i <= n) row_ptr[i] = run + x;               // inclusive -> row_ptr[i] = end of row i-1
+        run += __shfl_sync(0xffffffffu, x, 31);
+      }
+      if (lane == 0) { row_ptr[0] = 0; s_total = run; }
+    }
+    __syncthreads();
+    {
+      uint32_t* col = a.pool_col + a.pool_off[s];
+      float* val = a.pool_val + a.pool_off[s];
+      const int64_t cap = a.pool_off[s + 1] - a.pool_off[s];
+      const unsigned lt = (1u << lane) - 1u;
+      for (int i = 1 + warp; i <= n; i += MC_WARPS) {
+        int run = row_ptr[i - 1];
+        for (int jb = i + 1; jb <= n; jb += 32) {
+          const int j = jb + lane;
+          float p = 0.f;
+          bool keep = false;
+          if (j <= n) { p = (float)(w.qb[IX(i, j)] * w.O[IX(i, j)] * invZ); keep = p > th; }
+          const unsigned m = __ballot_sync(0xffffffffu, keep);
+          if (keep) { const int k = run + __popc(m & lt); if (k < cap) { col[k] = (uint32_t)(j - 1); val[k] = p; } }
+          run += __popc(m);
+        }
+      }
+      if (tid == 0) { a.seq_nnz[s] = s_total; a.seq_lnz[s] = lnZ; }
+    }
+  }
+#undef IX
+}
+
+}  // namespace dafs

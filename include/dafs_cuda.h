@@ -125,6 +125,33 @@ int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* plan, dafs_pairhmm_info* info
  * the reference's ProbabilisticModel constructor (ProbabilisticModel.h:55-88). */
 int dafs_cuda_pairhmm_tables(float* out54);
 
+/* ---- (2) McCaskill base-pairing probabilities -----------------------------
+ * What RNAfold(bl = true)::calculate(seq, bp) delivers (src/fold.cpp:78-116:
+ * ViennaRNA pf_fold + export_bppm under the BL* tables of
+ * src/boltzmann_param.c): per sequence the upper-triangular rows i < j with
+ * float(p) > th, columns ascending.  th is Fold::Model::threshold() (CUTOFF =
+ * 0.01, src/dafs.cpp:65,1700).  Alphabet: ACGU, T = U, case-insensitive, other
+ * bytes cannot pair (ViennaRNA's encoding).  1 <= len[i] <= 6000.
+ * Unit u of the batch = sequence u, len[u]+1 row_ptr entries.                */
+int dafs_cuda_mccaskill_all(int nseq, const char* const* seq, const int* len, float th, int ngpu,
+                            dafs_csr_batch* out);
+
+/* Split-phase form, like the pair-HMM plan.  fetch: lnz may be NULL or receive
+ * ln Z per sequence (= -ensemble free energy / kT).                          */
+typedef struct dafs_mccaskill_plan dafs_mccaskill_plan;
+int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq, const int* len, float th,
+                                    dafs_mccaskill_plan** plan);
+int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* plan);
+int dafs_cuda_mccaskill_plan_sync(dafs_mccaskill_plan* plan, float* device_ms, int64_t* nnz);
+int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* plan, dafs_csr_batch* out, double* lnz);
+void dafs_cuda_mccaskill_plan_destroy(dafs_mccaskill_plan* plan);
+typedef struct dafs_mccaskill_info {
+  int grid, block, smem_bytes, row_stride, table_bytes;
+  int64_t workspace_bytes;
+  float last_ms;
+} dafs_mccaskill_info;
+int dafs_cuda_mccaskill_plan_info(dafs_mccaskill_plan* plan, dafs_mccaskill_info* info);
+
 /* ---- (3) dual decomposition ------------------------------------------------
  * One problem = one call of DAFS::solve_by_dd(x, y, z, p_x, p_y, p_z, aln1, aln2)
  * (src/dafs.cpp:1006): dense row-major probability matrices exactly as the

@@ -195,3 +195,45 @@ def dd_problem(length, family=0, a=0, b=1, l2=None, mutation=0.2, th=0.01, mix=F
         p_y = np.maximum(p_y, synthetic_bpp(length, family + 1, 1)[:len(sb), :len(sb)])
     p_z = oracle_pair_dense(sa, sb, th)
     return p_x, np.ascontiguousarray(p_y), p_z
+
+
+# ---- McCaskill ------------------------------------------------------------------
+BLSTAR = os.path.join(ROOT, "dafs_b200", "data", "blstar37.i32")
+_mc_loaded = False
+
+
+def _mc():
+    global _mc_loaded
+    L = oracle()
+    if not _mc_loaded:
+        L.oracle_mccaskill_load.argtypes = [C.c_char_p]
+        assert L.oracle_mccaskill_load(BLSTAR.encode()) == 0
+        L.oracle_mccaskill.restype = C.c_double
+        L.oracle_mccaskill.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
+        L.oracle_mccaskill_bruteforce.restype = C.c_double
+        L.oracle_mccaskill_bruteforce.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
+        L.oracle_mccaskill_csr.argtypes = [C.c_char_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        _mc_loaded = True
+    return L
+
+
+def oracle_mccaskill(seq):
+    """(dense FP64 P[n,n] with i<j set, ln Z) from the FP64 restatement."""
+    n = len(seq)
+    P = np.zeros((n, n), np.float64)
+    lnz = _mc().oracle_mccaskill(seq, n, P.ctypes.data)
+    return P, float(lnz)
+
+
+def oracle_mccaskill_bruteforce(seq):
+    n = len(seq)
+    P = np.zeros((n, n), np.float64)
+    Z = _mc().oracle_mccaskill_bruteforce(seq, n, P.ctypes.data)
+    return P, float(Z)
+
+
+def oracle_mccaskill_csr(seq, th=0.01):
+    n = len(seq)
+    rp = np.zeros(n + 1, np.int32); col = np.zeros(n * n // 2 + 1, np.uint32); val = np.zeros(n * n // 2 + 1, np.float32)
+    nnz = _mc().oracle_mccaskill_csr(seq, n, th, rp.ctypes.data, col.ctypes.data, val.ctypes.data)
+    return rp, col[:nnz].copy(), val[:nnz].copy()

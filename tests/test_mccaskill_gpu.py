@@ -1,0 +1,95 @@
+"""GPU parity tests of (2): mccaskill_kernel against the FP64 restatement
+(oracle/mccaskill_oracle.c; parity with the reference itself is UNPINNED, see its
+header).  Tolerance: |p_gpu - p_oracle| <= 1e-4 absolute (BASELINE.json
+north_star); observed differences are ~1e-6 (FP32-stored Boltzmann factors)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+from dafs_b200.synth import fasta_read, random_rna
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def dafs():
+    import dafs_b200
+    dafs_b200.init(1)
+    return dafs_b200
+
+
+def check_batch(dafs, seqs, th=0.01):
+    with dafs.McCaskillPlan(seqs, th) as plan:
+        plan.run()
+        b, lnz = plan.fetch()
+        with b:
+            assert b.n_units == len(seqs)
+            worst = 0.0
+            for u, s in enumerate(seqs):
+                n = len(s)
+                P, lz = ou.oracle_mccaskill(s)
+                assert abs(lnz[u] - lz) < 1e-5 * max(1.0, abs(lz)), (u, lnz[u], lz)
+                rp, col, val = b.unit(u)
+                assert len(rp) == n + 1 and rp[0] == 0 and rp[-1] == len(col)
+                rows = np.repeat(np.arange(n), np.diff(rp))
+                assert (col > rows).all()                               # upper triangle
+                for r in range(n):                                      # ascending columns
+                    c = col[rp[r]:rp[r + 1]]
+                    assert (np.diff(c.astype(np.int64)) > 0).all()
+                assert (val > th).all()
+                G = np.zeros((n, n))
+                G[rows, col] = val
+                keep_o = P.astype(np.float32) > th
+                # every entry either side keeps must agree within TOL; entries within TOL
+                # of the threshold may legitimately differ in membership
+                diff = np.abs(G - np.where(keep_o, P, 0.0))
+                near = np.abs(P - th) <= TOL
+                assert diff[~near].max(initial=0.0) <= TOL
+                worst = max(worst, np.abs(G - P)[G > 0].max(initial=0.0))
+            return worst
+
+
+def test_short_and_designed(dafs):
+    seqs = [b"GGCGAAAGCCGCGAAAGCGCC", b"GCGGCAAAAGCCGCUUUUGCGC", b"GGGGACGGGGACGGGGACGG", b"GGGAAAUCCC", b"A", b"ACGU",
+            b"ACGUNNACGU", b"gggaaauccc", b"GGGAAATCCC"]
+    assert check_batch(dafs, seqs) <= TOL
+
+
+def test_rfam_examples(dafs):
+    for fa in ("RF00005_0.fa", "RF00017_4.fa"):
+        seqs = fasta_read(os.path.join(ROOT, "tests", "golden", fa))[1]
+        assert check_batch(dafs, seqs) <= TOL
+
+
+@pytest.mark.parametrize("n,count", [(73, 6), (150, 6), (300, 4), (601, 2)])
+def test_random_lengths(dafs, n, count):
+    seqs = random_rna(count, n, config_id=3)
+    assert check_batch(dafs, seqs) <= TOL
+
+
+def test_ragged_batch_and_thresholds(dafs):
+    r = random_rna(8, 200, config_id=9)
+    seqs = [r[k][:20 + 25 * k] for k in range(8)]
+    for th in (0.01, 0.2, 0.001):
+        assert check_batch(dafs, seqs, th) <= TOL
+
+
+def test_gc_rich_needs_rescaling(dafs):
+    """ln Z / n ~ 1: the first inside pass ends far from 1 and the kernel reruns
+    with the ensemble's own scale."""
+    s = (b"GGGGCCCCGGGGAAAACCCCGGGGCCCC" * 20)[:500]
+    assert check_batch(dafs, [s]) <= TOL
+
+
+def test_all_entry_point_matches_plan(dafs):
+    seqs = random_rna(5, 90, config_id=11)
+    with dafs.mccaskill_all(seqs, 0.01) as a, dafs.McCaskillPlan(seqs, 0.01) as plan:
+        plan.run()
+        b, _ = plan.fetch()
+        with b:
+            assert np.array_equal(a.row_ptr, b.row_ptr) and np.array_equal(a.col, b.col)
+            assert np.array_equal(a.val.view(np.uint32), b.val.view(np.uint32))
