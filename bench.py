@@ -44,6 +44,42 @@ def shard(npairs, rank, world):
     return np.arange(rank, npairs, world, dtype=np.int64)
 
 
+def gather_csr(dist, world, dev, col, val, nz_off, n_units, row_ptr=None):
+    """All-gather-v of per-rank CSR fragments: sizes first, then the max-padded
+    payload.  Returns, on every rank, a list over ranks of (col, val, nz_off,
+    n_units) views.  This is the only exchange step of the path."""
+    import torch
+    nrows = 0 if row_ptr is None else row_ptr.numel()
+    sizes = torch.tensor([col.numel(), n_units, nrows], dtype=torch.int64, device=dev)
+    all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(all_sizes, sizes)
+    all_sizes = all_sizes.view(world, 3).cpu()
+    mx_nnz, mx_units, mx_rows = (int(all_sizes[:, k].max()) for k in range(3))
+
+    def pad(x, n):
+        if x.numel() == n:
+            return x.contiguous()
+        y = torch.zeros(n, dtype=x.dtype, device=dev)
+        y[:x.numel()] = x
+        return y
+    outs = []
+    todo = [(col, mx_nnz), (val, mx_nnz), (nz_off, mx_units + 1)]
+    if row_ptr is not None:
+        todo.append((row_ptr, mx_rows))
+    for x, n in todo:
+        g = torch.empty(world * n, dtype=x.dtype, device=dev)
+        dist.all_gather_into_tensor(g, pad(x, n))
+        outs.append(g.view(world, n))
+    res = []
+    for r in range(world):
+        nn, nu, nr = (int(all_sizes[r, k]) for k in range(3))
+        item = (outs[0][r, :nn], outs[1][r, :nn], outs[2][r, :nu + 1], nu)
+        if row_ptr is not None:
+            item = item + (outs[3][r, :nr],)
+        res.append(item)
+    return res
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled during the timed region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -235,27 +271,24 @@ def run_ours(args):
         else:
             _, n_mine = p2.sync()
             rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
-            sizes = torch.tensor([n_mine, rows_mine, len(mine)], dtype=torch.int64, device=dev)
-            all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(all_sizes, sizes)
-            mx = all_sizes.view(world, 3).max(dim=0).values.tolist()
-            col = torch.empty(mx[0], dtype=torch.int32, device=dev)
-            val = torch.empty(mx[0], dtype=torch.float32, device=dev)
-            rp = torch.empty(mx[1], dtype=torch.int32, device=dev)
-            nzo = torch.empty(mx[2] + 1, dtype=torch.int64, device=dev)
-            p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), mx[0])
-            g = [torch.empty(world * x.numel(), dtype=x.dtype, device=dev) for x in (col, val, rp, nzo)]
-            for dst, src in zip(g, (col, val, rp, nzo)):
-                dist.all_gather_into_tensor(dst, src)          # NCCL over NVLink
+            col = torch.empty(max(n_mine, 1), dtype=torch.int32, device=dev)
+            val = torch.empty(max(n_mine, 1), dtype=torch.float32, device=dev)
+            rp = torch.empty(max(rows_mine, 1), dtype=torch.int32, device=dev)
+            nzo = torch.empty(len(mine) + 1, dtype=torch.int64, device=dev)
+            p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), max(n_mine, 1))
+            frags = gather_csr(dist, world, dev, col[:n_mine], val[:n_mine], nzo, len(mine), rp[:rows_mine])  # NCCL
             if rank == 0:
                 d2h = 0
-                for k, x in enumerate(g):
-                    if k not in pinned or pinned[k].numel() < x.numel():
-                        pinned[k] = torch.empty(x.numel(), dtype=x.dtype, pin_memory=True)
-                    pinned[k][:x.numel()].copy_(x, non_blocking=True)
-                    d2h += x.numel() * x.element_size()
+                k = 0
+                for fr in frags:
+                    for x in (fr[0], fr[1], fr[2], fr[4]):
+                        if k not in pinned or pinned[k].numel() < x.numel() or pinned[k].dtype != x.dtype:
+                            pinned[k] = torch.empty(max(x.numel(), 1), dtype=x.dtype, pin_memory=True)
+                        pinned[k][:x.numel()].copy_(x, non_blocking=True)
+                        d2h += x.numel() * x.element_size()
+                        k += 1
                 torch.cuda.synchronize()
-                checksum = int(all_sizes.view(world, 3)[:, 0].sum().item())
+                checksum = sum(int(fr[0].numel()) for fr in frags)
         p2.close()
         barrier()
         if it >= W:
