@@ -77,18 +77,26 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
           if (u == 4) { for (int c = 0; c < 6; ++c) s6 = s6 * 5 + S[i + c]; }
           vb = mc_hairpin(T, u, type, S[i + 1], S[j - 1], s6) * scale[u + 2];
         }
+        // interior loops (k,l): lanes over l, k in batches of 8 so that eight qb
+        // loads are in flight per lane (qb(k,l) == 0 for pairs that cannot form)
         const int kmax = min(i + MC_MAXLOOP + 1, j - MC_TURN - 2);
-        for (int k = i + 1; k <= kmax; ++k) {
-          const int u1 = k - i - 1;
-          const int lmin = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + u1);
-          const int l = lmin + lane;
-          if (l < j) {
-            const int t2 = mc_pair(S[k], S[l]);
-            if (t2) {
-              const double qkl = w.qb[IX(k, l)];
-              if (qkl != 0.0)
-                vb += qkl * mc_interior(T, u1, j - l - 1, type, mc_rtype(t2), S[i + 1], S[j - 1], S[k - 1], S[l + 1]) *
-                      scale[u1 + j - l + 1];
+        const int si1 = S[i + 1], sj1 = S[j - 1];
+        for (int k0 = i + 1; k0 <= kmax; k0 += 8) {
+          double qv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int k = k0 + u;
+            const int l = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + (k - i - 1)) + lane;
+            qv[u] = (k <= kmax && l < j) ? w.qb[IX(k, l)] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (qv[u] != 0.0) {
+              const int k = k0 + u, u1 = k - i - 1;
+              const int l = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + u1) + lane;
+              const int t2 = mc_pair(S[k], S[l]);
+              vb += qv[u] * mc_interior(T, u1, j - l - 1, type, mc_rtype(t2), si1, sj1, S[k - 1], S[l + 1]) *
+                    scale[u1 + j - l + 1];
             }
           }
         }
@@ -162,16 +170,23 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       double o = 0.0;
       if (lane == 0) o = w.q[IX(1, i - 1)] * w.q[IX(j + 1, n)] * mc_stem(T, type, si1, sj1, false);
       const int pmin = max(1, i - MC_MAXLOOP - 1);
-      for (int p = i - 1; p >= pmin; --p) {
-        const int u1 = i - p - 1;
+      {
+        const int sp1 = S[i - 1], sq1 = S[j + 1];
         const int qx = j + 1 + lane;
-        if (qx <= n && qx - j - 1 + u1 <= MC_MAXLOOP) {
-          const int tp = mc_pair(S[p], S[qx]);
-          if (tp) {
-            const double opq = w.O[IX(p, qx)];
-            if (opq != 0.0)
-              o += opq * mc_interior(T, u1, qx - j - 1, tp, t2, S[p + 1], S[qx - 1], S[i - 1], S[j + 1]) *
-                   scale[u1 + qx - j + 1];
+        for (int p0 = i - 1; p0 >= pmin; p0 -= 8) {
+          double ov[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int p = p0 - u;
+            ov[u] = (p >= pmin && qx <= n && qx - j - 1 + (i - p - 1) <= MC_MAXLOOP) ? w.O[IX(p, qx)] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (ov[u] != 0.0) {
+              const int p = p0 - u, u1 = i - p - 1;
+              const int tp = mc_pair(S[p], S[qx]);
+              o += ov[u] * mc_interior(T, u1, qx - j - 1, tp, t2, S[p + 1], S[qx - 1], sp1, sq1) * scale[u1 + qx - j + 1];
+            }
           }
         }
       }
