@@ -19,10 +19,12 @@ static const int kMaxL = 16384;
 // Host image of one problem: the position-independent constant block the kernel
 // stages into shared memory (DDHdr + sections), and where its results go.
 struct NusHost {
-  int L = 0, n = 0, max_col = 0;
-  float w = 0;
-  uint32_t col_ptr = 0, row_ptr = 0, row_ent = 0, ent_ij = 0, ent_p = 0, ent_flag = 0;   // offsets in the block
-  size_t out = 0;                                                                      // offset in the result buffer
+  DDNusHdr h{};                 // offsets into the block
+  int max_col = 0;              // most candidates in one column
+  size_t out = 0;               // offset in the result buffer
+  std::vector<int> row_ptr_full;   // [L+1] over all entries (host only: CBP -> entry id)
+  std::vector<int> row_ent_full;
+  std::vector<uint32_t> ij;
 };
 struct ProbHost {
   NusHost sx, sy;
@@ -38,18 +40,94 @@ static size_t up16(size_t x) { return (x + 15) & ~size_t(15); }
 template <class T>
 static size_t put(std::vector<char>& buf, const T* data, size_t n) {
   const size_t off = up16(buf.size());
-  buf.resize(off + sizeof(T) * n);
+  buf.resize(off + sizeof(T) * std::max<size_t>(n, 1));
   if (n) std::memcpy(buf.data() + off, data, sizeof(T) * n);
   return off;
 }
 
-struct Ent { int i, j; float p; uint8_t flag; };
+struct Ent { int i, j; float p; uint8_t flag; bool cand; };
+
+// Packs one Nussinov structure into the block: candidates (span > 2) first, in
+// column order, then the span <= 2 projections; live rows / columns and the
+// index maps of the compressed grid (dd_kernel.cuh).
+static void pack_nus(NusHost& H, std::vector<char>& cst, int L, float w, std::vector<Ent>& ents) {
+  std::stable_sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) {
+    if (a.cand != b.cand) return a.cand;                       // candidates first
+    return a.j != b.j ? a.j < b.j : a.i > b.i;                 // ascending j, descending i
+  });
+  const int n = (int)ents.size();
+  int nd = 0;
+  while (nd < n && ents[nd].cand) ++nd;
+  std::vector<uint16_t> rowI, colJ;
+  {
+    std::vector<char> ri(L, 0), cj(L, 0);
+    for (int e = 0; e < nd; ++e) { ri[ents[e].i] = 1; cj[ents[e].j] = 1; }
+    for (int k = 0; k < L; ++k) { if (ri[k]) rowI.push_back((uint16_t)k); if (cj[k]) colJ.push_back((uint16_t)k); }
+  }
+  const int nI = (int)rowI.size(), nJ = (int)colJ.size();
+  std::vector<uint16_t> rowmap(L + 1), colmap(L + 1), bstart(std::max(nI, 1));
+  {
+    int a = 0;
+    for (int i = 0; i <= L; ++i) { while (a < nI && rowI[a] < i) ++a; rowmap[i] = (uint16_t)a; }
+    int b = 0;                                                // colmap[j] = #live columns <= j
+    for (int j = 0; j <= L; ++j) { while (b < nJ && colJ[b] <= j) ++b; colmap[j] = (uint16_t)b; }
+    for (int x = 0; x < nI; ++x) bstart[x] = colmap[rowI[x]];   // first live column index with J > I[a]
+  }
+  std::vector<int> col_ptr(nJ + 1, 0), row_ptr(nI + 1, 0), row_ent(std::max(nd, 1)), ent_c(std::max(nd, 1));
+  std::vector<uint32_t> ab(std::max(nd, 1)), ij(std::max(n, 1));
+  std::vector<float> pv(std::max(n, 1));
+  std::vector<uint8_t> fl(std::max(n, 1));
+  for (int e = 0; e < n; ++e) {
+    ij[e] = (uint32_t)ents[e].i | ((uint32_t)ents[e].j << 16);
+    pv[e] = ents[e].p; fl[e] = ents[e].flag;
+  }
+  int max_col = 0;
+  for (int e = 0; e < nd; ++e) {
+    const int a = rowmap[ents[e].i], b = (int)colmap[ents[e].j] - 1;
+    ab[e] = (uint32_t)a | ((uint32_t)b << 16);
+    ent_c[e] = ents[e].i >= 1 ? (int)colmap[ents[e].i - 1] - 1 : -1;   // last live column <= i-1
+    col_ptr[b + 1]++; row_ptr[a + 1]++;
+  }
+  for (int b = 0; b < nJ; ++b) { max_col = std::max(max_col, col_ptr[b + 1]); col_ptr[b + 1] += col_ptr[b]; }
+  for (int a = 0; a < nI; ++a) row_ptr[a + 1] += row_ptr[a];
+  {
+    std::vector<int> fill(row_ptr.begin(), row_ptr.end() - 1);
+    for (int e = 0; e < nd; ++e) row_ent[fill[ab[e] & 0xffffu]++] = e;   // ascending b inside a row
+  }
+  // host-only full row lists (all entries) for CBP -> entry id
+  H.row_ptr_full.assign(L + 1, 0);
+  for (int e = 0; e < n; ++e) H.row_ptr_full[ents[e].i + 1]++;
+  for (int k = 0; k < L; ++k) H.row_ptr_full[k + 1] += H.row_ptr_full[k];
+  H.row_ent_full.assign(std::max(n, 1), 0);
+  {
+    std::vector<int> fill(H.row_ptr_full.begin(), H.row_ptr_full.end() - 1);
+    for (int e = 0; e < n; ++e) H.row_ent_full[fill[ents[e].i]++] = e;
+  }
+  H.ij = ij;
+  DDNusHdr& h = H.h;
+  h.L = L; h.n = n; h.nd = nd; h.nI = nI; h.nJ = nJ; h.w = w;
+  H.max_col = max_col;
+  h.col_ptr = (uint32_t)put(cst, col_ptr.data(), col_ptr.size());
+  h.row_ptr = (uint32_t)put(cst, row_ptr.data(), row_ptr.size());
+  h.row_ent = (uint32_t)put(cst, row_ent.data(), (size_t)nd);
+  h.ent_ab = (uint32_t)put(cst, ab.data(), (size_t)nd);
+  h.ent_c = (uint32_t)put(cst, ent_c.data(), (size_t)nd);
+  h.ent_ij = (uint32_t)put(cst, ij.data(), (size_t)n);
+  h.ent_p = (uint32_t)put(cst, pv.data(), (size_t)n);
+  h.ent_flag = (uint32_t)put(cst, fl.data(), (size_t)n);
+  h.rowI = (uint32_t)put(cst, rowI.data(), rowI.size());
+  h.colJ = (uint32_t)put(cst, colJ.data(), colJ.size());
+  h.bstart = (uint32_t)put(cst, bstart.data(), (size_t)nI);
+  h.rowmap = (uint32_t)put(cst, rowmap.data(), rowmap.size());
+  h.colmap = (uint32_t)put(cst, colmap.data(), colmap.size());
+}
 
 // Entries of one structure: decoder candidates (w*(p-th) > 0 with q = 0, span
 // > 2: src/nussinov.cpp:234-237) plus the projection c_x of the CBPs
 // (src/dafs.cpp:1037).  Nothing else can ever get a non-zero multiplier:
 // q changes only for c_x entries and for decoded pairs (dafs.cpp:1121-1150),
-// and a decoded pair had s > 0.
+// and a decoded pair had s > 0.  A c_x entry with span > 2 is a candidate too
+// (its multiplier can turn s positive).
 static void build_nus(NusHost& H, std::vector<char>& cst, size_t& res, int L, const float* p, float w,
                       float th, const std::vector<std::pair<int, int>>& proj /* sorted unique (i,j) */) {
   std::vector<Ent> ents;
@@ -62,53 +140,18 @@ static void build_nus(NusHost& H, std::vector<char>& cst, size_t& res, int L, co
       if (pc < proj.size() && proj[pc].first == i && proj[pc].second == j) inproj = true;
       const bool span = (j - i > 2);
       const float s0 = w * (pij - th);
-      const bool cand = span && (s0 > 0.0f);
-      if (cand || inproj) ents.push_back({i, j, pij, (uint8_t)((inproj ? 1 : 0) | (span ? 2 : 0))});
+      if ((span && s0 > 0.0f) || inproj) ents.push_back({i, j, pij, (uint8_t)(inproj ? 1 : 0), span});
     }
-  // column order: ascending j, descending i
-  std::sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.j != b.j ? a.j < b.j : a.i > b.i; });
-  const int n = (int)ents.size();
-  std::vector<int> col_ptr(L + 1, 0), row_ptr(L + 1, 0), row_ent(n);
-  std::vector<uint32_t> ij(n);
-  std::vector<float> pv(n);
-  std::vector<uint8_t> fl(n);
-  for (int e = 0; e < n; ++e) {
-    col_ptr[ents[e].j + 1]++; row_ptr[ents[e].i + 1]++;
-    ij[e] = (uint32_t)ents[e].i | ((uint32_t)ents[e].j << 16);
-    pv[e] = ents[e].p; fl[e] = ents[e].flag;
-  }
-  int max_col = 0;
-  for (int k = 0; k < L; ++k) {
-    max_col = std::max(max_col, col_ptr[k + 1]);
-    col_ptr[k + 1] += col_ptr[k]; row_ptr[k + 1] += row_ptr[k];
-  }
-  {
-    std::vector<int> fill(row_ptr.begin(), row_ptr.end() - 1);
-    // entries arrive in ascending j, so each row list comes out ascending in j
-    for (int e = 0; e < n; ++e) row_ent[fill[ents[e].i]++] = e;
-  }
-  H.L = L; H.n = n; H.w = w; H.max_col = max_col;
-  H.col_ptr = (uint32_t)put(cst, col_ptr.data(), col_ptr.size());
-  H.row_ptr = (uint32_t)put(cst, row_ptr.data(), row_ptr.size());
-  H.row_ent = (uint32_t)put(cst, row_ent.data(), row_ent.size());
-  H.ent_ij = (uint32_t)put(cst, ij.data(), ij.size());
-  H.ent_p = (uint32_t)put(cst, pv.data(), pv.size());
-  H.ent_flag = (uint32_t)put(cst, fl.data(), fl.size());
+  pack_nus(H, cst, L, w, ents);
   H.out = up16(res); res = H.out + sizeof(uint32_t) * L;
 }
 
-// entry id of (i, j) in a structure built by build_nus (must exist)
-static int find_ent(const std::vector<char>& cst, const NusHost& H, int i, int j) {
-  const int* row_ptr = reinterpret_cast<const int*>(cst.data() + H.row_ptr);
-  const int* row_ent = reinterpret_cast<const int*>(cst.data() + H.row_ent);
-  const uint32_t* ij = reinterpret_cast<const uint32_t*>(cst.data() + H.ent_ij);
-  int lo = row_ptr[i], hi = row_ptr[i + 1];
-  while (lo < hi) {
-    const int mid = (lo + hi) / 2;
-    const int jj = (int)(ij[row_ent[mid]] >> 16);
-    if (jj < j) lo = mid + 1; else hi = mid;
-  }
-  return row_ent[lo];
+// entry id of (i, j) in a structure built by pack_nus (must exist)
+static int find_ent(const NusHost& H, int i, int j) {
+  int lo = H.row_ptr_full[i], hi = H.row_ptr_full[i + 1];
+  for (int k = lo; k < hi; ++k)
+    if ((int)(H.ij[H.row_ent_full[k]] >> 16) == j) return H.row_ent_full[k];
+  return -1;
 }
 
 // SparseNeedlemanWunsch::initialize, src/needleman_wunsch.cpp:198-253
@@ -235,17 +278,16 @@ static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H)
     return cz_id[std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin()];
   };
   for (size_t u = 0; u < cbp.size(); ++u)
-    cb[u] = make_int4(find_ent(H.cst, H.sx, cbp[u].i, cbp[u].j), find_ent(H.cst, H.sy, cbp[u].k, cbp[u].l),
+    cb[u] = make_int4(find_ent(H.sx, cbp[u].i, cbp[u].j), find_ent(H.sy, cbp[u].k, cbp[u].l),
                       zid(cbp[u].i, cbp[u].k), zid(cbp[u].j, cbp[u].l));
   h.cbp = (uint32_t)put(H.cst, cb.data(), cb.size());
   H.cst.resize(up16(H.cst.size()));
-  h.L1 = L1; h.L2 = L2; h.nx = H.sx.n; h.ny = H.sy.n; h.nz = H.nz; h.ncbp = H.ncbp; h.t_max = q.t_max;
+  h.L1 = L1; h.L2 = L2; h.nz = H.nz; h.ncbp = H.ncbp; h.t_max = q.t_max;
   h.bytes = (int)H.cst.size();
-  h.th_s = q.th_s; h.th_a = q.th_a; h.eta0 = q.eta0; h.wx = wx; h.wy = wy;
-  h.x_col_ptr = H.sx.col_ptr; h.x_row_ptr = H.sx.row_ptr; h.x_row_ent = H.sx.row_ent;
-  h.x_ij = H.sx.ent_ij; h.x_p = H.sx.ent_p; h.x_flag = H.sx.ent_flag;
-  h.y_col_ptr = H.sy.col_ptr; h.y_row_ptr = H.sy.row_ptr; h.y_row_ent = H.sy.row_ent;
-  h.y_ij = H.sy.ent_ij; h.y_p = H.sy.ent_p; h.y_flag = H.sy.ent_flag;
+  h.th_s = q.th_s; h.th_a = q.th_a; h.eta0 = q.eta0;
+  h.x = H.sx.h; h.y = H.sy.h;
+  H.sx.row_ptr_full = std::vector<int>(); H.sx.row_ent_full = std::vector<int>(); H.sx.ij = std::vector<uint32_t>();
+  H.sy.row_ptr_full = std::vector<int>(); H.sy.row_ent_full = std::vector<int>(); H.sy.ij = std::vector<uint32_t>();
   std::memcpy(H.cst.data(), &h, sizeof h);
   H.z_out = up16(res); res = H.z_out + sizeof(uint32_t) * L1;
   H.result = up16(res); res = H.result + 64;
@@ -273,6 +315,7 @@ struct dafs_dd_plan {
   char* d_ws = nullptr;
   dafs::DDLayout lay{};
   int grid = 0, smem = 0, ctas_per_sm = 0;
+  bool all_smem = false;
   int64_t total_cbp = 0, total_entries = 0;
   bool launched = false;
   float last_ms = 0;
@@ -288,16 +331,17 @@ static void free_dd_plan(dafs_dd_plan* p) {
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 
-struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nz = 1, ncbp = 1, col = 0, cst = 16; };
+struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nz = 1, ncbp = 1, col = 0, cst = 16, nIx = 1, nJx = 1, nIy = 1, nJy = 1; };
 
 // Scratch layout from the batch maxima: items go to shared memory in priority
 // order (enum order in dd_kernel.cuh) while they fit, the rest to the per-CTA
 // global workspace.
 static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, int* smem_bytes, size_t* ws_bytes) {
-  lay.lp1 = (m.L1 + 2) & ~1;
-  lay.lp2 = (m.L2 + 2) & ~1;
+  lay.lp1 = (m.nJx + 2) & ~1;      // even stride: lane*lp + (B0 + s - lane) hits 32 distinct banks
+  lay.lp2 = (m.nJy + 2) & ~1;
+  lay.trs1 = m.nJx; lay.trs2 = m.nJy;
   lay.w16 = (m.L2 + 15) / 16;
-  lay.tr16 = (m.col > 250) ? 1u : 0u;
+  lay.tr16 = (m.col > 120) ? 1u : 0u;
   const size_t trb = lay.tr16 ? 2 : 1;
   size_t sz[DD_NITEMS];
   sz[DD_CST] = (size_t)m.cst;
@@ -307,8 +351,8 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
   sz[DD_BROW_X] = 4 * (size_t)lay.lp1; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2;
   sz[DD_BROW_Z] = 4 * (size_t)(m.L2 + 2);
   sz[DD_TRZ] = 4 * (size_t)(m.L1 + 1) * lay.w16;
-  sz[DD_TR_X] = trb * ((size_t)m.L1 * (m.L1 - 1) / 2 + 1);
-  sz[DD_TR_Y] = trb * ((size_t)m.L2 * (m.L2 - 1) / 2 + 1);
+  sz[DD_TR_X] = trb * ((size_t)m.nIx * m.nJx + 1);
+  sz[DD_TR_Y] = trb * ((size_t)m.nIy * m.nJy + 1);
   sz[DD_SS_X] = 4 * (size_t)m.L1; sz[DD_SS_Y] = 4 * (size_t)m.L2; sz[DD_ZRES] = 4 * (size_t)m.L1;
   sz[DD_STK_X] = 4 * (size_t)(m.L1 / 2 + 4); sz[DD_STK_Y] = 4 * (size_t)(m.L2 / 2 + 4);
   sz[DD_TAL_X] = 4 * (size_t)m.nx; sz[DD_TAL_Y] = 4 * (size_t)m.ny; sz[DD_TAL_Z] = 4 * (size_t)m.nz;
@@ -375,11 +419,13 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     H.cst_base = cst; cst += H.cst.size(); cst = (cst + 255) & ~size_t(255);
     H.res_base = res; res += H.res_bytes;
     m.L1 = std::max(m.L1, H.L1); m.L2 = std::max(m.L2, H.L2);
-    m.nx = std::max(m.nx, H.sx.n); m.ny = std::max(m.ny, H.sy.n);
+    m.nx = std::max(m.nx, H.sx.h.n); m.ny = std::max(m.ny, H.sy.h.n);
+    m.nIx = std::max(m.nIx, H.sx.h.nI); m.nJx = std::max(m.nJx, H.sx.h.nJ);
+    m.nIy = std::max(m.nIy, H.sy.h.nI); m.nJy = std::max(m.nJy, H.sy.h.nJ);
     m.nz = std::max(m.nz, H.nz); m.ncbp = std::max(m.ncbp, H.ncbp);
     m.col = std::max(m.col, std::max(H.sx.max_col, H.sy.max_col));
     m.cst = std::max(m.cst, (int)H.cst.size());
-    p->total_cbp += H.ncbp; p->total_entries += H.sx.n + H.sy.n + H.nz;
+    p->total_cbp += H.ncbp; p->total_entries += H.sx.h.n + H.sy.h.n + H.nz;
   }
   p->cst_bytes = cst; p->res_bytes = res;
   PLAN_TRY(cudaMalloc(&p->d_cst, std::max<size_t>(cst, 256)));
@@ -424,9 +470,15 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   const size_t budget = (size_t)prop.sharedMemPerBlockOptin - 2048;
   size_t ws_per = 0;
   plan_layout(p->lay, m, budget, &p->smem, &ws_per);
-  PLAN_TRY(cudaFuncSetAttribute(dd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+  p->all_smem = (p->lay.in_smem == (1u << DD_NITEMS) - 1u);
   int blocks = 0;
-  PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel, DD_THREADS, p->smem));
+  if (p->all_smem) {
+    PLAN_TRY(cudaFuncSetAttribute(dd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel<true>, DD_THREADS, p->smem));
+  } else {
+    PLAN_TRY(cudaFuncSetAttribute(dd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel<false>, DD_THREADS, p->smem));
+  }
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
   p->ctas_per_sm = blocks;
   p->grid = std::max(1, std::min(nprob, prop.multiProcessorCount * blocks));
@@ -448,8 +500,13 @@ extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
   a.prob = p->d_prob; a.order = p->d_order; a.nprob = p->nprob; a.queue = p->d_queue; a.lay = p->lay;
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-  dd_kernel<<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
+  if (p->all_smem) {
+    DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    dd_kernel<true><<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
+  } else {
+    DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    dd_kernel<false><<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
+  }
   DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
   return DAFS_CUDA_OK;
@@ -529,11 +586,14 @@ extern "C" int dafs_cuda_dd_solve_batch(int nprob, const dafs_dd_problem* prob, 
 // ---- single decodes ------------------------------------------------------------
 namespace dafs {
 
-__global__ void __launch_bounds__(32) nussinov_single_kernel(const DDNus S, const NusScratch sc, float th,
-                                                             float* score) {
+__global__ void __launch_bounds__(32) nussinov_single_kernel(const char* blk, float* q, const NusScratch sc, float th,
+                                                             uint32_t* out, float* score) {
+  const DDNus S = dd_make_nus(blk, *reinterpret_cast<const DDNusHdr*>(blk), q);
+  for (int e = threadIdx.x; e < S.nd; e += 32) sc.es[e] = -INFINITY;
+  __syncwarp();
   const float v = nussinov_warp(S, sc, th, threadIdx.x, nullptr);
   if (threadIdx.x == 0) *score = v;
-  for (int i = threadIdx.x; i < S.L; i += 32) S.out[i] = sc.ss[i];
+  for (int i = threadIdx.x; i < S.L; i += 32) out[i] = sc.ss[i];
 }
 
 __global__ void __launch_bounds__(32) nw_single_kernel(const DDAln A, const NwScratch sc, uint32_t* al, float* score,
@@ -559,54 +619,39 @@ extern "C" int dafs_cuda_nussinov_decode(int L, float th, float w, const float* 
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
   if (!q) w = 1.0f;   // plain overload: s = p - th == 1*(p - th) - 0 exactly
   // candidates: s > 0, span > 2 (nussinov.cpp:234-237); nothing else is ever read
-  struct E { int i, j; float p, q; };
-  std::vector<E> ents;
+  std::vector<Ent> ents;
+  std::vector<float> qv;
   for (int i = 0; i < L; ++i)
     for (int j = i + 3; j < L; ++j) {
-      const float pv = p[(size_t)i * L + j], qv = q ? q[(size_t)i * L + j] : 0.0f;
-      const float s = w * (pv - th) - qv;
-      if (s > 0.0) ents.push_back({i, j, pv, qv});
+      const float pv = p[(size_t)i * L + j], qq = q ? q[(size_t)i * L + j] : 0.0f;
+      const float s = w * (pv - th) - qq;
+      if (s > 0.0) ents.push_back({i, j, pv, 0, true});
     }
-  std::sort(ents.begin(), ents.end(), [](const E& a, const E& b) { return a.j != b.j ? a.j < b.j : a.i > b.i; });
-  const int n = (int)ents.size();
-  std::vector<int> col_ptr(L + 1, 0), row_ptr(L + 1, 0), row_ent(std::max(n, 1));
-  std::vector<uint32_t> ij(std::max(n, 1));
-  std::vector<float> pv(std::max(n, 1)), qv(std::max(n, 1));
-  std::vector<uint8_t> fl(std::max(n, 1), 2);
-  for (int e = 0; e < n; ++e) {
-    col_ptr[ents[e].j + 1]++; row_ptr[ents[e].i + 1]++;
-    ij[e] = (uint32_t)ents[e].i | ((uint32_t)ents[e].j << 16); pv[e] = ents[e].p; qv[e] = ents[e].q;
-  }
-  int maxcol = 0;
-  for (int k = 0; k < L; ++k) { maxcol = std::max(maxcol, col_ptr[k + 1]); col_ptr[k + 1] += col_ptr[k]; row_ptr[k + 1] += row_ptr[k]; }
-  { std::vector<int> fill(row_ptr.begin(), row_ptr.end() - 1); for (int e = 0; e < n; ++e) row_ent[fill[ents[e].i]++] = e; }
-  const bool tr16 = maxcol > 250;
-  const int lp = (L + 2) & ~1;
-  const size_t ntr = (size_t)L * (L - 1) / 2 + 1;
+  NusHost H;
+  std::vector<char> blk(sizeof(DDNusHdr), 0);
+  pack_nus(H, blk, L, w, ents);          // sorts ents into column order
+  std::memcpy(blk.data(), &H.h, sizeof(DDNusHdr));
+  blk.resize(up16(blk.size()));
+  const int n = H.h.n, nI = std::max(H.h.nI, 1), nJ = std::max(H.h.nJ, 1);
+  qv.resize(std::max(n, 1));
+  for (int e = 0; e < n; ++e) qv[e] = q ? q[(size_t)ents[e].i * L + ents[e].j] : 0.0f;
+  const bool tr16 = H.max_col > 120;
+  const int lp = (nJ + 2) & ~1;
+  const size_t ntr = (size_t)nI * nJ + 1;
   DevBuf B;
-  B.size = 64 * 16 + 4 * (size_t)(2 * (L + 1) + 6 * (size_t)std::max(n, 1) + 33 * (size_t)lp + 2 * L + L / 2 + 8) + (tr16 ? 2 : 1) * ntr + 64;
+  B.size = blk.size() + 64 * 16 + 4 * (size_t)(2 * (size_t)std::max(n, 1) + 33 * (size_t)lp + 2 * L + L / 2 + 16) + (tr16 ? 2 : 1) * ntr + 64;
   DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
-  DDNus S; NusScratch sc;
-  int* d_col = B.take<int>(L + 1); int* d_row = B.take<int>(L + 1); int* d_re = B.take<int>(n);
-  uint32_t* d_ij = B.take<uint32_t>(n); float* d_p = B.take<float>(n); float* d_q = B.take<float>(n);
-  uint8_t* d_fl = B.take<uint8_t>(n);
+  NusScratch sc;
+  char* d_blk = B.take<char>(blk.size());
+  float* d_q = B.take<float>(n);
   sc.es = B.take<float>(n); sc.row = B.take<float>(32 * (size_t)lp); sc.brow = B.take<float>(lp);
   sc.ss = B.take<uint32_t>(L); sc.stk = B.take<uint32_t>(L / 2 + 4);
   uint32_t* d_out = B.take<uint32_t>(L); float* d_score = B.take<float>(1);
   sc.tr = tr16 ? (void*)B.take<uint16_t>(ntr) : (void*)B.take<uint8_t>(ntr);
-  sc.lp = lp; sc.tr16 = tr16;
-  S.L = L; S.n = n; S.col_ptr = d_col; S.row_ptr = d_row; S.row_ent = d_re; S.ent_ij = d_ij; S.ent_p = d_p;
-  S.ent_flag = d_fl; S.ent_q = d_q; S.w = w; S.out = d_out;
-  DAFS_CUDA_TRY(cudaMemcpy(d_col, col_ptr.data(), sizeof(int) * (L + 1), cudaMemcpyHostToDevice));
-  DAFS_CUDA_TRY(cudaMemcpy(d_row, row_ptr.data(), sizeof(int) * (L + 1), cudaMemcpyHostToDevice));
-  if (n) {
-    DAFS_CUDA_TRY(cudaMemcpy(d_re, row_ent.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
-    DAFS_CUDA_TRY(cudaMemcpy(d_ij, ij.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice));
-    DAFS_CUDA_TRY(cudaMemcpy(d_p, pv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
-    DAFS_CUDA_TRY(cudaMemcpy(d_q, qv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
-    DAFS_CUDA_TRY(cudaMemcpy(d_fl, fl.data(), n, cudaMemcpyHostToDevice));
-  }
-  nussinov_single_kernel<<<1, 32>>>(S, sc, th, d_score);
+  sc.lp = lp; sc.trs = nJ; sc.tr16 = tr16;
+  DAFS_CUDA_TRY(cudaMemcpy(d_blk, blk.data(), blk.size(), cudaMemcpyHostToDevice));
+  DAFS_CUDA_TRY(cudaMemcpy(d_q, qv.data(), sizeof(float) * std::max(n, 1), cudaMemcpyHostToDevice));
+  nussinov_single_kernel<<<1, 32>>>(d_blk, d_q, sc, th, d_out, d_score);
   DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaMemcpy(ss, d_out, sizeof(uint32_t) * L, cudaMemcpyDeviceToHost));
   float sv = 0;

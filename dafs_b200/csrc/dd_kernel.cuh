@@ -13,12 +13,19 @@
 // Warp 0 decodes x, warp 1 decodes y, warp 2 decodes z, concurrently; then all
 // threads tally and update the multipliers.  Neither decoder uses a block
 // barrier inside its DP:
-//   * Nussinov: lanes own 32 consecutive rows (a "wave", bottom rows first) and
-//     walk their row left to right, one column behind the row below, whose
-//     values arrive by warp shuffle; bifurcations read the lane's own row from
-//     shared memory and the candidate values of the column (reference: bp[j]).
-//   * NW: the mirror image (32 rows per wave, top rows first, one column behind
-//     the row above); p_z and q_z come from sparse row lists, traceback codes
+//   * Nussinov runs on the COMPRESSED grid of live rows x live columns (rows /
+//     columns that carry at least one decoder candidate).  A cell in a dead
+//     column equals its left neighbour and a cell in a dead row equals the one
+//     below (both exactly: the maxima range over identical float sums), so only
+//     live x live cells are computed; the traceback re-derives the reference's
+//     choices in dead rows / columns from one extra bit per live cell.  Lanes own
+//     32 consecutive live rows (a wave, bottom first) and walk the live columns
+//     left to right, one column behind the row below, whose values arrive by
+//     warp shuffle; bifurcations read the lane's own row and the column's
+//     candidate list in the reference's push order (bp[j], descending i).
+//   * NW: 32 rows per wave, top rows first, one column behind the row above,
+//     only across the wave's part of the alignment envelope; p_z and q_z come
+//     from sparse row lists (every other cell adds exactly 0); traceback codes
 //     are packed 2 bits per cell.
 // Multipliers are sparse: for x and y the decoder's candidates plus the CBP
 // projections c_x / c_y, for z the projection c_z -- nothing else can ever
@@ -32,22 +39,37 @@ namespace dafs {
 
 #define DD_NOPAIR 0xffffffffu
 
-// Header of one problem's constant block (built on the host, dd.cu).  The block
-// is contiguous and position independent: the kernel copies it to shared memory
-// when it fits and works on it in place in HBM otherwise.  Offsets are bytes from
-// the start of the block, every section 16-byte aligned.
+// Offsets (bytes from the start of the problem's constant block) of one
+// Nussinov structure.  Entries [0, nd) are the decoder candidates (span > 2) in
+// column order -- ascending j, then descending i, the order in which the
+// reference pushes to bp[j] (nussinov.cpp:236-245); entries [nd, n) are CBP
+// projections with span <= 2, which only carry multipliers.
+struct DDNusHdr {
+  int L, n, nd, nI, nJ, pad;
+  float w;                     // w_*2*N1/(N1+N2)  (dafs.cpp:1091)
+  uint32_t col_ptr;            // int[nJ+1]   candidates of live column b
+  uint32_t row_ptr;            // int[nI+1]
+  uint32_t row_ent;            // int[nd]     entry ids of live row a, ascending b
+  uint32_t ent_ab;             // u32[nd]     a | b << 16 (live row / live column index)
+  uint32_t ent_c;              // i32[nd]     largest live column index with J <= i-1, or -1
+  uint32_t ent_ij;             // u32[n]      i | j << 16
+  uint32_t ent_p;              // f32[n]
+  uint32_t ent_flag;           // u8[n]       bit0: in c_x (dafs.cpp:1037)
+  uint32_t rowI;               // u16[nI]     live rows, ascending
+  uint32_t colJ;               // u16[nJ]     live columns, ascending
+  uint32_t bstart;             // u16[nI]     first live column index with J > I[a]
+  uint32_t rowmap;             // u16[L+1]    i -> index of the first live row >= i (nI if none)
+  uint32_t colmap;             // u16[L+1]    j -> 1 + index of the last live column <= j (0 if none)
+};
+
 struct DDHdr {
-  int L1, L2, nx, ny, nz, ncbp, t_max, bytes;
-  float th_s, th_a, eta0, wx, wy;          // wx = w_*2*N1/(N1+N2), wy likewise (dafs.cpp:1091-1092)
-  int pad0, pad1, pad2;
-  // x / y: Nussinov entries in column order (ascending j, descending i: the push
-  // order of the reference's bp[j], nussinov.cpp:236-245)
-  uint32_t x_col_ptr, x_row_ptr, x_row_ent, x_ij, x_p, x_flag;
-  uint32_t y_col_ptr, y_row_ptr, y_row_ent, y_ij, y_p, y_flag;
+  int L1, L2, nz, ncbp, t_max, bytes;
+  float th_s, th_a, eta0;
+  int pad0;
+  DDNusHdr x, y;
   // z: per row i the cells (i,k) with p_z != 0 or in c_z, ascending k
   uint32_t z_row_ptr, z_col, z_p, z_flag, z_env;
-  uint32_t cbp;                            // int4 {entry in x, entry in y, z entry of (i,k), z entry of (j,l)}
-  uint32_t pad3, pad4;
+  uint32_t cbp;                // int4 {entry in x, entry in y, z entry of (i,k), z entry of (j,l)}
 };
 
 struct DDProbRef {
@@ -59,18 +81,70 @@ struct DDProbRef {
   float* trace;                // optional [t_max*3] {L, eta, violated} per iteration (-v 2, dafs.cpp:1273)
 };
 
-// One Nussinov structure (x or y) of the problem a CTA works on.
+// Per-CTA scratch arrays; each lives in shared memory when it fits (host decides,
+// in this order) and in a per-CTA global workspace otherwise.
+enum {
+  DD_CST, DD_Q_X, DD_Q_Y, DD_Q_Z, DD_ES_X, DD_ES_Y, DD_ROW_X, DD_ROW_Y, DD_BROW_X, DD_BROW_Y, DD_BROW_Z,
+  DD_TRZ, DD_TR_X, DD_TR_Y, DD_SS_X, DD_SS_Y, DD_ZRES, DD_STK_X, DD_STK_Y, DD_TAL_X, DD_TAL_Y, DD_TAL_Z,
+  DD_SW, DD_NITEMS
+};
+struct DDLayout {
+  uint32_t off[DD_NITEMS];     // byte offset in smem or in the CTA's workspace
+  uint32_t in_smem;            // bit per item
+  uint32_t tr16;               // Nussinov traceback codes need 16 bits (a column with > 120 candidates)
+  int lp1, lp2;                // row stride of the Nussinov row buffers (max live columns, odd)
+  int trs1, trs2;              // row stride of the Nussinov traceback arrays (max live columns)
+  int w16;                     // NW traceback words per row: ceil(max L2 / 16)
+  char* ws;                    // global workspace
+  size_t ws_stride;            // per CTA
+};
+
+struct DDArgs {
+  const DDProbRef* prob;
+  const int32_t* order;        // queue position -> problem (largest first)
+  int nprob;
+  int* queue;
+  DDLayout lay;
+};
+
+// One Nussinov structure as the decoder sees it (pointers into the staged block).
 struct DDNus {
-  int L, n;
-  const int* col_ptr;          // [L+1] entries of column j
-  const int* row_ptr;          // [L+1]
-  const int* row_ent;          // [n] entry ids of row i, ascending j
-  const uint32_t* ent_ij;      // [n] i | j << 16
-  const float* ent_p;          // [n]
-  const uint8_t* ent_flag;     // [n] bit0: in c_x (dafs.cpp:1037), bit1: j-i > 2 (decoder candidate)
-  float* ent_q;                // [n] multipliers q_x[i][j]
+  int L, n, nd, nI, nJ;
   float w;
-  uint32_t* out;               // [L] result in HBM
+  const int* col_ptr; const int* row_ptr; const int* row_ent;
+  const uint32_t* ent_ab; const int* ent_c; const uint32_t* ent_ij; const float* ent_p; const uint8_t* ent_flag;
+  const uint16_t* rowI; const uint16_t* colJ; const uint16_t* bstart; const uint16_t* rowmap; const uint16_t* colmap;
+  float* ent_q;                // [n] multipliers q_x[i][j]
+};
+
+__device__ __forceinline__ DDNus dd_make_nus(const char* blk, const DDNusHdr& h, float* q) {
+  DDNus S;
+  S.L = h.L; S.n = h.n; S.nd = h.nd; S.nI = h.nI; S.nJ = h.nJ; S.w = h.w; S.ent_q = q;
+  S.col_ptr = reinterpret_cast<const int*>(blk + h.col_ptr);
+  S.row_ptr = reinterpret_cast<const int*>(blk + h.row_ptr);
+  S.row_ent = reinterpret_cast<const int*>(blk + h.row_ent);
+  S.ent_ab = reinterpret_cast<const uint32_t*>(blk + h.ent_ab);
+  S.ent_c = reinterpret_cast<const int*>(blk + h.ent_c);
+  S.ent_ij = reinterpret_cast<const uint32_t*>(blk + h.ent_ij);
+  S.ent_p = reinterpret_cast<const float*>(blk + h.ent_p);
+  S.ent_flag = reinterpret_cast<const uint8_t*>(blk + h.ent_flag);
+  S.rowI = reinterpret_cast<const uint16_t*>(blk + h.rowI);
+  S.colJ = reinterpret_cast<const uint16_t*>(blk + h.colJ);
+  S.bstart = reinterpret_cast<const uint16_t*>(blk + h.bstart);
+  S.rowmap = reinterpret_cast<const uint16_t*>(blk + h.rowmap);
+  S.colmap = reinterpret_cast<const uint16_t*>(blk + h.colmap);
+  return S;
+}
+
+struct NusScratch {
+  float* es;        // [nd] value a candidate contributes: dp[i+1][j-1] + s, or -inf when inactive
+  float* row;       // [32*lp] dp rows (over live columns) of the current wave
+  float* brow;      // [lp] dp row of the live row just below the next wave
+  void* tr;         // [nI*trs] traceback codes: t | down_ge << 7 (or << 15)
+  uint32_t* ss;     // [L] result
+  uint32_t* stk;    // traceback stack
+  int lp, trs;
+  bool tr16;
 };
 
 // The alignment part: sparse p_z / q_z rows and the envelope.
@@ -85,164 +159,147 @@ struct DDAln {
   const uint2* env;            // [L1+1] {first, second}   (needleman_wunsch.cpp:198-253)
 };
 
-// Per-CTA scratch arrays; each lives in shared memory when it fits (host decides,
-// in this order) and in a per-CTA global workspace otherwise.
-enum {
-  DD_CST, DD_Q_X, DD_Q_Y, DD_Q_Z, DD_ES_X, DD_ES_Y, DD_ROW_X, DD_ROW_Y, DD_BROW_X, DD_BROW_Y, DD_BROW_Z,
-  DD_TRZ, DD_TR_X, DD_TR_Y, DD_SS_X, DD_SS_Y, DD_ZRES, DD_STK_X, DD_STK_Y, DD_TAL_X, DD_TAL_Y, DD_TAL_Z,
-  DD_SW, DD_NITEMS
-};
-struct DDLayout {
-  uint32_t off[DD_NITEMS];     // byte offset in smem or in the CTA's workspace
-  uint32_t in_smem;            // bit per item
-  uint32_t tr16;               // traceback codes of Nussinov need 16 bits (a column with > 250 entries)
-  int lp1, lp2;                // padded row length of the Nussinov row buffers
-  int w16;                     // NW traceback words per row: ceil(max L2 / 16)
-  char* ws;                    // global workspace
-  size_t ws_stride;            // per CTA
+struct NwScratch {
+  float* brow;      // [L2+2] dp row above the current wave (row of the previous wave's last lane)
+  uint32_t* trz;    // traceback codes, 2 bits per cell (0 ' ', 1 'M', 2 'X', 3 'Y'), w16 words per row
+  uint32_t* zres;   // [L1] result
+  int w16;
 };
 
-struct DDArgs {
-  const DDProbRef* prob;
-  const int32_t* order;        // queue position -> problem (largest first)
-  int nprob;
-  int* queue;
-  DDLayout lay;
-};
+}  // namespace dafs
 
-template <class T>
-__device__ __forceinline__ T* dd_item(const DDLayout& lay, char* smem, int item) {
-  char* base = (lay.in_smem >> item) & 1u ? smem : lay.ws + (size_t)blockIdx.x * lay.ws_stride;
-  return reinterpret_cast<T*>(base + lay.off[item]);
+namespace dafs {
+
+__device__ __forceinline__ void nus_tr_store(const NusScratch& sc, int idx, int t, bool flag) {
+  if (sc.tr16) reinterpret_cast<uint16_t*>(sc.tr)[idx] = (uint16_t)(t | (flag ? 0x8000 : 0));
+  else reinterpret_cast<uint8_t*>(sc.tr)[idx] = (uint8_t)(t | (flag ? 0x80 : 0));
 }
-
-__device__ __forceinline__ int dd_tri(int L, int i, int j) {   // i < j, row-major upper triangle
-  return i * (2 * L - i - 1) / 2 + (j - i - 1);
-}
-
-struct NusScratch {
-  float* es;        // [n] value a candidate contributes: dp[i+1][j-1] + s, or -inf when inactive
-  float* row;       // [32*lp] dp rows of the current wave
-  float* brow;      // [lp] dp row just above the next wave (row of the wave's last lane)
-  void* tr;         // traceback codes, triangular
-  uint32_t* ss;     // [L] result
-  uint32_t* stk;    // traceback stack
-  int lp;
-  bool tr16;
-};
-
-__device__ __forceinline__ void nus_tr_store(const NusScratch& sc, int idx, int t) {
-  if (sc.tr16) reinterpret_cast<uint16_t*>(sc.tr)[idx] = (uint16_t)t;
-  else reinterpret_cast<uint8_t*>(sc.tr)[idx] = (uint8_t)t;
-}
+// returns t in the low bits and the down_ge flag in bit 16
 __device__ __forceinline__ int nus_tr_load(const NusScratch& sc, int idx) {
-  return sc.tr16 ? (int)reinterpret_cast<const uint16_t*>(sc.tr)[idx]
-                 : (int)reinterpret_cast<const uint8_t*>(sc.tr)[idx];
+  if (sc.tr16) { const int v = reinterpret_cast<const uint16_t*>(sc.tr)[idx]; return (v & 0x7fff) | ((v & 0x8000) << 1); }
+  const int v = reinterpret_cast<const uint8_t*>(sc.tr)[idx];
+  return (v & 0x7f) | ((v & 0x80) << 9);
 }
 
-// SparseNussinov::decode(w, p, q, ss): fill + traceback by one warp.
+// SparseNussinov::decode(w, p, q, ss): fill + traceback by one warp on the
+// compressed grid.  With f(i,j) the reference's dp[i][j], I[] / J[] the live rows
+// / columns and D[a][b] = f(I[a], J[b]) (0 where I[a] >= J[b]):
+//   f(i+1, J[b])   = D[a+1][b]        ("below":  value of the lane one row down)
+//   f(i, J[b]-1)   = D[a][b-1]        ("left":   this lane's previous value)
+//   f(i+1, J[b]-1) = D[a+1][b-1]      ("diag")
+//   f(i, k-1)      = D[a][c(k)]       (c(k) = last live column <= k-1, ent_c)
 // Returns dp[0][L-1] in every lane.
-__device__ __noinline__ float nussinov_warp(const DDNus S, const NusScratch sc, float th, int lane,
-                                            unsigned long long* prof) {
+__device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch& sc, float th, int lane,
+                                               unsigned long long* prof) {
   const long long t0 = clock64();
-  const int L = S.L, lp = sc.lp;
+  const int nI = S.nI, nJ = S.nJ, lp = sc.lp, trs = sc.trs;
   float score = 0.0f;
   float* myrow = sc.row + lane * lp;
-  for (int hi = L - 1; hi >= 0; hi -= 32) {
-    const int row = hi - lane;
-    const bool live = row >= 0;
-    int rcur = 0, rend = 0;
-    if (live) { rcur = S.row_ptr[row]; rend = S.row_ptr[row + 1]; myrow[row] = 0.0f; }
-    int next_j = (rcur < rend) ? (int)(S.ent_ij[S.row_ent[rcur]] >> 16) : 0x7fffffff;
-    float cur = 0.0f;          // dp[row][j-1] entering a step, dp[row][j] leaving it
-    float below_prev = 0.0f;   // dp[row+1][j-1]
-    const bool have_brow = (hi + 1 < L);
-    const int nsteps = (L - 1 - hi) + 32;
+  for (int b = lane; b < nJ; b += 32) sc.brow[b] = 0.0f;     // nothing below the bottom live row
+  __syncwarp();
+  for (int ahi = nI - 1; ahi >= 0; ahi -= 32) {
+    const int a = ahi - lane;
+    const bool live = a >= 0;
+    int i = 0, bs = 0x3fffffff, rcur = 0, rend = 0;
+    if (live) { i = S.rowI[a]; bs = S.bstart[a]; rcur = S.row_ptr[a]; rend = S.row_ptr[a + 1]; }
+    int next_b = (rcur < rend) ? (int)(S.ent_ab[S.row_ent[rcur]] >> 16) : 0x7fffffff;
+    // lane t works on live column B0 + s - t at step s; every lane must reach its
+    // first valid column bs at some s >= 0
+    int B0 = live ? bs + lane : 0x3fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) B0 = min(B0, __shfl_xor_sync(0xffffffffu, B0, o));
+    const int nsteps = (nJ - B0) + 31;
+    float cur = 0.0f;          // D[a][b-1] entering a step, D[a][b] leaving it
+    float below_prev = 0.0f;   // D[a+1][b-1]
+    float brow_next = (lane == 0 && B0 >= 0 && B0 < nJ) ? sc.brow[B0] : 0.0f;
     for (int s = 0; s < nsteps; ++s) {
-      const int j = row + 1 + s;
+      const int b = B0 + s - lane;
       float below = __shfl_up_sync(0xffffffffu, cur, 1);
-      if (lane == 0) below = (have_brow && j < L) ? sc.brow[j] : 0.0f;
-      if (live && j < L) {
-        const int l = s + 1;                               // j - row
+      if (lane == 0) { below = brow_next; brow_next = (b + 1 < nJ) ? sc.brow[b + 1] : 0.0f; }
+      if (live && b >= bs && b < nJ) {
+        const int j = S.colJ[b];
+        const int span = j - i;
         float v = 0.0f;
         int t = 0;
-        if (l >= 2) { v = below; t = 1; }                  // nussinov.cpp:224-228
-        if (l >= 2 && v < cur) { v = cur; t = 2; }         // :229-233
-        if (j == next_j) {                                 // (row, j) is an entry
+        if (span >= 2) { v = below; t = 1; }                 // nussinov.cpp:224-228
+        if (span >= 2 && v < cur) { v = cur; t = 2; }        // :229-233
+        if (b == next_b) {                                   // (i, j) is a candidate (:234)
           const int e = S.row_ent[rcur];
           ++rcur;
-          next_j = (rcur < rend) ? (int)(S.ent_ij[S.row_ent[rcur]] >> 16) : 0x7fffffff;
-          if (S.ent_flag[e] & 2) {                         // :234  i+1 < j-1
-            const float sv = __fsub_rn(__fmul_rn(S.w, __fsub_rn(S.ent_p[e], th)), S.ent_q[e]);   // :236
-            float c = -INFINITY;
-            if (sv > 0.0f) {
-              c = __fadd_rn(below_prev, sv);               // :239
-              if (v < c) { v = c; t = 3; }                 // :240-244
-            }
-            sc.es[e] = c;
+          next_b = (rcur < rend) ? (int)(S.ent_ab[S.row_ent[rcur]] >> 16) : 0x7fffffff;
+          const float sv = __fsub_rn(__fmul_rn(S.w, __fsub_rn(S.ent_p[e], th)), S.ent_q[e]);   // :236
+          float c = -INFINITY;
+          if (sv > 0.0f) {
+            c = __fadd_rn(below_prev, sv);                   // :239
+            if (v < c) { v = c; t = 3; }                     // :240-244
           }
+          sc.es[e] = c;
         }
-        // bifurcations: entries of column j with k > row, in push order (:247-259)
-        const int cb = S.col_ptr[j], ce = S.col_ptr[j + 1];
+        // bifurcations: candidates of column j with k > i, in push order (:247-259)
+        const int cb = S.col_ptr[b], ce = S.col_ptr[b + 1];
         for (int e = cb; e < ce; ++e) {
-          const int k = (int)(S.ent_ij[e] & 0xffffu);
-          if (k <= row) break;
-          const float c = __fadd_rn(myrow[k - 1], sc.es[e]);
+          const int ka = (int)(S.ent_ab[e] & 0xffffu);
+          if (ka <= a) break;
+          const int cc = S.ent_c[e];
+          const float lv = (cc >= bs) ? myrow[cc] : 0.0f;    // dp[i][k-1]
+          const float c = __fadd_rn(lv, sc.es[e]);
           if (v < c) { v = c; t = 4 + (e - cb); }
         }
-        myrow[j] = v;
-        nus_tr_store(sc, dd_tri(L, row, j), t);
-        below_prev = below;
+        myrow[b] = v;
+        nus_tr_store(sc, a * trs + b, t, !(below < v));
         cur = v;
-        if (row == 0 && j == L - 1) score = v;
+        if (a == 0 && b == nJ - 1) score = v;
       }
+      below_prev = below;
       __syncwarp();
     }
     // the row of the last lane becomes the "row below" of the next wave
-    if (hi - 32 >= 0) {
-      const int r31 = hi - 31;
-      for (int j = r31 + lane; j < L; j += 32) sc.brow[j] = sc.row[31 * lp + j];
+    if (ahi - 32 >= 0) {
+      const int bs31 = __shfl_sync(0xffffffffu, bs, 31);
+      for (int b = lane; b < nJ; b += 32) sc.brow[b] = (b >= bs31) ? sc.row[31 * lp + b] : 0.0f;
     }
     __syncwarp();
   }
-  {
-    const int owner = (L - 1) & 31;     // lane of row 0 in the last wave: hi = (L-1)%32 there
-    score = __shfl_sync(0xffffffffu, score, owner);
-  }
-
+  score = __shfl_sync(0xffffffffu, score, (nI > 0) ? ((nI - 1) & 31) : 0);
   const long long t1 = clock64();
-  // ---- traceback (:265-295), all lanes in lock step; runs of code 1 / 2 are
-  // skipped 32 cells at a time.  The order in which the reference's stack is
-  // served does not change ss.
-  for (int i = lane; i < L; i += 32) sc.ss[i] = DD_NOPAIR;
+
+  // ---- traceback (:265-295) on full coordinates, all lanes in lock step.  The
+  // order in which the reference's stack is served does not change ss.
+  for (int k = lane; k < S.L; k += 32) sc.ss[k] = DD_NOPAIR;
   __syncwarp();
   int sp = 0;
-  int i = 0, j = L - 1;
+  int i = 0, j = S.L - 1;
   for (;;) {
     bool pop = false;
     if (i >= j) pop = true;
     else {
-      const int c = nus_tr_load(sc, dd_tri(L, i, j));
-      if (c == 0) pop = true;
-      else if (c == 1) {
-        const int ii = i + 1 + lane;
-        const int cc = (ii < j) ? nus_tr_load(sc, dd_tri(L, ii, j)) : 0;
-        const unsigned m = __ballot_sync(0xffffffffu, cc != 1);
-        i += 1 + (m ? (__ffs(m) - 1) : 32);
-      } else if (c == 2) {
-        const int jj = j - 1 - lane;
-        const int cc = (jj > i) ? nus_tr_load(sc, dd_tri(L, i, jj)) : 0;
-        const unsigned m = __ballot_sync(0xffffffffu, cc != 2);
-        j -= 1 + (m ? (__ffs(m) - 1) : 32);
-      } else if (c == 3) {
-        if (lane == 0) sc.ss[i] = (uint32_t)j;
-        ++i; --j;
-      } else {
-        const int e = S.col_ptr[j] + (c - 4);
-        const int k = (int)(S.ent_ij[e] & 0xffffu);
-        if (lane == 0) { sc.ss[k] = (uint32_t)j; sc.stk[sp] = (uint32_t)(k + 1) | ((uint32_t)(j - 1) << 16); }
-        ++sp;
-        j = k - 1;
+      const int a = S.rowmap[i];
+      const int bj = (int)S.colmap[j] - 1;
+      if (a >= nI || bj < 0) pop = true;                    // no candidate inside [i, j]
+      else {
+        const int ia = S.rowI[a], jb = S.colJ[bj];
+        if (ia >= j || jb <= ia) pop = true;                // dead rows: t = 1 down to span 1; or nothing to pair
+        else {
+          i = ia;                                           // t = 1 through the dead rows above I[a]
+          const int code = nus_tr_load(sc, a * trs + bj);
+          if (jb != j) {
+            // dead column: t = 2 iff f(i+1, j-1) < f(i, j-1), both equal their values at J[bj]
+            if (code & 0x10000) i = i + 1; else j = jb;
+          } else {
+            const int t = code & 0xffff;
+            if (t == 0) pop = true;
+            else if (t == 1) i = i + 1;
+            else if (t == 2) j = j - 1;
+            else if (t == 3) { if (lane == 0) sc.ss[i] = (uint32_t)j; ++i; --j; }
+            else {
+              const int e = S.col_ptr[bj] + (t - 4);
+              const int k = (int)(S.ent_ij[e] & 0xffffu);
+              if (lane == 0) { sc.ss[k] = (uint32_t)j; sc.stk[sp] = (uint32_t)(k + 1) | ((uint32_t)(j - 1) << 16); }
+              ++sp;
+              j = k - 1;
+            }
+          }
+        }
       }
     }
     if (pop) {
@@ -250,6 +307,7 @@ __device__ __noinline__ float nussinov_warp(const DDNus S, const NusScratch sc, 
       --sp;
       __syncwarp();
       const uint32_t w = sc.stk[sp];
+      __syncwarp();
       i = (int)(w & 0xffffu); j = (int)(w >> 16);
     }
   }
@@ -262,61 +320,63 @@ __device__ __noinline__ float nussinov_warp(const DDNus S, const NusScratch sc, 
 
 namespace dafs {
 
-struct NwScratch {
-  float* brow;      // [L2+1] dp row above the current wave (row of the previous wave's last lane)
-  uint32_t* trz;    // traceback codes, 2 bits per cell (0 ' ', 1 'M', 2 'X', 3 'Y'), w16 words per row
-  uint32_t* zres;   // [L1] result
-  int w16;
-};
-
-// SparseNeedlemanWunsch::decode(p, q, al) by one warp: lanes own 32 consecutive
-// rows (a wave, top rows first) and walk their row left to right, one column
-// behind the row above, whose values arrive by warp shuffle.  p_z and q_z are
-// read from the sparse row lists (every other cell has p = q = 0).  Returns
-// dp[L1][L2] in every lane; *bad is set if the traceback meets an unfilled cell
-// (the reference would spin there, needleman_wunsch.cpp:309).
-__device__ __noinline__ float nw_warp(const DDAln A, const NwScratch sc, int lane, int* bad,
-                                      unsigned long long* prof) {
+// SparseNeedlemanWunsch::decode(p, q, al) by one warp.  Returns dp[L1][L2] in
+// every lane; *bad is set if the traceback meets an unfilled cell (the reference
+// would spin there, needleman_wunsch.cpp:309).
+__device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, int lane, int* bad,
+                                         unsigned long long* prof) {
   const long long t0 = clock64();
   const int L1 = A.L1, L2 = A.L2, w16 = sc.w16;
   const float th = A.th;
   float score = 0.0f;
+  for (int k = lane; k <= L2; k += 32) sc.brow[k] = 0.0f;          // row 0: dp[0][k] = 0 (:270-274)
+  __syncwarp();
   for (int lo = 1; lo <= L1; lo += 32) {
     const int row = lo + lane;
     const bool live = row <= L1;
+    const int hi = min(L1, lo + 31);
+    // the envelope is monotone (:240-246): the wave needs columns ef(lo) .. el(hi) only
+    const int kmin = max(1, (int)A.env[lo].x), kmax = (int)A.env[hi].y;
     int ecur = 0, eend = 0, ef = 1, el = 0;
     if (live) {
       ecur = A.row_ptr[row - 1]; eend = A.row_ptr[row];
       const uint2 ev = A.env[row];
       ef = max(1, (int)ev.x); el = (int)ev.y;
+      while (ecur < eend && (int)A.col[ecur] + 1 < kmin) ++ecur;
     }
-    int next_k = (ecur < eend) ? (int)A.col[ecur] + 1 : 0x7fffffff;
-    float cur = 0.0f;      // dp[row][k-1] entering a step (dp[row][0] = 0, :265-268)
-    float diag = 0.0f;     // dp[row-1][k-1]        (dp[.][0] = 0)
+    int next_k = 0x7fffffff; float next_p = 0.0f, next_q = 0.0f;
+    if (ecur < eend) { next_k = (int)A.col[ecur] + 1; next_p = A.p[ecur]; next_q = A.q[ecur]; }
+    // dp[row][kmin-1] and dp[row-1][kmin-1]: column 0 is 0 (:265-268), any other
+    // column left of the wave lies outside these rows' envelopes (:262-264)
+    const float edge = (kmin == 1) ? 0.0f : -FLT_MAX;
+    float cur = edge;
+    float diag = (lane == 0) ? sc.brow[kmin - 1] : edge;
+    float up_next = (lane == 0) ? sc.brow[kmin] : 0.0f;
     uint32_t word = 0;
     uint32_t* trow = sc.trz + row * w16;
-    const int nsteps = L2 + 31;
+    const int nsteps = (kmax - kmin + 1) + 31;
     for (int s = 0; s < nsteps; ++s) {
-      const int k = s - lane + 1;
-      float up = __shfl_up_sync(0xffffffffu, cur, 1);        // dp[row-1][k]
-      if (lane == 0) up = (lo > 1 && k <= L2) ? sc.brow[k] : 0.0f;   // row 0: dp[0][k] = 0 (:270-274)
-      if (live && k >= 1 && k <= L2) {
+      const int k = kmin + s - lane;
+      float up = __shfl_up_sync(0xffffffffu, cur, 1);                // dp[row-1][k]
+      if (lane == 0) { up = up_next; up_next = (k + 1 <= L2) ? sc.brow[k + 1] : 0.0f; }
+      if (live && k >= kmin && k <= kmax) {
         float pv = 0.0f, qv = 0.0f;
         if (k == next_k) {
-          pv = A.p[ecur]; qv = A.q[ecur];
+          pv = next_p; qv = next_q;
           ++ecur;
-          next_k = (ecur < eend) ? (int)A.col[ecur] + 1 : 0x7fffffff;
+          next_k = 0x7fffffff;
+          if (ecur < eend) { next_k = (int)A.col[ecur] + 1; next_p = A.p[ecur]; next_q = A.q[ecur]; }
         }
-        float v;
-        uint32_t code;
+        float v = -FLT_MAX;                                          // :262-264
+        uint32_t code = 0u;
         if (k >= ef && k <= el) {
           v = __fadd_rn(__fsub_rn(__fadd_rn(diag, pv), th), qv);     // :282
           code = 1u;
           if (v < up) { v = up; code = 2u; }                         // :284-288
           if (v < cur) { v = cur; code = 3u; }                       // :289-293
-        } else { v = -FLT_MAX; code = 0u; }                          // :262-264
+        }
         word |= code << (2 * ((k - 1) & 15));
-        if (((k & 15) == 0) || k == L2) { trow[(k - 1) >> 4] = word; word = 0; }
+        if (((k & 15) == 0) || k == kmax) { trow[(k - 1) >> 4] = word; word = 0; }
         diag = up;
         cur = v;
         if (lane == 31) sc.brow[k] = v;
@@ -324,6 +384,11 @@ __device__ __noinline__ float nw_warp(const DDAln A, const NwScratch sc, int lan
       }
       __syncwarp();
     }
+    if (lo + 32 <= L1) {          // complete the row handed to the next wave: unfilled cells
+      for (int k = 1 + lane; k <= L2; k += 32) if (k < kmin || k > kmax) sc.brow[k] = -FLT_MAX;
+      if (lane == 0) sc.brow[0] = 0.0f;
+    }
+    __syncwarp();
   }
   score = __shfl_sync(0xffffffffu, score, (L1 - 1) & 31);
   const long long t1 = clock64();
@@ -349,12 +414,6 @@ __device__ __noinline__ float nw_warp(const DDAln A, const NwScratch sc, int lan
 __device__ __forceinline__ float dd_max0(float v) { return (0.0f < v) ? v : 0.0f; }
 
 struct DDShared {
-  DDNus sx, sy;
-  DDAln az;
-  const int4* cbp;
-  int ncbp, t_max;
-  float th_s, eta0;
-  float* trace;
   float part[3];
   float s, s_prev, c, eta;
   unsigned violated;
@@ -383,33 +442,40 @@ __device__ __forceinline__ void dd_update_nus(const DDNus& S, const uint32_t* ss
 
 #define DD_THREADS 96
 
+// SMEM: every scratch item and the constant block are in shared memory (the host
+// says so), which lets the compiler address them as shared (LDS/STS, 32-bit
+// addresses); otherwise pointers are generic and items may sit in HBM.
+template <bool SMEM>
 __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
   extern __shared__ __align__(16) char smem[];
   __shared__ DDShared sh;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const DDLayout& lay = a.lay;
-  NusScratch nx, ny;
-  nx.es = dd_item<float>(lay, smem, DD_ES_X); ny.es = dd_item<float>(lay, smem, DD_ES_Y);
-  nx.row = dd_item<float>(lay, smem, DD_ROW_X); ny.row = dd_item<float>(lay, smem, DD_ROW_Y);
-  nx.brow = dd_item<float>(lay, smem, DD_BROW_X); ny.brow = dd_item<float>(lay, smem, DD_BROW_Y);
-  nx.tr = dd_item<void>(lay, smem, DD_TR_X); ny.tr = dd_item<void>(lay, smem, DD_TR_Y);
-  nx.ss = dd_item<uint32_t>(lay, smem, DD_SS_X); ny.ss = dd_item<uint32_t>(lay, smem, DD_SS_Y);
-  nx.stk = dd_item<uint32_t>(lay, smem, DD_STK_X); ny.stk = dd_item<uint32_t>(lay, smem, DD_STK_Y);
-  nx.lp = lay.lp1; ny.lp = lay.lp2; nx.tr16 = ny.tr16 = lay.tr16 != 0;
+  char* const wsb = SMEM ? smem : lay.ws + (size_t)blockIdx.x * lay.ws_stride;
+#define DD_ITEM(T, item) reinterpret_cast<T*>((SMEM || ((lay.in_smem >> (item)) & 1u) ? smem : wsb) + lay.off[item])
+  // this warp's Nussinov structure: x for warp 0, y for warp 1 (warp 2 aligns)
+  const int wy = (warp == 1) ? 1 : 0;
+  NusScratch ns;
+  ns.es = DD_ITEM(float, DD_ES_X + wy); ns.row = DD_ITEM(float, DD_ROW_X + wy);
+  ns.brow = DD_ITEM(float, DD_BROW_X + wy); ns.tr = DD_ITEM(void, DD_TR_X + wy);
+  ns.ss = DD_ITEM(uint32_t, DD_SS_X + wy); ns.stk = DD_ITEM(uint32_t, DD_STK_X + wy);
+  ns.lp = wy ? lay.lp2 : lay.lp1; ns.trs = wy ? lay.trs2 : lay.trs1; ns.tr16 = lay.tr16 != 0;
   NwScratch nz;
-  nz.brow = dd_item<float>(lay, smem, DD_BROW_Z);
-  nz.trz = dd_item<uint32_t>(lay, smem, DD_TRZ);
-  nz.zres = dd_item<uint32_t>(lay, smem, DD_ZRES);
+  nz.brow = DD_ITEM(float, DD_BROW_Z); nz.trz = DD_ITEM(uint32_t, DD_TRZ); nz.zres = DD_ITEM(uint32_t, DD_ZRES);
   nz.w16 = lay.w16;
-  int* tal_x = dd_item<int>(lay, smem, DD_TAL_X);
-  int* tal_y = dd_item<int>(lay, smem, DD_TAL_Y);
-  int* tal_z = dd_item<int>(lay, smem, DD_TAL_Z);
-  float* sw = dd_item<float>(lay, smem, DD_SW);
-  float* q_x = dd_item<float>(lay, smem, DD_Q_X);
-  float* q_y = dd_item<float>(lay, smem, DD_Q_Y);
-  float* q_z = dd_item<float>(lay, smem, DD_Q_Z);
-  char* cst_s = dd_item<char>(lay, smem, DD_CST);
-  const bool cst_in_smem = (lay.in_smem >> DD_CST) & 1u;
+  uint32_t* ss_x = DD_ITEM(uint32_t, DD_SS_X);
+  uint32_t* ss_y = DD_ITEM(uint32_t, DD_SS_Y);
+  float* es_x = DD_ITEM(float, DD_ES_X);
+  float* es_y = DD_ITEM(float, DD_ES_Y);
+  int* tal_x = DD_ITEM(int, DD_TAL_X);
+  int* tal_y = DD_ITEM(int, DD_TAL_Y);
+  int* tal_z = DD_ITEM(int, DD_TAL_Z);
+  float* sw = DD_ITEM(float, DD_SW);
+  float* q_x = DD_ITEM(float, DD_Q_X);
+  float* q_y = DD_ITEM(float, DD_Q_Y);
+  float* q_z = DD_ITEM(float, DD_Q_Z);
+  char* cst_s = DD_ITEM(char, DD_CST);
+  const bool cst_in_smem = SMEM || ((lay.in_smem >> DD_CST) & 1u);
 
   for (;;) {
     __syncthreads();
@@ -417,68 +483,53 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     __syncthreads();
     if (sh.q >= a.nprob) break;
     const DDProbRef pr = a.prob[a.order[sh.q]];
-    const DDHdr* gh = reinterpret_cast<const DDHdr*>(pr.cst);
     const char* blk = pr.cst;
     if (cst_in_smem) {            // stage the constant block: coalesced 16-byte copies
-      const int n16 = gh->bytes >> 4;
+      const int n16 = reinterpret_cast<const DDHdr*>(pr.cst)->bytes >> 4;
       const uint4* src = reinterpret_cast<const uint4*>(pr.cst);
       uint4* dst = reinterpret_cast<uint4*>(cst_s);
       for (int k = tid; k < n16; k += DD_THREADS) dst[k] = src[k];
       blk = cst_s;
     }
     __syncthreads();
-    if (tid == 0) {
-      const DDHdr& h = *reinterpret_cast<const DDHdr*>(blk);
-      DDNus& X = sh.sx; DDNus& Y = sh.sy; DDAln& Z = sh.az;
-      X.L = h.L1; X.n = h.nx; X.w = h.wx; X.out = pr.x_out; X.ent_q = q_x;
-      X.col_ptr = reinterpret_cast<const int*>(blk + h.x_col_ptr);
-      X.row_ptr = reinterpret_cast<const int*>(blk + h.x_row_ptr);
-      X.row_ent = reinterpret_cast<const int*>(blk + h.x_row_ent);
-      X.ent_ij = reinterpret_cast<const uint32_t*>(blk + h.x_ij);
-      X.ent_p = reinterpret_cast<const float*>(blk + h.x_p);
-      X.ent_flag = reinterpret_cast<const uint8_t*>(blk + h.x_flag);
-      Y.L = h.L2; Y.n = h.ny; Y.w = h.wy; Y.out = pr.y_out; Y.ent_q = q_y;
-      Y.col_ptr = reinterpret_cast<const int*>(blk + h.y_col_ptr);
-      Y.row_ptr = reinterpret_cast<const int*>(blk + h.y_row_ptr);
-      Y.row_ent = reinterpret_cast<const int*>(blk + h.y_row_ent);
-      Y.ent_ij = reinterpret_cast<const uint32_t*>(blk + h.y_ij);
-      Y.ent_p = reinterpret_cast<const float*>(blk + h.y_p);
-      Y.ent_flag = reinterpret_cast<const uint8_t*>(blk + h.y_flag);
-      Z.L1 = h.L1; Z.L2 = h.L2; Z.n = h.nz; Z.th = h.th_a; Z.q = q_z;
-      Z.row_ptr = reinterpret_cast<const int*>(blk + h.z_row_ptr);
-      Z.col = reinterpret_cast<const uint16_t*>(blk + h.z_col);
-      Z.p = reinterpret_cast<const float*>(blk + h.z_p);
-      Z.flag = reinterpret_cast<const uint8_t*>(blk + h.z_flag);
-      Z.env = reinterpret_cast<const uint2*>(blk + h.z_env);
-      sh.cbp = reinterpret_cast<const int4*>(blk + h.cbp);
-      sh.ncbp = h.ncbp; sh.t_max = h.t_max; sh.th_s = h.th_s; sh.eta0 = h.eta0; sh.trace = pr.trace;
-      sh.c = 0.0f; sh.eta = h.eta0; sh.s_prev = 0.0f; sh.violated = 0; sh.done = 0; sh.bad = 0;
-      for (int k = 0; k < 8; ++k) sh.prof[k] = 0;
-    }
-    __syncthreads();
-    const int L1 = sh.az.L1, L2 = sh.az.L2, ncbp = sh.ncbp, t_max = sh.t_max;
+    const DDHdr& h = *reinterpret_cast<const DDHdr*>(blk);
+    const DDNus X = dd_make_nus(blk, h.x, q_x), Y = dd_make_nus(blk, h.y, q_y);
+    const DDNus& mine = wy ? Y : X;
+    DDAln Z;
+    Z.L1 = h.L1; Z.L2 = h.L2; Z.n = h.nz; Z.th = h.th_a; Z.q = q_z;
+    Z.row_ptr = reinterpret_cast<const int*>(blk + h.z_row_ptr);
+    Z.col = reinterpret_cast<const uint16_t*>(blk + h.z_col);
+    Z.p = reinterpret_cast<const float*>(blk + h.z_p);
+    Z.flag = reinterpret_cast<const uint8_t*>(blk + h.z_flag);
+    Z.env = reinterpret_cast<const uint2*>(blk + h.z_env);
+    const int4* cbp = reinterpret_cast<const int4*>(blk + h.cbp);
+    const int L1 = h.L1, L2 = h.L2, ncbp = h.ncbp, t_max = h.t_max;
+    const float th_s = h.th_s, eta0 = h.eta0;
 
     // ---- q = 0 (dafs.cpp:1067-1069), scratch reset ----------------------------
-    for (int e = tid; e < sh.sx.n; e += DD_THREADS) { q_x[e] = 0.0f; nx.es[e] = -INFINITY; tal_x[e] = 0; }
-    for (int e = tid; e < sh.sy.n; e += DD_THREADS) { q_y[e] = 0.0f; ny.es[e] = -INFINITY; tal_y[e] = 0; }
-    for (int e = tid; e < sh.az.n; e += DD_THREADS) { q_z[e] = 0.0f; tal_z[e] = 0; }
-    for (int k = tid; k < L1; k += DD_THREADS) { nx.ss[k] = DD_NOPAIR; nz.zres[k] = DD_NOPAIR; }
-    for (int k = tid; k < L2; k += DD_THREADS) ny.ss[k] = DD_NOPAIR;
+    for (int e = tid; e < X.n; e += DD_THREADS) { q_x[e] = 0.0f; tal_x[e] = 0; if (e < X.nd) es_x[e] = -INFINITY; }
+    for (int e = tid; e < Y.n; e += DD_THREADS) { q_y[e] = 0.0f; tal_y[e] = 0; if (e < Y.nd) es_y[e] = -INFINITY; }
+    for (int e = tid; e < Z.n; e += DD_THREADS) { q_z[e] = 0.0f; tal_z[e] = 0; }
+    for (int k = tid; k < L1; k += DD_THREADS) { ss_x[k] = DD_NOPAIR; nz.zres[k] = DD_NOPAIR; }
+    for (int k = tid; k < L2; k += DD_THREADS) ss_y[k] = DD_NOPAIR;
+    if (tid == 0) {
+      sh.c = 0.0f; sh.eta = eta0; sh.s_prev = 0.0f; sh.violated = 0; sh.done = 0; sh.bad = 0;
+      for (int k = 0; k < 8; ++k) sh.prof[k] = 0;
+    }
     __syncthreads();
 
     int t = 0;
     for (; t < t_max; ++t) {
       // ---- the three subproblems (dafs.cpp:1090-1093) -------------------------
       const long long tp0 = clock64();
-      if (warp == 0) { const float v = nussinov_warp(sh.sx, nx, sh.th_s, lane, sh.prof + 0); if (lane == 0) sh.part[0] = v; }
-      else if (warp == 1) { const float v = nussinov_warp(sh.sy, ny, sh.th_s, lane, sh.prof + 2); if (lane == 0) sh.part[1] = v; }
-      else { const float v = nw_warp(sh.az, nz, lane, &sh.bad, sh.prof + 4); if (lane == 0) sh.part[2] = v; }
+      if (warp < 2) { const float v = nussinov_warp(mine, ns, th_s, lane, sh.prof + 2 * wy); if (lane == 0) sh.part[wy] = v; }
+      else { const float v = nw_warp(Z, nz, lane, &sh.bad, sh.prof + 4); if (lane == 0) sh.part[2] = v; }
       if (tid == 0) sh.violated = 0;
       __syncthreads();
       const long long tp1 = clock64();
       // ---- tally (:1103-1117) ---------------------------------------------------
       for (int u = tid; u < ncbp; u += DD_THREADS) {
-        const int4 cb = sh.cbp[u];
+        const int4 cb = cbp[u];
         const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_z[cb.z]), q_z[cb.w]);
         sw[u] = s_w;
         if (s_w > 0.0f) {
@@ -498,26 +549,23 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       // ---- multiplier updates (:1121-1254) -----------------------------------------
       const float eta = sh.eta;
       unsigned viol = 0;
-      dd_update_nus(sh.sx, nx.ss, tal_x, eta, viol, tid, DD_THREADS);
-      dd_update_nus(sh.sy, ny.ss, tal_y, eta, viol, tid, DD_THREADS);
-      // z (:1223-1254), one thread per c_z entry.  Cells outside c_z have t_z = 0
-      // and q_z = 0, and stay there: max(0, 0 - eta*(1-0)) = 0 for eta >= 0 or NaN
-      // (the host rejects eta0 < 0).
-      {
-        const DDAln& Z = sh.az;
-        for (int i = tid; i < L1; i += DD_THREADS) {
-          const uint32_t zi = nz.zres[i];
-          for (int e = Z.row_ptr[i]; e < Z.row_ptr[i + 1]; ++e) {
-            if (!(Z.flag[e] & 1)) continue;
-            const int tz = tal_z[e];
-            tal_z[e] = 0;
-            if (zi == (uint32_t)Z.col[e]) {                       // z_ik == 1  (:1226-1238)
-              if (tz > 1) ++viol;
-              q_z[e] = dd_max0(__fsub_rn(q_z[e], __fmul_rn(eta, (float)(1 - tz))));
-            } else {                                               // z_ik == 0  (:1239-1253)
-              if (tz > 0) ++viol;
-              q_z[e] = dd_max0(__fadd_rn(q_z[e], __fmul_rn(eta, (float)tz)));
-            }
+      dd_update_nus(X, ss_x, tal_x, eta, viol, tid, DD_THREADS);
+      dd_update_nus(Y, ss_y, tal_y, eta, viol, tid, DD_THREADS);
+      // z (:1223-1254), one thread per row over its c_z entries.  Cells outside c_z
+      // have t_z = 0 and q_z = 0, and stay there: max(0, 0 - eta*(1-0)) = 0 for
+      // eta >= 0 or NaN (the host rejects eta0 < 0).
+      for (int i = tid; i < L1; i += DD_THREADS) {
+        const uint32_t zi = nz.zres[i];
+        for (int e = Z.row_ptr[i]; e < Z.row_ptr[i + 1]; ++e) {
+          if (!(Z.flag[e] & 1)) continue;
+          const int tz = tal_z[e];
+          tal_z[e] = 0;
+          if (zi == (uint32_t)Z.col[e]) {                       // z_ik == 1  (:1226-1238)
+            if (tz > 1) ++viol;
+            q_z[e] = dd_max0(__fsub_rn(q_z[e], __fmul_rn(eta, (float)(1 - tz))));
+          } else {                                               // z_ik == 0  (:1239-1253)
+            if (tz > 0) ++viol;
+            q_z[e] = dd_max0(__fadd_rn(q_z[e], __fmul_rn(eta, (float)tz)));
           }
         }
       }
@@ -526,25 +574,25 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       if (tid == 0) {
         const unsigned violated = sh.violated;
         const float s = sh.s;
-        if (sh.trace) { sh.trace[3 * t] = s; sh.trace[3 * t + 1] = eta; sh.trace[3 * t + 2] = (float)violated; }
+        if (pr.trace) { pr.trace[3 * t] = s; pr.trace[3 * t + 1] = eta; pr.trace[3 * t + 2] = (float)violated; }
         if (violated == 0) sh.done = 1;                     // :1278
         else {
           if (s > sh.s_prev || t == 0) {                    // :1283-1288
             const float n4 = __fmul_rn(4.0f, (float)(unsigned long long)ncbp);
             const float av = dd_max0(__fsub_rn(n4, (float)violated));
             sh.c = (float)((double)sh.c + (double)av / (4.0 * (double)ncbp));
-            sh.eta = (float)((double)sh.eta0 / (1.0 + (double)sh.c));
+            sh.eta = (float)((double)eta0 / (1.0 + (double)sh.c));
           }
           sh.s_prev = s;
         }
+        sh.prof[6] += tp1 - tp0; sh.prof[7] += clock64() - tp1;
       }
       __syncthreads();
-      if (tid == 0) { sh.prof[6] += tp1 - tp0; sh.prof[7] += clock64() - tp1; }
       if (sh.done) break;
     }
     // ---- results -------------------------------------------------------------------
-    for (int k = tid; k < L1; k += DD_THREADS) { pr.x_out[k] = nx.ss[k]; pr.z_out[k] = nz.zres[k]; }
-    for (int k = tid; k < L2; k += DD_THREADS) pr.y_out[k] = ny.ss[k];
+    for (int k = tid; k < L1; k += DD_THREADS) { pr.x_out[k] = ss_x[k]; pr.z_out[k] = nz.zres[k]; }
+    for (int k = tid; k < L2; k += DD_THREADS) pr.y_out[k] = ss_y[k];
     if (tid == 0) {
       pr.result[0] = sh.s_prev;
       reinterpret_cast<int*>(pr.result)[1] = t;
@@ -553,6 +601,7 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       for (int k = 0; k < 8; ++k) pr.result[4 + k] = (float)sh.prof[k];
     }
   }
+#undef DD_ITEM
 }
 
 }  // namespace dafs
