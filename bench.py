@@ -201,6 +201,94 @@ def config_dict(ngpu):
 
 
 # ---------------------------------------------------------------------------
+# The other two stages of the path ("plus DD problems/sec and
+# iterations/sec for C3; plus sequences/sec for McCaskill on C5"), reported under
+# "stages" next to the headline.  Units are dealt round-robin to ranks like the
+# pairs; every figure is device time (CUDA events inside the library), max over ranks.
+def c3_problems(rank, world, t_max=600):
+    """C3: N=64, L=150, one two-leaf problem per pair: p_z from the pair-HMM stage,
+    p_x / p_y synthetic base-pairing probabilities (dafs_b200/synth.py)."""
+    import dafs_b200
+    n, L = 64, 150
+    seqs = dafs_b200.random_rna(n, L, config_id=3)
+    bpp = [dafs_b200.synthetic_bpp(L, 3 + s % 4, s) for s in range(n)]
+    pi, pj = dafs_b200.all_pairs(n)
+    mine = shard(len(pi), rank, world)
+    with dafs_b200.pairhmm_pairs(seqs, pi[mine], pj[mine], TH) as b:
+        pz = [b.dense(u, L) for u in range(len(mine))]
+    return [dict(p_x=bpp[pi[g]], p_y=bpp[pj[g]], p_z=pz[u], t_max=t_max) for u, g in enumerate(mine)], len(pi)
+
+
+def cpu_threads(fn, items, cores):
+    from concurrent.futures import ThreadPoolExecutor
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cores) as ex:
+        out = list(ex.map(fn, items))
+    return time.perf_counter() - t0, out
+
+
+def run_stages(rank, world, max_over_ranks, steps, with_cpu):
+    import dafs_b200
+    out = {}
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    # ---- (3) DD on C3 ------------------------------------------------------------
+    probs, nprob = c3_problems(rank, world)
+    t0 = time.perf_counter()
+    plan = dafs_b200.DDPlan(probs)
+    t_create = time.perf_counter() - t0
+    ms = []
+    for it in range(2 + steps):
+        plan.run(); m = plan.sync()
+        if it >= 2:
+            ms.append(m)
+    res = plan.fetch()
+    info = plan.info()
+    plan.close()
+    iters = float(sum(min(r["iters"] + 1, 600) for r in res))
+    t = max_over_ranks(sum(ms) / len(ms)) * 1e-3
+    iters_all = max_over_ranks(iters) if world == 1 else None
+    out["dd_C3"] = {"workload": "C3: N=64 L=150, %d two-leaf problems, -m 600, reference stopping rule" % nprob,
+                    "problems_per_s": nprob / t, "ms_per_step": t * 1e3,
+                    "iterations_per_s_rank0": iters / (sum(ms) / len(ms) * 1e-3), "iterations_rank0": iters,
+                    "plan_create_s_rank0": t_create, "grid": info["grid"], "smem_bytes": info["smem_bytes"],
+                    "gpu_launches_per_step": 1}
+    if with_cpu and rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_util as ou
+        kind = "reference" if ou.have_ref() else "port"
+        f = ou.ref_dd if ou.have_ref() else ou.oracle_dd
+        sample = probs[:: max(1, len(probs) // (4 * cores))][: 4 * cores]
+        dt, o = cpu_threads(lambda p: f(p["p_x"], p["p_y"], p["p_z"], t_max=600), sample, cores)
+        out["dd_C3"]["cpu_baseline"] = {"value": len(sample) / dt, "unit": "problems/s", "cores": cores, "kind": kind,
+                                        "iterations_per_s": sum(min(r["iters"] + 1, 600) for r in o) / dt,
+                                        "sample": "%d of the %d problems, %d host threads" % (len(sample), nprob, cores)}
+    # ---- (2) McCaskill on C4's sequences and on C5 -------------------------------
+    for name, n, L, cid in (("mccaskill_C4", NSEQ, LEN, CONFIG_ID), ("mccaskill_C5", 16, 1500, 5)):
+        seqs = dafs_b200.random_rna(n, L, config_id=cid)
+        mine = [seqs[k] for k in shard(n, rank, world)]
+        plan = dafs_b200.McCaskillPlan(mine, TH)
+        ms = []
+        reps = steps if L < 1000 else min(steps, 2)
+        for it in range(1 + reps):
+            plan.run(); m, nnz = plan.sync()
+            if it >= 1:
+                ms.append(m)
+        info = plan.info()
+        plan.close()
+        t = max_over_ranks(sum(ms) / len(ms)) * 1e-3
+        out[name] = {"workload": "N=%d L=%d random RNA, BL* parameters, cutoff %g" % (n, L, TH),
+                     "sequences_per_s": n / t, "ms_per_step": t * 1e3, "nnz_rank0": int(nnz), "dtype": "f64",
+                     "grid": info["grid"], "block": info["block"], "smem_bytes": info["smem_bytes"],
+                     "gpu_launches_per_step": 3}
+        if with_cpu and rank == 0:
+            import oracle_util as ou
+            k = min(cores, n) if L < 1000 else min(cores, n, 4)
+            dt, _ = cpu_threads(lambda q: ou.oracle_mccaskill(q)[1], seqs[:k], k)
+            out[name]["cpu_baseline"] = {"value": k / dt, "unit": "sequences/s", "cores": k, "kind": "port",
+                                         "sample": "%d sequences, one per host thread (FP64 restatement, parity unpinned)" % k}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -302,6 +390,7 @@ def run_ours(args):
         flop_launch = len(mine) * cells * FLOP_PER_CELL
         achieved = flop_launch / (kernel_ms * 1e-3) / 1e12
         peaks = measured_peaks()
+        fma_tf, muladd_tf = dafs_b200.fp32_probe()
         alg_bytes = len(mine) * (2 * LEN + 4 * (LEN + 1)) + 8 * (nnz_total // world)
         traffic = None
         try:
@@ -320,12 +409,16 @@ def run_ours(args):
             "kernel": {"name": "pairhmm_kernel<C=%d>" % info["cols_per_lane"], "grid": info["grid"],
                        "block": info["warps_per_cta"] * 32, "avg_ms": kernel_ms,
                        "workspace_bytes": info["workspace_bytes"]},
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": FP32_NOMINAL_TFLOPS, "unit": "TFLOP/s",
-                         "frac": achieved / FP32_NOMINAL_TFLOPS, "traffic": traffic,
-                         "note": "FP32 CUDA-core bound (no tensor-core or HBM roofline applies); peak = nominal FMA "
-                                 "peak 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry); "
-                                 "bit-exact parity forbids FMA, so the reachable ceiling is peak/2; "
-                                 "achieved = %d algorithmic flop/cell x cells per launch / kernel time" % FLOP_PER_CELL},
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fma_tf, "unit": "TFLOP/s",
+                         "frac": achieved / fma_tf, "traffic": traffic,
+                         "peak_nominal": FP32_NOMINAL_TFLOPS, "peak_unfused_muladd": muladd_tf,
+                         "frac_of_unfused": achieved / muladd_tf,
+                         "note": "FP32 CUDA-core bound (SURVEY.md 8(d): neither the HBM nor the tensor roofline applies; "
+                                 "the HBM view is in roofline_hbm); peak = FFMA rate measured by dafs_cuda_fp32_probe in "
+                                 "this run (MEASURED_PEAKS.json has no FP32 entry; nominal 148 SM x 128 x 2 x 1.965 GHz "
+                                 "in peak_nominal); bit-exact parity forbids FMA, so the reachable ceiling is "
+                                 "peak_unfused_muladd; achieved = %d algorithmic flop/cell x cells per launch / kernel "
+                                 "time" % FLOP_PER_CELL},
             "roofline_hbm": {"bound": "hbm", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
                              "peak": (peaks or {}).get("hbm_gbs", 6650.0), "unit": "GB/s",
                              "peak_source": "measured" if peaks else "fallback",
@@ -335,6 +428,12 @@ def run_ours(args):
         if world == 1 and not args.no_cpu:
             cb, _ = time_cpu(seqs, npairs, 12.0)
             line["cpu_baseline"] = cb
+    stages = None
+    if not args.no_stages:
+        stages = run_stages(rank, world, max_over_ranks, min(K, 5), world == 1 and not args.no_cpu)
+    if rank == 0:
+        if stages:
+            line["stages"] = stages
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -346,7 +445,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--no-stages", action="store_true", help="headline pair-HMM stage only")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

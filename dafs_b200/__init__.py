@@ -12,6 +12,7 @@ from .capi import (  # noqa: F401
     PairHmmPlan,
     all_pairs,
     device_count,
+    fp32_probe,
     init,
     lib,
     library_path,

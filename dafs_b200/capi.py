@@ -87,6 +87,15 @@ def device_count():
     return int(lib().dafs_cuda_device_count())
 
 
+def fp32_probe():
+    """(FFMA TFLOP/s, FMUL+FADD TFLOP/s) measured on the current device."""
+    a, b = C.c_double(0), C.c_double(0)
+    L = lib()
+    L.dafs_cuda_fp32_probe.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    _check(L.dafs_cuda_fp32_probe(C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
 def _as_bytes(seqs):
     return [s.encode("ascii") if isinstance(s, str) else bytes(s) for s in seqs]
 

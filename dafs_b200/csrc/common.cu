@@ -73,9 +73,57 @@ void pinned_trim() {
   g_pin_cached = 0;
 }
 
+// FP32 issue-rate probe: 8 independent chains per thread, 4 CTAs of 256 per SM.
+// FMA = true counts 2 flop per FFMA; false issues FMUL + FADD (what the bit-exact
+// pair-HMM arithmetic is restricted to, pairhmm_math.cuh) and counts 1 each.
+template <bool FMA>
+__global__ void __launch_bounds__(256) fp32_probe_kernel(float* out, float a, float b, int iters) {
+  float v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = (float)(threadIdx.x + k) * 1e-3f;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = FMA ? __fmaf_rn(v[k], a, b) : __fadd_rn(__fmul_rn(v[k], a), b);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += v[k];
+  if (s == 12345.678f) out[0] = s;
+}
+
 }  // namespace dafs
 
 extern "C" {
+
+int dafs_cuda_fp32_probe(double* fma_tflops, double* muladd_tflops) {
+  int dev = 0, sms = 0;
+  DAFS_CUDA_TRY(cudaGetDevice(&dev));
+  DAFS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  float* out = nullptr;
+  DAFS_CUDA_TRY(cudaMalloc(&out, 4));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int iters = 1 << 15, grid = sms * 8;
+  double best[2] = {0, 0};
+  for (int mode = 0; mode < 2; ++mode)
+    for (int rep = 0; rep < 4; ++rep) {
+      cudaEventRecord(e0);
+      if (mode == 0) dafs::fp32_probe_kernel<true><<<grid, 256>>>(out, 0.999f, 1e-3f, iters);
+      else dafs::fp32_probe_kernel<false><<<grid, 256>>>(out, 0.999f, 1e-3f, iters);
+      cudaEventRecord(e1);
+      DAFS_CUDA_TRY(cudaEventSynchronize(e1));
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, e1);
+      const double tf = 2.0 * 8 * iters * 256.0 * grid / (ms * 1e-3) / 1e12;
+      if (rep && tf > best[mode]) best[mode] = tf;
+    }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(out);
+  DAFS_CUDA_TRY(cudaGetLastError());
+  if (fma_tflops) *fma_tflops = best[0];
+  if (muladd_tflops) *muladd_tflops = best[1];
+  return DAFS_CUDA_OK;
+}
 
 const char* dafs_cuda_last_error(void) { return dafs::last_error().c_str(); }
 

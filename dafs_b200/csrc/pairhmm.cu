@@ -303,6 +303,17 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
   const int max_grid = prop.multiProcessorCount * kMinBlocks;
   p->grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_grid, (npairs + kWarps - 1) / kWarps));
+  {
+    // three planes per warp slot; long sequences get fewer resident CTAs rather
+    // than more than 60 % of the free HBM
+    size_t free_b = 0, total_b = 0;
+    PLAN_TRY(cudaMemGetInfo(&free_b, &total_b));
+    const int64_t per_cta = (int64_t)sizeof(float) * 3 * p->plane_stride * kWarps;
+    const int64_t fit = (int64_t)((double)free_b * 0.6) / std::max<int64_t>(per_cta, 1);
+    if (fit < 1) return bail(fail(DAFS_CUDA_ENOMEM, "pair-HMM workspace for %d x %d does not fit in HBM", max_l1, max_l2));
+    p->grid = (int)std::min<int64_t>(p->grid, fit);
+  }
+  if (max_l1 > 65534 || max_l2 > 65534) return bail(fail(DAFS_CUDA_EINVAL, "sequences longer than 65534 are not supported"));
   const int64_t slots = (int64_t)p->grid * kWarps;
 
   PLAN_TRY(cudaMalloc(&p->d_seq, enc.size()));
@@ -310,7 +321,7 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * std::max(nseq, 1)));
   PLAN_TRY(cudaMalloc(&p->d_pairs, sizeof(int2) * pairs.size()));
   PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * order.size()));
-  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * 2 * p->plane_stride * slots));
+  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * 3 * p->plane_stride * slots));
   PLAN_TRY(cudaMalloc(&p->d_bnd, sizeof(float4) * p->bnd_stride * 2 * slots));
   PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
   PLAN_TRY(cudaMalloc(&p->d_pool_count, sizeof(unsigned long long)));
@@ -368,7 +379,7 @@ extern "C" int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* p, float* device_m
 extern "C" int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* p, dafs_pairhmm_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   info->cols_per_lane = p->C; info->grid = p->grid; info->warps_per_cta = dafs::kWarps;
-  info->workspace_bytes = (int64_t)sizeof(float) * 2 * p->plane_stride * p->grid * dafs::kWarps;
+  info->workspace_bytes = (int64_t)sizeof(float) * 3 * p->plane_stride * p->grid * dafs::kWarps;
   info->last_total_ms = p->last_ms; info->last_kernel_ms = p->last_kernel_ms;
   info->launches_per_run = 3;
   return DAFS_CUDA_OK;

@@ -1,5 +1,12 @@
-// Backward sweep of one column stripe (ProbabilisticModel.h:197-259); B_M goes to
-// its own plane so the DP loop issues no global loads.
+// Backward sweep of one column stripe (ProbabilisticModel.h:197-259), fused with
+// the first half of the posterior: B_M never goes to memory.  At the top of a step
+// the lane loads its C values of the forward plane for the row it is about to
+// compute (consumed only after the ~1000 instructions of the row, so the load
+// latency is hidden), and every cell whose F_M + B_M clears a loose bound
+// (candidate test, see pairhmm_pair) is appended to the pair's candidate list as
+// (row << 16 | column, F_M + B_M).  Rows of one stripe leave the pipeline from the
+// highest column to the lowest and stripes run right to left, so inside the list
+// the entries of any one row are in strictly descending column order.
 // Mirror image of forward_stripe: lane 31 starts, rows run L1..0, each lane walks
 // its columns right to left and hands its first column to lane t-1.
 #pragma once
@@ -18,8 +25,9 @@ struct StripeColsB {      // per-lane constants: column j+1 of each owned column
 template <int C>
 __device__ __forceinline__ void backward_stripe(
     const PairHmmSmem& sm, const uint8_t* __restrict__ s1, int L1, int L2, int stripe,
-    int nstripes, int lane, const StripeColsB<C>& sc, float* __restrict__ plane, int PW,
-    const float4* __restrict__ bnd_in, float4* __restrict__ bnd_out, float (&bcap)[3]) {
+    int nstripes, int lane, const StripeColsB<C>& sc, const float* __restrict__ planeF, int PW,
+    const float4* __restrict__ bnd_in, float4* __restrict__ bnd_out, float (&bcap)[3],
+    float lthr, uint32_t* __restrict__ ckey, float* __restrict__ csum, int& run) {
   const float T00 = c_tab.trans[0], T01 = c_tab.trans[1], T02 = c_tab.trans[2];
   const float T10 = c_tab.trans[3], T11 = c_tab.trans[4];
   const float T20 = c_tab.trans[6], T22 = c_tab.trans[8];
@@ -42,7 +50,22 @@ __device__ __forceinline__ void backward_stripe(
     const int cls1 = cls_next;                       // class of seq1[i+1] (1-based)
     // next step works on row i-1 and needs the symbol of row i: s1[i-1]
     if (i >= 1 && i <= L1) cls_next = s1[i - 1];
-    if (i < 0 || i > L1) continue;
+    unsigned cm = 0;                                 // candidate cells of this lane's row
+    float fv[C];
+    if (i >= 0 && i <= L1) {
+    {
+      const float* frow = planeF + (int64_t)i * PW + j0;
+      if constexpr (C % 2 == 0) {
+#pragma unroll
+        for (int c = 0; c < C; c += 2) {
+          const float2 v = __ldcs(reinterpret_cast<const float2*>(frow) + c / 2);
+          fv[c] = v.x; fv[c + 1] = v.y;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) fv[c] = __ldcs(frow + c);
+      }
+    }
     if (lane == 31) {
       if (stripe + 1 < nstripes) { const float4 b = bnd_in[i]; rM = b.x; rY = b.z; }
       else { rM = rY = DAFS_LOG_ZERO; }
@@ -51,7 +74,6 @@ __device__ __forceinline__ void backward_stripe(
     const float* mrow = sm.match + cls1 * 8 * 32;
     float rightY = rY;                               // B_Y(i, j+1)
     float gM = dM;                                   // B_M(i+1, j+1)
-    float* prow = plane + (int64_t)i * PW + j0;            // B_M plane
     const int seed = (i == L1) ? (L2 - j0) : -1;     // column slot of cell (L1, L2)
 #pragma unroll
     for (int c = C - 1; c >= 0; --c) {
@@ -68,7 +90,13 @@ __device__ __forceinline__ void backward_stripe(
       gM = pM[c];
       pM[c] = nM; pX[c] = nX; pY[c] = nY;
       rightY = nY;
-      prow[c] = nM;
+      fv[c] = __fadd_rn(fv[c], nM);                  // forward + backward (:393-397)
+      if (fv[c] > lthr) cm |= 1u << c;
+    }
+    {
+      // rows 1..L1 and columns 1..L2 only (ComputePosteriorMatrix, :386-399)
+      const int lo = max(0, 1 - j0), hi = min(C, L2 + 1 - j0);
+      cm = (i >= 1 && lo < hi) ? (cm >> lo << lo) & ((1u << hi) - 1u) : 0u;
     }
     dM = rM;
     oM = pM[0]; oY = pY[0];
@@ -76,6 +104,26 @@ __device__ __forceinline__ void backward_stripe(
     if (stripe == 0 && lane == 0) {
       if (i == 1) { bcap[0] = pM[1]; bcap[1] = pX[0]; }
       if (i == 0) bcap[2] = pY[1];
+    }
+    }  // active row
+    // ---- append this step's candidates (warp-uniform control flow) ----------
+    const int n = __popc(cm);
+    if (__any_sync(0xffffffffu, n != 0)) {
+      int incl = n;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      int pos = run + incl - n;
+#pragma unroll
+      for (int c = C - 1; c >= 0; --c)
+        if (cm >> c & 1u) {
+          ckey[pos] = ((uint32_t)i << 16) | (uint32_t)(j0 + c);
+          csum[pos] = fv[c];
+          ++pos;
+        }
+      run += __shfl_sync(0xffffffffu, incl, 31);
     }
   }
 }

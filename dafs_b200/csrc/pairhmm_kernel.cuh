@@ -13,8 +13,9 @@
 // skewed pipeline: at step s lane t works on row s-t and hands its last column
 // to lane t+1 with warp shuffles.  There is no block-level barrier anywhere in
 // the DP.  The forward match plane F_M (the only O(L1*L2) intermediate) goes to
-// a per-warp slot in HBM, the backward sweep overwrites it with F_M+B_M, and a
-// coalesced sweep of that slot produces the thresholded CSR rows.
+// a per-warp slot in HBM; the backward sweep reads it back row by row, never
+// stores B_M, and emits the few cells that can pass the threshold as a candidate
+// list, from which the CSR rows are built (pairhmm_post.cuh).
 #pragma once
 #include <cstdint>
 
@@ -38,8 +39,8 @@ struct PairHmmArgs {
   int npairs;
   float th;                  // keep p > th
   float xcut;                // cells with F+B-total <= xcut cannot exceed th
-  float* planes;             // per-warp-slot planes: F_M then B_M
-  int64_t plane_stride;      // floats per plane (a slot holds two)
+  float* planes;             // per-warp-slot: F_M plane, candidate keys, candidate sums
+  int64_t plane_stride;      // words per plane (a slot holds three)
   float4* bnd;               // per-warp-slot stripe-boundary columns (2 buffers)
   int64_t bnd_stride;        // float4 per buffer
   int* queue;                // work counter

@@ -22,8 +22,10 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
   const int SW = 32 * C;
   const int nstripes = (L2 + 1 + SW - 1) / SW;
   const int PW = nstripes * SW;
-  float* planeF = a.planes + (int64_t)slot * 2 * a.plane_stride;
-  float* planeB = planeF + a.plane_stride;
+  // slot = forward plane | candidate keys | candidate sums (plane_stride words each)
+  float* planeF = a.planes + (int64_t)slot * 3 * a.plane_stride;
+  uint32_t* ckey = reinterpret_cast<uint32_t*>(planeF + a.plane_stride);
+  float* csum = planeF + 2 * a.plane_stride;
   float4* bnd0 = a.bnd + (int64_t)slot * 2 * a.bnd_stride;
   float4* bnd1 = bnd0 + a.bnd_stride;
 
@@ -49,25 +51,7 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
     for (int k = 0; k < 3; ++k) fend[k] = __shfl_sync(0xffffffffu, fend[k], owner);
   }
 
-  // ---- backward -----------------------------------------------------------
-  float bcap[3] = {DAFS_LOG_ZERO, DAFS_LOG_ZERO, DAFS_LOG_ZERO};
-  for (int s = nstripes - 1; s >= 0; --s) {
-    StripeColsB<C> sc;
-    const int j0 = s * SW + lane * C;
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int cls = col_class(s2, L2, j0 + c + 1);
-      sc.mofs[c] = cls * 32 + lane;
-      sc.ins[c] = sm.ins[cls * 32 + lane];
-    }
-    backward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeB, PW,
-                       (s & 1) ? bnd0 : bnd1, (s & 1) ? bnd1 : bnd0, bcap);
-    __syncwarp();
-  }
-#pragma unroll
-  for (int k = 0; k < 3; ++k) bcap[k] = __shfl_sync(0xffffffffu, bcap[k], 0);
-
-  // ---- total probability: ProbabilisticModel.h:337-365 ----------------------
+  // ---- total probability, forward half: ProbabilisticModel.h:337-349 -----------
   float tf = DAFS_LOG_ZERO;
 #pragma unroll
   for (int k = 0; k < 3; ++k) tf = pairhmm_lse(sm.lut, tf, __fadd_rn(fend[k], c_tab.init[k]));
@@ -75,70 +59,106 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
   const float f11 = __fadd_rn(c_tab.init[0], c_tab.match[c11 * 8 + c21]);   // :123-131 seeds
   const float f10 = __fadd_rn(c_tab.init[1], c_tab.ins[c11]);
   const float f01 = __fadd_rn(c_tab.init[2], c_tab.ins[c21]);
-  float tb = __fadd_rn(f11, bcap[0]);
-  tb = pairhmm_lse(sm.lut, tb, __fadd_rn(f10, bcap[1]));
-  tb = pairhmm_lse(sm.lut, tb, __fadd_rn(f01, bcap[2]));
-  const float total = __fmul_rn(__fadd_rn(tf, tb), 0.5f);                  // (tf+tb)/2 exactly
+
+  // ---- backward + candidate cells ---------------------------------------------
+  // The posterior of a cell is EXP(F_M + B_M - total) with total = (tf + tb) / 2,
+  // and tb is only known when the backward sweep ends.  The sweep therefore keeps
+  // every cell with F_M + B_M > tf + xcut - kSlack; as long as |total - tf| <
+  // kSlack / 2 that is a superset of the cells the exact test below keeps.  If the
+  // two totals ever disagree by more, the sweep is repeated keeping every cell.
+  const float kSlack = 0.25f;
+  float lthr = __fsub_rn(__fadd_rn(tf, a.xcut), kSlack);
+  float total;
+  int run;
+  for (;;) {
+    float bcap[3] = {DAFS_LOG_ZERO, DAFS_LOG_ZERO, DAFS_LOG_ZERO};
+    run = 0;
+    for (int s = nstripes - 1; s >= 0; --s) {
+      StripeColsB<C> sc;
+      const int j0 = s * SW + lane * C;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int cls = col_class(s2, L2, j0 + c + 1);
+        sc.mofs[c] = cls * 32 + lane;
+        sc.ins[c] = sm.ins[cls * 32 + lane];
+      }
+      backward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeF, PW,
+                         (s & 1) ? bnd0 : bnd1, (s & 1) ? bnd1 : bnd0, bcap, lthr, ckey, csum, run);
+      __syncwarp();
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) bcap[k] = __shfl_sync(0xffffffffu, bcap[k], 0);
+    // backward half of the total: ProbabilisticModel.h:350-361
+    float tb = __fadd_rn(f11, bcap[0]);
+    tb = pairhmm_lse(sm.lut, tb, __fadd_rn(f10, bcap[1]));
+    tb = pairhmm_lse(sm.lut, tb, __fadd_rn(f01, bcap[2]));
+    total = __fmul_rn(__fadd_rn(tf, tb), 0.5f);                            // (tf+tb)/2 exactly
+    if (lthr == -INFINITY || fabsf(__fsub_rn(total, tf)) < 0.5f * kSlack) break;
+    lthr = -INFINITY;
+  }
   if (lane == 0) a.pair_total[pair] = total;
 
   // ---- posterior + sparsify: :393-398, wrapper.cpp:125-128, align.cpp:69-78 --
-  // One coalesced sweep over rows 1..L1 of both planes.  Kept entries are
-  // compacted, already in CSR order, into the part of the planes the sweep has
-  // consumed (entry k lands at index k < PW <= every index still to be read:
-  // row 0 is never read), columns over B_M and values over F_M.  Then the warp
-  // reserves its range of the output pool and copies the compact run there.
+  // Pass 1 applies the reference's test to every candidate (the posterior replaces
+  // the sum, a dropped candidate gets key ~0) and counts the survivors per row in
+  // the now dead forward plane; a scan turns the counts into row_ptr; pass 2 walks
+  // the list in order and places each survivor from the END of its row backwards,
+  // which turns the descending column order of the list into ascending CSR order.
   int32_t* row_ptr = a.row_ptr + a.row_off[pair];
+  int* cnt = reinterpret_cast<int*>(planeF);
   const unsigned lt_mask = (1u << lane) - 1u;
-  uint32_t* ccol = reinterpret_cast<uint32_t*>(planeB);
-  float* cval = planeF;
-  int run = 0;
-  if (lane == 0) row_ptr[0] = 0;
-  for (int i = 1; i <= L1; ++i) {
-    const float* frow = planeF + (int64_t)i * PW;
-    const float* brow = planeB + (int64_t)i * PW;
-    for (int jb = 1; jb <= L2; jb += 128) {
-      float f[4], bb[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int j = jb + 32 * u + lane;
-        const bool in = j <= L2;
-        f[u] = in ? frow[j] : DAFS_LOG_ZERO;
-        bb[u] = in ? brow[j] : DAFS_LOG_ZERO;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (jb + 32 * u > L2) break;                      // warp-uniform
-        const int j = jb + 32 * u + lane;
-        const float x = __fsub_rn(__fadd_rn(f[u], bb[u]), total);   // forward + backward - total
-        float p = 0.f;
-        bool keep = false;
-        if (j <= L2 && x > a.xcut) {
-          p = pairhmm_exp(fminf(x, 0.0f));
-          keep = (p >= a.th) && (p > a.th);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-          const int k = run + __popc(m & lt_mask);
-          ccol[k] = (uint32_t)(j - 1);
-          cval[k] = p;
-        }
-        run += __popc(m);
-      }
+  for (int i = lane; i <= L1; i += 32) __stcg(cnt + i, 0);
+  __syncwarp();
+  for (int k = lane; k < run; k += 32) {
+    const uint32_t key = ckey[k];
+    const float x = __fsub_rn(csum[k], total);                             // forward + backward - total
+    float p = 0.f;
+    bool keep = false;
+    if (x > a.xcut) {
+      p = pairhmm_exp(fminf(x, 0.0f));
+      keep = (p >= a.th) && (p > a.th);
     }
-    if (lane == 0) row_ptr[i] = run;
+    if (keep) { csum[k] = p; atomicAdd(cnt + (key >> 16), 1); }
+    else ckey[k] = 0xffffffffu;
+  }
+  __syncwarp();
+  int kept = 0;
+  if (lane == 0) row_ptr[0] = 0;
+  for (int i0 = 1; i0 <= L1; i0 += 32) {
+    const int i = i0 + lane;
+    int incl = i <= L1 ? __ldcg(cnt + i) : 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (i <= L1) { row_ptr[i] = kept + incl; __stcg(cnt + i, kept + incl); }   // cnt[i] <- end of row i
+    kept += __shfl_sync(0xffffffffu, incl, 31);
   }
   unsigned long long b = 0;
   if (lane == 0) {
-    b = atomicAdd(a.pool_count, (unsigned long long)run);
+    b = atomicAdd(a.pool_count, (unsigned long long)kept);
     a.pair_pool_off[pair] = (int64_t)b;
-    a.pair_nnz[pair] = run;
+    a.pair_nnz[pair] = kept;
   }
   const int64_t base = (int64_t)__shfl_sync(0xffffffffu, b, 0);
   __syncwarp();
-  if (base + run <= a.pool_cap) {
-    for (int k = lane; k < run; k += 32) {
-      a.pool_col[base + k] = ccol[k];
-      a.pool_val[base + k] = cval[k];
+  if (base + kept <= a.pool_cap) {
+    for (int k0 = 0; k0 < run; k0 += 32) {
+      const int k = k0 + lane;
+      const uint32_t key = k < run ? ckey[k] : 0xffffffffu;
+      const bool keep = key != 0xffffffffu;
+      const int row = (int)(key >> 16);
+      const unsigned same = __match_any_sync(0xffffffffu, keep ? row : 0x10000 + lane);
+      const int end = keep ? __ldcg(cnt + row) : 0;
+      __syncwarp();                                                             // every read before any update
+      if (keep) {
+        const int pos = end - 1 - __popc(same & lt_mask);
+        a.pool_col[base + pos] = (key & 0xffffu) - 1u;
+        a.pool_val[base + pos] = csum[k];
+        if ((same >> lane) == 1u) __stcg(cnt + row, end - __popc(same));        // highest lane of the group
+      }
+      __syncwarp();
     }
   }
 }

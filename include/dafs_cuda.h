@@ -40,6 +40,11 @@ int dafs_cuda_init(int ngpu /* 0 = all visible */);
 void dafs_cuda_shutdown(void);
 const char* dafs_cuda_last_error(void);
 int dafs_cuda_device_count(void);
+/* Measured FP32 issue rate of the current device, the denominator of the pair-HMM
+ * roofline (MEASURED_PEAKS.json has no FP32 entry): dependent-chain
+ * FFMA (2 flop each) and FMUL+FADD (the unfused arithmetic bit-exact parity
+ * allows).  TFLOP/s, best of 3 after a warm-up launch.                          */
+int dafs_cuda_fp32_probe(double* fma_tflops, double* muladd_tflops);
 
 /* ---- sparse results ------------------------------------------------------
  * A batch of row-sparse matrices, one per unit (a sequence pair for (1), a
