@@ -8,7 +8,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def library_path():
-    return os.path.join(_HERE, "libdafs_cuda.so")
+    """In-tree libdafs_cuda.so; DAFS_CUDA_LIB points at another build (tuning experiments)."""
+    return os.environ.get("DAFS_CUDA_LIB") or os.path.join(_HERE, "libdafs_cuda.so")
 
 
 class DafsCudaError(RuntimeError):

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <numeric>
 #include <thread>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -128,7 +129,10 @@ struct dafs_pairhmm_plan {
 namespace dafs {
 
 static const int kWarps = 4;     // warps per CTA
-static const int kMinBlocks = 4; // CTAs per SM the kernel is compiled for (<=128 regs)
+#ifndef DAFS_PAIRHMM_MINB
+#define DAFS_PAIRHMM_MINB 4
+#endif
+static const int kMinBlocks = DAFS_PAIRHMM_MINB; // CTAs per SM the kernel is compiled for (4 -> <=128 regs)
 
 static void free_plan_buffers(dafs_pairhmm_plan* p) {
   cudaFree(p->d_seq); cudaFree(p->d_seq_off); cudaFree(p->d_seq_len); cudaFree(p->d_pairs);
@@ -156,15 +160,23 @@ static int alloc_pool(dafs_pairhmm_plan* p, int64_t cap) {
   return DAFS_CUDA_OK;
 }
 
-// Columns per lane: minimise the padded DP width over the instantiated widths,
-// larger C (fewer stripes) on ties.
+// Columns per lane: minimise (padded DP width) x (measured cost per padded cell of
+// that instantiation).  The relative costs are from the C4 sweep on B200
+// (tools/sweep_pairhmm.sh, profiles/r01_pairhmm_cols_sweep.txt): wide lanes
+// amortise the per-step shuffles, narrow ones keep the unrolled row body inside
+// the instruction cache.
 static const int kColsPerLane[] = {2, 3, 4, 5, 6, 8, 10, 12};
+static const float kColsCost[] = {1.30f, 1.14f, 1.00f, 1.00f, 0.94f, 0.92f, 1.01f, 1.08f};
 static int choose_cols(int max_l2) {
-  int best = 12; int64_t best_w = INT64_MAX;
-  for (int c : kColsPerLane) {
-    const int sw = 32 * c;
-    const int64_t w = (int64_t)((max_l2 + 1 + sw - 1) / sw) * sw;
-    if (w <= best_w) { best_w = w; best = c; }
+  if (const char* e = getenv("DAFS_PAIRHMM_COLS")) {          // tuning knob
+    const int want = atoi(e);
+    for (int c : kColsPerLane) if (c == want) return c;
+  }
+  int best = 5; double best_w = 1e300;
+  for (size_t k = 0; k < sizeof(kColsPerLane) / sizeof(int); ++k) {
+    const int sw = 32 * kColsPerLane[k];
+    const double w = (double)((max_l2 + 1 + sw - 1) / sw) * sw * kColsCost[k];
+    if (w < best_w) { best_w = w; best = kColsPerLane[k]; }
   }
   return best;
 }

@@ -61,7 +61,7 @@ __constant__ PairHmmTables c_tab;
 // Per-block shared tables, replicated once per lane (index*32 + lane) so that a
 // warp whose lanes look up different symbols never has a bank conflict.
 struct PairHmmSmem {
-  float4 lut[4];            // LOOKUP coefficient rows {c3,c2,c1,c0}
+  float4 lut[DAFS_LOOKUP_SLOTS];   // LOOKUP coefficient rows {c3,c2,c1,c0} by ceil(2 d)
   float match[64 * 32];
   float ins[8 * 32];
 };

@@ -12,19 +12,27 @@ namespace dafs {
 #define DAFS_LOG_ZERO (-2e20f)
 
 // LOOKUP(d) = log(1 + e^-d)-ish on [0, 7.5): four cubic pieces, Horner form,
-// float literals (ScoreType.h:187-198).  The four coefficient rows live in
-// shared memory as float4 {c3,c2,c1,c0}; a lane picks its row with three
-// compares and fetches it with one LDS.128 (rows sit in disjoint banks, equal
-// rows broadcast: conflict-free) instead of twelve register selects.
+// float literals (ScoreType.h:187-198).  The piece boundaries 1.0 / 2.5 / 4.5 are
+// multiples of one half and the reference's tests are strict (d > 1.0f ...), so
+// the piece is a function of n = ceil(2 d): 0..2 -> piece 0, 3..5 -> 1, 6..9 -> 2,
+// 10.. -> 3.  n comes out of ONE instruction: fma(d, 2, 1.5 * 2^23) rounded
+// towards +inf leaves ceil(2 d) in the low mantissa bits (2 d is exact, the sum is
+// rounded once).  The coefficient rows {c3,c2,c1,c0} live in shared memory as a
+// 17-entry float4 table indexed by n, fetched with one LDS.128 -- this replaces
+// three compares and three selects per LOOKUP and moves the work from the ALU
+// pipe to the FMA pipe.  d is clamped to 8 first (n <= 16); for d >= 7.5 the
+// caller discards the value anyway.
 #define DAFS_LOOKUP_ROWS                                                                   \
   {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f},      \
   {-0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f},      \
   {-0.004605031767994f, 0.063427417320019f, 0.695956496475118f, 0.514272634594009f},      \
   {-0.000458661602210f, 0.009695946122598f, 0.930734667215156f, 0.168037164329057f}
+#define DAFS_LOOKUP_SLOTS 17
+__host__ __device__ __forceinline__ int pairhmm_lookup_piece(int n) { return n >= 10 ? 3 : n >= 6 ? 2 : n >= 3 ? 1 : 0; }
 
 __device__ __forceinline__ float pairhmm_lookup(const float4* __restrict__ tab, float d) {
-  const int row = (d > 4.50f) ? 3 : (d > 2.50f) ? 2 : (d > 1.00f) ? 1 : 0;
-  const float4 k = tab[row];
+  const float t = __fmaf_ru(fminf(d, 8.0f), 2.0f, 12582912.0f);
+  const float4 k = tab[__float_as_int(t) - 0x4b400000];
   float r = __fadd_rn(__fmul_rn(k.x, d), k.y);
   r = __fadd_rn(__fmul_rn(r, d), k.z);
   r = __fadd_rn(__fmul_rn(r, d), k.w);

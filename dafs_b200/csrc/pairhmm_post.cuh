@@ -166,9 +166,9 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
 template <int C, int WARPS, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) pairhmm_kernel(const PairHmmArgs a) {
   __shared__ PairHmmSmem sm;
-  if (threadIdx.x < 4) {
+  if (threadIdx.x < DAFS_LOOKUP_SLOTS) {
     const float4 rows[4] = {DAFS_LOOKUP_ROWS};
-    sm.lut[threadIdx.x] = rows[threadIdx.x];
+    sm.lut[threadIdx.x] = rows[pairhmm_lookup_piece(threadIdx.x)];
   }
   for (int k = threadIdx.x; k < 64 * 32; k += blockDim.x) sm.match[k] = c_tab.match[k >> 5];
   for (int k = threadIdx.x; k < 8 * 32; k += blockDim.x) sm.ins[k] = c_tab.ins[k >> 5];
