@@ -204,14 +204,14 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   cudaDeviceProp prop;
   PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  p->smem = (int)(tab_bytes + 2 * sizeof(double) * (p->W + 2) + p->W + 16);
+  p->smem = (int)(tab_bytes + sizeof(double) * MC_CGEN_ROWS * 32 + 2 * sizeof(double) * (p->W + 2) + p->W + 16);
   if ((size_t)p->smem > prop.sharedMemPerBlockOptin)
     return bail(fail(DAFS_CUDA_ENOTSUP, "sequence of %d nt needs %d bytes of shared memory", maxn, p->smem));
   PLAN_TRY(cudaFuncSetAttribute(mccaskill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   int blocks = 0;
   PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, mccaskill_kernel, MC_THREADS, p->smem));
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "mccaskill_kernel does not fit on an SM"));
-  p->ws_stride = (size_t)10 * p->W * p->W;
+  p->ws_stride = (size_t)MC_NARRAYS * p->W * p->W;
   size_t free_b = 0, total_b = 0;
   PLAN_TRY(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cta = p->ws_stride * sizeof(double);

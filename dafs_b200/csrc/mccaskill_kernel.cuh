@@ -54,17 +54,61 @@ __device__ __forceinline__ double mc_warp_sum(double v) {
 }
 
 struct McWs {
-  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT;
+  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT, *G, *H;
 };
+#define MC_NARRAYS 12
+
+// Interior loops.  A loop with u1, u2 unpaired bases is "generic" when ViennaRNA's
+// exp_E_IntLoop takes its last branch, internal[u1+u2] * mismatchI(outer) *
+// mismatchI(inner) * ninio[|u1-u2|]: every (u1,u2) with min >= 1 except 1x1, 1x2,
+// 2x1, 2x2.  For those the weight factorises into a part of the outer pair, a part
+// of the inner pair and a part of (u1,u2) alone, so with
+//   G(k,l) = qb(k,l) * mismatchI[rtype(k,l)][S[l+1]][S[k-1]]      (inside)
+//   H(p,q) = O(p,q)  * mismatchI[type(p,q)][S[p+1]][S[q-1]]       (outside)
+//   cgen[u1][u2] = internal[u1+u2] * ninio[|u1-u2|] * scale[u1+u2+2]   (0 for the rest)
+// the generic part of a cell is one masked dot product of a 30x30 triangle of G
+// (or H) with cgen, and only the 65 special loops (stack, bulges, 1x1, 1x2, 2x1,
+// 2x2) are evaluated through mc_interior.
+#define MC_CGEN_ROWS 37      // u1 = 0..36 (rows past 30 are zero: the u1 loop is unrolled by six)
+
+// sum over u1 >= 1, 1 <= u2 = lane of A[u1*row_step + u2*col_step] * cgen[u1][u2]
+// subject to u1 <= u1max, u2 <= u2max, u1 + u2 <= usum (<= MC_MAXLOOP).  Lane-partial.
+__device__ __forceinline__ double mc_generic_sum(const double* __restrict__ A, ptrdiff_t row_step, int col_step,
+                                                 const double* __restrict__ cgen, int u1max, int u2max, int usum,
+                                                 int lane) {
+  double s = 0.0;
+  const int u2 = lane;
+  const bool lane_ok = u2 >= 1 && u2 <= u2max;
+  const double* a = A + (ptrdiff_t)u2 * col_step;
+  const int top = min(u1max, usum - 1);
+  for (int u0 = 1; u0 <= top; u0 += 6) {
+    double v[6];
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+      const int u1 = u0 + t;
+      v[t] = (lane_ok && u1 <= u1max && u1 + u2 <= usum) ? a[(ptrdiff_t)u1 * row_step] : 0.0;
+    }
+#pragma unroll
+    for (int t = 0; t < 6; ++t) s += v[t] * cgen[(u0 + t) * 32 + u2];
+  }
+  return s;
+}
 
 // Inside recursion over all spans for the current scale.  Returns nothing; q(1,n) is in ws.q.
 __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                          const double* mlb, const McWs& w, int warp, int lane) {
+                          const double* mlb, const double* cgen, int* next_cell, const McWs& w, int warp, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
   for (int i = 1 + threadIdx.x; i <= n + 1; i += MC_THREADS) w.q[IX(i, i - 1)] = 1.0;
+  if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
   __syncthreads();
   for (int d = 0; d < n; ++d) {
-    for (int i = 1 + warp; i + d <= n; i += MC_WARPS) {
+    // cells of the diagonal are handed out dynamically: a cell whose ends can pair
+    // costs several times one whose ends cannot
+    for (;;) {
+      int i = 0;
+      if (lane == 0) i = 1 + atomicAdd(&next_cell[d & 1], 1);
+      i = __shfl_sync(0xffffffffu, i, 0);
+      if (i + d > n) break;
       const int j = i + d;
       const int si = S[i], sj = S[j];
       const int type = mc_pair(si, sj);
@@ -77,26 +121,28 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
           if (u == 4) { for (int c = 0; c < 6; ++c) s6 = s6 * 5 + S[i + c]; }
           vb = mc_hairpin(T, u, type, S[i + 1], S[j - 1], s6) * scale[u + 2];
         }
-        // interior loops (k,l): lanes over l, k in batches of 8 so that eight qb
-        // loads are in flight per lane (qb(k,l) == 0 for pairs that cannot form)
-        const int kmax = min(i + MC_MAXLOOP + 1, j - MC_TURN - 2);
         const int si1 = S[i + 1], sj1 = S[j - 1];
-        for (int k0 = i + 1; k0 <= kmax; k0 += 8) {
-          double qv[8];
+        const int usum = min(MC_MAXLOOP, d - MC_TURN - 3);       // u1 + u2 <= usum keeps l - k > TURN
+        if (usum >= 0) {
+          // generic loops
+          if (usum >= 2)
+            vb += (double)T.mmI[type - 1][si1][sj1] *
+                  mc_generic_sum(w.G + IX(i + 1, j - 1), (ptrdiff_t)W, -1, cgen, MC_MAXLOOP, MC_MAXLOOP, usum, lane);
+          // special loops: round 0 = stack and right bulges (u1 = 0, u2 = lane), round 1 = left
+          // bulges (u1 = lane, u2 = 0), round 2 = 1x1, 1x2, 2x1, 2x2 on lanes 0..3
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int k = k0 + u;
-            const int l = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + (k - i - 1)) + lane;
-            qv[u] = (k <= kmax && l < j) ? w.qb[IX(k, l)] : 0.0;
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            if (qv[u] != 0.0) {
-              const int k = k0 + u, u1 = k - i - 1;
-              const int l = max(k + MC_TURN + 1, j - 1 - MC_MAXLOOP + u1) + lane;
-              const int t2 = mc_pair(S[k], S[l]);
-              vb += qv[u] * mc_interior(T, u1, j - l - 1, type, mc_rtype(t2), si1, sj1, S[k - 1], S[l + 1]) *
-                    scale[u1 + j - l + 1];
+          for (int round = 0; round < 3; ++round) {
+            int u1, u2;
+            bool ok;
+            if (round == 0) { u1 = 0; u2 = lane; ok = lane <= usum; }
+            else if (round == 1) { u1 = lane; u2 = 0; ok = lane >= 1 && lane <= usum; }
+            else { u1 = 1 + (lane >> 1); u2 = 1 + (lane & 1); ok = lane < 4 && u1 + u2 <= usum; }
+            if (ok) {
+              const int k = i + 1 + u1, l = j - 1 - u2;
+              const double v = w.qb[IX(k, l)];
+              if (v != 0.0)
+                vb += v * mc_interior(T, u1, u2, type, mc_rtype(mc_pair(S[k], S[l])), si1, sj1, S[k - 1], S[l + 1]) *
+                      scale[u1 + u2 + 2];
             }
           }
         }
@@ -118,6 +164,7 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
       if (lane == 0) {
         if (closes) vb += sml * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
         w.qb[IX(i, j)] = vb;
+        w.G[IX(i, j)] = (vb != 0.0) ? vb * (double)T.mmI[mc_rtype(type) - 1][S[j + 1]][S[i - 1]] : 0.0;
         const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
         double m1 = (d > 0 ? w.qm1T[IX(j - 1, i)] : 0.0) * mlb[1];
         double e1 = (d > 0 ? w.qqT[IX(j - 1, i)] : 0.0) * scale[1];
@@ -130,6 +177,7 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
         w.q[IX(i, j)] = scale[d + 1] + e1 + sq;
       }
     }
+    if (threadIdx.x == 0) next_cell[(d + 1) & 1] = 0;
     __syncthreads();
   }
 #undef IX
@@ -137,16 +185,21 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
 
 // Outside recursion; needs the inside arrays of the same scale.
 __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                           const double* mlb, const McWs& w, int warp, int lane) {
+                           const double* mlb, const double* cgen, int* next_cell, const McWs& w, int warp, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
-  // O, OM, prmlT, prm_lT start at zero: entries that are never written (pairs
+  // O, H, OM, prmlT, prm_lT start at zero: entries that are never written (pairs
   // that cannot form, q > n) are read as 0.
   for (size_t c = threadIdx.x; c < (size_t)(n + 2) * W; c += MC_THREADS) {
-    w.O[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0;
+    w.O[c] = 0.0; w.H[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0;
   }
+  if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
   __syncthreads();
   for (int d = n - 1; d > MC_TURN; --d) {
-    for (int i = 1 + warp; i + d <= n; i += MC_WARPS) {
+    for (;;) {
+      int i = 0;
+      if (lane == 0) i = 1 + atomicAdd(&next_cell[d & 1], 1);
+      i = __shfl_sync(0xffffffffu, i, 0);
+      if (i + d > n) break;
       const int j = i + d;
       // (a) prm_l(i,j), prml(i,j): OM of spans >= d+1 only
       if (j + 1 <= n) {
@@ -169,24 +222,26 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       const int t2 = mc_rtype(type);
       double o = 0.0;
       if (lane == 0) o = w.q[IX(1, i - 1)] * w.q[IX(j + 1, n)] * mc_stem(T, type, si1, sj1, false);
-      const int pmin = max(1, i - MC_MAXLOOP - 1);
-      {
+      if (i > 1 && j < n) {
+        // (p,q) = (i-1-u1, j+1+u2) encloses (i,j)
         const int sp1 = S[i - 1], sq1 = S[j + 1];
-        const int qx = j + 1 + lane;
-        for (int p0 = i - 1; p0 >= pmin; p0 -= 8) {
-          double ov[8];
+        const int u1max = min(MC_MAXLOOP, i - 2), u2max = min(MC_MAXLOOP, n - j - 1);
+        if (u1max >= 1 && u2max >= 1)
+          o += (double)T.mmI[t2 - 1][sq1][sp1] *
+               mc_generic_sum(w.H + IX(i - 1, j + 1), -(ptrdiff_t)W, 1, cgen, u1max, u2max, MC_MAXLOOP, lane);
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int p = p0 - u;
-            ov[u] = (p >= pmin && qx <= n && qx - j - 1 + (i - p - 1) <= MC_MAXLOOP) ? w.O[IX(p, qx)] : 0.0;
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            if (ov[u] != 0.0) {
-              const int p = p0 - u, u1 = i - p - 1;
-              const int tp = mc_pair(S[p], S[qx]);
-              o += ov[u] * mc_interior(T, u1, qx - j - 1, tp, t2, S[p + 1], S[qx - 1], sp1, sq1) * scale[u1 + qx - j + 1];
-            }
+        for (int round = 0; round < 3; ++round) {
+          int u1, u2;
+          bool ok;
+          if (round == 0) { u1 = 0; u2 = lane; ok = lane <= MC_MAXLOOP; }
+          else if (round == 1) { u1 = lane; u2 = 0; ok = lane >= 1 && lane <= MC_MAXLOOP; }
+          else { u1 = 1 + (lane >> 1); u2 = 1 + (lane & 1); ok = lane < 4; }
+          if (ok && u1 <= u1max && u2 <= u2max) {
+            const int p = i - 1 - u1, qx = j + 1 + u2;
+            const double v = w.O[IX(p, qx)];
+            if (v != 0.0)
+              o += v * mc_interior(T, u1, u2, mc_pair(S[p], S[qx]), t2, S[p + 1], S[qx - 1], sp1, sq1) *
+                   scale[u1 + u2 + 2];
           }
         }
       }
@@ -202,9 +257,11 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       if (lane == 0) {
         o += t * mc_stem(T, type, si1, sj1, true);
         w.O[IX(i, j)] = o;
+        w.H[IX(i, j)] = o * (double)T.mmI[type - 1][S[i + 1]][S[j - 1]];
         w.OM[IX(i, j)] = o * ((double)T.ml_closing * mc_stem(T, t2, S[j - 1], S[i + 1], true)) * scale[2];
       }
     }
+    if (threadIdx.x == 0) next_cell[(d - 1) & 1] = 0;
     __syncthreads();
   }
 #undef IX
@@ -214,14 +271,16 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
 
 namespace dafs {
 
-// Dynamic shared memory: McTables | scale[W+1] | mlb[W+1] | codes[W+8]
+// Dynamic shared memory: McTables | cgen[37][32] | scale[W+2] | mlb[W+2] | codes[W+8]
 __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   extern __shared__ __align__(16) char smem[];
   __shared__ int s_q;
   __shared__ int s_total;
+  __shared__ int s_next[2];
   McTables& T = *reinterpret_cast<McTables*>(smem);
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  double* scale = reinterpret_cast<double*>(smem + tab_bytes);
+  double* cgen = reinterpret_cast<double*>(smem + tab_bytes);
+  double* scale = cgen + MC_CGEN_ROWS * 32;
   double* mlb = scale + (a.W + 2);
   uint8_t* S = reinterpret_cast<uint8_t*>(mlb + (a.W + 2));
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -237,6 +296,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     const size_t A = (size_t)W * W;
     w.q = base; w.qb = base + A; w.qm = base + 2 * A; w.qmT = base + 3 * A; w.qm1T = base + 4 * A;
     w.qqT = base + 5 * A; w.O = base + 6 * A; w.OM = base + 7 * A; w.prmlT = base + 8 * A; w.prm_lT = base + 9 * A;
+    w.G = base + 10 * A; w.H = base + 11 * A;
   }
 #define IX(i, j) ((size_t)(i) * W + (j))
   for (;;) {
@@ -257,8 +317,13 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     for (int attempt = 0; attempt < 8; ++attempt) {
       __syncthreads();
       for (int k = tid; k <= n + 2; k += MC_THREADS) { scale[k] = exp(-(double)k * lns); mlb[k] = exp((double)k * (ln_mlbase - lns)); }
+      for (int k = tid; k < MC_CGEN_ROWS * 32; k += MC_THREADS) {
+        const int u1 = k >> 5, u2 = k & 31, ul = max(u1, u2), us = min(u1, u2);
+        const bool generic = us >= 1 && u1 + u2 <= MC_MAXLOOP && !(us == 1 && ul <= 2) && !(us == 2 && ul == 2);
+        cgen[k] = generic ? (double)T.internal[u1 + u2] * (double)T.ninio[ul - us] * exp(-(double)(u1 + u2 + 2) * lns) : 0.0;
+      }
       __syncthreads();
-      mc_inside(T, S, n, W, scale, mlb, w, warp, lane);
+      mc_inside(T, S, n, W, scale, mlb, cgen, s_next, w, warp, lane);
       Z = w.q[IX(1, n)];
       if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
       if (!(Z > 0.0)) { lns -= 0.25; continue; }
@@ -266,7 +331,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
       if (fabs(log(Z)) <= 150.0) break;
       lns = lnZ / (double)n;                            // rerun with the ensemble's own scale
     }
-    mc_outside(T, S, n, W, scale, mlb, w, warp, lane);
+    mc_outside(T, S, n, W, scale, mlb, cgen, s_next, w, warp, lane);
     // ---- read-out: p = float(qb*O/Z) > th, rows ascending, columns ascending ----
     int32_t* row_ptr = a.row_ptr + a.row_off[s];
     const float th = a.th;
