@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstring>
 #include <thread>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -121,14 +122,13 @@ struct dafs_mccaskill_plan {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int nseq = 0, W = 0, grid = 0, smem = 0;
+  int nseq = 0, W = 0, grid = 0, smem = 0, cluster = 1;
   float th = 0;
   int64_t total_rows = 0, pool_cap = 0;
   std::vector<int64_t> row_off;
   uint8_t* d_seq = nullptr; int64_t* d_seq_off = nullptr; int32_t* d_seq_len = nullptr; int32_t* d_order = nullptr;
   dafs::McTables* d_tab = nullptr;
   double* d_ws = nullptr; size_t ws_stride = 0;
-  int* d_queue = nullptr;
   int64_t* d_row_off = nullptr; int32_t* d_row_ptr = nullptr;
   int64_t* d_pool_off = nullptr; uint32_t* d_pool_col = nullptr; float* d_pool_val = nullptr;
   int32_t* d_seq_nnz = nullptr; double* d_seq_lnz = nullptr;
@@ -141,7 +141,7 @@ struct dafs_mccaskill_plan {
 namespace dafs {
 static void free_mc_plan(dafs_mccaskill_plan* p) {
   cudaFree(p->d_seq); cudaFree(p->d_seq_off); cudaFree(p->d_seq_len); cudaFree(p->d_order); cudaFree(p->d_tab);
-  cudaFree(p->d_ws); cudaFree(p->d_queue); cudaFree(p->d_row_off); cudaFree(p->d_row_ptr); cudaFree(p->d_pool_off);
+  cudaFree(p->d_ws); cudaFree(p->d_row_off); cudaFree(p->d_row_ptr); cudaFree(p->d_pool_off);
   cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_seq_nnz); cudaFree(p->d_seq_lnz);
   cudaFree(p->d_nz_off); cudaFree(p->d_col); cudaFree(p->d_val);
   if (p->ev0) cudaEventDestroy(p->ev0);
@@ -179,7 +179,6 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
   PLAN_TRY(cudaEventCreate(&p->ev0));
   PLAN_TRY(cudaEventCreate(&p->ev1));
-  PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
   if (nseq == 0) { *out = p; return DAFS_CUDA_OK; }
 
   std::vector<int64_t> seq_off(nseq + 1, 0), pool_off(nseq + 1, 0);
@@ -216,14 +215,23 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   PLAN_TRY(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cta = p->ws_stride * sizeof(double);
   const int by_mem = (int)std::max<size_t>(1, (free_b * 6 / 10) / per_cta);
-  p->grid = std::max(1, std::min(std::min(nseq, prop.multiProcessorCount * blocks), by_mem));
+  // CTAs per sequence: a lone CTA when there is at least one sequence per SM slot,
+  // otherwise the largest portable cluster (2, 4, 8) that still gives every
+  // sequence a team; DAFS_MCCASKILL_CLUSTER overrides (tuning knob).
+  const int slots = prop.multiProcessorCount * blocks;
+  int nc = 1;
+  while (nc < 8 && (int64_t)nseq * nc * 2 <= slots) nc *= 2;
+  if (const char* e = getenv("DAFS_MCCASKILL_CLUSTER")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) nc = v; }
+  p->cluster = nc;
+  const int teams = std::max(1, std::min(std::min(nseq, slots / nc), by_mem));
+  p->grid = teams * nc;
 
   PLAN_TRY(cudaMalloc(&p->d_seq, enc.size()));
   PLAN_TRY(cudaMalloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
   PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * nseq));
   PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * nseq));
   PLAN_TRY(cudaMalloc(&p->d_tab, sizeof(McTables)));
-  PLAN_TRY(cudaMalloc(&p->d_ws, per_cta * p->grid));
+  PLAN_TRY(cudaMalloc(&p->d_ws, per_cta * (p->grid / p->cluster)));
   PLAN_TRY(cudaMalloc(&p->d_row_off, sizeof(int64_t) * (nseq + 1)));
   PLAN_TRY(cudaMalloc(&p->d_row_ptr, sizeof(int32_t) * p->total_rows));
   PLAN_TRY(cudaMalloc(&p->d_pool_off, sizeof(int64_t) * (nseq + 1)));
@@ -255,14 +263,21 @@ extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   if (p->nseq == 0) { p->nnz = 0; return DAFS_CUDA_OK; }
   McArgs a;
   a.seq = p->d_seq; a.seq_off = p->d_seq_off; a.seq_len = p->d_seq_len; a.order = p->d_order; a.nseq = p->nseq;
-  a.W = p->W; a.th = p->th; a.tab = p->d_tab; a.ws = p->d_ws; a.ws_stride = p->ws_stride; a.queue = p->d_queue;
+  a.W = p->W; a.th = p->th; a.tab = p->d_tab; a.ws = p->d_ws; a.ws_stride = p->ws_stride; a.cluster = p->cluster;
   a.row_off = p->d_row_off; a.row_ptr = p->d_row_ptr; a.pool_off = p->d_pool_off; a.pool_col = p->d_pool_col;
   a.pool_val = p->d_pool_val; a.seq_nnz = p->d_seq_nnz; a.seq_lnz = p->d_seq_lnz;
-  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
   DAFS_CUDA_TRY(cudaFuncSetAttribute(mccaskill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-  mccaskill_kernel<<<p->grid, MC_THREADS, p->smem, p->stream>>>(a);
-  DAFS_CUDA_TRY(cudaGetLastError());
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p->grid); cfg.blockDim = dim3(MC_THREADS);
+    cfg.dynamicSmemBytes = p->smem; cfg.stream = p->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = p->cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    DAFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, mccaskill_kernel, a));
+  }
   mc_scan_kernel<<<1, 32, 0, p->stream>>>(p->d_seq_nnz, p->nseq, p->d_nz_off);
   DAFS_CUDA_TRY(cudaGetLastError());
   mc_gather_kernel<<<std::min(p->nseq, 1024), 256, 0, p->stream>>>(p->nseq, p->d_pool_off, p->d_seq_nnz, p->d_nz_off,
@@ -326,7 +341,7 @@ extern "C" int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* p, dafs_csr_b
 extern "C" int dafs_cuda_mccaskill_plan_info(dafs_mccaskill_plan* p, dafs_mccaskill_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   info->grid = p->grid; info->block = MC_THREADS; info->smem_bytes = p->smem; info->row_stride = p->W;
-  info->workspace_bytes = (int64_t)(p->ws_stride * sizeof(double)) * p->grid;
+  info->workspace_bytes = (int64_t)(p->ws_stride * sizeof(double)) * (p->grid / p->cluster);
   info->table_bytes = (int)sizeof(dafs::McTables);
   info->last_ms = p->last_ms;
   return DAFS_CUDA_OK;

@@ -1,23 +1,30 @@
 // K3/K4: McCaskill inside / outside base-pairing probabilities in scaled FP64,
-// one CTA per sequence (persistent grid, atomic queue), span-length diagonals
-// separated by one block barrier each.  Replaces what RNAfold::calculate
+// one CTA -- or one thread-block cluster when there are fewer sequences than SMs --
+// per sequence (persistent grid), span-length diagonals separated by one block /
+// cluster barrier each.  Replaces what RNAfold::calculate
 // (src/fold.cpp:78-116) gets from ViennaRNA's pf_fold + export_bppm, including
 // its read-out: float(p) > th kept, rows i < j, ascending j (:108-114).
 //
 // Quantities (1-based, W = n_max + 2 row stride):
 //   qb(i,j)  = hairpin + sum interior + MLclose(i,j) * sum_k qm(i+1,k-1) * qm1(k,j-1)
 //   qm1(i,j) = qm1(i,j-1)*mlb + qb(i,j)*MLstem(i,j)           (ViennaRNA's rolling qqm)
-//   qm(i,j)  = sum_{k=i..j} (mlb^(k-i) + qm(i,k-1)) * qm1(k,j)
+//   qm(i,j)  = sum_{k=i..j} (mlb^(k-i) + qm(i,k-1)) * qm1(k,j)  =  A(i,j) + R(i,j)  with
+//              A(i,j) = sum_{k=i+1..j} qm(i,k-1)*qm1(k,j)   and   R(i,j) = qm1(i,j) + mlb*R(i+1,j);
+//              the multiloop closing sum of qb(i,j) is then just A(i+1,j-1)
 //   qq(i,j)  = qq(i,j-1)*sc + qb(i,j)*Ext(i,j)                (ViennaRNA's rolling qq)
 //   q(i,j)   = sc^(j-i+1) + qq(i,j) + sum_{k=i..j-1} q(i,k) * qq(k+1,j)
 //   O(i,j)   = q(1,i-1)*q(j+1,n)*Ext(i,j) + sum_{interior (p,q)} O(p,q)*wI*sc^(..)
 //            + MLstem(i,j) * sum_{p<i} [ prm_l(p,j)*qm(p+1,i-1) + prml(p,j)*(mlb^(i-p-1) + qm(p+1,i-1)) ]
+//            = ... MLstem(i,j) * [ sum_{p<i-1} PL(p,j)*qm(p+1,i-1) + tB(i,j) ],  PL = prm_l + prml,
+//              tB(i,j) = prml(i-1,j) + mlb*tB(i-1,j)
 //   prm_l(p,j) = prm_l(p,j+1)*mlb + OM(p,j+1),  prml(p,j) = sum_{q>j+1} OM(p,q)*qm(j+1,q-1),
 //   OM = O*MLclose*sc^2,   P(i,j) = qb*O / q(1,n).
 // Every O(span) inner sum runs over one index with a warp striding it; arrays
 // that are read along their first index are kept transposed (qm1T, qqT, qmT,
 // prmlT, prm_lT) so that all of those reads are coalesced.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "mccaskill_model.cuh"
 
 namespace dafs {
@@ -28,12 +35,12 @@ struct McArgs {
   const int32_t* seq_len;      // [nseq]
   const int32_t* order;        // queue position -> sequence (longest first)
   int nseq;
+  int cluster;                 // CTAs per sequence (= the launch's cluster size)
   int W;                       // row stride of the DP arrays = max n + 2
   float th;
   const McTables* tab;         // in HBM; staged to shared memory by every CTA
-  double* ws;                  // per-CTA workspace: 10 arrays of W*W doubles
-  size_t ws_stride;            // doubles per CTA
-  int* queue;
+  double* ws;                  // per-team workspace: MC_NARRAYS arrays of W*W doubles
+  size_t ws_stride;            // doubles per team
   // outputs
   const int64_t* row_off;      // [nseq+1] start of each sequence's row_ptr block (n+1 entries)
   int32_t* row_ptr;
@@ -44,7 +51,9 @@ struct McArgs {
   double* seq_lnz;             // [nseq] ln Z (diagnostic, = -G_ensemble/kT)
 };
 
-#define MC_THREADS 512
+#ifndef MC_THREADS
+#define MC_THREADS 768      // 80 registers per thread: one CTA of 24 warps per SM
+#endif
 #define MC_WARPS (MC_THREADS / 32)
 
 __device__ __forceinline__ double mc_warp_sum(double v) {
@@ -53,10 +62,24 @@ __device__ __forceinline__ double mc_warp_sum(double v) {
   return v;
 }
 
-struct McWs {
-  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT, *G, *H;
+// The CTAs of one thread-block cluster share a sequence: cell c of a diagonal
+// belongs to CTA c % nc, the per-diagonal barrier is the cluster barrier (release /
+// acquire at cluster scope, so the global-memory DP arrays written by one CTA are
+// visible to the others), a lone CTA uses the block barrier.
+struct McTeam {
+  int rank, nc;
 };
-#define MC_NARRAYS 12
+__device__ __forceinline__ void mc_sync(const McTeam& tm) {
+  if (tm.nc == 1) __syncthreads();
+  else cooperative_groups::this_cluster().sync();
+}
+
+struct McWs {
+  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT;
+  double *G, *A, *R;       // inside only
+  double *H, *PLT, *tB;    // outside only: they reuse the storage of G, A, R
+};
+#define MC_NARRAYS 13
 
 // Interior loops.  A loop with u1, u2 unpaired bases is "generic" when ViennaRNA's
 // exp_E_IntLoop takes its last branch, internal[u1+u2] * mismatchI(outer) *
@@ -69,7 +92,8 @@ struct McWs {
 // the generic part of a cell is one masked dot product of a 30x30 triangle of G
 // (or H) with cgen, and only the 65 special loops (stack, bulges, 1x1, 1x2, 2x1,
 // 2x2) are evaluated through mc_interior.
-#define MC_CGEN_ROWS 37      // u1 = 0..36 (rows past 30 are zero: the u1 loop is unrolled by six)
+#define MC_GEN_BATCH 10      // loads of G / H in flight per lane
+#define MC_CGEN_ROWS 41      // u1 = 0..40 (rows past 30 are zero: the u1 loop runs in batches)
 
 // sum over u1 >= 1, 1 <= u2 = lane of A[u1*row_step + u2*col_step] * cgen[u1][u2]
 // subject to u1 <= u1max, u2 <= u2max, u1 + u2 <= usum (<= MC_MAXLOOP).  Lane-partial.
@@ -81,38 +105,45 @@ __device__ __forceinline__ double mc_generic_sum(const double* __restrict__ A, p
   const bool lane_ok = u2 >= 1 && u2 <= u2max;
   const double* a = A + (ptrdiff_t)u2 * col_step;
   const int top = min(u1max, usum - 1);
-  for (int u0 = 1; u0 <= top; u0 += 6) {
-    double v[6];
+  for (int u0 = 1; u0 <= top; u0 += MC_GEN_BATCH) {
+    double v[MC_GEN_BATCH];
 #pragma unroll
-    for (int t = 0; t < 6; ++t) {
+    for (int t = 0; t < MC_GEN_BATCH; ++t) {
       const int u1 = u0 + t;
       v[t] = (lane_ok && u1 <= u1max && u1 + u2 <= usum) ? a[(ptrdiff_t)u1 * row_step] : 0.0;
     }
 #pragma unroll
-    for (int t = 0; t < 6; ++t) s += v[t] * cgen[(u0 + t) * 32 + u2];
+    for (int t = 0; t < MC_GEN_BATCH; ++t) s += v[t] * cgen[(u0 + t) * 32 + u2];
   }
   return s;
 }
 
 // Inside recursion over all spans for the current scale.  Returns nothing; q(1,n) is in ws.q.
 __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                          const double* mlb, const double* cgen, int* next_cell, const McWs& w, int warp, int lane) {
+                          const double* mlb, const double* cgen, int* next_cell, const McWs& w, const McTeam& tm,
+                          int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
-  for (int i = 1 + threadIdx.x; i <= n + 1; i += MC_THREADS) w.q[IX(i, i - 1)] = 1.0;
+  for (int i = 1 + tm.rank * MC_THREADS + threadIdx.x; i <= n + 1; i += tm.nc * MC_THREADS) w.q[IX(i, i - 1)] = 1.0;
   if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
-  __syncthreads();
+  mc_sync(tm);
   for (int d = 0; d < n; ++d) {
     // cells of the diagonal are handed out dynamically: a cell whose ends can pair
     // costs several times one whose ends cannot
     for (;;) {
       int i = 0;
-      if (lane == 0) i = 1 + atomicAdd(&next_cell[d & 1], 1);
+      if (lane == 0) i = 1 + tm.rank + tm.nc * atomicAdd(&next_cell[d & 1], 1);
       i = __shfl_sync(0xffffffffu, i, 0);
       if (i + d > n) break;
       const int j = i + d;
       const int si = S[i], sj = S[j];
       const int type = mc_pair(si, sj);
       const bool closes = (d > MC_TURN) && type != 0;
+      // operands of the lane-0 epilogue, requested now so that their latency hides
+      // behind the sums (uniform addresses: one broadcast transaction each)
+      const double pre_A = (closes && d > 2) ? w.A[IX(i + 1, j - 1)] : 0.0;
+      const double pre_m1 = d > 0 ? w.qm1T[IX(j - 1, i)] : 0.0;
+      const double pre_e1 = d > 0 ? w.qqT[IX(j - 1, i)] : 0.0;
+      const double pre_R = d > 0 ? w.R[IX(i + 1, j)] : 0.0;
       double vb = 0.0;          // hairpin + interior part of qb, lane-partial
       if (closes) {
         if (lane == 0) {
@@ -147,72 +178,101 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
           }
         }
       }
-      // the three O(d) sums share one pass over k = i+1 .. j
-      double sm = 0.0, sq = 0.0, sml = 0.0;
+      // the two O(d) sums share one pass over k = i+1 .. j; four strides of 32 per
+      // round keep up to 16 independent loads in flight per lane
+      double sm = 0.0, sq = 0.0;
       const double* qm_i = w.qm + IX(i, 0);
-      const double* qm_i1 = w.qm + IX(i + 1, 0);
       const double* q_i = w.q + IX(i, 0);
       const double* qm1T_j = w.qm1T + IX(j, 0);
-      const double* qm1T_j1 = w.qm1T + IX(j - 1, 0);
       const double* qqT_j = w.qqT + IX(j, 0);
-      for (int k = i + 1 + lane; k <= j; k += 32) {
-        sm += (mlb[k - i] + qm_i[k - 1]) * qm1T_j[k];
-        sq += q_i[k - 1] * qqT_j[k];
-        if (closes && k >= i + 2 && k <= j - 1) sml += qm_i1[k - 1] * qm1T_j1[k];
+      for (int kb = i + 1 + lane; kb <= j; kb += 128) {
+        double a0[4], a1[4], b0[4], b1[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int k = kb + 32 * u;
+          const bool ok = k <= j;
+          a0[u] = ok ? qm_i[k - 1] : 0.0;  a1[u] = ok ? qm1T_j[k] : 0.0;
+          b0[u] = ok ? q_i[k - 1] : 0.0;   b1[u] = ok ? qqT_j[k] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { sm += a0[u] * a1[u]; sq += b0[u] * b1[u]; }
       }
-      vb = mc_warp_sum(vb); sm = mc_warp_sum(sm); sq = mc_warp_sum(sq); sml = mc_warp_sum(sml);
+      vb = mc_warp_sum(vb); sm = mc_warp_sum(sm); sq = mc_warp_sum(sq);
       if (lane == 0) {
-        if (closes) vb += sml * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
+        if (closes)
+          vb += pre_A * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
         w.qb[IX(i, j)] = vb;
         w.G[IX(i, j)] = (vb != 0.0) ? vb * (double)T.mmI[mc_rtype(type) - 1][S[j + 1]][S[i - 1]] : 0.0;
         const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
-        double m1 = (d > 0 ? w.qm1T[IX(j - 1, i)] : 0.0) * mlb[1];
-        double e1 = (d > 0 ? w.qqT[IX(j - 1, i)] : 0.0) * scale[1];
+        double m1 = pre_m1 * mlb[1];
+        double e1 = pre_e1 * scale[1];
         if (vb != 0.0) { m1 += vb * mc_stem(T, type, si1, sj1, true); e1 += vb * mc_stem(T, type, si1, sj1, false); }
         w.qm1T[IX(j, i)] = m1;
         w.qqT[IX(j, i)] = e1;
-        const double vqm = sm + m1;                   // k = i term: (mlb^0 + 0) * qm1(i,j)
+        const double r = m1 + pre_R * mlb[1];
+        w.A[IX(i, j)] = sm;
+        w.R[IX(i, j)] = r;
+        const double vqm = sm + r;
         w.qm[IX(i, j)] = vqm;
         w.qmT[IX(j, i)] = vqm;
         w.q[IX(i, j)] = scale[d + 1] + e1 + sq;
       }
     }
     if (threadIdx.x == 0) next_cell[(d + 1) & 1] = 0;
-    __syncthreads();
+    mc_sync(tm);
   }
 #undef IX
 }
 
 // Outside recursion; needs the inside arrays of the same scale.
 __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                           const double* mlb, const double* cgen, int* next_cell, const McWs& w, int warp, int lane) {
+                           const double* mlb, const double* cgen, int* next_cell, const McWs& w, const McTeam& tm,
+                           int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
-  // O, H, OM, prmlT, prm_lT start at zero: entries that are never written (pairs
-  // that cannot form, q > n) are read as 0.
-  for (size_t c = threadIdx.x; c < (size_t)(n + 2) * W; c += MC_THREADS) {
-    w.O[c] = 0.0; w.H[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0;
+  // O, H, OM, prmlT, prm_lT, PLT, tB start at zero: entries that are never written
+  // (pairs that cannot form, q > n) are read as 0.
+  for (size_t c = (size_t)tm.rank * MC_THREADS + threadIdx.x; c < (size_t)(n + 2) * W; c += (size_t)tm.nc * MC_THREADS) {
+    w.O[c] = 0.0; w.H[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0; w.PLT[c] = 0.0; w.tB[c] = 0.0;
   }
   if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
-  __syncthreads();
+  mc_sync(tm);
   for (int d = n - 1; d > MC_TURN; --d) {
     for (;;) {
       int i = 0;
-      if (lane == 0) i = 1 + atomicAdd(&next_cell[d & 1], 1);
+      if (lane == 0) i = 1 + tm.rank + tm.nc * atomicAdd(&next_cell[d & 1], 1);
       i = __shfl_sync(0xffffffffu, i, 0);
       if (i + d > n) break;
       const int j = i + d;
+      const double pre_pl = j + 1 <= n ? w.prm_lT[IX(j + 1, i)] : 0.0;
+      const double pre_om = j + 1 <= n ? w.OM[IX(i, j + 1)] : 0.0;
+      const double pre_prml = i > 1 ? w.prmlT[IX(j, i - 1)] : 0.0;
+      const double pre_tB = i > 1 ? w.tB[IX(i - 1, j)] : 0.0;
+      const double pre_q1 = w.q[IX(1, i - 1)], pre_q2 = w.q[IX(j + 1, n)];
       // (a) prm_l(i,j), prml(i,j): OM of spans >= d+1 only
       if (j + 1 <= n) {
         double t = 0.0;
         const double* OM_i = w.OM + IX(i, 0);
         const double* qm_j1 = w.qm + IX(j + 1, 0);
-        for (int qx = j + 2 + lane; qx <= n; qx += 32) t += OM_i[qx] * qm_j1[qx - 1];
+        for (int qb0 = j + 2 + lane; qb0 <= n; qb0 += 128) {
+          double x0[4], x1[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int qx = qb0 + 32 * u;
+            x0[u] = qx <= n ? OM_i[qx] : 0.0; x1[u] = qx <= n ? qm_j1[qx - 1] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) t += x0[u] * x1[u];
+        }
         t = mc_warp_sum(t);
         if (lane == 0) {
+          const double pl = pre_pl * mlb[1] + pre_om;
           w.prmlT[IX(j, i)] = t;
-          w.prm_lT[IX(j, i)] = w.prm_lT[IX(j + 1, i)] * mlb[1] + OM_i[j + 1];
+          w.prm_lT[IX(j, i)] = pl;
+          w.PLT[IX(j, i)] = t + pl;
         }
       }
+      const double tb = pre_prml + mlb[1] * pre_tB;
+      if (lane == 0 && i > 1) w.tB[IX(i, j)] = tb;
       // (b) O(i,j)
       const int type = mc_pair(S[i], S[j]);
       if (!type) continue;
@@ -221,7 +281,7 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
       const int t2 = mc_rtype(type);
       double o = 0.0;
-      if (lane == 0) o = w.q[IX(1, i - 1)] * w.q[IX(j + 1, n)] * mc_stem(T, type, si1, sj1, false);
+      if (lane == 0) o = pre_q1 * pre_q2 * mc_stem(T, type, si1, sj1, false);
       if (i > 1 && j < n) {
         // (p,q) = (i-1-u1, j+1+u2) encloses (i,j)
         const int sp1 = S[i - 1], sq1 = S[j + 1];
@@ -246,23 +306,28 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
         }
       }
       double t = 0.0;
-      const double* prm_l_j = w.prm_lT + IX(j, 0);
-      const double* prml_j = w.prmlT + IX(j, 0);
+      const double* pl_j = w.PLT + IX(j, 0);
       const double* qmT_i1 = w.qmT + IX(i - 1, 0);       // qm(p+1, i-1) = qmT[i-1][p+1]
-      for (int p = 1 + lane; p < i; p += 32) {
-        const double qml = (p + 1 <= i - 1) ? qmT_i1[p + 1] : 0.0;
-        t += prm_l_j[p] * qml + prml_j[p] * (mlb[i - p - 1] + qml);
+      for (int pb = 1 + lane; pb < i - 1; pb += 128) {
+        double x0[4], x1[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int p = pb + 32 * u;
+          x0[u] = p < i - 1 ? pl_j[p] : 0.0; x1[u] = p < i - 1 ? qmT_i1[p + 1] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) t += x0[u] * x1[u];
       }
       o = mc_warp_sum(o); t = mc_warp_sum(t);
       if (lane == 0) {
-        o += t * mc_stem(T, type, si1, sj1, true);
+        o += (t + tb) * mc_stem(T, type, si1, sj1, true);
         w.O[IX(i, j)] = o;
         w.H[IX(i, j)] = o * (double)T.mmI[type - 1][S[i + 1]][S[j - 1]];
         w.OM[IX(i, j)] = o * ((double)T.ml_closing * mc_stem(T, t2, S[j - 1], S[i + 1], true)) * scale[2];
       }
     }
     if (threadIdx.x == 0) next_cell[(d - 1) & 1] = 0;
-    __syncthreads();
+    mc_sync(tm);
   }
 #undef IX
 }
@@ -274,7 +339,6 @@ namespace dafs {
 // Dynamic shared memory: McTables | cgen[37][32] | scale[W+2] | mlb[W+2] | codes[W+8]
 __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   extern __shared__ __align__(16) char smem[];
-  __shared__ int s_q;
   __shared__ int s_total;
   __shared__ int s_next[2];
   McTables& T = *reinterpret_cast<McTables*>(smem);
@@ -284,6 +348,11 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   double* mlb = scale + (a.W + 2);
   uint8_t* S = reinterpret_cast<uint8_t*>(mlb + (a.W + 2));
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  McTeam tm;
+  tm.nc = a.cluster;
+  tm.rank = tm.nc > 1 ? (int)cooperative_groups::this_cluster().block_rank() : 0;
+  const int team = blockIdx.x / tm.nc, nteams = gridDim.x / tm.nc;
+  const int gwarp = tm.rank * MC_WARPS + warp, nwarps = tm.nc * MC_WARPS;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.tab);
     uint32_t* dst = reinterpret_cast<uint32_t*>(&T);
@@ -292,19 +361,18 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   const int W = a.W;
   McWs w;
   {
-    double* base = a.ws + (size_t)blockIdx.x * a.ws_stride;
+    double* base = a.ws + (size_t)team * a.ws_stride;
     const size_t A = (size_t)W * W;
     w.q = base; w.qb = base + A; w.qm = base + 2 * A; w.qmT = base + 3 * A; w.qm1T = base + 4 * A;
     w.qqT = base + 5 * A; w.O = base + 6 * A; w.OM = base + 7 * A; w.prmlT = base + 8 * A; w.prm_lT = base + 9 * A;
-    w.G = base + 10 * A; w.H = base + 11 * A;
+    w.G = base + 10 * A; w.A = base + 11 * A; w.R = base + 12 * A;
+    w.H = w.G; w.PLT = w.A; w.tB = w.R;
   }
 #define IX(i, j) ((size_t)(i) * W + (j))
-  for (;;) {
-    __syncthreads();
-    if (tid == 0) s_q = atomicAdd(a.queue, 1);
-    __syncthreads();
-    if (s_q >= a.nseq) break;
-    const int s = a.order[s_q];
+  // sequences are dealt to the teams round-robin in length order (longest first)
+  for (int sq = team; sq < a.nseq; sq += nteams) {
+    mc_sync(tm);
+    const int s = a.order[sq];
     const int n = a.seq_len[s];
     const uint8_t* gs = a.seq + a.seq_off[s];
     for (int k = tid; k <= n + 1; k += MC_THREADS) S[k] = (k >= 1 && k <= n) ? gs[k - 1] : (uint8_t)0;
@@ -323,7 +391,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
         cgen[k] = generic ? (double)T.internal[u1 + u2] * (double)T.ninio[ul - us] * exp(-(double)(u1 + u2 + 2) * lns) : 0.0;
       }
       __syncthreads();
-      mc_inside(T, S, n, W, scale, mlb, cgen, s_next, w, warp, lane);
+      mc_inside(T, S, n, W, scale, mlb, cgen, s_next, w, tm, lane);
       Z = w.q[IX(1, n)];
       if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
       if (!(Z > 0.0)) { lns -= 0.25; continue; }
@@ -331,12 +399,12 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
       if (fabs(log(Z)) <= 150.0) break;
       lns = lnZ / (double)n;                            // rerun with the ensemble's own scale
     }
-    mc_outside(T, S, n, W, scale, mlb, cgen, s_next, w, warp, lane);
+    mc_outside(T, S, n, W, scale, mlb, cgen, s_next, w, tm, lane);
     // ---- read-out: p = float(qb*O/Z) > th, rows ascending, columns ascending ----
     int32_t* row_ptr = a.row_ptr + a.row_off[s];
     const float th = a.th;
     const double invZ = 1.0 / Z;
-    for (int i = 1 + warp; i <= n; i += MC_WARPS) {
+    for (int i = 1 + gwarp; i <= n; i += nwarps) {
       int cnt = 0;
       for (int jb = i + 1; jb <= n; jb += 32) {
         const int j = jb + lane;
@@ -346,8 +414,8 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
       }
       if (lane == 0) row_ptr[i] = cnt;                  // count of row i-1 (0-based), scanned below
     }
-    __syncthreads();
-    if (warp == 0) {                                    // exclusive scan over rows by one warp
+    mc_sync(tm);
+    if (gwarp == 0) {                                   // exclusive scan over rows by one warp
       int run = 0;
       for (int b = 1; b <= n; b += 32) {
         const int i = b + lane;
@@ -360,13 +428,13 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
       }
       if (lane == 0) { row_ptr[0] = 0; s_total = run; }
     }
-    __syncthreads();
+    mc_sync(tm);
     {
       uint32_t* col = a.pool_col + a.pool_off[s];
       float* val = a.pool_val + a.pool_off[s];
       const int64_t cap = a.pool_off[s + 1] - a.pool_off[s];
       const unsigned lt = (1u << lane) - 1u;
-      for (int i = 1 + warp; i <= n; i += MC_WARPS) {
+      for (int i = 1 + gwarp; i <= n; i += nwarps) {
         int run = row_ptr[i - 1];
         for (int jb = i + 1; jb <= n; jb += 32) {
           const int j = jb + lane;
@@ -378,7 +446,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
           run += __popc(m);
         }
       }
-      if (tid == 0) { a.seq_nnz[s] = s_total; a.seq_lnz[s] = lnZ; }
+      if (tid == 0 && tm.rank == 0) { a.seq_nnz[s] = s_total; a.seq_lnz[s] = lnZ; }
     }
   }
 #undef IX
