@@ -6,6 +6,8 @@
 #include <cmath>
 #include <cstring>
 #include <thread>
+#include <cstdlib>
+#include <cstdio>
 #include <vector>
 
 #include "common.cuh"
@@ -28,7 +30,7 @@ struct NusHost {
 };
 struct ProbHost {
   NusHost sx, sy;
-  int L1 = 0, L2 = 0, nz = 0, ncbp = 0, t_max = 0;
+  int L1 = 0, L2 = 0, nb = 0, bw = 0, ncz = 0, ncbp = 0, t_max = 0;
   size_t z_out = 0, result = 0, trace = 0;                     // result buffer
   std::vector<char> cst;                                       // the constant block
   size_t res_bytes = 0;
@@ -243,46 +245,50 @@ static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H)
   H.cst.assign(sizeof(DDHdr), 0);
   build_nus(H.sx, H.cst, res, L1, q.p_x, wx, q.th_s, cx);
   build_nus(H.sy, H.cst, res, L2, q.p_y, wy, q.th_s, cy);
-  // z: cells with p_z != 0 (every other cell adds exactly 0 in needleman_wunsch.cpp:282)
-  // or in c_z (the only cells whose multiplier can leave 0), row by row, ascending k
-  std::vector<int> z_row_ptr(L1 + 1, 0);
-  std::vector<uint16_t> z_col;
-  std::vector<float> z_p;
-  std::vector<uint8_t> z_flag;
-  std::vector<int> cz_id(cz.size());
-  {
-    size_t c = 0;
-    for (int i = 0; i < L1; ++i) {
-      const float* row = q.p_z + (size_t)i * L2;
-      for (int k = 0; k < L2; ++k) {
-        const bool in_cz = (c < cz.size() && cz[c].first == i && cz[c].second == k);
-        if (row[k] != 0.0f || in_cz) {
-          if (in_cz) { cz_id[c] = (int)z_col.size(); ++c; }
-          z_col.push_back((uint16_t)k); z_p.push_back(row[k]); z_flag.push_back(in_cz ? 1 : 0);
-        }
-      }
-      z_row_ptr[i + 1] = (int)z_col.size();
-    }
-  }
-  H.nz = (int)z_col.size();
+  // z: the aligner only ever evaluates cells inside the envelope
+  // (needleman_wunsch.cpp:262-264), so p_z is kept as a dense band over it; the
+  // multipliers q_z can leave 0 only on c_z, kept as a short list per row with the
+  // band position of each cell.
   std::vector<uint2> env;
   build_envelope(L1, L2, q.th_a, q.p_z, env);
+  std::vector<int> boff(L1 + 2, 0);
+  std::vector<float> pb;
+  for (int r = 1; r <= L1; ++r) {
+    boff[r] = (int)pb.size();
+    const int ef = std::max(1, (int)env[r].x), el = (int)env[r].y;
+    for (int k = ef; k <= el; ++k) pb.push_back(q.p_z[(size_t)(r - 1) * L2 + (k - 1)]);
+    H.bw = std::max(H.bw, el - ef + 1);
+  }
+  boff[L1 + 1] = (int)pb.size();
+  H.nb = (int)pb.size();
+  std::vector<int> cz_row_ptr(L1 + 1, 0), cz_bidx(cz.size());
+  std::vector<uint16_t> cz_col(cz.size());
+  for (size_t c = 0; c < cz.size(); ++c) {
+    const int i = cz[c].first, k = cz[c].second;               // 0-based; row r = i+1, column k+1
+    ++cz_row_ptr[i + 1];
+    cz_col[c] = (uint16_t)k;
+    const int ef = std::max(1, (int)env[i + 1].x), el = (int)env[i + 1].y;
+    cz_bidx[c] = (k + 1 >= ef && k + 1 <= el) ? boff[i + 1] + (k + 1 - ef) : -1;
+  }
+  for (int i = 0; i < L1; ++i) cz_row_ptr[i + 1] += cz_row_ptr[i];
+  H.ncz = (int)cz.size();
   DDHdr h{};
-  h.z_row_ptr = (uint32_t)put(H.cst, z_row_ptr.data(), z_row_ptr.size());
-  h.z_col = (uint32_t)put(H.cst, z_col.data(), z_col.size());
-  h.z_p = (uint32_t)put(H.cst, z_p.data(), z_p.size());
-  h.z_flag = (uint32_t)put(H.cst, z_flag.data(), z_flag.size());
   h.z_env = (uint32_t)put(H.cst, env.data(), env.size());
+  h.z_boff = (uint32_t)put(H.cst, boff.data(), boff.size());
+  h.z_pb = (uint32_t)put(H.cst, pb.data(), pb.size());
+  h.cz_row_ptr = (uint32_t)put(H.cst, cz_row_ptr.data(), cz_row_ptr.size());
+  h.cz_col = (uint32_t)put(H.cst, cz_col.data(), cz_col.size());
+  h.cz_bidx = (uint32_t)put(H.cst, cz_bidx.data(), cz_bidx.size());
   std::vector<int4> cb(cbp.size());
   auto zid = [&](int i, int k) {
-    return cz_id[std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin()];
+    return (int)(std::lower_bound(cz.begin(), cz.end(), std::make_pair(i, k)) - cz.begin());
   };
   for (size_t u = 0; u < cbp.size(); ++u)
     cb[u] = make_int4(find_ent(H.sx, cbp[u].i, cbp[u].j), find_ent(H.sy, cbp[u].k, cbp[u].l),
                       zid(cbp[u].i, cbp[u].k), zid(cbp[u].j, cbp[u].l));
   h.cbp = (uint32_t)put(H.cst, cb.data(), cb.size());
   H.cst.resize(up16(H.cst.size()));
-  h.L1 = L1; h.L2 = L2; h.nz = H.nz; h.ncbp = H.ncbp; h.t_max = q.t_max;
+  h.L1 = L1; h.L2 = L2; h.nb = H.nb; h.ncz = H.ncz; h.ncbp = H.ncbp; h.t_max = q.t_max;
   h.bytes = (int)H.cst.size();
   h.th_s = q.th_s; h.th_a = q.th_a; h.eta0 = q.eta0;
   h.x = H.sx.h; h.y = H.sy.h;
@@ -331,7 +337,7 @@ static void free_dd_plan(dafs_dd_plan* p) {
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 
-struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nz = 1, ncbp = 1, col = 0, cst = 16, nIx = 1, nJx = 1, nIy = 1, nJy = 1; };
+struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nb = 1, bw = 1, ncz = 1, ncbp = 1, col = 0, cst = 16, nIx = 1, nJx = 1, nIy = 1, nJy = 1; };
 
 // Scratch layout from the batch maxima: items go to shared memory in priority
 // order (enum order in dd_kernel.cuh) while they fit, the rest to the per-CTA
@@ -340,22 +346,22 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
   lay.lp1 = (m.nJx + 2) & ~1;      // even stride: lane*lp + (B0 + s - lane) hits 32 distinct banks
   lay.lp2 = (m.nJy + 2) & ~1;
   lay.trs1 = m.nJx; lay.trs2 = m.nJy;
-  lay.w16 = (m.L2 + 15) / 16;
+  lay.ts = (m.bw + 31) / 32;
   lay.tr16 = (m.col > 120) ? 1u : 0u;
   const size_t trb = lay.tr16 ? 2 : 1;
   size_t sz[DD_NITEMS];
   sz[DD_CST] = (size_t)m.cst;
-  sz[DD_Q_X] = 4 * (size_t)m.nx; sz[DD_Q_Y] = 4 * (size_t)m.ny; sz[DD_Q_Z] = 4 * (size_t)m.nz;
+  sz[DD_Q_X] = 4 * (size_t)m.nx; sz[DD_Q_Y] = 4 * (size_t)m.ny; sz[DD_Q_Z] = 4 * (size_t)m.nb; sz[DD_Q_CZ] = 4 * (size_t)m.ncz;
   sz[DD_ES_X] = 4 * (size_t)m.nx; sz[DD_ES_Y] = 4 * (size_t)m.ny;
   sz[DD_ROW_X] = 4 * (size_t)32 * lay.lp1; sz[DD_ROW_Y] = 4 * (size_t)32 * lay.lp2;
   sz[DD_BROW_X] = 4 * (size_t)lay.lp1; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2;
-  sz[DD_BROW_Z] = 4 * (size_t)(m.L2 + 2);
-  sz[DD_TRZ] = 4 * (size_t)(m.L1 + 1) * lay.w16;
+  sz[DD_BROW_Z] = 4 * 2 * (size_t)(m.L2 + 2);
+  sz[DD_TRZ] = 8 * (size_t)(m.L1 + 1) * lay.ts;
   sz[DD_TR_X] = trb * ((size_t)m.nIx * m.nJx + 1);
   sz[DD_TR_Y] = trb * ((size_t)m.nIy * m.nJy + 1);
   sz[DD_SS_X] = 4 * (size_t)m.L1; sz[DD_SS_Y] = 4 * (size_t)m.L2; sz[DD_ZRES] = 4 * (size_t)m.L1;
   sz[DD_STK_X] = 4 * (size_t)(m.L1 / 2 + 4); sz[DD_STK_Y] = 4 * (size_t)(m.L2 / 2 + 4);
-  sz[DD_TAL_X] = 4 * (size_t)m.nx; sz[DD_TAL_Y] = 4 * (size_t)m.ny; sz[DD_TAL_Z] = 4 * (size_t)m.nz;
+  sz[DD_TAL_X] = 4 * (size_t)m.nx; sz[DD_TAL_Y] = 4 * (size_t)m.ny; sz[DD_TAL_Z] = 4 * (size_t)m.ncz;
   sz[DD_SW] = 4 * (size_t)m.ncbp;
   size_t s_off = 0, g_off = 0;
   lay.in_smem = 0;
@@ -366,6 +372,13 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
   }
   *smem_bytes = (int)s_off;
   *ws_bytes = up16(g_off) + 256;
+  if (getenv("DAFS_DD_DEBUG_LAYOUT")) {
+    static const char* names[DD_NITEMS] = {"CST", "Q_X", "Q_Y", "Q_Z", "Q_CZ", "ES_X", "ES_Y", "ROW_X", "ROW_Y", "BROW_X", "BROW_Y",
+                                           "BROW_Z", "TRZ", "TR_X", "TR_Y", "SS_X", "SS_Y", "ZRES", "STK_X", "STK_Y",
+                                           "TAL_X", "TAL_Y", "TAL_Z", "SW"};
+    for (int k = 0; k < DD_NITEMS; ++k) fprintf(stderr, "dd layout %-7s %8zu B %s\n", names[k], sz[k], (lay.in_smem >> k & 1) ? "smem" : "hbm");
+    fprintf(stderr, "dd layout total smem %zu B; nx %d ny %d nb %d ncz %d ncbp %d nI/nJ x %d/%d y %d/%d\n", s_off, m.nx, m.ny, m.nb, m.ncz, m.ncbp, m.nIx, m.nJx, m.nIy, m.nJy);
+  }
 }
 
 }  // namespace dafs
@@ -422,10 +435,10 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     m.nx = std::max(m.nx, H.sx.h.n); m.ny = std::max(m.ny, H.sy.h.n);
     m.nIx = std::max(m.nIx, H.sx.h.nI); m.nJx = std::max(m.nJx, H.sx.h.nJ);
     m.nIy = std::max(m.nIy, H.sy.h.nI); m.nJy = std::max(m.nJy, H.sy.h.nJ);
-    m.nz = std::max(m.nz, H.nz); m.ncbp = std::max(m.ncbp, H.ncbp);
+    m.nb = std::max(m.nb, H.nb); m.bw = std::max(m.bw, H.bw); m.ncz = std::max(m.ncz, H.ncz); m.ncbp = std::max(m.ncbp, H.ncbp);
     m.col = std::max(m.col, std::max(H.sx.max_col, H.sy.max_col));
     m.cst = std::max(m.cst, (int)H.cst.size());
-    p->total_cbp += H.ncbp; p->total_entries += H.sx.h.n + H.sy.h.n + H.nz;
+    p->total_cbp += H.ncbp; p->total_entries += H.sx.h.n + H.sy.h.n + H.nb;
   }
   p->cst_bytes = cst; p->res_bytes = res;
   PLAN_TRY(cudaMalloc(&p->d_cst, std::max<size_t>(cst, 256)));
@@ -668,37 +681,40 @@ extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, con
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
   std::vector<uint2> env;
   build_envelope(L1, L2, th, p, env);
-  // cells with p != 0 or q != 0; every other cell adds exactly 0 twice (:282)
-  std::vector<int> row_ptr(L1 + 1, 0);
-  std::vector<uint16_t> col;
+  // dense bands of p and q over the envelope (cells outside it are never evaluated, :262-264)
+  std::vector<int> boff(L1 + 2, 0);
   std::vector<float> pv, qv;
-  for (int i = 0; i < L1; ++i) {
-    for (int k = 0; k < L2; ++k) {
-      const float a = p[(size_t)i * L2 + k], b = q ? q[(size_t)i * L2 + k] : 0.0f;
-      if (a != 0.0f || b != 0.0f) { col.push_back((uint16_t)k); pv.push_back(a); qv.push_back(b); }
+  int bw = 1;
+  for (int r = 1; r <= L1; ++r) {
+    boff[r] = (int)pv.size();
+    const int ef = std::max(1, (int)env[r].x), el = (int)env[r].y;
+    bw = std::max(bw, el - ef + 1);
+    for (int k = ef; k <= el; ++k) {
+      pv.push_back(p[(size_t)(r - 1) * L2 + (k - 1)]);
+      qv.push_back(q ? q[(size_t)(r - 1) * L2 + (k - 1)] : 0.0f);
     }
-    row_ptr[i + 1] = (int)col.size();
   }
-  const int n = (int)col.size(), w16 = (L2 + 15) / 16;
+  boff[L1 + 1] = (int)pv.size();
+  const int n = (int)pv.size(), ts = (bw + 31) / 32;
   DevBuf B;
-  B.size = 16 * 16 + 4 * ((size_t)(L1 + 1) * (3 + w16) + 3 * (size_t)std::max(n, 1) + (L2 + 2) + 2 * (size_t)L1 + 8) + 64;
+  B.size = 16 * 16 + 4 * ((size_t)(L1 + 2) * (3 + 2 * ts) + 2 * (size_t)std::max(n, 1) + 2 * (L2 + 2) + 2 * (size_t)L1 + 8) + 64;
   DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
   DDAln A{}; NwScratch sc{};
-  int* d_rp = B.take<int>(L1 + 1); uint16_t* d_col = B.take<uint16_t>(n);
+  int* d_boff = B.take<int>(L1 + 2);
   float* d_p = B.take<float>(n); float* d_q = B.take<float>(n);
   uint2* d_env = B.take<uint2>(L1 + 1);
-  sc.brow = B.take<float>(L2 + 2); sc.trz = B.take<uint32_t>((size_t)(L1 + 1) * w16); sc.zres = B.take<uint32_t>(L1);
-  sc.w16 = w16;
+  sc.rowbuf = B.take<float>(2 * (L2 + 2)); sc.trz = B.take<uint2>((size_t)(L1 + 1) * ts); sc.zres = B.take<uint32_t>(L1);
+  sc.ts = ts;
   uint32_t* d_al = B.take<uint32_t>(L1); float* d_score = B.take<float>(1); int* d_bad = B.take<int>(1);
-  DAFS_CUDA_TRY(cudaMemcpy(d_rp, row_ptr.data(), sizeof(int) * (L1 + 1), cudaMemcpyHostToDevice));
+  DAFS_CUDA_TRY(cudaMemcpy(d_boff, boff.data(), sizeof(int) * (L1 + 2), cudaMemcpyHostToDevice));
   if (n) {
-    DAFS_CUDA_TRY(cudaMemcpy(d_col, col.data(), sizeof(uint16_t) * n, cudaMemcpyHostToDevice));
     DAFS_CUDA_TRY(cudaMemcpy(d_p, pv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
     DAFS_CUDA_TRY(cudaMemcpy(d_q, qv.data(), sizeof(float) * n, cudaMemcpyHostToDevice));
   }
   DAFS_CUDA_TRY(cudaMemcpy(d_env, env.data(), sizeof(uint2) * (L1 + 1), cudaMemcpyHostToDevice));
   DAFS_CUDA_TRY(cudaMemset(d_bad, 0, sizeof(int)));
-  A.L1 = L1; A.L2 = L2; A.n = n; A.th = th; A.row_ptr = d_rp; A.col = d_col; A.p = d_p; A.q = d_q; A.env = d_env;
+  DAFS_CUDA_TRY(cudaMemset(d_score, 0, sizeof(float)));
+  A.L1 = L1; A.L2 = L2; A.th = th; A.env = d_env; A.boff = d_boff; A.pb = d_p; A.qb = d_q;
   nw_single_kernel<<<1, 32>>>(A, sc, d_al, d_score, d_bad);
   DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaMemcpy(al, d_al, sizeof(uint32_t) * L1, cudaMemcpyDeviceToHost));

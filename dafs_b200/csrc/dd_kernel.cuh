@@ -23,10 +23,11 @@
 //     left to right, one column behind the row below, whose values arrive by
 //     warp shuffle; bifurcations read the lane's own row and the column's
 //     candidate list in the reference's push order (bp[j], descending i).
-//   * NW: 32 rows per wave, top rows first, one column behind the row above,
-//     only across the wave's part of the alignment envelope; p_z and q_z come
-//     from sparse row lists (every other cell adds exactly 0); traceback codes
-//     are packed 2 bits per cell.
+//   * NW: only across the alignment envelope; p_z and q_z are
+//     kept as dense BANDS (row r holds columns ef(r)..el(r) of the envelope, the
+//     only cells the recursion ever evaluates), so a step is two indexed loads,
+//     three adds and two compares.  There is no gap cost, so a row is a prefix
+//     maximum over its band: one warp does a whole row per step (see nw_warp).
 // Multipliers are sparse: for x and y the decoder's candidates plus the CBP
 // projections c_x / c_y, for z the projection c_z -- nothing else can ever
 // become non-zero (see dd.cu).
@@ -63,13 +64,19 @@ struct DDNusHdr {
 };
 
 struct DDHdr {
-  int L1, L2, nz, ncbp, t_max, bytes;
+  int L1, L2, ncbp, t_max, bytes, pad1;
   float th_s, th_a, eta0;
   int pad0;
   DDNusHdr x, y;
-  // z: per row i the cells (i,k) with p_z != 0 or in c_z, ascending k
-  uint32_t z_row_ptr, z_col, z_p, z_flag, z_env;
-  uint32_t cbp;                // int4 {entry in x, entry in y, z entry of (i,k), z entry of (j,l)}
+  // z: the envelope, the band of p_z inside it, and the cells of c_z (dafs.cpp:1039-1040)
+  int nb, ncz;                 // band cells, |c_z|
+  uint32_t z_env;              // uint2[L1+1] {first, second}   (needleman_wunsch.cpp:198-253)
+  uint32_t z_boff;             // int[L1+2]   band index of (row r, column k) = boff[r] + k - max(1, first(r))
+  uint32_t z_pb;               // f32[nb]     p_z over the band
+  uint32_t cz_row_ptr;         // int[L1+1]   c_z cells of row i (0-based), ascending k
+  uint32_t cz_col;             // u16[ncz]
+  uint32_t cz_bidx;            // i32[ncz]    band index of the cell, -1 outside the envelope
+  uint32_t cbp;                // int4 {entry in x, entry in y, c_z id of (i,k), c_z id of (j,l)}
 };
 
 struct DDProbRef {
@@ -84,7 +91,7 @@ struct DDProbRef {
 // Per-CTA scratch arrays; each lives in shared memory when it fits (host decides,
 // in this order) and in a per-CTA global workspace otherwise.
 enum {
-  DD_CST, DD_Q_X, DD_Q_Y, DD_Q_Z, DD_ES_X, DD_ES_Y, DD_ROW_X, DD_ROW_Y, DD_BROW_X, DD_BROW_Y, DD_BROW_Z,
+  DD_CST, DD_Q_X, DD_Q_Y, DD_Q_Z, DD_Q_CZ, DD_ES_X, DD_ES_Y, DD_ROW_X, DD_ROW_Y, DD_BROW_X, DD_BROW_Y, DD_BROW_Z,
   DD_TRZ, DD_TR_X, DD_TR_Y, DD_SS_X, DD_SS_Y, DD_ZRES, DD_STK_X, DD_STK_Y, DD_TAL_X, DD_TAL_Y, DD_TAL_Z,
   DD_SW, DD_NITEMS
 };
@@ -94,7 +101,7 @@ struct DDLayout {
   uint32_t tr16;               // Nussinov traceback codes need 16 bits (a column with > 120 candidates)
   int lp1, lp2;                // row stride of the Nussinov row buffers (max live columns, odd)
   int trs1, trs2;              // row stride of the Nussinov traceback arrays (max live columns)
-  int w16;                     // NW traceback words per row: ceil(max L2 / 16)
+  int ts;                      // NW traceback words (uint2) per row: ceil(widest band / 32)
   char* ws;                    // global workspace
   size_t ws_stride;            // per CTA
 };
@@ -147,23 +154,22 @@ struct NusScratch {
   bool tr16;
 };
 
-// The alignment part: sparse p_z / q_z rows and the envelope.
+// The alignment part: the envelope and the dense bands of p_z / q_z inside it.
 struct DDAln {
-  int L1, L2, n;
+  int L1, L2;
   float th;
-  const int* row_ptr;          // [L1+1]
-  const uint16_t* col;         // [n] 0-based column k
-  const float* p;              // [n] p_z[i][k]
-  const uint8_t* flag;         // [n] bit0: (i,k) in c_z (dafs.cpp:1039-1040)
-  float* q;                    // [n] multipliers q_z[i][k] (zero everywhere else, see dd.cu)
   const uint2* env;            // [L1+1] {first, second}   (needleman_wunsch.cpp:198-253)
+  const int* boff;             // [L1+2] band offsets (row r starts at boff[r], column max(1, first(r)))
+  const float* pb;             // [nb] p_z over the band
+  const float* qb;             // [nb] multipliers q_z over the band (non-zero only on c_z, see dd.cu)
 };
 
 struct NwScratch {
-  float* brow;      // [L2+2] dp row above the current wave (row of the previous wave's last lane)
-  uint32_t* trz;    // traceback codes, 2 bits per cell (0 ' ', 1 'M', 2 'X', 3 'Y'), w16 words per row
+  float* rowbuf;    // 2 x [L2+2] dp rows (even / odd row)
+  uint2* trz;       // [(L1+1) * ts] traceback codes (0 ' ', 1 'M', 2 'X', 3 'Y') as bit planes {low, high}
+                    //               per 32 band columns
   uint32_t* zres;   // [L1] result
-  int w16;
+  int ts;           // words per row = ceil(widest band / 32)
 };
 
 }  // namespace dafs
@@ -320,89 +326,97 @@ __device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch&
 
 namespace dafs {
 
-// SparseNeedlemanWunsch::decode(p, q, al) by one warp.  Returns dp[L1][L2] in
-// every lane; *bad is set if the traceback meets an unfilled cell (the reference
-// would spin there, needleman_wunsch.cpp:309).
+// SparseNeedlemanWunsch::decode(p, q, al) by one warp, one ROW per step.
+// The reference's cell update (needleman_wunsch.cpp:282-293)
+//   v = dp[i-1][k-1] + p - th + q;  if (v < dp[i-1][k]) v = dp[i-1][k];  if (v < dp[i][k-1]) v = dp[i][k-1];
+// has no gap cost, so along a row dp[i][k] = max(a[k], dp[i][k-1]) with
+// a[k] = max(dp[i-1][k-1] + p - th + q, dp[i-1][k]) depending on the row above only:
+// the row is an (exact, order-independent) prefix maximum of a.  Lanes take 32
+// consecutive columns of the row's band [ef, el] (needleman_wunsch.cpp:262-264: nothing
+// outside it is ever evaluated), compute a, scan it with five shuffles, and derive the
+// reference's traceback code from the strict compares in its order: 3 if a < dp[i][k-1],
+// else 2 if the diagonal term < dp[i-1][k], else 1.  Codes are stored band-relative as
+// two bit planes per 32 columns.  The row above comes from a double-buffered row in
+// shared memory; cells of it outside ITS band are -FLT_MAX, column 0 and row 0 are 0
+// (:265-274).  Returns dp[L1][L2] in every lane; *bad is set if the traceback meets an
+// unfilled cell (the reference would spin there, :309).
 __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, int lane, int* bad,
                                          unsigned long long* prof) {
   const long long t0 = clock64();
-  const int L1 = A.L1, L2 = A.L2, w16 = sc.w16;
+  const int L1 = A.L1, L2 = A.L2, ts = sc.ts;
   const float th = A.th;
   float score = 0.0f;
-  for (int k = lane; k <= L2; k += 32) sc.brow[k] = 0.0f;          // row 0: dp[0][k] = 0 (:270-274)
-  __syncwarp();
-  for (int lo = 1; lo <= L1; lo += 32) {
-    const int row = lo + lane;
-    const bool live = row <= L1;
-    const int hi = min(L1, lo + 31);
-    // the envelope is monotone (:240-246): the wave needs columns ef(lo) .. el(hi) only
-    const int kmin = max(1, (int)A.env[lo].x), kmax = (int)A.env[hi].y;
-    int ecur = 0, eend = 0, ef = 1, el = 0;
-    if (live) {
-      ecur = A.row_ptr[row - 1]; eend = A.row_ptr[row];
-      const uint2 ev = A.env[row];
-      ef = max(1, (int)ev.x); el = (int)ev.y;
-      while (ecur < eend && (int)A.col[ecur] + 1 < kmin) ++ecur;
-    }
-    int next_k = 0x7fffffff; float next_p = 0.0f, next_q = 0.0f;
-    if (ecur < eend) { next_k = (int)A.col[ecur] + 1; next_p = A.p[ecur]; next_q = A.q[ecur]; }
-    // dp[row][kmin-1] and dp[row-1][kmin-1]: column 0 is 0 (:265-268), any other
-    // column left of the wave lies outside these rows' envelopes (:262-264)
-    const float edge = (kmin == 1) ? 0.0f : -FLT_MAX;
-    float cur = edge;
-    float diag = (lane == 0) ? sc.brow[kmin - 1] : edge;
-    float up_next = (lane == 0) ? sc.brow[kmin] : 0.0f;
-    uint32_t word = 0;
-    uint32_t* trow = sc.trz + row * w16;
-    const int nsteps = (kmax - kmin + 1) + 31;
-    for (int s = 0; s < nsteps; ++s) {
-      const int k = kmin + s - lane;
-      float up = __shfl_up_sync(0xffffffffu, cur, 1);                // dp[row-1][k]
-      if (lane == 0) { up = up_next; up_next = (k + 1 <= L2) ? sc.brow[k + 1] : 0.0f; }
-      if (live && k >= kmin && k <= kmax) {
-        float pv = 0.0f, qv = 0.0f;
-        if (k == next_k) {
-          pv = next_p; qv = next_q;
-          ++ecur;
-          next_k = 0x7fffffff;
-          if (ecur < eend) { next_k = (int)A.col[ecur] + 1; next_p = A.p[ecur]; next_q = A.q[ecur]; }
-        }
-        float v = -FLT_MAX;                                          // :262-264
-        uint32_t code = 0u;
-        if (k >= ef && k <= el) {
-          v = __fadd_rn(__fsub_rn(__fadd_rn(diag, pv), th), qv);     // :282
-          code = 1u;
-          if (v < up) { v = up; code = 2u; }                         // :284-288
-          if (v < cur) { v = cur; code = 3u; }                       // :289-293
-        }
-        word |= code << (2 * ((k - 1) & 15));
-        if (((k & 15) == 0) || k == kmax) { trow[(k - 1) >> 4] = word; word = 0; }
-        diag = up;
-        cur = v;
-        if (lane == 31) sc.brow[k] = v;
-        if (row == L1 && k == L2) score = v;
+  int pef = 0, pel = L2;                                  // band of the row above (row 0: every column, all 0)
+  for (int r = 1; r <= L1; ++r) {
+    const uint2 ev = A.env[r];
+    const int ef = max(1, (int)ev.x), el = (int)ev.y;
+    const int bb = A.boff[r] - ef;                         // band index of (r, k) = bb + k
+    const float* prev = sc.rowbuf + ((r - 1) & 1) * (L2 + 2);
+    float* mine = sc.rowbuf + (r & 1) * (L2 + 2);
+    uint2* trow = sc.trz + (size_t)r * ts;
+    float carry = (ef == 1) ? 0.0f : -FLT_MAX;            // dp[r][ef-1]
+    int chunk = 0;
+    for (int k0 = ef; k0 <= el; k0 += 32, ++chunk) {
+      const int k = k0 + lane;
+      const bool in = k <= el;
+      float up = 0.0f, dg = 0.0f, pv = 0.0f, qv = 0.0f;
+      if (in) { pv = A.pb[bb + k]; qv = A.qb[bb + k]; }
+      if (r > 1) {
+        up = (k >= pef && k <= pel) ? prev[k] : -FLT_MAX;                          // dp[r-1][k]
+        dg = (k == 1) ? 0.0f : ((k - 1 >= pef && k - 1 <= pel) ? prev[k - 1] : -FLT_MAX);   // dp[r-1][k-1]
       }
-      __syncwarp();
-    }
-    if (lo + 32 <= L1) {          // complete the row handed to the next wave: unfilled cells
-      for (int k = 1 + lane; k <= L2; k += 32) if (k < kmin || k > kmax) sc.brow[k] = -FLT_MAX;
-      if (lane == 0) sc.brow[0] = 0.0f;
+      const float m = __fadd_rn(__fsub_rn(__fadd_rn(dg, pv), th), qv);             // :282
+      const bool c2 = m < up;                                                      // :284
+      float x = in ? (c2 ? up : m) : -FLT_MAX;
+      const float a = x;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const float y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x = fmaxf(x, y);
+      }
+      const float v = fmaxf(x, carry);                                             // dp[r][k]
+      float left = __shfl_up_sync(0xffffffffu, v, 1);                              // dp[r][k-1]
+      if (lane == 0) left = carry;
+      const bool c3 = a < left;                                                    // :289
+      const unsigned lo = __ballot_sync(0xffffffffu, in && (c3 || !c2));           // codes 1 and 3
+      const unsigned hi = __ballot_sync(0xffffffffu, in && (c3 || c2));            // codes 2 and 3
+      if (lane == 0) trow[chunk] = make_uint2(lo, hi);
+      if (in) mine[k] = v;
+      if (r == L1 && k == L2) score = v;
+      carry = __shfl_sync(0xffffffffu, v, 31);
     }
     __syncwarp();
+    pef = ef; pel = el;
   }
-  score = __shfl_sync(0xffffffffu, score, (L1 - 1) & 31);
+  {
+    // dp[L1][L2] sits in the lane that owned column L2 of the last row (el(L1) = L2)
+    const int ef = max(1, (int)A.env[L1].x);
+    score = __shfl_sync(0xffffffffu, score, (L2 - ef) & 31);
+  }
   const long long t1 = clock64();
   // ---- traceback (:300-312) + alignment read-out (:317-335) ------------------
   for (int i = lane; i < L1; i += 32) sc.zres[i] = DD_NOPAIR;
   __syncwarp();
   if (lane == 0) {
     int i = L1, k = L2;
+    uint2 ev = A.env[L1];
     while (i > 0 && k > 0) {       // row 0 is all 'Y', column 0 all 'X': nothing more to record
-      const uint32_t code = (sc.trz[i * w16 + ((k - 1) >> 4)] >> (2 * ((k - 1) & 15))) & 3u;
+      const uint2 ev_up = A.env[i - 1];                            // wanted when the walk moves up: ask now
+      const int ef = max(1, (int)ev.x), c = k - ef;
+      if (c < 0 || k > (int)ev.y) { *bad = 1; break; }             // a cell that was never filled
+      const uint2 w = sc.trz[(size_t)i * ts + (c >> 5)];
+      // a run of 'Y' codes (3) only moves left and records nothing: jump to the nearest
+      // column at or left of k in this word whose code is not 3
+      const int b = c & 31;
+      const uint32_t stop = ~(w.x & w.y) & (0xffffffffu >> (31 - b));
+      if (stop == 0u) { k -= b + 1; continue; }                    // the run leaves the word
+      const int b2 = 31 - __clz(stop);
+      k -= b - b2;
+      const uint32_t code = ((w.x >> b2) & 1u) | (((w.y >> b2) & 1u) << 1);
       if (code == 1u) { --i; --k; sc.zres[i] = (uint32_t)k; }
       else if (code == 2u) --i;
-      else if (code == 3u) --k;
       else { *bad = 1; break; }
+      ev = ev_up;
     }
   }
   __syncwarp();
@@ -461,8 +475,8 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
   ns.ss = DD_ITEM(uint32_t, DD_SS_X + wy); ns.stk = DD_ITEM(uint32_t, DD_STK_X + wy);
   ns.lp = wy ? lay.lp2 : lay.lp1; ns.trs = wy ? lay.trs2 : lay.trs1; ns.tr16 = lay.tr16 != 0;
   NwScratch nz;
-  nz.brow = DD_ITEM(float, DD_BROW_Z); nz.trz = DD_ITEM(uint32_t, DD_TRZ); nz.zres = DD_ITEM(uint32_t, DD_ZRES);
-  nz.w16 = lay.w16;
+  nz.rowbuf = DD_ITEM(float, DD_BROW_Z); nz.trz = DD_ITEM(uint2, DD_TRZ); nz.zres = DD_ITEM(uint32_t, DD_ZRES);
+  nz.ts = lay.ts;
   uint32_t* ss_x = DD_ITEM(uint32_t, DD_SS_X);
   uint32_t* ss_y = DD_ITEM(uint32_t, DD_SS_Y);
   float* es_x = DD_ITEM(float, DD_ES_X);
@@ -473,7 +487,8 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
   float* sw = DD_ITEM(float, DD_SW);
   float* q_x = DD_ITEM(float, DD_Q_X);
   float* q_y = DD_ITEM(float, DD_Q_Y);
-  float* q_z = DD_ITEM(float, DD_Q_Z);
+  float* q_z = DD_ITEM(float, DD_Q_Z);       // band
+  float* q_cz = DD_ITEM(float, DD_Q_CZ);     // one per c_z cell
   char* cst_s = DD_ITEM(char, DD_CST);
   const bool cst_in_smem = SMEM || ((lay.in_smem >> DD_CST) & 1u);
 
@@ -496,12 +511,14 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     const DDNus X = dd_make_nus(blk, h.x, q_x), Y = dd_make_nus(blk, h.y, q_y);
     const DDNus& mine = wy ? Y : X;
     DDAln Z;
-    Z.L1 = h.L1; Z.L2 = h.L2; Z.n = h.nz; Z.th = h.th_a; Z.q = q_z;
-    Z.row_ptr = reinterpret_cast<const int*>(blk + h.z_row_ptr);
-    Z.col = reinterpret_cast<const uint16_t*>(blk + h.z_col);
-    Z.p = reinterpret_cast<const float*>(blk + h.z_p);
-    Z.flag = reinterpret_cast<const uint8_t*>(blk + h.z_flag);
+    Z.L1 = h.L1; Z.L2 = h.L2; Z.th = h.th_a; Z.qb = q_z;
     Z.env = reinterpret_cast<const uint2*>(blk + h.z_env);
+    Z.boff = reinterpret_cast<const int*>(blk + h.z_boff);
+    Z.pb = reinterpret_cast<const float*>(blk + h.z_pb);
+    const int* cz_row_ptr = reinterpret_cast<const int*>(blk + h.cz_row_ptr);
+    const uint16_t* cz_col = reinterpret_cast<const uint16_t*>(blk + h.cz_col);
+    const int* cz_bidx = reinterpret_cast<const int*>(blk + h.cz_bidx);
+    const int nb = h.nb, ncz = h.ncz;
     const int4* cbp = reinterpret_cast<const int4*>(blk + h.cbp);
     const int L1 = h.L1, L2 = h.L2, ncbp = h.ncbp, t_max = h.t_max;
     const float th_s = h.th_s, eta0 = h.eta0;
@@ -509,7 +526,8 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     // ---- q = 0 (dafs.cpp:1067-1069), scratch reset ----------------------------
     for (int e = tid; e < X.n; e += DD_THREADS) { q_x[e] = 0.0f; tal_x[e] = 0; if (e < X.nd) es_x[e] = -INFINITY; }
     for (int e = tid; e < Y.n; e += DD_THREADS) { q_y[e] = 0.0f; tal_y[e] = 0; if (e < Y.nd) es_y[e] = -INFINITY; }
-    for (int e = tid; e < Z.n; e += DD_THREADS) { q_z[e] = 0.0f; tal_z[e] = 0; }
+    for (int e = tid; e < nb; e += DD_THREADS) q_z[e] = 0.0f;
+    for (int e = tid; e < ncz; e += DD_THREADS) { q_cz[e] = 0.0f; tal_z[e] = 0; }
     for (int k = tid; k < L1; k += DD_THREADS) { ss_x[k] = DD_NOPAIR; nz.zres[k] = DD_NOPAIR; }
     for (int k = tid; k < L2; k += DD_THREADS) ss_y[k] = DD_NOPAIR;
     if (tid == 0) {
@@ -530,7 +548,7 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       // ---- tally (:1103-1117) ---------------------------------------------------
       for (int u = tid; u < ncbp; u += DD_THREADS) {
         const int4 cb = cbp[u];
-        const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_z[cb.z]), q_z[cb.w]);
+        const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_cz[cb.z]), q_cz[cb.w]);
         sw[u] = s_w;
         if (s_w > 0.0f) {
           atomicAdd(&tal_x[cb.x], 1); atomicAdd(&tal_y[cb.y], 1);
@@ -551,22 +569,25 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       unsigned viol = 0;
       dd_update_nus(X, ss_x, tal_x, eta, viol, tid, DD_THREADS);
       dd_update_nus(Y, ss_y, tal_y, eta, viol, tid, DD_THREADS);
-      // z (:1223-1254), one thread per row over its c_z entries.  Cells outside c_z
+      // z (:1223-1254), one thread per row over its c_z cells.  Cells outside c_z
       // have t_z = 0 and q_z = 0, and stay there: max(0, 0 - eta*(1-0)) = 0 for
       // eta >= 0 or NaN (the host rejects eta0 < 0).
       for (int i = tid; i < L1; i += DD_THREADS) {
         const uint32_t zi = nz.zres[i];
-        for (int e = Z.row_ptr[i]; e < Z.row_ptr[i + 1]; ++e) {
-          if (!(Z.flag[e] & 1)) continue;
+        for (int e = cz_row_ptr[i]; e < cz_row_ptr[i + 1]; ++e) {
           const int tz = tal_z[e];
           tal_z[e] = 0;
-          if (zi == (uint32_t)Z.col[e]) {                       // z_ik == 1  (:1226-1238)
+          float qn;
+          if (zi == (uint32_t)cz_col[e]) {                      // z_ik == 1  (:1226-1238)
             if (tz > 1) ++viol;
-            q_z[e] = dd_max0(__fsub_rn(q_z[e], __fmul_rn(eta, (float)(1 - tz))));
+            qn = dd_max0(__fsub_rn(q_cz[e], __fmul_rn(eta, (float)(1 - tz))));
           } else {                                               // z_ik == 0  (:1239-1253)
             if (tz > 0) ++viol;
-            q_z[e] = dd_max0(__fadd_rn(q_z[e], __fmul_rn(eta, (float)tz)));
+            qn = dd_max0(__fadd_rn(q_cz[e], __fmul_rn(eta, (float)tz)));
           }
+          q_cz[e] = qn;
+          const int bi = cz_bidx[e];
+          if (bi >= 0) q_z[bi] = qn;                             // the copy the aligner reads
         }
       }
       if (viol) atomicAdd(&sh.violated, viol);
@@ -585,7 +606,7 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
           }
           sh.s_prev = s;
         }
-        sh.prof[6] += tp1 - tp0; sh.prof[7] += clock64() - tp1;
+
       }
       __syncthreads();
       if (sh.done) break;
