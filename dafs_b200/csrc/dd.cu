@@ -469,11 +469,14 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     D.trace = p->want_trace ? reinterpret_cast<float*>(r + H.trace) : nullptr;
     order[k] = k;
   }
-  std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
-    const ProbHost &A = p->host[a], &B = p->host[b];
-    return (int64_t)A.t_max * ((int64_t)A.L1 * A.L1 + (int64_t)A.L2 * A.L2 + (int64_t)A.L1 * A.L2) >
-           (int64_t)B.t_max * ((int64_t)B.L1 * B.L1 + (int64_t)B.L2 * B.L2 + (int64_t)B.L1 * B.L2);
-  });
+  // Longest expected job first: the batch ends with its slowest problem, and a problem
+  // runs the longer the more base-pair constraints it has to reconcile (none: one
+  // iteration; many: it usually runs into the -m cap).
+  auto cost = [&](const ProbHost& H) {
+    const double cells = (double)H.L1 * H.L1 + (double)H.L2 * H.L2 + (double)H.L1 * H.L2;
+    return cells * (double)std::min<int64_t>(H.t_max, 1 + (int64_t)H.ncbp);
+  };
+  std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost(p->host[a]) > cost(p->host[b]); });
   PLAN_TRY(cudaMemcpy(p->d_prob, dp.data(), sizeof(DDProbRef) * nprob, cudaMemcpyHostToDevice));
   PLAN_TRY(cudaMemcpy(p->d_order, order.data(), sizeof(int32_t) * nprob, cudaMemcpyHostToDevice));
 

@@ -345,25 +345,32 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
   const long long t0 = clock64();
   const int L1 = A.L1, L2 = A.L2, ts = sc.ts;
   const float th = A.th;
-  float score = 0.0f;
-  int pef = 0, pel = L2;                                  // band of the row above (row 0: every column, all 0)
+  // Both row buffers start at -FLT_MAX ("outside every band").  A row writes its band
+  // and the cell just left of it (0 in column 0, :265-268, else -FLT_MAX, :262-264); the
+  // bands only move right, so whatever the next row reads outside this row's band is
+  // either that cell or was never written since the fill: no band tests on the reads.
+  for (int k = lane; k < 2 * (L2 + 2); k += 32) sc.rowbuf[k] = -FLT_MAX;
+  __syncwarp();
+  float* prev = sc.rowbuf + (L2 + 2);
+  float* mine = sc.rowbuf;
+  uint2* trow = sc.trz;
   for (int r = 1; r <= L1; ++r) {
+    { float* t = prev; prev = mine; mine = t; }
+    trow += ts;
     const uint2 ev = A.env[r];
     const int ef = max(1, (int)ev.x), el = (int)ev.y;
-    const int bb = A.boff[r] - ef;                         // band index of (r, k) = bb + k
-    const float* prev = sc.rowbuf + ((r - 1) & 1) * (L2 + 2);
-    float* mine = sc.rowbuf + (r & 1) * (L2 + 2);
-    uint2* trow = sc.trz + (size_t)r * ts;
+    const float* pb = A.pb + (A.boff[r] - ef);             // band index of (r, k) = boff[r] - ef + k
+    const float* qb = A.qb + (A.boff[r] - ef);
     float carry = (ef == 1) ? 0.0f : -FLT_MAX;            // dp[r][ef-1]
+    if (lane == 0) mine[ef - 1] = carry;
     int chunk = 0;
     for (int k0 = ef; k0 <= el; k0 += 32, ++chunk) {
       const int k = k0 + lane;
       const bool in = k <= el;
-      float up = 0.0f, dg = 0.0f, pv = 0.0f, qv = 0.0f;
-      if (in) { pv = A.pb[bb + k]; qv = A.qb[bb + k]; }
-      if (r > 1) {
-        up = (k >= pef && k <= pel) ? prev[k] : -FLT_MAX;                          // dp[r-1][k]
-        dg = (k == 1) ? 0.0f : ((k - 1 >= pef && k - 1 <= pel) ? prev[k - 1] : -FLT_MAX);   // dp[r-1][k-1]
+      float up = 0.0f, dg = 0.0f, pv = 0.0f, qv = 0.0f;   // row 0 is 0 everywhere (:270-274)
+      if (in) {
+        pv = pb[k]; qv = qb[k];
+        if (r > 1) { up = prev[k]; dg = prev[k - 1]; }     // dp[r-1][k], dp[r-1][k-1]
       }
       const float m = __fadd_rn(__fsub_rn(__fadd_rn(dg, pv), th), qv);             // :282
       const bool c2 = m < up;                                                      // :284
@@ -382,17 +389,11 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
       const unsigned hi = __ballot_sync(0xffffffffu, in && (c3 || c2));            // codes 2 and 3
       if (lane == 0) trow[chunk] = make_uint2(lo, hi);
       if (in) mine[k] = v;
-      if (r == L1 && k == L2) score = v;
       carry = __shfl_sync(0xffffffffu, v, 31);
     }
     __syncwarp();
-    pef = ef; pel = el;
   }
-  {
-    // dp[L1][L2] sits in the lane that owned column L2 of the last row (el(L1) = L2)
-    const int ef = max(1, (int)A.env[L1].x);
-    score = __shfl_sync(0xffffffffu, score, (L2 - ef) & 31);
-  }
+  const float score = mine[L2];                            // el(L1) = L2: dp[L1][L2] was written
   const long long t1 = clock64();
   // ---- traceback (:300-312) + alignment read-out (:317-335) ------------------
   for (int i = lane; i < L1; i += 32) sc.zres[i] = DD_NOPAIR;
