@@ -1,5 +1,6 @@
-// Lifecycle + error plumbing of libdafs_cuda, and a small cache of pinned host
-// buffers so repeated calls do not pay cudaHostAlloc every time.
+// Lifecycle + error plumbing of libdafs_cuda, and small caches of pinned host
+// buffers and large device buffers so repeated calls do not pay cudaHostAlloc /
+// cudaMalloc / cudaFree every time.
 #include "common.cuh"
 
 #include <map>
@@ -71,6 +72,88 @@ void pinned_trim() {
   for (auto& kv : g_pin_free) { g_pin_cap.erase(kv.second); cudaFreeHost(kv.second); }
   g_pin_free.clear();
   g_pin_cached = 0;
+}
+
+// ---- device buffers ------------------------------------------------------------
+// cudaFree of a multi-GB workspace costs tens of milliseconds (and synchronises
+// the device); plans are created and destroyed per call by the reference-facing
+// adapters, so large device buffers are parked here instead and handed to the
+// next plan that asks for a similar size on the same device.
+namespace {
+struct DevBlock { void* p; size_t cap; int dev; };
+std::mutex g_dev_mu;
+std::vector<DevBlock> g_dev_free;
+std::map<void*, std::pair<size_t, int>> g_dev_cap;   // cached-class allocations in use
+size_t g_dev_cached = 0;
+const size_t kDevCacheMin = size_t(1) << 20;
+const size_t kDevCacheLimit = size_t(32) << 30;
+}  // namespace
+
+cudaError_t dev_malloc(void** out, size_t bytes) {
+  *out = nullptr;
+  if (bytes == 0) bytes = 1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (bytes >= kDevCacheMin) {
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    int best = -1;
+    for (int k = 0; k < (int)g_dev_free.size(); ++k) {
+      const DevBlock& b = g_dev_free[k];
+      if (b.dev == dev && b.cap >= bytes && b.cap <= bytes + bytes / 2 + kDevCacheMin &&
+          (best < 0 || b.cap < g_dev_free[best].cap)) best = k;
+    }
+    if (best >= 0) {
+      const DevBlock b = g_dev_free[best];
+      g_dev_free.erase(g_dev_free.begin() + best);
+      g_dev_cached -= b.cap;
+      g_dev_cap[b.p] = {b.cap, b.dev};
+      *out = b.p;
+      return cudaSuccess;
+    }
+  }
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e == cudaErrorMemoryAllocation) {        // give the parked buffers back and try once more
+    cudaGetLastError();
+    dev_trim();
+    e = cudaMalloc(out, bytes);
+  }
+  if (e == cudaSuccess && bytes >= kDevCacheMin) {
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    g_dev_cap[*out] = {bytes, dev};
+  }
+  return e;
+}
+
+void dev_free(void* p) {
+  if (!p) return;
+  {
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    auto it = g_dev_cap.find(p);
+    if (it != g_dev_cap.end()) {
+      const size_t cap = it->second.first;
+      const int dev = it->second.second;
+      g_dev_cap.erase(it);
+      if (g_dev_cached + cap <= kDevCacheLimit) {
+        g_dev_free.push_back({p, cap, dev});
+        g_dev_cached += cap;
+        return;
+      }
+    }
+  }
+  cudaFree(p);
+}
+
+void dev_trim() {
+  std::vector<DevBlock> blocks;
+  {
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    blocks.swap(g_dev_free);
+    g_dev_cached = 0;
+  }
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (const DevBlock& b : blocks) { cudaSetDevice(b.dev); cudaFree(b.p); }
+  cudaSetDevice(cur);
 }
 
 // FP32 issue-rate probe: 8 independent chains per thread, 4 CTAs of 256 per SM.
@@ -152,7 +235,7 @@ int dafs_cuda_init(int ngpu) {
   return DAFS_CUDA_OK;
 }
 
-void dafs_cuda_shutdown(void) { dafs::pinned_trim(); }
+void dafs_cuda_shutdown(void) { dafs::pinned_trim(); dafs::dev_trim(); }
 
 void dafs_cuda_free_batch(dafs_csr_batch* b) {
   if (!b) return;

@@ -30,6 +30,15 @@ void* pinned_alloc(size_t bytes);
 void pinned_free(void* p);
 void pinned_trim();
 
+// Device memory with a cache for large blocks (>= 1 MiB): drop-in for cudaMalloc /
+// cudaFree; freed blocks are parked and reused by size on the same device until
+// dafs_cuda_shutdown() (or an out-of-memory condition) releases them.  Kernels that
+// used a parked buffer have always been synchronised by the plan that owned it.
+cudaError_t dev_malloc(void** out, size_t bytes);
+template <class T> inline cudaError_t dev_malloc(T** out, size_t bytes) { return dev_malloc(reinterpret_cast<void**>(out), bytes); }
+void dev_free(void* p);
+void dev_trim();
+
 // Symbol classes of the ProbCons alphabet "ACGUTN" (probconsRNA/Defaults.h:28,
 // wrapper.cpp:158-170).  U and T rows of the reference's tables are identical,
 // so they share class 3; 4 = N; 5 = every other byte (1e-10 / 1e-5 emissions).

@@ -330,8 +330,8 @@ struct dafs_dd_plan {
 namespace dafs {
 
 static void free_dd_plan(dafs_dd_plan* p) {
-  cudaFree(p->d_cst); cudaFree(p->d_res); cudaFree(p->d_prob); cudaFree(p->d_order);
-  cudaFree(p->d_queue); cudaFree(p->d_ws);
+  dev_free(p->d_cst); dev_free(p->d_res); dev_free(p->d_prob); dev_free(p->d_order);
+  dev_free(p->d_queue); dev_free(p->d_ws);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->stream) cudaStreamDestroy(p->stream);
@@ -414,7 +414,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
   PLAN_TRY(cudaEventCreate(&p->ev0));
   PLAN_TRY(cudaEventCreate(&p->ev1));
-  PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
+  PLAN_TRY(dev_malloc(&p->d_queue, sizeof(int)));
   if (nprob == 0) { *out = p; return DAFS_CUDA_OK; }
 
   // per-problem setup on the host cores (independent problems)
@@ -441,10 +441,10 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     p->total_cbp += H.ncbp; p->total_entries += H.sx.h.n + H.sy.h.n + H.nb;
   }
   p->cst_bytes = cst; p->res_bytes = res;
-  PLAN_TRY(cudaMalloc(&p->d_cst, std::max<size_t>(cst, 256)));
-  PLAN_TRY(cudaMalloc(&p->d_res, std::max<size_t>(res, 256)));
-  PLAN_TRY(cudaMalloc(&p->d_prob, sizeof(DDProbRef) * nprob));
-  PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * nprob));
+  PLAN_TRY(dev_malloc(&p->d_cst, std::max<size_t>(cst, 256)));
+  PLAN_TRY(dev_malloc(&p->d_res, std::max<size_t>(res, 256)));
+  PLAN_TRY(dev_malloc(&p->d_prob, sizeof(DDProbRef) * nprob));
+  PLAN_TRY(dev_malloc(&p->d_order, sizeof(int32_t) * nprob));
   {
     // one pinned staging buffer -> one H2D copy
     char* stage = (char*)pinned_alloc(std::max<size_t>(cst, 256));
@@ -499,7 +499,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   p->ctas_per_sm = blocks;
   p->grid = std::max(1, std::min(nprob, prop.multiProcessorCount * blocks));
   p->lay.ws_stride = ws_per;
-  PLAN_TRY(cudaMalloc(&p->d_ws, ws_per * p->grid));
+  PLAN_TRY(dev_malloc(&p->d_ws, ws_per * p->grid));
   p->lay.ws = p->d_ws;
 #undef PLAN_TRY
   *out = p;
@@ -621,7 +621,7 @@ __global__ void __launch_bounds__(32) nw_single_kernel(const DDAln A, const NwSc
 
 struct DevBuf {   // one cudaMalloc, carved
   char* base = nullptr; size_t size = 0, used = 0;
-  ~DevBuf() { cudaFree(base); }
+  ~DevBuf() { dev_free(base); }
   template <class T> T* take(size_t n) { used = up16(used); T* p = reinterpret_cast<T*>(base + used); used += sizeof(T) * std::max<size_t>(n, 1); return p; }
 };
 
@@ -656,7 +656,7 @@ extern "C" int dafs_cuda_nussinov_decode(int L, float th, float w, const float* 
   const size_t ntr = (size_t)nI * nJ + 1;
   DevBuf B;
   B.size = blk.size() + 64 * 16 + 4 * (size_t)(2 * (size_t)std::max(n, 1) + 33 * (size_t)lp + 2 * L + L / 2 + 16) + (tr16 ? 2 : 1) * ntr + 64;
-  DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
+  DAFS_CUDA_TRY(dev_malloc(&B.base, B.size));
   NusScratch sc;
   char* d_blk = B.take<char>(blk.size());
   float* d_q = B.take<float>(n);
@@ -701,7 +701,7 @@ extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, con
   const int n = (int)pv.size(), ts = (bw + 31) / 32;
   DevBuf B;
   B.size = 16 * 16 + 4 * ((size_t)(L1 + 2) * (3 + 2 * ts) + 2 * (size_t)std::max(n, 1) + 2 * (L2 + 2) + 2 * (size_t)L1 + 8) + 64;
-  DAFS_CUDA_TRY(cudaMalloc(&B.base, B.size));
+  DAFS_CUDA_TRY(dev_malloc(&B.base, B.size));
   DDAln A{}; NwScratch sc{};
   int* d_boff = B.take<int>(L1 + 2);
   float* d_p = B.take<float>(n); float* d_q = B.take<float>(n);

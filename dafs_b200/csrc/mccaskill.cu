@@ -140,10 +140,10 @@ struct dafs_mccaskill_plan {
 
 namespace dafs {
 static void free_mc_plan(dafs_mccaskill_plan* p) {
-  cudaFree(p->d_seq); cudaFree(p->d_seq_off); cudaFree(p->d_seq_len); cudaFree(p->d_order); cudaFree(p->d_tab);
-  cudaFree(p->d_ws); cudaFree(p->d_row_off); cudaFree(p->d_row_ptr); cudaFree(p->d_pool_off);
-  cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_seq_nnz); cudaFree(p->d_seq_lnz);
-  cudaFree(p->d_nz_off); cudaFree(p->d_col); cudaFree(p->d_val);
+  dev_free(p->d_seq); dev_free(p->d_seq_off); dev_free(p->d_seq_len); dev_free(p->d_order); dev_free(p->d_tab);
+  dev_free(p->d_ws); dev_free(p->d_row_off); dev_free(p->d_row_ptr); dev_free(p->d_pool_off);
+  dev_free(p->d_pool_col); dev_free(p->d_pool_val); dev_free(p->d_seq_nnz); dev_free(p->d_seq_lnz);
+  dev_free(p->d_nz_off); dev_free(p->d_col); dev_free(p->d_val);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->stream) cudaStreamDestroy(p->stream);
@@ -226,22 +226,22 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   const int teams = std::max(1, std::min(std::min(nseq, slots / nc), by_mem));
   p->grid = teams * nc;
 
-  PLAN_TRY(cudaMalloc(&p->d_seq, enc.size()));
-  PLAN_TRY(cudaMalloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * nseq));
-  PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * nseq));
-  PLAN_TRY(cudaMalloc(&p->d_tab, sizeof(McTables)));
-  PLAN_TRY(cudaMalloc(&p->d_ws, per_cta * (p->grid / p->cluster)));
-  PLAN_TRY(cudaMalloc(&p->d_row_off, sizeof(int64_t) * (nseq + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_row_ptr, sizeof(int32_t) * p->total_rows));
-  PLAN_TRY(cudaMalloc(&p->d_pool_off, sizeof(int64_t) * (nseq + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_pool_col, sizeof(uint32_t) * p->pool_cap));
-  PLAN_TRY(cudaMalloc(&p->d_pool_val, sizeof(float) * p->pool_cap));
-  PLAN_TRY(cudaMalloc(&p->d_seq_nnz, sizeof(int32_t) * nseq));
-  PLAN_TRY(cudaMalloc(&p->d_seq_lnz, sizeof(double) * nseq));
-  PLAN_TRY(cudaMalloc(&p->d_nz_off, sizeof(int64_t) * (nseq + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_col, sizeof(uint32_t) * p->pool_cap));
-  PLAN_TRY(cudaMalloc(&p->d_val, sizeof(float) * p->pool_cap));
+  PLAN_TRY(dev_malloc(&p->d_seq, enc.size()));
+  PLAN_TRY(dev_malloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(dev_malloc(&p->d_seq_len, sizeof(int32_t) * nseq));
+  PLAN_TRY(dev_malloc(&p->d_order, sizeof(int32_t) * nseq));
+  PLAN_TRY(dev_malloc(&p->d_tab, sizeof(McTables)));
+  PLAN_TRY(dev_malloc(&p->d_ws, per_cta * (p->grid / p->cluster)));
+  PLAN_TRY(dev_malloc(&p->d_row_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(dev_malloc(&p->d_row_ptr, sizeof(int32_t) * p->total_rows));
+  PLAN_TRY(dev_malloc(&p->d_pool_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(dev_malloc(&p->d_pool_col, sizeof(uint32_t) * p->pool_cap));
+  PLAN_TRY(dev_malloc(&p->d_pool_val, sizeof(float) * p->pool_cap));
+  PLAN_TRY(dev_malloc(&p->d_seq_nnz, sizeof(int32_t) * nseq));
+  PLAN_TRY(dev_malloc(&p->d_seq_lnz, sizeof(double) * nseq));
+  PLAN_TRY(dev_malloc(&p->d_nz_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(dev_malloc(&p->d_col, sizeof(uint32_t) * p->pool_cap));
+  PLAN_TRY(dev_malloc(&p->d_val, sizeof(float) * p->pool_cap));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq, enc.data(), enc.size(), cudaMemcpyHostToDevice, p->stream));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq_off, seq_off.data(), sizeof(int64_t) * (nseq + 1), cudaMemcpyHostToDevice, p->stream));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq_len, len, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, p->stream));

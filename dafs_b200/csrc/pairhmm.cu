@@ -135,12 +135,12 @@ static const int kWarps = 4;     // warps per CTA
 static const int kMinBlocks = DAFS_PAIRHMM_MINB; // CTAs per SM the kernel is compiled for (4 -> <=128 regs)
 
 static void free_plan_buffers(dafs_pairhmm_plan* p) {
-  cudaFree(p->d_seq); cudaFree(p->d_seq_off); cudaFree(p->d_seq_len); cudaFree(p->d_pairs);
-  cudaFree(p->d_order); cudaFree(p->d_planes); cudaFree(p->d_bnd); cudaFree(p->d_queue);
-  cudaFree(p->d_pool_count); cudaFree(p->d_row_off); cudaFree(p->d_row_ptr);
-  cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_pair_pool_off);
-  cudaFree(p->d_pair_nnz); cudaFree(p->d_pair_total); cudaFree(p->d_nz_off);
-  cudaFree(p->d_col); cudaFree(p->d_val);
+  dev_free(p->d_seq); dev_free(p->d_seq_off); dev_free(p->d_seq_len); dev_free(p->d_pairs);
+  dev_free(p->d_order); dev_free(p->d_planes); dev_free(p->d_bnd); dev_free(p->d_queue);
+  dev_free(p->d_pool_count); dev_free(p->d_row_off); dev_free(p->d_row_ptr);
+  dev_free(p->d_pool_col); dev_free(p->d_pool_val); dev_free(p->d_pair_pool_off);
+  dev_free(p->d_pair_nnz); dev_free(p->d_pair_total); dev_free(p->d_nz_off);
+  dev_free(p->d_col); dev_free(p->d_val);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->evk0) cudaEventDestroy(p->evk0);
@@ -149,13 +149,13 @@ static void free_plan_buffers(dafs_pairhmm_plan* p) {
 }
 
 static int alloc_pool(dafs_pairhmm_plan* p, int64_t cap) {
-  cudaFree(p->d_pool_col); cudaFree(p->d_pool_val); cudaFree(p->d_col); cudaFree(p->d_val);
+  dev_free(p->d_pool_col); dev_free(p->d_pool_val); dev_free(p->d_col); dev_free(p->d_val);
   p->d_pool_col = nullptr; p->d_pool_val = nullptr; p->d_col = nullptr; p->d_val = nullptr;
   cap = std::max<int64_t>(cap, 32);
-  DAFS_CUDA_TRY(cudaMalloc(&p->d_pool_col, cap * sizeof(uint32_t)));
-  DAFS_CUDA_TRY(cudaMalloc(&p->d_pool_val, cap * sizeof(float)));
-  DAFS_CUDA_TRY(cudaMalloc(&p->d_col, cap * sizeof(uint32_t)));
-  DAFS_CUDA_TRY(cudaMalloc(&p->d_val, cap * sizeof(float)));
+  DAFS_CUDA_TRY(dev_malloc(&p->d_pool_col, cap * sizeof(uint32_t)));
+  DAFS_CUDA_TRY(dev_malloc(&p->d_pool_val, cap * sizeof(float)));
+  DAFS_CUDA_TRY(dev_malloc(&p->d_col, cap * sizeof(uint32_t)));
+  DAFS_CUDA_TRY(dev_malloc(&p->d_val, cap * sizeof(float)));
   p->pool_cap = cap;
   return DAFS_CUDA_OK;
 }
@@ -328,21 +328,21 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   if (max_l1 > 65534 || max_l2 > 65534) return bail(fail(DAFS_CUDA_EINVAL, "sequences longer than 65534 are not supported"));
   const int64_t slots = (int64_t)p->grid * kWarps;
 
-  PLAN_TRY(cudaMalloc(&p->d_seq, enc.size()));
-  PLAN_TRY(cudaMalloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_seq_len, sizeof(int32_t) * std::max(nseq, 1)));
-  PLAN_TRY(cudaMalloc(&p->d_pairs, sizeof(int2) * pairs.size()));
-  PLAN_TRY(cudaMalloc(&p->d_order, sizeof(int32_t) * order.size()));
-  PLAN_TRY(cudaMalloc(&p->d_planes, sizeof(float) * 3 * p->plane_stride * slots));
-  PLAN_TRY(cudaMalloc(&p->d_bnd, sizeof(float4) * p->bnd_stride * 2 * slots));
-  PLAN_TRY(cudaMalloc(&p->d_queue, sizeof(int)));
-  PLAN_TRY(cudaMalloc(&p->d_pool_count, sizeof(unsigned long long)));
-  PLAN_TRY(cudaMalloc(&p->d_row_off, sizeof(int64_t) * (npairs + 1)));
-  PLAN_TRY(cudaMalloc(&p->d_row_ptr, sizeof(int32_t) * std::max<int64_t>(p->total_rows, 1)));
-  PLAN_TRY(cudaMalloc(&p->d_pair_pool_off, sizeof(int64_t) * pairs.size()));
-  PLAN_TRY(cudaMalloc(&p->d_pair_nnz, sizeof(int32_t) * pairs.size()));
-  PLAN_TRY(cudaMalloc(&p->d_pair_total, sizeof(float) * pairs.size()));
-  PLAN_TRY(cudaMalloc(&p->d_nz_off, sizeof(int64_t) * (npairs + 1)));
+  PLAN_TRY(dev_malloc(&p->d_seq, enc.size()));
+  PLAN_TRY(dev_malloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
+  PLAN_TRY(dev_malloc(&p->d_seq_len, sizeof(int32_t) * std::max(nseq, 1)));
+  PLAN_TRY(dev_malloc(&p->d_pairs, sizeof(int2) * pairs.size()));
+  PLAN_TRY(dev_malloc(&p->d_order, sizeof(int32_t) * order.size()));
+  PLAN_TRY(dev_malloc(&p->d_planes, sizeof(float) * 3 * p->plane_stride * slots));
+  PLAN_TRY(dev_malloc(&p->d_bnd, sizeof(float4) * p->bnd_stride * 2 * slots));
+  PLAN_TRY(dev_malloc(&p->d_queue, sizeof(int)));
+  PLAN_TRY(dev_malloc(&p->d_pool_count, sizeof(unsigned long long)));
+  PLAN_TRY(dev_malloc(&p->d_row_off, sizeof(int64_t) * (npairs + 1)));
+  PLAN_TRY(dev_malloc(&p->d_row_ptr, sizeof(int32_t) * std::max<int64_t>(p->total_rows, 1)));
+  PLAN_TRY(dev_malloc(&p->d_pair_pool_off, sizeof(int64_t) * pairs.size()));
+  PLAN_TRY(dev_malloc(&p->d_pair_nnz, sizeof(int32_t) * pairs.size()));
+  PLAN_TRY(dev_malloc(&p->d_pair_total, sizeof(float) * pairs.size()));
+  PLAN_TRY(dev_malloc(&p->d_nz_off, sizeof(int64_t) * (npairs + 1)));
   { const int rc = alloc_pool(p, est_nnz); if (rc) return bail(rc); }
   PLAN_TRY(cudaMemcpyAsync(p->d_seq, enc.data(), enc.size(), cudaMemcpyHostToDevice, p->stream));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq_off, seq_off.data(), sizeof(int64_t) * (nseq + 1), cudaMemcpyHostToDevice, p->stream));
