@@ -85,16 +85,19 @@ __global__ void scan_nnz_kernel(const int32_t* __restrict__ nnz, int n, int64_t*
   for (int k = b; k < e; ++k) { off[k] = run; run += nnz[k]; }
 }
 
-// Pool (completion order) -> pair order.  One warp per pair.
+// Pool (completion order) -> pair order.  One warp per pair.  When the pool was
+// too small (the host sees pool_count > cap, grows it and runs again) the pairs
+// that did not fit are skipped: neither side may be touched past cap.
 __global__ void gather_csr_kernel(int npairs, const int64_t* __restrict__ pool_off,
                                   const int32_t* __restrict__ nnz, const int64_t* __restrict__ nz_off,
                                   const uint32_t* __restrict__ pcol, const float* __restrict__ pval,
-                                  uint32_t* __restrict__ col, float* __restrict__ val) {
+                                  uint32_t* __restrict__ col, float* __restrict__ val, int64_t cap) {
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   for (int p = blockIdx.x * wpb + (threadIdx.x >> 5); p < npairs; p += gridDim.x * wpb) {
     const int64_t src = pool_off[p], dst = nz_off[p];
     const int n = nnz[p];
+    if (src + n > cap || dst + n > cap) continue;
     for (int k = lane; k < n; k += 32) { col[dst + k] = pcol[src + k]; val[dst + k] = pval[src + k]; }
   }
 }
@@ -221,7 +224,7 @@ static int launch_all(dafs_pairhmm_plan* p) {
   const int gblocks = std::min(p->npairs / 8 + 1, 148 * 8);
   gather_csr_kernel<<<gblocks, 256, 0, p->stream>>>(p->npairs, p->d_pair_pool_off, p->d_pair_nnz,
                                                     p->d_nz_off, p->d_pool_col, p->d_pool_val,
-                                                    p->d_col, p->d_val);
+                                                    p->d_col, p->d_val, p->pool_cap);
   DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
   p->launched = true;
@@ -309,7 +312,7 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   p->C = choose_cols(max_l2);
   const int sw = 32 * p->C;
   const int64_t pw = (int64_t)((max_l2 + 1 + sw - 1) / sw) * sw;
-  p->plane_stride = (int64_t)(max_l1 + 1) * pw;
+  p->plane_stride = (int64_t)(max_l1 + 32) * pw;     // pipeline-order plane: L1 + 32 steps per stripe
   p->bnd_stride = max_l1 + 1;
   cudaDeviceProp prop;
   PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));

@@ -1,8 +1,9 @@
 // Backward sweep of one column stripe (ProbabilisticModel.h:197-259), fused with
-// the first half of the posterior: B_M never goes to memory.  At the top of a step
-// the lane loads its C values of the forward plane for the row it is about to
-// compute (consumed only after the ~1000 instructions of the row, so the load
-// latency is hidden), and every cell whose F_M + B_M clears a loose bound
+// the first half of the posterior: B_M never goes to memory.  The forward plane is
+// stored in pipeline order (pairhmm_kernel.cuh), so the C values a lane needs at
+// step s' are the ones it wrote at forward step L1 + 31 - s': C coalesced loads,
+// issued one whole step before they are used.  Every cell whose F_M + B_M clears a
+// loose bound
 // (candidate test, see pairhmm_pair) is appended to the pair's candidate list as
 // (row << 16 | column, F_M + B_M).  Rows of one stripe leave the pipeline from the
 // highest column to the lowest and stripes run right to left, so inside the list
@@ -25,7 +26,7 @@ struct StripeColsB {      // per-lane constants: column j+1 of each owned column
 template <int C>
 __device__ __forceinline__ void backward_stripe(
     const PairHmmSmem& sm, const uint8_t* __restrict__ s1, int L1, int L2, int stripe,
-    int nstripes, int lane, const StripeColsB<C>& sc, const float* __restrict__ planeF, int PW,
+    int nstripes, int lane, const StripeColsB<C>& sc, float* __restrict__ planeF,
     const float4* __restrict__ bnd_in, float4* __restrict__ bnd_out, float (&bcap)[3],
     float lthr, uint32_t* __restrict__ ckey, float* __restrict__ csum, int& run) {
   const float T00 = c_tab.trans[0], T01 = c_tab.trans[1], T02 = c_tab.trans[2];
@@ -33,43 +34,62 @@ __device__ __forceinline__ void backward_stripe(
   const float T20 = c_tab.trans[6], T22 = c_tab.trans[8];
   const int j0 = stripe * 32 * C + lane * C;
   const int rl = 31 - lane;                          // pipeline position
+  const bool has_right = stripe + 1 < nstripes;
+  const float* pin = stripe_plane<C>(planeF, stripe, L1) + lane;
 
   float pM[C], pX[C], pY[C];                         // B(i+1, j0+c)
 #pragma unroll
   for (int c = 0; c < C; ++c) pM[c] = pX[c] = pY[c] = DAFS_LOG_ZERO;
   float dM = DAFS_LOG_ZERO;                          // B_M(i+1, j0+C)
   float oM = DAFS_LOG_ZERO, oY = DAFS_LOG_ZERO;      // my first column, last step
-  // Row i needs the symbol of row i+1; row L1 has none (any finite class: it only
-  // meets LOG_ZERO terms).
-  int cls_next = kClsOther;
+  // Row i needs the symbol of row i+1 (row L1 has none: any finite class, it only
+  // meets LOG_ZERO terms).  Rows enter at lane 31 and move down one lane per step:
+  // lane j of the window of block b holds what lane 31 needs at step 32 b + j, the
+  // symbol of row L1 - (32 b + j) + 1 and the boundary column of the stripe to the right.
+  auto load_sym = [&](int b) -> int { const int r = L1 - (32 * b + lane) + 1; return (r >= 1 && r <= L1) ? (int)s1[r - 1] : (int)kClsOther; };
+  auto load_bnd = [&](int b) -> float4 {
+    const int r = L1 - (32 * b + lane);
+    return (has_right && r >= 0) ? bnd_in[r] : make_float4(DAFS_LOG_ZERO, 0.f, DAFS_LOG_ZERO, 0.f);
+  };
+  int win = load_sym(0), win_next = load_sym(1);
+  float4 bw = load_bnd(0), bw_next = load_bnd(1);
+  int cls1 = kClsOther;
   const int nsteps = L1 + 1 + 31;
+  // forward values of the cells of step s': written at forward step nsteps - 1 - s'
+  float fnext[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) fnext[c] = __ldcs(pin + ((int64_t)(nsteps - 1) * C + c) * 32);
   for (int step = 0; step < nsteps; ++step) {
+    const int wl = step & 31;
     float rM = __shfl_down_sync(0xffffffffu, oM, 1);
     float rY = __shfl_down_sync(0xffffffffu, oY, 1);
-    const int i = L1 - (step - rl);
-    const int cls1 = cls_next;                       // class of seq1[i+1] (1-based)
-    // next step works on row i-1 and needs the symbol of row i: s1[i-1]
-    if (i >= 1 && i <= L1) cls_next = s1[i - 1];
-    unsigned cm = 0;                                 // candidate cells of this lane's row
-    float fv[C];
-    if (i >= 0 && i <= L1) {
     {
-      const float* frow = planeF + (int64_t)i * PW + j0;
-      if constexpr (C % 2 == 0) {
-#pragma unroll
-        for (int c = 0; c < C; c += 2) {
-          const float2 v = __ldcs(reinterpret_cast<const float2*>(frow) + c / 2);
-          fv[c] = v.x; fv[c + 1] = v.y;
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < C; ++c) fv[c] = __ldcs(frow + c);
-      }
+      const int c_in = __shfl_sync(0xffffffffu, win, wl);
+      const int c_dn = __shfl_down_sync(0xffffffffu, cls1, 1);
+      cls1 = lane == 31 ? c_in : c_dn;
     }
-    if (lane == 31) {
-      if (stripe + 1 < nstripes) { const float4 b = bnd_in[i]; rM = b.x; rY = b.z; }
-      else { rM = rY = DAFS_LOG_ZERO; }
+    if (has_right) {
+      const float bM = __shfl_sync(0xffffffffu, bw.x, wl);
+      const float bY = __shfl_sync(0xffffffffu, bw.z, wl);
+      if (lane == 31) { rM = bM; rY = bY; }
+    } else if (lane == 31) {
+      rM = rY = DAFS_LOG_ZERO;
     }
+    if (wl == 31) {
+      win = win_next; bw = bw_next;
+      const int b = (step >> 5) + 2;
+      win_next = load_sym(b); bw_next = load_bnd(b);
+    }
+    float fv[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) fv[c] = fnext[c];
+    if (step + 1 < nsteps) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) fnext[c] = __ldcs(pin + ((int64_t)(nsteps - 2 - step) * C + c) * 32);
+    }
+    const int i = L1 - (step - rl);
+    unsigned cm = 0;                                 // candidate cells of this lane's row
+    if (i >= 0 && i <= L1) {
     const float insRow = sm.ins[cls1 * 32 + lane];
     const float* mrow = sm.match + cls1 * 8 * 32;
     float rightY = rY;                               // B_Y(i, j+1)

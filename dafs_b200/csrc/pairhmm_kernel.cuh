@@ -13,9 +13,16 @@
 // skewed pipeline: at step s lane t works on row s-t and hands its last column
 // to lane t+1 with warp shuffles.  There is no block-level barrier anywhere in
 // the DP.  The forward match plane F_M (the only O(L1*L2) intermediate) goes to
-// a per-warp slot in HBM; the backward sweep reads it back row by row, never
-// stores B_M, and emits the few cells that can pass the threshold as a candidate
-// list, from which the CSR rows are built (pairhmm_post.cuh).
+// a per-warp slot in HBM in PIPELINE order -- element (step, column slot c, lane),
+// i.e. what the warp produces in one step is contiguous -- so the stores and, in
+// the backward sweep, the loads are fully coalesced 128-byte lines (lane t at
+// backward step s' needs exactly what it wrote at forward step L1 + 31 - s').
+// The backward sweep fetches those lines one step ahead, never stores B_M, and
+// emits the few cells that can pass the threshold as a candidate list, from which
+// the CSR rows are built (pairhmm_post.cuh).  Row symbols and stripe-boundary
+// columns reach the pipeline through 32-step register windows (one coalesced load
+// per 32 steps, fetched a window ahead) and shuffles, so the inner loop has no
+// load whose latency it has to wait for.
 #pragma once
 #include <cstdint>
 
@@ -75,43 +82,74 @@ struct StripeCols {       // per-lane constants of the current stripe
 // ---------------------------------------------------------------------------
 // Forward sweep over one stripe.  Returns (through fend) F_k(L1, L2) when the
 // stripe contains column L2.
+// plane_row(plane, stripe, L1, C): start of the stripe's region, (L1 + 32) steps of 32*C floats
+template <int C>
+__device__ __forceinline__ float* stripe_plane(float* plane, int stripe, int L1) {
+  return plane + (int64_t)stripe * (L1 + 32) * (32 * C);
+}
+
 template <int C>
 __device__ __forceinline__ void forward_stripe(
     const PairHmmSmem& sm, const uint8_t* __restrict__ s1, int L1, int L2, int stripe,
-    int nstripes, int lane, const StripeCols<C>& sc, float* __restrict__ plane, int PW,
+    int nstripes, int lane, const StripeCols<C>& sc, float* __restrict__ plane,
     const float4* __restrict__ bnd_in, float4* __restrict__ bnd_out, float (&fend)[3]) {
   const float T00 = c_tab.trans[0], T01 = c_tab.trans[1], T02 = c_tab.trans[2];
   const float T10 = c_tab.trans[3], T11 = c_tab.trans[4];
   const float T20 = c_tab.trans[6], T22 = c_tab.trans[8];
   const int j0 = stripe * 32 * C + lane * C;
   const bool origin = (stripe == 0 && lane == 0);   // owns cells (0,0),(0,1),(1,0),(1,1)
+  const bool has_left = stripe > 0;
+  float* pout = stripe_plane<C>(plane, stripe, L1) + lane;
 
   float pM[C], pX[C], pY[C];                        // F(i-1, j0+c)
 #pragma unroll
   for (int c = 0; c < C; ++c) pM[c] = pX[c] = pY[c] = DAFS_LOG_ZERO;
   float dM = DAFS_LOG_ZERO, dX = DAFS_LOG_ZERO, dY = DAFS_LOG_ZERO;   // F(i-1, j0-1)
   float oM = DAFS_LOG_ZERO, oX = DAFS_LOG_ZERO, oY = DAFS_LOG_ZERO;   // my last column, last step
-  // Lane t works on row s-t at step s.  Row 0 has no symbol; any finite class
-  // works there because every term it feeds is LOG_ZERO-absorbed.
-  int cls_next = kClsOther;                         // class of seq1 for the next step's row
+  // Lane t works on row s-t at step s, so a row's symbol enters at lane 0 and moves
+  // up one lane per step.  Lane j of the window of block b holds the symbol lane 0
+  // needs at step 32 b + j (row 0 has no symbol; any finite class works there
+  // because every term it feeds is LOG_ZERO-absorbed); the stripe-boundary column
+  // of the stripe to the left enters the same way.
+  auto load_sym = [&](int b) -> int { const int r = 32 * b + lane; return (r >= 1 && r <= L1) ? (int)s1[r - 1] : (int)kClsOther; };
+  auto load_bnd = [&](int b) -> float4 {
+    const int r = 32 * b + lane;
+    return (has_left && r <= L1) ? bnd_in[r] : make_float4(DAFS_LOG_ZERO, DAFS_LOG_ZERO, DAFS_LOG_ZERO, 0.f);
+  };
+  int win = load_sym(0), win_next = load_sym(1);
+  float4 bw = load_bnd(0), bw_next = load_bnd(1);
+  int cls1 = kClsOther;
   const int nsteps = L1 + 1 + 31;
   for (int step = 0; step < nsteps; ++step) {
+    const int wl = step & 31;
     float lM = __shfl_up_sync(0xffffffffu, oM, 1);
     float lX = __shfl_up_sync(0xffffffffu, oX, 1);
     float lY = __shfl_up_sync(0xffffffffu, oY, 1);
-    const int i = step - lane;
-    const int cls1 = cls_next;
-    if (i + 1 >= 1 && i + 1 <= L1) cls_next = s1[i];          // prefetch symbol of row i+1
-    if (i < 0 || i > L1) continue;
-    if (lane == 0) {
-      if (stripe > 0) { const float4 b = bnd_in[i]; lM = b.x; lX = b.y; lY = b.z; }
-      else { lM = lX = lY = DAFS_LOG_ZERO; }
+    {
+      const int c_in = __shfl_sync(0xffffffffu, win, wl);
+      const int c_up = __shfl_up_sync(0xffffffffu, cls1, 1);
+      cls1 = lane == 0 ? c_in : c_up;
     }
+    if (has_left) {
+      const float bM = __shfl_sync(0xffffffffu, bw.x, wl);
+      const float bX = __shfl_sync(0xffffffffu, bw.y, wl);
+      const float bY = __shfl_sync(0xffffffffu, bw.z, wl);
+      if (lane == 0) { lM = bM; lX = bX; lY = bY; }
+    } else if (lane == 0) {
+      lM = lX = lY = DAFS_LOG_ZERO;
+    }
+    if (wl == 31) {
+      win = win_next; bw = bw_next;
+      const int b = (step >> 5) + 2;
+      win_next = load_sym(b); bw_next = load_bnd(b);
+    }
+    const int i = step - lane;
+    if (i < 0 || i > L1) continue;
     const float insRow = sm.ins[cls1 * 32 + lane];
     const float* mrow = sm.match + cls1 * 8 * 32;
     float leftM = lM, leftY = lY;
     float gM = dM, gX = dX, gY = dY;                           // diagonal F(i-1, j-1)
-    float* prow = plane + (int64_t)i * PW + j0;
+    float* prow = pout + (int64_t)step * (32 * C);
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       // ProbabilisticModel.h:151-156
@@ -130,7 +168,7 @@ __device__ __forceinline__ void forward_stripe(
       gM = pM[c]; gX = pX[c]; gY = pY[c];
       pM[c] = nM; pX[c] = nX; pY[c] = nY;
       leftM = nM; leftY = nY;
-      prow[c] = nM;
+      prow[c * 32] = nM;
     }
     dM = lM; dX = lX; dY = lY;
     oM = pM[C - 1]; oX = pX[C - 1]; oY = pY[C - 1];

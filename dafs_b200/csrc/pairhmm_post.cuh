@@ -40,7 +40,7 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
       sc.mofs[c] = cls * 32 + lane;
       sc.ins[c] = sm.ins[cls * 32 + lane];
     }
-    forward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeF, PW,
+    forward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeF,
                       (s & 1) ? bnd0 : bnd1, (s & 1) ? bnd1 : bnd0, fend);
     __syncwarp();
   }
@@ -82,7 +82,7 @@ __device__ __forceinline__ void pairhmm_pair(const PairHmmArgs& a, const PairHmm
         sc.mofs[c] = cls * 32 + lane;
         sc.ins[c] = sm.ins[cls * 32 + lane];
       }
-      backward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeF, PW,
+      backward_stripe<C>(sm, s1, L1, L2, s, nstripes, lane, sc, planeF,
                          (s & 1) ? bnd0 : bnd1, (s & 1) ? bnd1 : bnd0, bcap, lthr, ckey, csum, run);
       __syncwarp();
     }
