@@ -381,6 +381,8 @@ def run_ours(args):
         barrier()
         if it >= W:
             e2e_times.append(time.perf_counter() - t0)
+    if rank == 0:
+        print("e2e per step (ms):", " ".join("%.1f" % (x * 1e3) for x in e2e_times), file=sys.stderr)
     e2e_s = max_over_ranks(sum(e2e_times) / len(e2e_times))
     d2h_max = int(max_over_ranks(float(d2h)))
 

@@ -3,6 +3,7 @@
 // cudaMalloc / cudaFree every time.
 #include "common.cuh"
 
+#include <algorithm>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -85,7 +86,8 @@ std::mutex g_dev_mu;
 std::vector<DevBlock> g_dev_free;
 std::map<void*, std::pair<size_t, int>> g_dev_cap;   // cached-class allocations in use
 size_t g_dev_cached = 0;
-const size_t kDevCacheMin = size_t(1) << 20;
+const size_t kDevCacheMin = 256;                      // everything but the tiniest counters
+const size_t kDevSmall = size_t(1) << 20;
 const size_t kDevCacheLimit = size_t(32) << 30;
 }  // namespace
 
@@ -99,8 +101,8 @@ cudaError_t dev_malloc(void** out, size_t bytes) {
     int best = -1;
     for (int k = 0; k < (int)g_dev_free.size(); ++k) {
       const DevBlock& b = g_dev_free[k];
-      if (b.dev == dev && b.cap >= bytes && b.cap <= bytes + bytes / 2 + kDevCacheMin &&
-          (best < 0 || b.cap < g_dev_free[best].cap)) best = k;
+      const size_t most = bytes < kDevSmall ? std::max<size_t>(2 * bytes, 4096) : bytes + bytes / 2;
+      if (b.dev == dev && b.cap >= bytes && b.cap <= most && (best < 0 || b.cap < g_dev_free[best].cap)) best = k;
     }
     if (best >= 0) {
       const DevBlock b = g_dev_free[best];

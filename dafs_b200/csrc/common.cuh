@@ -30,8 +30,8 @@ void* pinned_alloc(size_t bytes);
 void pinned_free(void* p);
 void pinned_trim();
 
-// Device memory with a cache for large blocks (>= 1 MiB): drop-in for cudaMalloc /
-// cudaFree; freed blocks are parked and reused by size on the same device until
+// Device memory with a cache: drop-in for cudaMalloc / cudaFree; freed blocks are
+// parked and reused by size on the same device until
 // dafs_cuda_shutdown() (or an out-of-memory condition) releases them.  Kernels that
 // used a parked buffer have always been synchronised by the plan that owned it.
 cudaError_t dev_malloc(void** out, size_t bytes);

@@ -1,10 +1,15 @@
-"""Breakdown of one end-to-end pair-HMM call (host buffers in, host CSR out)."""
+"""Breakdown of one end-to-end pair-HMM call (host buffers in, host CSR out).
+usage: python tools/prof_e2e.py [torch]   (with "torch": inside a torch CUDA context, like bench.py)"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import dafs_b200
+if len(sys.argv) > 1:
+    import torch
+    torch.cuda.set_device(0)
+    torch.cuda.synchronize()
 seqs = dafs_b200.random_rna(256, 300, config_id=4)
 pi, pj = dafs_b200.all_pairs(256)
-for it in range(4):
+for it in range(5):
     t0 = time.perf_counter()
     p = dafs_b200.PairHmmPlan(seqs, pi, pj, 0.01)
     t1 = time.perf_counter()
