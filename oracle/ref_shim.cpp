@@ -8,7 +8,9 @@
 //   * SparseNussinov::decode  (both)         (src/nussinov.cpp:207-392)
 //   * SparseNeedlemanWunsch::initialize/decode (src/needleman_wunsch.cpp:198-422)
 //   * DAFS::solve_by_dd                      (src/dafs.cpp:1006-1295, lifted)
-// The two "lifted" pieces are cut out of dafs.cpp by the Makefile with awk at
+//   * transpose_mp, DAFS::relax_matching_probability,
+//     DAFS::relax_basepairing_probability    (src/dafs.cpp:155-167, 258-375, lifted)
+// The "lifted" pieces are cut out of dafs.cpp by the Makefile with awk at
 // build time into oracle/_ref/*.inc (dafs.cpp itself needs ViennaRNA, which is
 // not on this box) and #included below; no reference source is stored here.
 #include <algorithm>
@@ -58,6 +60,14 @@ class DAFS {
   std::unique_ptr<Align::Decoder> a_decoder_;
   std::unique_ptr<Fold::Decoder> s_decoder_;
   uint verbose_ = 0;
+  // members the consistency transformation touches (dafs.cpp:119-135)
+  std::vector<std::string> fa_;
+  std::vector<std::vector<MP>> mp_;
+  std::vector<BP> bp_;
+  VVF sim_;
+  float w_pct_a_ = 0.25f, w_pct_s_ = 0.25f;
+  void relax_matching_probability();
+  void relax_basepairing_probability();
   void output_verbose(const VU&, const VU&, const VU&, const ALN&, const ALN&) const {}
   float solve_by_dd(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z,
                     const ALN& aln1, const ALN& aln2) const;
@@ -73,6 +83,7 @@ inline void info_capture(uint t, uint v) { g_last_iters = (int)t; g_last_violate
 #undef info
 
 #include "_ref/similarity.inc"
+#include "_ref/pct.inc"
 
 static VVF to_vvf(const float* a, int r, int c) {
   VVF m(r, VF(c));
@@ -184,3 +195,83 @@ extern "C" int ref_probcons_all(int nseq, const char* const* seq, float th, long
   for (auto& t : th_) t.join();
   return 0;
 }
+
+// ---- consistency transformation: DAFS::run(), src/dafs.cpp:1796-1827 ----------
+// Inputs in the layout of dafs_csr_batch: mp = all i<j pairs row-major (rows =
+// len[i]), bp = one unit per sequence (rows = len).  Runs transpose_mp for every
+// pair, calculate_similarity_score, relax_basepairing_probability (w_pct_s != 0)
+// and relax_matching_probability (w_pct_a != 0), in the reference's order, and
+// keeps the results until the next call; ref_pct_copy() hands them out in the same
+// layout (mp: i<j pairs only).
+namespace {
+DAFS* g_pct = nullptr;
+template <class M>
+void from_csr(M& m, int rows, const int* row_ptr, const unsigned* col, const float* val) {
+  m.assign(rows, typename M::value_type());
+  for (int r = 0; r < rows; ++r)
+    for (int k = row_ptr[r]; k < row_ptr[r + 1]; ++k) m[r].push_back(std::make_pair((uint)col[k], val[k]));
+}
+}  // namespace
+
+extern "C" {
+
+void ref_pct_run(int n, const int* len, const long long* mp_row_off, const int* mp_row_ptr, const long long* mp_nz_off,
+                 const unsigned* mp_col, const float* mp_val, const long long* bp_row_off, const int* bp_row_ptr,
+                 const long long* bp_nz_off, const unsigned* bp_col, const float* bp_val, float w_pct_a,
+                 float w_pct_s, float* sim_out, long long* sizes /* mp rows, mp nnz, bp rows, bp nnz */) {
+  delete g_pct;
+  g_pct = new DAFS();
+  DAFS& d = *g_pct;
+  const uint N = (uint)n;
+  d.w_pct_a_ = w_pct_a; d.w_pct_s_ = w_pct_s;
+  d.fa_.resize(N);
+  for (uint i = 0; i < N; ++i) d.fa_[i] = std::string((size_t)len[i], 'N');
+  d.bp_.resize(N);
+  for (uint i = 0; i < N; ++i) from_csr(d.bp_[i], len[i], bp_row_ptr + bp_row_off[i], bp_col + bp_nz_off[i], bp_val + bp_nz_off[i]);
+  d.mp_.assign(N, std::vector<MP>(N));
+  long long u = 0;
+  for (uint i = 0; i < N; ++i) {
+    d.mp_[i][i].resize(len[i]);                                   // align.cpp:41-44
+    for (int x = 0; x < len[i]; ++x) d.mp_[i][i][x].push_back(std::make_pair((uint)x, 1.0f));
+    for (uint j = i + 1; j < N; ++j, ++u) {
+      from_csr(d.mp_[i][j], len[i], mp_row_ptr + mp_row_off[u], mp_col + mp_nz_off[u], mp_val + mp_nz_off[u]);
+      transpose_mp(d.mp_[i][j], d.mp_[j][i], len[i], len[j]);   // dafs.cpp:1797-1799
+    }
+  }
+  d.sim_.assign(N, VF(N));                                         // dafs.cpp:1812-1819
+  for (uint i = 0; i < N; ++i) {
+    d.sim_[i][i] = 1.0;
+    for (uint j = i + 1; j < N; ++j)
+      d.sim_[i][j] = d.sim_[j][i] = calculate_similarity_score(d.mp_[i][j], len[i], len[j]);
+  }
+  if (sim_out) for (uint i = 0; i < N; ++i) for (uint j = 0; j < N; ++j) sim_out[i * N + j] = d.sim_[i][j];
+  if (w_pct_s != 0.0) d.relax_basepairing_probability();           // dafs.cpp:1822-1823
+  if (w_pct_a != 0.0) d.relax_matching_probability();              // dafs.cpp:1826-1827
+  long long mr = 0, mn = 0, br = 0, bn = 0;
+  for (uint i = 0; i < N; ++i) {
+    br += len[i] + 1;
+    for (auto& r : d.bp_[i]) bn += (long long)r.size();
+    for (uint j = i + 1; j < N; ++j) { mr += len[i] + 1; for (auto& r : d.mp_[i][j]) mn += (long long)r.size(); }
+  }
+  sizes[0] = mr; sizes[1] = mn; sizes[2] = br; sizes[3] = bn;
+}
+
+void ref_pct_copy(int* mp_row_ptr, unsigned* mp_col, float* mp_val, int* bp_row_ptr, unsigned* bp_col, float* bp_val) {
+  DAFS& d = *g_pct;
+  const uint N = (uint)d.fa_.size();
+  long long rp = 0, nz = 0;
+  for (uint i = 0; i < N; ++i)
+    for (uint j = i + 1; j < N; ++j) {
+      int run = 0;
+      mp_row_ptr[rp++] = 0;
+      for (auto& r : d.mp_[i][j]) { for (auto& e : r) { mp_col[nz] = e.first; mp_val[nz] = e.second; ++nz; ++run; } mp_row_ptr[rp++] = run; }
+    }
+  rp = 0; nz = 0;
+  for (uint i = 0; i < N; ++i) {
+    int run = 0;
+    bp_row_ptr[rp++] = 0;
+    for (auto& r : d.bp_[i]) { for (auto& e : r) { bp_col[nz] = e.first; bp_val[nz] = e.second; ++nz; ++run; } bp_row_ptr[rp++] = run; }
+  }
+}
+
+}  // extern "C"

@@ -237,3 +237,61 @@ def oracle_mccaskill_csr(seq, th=0.01):
     rp = np.zeros(n + 1, np.int32); col = np.zeros(n * n // 2 + 1, np.uint32); val = np.zeros(n * n // 2 + 1, np.float32)
     nnz = _mc().oracle_mccaskill_csr(seq, n, th, rp.ctypes.data, col.ctypes.data, val.ctypes.data)
     return rp, col[:nnz].copy(), val[:nnz].copy()
+
+
+# ---- consistency transformation (PCT) ---------------------------------------------
+class FlatCsr:
+    """A batch of row-sparse matrices in the layout of dafs_csr_batch."""
+
+    def __init__(self, units):
+        """units: list of (row_ptr[rows+1], col, val) per unit."""
+        self.n_units = len(units)
+        self.row_off = np.zeros(len(units) + 1, np.int64)
+        self.nz_off = np.zeros(len(units) + 1, np.int64)
+        for u, (rp, col, val) in enumerate(units):
+            self.row_off[u + 1] = self.row_off[u] + len(rp)
+            self.nz_off[u + 1] = self.nz_off[u] + len(col)
+        self.row_ptr = np.concatenate([np.asarray(u[0], np.int32) for u in units]) if units else np.zeros(0, np.int32)
+        self.col = np.ascontiguousarray(np.concatenate([np.asarray(u[1], np.uint32) for u in units] + [np.zeros(0, np.uint32)]))
+        self.val = np.ascontiguousarray(np.concatenate([np.asarray(u[2], np.float32) for u in units] + [np.zeros(0, np.float32)]))
+        self.row_ptr = np.ascontiguousarray(self.row_ptr)
+
+    def unit(self, u):
+        r0, r1 = int(self.row_off[u]), int(self.row_off[u + 1])
+        z0, z1 = int(self.nz_off[u]), int(self.nz_off[u + 1])
+        return self.row_ptr[r0:r1], self.col[z0:z1], self.val[z0:z1]
+
+
+def pct_inputs(seqs, th_a=0.01, th_bp=0.01):
+    """(lens, mp over all i<j pairs, bp per sequence) from the CPU restatements."""
+    n = len(seqs)
+    mp = [oracle_pair_csr(seqs[i], seqs[j], th_a)[:3] for i in range(n) for j in range(i + 1, n)]
+    bp = [oracle_mccaskill_csr(s, th_bp) for s in seqs]
+    return np.array([len(s) for s in seqs], np.int32), FlatCsr(mp), FlatCsr(bp)
+
+
+def _pct(lib, prefix, lens, mp, bp, w_pct_a, w_pct_s):
+    run, copy = getattr(lib, prefix + "_pct_run"), getattr(lib, prefix + "_pct_copy")
+    run.restype = None; copy.restype = None
+    run.argtypes = [C.c_int, C.c_void_p] + [C.c_void_p] * 10 + [C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    copy.argtypes = [C.c_void_p] * 6
+    n = len(lens)
+    lens = np.ascontiguousarray(lens, np.int32)
+    sim = np.zeros((n, n), np.float32)
+    sizes = np.zeros(4, np.int64)
+    run(n, lens.ctypes.data, mp.row_off.ctypes.data, mp.row_ptr.ctypes.data, mp.nz_off.ctypes.data, mp.col.ctypes.data,
+        mp.val.ctypes.data, bp.row_off.ctypes.data, bp.row_ptr.ctypes.data, bp.nz_off.ctypes.data, bp.col.ctypes.data,
+        bp.val.ctypes.data, w_pct_a, w_pct_s, sim.ctypes.data, sizes.ctypes.data)
+    mrp = np.zeros(sizes[0], np.int32); mcol = np.zeros(max(sizes[1], 1), np.uint32); mval = np.zeros(max(sizes[1], 1), np.float32)
+    brp = np.zeros(sizes[2], np.int32); bcol = np.zeros(max(sizes[3], 1), np.uint32); bval = np.zeros(max(sizes[3], 1), np.float32)
+    copy(mrp.ctypes.data, mcol.ctypes.data, mval.ctypes.data, brp.ctypes.data, bcol.ctypes.data, bval.ctypes.data)
+    return {"sim": sim, "mp_row_ptr": mrp, "mp_col": mcol[:sizes[1]], "mp_val": mval[:sizes[1]],
+            "bp_row_ptr": brp, "bp_col": bcol[:sizes[3]], "bp_val": bval[:sizes[3]]}
+
+
+def oracle_pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
+    return _pct(oracle(), "oracle", lens, mp, bp, w_pct_a, w_pct_s)
+
+
+def ref_pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
+    return _pct(ref(), "ref", lens, mp, bp, w_pct_a, w_pct_s)
