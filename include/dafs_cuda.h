@@ -230,6 +230,30 @@ int dafs_cuda_nussinov_decode(int L, float th, float w, const float* p, const fl
 int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, const float* q, uint32_t* al,
                         float* score);
 
+/* ---- (4) probabilistic consistency transformation --------------------------
+ * The stage DAFS::run() executes between the posteriors and the guide tree
+ * (src/dafs.cpp:1796-1827): transpose_mp for every pair (:155-167, :1797-1799),
+ * calculate_similarity_score for every pair (:713-764, :1812-1819),
+ * relax_basepairing_probability when w_pct_s != 0 (:326-375, option -q) and
+ * relax_matching_probability when w_pct_a != 0 (:258-324, option -p), in that
+ * order; the defaults are 0.25 / 0.25 (:1622, :1631).  Bit-exact with the
+ * reference: every cell is accumulated in the reference's (z, k) / (y, k, l)
+ * order with unfused FP32 arithmetic and its mixed float / double weights.
+ *   mp      all i<j pairs, row-major, rows = len[i]  (what dafs_cuda_pairhmm_all returns)
+ *   bp      one unit per sequence, rows = len        (what dafs_cuda_mccaskill_all returns)
+ *   sim     out, [nseq*nseq] row-major, or NULL
+ *   mp_out  relaxed matching probabilities, same layout as mp (the reference's
+ *           mp_[x][y] for x < y; mp_[y][x] is its transpose, mp_[x][x] the identity)
+ *   bp_out  relaxed base-pairing probabilities, same layout as bp
+ * With a weight of 0 the corresponding output is a copy of the input.           */
+int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
+                  float w_pct_a, float w_pct_s, float* sim, dafs_csr_batch* mp_out,
+                  dafs_csr_batch* bp_out);
+
+/* Device time of the kernels of the last dafs_cuda_pct call on this thread, in ms:
+ * {transpose, similarity, relax_bp, relax_mp, total incl. H2D/D2H}.              */
+void dafs_cuda_pct_last_ms(float out5[5]);
+
 #ifdef __cplusplus
 }
 #endif
