@@ -1,6 +1,7 @@
 // Host side of dafs_cuda_pct: the consistency transformation of DAFS::run()
 // (src/dafs.cpp:1796-1827) on the device.  Kernels: pct_kernel.cuh.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -159,7 +160,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   if (bp->n_units != n) return fail(DAFS_CUDA_EINVAL, "bp holds %lld units, %d sequences expected", (long long)bp->n_units, n);
   int maxL = 0;
   for (int i = 0; i < n; ++i) {
-    if (len[i] < 1) return fail(DAFS_CUDA_EINVAL, "len[%d] = %d", i, len[i]);
+    if (len[i] < 1 || len[i] > 65535) return fail(DAFS_CUDA_EINVAL, "len[%d] = %d (1 .. 65535)", i, len[i]);
     maxL = std::max(maxL, len[i]);
   }
   // geometry on the host: pair list, row-block offsets of U / T / outputs
@@ -209,13 +210,18 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   DAFS_CUDA_TRY(B.get(&d_b_row_off, n + 1));
   DAFS_CUDA_TRY(B.get(&d_b_nz_off, n + 1));
   DAFS_CUDA_TRY(B.get(&d_orow_bp, n + 1));
-  DAFS_CUDA_TRY(B.get(&d_u_row_ptr, u_row_off[npairs]));
-  DAFS_CUDA_TRY(B.get(&d_u_col, mp_nnz));
-  DAFS_CUDA_TRY(B.get(&d_u_val, mp_nnz));
-  DAFS_CUDA_TRY(B.get(&A.t_row_ptr, t_row_off[npairs]));
-  DAFS_CUDA_TRY(B.get(&d_cursor, t_row_off[npairs]));
-  DAFS_CUDA_TRY(B.get(&A.t_col, mp_nnz));
-  DAFS_CUDA_TRY(B.get(&A.t_val, mp_nnz));
+  // U and T share one set of arrays: [U | T]
+  const int64_t RU = u_row_off[npairs], RT = t_row_off[npairs];
+  DAFS_CUDA_TRY(B.get(&d_u_row_ptr, RU + RT));
+  DAFS_CUDA_TRY(B.get(&d_u_col, 2 * mp_nnz));
+  DAFS_CUDA_TRY(B.get(&d_u_val, 2 * mp_nnz));
+  A.t_row_ptr = d_u_row_ptr + RU; A.t_col = d_u_col + mp_nnz; A.t_val = d_u_val + mp_nnz;
+  A.rp_all = d_u_row_ptr; A.col_all = d_u_col; A.val_all = d_u_val; A.ru = RU; A.nnz = mp_nnz;
+  DAFS_CUDA_TRY(B.get(&d_cursor, RT));
+  DAFS_CUDA_TRY(B.get(&A.desc, (size_t)n * n));
+  DAFS_CUDA_TRY(B.get(&A.descT, (size_t)n * n));
+  DAFS_CUDA_TRY(B.get(&A.head, RU + RT + b_row_off[n]));
+  A.rt = RT;
   DAFS_CUDA_TRY(B.get(&d_b_row_ptr, b_row_off[n]));
   DAFS_CUDA_TRY(B.get(&d_b_col, bp_nnz));
   DAFS_CUDA_TRY(B.get(&d_b_val, bp_nnz));
@@ -257,6 +263,8 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
 
   // K6, K7
   DAFS_CUDA_TRY(cudaEventRecord(G.ev[1], st));
+  pct_desc_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(A);
+  pct_identity_heads_kernel<<<n, 128, 0, st>>>(A);
   if (npairs) pct_transpose_kernel<<<grid_for(npairs, 4), 128, 0, st>>>(A, npairs, d_pairs, d_cursor);
   DAFS_CUDA_TRY(cudaEventRecord(G.ev[2], st));
   {
@@ -279,7 +287,6 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   const size_t smem = (size_t)wpb * accW * sizeof(float);
   if (smem > (size_t(227) << 10)) return fail(DAFS_CUDA_EINVAL, "sequence of length %d is too long for the consistency kernels", maxL);
   if (smem > (48 << 10)) {
-    DAFS_CUDA_TRY(cudaFuncSetAttribute(pct_relax_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DAFS_CUDA_TRY(cudaFuncSetAttribute(pct_relax_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
 
@@ -322,6 +329,33 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     DAFS_CUDA_TRY(B.get(&d_w, (size_t)npairs * n));
     DAFS_CUDA_TRY(B.get(&d_sw, npairs));
     pct_weights_mp_kernel<<<(int)((npairs + 127) / 128), 128, 0, st>>>(n, npairs, d_pairs, A.sim, w_pct_a, d_w, d_sw);
+    // tasks = (pair, block of 32 rows) in tiles of 16 x 16 pairs: a tile reads mp_[x][.] of
+    // 16 x's and mp_[.][y] of 16 y's, which stay in L2 while its tasks run
+    std::vector<int2> tasks;
+    tasks.reserve((size_t)npairs * ((maxL + 31) / 32));
+    const int TILE = 16;
+    for (int x0 = 0; x0 < n; x0 += TILE)
+      for (int y0 = x0; y0 < n; y0 += TILE)
+        for (int x = x0; x < std::min(n, x0 + TILE); ++x)
+          for (int rb = 0; rb < (len[x] + 31) / 32; ++rb)     // the warps of a CTA share (x, rows)
+            for (int y = std::max(y0, x + 1); y < std::min(n, y0 + TILE); ++y)
+              tasks.push_back(make_int2((int)((int64_t)x * n - (int64_t)x * (x + 1) / 2 + (y - x - 1)), rb));
+    const int64_t ntasks = (int64_t)tasks.size();
+    int2* d_tasks = nullptr;
+    DAFS_CUDA_TRY(B.get(&d_tasks, ntasks));
+    DAFS_CUDA_TRY(h2d(d_tasks, tasks.data(), sizeof(int2) * ntasks));
+    int mp_grid = 0;
+    {
+      int dev = 0, sms = 148, per_sm = 1;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_kernel, 256, 0));
+      mp_grid = (int)std::max<int64_t>(1, std::min<int64_t>((ntasks + 7) / 8, (int64_t)sms * std::max(per_sm, 1)));
+    }
+    if (const char* g = getenv("DAFS_PCT_MP_GRID")) mp_grid = std::max(1, atoi(g));
+    while (mp_grid > 1 && (size_t)mp_grid * 8 * maxL * 32 * sizeof(float) > (size_t(2) << 30)) mp_grid /= 2;
+    float* d_acc = nullptr;
+    DAFS_CUDA_TRY(B.get(&d_acc, (size_t)mp_grid * 8 * maxL * 32));
     Pool P;
     const int64_t rows = orow_mp[npairs];
     if ((rc = P.alloc(B, rows, std::max<int64_t>(2 * mp_nnz, 1024)))) { dafs_cuda_free_batch(bp_out); return rc; }
@@ -329,7 +363,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     for (int attempt = 0; attempt < 2; ++attempt) {
       cudaError_t e = cudaMemsetAsync(P.O.pool_count, 0, sizeof(unsigned long long), st);
       if (e == cudaSuccess) {
-        pct_relax_mp_kernel<<<grid_for(rows, wpb), 32 * wpb, smem, st>>>(A, npairs, d_pairs, d_orow_mp, d_w, d_sw, P.O, accW);
+        pct_relax_mp_kernel<<<mp_grid, 256, 0, st>>>(A, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, d_acc, maxL);
         e = cudaGetLastError();
       }
       if (e == cudaSuccess) e = cudaMemcpyAsync(&need, P.O.pool_count, sizeof need, cudaMemcpyDeviceToHost, st);

@@ -23,6 +23,9 @@
 
 namespace dafs {
 
+#ifndef PCT_MP_MINB
+#define PCT_MP_MINB 3        // resident CTAs of 256 threads per SM for K9 (register cap 80)
+#endif
 #define PCT_CUTOFF 0.01   // src/dafs.cpp:47, a double constant
 
 struct PctMat {             // one mp_[a][b]: rows of a, columns of b
@@ -31,15 +34,29 @@ struct PctMat {             // one mp_[a][b]: rows of a, columns of b
   const float* val;
 };
 
+// Where mp_[a][b] lives: offsets into the combined arrays (U first, then T).  nz < 0 =
+// identity: no CSR, but rp still addresses a block of heads {1, r, 1.0f} (after U and T).
+struct PctDesc { int64_t rp, nz; };
+
 struct PctArgs {
   int n;                    // sequences
   const int* len;           // [n]
-  // mp: U = pairs a < b in row-major order, T = their transposes
+  // mp: U = pairs a < b in row-major order, T = their transposes; both in one set of
+  // arrays (rp_all = [U row_ptr blocks | T row_ptr blocks], col_all / val_all likewise)
   const int64_t* u_row_off; // [npairs+1] into u_row_ptr (len[a]+1 per pair)
   const int64_t* t_row_off; // [npairs+1] into t_row_ptr (len[b]+1 per pair)
   const int64_t* nz_off;    // [npairs+1] entries of pair u in both U and T
   const int* u_row_ptr; const uint32_t* u_col; const float* u_val;
   int* t_row_ptr; uint32_t* t_col; float* t_val;
+  const int* rp_all; const uint32_t* col_all; const float* val_all;
+  int64_t ru, nnz;          // sizes of the U parts of rp_all / col_all
+  PctDesc* desc;            // [n*n]  desc[a*n+b]  = mp_[a][b]
+  PctDesc* descT;           // [n*n]  descT[b*n+a] = mp_[a][b]
+  // per row of rp_all, then per row of the n identity blocks (len+1 each, at ru + rt +
+  // b_row_off[a]): {entries, k0 | k1 << 16, p0, p1}.  A missing k is the number of columns,
+  // which in the matrix that k indexes next is the spare last row: its head is empty.
+  uint4* head;
+  int64_t rt;
   // bp: one CSR per sequence
   const int64_t* b_row_off; // [n+1] (len+1 per sequence)
   const int64_t* b_nz_off;  // [n+1]
@@ -51,16 +68,23 @@ __device__ __forceinline__ int64_t pct_pair_index(int n, int a, int b) {   // a 
   return (int64_t)a * n - (int64_t)a * (a + 1) / 2 + (b - a - 1);
 }
 
+__global__ void pct_desc_kernel(PctArgs A) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= A.n * A.n) return;
+  const int a = t / A.n, b = t % A.n;
+  PctDesc d;
+  if (a == b) { d.rp = A.ru + A.rt + A.b_row_off[a]; d.nz = -1; }
+  else if (a < b) { const int64_t u = pct_pair_index(A.n, a, b); d.rp = A.u_row_off[u]; d.nz = A.nz_off[u]; }
+  else { const int64_t u = pct_pair_index(A.n, b, a); d.rp = A.ru + A.t_row_off[u]; d.nz = A.nnz + A.nz_off[u]; }
+  A.desc[(int64_t)a * A.n + b] = d;
+  A.descT[(int64_t)b * A.n + a] = d;
+}
+
 __device__ __forceinline__ PctMat pct_mat(const PctArgs& A, int a, int b) {
+  const PctDesc d = A.desc[(int64_t)a * A.n + b];
   PctMat m;
-  if (a == b) { m.row_ptr = nullptr; m.col = nullptr; m.val = nullptr; return m; }
-  if (a < b) {
-    const int64_t u = pct_pair_index(A.n, a, b);
-    m.row_ptr = A.u_row_ptr + A.u_row_off[u]; m.col = A.u_col + A.nz_off[u]; m.val = A.u_val + A.nz_off[u];
-  } else {
-    const int64_t u = pct_pair_index(A.n, b, a);
-    m.row_ptr = A.t_row_ptr + A.t_row_off[u]; m.col = A.t_col + A.nz_off[u]; m.val = A.t_val + A.nz_off[u];
-  }
+  if (d.nz < 0) { m.row_ptr = nullptr; m.col = nullptr; m.val = nullptr; return m; }
+  m.row_ptr = A.rp_all + d.rp; m.col = A.col_all + d.nz; m.val = A.val_all + d.nz;
   return m;
 }
 
@@ -114,7 +138,34 @@ __global__ void __launch_bounds__(128) pct_transpose_kernel(PctArgs A, int64_t n
       }
       __syncwarp();
     }
+    // row heads of U and T: entry count and the first two entries of every row
+    uint4* hu = A.head + A.u_row_off[u];
+    for (int i = lane; i <= L1; i += 32) {
+      const int b = rp[min(i, L1 - 1)], c = i < L1 ? rp[i + 1] - b : 0;
+      uint4 h = make_uint4((unsigned)c, (unsigned)L2 | ((unsigned)L2 << 16), 0u, 0u);
+      if (c > 0) { h.y = col[b] | ((unsigned)L2 << 16); h.z = __float_as_uint(val[b]); }
+      if (c > 1) { h.y = col[b] | (col[b + 1] << 16); h.w = __float_as_uint(val[b + 1]); }
+      hu[i] = h;
+    }
+    uint4* ht = A.head + A.ru + A.t_row_off[u];
+    for (int j = lane; j <= L2; j += 32) {
+      const int b = __ldcg(trp + min(j, L2 - 1)), c = j < L2 ? __ldcg(trp + j + 1) - b : 0;
+      uint4 h = make_uint4((unsigned)c, (unsigned)L1 | ((unsigned)L1 << 16), 0u, 0u);
+      if (c > 0) { h.y = __ldcg(tcol + b) | ((unsigned)L1 << 16); h.z = __float_as_uint(__ldcg(tval + b)); }
+      if (c > 1) { h.y = __ldcg(tcol + b) | (__ldcg(tcol + b + 1) << 16); h.w = __float_as_uint(__ldcg(tval + b + 1)); }
+      ht[j] = h;
+    }
   }
+}
+
+// heads of the identity matrices mp_[a][a]: row r = {1, r, 1.0f}, spare row empty
+__global__ void pct_identity_heads_kernel(PctArgs A) {
+  const int a = blockIdx.x;
+  const int L = A.len[a];
+  uint4* h = A.head + A.ru + A.rt + A.b_row_off[a];
+  for (int r = threadIdx.x; r <= L; r += blockDim.x)
+    h[r] = r < L ? make_uint4(1u, (unsigned)r | ((unsigned)L << 16), 0x3f800000u, 0u)
+                 : make_uint4(0u, (unsigned)L | ((unsigned)L << 16), 0u, 0u);
 }
 
 // ---- K7: calculate_similarity_score ------------------------------------------------
@@ -304,74 +355,141 @@ __device__ __forceinline__ void pct_emit_row(const PctOut& O, int64_t row, float
 }
 
 // ---- K9: relax_matching_probability ---------------------------------------------------
-// One warp per row i of one pair (x < y).  For z = 0..n-1 in order: the k's of row i
-// of mp_[x][z] in ascending order, for each the row k of mp_[z][y]; lanes take the
-// flattened (k, j) products, which are loaded in two rounds (all k's of the row at
-// once, then all their j's) and added group by group in k order -- within a group the
-// columns j are distinct.  Accumulator: one float per column of y in shared memory.
-__global__ void __launch_bounds__(128) pct_relax_mp_kernel(PctArgs A, int64_t npairs, const int2* __restrict__ pairs,
+// One THREAD per row i of one pair (x < y); a warp holds 32 consecutive rows of the same
+// pair (task = (pair, block of 32 rows), listed by the host in tiles of pairs so that
+// the matrices a tile reads stay in L2).  For z = 0..n-1 in order: the k's of row i of
+// mp_[x][z] in ascending order, for each the row k of mp_[z][y],
+// acc[j] += (p_ik * p_jk) * w -- the reference's order for every cell.
+// Rows are read through their 16-byte heads (count + first two entries), so a z step is
+// a chain of two loads; the chain is software-pipelined over z (head of row i for z+2,
+// heads of its k's for z+1, arithmetic for z).  Rows with more than two entries take
+// the CSR for the rest.
+// The accumulator row of a thread lives in a per-warp scratch of W x 32 floats in
+// global memory, skewed so that the 32 rows of a warp meet on one 128-byte line when
+// they follow the same diagonal (cell (lane l, column j) at ((j - l) mod W) * 32 + l);
+// it is zeroed lazily over the range of columns the row has touched, which is also the
+// range the read-out scans.
+struct PctAcc {
+  float* a; int W, lane, jmin, jw;                          // touched columns: [jmin, jmin + jw)
+  __device__ __forceinline__ int idx(int j) const { int c = j - lane; if (c < 0) c += W; return c * 32 + lane; }
+  __device__ __forceinline__ void add(int j, float t);
+};
+
+// first touch of a row, or a column outside the touched range: zero the new cells.
+// Out of line and by value (the hot loop keeps PctAcc in registers); returns (jmin, jw).
+__device__ __noinline__ int2 pct_acc_extend(float* a, int W, int lane, int jmin, int jw, int j) {
+  PctAcc t; t.a = a; t.W = W; t.lane = lane;
+  if (jw == 0) { a[t.idx(j)] = 0.0f; return make_int2(j, 1); }
+  if (j < jmin) { for (int q = j; q < jmin; ++q) a[t.idx(q)] = 0.0f; return make_int2(j, jw + jmin - j); }
+  for (int q = jmin + jw; q <= j; ++q) a[t.idx(q)] = 0.0f;
+  return make_int2(jmin, j - jmin + 1);
+}
+
+__device__ __forceinline__ void PctAcc::add(int j, float t) {
+  if ((unsigned)(j - jmin) >= (unsigned)jw) { const int2 r = pct_acc_extend(a, W, lane, jmin, jw, j); jmin = r.x; jw = r.y; }
+  const int k = idx(j);
+  a[k] = __fadd_rn(a[k], t);                                // 0 + t = t on the first touch
+}
+
+struct PctPtrs { const int* rp; const uint32_t* col; const float* val; const uint4* head; };
+
+// entries 3.. of row k of mp_[z][y] (rare: sharp posteriors keep one or two per row)
+__device__ __noinline__ int2 pct_mp_row_tail(PctPtrs P, PctAcc acc, int64_t rp, int64_t nz, int k, float p_ik, int cnt, float wz) {
+  const int bs = P.rp[rp + k];
+  for (int c = bs + 2; c < bs + cnt; ++c)
+    acc.add((int)P.col[nz + c], __fmul_rn(__fmul_rn(p_ik, P.val[nz + c]), wz));
+  return make_int2(acc.jmin, acc.jw);
+}
+
+// all products of one k: row k of mp_[z][y] through its head hb
+__device__ __forceinline__ void pct_mp_row(const PctPtrs& P, PctAcc& acc, const PctDesc& dB, int k, float p_ik,
+                                           const uint4& hb, float wz) {
+  if (hb.x >= 1u) acc.add((int)(hb.y & 0xffffu), __fmul_rn(__fmul_rn(p_ik, __uint_as_float(hb.z)), wz));
+  if (hb.x >= 2u) acc.add((int)(hb.y >> 16), __fmul_rn(__fmul_rn(p_ik, __uint_as_float(hb.w)), wz));
+  if (hb.x > 2u) { const int2 r = pct_mp_row_tail(P, acc, dB.rp, dB.nz, k, p_ik, (int)hb.x, wz); acc.jmin = r.x; acc.jw = r.y; }
+}
+
+// entries 3.. of row i of mp_[x][z]
+__device__ __noinline__ int2 pct_mp_tail(PctPtrs P, PctAcc acc, int64_t arp, int64_t anz, int64_t brp, int64_t bnz, int i,
+                                         int cnt, float wz) {
+  const int s = P.rp[arp + i];
+  PctDesc db; db.rp = brp; db.nz = bnz;
+  for (int ke = s + 2; ke < s + cnt; ++ke) {
+    const int k = (int)P.col[anz + ke];
+    const uint4 hb = P.head[brp + k];
+    pct_mp_row(P, acc, db, k, P.val[anz + ke], hb, wz);
+  }
+  return make_int2(acc.jmin, acc.jw);
+}
+
+__global__ void __launch_bounds__(256, PCT_MP_MINB) pct_relax_mp_kernel(PctArgs A, int64_t ntasks, const int2* __restrict__ tasks,
+                                                           const int2* __restrict__ pairs,
                                                            const int64_t* __restrict__ out_row_off,
                                                            const float* __restrict__ w, const float* __restrict__ sum_w,
-                                                           PctOut O, int accW) {
-  extern __shared__ float pct_smem[];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  float* acc = pct_smem + (size_t)wib * accW;
-  const int64_t total_rows = out_row_off[npairs];
-  const int64_t wid = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+                                                           PctOut O, float* __restrict__ scratch, int W) {
+  const int lane = threadIdx.x & 31;
+  const int64_t wid = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nw = (int64_t)gridDim.x * (blockDim.x >> 5);
-  int64_t u = 0;
-  for (int64_t row = wid; row < total_rows; row += nw) {
-    // unit of this row: rows of pair u are [out_row_off[u], out_row_off[u+1]) (len[x] rows each, no +1)
-    u = pct_find_unit(out_row_off, npairs, row, u);
-    const int i = (int)(row - out_row_off[u]);
+  const int n = A.n;
+  PctAcc acc;
+  acc.a = scratch + wid * (int64_t)W * 32; acc.W = W; acc.lane = lane;
+  const uint4* __restrict__ head = A.head;
+  PctPtrs P; P.rp = A.rp_all; P.col = A.col_all; P.val = A.val_all; P.head = A.head;
+  for (int64_t task = wid; task < ntasks; task += nw) {
+    const int2 tk = tasks[task];
+    const int64_t u = tk.x;
     const int x = pairs[u].x, y = pairs[u].y;
-    const int L2 = A.len[y];
-    for (int j = lane; j < L2; j += 32) acc[j] = 0.0f;
-    __syncwarp();
-    const float* wu = w + u * A.n;
-    for (int z = 0; z < A.n; ++z) {
+    const int L1 = A.len[x];
+    const int i = tk.y * 32 + lane;
+    const bool live = i < L1;
+    const int ii = live ? i : L1;                            // the spare row: empty head
+    acc.jmin = 0; acc.jw = 0;
+    const float* wu = w + u * n;
+    const PctDesc* dA = A.desc + (int64_t)x * n;             // mp_[x][z]
+    const PctDesc* dB = A.descT + (int64_t)y * n;            // mp_[z][y]
+    // pipeline: ha2 = head of row i for z+2, ha1 for z+1 (heads of its k's in flight), ha0 / hb0x for z
+    uint4 ha0 = __ldg(head + dA[0].rp + ii);
+    uint4 ha1 = __ldg(head + dA[n > 1 ? 1 : 0].rp + ii);
+    PctDesc db0 = dB[0];
+    uint4 hb00 = __ldg(head + db0.rp + (ha0.y & 0xffffu));
+    uint4 hb01 = __ldg(head + db0.rp + (ha0.y >> 16));
+    for (int z = 0; z < n; ++z) {
       const float wz = wu[z];
-      const PctMat MA = pct_mat(A, x, z), MB = pct_mat(A, z, y);
-      int s = i, e = i + 1;                                 // identity: the single entry (i, 1.0f)
-      if (MA.row_ptr) { s = MA.row_ptr[i]; e = MA.row_ptr[i + 1]; }
-      for (int k0 = s; k0 < e; k0 += 32) {
-        // round 1: up to 32 k's of the row, and where their rows of mp_[z][y] live
-        const int ke = k0 + lane;
-        int ak = 0, bs = 0, cnt = 0; float ap = 0.0f;
-        if (ke < e) {
-          if (MA.row_ptr) { ak = (int)MA.col[ke]; ap = MA.val[ke]; } else { ak = i; ap = 1.0f; }
-          if (MB.row_ptr) { bs = MB.row_ptr[ak]; cnt = MB.row_ptr[ak + 1] - bs; } else { bs = ak; cnt = 1; }
-        }
-        const int incl = pct_warp_incl_scan(cnt, lane);
-        const int off = incl - cnt;
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        const int nk = min(32, e - k0);
-        for (int f0 = 0; f0 < total; f0 += 32) {
-          // round 2: 32 flattened products; g = the k group of mine
-          const int f = f0 + lane;
-          int g = 0;
-          for (int t = 1; t < nk; ++t) { const int o = __shfl_sync(0xffffffffu, off, t); if (f >= o) g = t; }
-          const int go = __shfl_sync(0xffffffffu, off, g), gb = __shfl_sync(0xffffffffu, bs, g);
-          const float gp = __shfl_sync(0xffffffffu, ap, g);
-          int j = 0; float t2 = 0.0f;
-          const bool live = f < total;
-          if (live) {
-            float pj;
-            if (MB.row_ptr) { j = (int)MB.col[gb + (f - go)]; pj = MB.val[gb + (f - go)]; } else { j = gb; pj = 1.0f; }
-            t2 = __fmul_rn(__fmul_rn(gp, pj), wz);                          // p_ik * p_jk * w  (:297)
-          }
-          // add group by group (ascending k); columns inside a group are distinct
-          const int gfirst = __shfl_sync(0xffffffffu, g, 0);
-          const int glast = __shfl_sync(0xffffffffu, live ? g : -1, min(31, total - f0 - 1));
-          for (int cur = gfirst; cur <= glast; ++cur) {
-            if (live && g == cur) acc[j] = __fadd_rn(acc[j], t2);
-            __syncwarp();
-          }
+      // loads for the steps ahead (past the end: repeated, never used)
+      const uint4 ha2 = __ldg(head + dA[min(z + 2, n - 1)].rp + ii);
+      const PctDesc db1 = dB[min(z + 1, n - 1)];
+      const uint4 hb10 = __ldg(head + db1.rp + (ha1.y & 0xffffu));
+      const uint4 hb11 = __ldg(head + db1.rp + (ha1.y >> 16));
+      // step z
+      if (ha0.x >= 1u) pct_mp_row(P, acc, db0, (int)(ha0.y & 0xffffu), __uint_as_float(ha0.z), hb00, wz);
+      if (ha0.x >= 2u) pct_mp_row(P, acc, db0, (int)(ha0.y >> 16), __uint_as_float(ha0.w), hb01, wz);
+      if (ha0.x > 2u) {
+        const PctDesc da = dA[z];
+        const int2 r = pct_mp_tail(P, acc, da.rp, da.nz, db0.rp, db0.nz, i, (int)ha0.x, wz);
+        acc.jmin = r.x; acc.jw = r.y;
+      }
+      ha0 = ha1; ha1 = ha2; db0 = db1; hb00 = hb10; hb01 = hb11;
+    }
+    // read-out: v = acc / sum_w > CUTOFF, ascending j (:302-311)
+    const float sw = sum_w[u];
+    int cnt = 0;
+    for (int j = acc.jmin; j < acc.jmin + acc.jw; ++j) cnt += (double)__fdiv_rn(acc.a[acc.idx(j)], sw) > PCT_CUTOFF;
+    const int incl = pct_warp_incl_scan(cnt, lane);
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long b = 0;
+    if (lane == 0 && total) b = atomicAdd(O.pool_count, (unsigned long long)total);
+    const int64_t base = (int64_t)__shfl_sync(0xffffffffu, b, 0) + (incl - cnt);
+    if (live) {
+      const int64_t row = out_row_off[u] + i;
+      O.row_pool[row] = base; O.row_cnt[row] = cnt;
+      if (base + cnt <= O.pool_cap) {
+        int64_t k = base;
+        for (int j = acc.jmin; j < acc.jmin + acc.jw; ++j) {
+          const float v = __fdiv_rn(acc.a[acc.idx(j)], sw);
+          if ((double)v > PCT_CUTOFF) { O.pool_col[k] = (uint32_t)j; O.pool_val[k] = v; ++k; }
         }
       }
     }
-    __syncwarp();
-    pct_emit_row(O, row, acc, 0, L2, sum_w[u], lane);
     __syncwarp();
   }
 }
