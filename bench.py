@@ -286,6 +286,43 @@ def run_stages(rank, world, max_over_ranks, steps, with_cpu):
             dt, _ = cpu_threads(lambda q: ou.oracle_mccaskill(q)[1], seqs[:k], k)
             out[name]["cpu_baseline"] = {"value": k / dt, "unit": "sequences/s", "cores": k, "kind": "port",
                                          "sample": "%d sequences, one per host thread (FP64 restatement, parity unpinned)" % k}
+    # ---- (4) consistency transformation on C4's sequences (next row) ----------
+    # All pairs feed every relaxed pair, so this stage does not shard: rank 0 runs it (N = 1 only).
+    if world == 1:
+        seqs = dafs_b200.random_rna(NSEQ, LEN, config_id=CONFIG_ID)
+        lens = np.array([len(q) for q in seqs], np.int32)
+        mp = dafs_b200.pairhmm_all(seqs, TH)
+        bp = dafs_b200.mccaskill_all(seqs, TH)
+        reps = max(1, min(steps, 3))
+        tot, parts = [], []
+        for it in range(1 + reps):
+            t0 = time.perf_counter()
+            sim, omp, obp = dafs_b200.pct(lens, mp, bp, 0.25, 0.25)
+            wall = time.perf_counter() - t0
+            nnz_out = (omp.nnz, obp.nnz)
+            omp.close(); obp.close()
+            if it >= 1:
+                tot.append(wall); parts.append(dafs_b200.pct_last_ms())
+        t = sum(tot) / len(tot)
+        triples = NSEQ * (NSEQ - 1) // 2 * NSEQ
+        out["pct_C4"] = {"workload": "C4 sequences: transpose_mp + similarity + relax_bp + relax_mp (w_pct_a = w_pct_s = 0.25) "
+                                     "on the %d pair posteriors and %d base-pairing matrices, host buffers in and out" % (len(lens) * (len(lens) - 1) // 2, len(lens)),
+                         "pair_z_triples_per_s": triples / t, "pairs_per_s": (triples // NSEQ) / t, "ms_per_step": t * 1e3,
+                         "device_ms": {k: sum(p[k] for p in parts) / len(parts) for k in parts[0]},
+                         "nnz_in": [mp.nnz, bp.nnz], "nnz_out": list(nnz_out), "dtype": "f32"}
+        if with_cpu and rank == 0:
+            import oracle_util as ou
+            kind = "reference" if ou.have_ref() else "port"
+            f = ou.ref_pct if ou.have_ref() else ou.oracle_pct
+            ns = 64                                                       # ~10 s of the reference's loops on one core
+            sub = ou.FlatCsr([mp.unit(i * NSEQ - i * (i + 1) // 2 + (j - i - 1)) for i in range(ns) for j in range(i + 1, ns)])
+            sbp = ou.FlatCsr([bp.unit(i) for i in range(ns)])
+            t0 = time.perf_counter()
+            f(lens[:ns], sub, sbp, 0.25, 0.25)
+            dt = time.perf_counter() - t0
+            out["pct_C4"]["cpu_baseline"] = {"value": (ns * (ns - 1) // 2 * ns) / dt, "unit": "(pair, z) triples/s", "cores": 1, "kind": kind,
+                                             "sample": "the first %d of the %d sequences (%d pairs x %d z), the reference's single-threaded loops" % (ns, NSEQ, ns * (ns - 1) // 2, ns)}
+        mp.close(); bp.close()
     return out
 
 

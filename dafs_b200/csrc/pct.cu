@@ -212,15 +212,17 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   DAFS_CUDA_TRY(B.get(&d_orow_bp, n + 1));
   // U and T share one set of arrays: [U | T]
   const int64_t RU = u_row_off[npairs], RT = t_row_off[npairs];
-  DAFS_CUDA_TRY(B.get(&d_u_row_ptr, RU + RT));
-  DAFS_CUDA_TRY(B.get(&d_u_col, 2 * mp_nnz));
-  DAFS_CUDA_TRY(B.get(&d_u_val, 2 * mp_nnz));
+  const int64_t RI = b_row_off[n], NI = b_row_off[n] - n;    // identity blocks: rows + 1 each, len entries
+  DAFS_CUDA_TRY(B.get(&d_u_row_ptr, RU + RT + RI));
+  DAFS_CUDA_TRY(B.get(&d_u_col, 2 * mp_nnz + NI));
+  DAFS_CUDA_TRY(B.get(&d_u_val, 2 * mp_nnz + NI));
   A.t_row_ptr = d_u_row_ptr + RU; A.t_col = d_u_col + mp_nnz; A.t_val = d_u_val + mp_nnz;
   A.rp_all = d_u_row_ptr; A.col_all = d_u_col; A.val_all = d_u_val; A.ru = RU; A.nnz = mp_nnz;
   DAFS_CUDA_TRY(B.get(&d_cursor, RT));
   DAFS_CUDA_TRY(B.get(&A.desc, (size_t)n * n));
   DAFS_CUDA_TRY(B.get(&A.descT, (size_t)n * n));
   DAFS_CUDA_TRY(B.get(&A.head, RU + RT + b_row_off[n]));
+  DAFS_CUDA_TRY(B.get(&A.ent_all, 2 * mp_nnz + NI));
   A.rt = RT;
   DAFS_CUDA_TRY(B.get(&d_b_row_ptr, b_row_off[n]));
   DAFS_CUDA_TRY(B.get(&d_b_col, bp_nnz));
@@ -264,7 +266,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   // K6, K7
   DAFS_CUDA_TRY(cudaEventRecord(G.ev[1], st));
   pct_desc_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(A);
-  pct_identity_heads_kernel<<<n, 128, 0, st>>>(A);
+  pct_identity_kernel<<<n, 128, 0, st>>>(A, d_u_row_ptr, d_u_col, d_u_val);
   if (npairs) pct_transpose_kernel<<<grid_for(npairs, 4), 128, 0, st>>>(A, npairs, d_pairs, d_cursor);
   DAFS_CUDA_TRY(cudaEventRecord(G.ev[2], st));
   {
@@ -333,7 +335,8 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     // 16 x's and mp_[.][y] of 16 y's, which stay in L2 while its tasks run
     std::vector<int2> tasks;
     tasks.reserve((size_t)npairs * ((maxL + 31) / 32));
-    const int TILE = 16;
+    int TILE = (double)mp_nnz > 2.5 * (double)orow_mp[npairs] ? 8 : 16;
+    if (const char* t = getenv("DAFS_PCT_TILE")) TILE = std::max(1, atoi(t));
     for (int x0 = 0; x0 < n; x0 += TILE)
       for (int y0 = x0; y0 < n; y0 += TILE)
         for (int x = x0; x < std::min(n, x0 + TILE); ++x)
@@ -344,18 +347,49 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     int2* d_tasks = nullptr;
     DAFS_CUDA_TRY(B.get(&d_tasks, ntasks));
     DAFS_CUDA_TRY(h2d(d_tasks, tasks.data(), sizeof(int2) * ntasks));
+    // Two kernels: rows of one or two entries (related sequences) go through the row heads, a
+    // thread per row; rows with many entries (unrelated sequences) take G = 8 lanes per row with
+    // the accumulator rows in shared memory.
+    bool dense = (double)mp_nnz > 2.5 * (double)orow_mp[npairs];
+    if (const char* k = getenv("DAFS_PCT_MP_KERNEL")) dense = k[0] == 'd';
+    int G = 8;                                               // lanes per row
+    if (const char* k = getenv("DAFS_PCT_G")) G = atoi(k) == 4 ? 4 : 8;
+    int wave = 0;                                            // 1: one launch per wave of resident warps
+    if (const char* k = getenv("DAFS_PCT_WAVE")) wave = atoi(k);
+    const int RW = 32 / G, UPT = 32 / RW;                    // rows per warp, units per task of 32 rows
+    const size_t dense_smem_want = (size_t)8 * RW * accW * sizeof(float);
+    bool dense_global = dense_smem_want > (size_t(200) << 10);
+    if (const char* k = getenv("DAFS_PCT_MP_KERNEL")) if (k[0] == 'd' && k[1] == 'g') dense_global = true;   // "dg": tests
+    if (dense_global) wave = 1;                              // the global scratch is sized for one wave
+    const size_t dense_smem = dense_global ? 0 : dense_smem_want;
     int mp_grid = 0;
+    size_t acc_floats_per_warp = dense ? (dense_global ? (size_t)RW * accW : 0) : (size_t)maxL * 32;
     {
       int dev = 0, sms = 148, per_sm = 1;
       cudaGetDevice(&dev);
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_kernel, 256, 0));
+      if (dense) {
+        if (dense_smem > (48 << 10)) {
+          DAFS_CUDA_TRY(cudaFuncSetAttribute(pct_relax_mp_dense_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dense_smem));
+          DAFS_CUDA_TRY(cudaFuncSetAttribute(pct_relax_mp_dense_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dense_smem));
+        }
+        if (G == 4) {
+          if (dense_global) DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_dense_kernel<4, false>, 256, 0));
+          else DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_dense_kernel<4, true>, 256, dense_smem));
+        } else {
+          if (dense_global) DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_dense_kernel<8, false>, 256, 0));
+          else DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_dense_kernel<8, true>, 256, dense_smem));
+        }
+      } else {
+        DAFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pct_relax_mp_kernel, 256, 0));
+      }
       mp_grid = (int)std::max<int64_t>(1, std::min<int64_t>((ntasks + 7) / 8, (int64_t)sms * std::max(per_sm, 1)));
     }
     if (const char* g = getenv("DAFS_PCT_MP_GRID")) mp_grid = std::max(1, atoi(g));
-    while (mp_grid > 1 && (size_t)mp_grid * 8 * maxL * 32 * sizeof(float) > (size_t(2) << 30)) mp_grid /= 2;
+    while (mp_grid > 1 && (size_t)mp_grid * 8 * acc_floats_per_warp * sizeof(float) > (size_t(2) << 30)) mp_grid /= 2;
+    const size_t acc_warps = (size_t)mp_grid * 8;
     float* d_acc = nullptr;
-    DAFS_CUDA_TRY(B.get(&d_acc, (size_t)mp_grid * 8 * maxL * 32));
+    DAFS_CUDA_TRY(B.get(&d_acc, acc_warps * acc_floats_per_warp));
     Pool P;
     const int64_t rows = orow_mp[npairs];
     if ((rc = P.alloc(B, rows, std::max<int64_t>(2 * mp_nnz, 1024)))) { dafs_cuda_free_batch(bp_out); return rc; }
@@ -363,7 +397,22 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     for (int attempt = 0; attempt < 2; ++attempt) {
       cudaError_t e = cudaMemsetAsync(P.O.pool_count, 0, sizeof(unsigned long long), st);
       if (e == cudaSuccess) {
-        pct_relax_mp_kernel<<<mp_grid, 256, 0, st>>>(A, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, d_acc, maxL);
+        if (dense) {
+          // one launch over all units, or one per wave of resident warps (global scratch)
+          const int64_t units = ntasks * UPT, per_wave = wave ? (int64_t)mp_grid * 8 : units;
+          for (int64_t u0 = 0; u0 < units; u0 += per_wave) {
+            const int gridw = (int)((std::min(per_wave, units - u0) + 7) / 8);
+            if (G == 4) {
+              if (dense_global) pct_relax_mp_dense_kernel<4, false><<<gridw, 256, 0, st>>>(A, u0, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, d_acc, accW);
+              else pct_relax_mp_dense_kernel<4, true><<<gridw, 256, dense_smem, st>>>(A, u0, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, nullptr, accW);
+            } else {
+              if (dense_global) pct_relax_mp_dense_kernel<8, false><<<gridw, 256, 0, st>>>(A, u0, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, d_acc, accW);
+              else pct_relax_mp_dense_kernel<8, true><<<gridw, 256, dense_smem, st>>>(A, u0, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, nullptr, accW);
+            }
+          }
+        }
+        else
+          pct_relax_mp_kernel<<<mp_grid, 256, 0, st>>>(A, ntasks, d_tasks, d_pairs, d_orow_mp, d_w, d_sw, P.O, d_acc, maxL);
         e = cudaGetLastError();
       }
       if (e == cudaSuccess) e = cudaMemcpyAsync(&need, P.O.pool_count, sizeof need, cudaMemcpyDeviceToHost, st);

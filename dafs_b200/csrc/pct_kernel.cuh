@@ -34,8 +34,8 @@ struct PctMat {             // one mp_[a][b]: rows of a, columns of b
   const float* val;
 };
 
-// Where mp_[a][b] lives: offsets into the combined arrays (U first, then T).  nz < 0 =
-// identity: no CSR, but rp still addresses a block of heads {1, r, 1.0f} (after U and T).
+// Where mp_[a][b] lives: offsets into the combined arrays: U first, then T, then the n
+// identity matrices mp_[a][a] (align.cpp:41-44) written out as CSR like the others.
 struct PctDesc { int64_t rp, nz; };
 
 struct PctArgs {
@@ -49,6 +49,7 @@ struct PctArgs {
   const int* u_row_ptr; const uint32_t* u_col; const float* u_val;
   int* t_row_ptr; uint32_t* t_col; float* t_val;
   const int* rp_all; const uint32_t* col_all; const float* val_all;
+  uint2* ent_all;           // the same entries interleaved, {column, value bits}: one 8-byte load per entry
   int64_t ru, nnz;          // sizes of the U parts of rp_all / col_all
   PctDesc* desc;            // [n*n]  desc[a*n+b]  = mp_[a][b]
   PctDesc* descT;           // [n*n]  descT[b*n+a] = mp_[a][b]
@@ -73,7 +74,7 @@ __global__ void pct_desc_kernel(PctArgs A) {
   if (t >= A.n * A.n) return;
   const int a = t / A.n, b = t % A.n;
   PctDesc d;
-  if (a == b) { d.rp = A.ru + A.rt + A.b_row_off[a]; d.nz = -1; }
+  if (a == b) { d.rp = A.ru + A.rt + A.b_row_off[a]; d.nz = 2 * A.nnz + A.b_row_off[a] - a; }
   else if (a < b) { const int64_t u = pct_pair_index(A.n, a, b); d.rp = A.u_row_off[u]; d.nz = A.nz_off[u]; }
   else { const int64_t u = pct_pair_index(A.n, b, a); d.rp = A.ru + A.t_row_off[u]; d.nz = A.nnz + A.nz_off[u]; }
   A.desc[(int64_t)a * A.n + b] = d;
@@ -83,7 +84,6 @@ __global__ void pct_desc_kernel(PctArgs A) {
 __device__ __forceinline__ PctMat pct_mat(const PctArgs& A, int a, int b) {
   const PctDesc d = A.desc[(int64_t)a * A.n + b];
   PctMat m;
-  if (d.nz < 0) { m.row_ptr = nullptr; m.col = nullptr; m.val = nullptr; return m; }
   m.row_ptr = A.rp_all + d.rp; m.col = A.col_all + d.nz; m.val = A.val_all + d.nz;
   return m;
 }
@@ -115,6 +115,9 @@ __global__ void __launch_bounds__(128) pct_transpose_kernel(PctArgs A, int64_t n
     uint32_t* tcol = A.t_col + A.nz_off[u];
     float* tval = A.t_val + A.nz_off[u];
     const int nnz = rp[L1];
+    uint2* uent = A.ent_all + A.nz_off[u];
+    uint2* tent = A.ent_all + A.nnz + A.nz_off[u];
+    for (int k = lane; k < nnz; k += 32) uent[k] = make_uint2(col[k], __float_as_uint(val[k]));
     for (int j = lane; j <= L2; j += 32) trp[j] = 0;
     __syncwarp();
     for (int k = lane; k < nnz; k += 32) atomicAdd(&trp[col[k] + 1], 1);
@@ -134,6 +137,7 @@ __global__ void __launch_bounds__(128) pct_transpose_kernel(PctArgs A, int64_t n
         const uint32_t j = col[k];
         const int pos = __ldcg(cur + j);
         tcol[pos] = (uint32_t)i; tval[pos] = val[k];
+        tent[pos] = make_uint2((unsigned)i, __float_as_uint(val[k]));
         __stcg(cur + j, pos + 1);
       }
       __syncwarp();
@@ -158,14 +162,18 @@ __global__ void __launch_bounds__(128) pct_transpose_kernel(PctArgs A, int64_t n
   }
 }
 
-// heads of the identity matrices mp_[a][a]: row r = {1, r, 1.0f}, spare row empty
-__global__ void pct_identity_heads_kernel(PctArgs A) {
+// the identity matrices mp_[a][a]: CSR rows {(r, 1.0f)} and heads {1, r, 1.0f}, spare row empty
+__global__ void pct_identity_kernel(PctArgs A, int* __restrict__ rp_all, uint32_t* __restrict__ col_all,
+                                    float* __restrict__ val_all) {
   const int a = blockIdx.x;
   const int L = A.len[a];
-  uint4* h = A.head + A.ru + A.rt + A.b_row_off[a];
-  for (int r = threadIdx.x; r <= L; r += blockDim.x)
-    h[r] = r < L ? make_uint4(1u, (unsigned)r | ((unsigned)L << 16), 0x3f800000u, 0u)
-                 : make_uint4(0u, (unsigned)L | ((unsigned)L << 16), 0u, 0u);
+  const int64_t rb = A.ru + A.rt + A.b_row_off[a], zb = 2 * A.nnz + A.b_row_off[a] - a;
+  for (int r = threadIdx.x; r <= L; r += blockDim.x) {
+    A.head[rb + r] = r < L ? make_uint4(1u, (unsigned)r | ((unsigned)L << 16), 0x3f800000u, 0u)
+                           : make_uint4(0u, (unsigned)L | ((unsigned)L << 16), 0u, 0u);
+    rp_all[rb + r] = r;
+    if (r < L) { col_all[zb + r] = (uint32_t)r; val_all[zb + r] = 1.0f; A.ent_all[zb + r] = make_uint2((unsigned)r, 0x3f800000u); }
+  }
 }
 
 // ---- K7: calculate_similarity_score ------------------------------------------------
@@ -491,6 +499,133 @@ __global__ void __launch_bounds__(256, PCT_MP_MINB) pct_relax_mp_kernel(PctArgs 
       }
     }
     __syncwarp();
+  }
+}
+
+// ---- K9, rows with many entries --------------------------------------------------------
+// Unrelated sequences give rows of 5-10 entries, i.e. ~50 products per (row, z): the
+// accumulator rows are then dense and must stay on chip.  G lanes share a row (32 / G
+// rows per warp), the accumulator row is in shared memory (SMEM) or, for sequences too
+// long for that, in global scratch.  Per z: the k's of row i are taken one per step in
+// ascending order, the G lanes take the entries of row k of mp_[z][y] (distinct
+// columns, so no two lanes meet on a cell inside a step; __syncwarp between steps).
+// The three dependent loads that lead to a step (row bounds of i, its k's, their row
+// bounds) are software-pipelined over z.
+// Every warp takes exactly one unit (32 / G rows of one pair) and walks z = 0..n-1 once.
+// Units are numbered in the host's tile order and CTAs start in that order, so the
+// pairs in flight at any time come from one or two tiles, whose matrices fit in L2
+// (unit0: first unit of this launch -- the global-scratch variant is launched in waves
+// of resident warps because its scratch is sized for one wave).
+template <int G, bool SMEM>
+__global__ void __launch_bounds__(256) pct_relax_mp_dense_kernel(PctArgs A, int64_t unit0, int64_t ntasks,
+                                                                 const int2* __restrict__ tasks,
+                                                                 const int2* __restrict__ pairs,
+                                                                 const int64_t* __restrict__ out_row_off,
+                                                                 const float* __restrict__ w, const float* __restrict__ sum_w,
+                                                                 PctOut O, float* __restrict__ gacc, int Wp) {
+  extern __shared__ float pct_smem[];
+  constexpr int RW = 32 / G;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int g = lane / G, q = lane % G;
+  const int64_t wid = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+  const int64_t unit = unit0 + wid;                          // (task, block of RW rows inside its 32)
+  if (unit >= ntasks * (32 / RW)) return;
+  float* acc = (SMEM ? pct_smem + (size_t)wib * RW * Wp : gacc + wid * (int64_t)(RW * Wp)) + (size_t)g * Wp;
+  const int n = A.n;
+  const int* __restrict__ rp = A.rp_all;
+  const uint2* __restrict__ ent = A.ent_all;
+  const int2 tk = tasks[unit / (32 / RW)];
+  const int64_t u = tk.x;
+  const int x = pairs[u].x, y = pairs[u].y;
+  const int L1 = A.len[x], L2 = A.len[y];
+  const int i0 = tk.y * 32 + (int)(unit % (32 / RW)) * RW;
+  if (i0 >= L1) return;
+  const float* wu = w + u * n;
+  const PctDesc* dA = A.desc + (int64_t)x * n;               // mp_[x][z]
+  const PctDesc* dB = A.descT + (int64_t)y * n;              // mp_[z][y]
+  const float sw = sum_w[u];
+  const int i = i0 + g;
+  const bool live = i < L1;
+  for (int j = q; j < L2; j += G) acc[j] = 0.0f;
+  __syncwarp();
+  // pipeline registers: row bounds for z .. z+3, k / p for z .. z+2, bounds of row k for z, z+1
+  int s0 = 0, e0 = 0, s1 = 0, e1 = 0, s2 = 0, e2 = 0, k1 = 0, b0 = 0, c0 = 0;
+  float p0 = 0.0f, p1 = 0.0f;
+  if (live) {
+    PctDesc d = dA[0]; s0 = rp[d.rp + i]; e0 = rp[d.rp + i + 1];
+    if (s0 + q < e0) { const uint2 t = ent[d.nz + s0 + q]; p0 = __uint_as_float(t.y); const PctDesc b = dB[0]; b0 = rp[b.rp + t.x]; c0 = rp[b.rp + t.x + 1]; }
+    d = dA[min(1, n - 1)]; s1 = rp[d.rp + i]; e1 = rp[d.rp + i + 1];
+    if (s1 + q < e1) { const uint2 t = ent[d.nz + s1 + q]; k1 = (int)t.x; p1 = __uint_as_float(t.y); }
+    d = dA[min(2, n - 1)]; s2 = rp[d.rp + i]; e2 = rp[d.rp + i + 1];
+  }
+  for (int z = 0; z < n; ++z) {
+    const float wz = wu[z];
+    const PctDesc dbz = dB[z];
+    const uint2* __restrict__ eb = ent + dbz.nz;             // entries of mp_[z][y]
+    // loads for the steps ahead (past the end: repeated, never used)
+    int s3 = 0, e3 = 0, k2 = 0, b1 = 0, c1 = 0;
+    float p2 = 0.0f;
+    if (live) {
+      const PctDesc d3 = dA[min(z + 3, n - 1)];
+      s3 = rp[d3.rp + i]; e3 = rp[d3.rp + i + 1];
+      if (s2 + q < e2) { const uint2 t = ent[dA[min(z + 2, n - 1)].nz + s2 + q]; k2 = (int)t.x; p2 = __uint_as_float(t.y); }
+      if (s1 + q < e1) { const int* rb = rp + dB[min(z + 1, n - 1)].rp; b1 = rb[k1]; c1 = rb[k1 + 1]; }
+    }
+    // step z: chunks of G k's
+    const int cnt = e0 - s0;
+    for (int ch = 0; __any_sync(FULL, ch < cnt); ch += G) {
+      int kb = b0, kc = c0; float pp = p0;
+      if (ch > 0) {                                          // more than G entries in row i: fetch now
+        kb = 0; kc = 0; pp = 0.0f;
+        if (s0 + ch + q < e0) {
+          const uint2 t = ent[dA[z].nz + s0 + ch + q];
+          pp = __uint_as_float(t.y);
+          kb = rp[dbz.rp + t.x]; kc = rp[dbz.rp + t.x + 1];
+        }
+      }
+      const int left = cnt - ch;
+      for (int t = 0; __any_sync(FULL, t < min(left, G)); ++t) {
+        const int src = (lane & ~(G - 1)) + t;
+        const float pt = __shfl_sync(FULL, pp, src);
+        const int bs = __shfl_sync(FULL, kb, src), be = __shfl_sync(FULL, kc, src);
+        const bool on = t < left;
+        for (int f = bs + q; __any_sync(FULL, on && f < be); f += G) {
+          if (on && f < be) {
+            const uint2 en = eb[f];
+            acc[en.x] = __fadd_rn(acc[en.x], __fmul_rn(__fmul_rn(pt, __uint_as_float(en.y)), wz));
+          }
+        }
+        __syncwarp();
+      }
+    }
+    s0 = s1; e0 = e1; s1 = s2; e1 = e2; s2 = s3; e2 = e3;
+    p0 = p1; k1 = k2; p1 = p2; b0 = b1; c0 = c1;
+  }
+  // read-out: v = acc / sum_w > CUTOFF, ascending j (:302-311); one pool reservation per warp
+  const unsigned gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << (g * G);
+  int cntk = 0;
+  for (int j0 = 0; j0 < L2; j0 += G) {
+    const int j = j0 + q;
+    const bool keep = live && j < L2 && (double)__fdiv_rn(acc[j], sw) > PCT_CUTOFF;
+    cntk += __popc(__ballot_sync(FULL, keep) & gmask);
+  }
+  int off = 0, total = 0;
+#pragma unroll
+  for (int r = 0; r < RW; ++r) { const int c = __shfl_sync(FULL, cntk, r * G); if (r < g) off += c; total += c; }
+  unsigned long long b = 0;
+  if (lane == 0 && total) b = atomicAdd(O.pool_count, (unsigned long long)total);
+  const int64_t base = (int64_t)__shfl_sync(FULL, b, 0) + off;
+  if (live && q == 0) { const int64_t row = out_row_off[u] + i; O.row_pool[row] = base; O.row_cnt[row] = cntk; }
+  const bool fits = base + cntk <= O.pool_cap;
+  int run = 0;
+  for (int j0 = 0; j0 < L2; j0 += G) {
+    const int j = j0 + q;
+    float v = 0.0f; bool keep = false;
+    if (live && j < L2) { v = __fdiv_rn(acc[j], sw); keep = (double)v > PCT_CUTOFF; }
+    const unsigned m = __ballot_sync(FULL, keep) & gmask;
+    if (keep && fits) { const int64_t k = base + run + __popc(m & ((1u << lane) - 1u)); O.pool_col[k] = (uint32_t)j; O.pool_val[k] = v; }
+    run += __popc(m);
   }
 }
 

@@ -61,8 +61,12 @@ def make(kind, n, L, seed=11):
     return random_rna(n, L, config_id=seed)
 
 
+@pytest.mark.parametrize("kernel", ["sparse", "dense"])
 @pytest.mark.parametrize("kind,n,L,wa,ws", CASES)
-def test_pct_matches_oracle(kind, n, L, wa, ws):
+def test_pct_matches_oracle(kind, n, L, wa, ws, kernel, monkeypatch):
+    """Both relax_matching_probability kernels (thread per row through the row heads /
+    eight lanes per row with shared-memory accumulators) on every case."""
+    monkeypatch.setenv("DAFS_PCT_MP_KERNEL", kernel)
     lens, mp, bp = ou.pct_inputs(make(kind, n, L))
     check(lens, mp, bp, wa, ws)
 
@@ -82,11 +86,16 @@ def test_pct_single_sequence():
     check(lens, mp, bp, 0.25, 0.25)
 
 
-def test_pct_dense_rows():
-    """A low threshold gives rows with many entries: several k per row, rows of mp_[z][y]
-    that span more than 32 products, equal columns reached through different k."""
-    seqs = make("family", 4, 48)
+@pytest.mark.parametrize("kernel", ["sparse", "dense", "dg", "auto"])
+def test_pct_dense_rows(kernel, monkeypatch):
+    """A low threshold gives rows with many entries: several k per row (more than the
+    two of a row head, more than the eight of one chunk), rows of mp_[z][y] with more
+    than eight entries, equal columns reached through different k."""
+    if kernel != "auto":
+        monkeypatch.setenv("DAFS_PCT_MP_KERNEL", kernel)    # "dg": dense kernel, accumulators in global scratch
+    seqs = make("random", 4, 48)
     lens, mp, bp = ou.pct_inputs(seqs, th_a=1e-4, th_bp=1e-4)
+    assert mp.nz_off[-1] > 9 * 48 * 6
     check(lens, mp, bp, 0.25, 0.25)
 
 

@@ -1,6 +1,6 @@
 """Consistency transformation at benchmark sizes: posteriors from the device, then
 dafs_cuda_pct; prints the per-kernel device times.
-usage: python tools/prof_pct.py [N] [L] [reps] [--check]   (--check: compare with the oracle)"""
+usage: python tools/prof_pct.py [N] [L] [reps] [--check]   (--check: compare with the oracle; --random: unrelated sequences instead of a family)"""
 import os
 import sys
 import time
@@ -14,7 +14,7 @@ args = [a for a in sys.argv[1:] if not a.startswith("--")]
 N = int(args[0]) if len(args) > 0 else 256
 L = int(args[1]) if len(args) > 1 else 300
 reps = int(args[2]) if len(args) > 2 else 3
-seqs = db.homolog_family(N, L, config_id=4)
+seqs = db.random_rna(N, L, config_id=4) if "--random" in sys.argv else db.homolog_family(N, L, config_id=4)
 lens = np.array([len(s) for s in seqs], np.int32)
 mp = db.pairhmm_all(seqs, 0.01)
 bp = db.mccaskill_all(seqs, 0.01)
