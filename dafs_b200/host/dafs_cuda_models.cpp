@@ -31,6 +31,35 @@ std::vector<float> flatten(const VVF& m, size_t cols) {
   return f;
 }
 
+// MP / BP rows of several units -> the arrays of a dafs_csr_batch (caller-owned vectors).
+struct PackedBatch {
+  std::vector<int64_t> row_off, nz_off;
+  std::vector<int32_t> row_ptr;
+  std::vector<uint32_t> col;
+  std::vector<float> val;
+  dafs_csr_batch view;
+  void add(const std::vector<SV>& rows) {
+    if (row_off.empty()) { row_off.push_back(0); nz_off.push_back(0); }
+    int32_t k = 0;
+    row_ptr.push_back(0);
+    for (const SV& r : rows) {
+      for (const auto& e : r) { col.push_back(e.first); val.push_back(e.second); }
+      k += (int32_t)r.size();
+      row_ptr.push_back(k);
+    }
+    row_off.push_back((int64_t)row_ptr.size());
+    nz_off.push_back((int64_t)col.size());
+  }
+  const dafs_csr_batch* finish() {
+    if (row_off.empty()) { row_off.push_back(0); nz_off.push_back(0); }
+    view = dafs_csr_batch();
+    view.n_units = (int64_t)row_off.size() - 1; view.nnz = (int64_t)col.size();
+    view.row_off = row_off.data(); view.row_ptr = row_ptr.data(); view.nz_off = nz_off.data();
+    view.col = col.data(); view.val = val.data();
+    return &view;
+  }
+};
+
 }  // namespace
 
 // ---- Align::Model ---------------------------------------------------------------
@@ -175,6 +204,38 @@ DDOutcome solve_by_dd(const DDOptions& o, VU& x, VU& y, VU& z, const VVF& p_x, c
   solve_by_dd_batch(o, in, out);
   x.swap(out[0].x); y.swap(out[0].y); z.swap(out[0].z);
   return out[0].outcome;
+}
+
+void consistency_transform(const std::vector<Fasta>& fa, std::vector<std::vector<MP> >& mp, std::vector<BP>& bp,
+                           float w_pct_a, float w_pct_s, VVF& sim) {
+  const uint N = fa.size();
+  std::vector<int> len(N);
+  PackedBatch pm, pb;
+  for (uint i = 0; i != N; ++i) {
+    len[i] = (int)fa[i].size();
+    pb.add(bp[i]);
+    for (uint j = i + 1; j != N; ++j) pm.add(mp[i][j]);
+  }
+  std::vector<float> s((size_t)N * N);
+  dafs_csr_batch om, ob;
+  if (dafs_cuda_pct((int)N, len.data(), pm.finish(), pb.finish(), w_pct_a, w_pct_s, s.data(), &om, &ob) != DAFS_CUDA_OK)
+    fail("dafs_cuda_pct");
+  sim.assign(N, VF(N));
+  int64_t u = 0;
+  for (uint i = 0; i != N; ++i) {
+    std::copy(s.begin() + (size_t)i * N, s.begin() + (size_t)(i + 1) * N, sim[i].begin());
+    unpack_unit(ob, i, bp[i]);
+    for (uint j = i + 1; j != N; ++j, ++u) {
+      unpack_unit(om, u, mp[i][j]);
+      // transpose_mp (src/dafs.cpp:155-167): rows of mp[i][j] in order give ascending rows per column
+      MP& t = mp[j][i];
+      t.assign(fa[j].size(), SV());
+      for (uint r = 0; r != mp[i][j].size(); ++r)
+        for (const auto& e : mp[i][j][r]) t[e.first].push_back(std::make_pair(r, e.second));
+    }
+  }
+  dafs_cuda_free_batch(&om);
+  dafs_cuda_free_batch(&ob);
 }
 
 }  // namespace dafs_cuda

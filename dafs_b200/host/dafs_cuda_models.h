@@ -89,6 +89,14 @@ struct DDInput { const VVF* p_x; const VVF* p_y; const VVF* p_z; unsigned n1, n2
 struct DDOutput { VU x, y, z; DDOutcome outcome; };
 void solve_by_dd_batch(const DDOptions& o, const std::vector<DDInput>& in, std::vector<DDOutput>& out);
 
+// Drop-in for the block of DAFS::run() between the posterior calls and build_tree()
+// (src/dafs.cpp:1797-1827, without the optional four-way step): transpose_mp for all
+// pairs, sim_, relax_basepairing_probability (w_pct_s != 0), relax_matching_probability
+// (w_pct_a != 0).  mp is what a_model_->calculate(fa_, mp_) left (mp[i][j] for i <= j);
+// on return mp[i][j] is filled for all i, j, bp and sim as the reference leaves them.
+void consistency_transform(const std::vector<Fasta>& fa, std::vector<std::vector<MP> >& mp, std::vector<BP>& bp,
+                           float w_pct_a, float w_pct_s, VVF& sim);
+
 }  // namespace dafs_cuda
 
 #endif  // DAFS_CUDA_MODELS_H_
