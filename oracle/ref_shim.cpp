@@ -10,6 +10,9 @@
 //   * DAFS::solve_by_dd                      (src/dafs.cpp:1006-1295, lifted)
 //   * transpose_mp, DAFS::relax_matching_probability,
 //     DAFS::relax_basepairing_probability    (src/dafs.cpp:155-167, 258-375, lifted)
+//   * DAFS::build_tree, average_matching_probability, average_basepairing_probability,
+//     project_alignment, project_secondary_structure, align_alignments, align
+//                                            (src/dafs.cpp:447-607, 766-951, 1499-1537, lifted)
 // The "lifted" pieces are cut out of dafs.cpp by the Makefile with awk at
 // build time into oracle/_ref/*.inc (dafs.cpp itself needs ViennaRNA, which is
 // not on this box) and #included below; no reference source is stored here.
@@ -19,6 +22,7 @@
 #include <cstring>
 #include <limits>
 #include <memory>
+#include <queue>
 #include <string>
 #include <vector>
 
@@ -68,6 +72,25 @@ class DAFS {
   float w_pct_a_ = 0.25f, w_pct_s_ = 0.25f;
   void relax_matching_probability();
   void relax_basepairing_probability();
+  // members the progressive stage touches (dafs.cpp:88-117, 145-150)
+  typedef std::pair<float, std::pair<uint, uint>> node_t;
+  std::vector<node_t> tree_;
+  bool use_alifold_ = false, use_bp_update_ = false;
+  void build_tree();
+  void project_alignment(ALN& aln, const ALN& aln1, const ALN& aln2, const VU& z) const;
+  void project_secondary_structure(VU& xx, VU& yy, const VU& x, const VU& y, const VU& z) const;
+  void average_matching_probability(VVF& posterior, const ALN& aln1, const ALN& aln2) const;
+  void average_basepairing_probability(VVF& posterior, const ALN& aln, bool use_alifold) const;
+  void update_basepairing_probability(VVF&, const VU&, const std::string&, const ALN&, bool) const {
+    throw "update_basepairing_probability needs ViennaRNA";
+  }
+  void align_alignments(ALN& aln, const ALN& aln1, const ALN& aln2) const;
+  float align_alignments(VU& ss, ALN& aln, const ALN& aln1, const ALN& aln2) const;
+  void align(ALN& aln, int ch) const;
+  float align(VU& ss, ALN& aln, int ch) const;
+  // dafs.cpp:107-115 without the IP solvers; logs every solve for the per-node tests
+  float solve(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z, const ALN& aln1,
+              const ALN& aln2) const;
   void output_verbose(const VU&, const VU&, const VU&, const ALN&, const ALN&) const {}
   float solve_by_dd(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z,
                     const ALN& aln1, const ALN& aln2) const;
@@ -84,6 +107,24 @@ inline void info_capture(uint t, uint v) { g_last_iters = (int)t; g_last_violate
 
 #include "_ref/similarity.inc"
 #include "_ref/pct.inc"
+
+// alifold.cpp needs ViennaRNA; the lifted average_basepairing_probability only
+// reaches it under use_alifold, which the progressive tests never set.
+struct Alifold {
+  explicit Alifold(float) {}
+  void fold(const ALN&, const std::vector<std::string>&, BP&) const { throw "Alifold needs ViennaRNA"; }
+};
+namespace {
+struct SolveLog { int L1, L2, iters; unsigned violated; float score; };
+std::vector<SolveLog> g_solve_log;
+}
+float DAFS::solve(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z, const ALN& aln1,
+                  const ALN& aln2) const {
+  const float s = solve_by_dd(x, y, z, p_x, p_y, p_z, aln1, aln2);
+  g_solve_log.push_back({(int)p_x.size(), (int)p_y.size(), g_last_iters, g_last_violated, s});
+  return s;
+}
+#include "_ref/progressive.inc"
 
 static VVF to_vvf(const float* a, int r, int c) {
   VVF m(r, VF(c));
@@ -275,3 +316,70 @@ void ref_pct_copy(int* mp_row_ptr, unsigned* mp_col, float* mp_val, int* bp_row_
 }
 
 }  // extern "C"
+
+// ---- progressive alignment along the guide tree: DAFS::run(), src/dafs.cpp:1829-1838 ------
+// mp / bp as for ref_pct_run (already relaxed, or raw).  sim != NULL: build_tree() from it and
+// return the tree in left/right/node_score; sim == NULL: left/right/node_score are the tree.
+// Then align(ss, aln, root) with use_alifold_ = false, use_bp_update_ = false.  Outputs: the
+// root alignment (rows in the reference's order: seq_order[r], gap pattern bits[r * cap + c]),
+// ss, and for every internal node in the order the recursion solved them (post-order) a log
+// row {L1, L2, iters, violated} + score.  Returns the root score.
+extern "C" float ref_progressive(int n, const int* len, const long long* mp_row_off, const int* mp_row_ptr,
+                                 const long long* mp_nz_off, const unsigned* mp_col, const float* mp_val,
+                                 const long long* bp_row_off, const int* bp_row_ptr, const long long* bp_nz_off,
+                                 const unsigned* bp_col, const float* bp_val, const float* sim, int* left, int* right,
+                                 float* node_score, float w, float th_s, float th_a, float eta0, int t_max,
+                                 int cap, int* L_out, int* seq_order, unsigned char* bits, unsigned* ss_out,
+                                 int* solve_log /* (n-1) * 4 */, float* solve_score /* n-1 */) {
+  DAFS d;
+  const uint N = (uint)n;
+  d.t_max_ = t_max; d.th_a_ = th_a; d.th_s_ = VF(1, th_s); d.w_ = w; d.eta0_ = eta0;
+  d.a_decoder_.reset(new SparseNeedlemanWunsch(th_a));
+  d.s_decoder_.reset(new SparseNussinov(th_s));
+  d.fa_.resize(N);
+  for (uint i = 0; i < N; ++i) d.fa_[i] = std::string((size_t)len[i], 'N');
+  d.bp_.resize(N);
+  for (uint i = 0; i < N; ++i) from_csr(d.bp_[i], len[i], bp_row_ptr + bp_row_off[i], bp_col + bp_nz_off[i], bp_val + bp_nz_off[i]);
+  d.mp_.assign(N, std::vector<MP>(N));
+  long long u = 0;
+  for (uint i = 0; i < N; ++i) {
+    d.mp_[i][i].resize(len[i]);
+    for (int x = 0; x < len[i]; ++x) d.mp_[i][i][x].push_back(std::make_pair((uint)x, 1.0f));
+    for (uint j = i + 1; j < N; ++j, ++u) {
+      from_csr(d.mp_[i][j], len[i], mp_row_ptr + mp_row_off[u], mp_col + mp_nz_off[u], mp_val + mp_nz_off[u]);
+      transpose_mp(d.mp_[i][j], d.mp_[j][i], len[i], len[j]);
+    }
+  }
+  if (sim) {
+    d.sim_.assign(N, VF(N));
+    for (uint i = 0; i < N; ++i) for (uint j = 0; j < N; ++j) d.sim_[i][j] = sim[i * N + j];
+    d.build_tree();
+    for (uint k = 0; k < 2 * N - 1; ++k) {
+      left[k] = (int)d.tree_[k].second.first; right[k] = (int)d.tree_[k].second.second;
+      node_score[k] = d.tree_[k].first;
+    }
+  } else {
+    d.tree_.resize(2 * N - 1);
+    for (uint k = 0; k < 2 * N - 1; ++k)
+      d.tree_[k] = std::make_pair(node_score[k], std::make_pair((uint)left[k], (uint)right[k]));
+  }
+  g_solve_log.clear();
+  VU ss;
+  ALN aln;
+  const float s = d.align(ss, aln, (int)d.tree_.size() - 1);
+  const int L = (int)aln.front().second.size();
+  *L_out = L;
+  if (L <= cap) {
+    for (uint r = 0; r < aln.size(); ++r) {
+      seq_order[r] = (int)aln[r].first;
+      for (int c = 0; c < L; ++c) bits[(size_t)r * cap + c] = aln[r].second[c] ? 1 : 0;
+    }
+    for (int c = 0; c < L && c < (int)ss.size(); ++c) ss_out[c] = ss[c];
+  }
+  for (size_t k = 0; k < g_solve_log.size() && k + 1 < N; ++k) {
+    solve_log[4 * k] = g_solve_log[k].L1; solve_log[4 * k + 1] = g_solve_log[k].L2;
+    solve_log[4 * k + 2] = g_solve_log[k].iters; solve_log[4 * k + 3] = (int)g_solve_log[k].violated;
+    solve_score[k] = g_solve_log[k].score;
+  }
+  return s;
+}

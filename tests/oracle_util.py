@@ -295,3 +295,106 @@ def oracle_pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
 
 def ref_pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
     return _pct(ref(), "ref", lens, mp, bp, w_pct_a, w_pct_s)
+
+
+# ---- progressive alignment along the guide tree --------------------------------------
+def pct_to_flat(lens, r):
+    """The dict _pct() returns -> (mp FlatCsr over i<j pairs, bp FlatCsr)."""
+    n = len(lens)
+    units, rp0, nz = [], 0, 0
+    for i in range(n):
+        for j in range(i + 1, n):
+            rp = r["mp_row_ptr"][rp0:rp0 + lens[i] + 1]; rp0 += lens[i] + 1
+            units.append((rp, r["mp_col"][nz:nz + rp[-1]], r["mp_val"][nz:nz + rp[-1]])); nz += int(rp[-1])
+    bunits, rp0, nz = [], 0, 0
+    for i in range(n):
+        rp = r["bp_row_ptr"][rp0:rp0 + lens[i] + 1]; rp0 += lens[i] + 1
+        bunits.append((rp, r["bp_col"][nz:nz + rp[-1]], r["bp_val"][nz:nz + rp[-1]])); nz += int(rp[-1])
+    return FlatCsr(units), FlatCsr(bunits)
+
+
+def oracle_build_tree(sim):
+    n = sim.shape[0]
+    sim = np.ascontiguousarray(sim, np.float32)
+    left = np.zeros(2 * n - 1, np.int32); right = np.zeros(2 * n - 1, np.int32); score = np.zeros(2 * n - 1, np.float32)
+    f = oracle().oracle_build_tree
+    f.restype = None; f.argtypes = [C.c_int] + [C.c_void_p] * 4
+    f(n, sim.ctypes.data, left.ctypes.data, right.ctypes.data, score.ctypes.data)
+    return left, right, score
+
+
+def _progressive(fn, is_ref, lens, mp, bp, tree=None, sim=None, w=4.0, th_s=0.2, th_a=0.01, eta0=0.5, t_max=600):
+    n = len(lens)
+    lens = np.ascontiguousarray(lens, np.int32)
+    cap = int(lens.sum()) + 1
+    nn = 2 * n - 1
+    if tree is not None:
+        left = np.ascontiguousarray(tree[0], np.int32).copy(); right = np.ascontiguousarray(tree[1], np.int32).copy()
+        score = np.zeros(nn, np.float32) if len(tree) < 3 else np.ascontiguousarray(tree[2], np.float32).copy()
+    else:
+        left = np.zeros(nn, np.int32); right = np.zeros(nn, np.int32); score = np.zeros(nn, np.float32)
+    L = C.c_int(0)
+    order = np.zeros(n, np.int32); bits = np.zeros((n, cap), np.uint8); ss = np.zeros(cap, np.uint32)
+    log = np.zeros((max(n - 1, 1), 4), np.int32); lscore = np.zeros(max(n - 1, 1), np.float32)
+    csr = [mp.row_off.ctypes.data, mp.row_ptr.ctypes.data, mp.nz_off.ctypes.data, mp.col.ctypes.data, mp.val.ctypes.data,
+           bp.row_off.ctypes.data, bp.row_ptr.ctypes.data, bp.nz_off.ctypes.data, bp.col.ctypes.data, bp.val.ctypes.data]
+    tail = [C.c_float(w), C.c_float(th_s), C.c_float(th_a), C.c_float(eta0), C.c_int(t_max), C.c_int(cap), C.byref(L),
+            C.c_void_p(order.ctypes.data), C.c_void_p(bits.ctypes.data), C.c_void_p(ss.ctypes.data),
+            C.c_void_p(log.ctypes.data), C.c_void_p(lscore.ctypes.data)]
+    fn.restype = C.c_float
+    head = [C.c_int(n), C.c_void_p(lens.ctypes.data)] + [C.c_void_p(x) for x in csr]
+    if is_ref:
+        simp = None
+        if tree is None:
+            sim = np.ascontiguousarray(sim, np.float32); simp = C.c_void_p(sim.ctypes.data)
+        s = fn(*head, simp, C.c_void_p(left.ctypes.data), C.c_void_p(right.ctypes.data), C.c_void_p(score.ctypes.data), *tail)
+    else:
+        s = fn(*head, C.c_void_p(left.ctypes.data), C.c_void_p(right.ctypes.data), *tail)
+    Lv = L.value
+    return {"score": np.float32(s), "L": Lv, "order": order, "bits": bits[:, :Lv].copy(), "ss": ss[:Lv].copy(),
+            "log": log[:n - 1], "log_score": lscore[:n - 1], "left": left, "right": right, "tree_score": score}
+
+
+def oracle_progressive(lens, mp, bp, tree, **kw):
+    return _progressive(oracle().oracle_progressive, False, lens, mp, bp, tree=tree, **kw)
+
+
+def ref_progressive(lens, mp, bp, tree=None, sim=None, **kw):
+    return _progressive(ref().ref_progressive, True, lens, mp, bp, tree=tree, sim=sim, **kw)
+
+
+def postorder_internal(left, right):
+    """Internal nodes in the order the reference's recursion solves them (dafs.cpp:1518-1537)."""
+    out = []
+    def rec(ch):
+        if left[ch] < 0:
+            return
+        rec(left[ch]); rec(right[ch]); out.append(ch)
+    rec(len(left) - 1)
+    return out
+
+
+def stemloop_family(n, length, seed, mutation=0.12):
+    """n homologs of a two-hairpin root: substitutions, short deletions and insertions (ragged
+    lengths), from numpy's frozen legacy generator so every box sees the same bytes."""
+    rs = np.random.RandomState(seed)
+    comp = {65: 85, 67: 71, 71: 67, 85: 65}
+    def hairpin(stem):
+        a = rs.choice(np.frombuffer(b"ACGU", np.uint8), stem)
+        return list(a) + list(b"GAAA") + [comp[int(c)] for c in a[::-1]]
+    half = max(4, (length // 2 - 6) // 2)
+    root = hairpin(half) + list(rs.choice(np.frombuffer(b"ACGU", np.uint8), 3)) + hairpin(max(4, (length - 2 * half - 11) // 2))
+    out = []
+    for _ in range(n):
+        seq = []
+        for c in root:
+            u = rs.rand()
+            if u < mutation * 0.25:
+                continue                                   # deletion
+            if u < mutation:
+                c = int(rs.choice(np.frombuffer(b"ACGU", np.uint8)))
+            seq.append(int(c))
+            if rs.rand() < mutation * 0.2:
+                seq.append(int(rs.choice(np.frombuffer(b"ACGU", np.uint8))))   # insertion
+        out.append(bytes(seq))
+    return out
