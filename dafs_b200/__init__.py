@@ -22,5 +22,6 @@ from .capi import (  # noqa: F401
 )
 from .capi_mc import McCaskillPlan, mccaskill_all  # noqa: F401
 from .capi_pct import pct, pct_last_ms  # noqa: F401
+from .capi_prog import guide_tree, progressive  # noqa: F401
 from .capi_dd import DDPlan, dd_solve_batch, nussinov_decode, nw_decode  # noqa: F401
 from .synth import fasta_read, homolog_family, random_rna, splitmix64, synthetic_bpp  # noqa: F401

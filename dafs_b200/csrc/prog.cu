@@ -1,0 +1,452 @@
+// Host side of dafs_cuda_progressive: DAFS::align(ss, aln, root) (src/dafs.cpp:1518-1537)
+// with every guide-tree node whose children are finished solved in the same WAVE:
+// one launch each of K11 / K12 (prog_kernel.cuh) builds p_x, p_y, p_z of all nodes of the
+// wave, one batched DD plan (dd.cu) solves them, project_alignment (:766-826) merges.
+// Sibling subtrees share no state (no RNG unless -r > 0), so the results are those of the
+// reference's depth-first recursion.  Also dafs_cuda_guide_tree (build_tree, :447-495).
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <queue>
+#include <vector>
+
+#include "common.cuh"
+#include "prog_kernel.cuh"
+
+using dafs::fail;
+
+namespace {
+
+struct DevBufs {
+  std::vector<void*> p;
+  ~DevBufs() { for (void* q : p) dafs::dev_free(q); }
+  template <class T> cudaError_t get(T** out, size_t count) {
+    void* q = nullptr;
+    const cudaError_t e = dafs::dev_malloc(&q, std::max<size_t>(count * sizeof(T), 256));
+    if (e == cudaSuccess) p.push_back(q);
+    *out = static_cast<T*>(q);
+    return e;
+  }
+};
+
+struct StreamGuard {
+  cudaStream_t s = nullptr;
+  cudaEvent_t a = nullptr, b = nullptr;
+  ~StreamGuard() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); if (s) cudaStreamDestroy(s); }
+};
+
+struct PinGuard {
+  void* p = nullptr;
+  ~PinGuard() { if (p) dafs::pinned_free(p); }
+};
+
+struct PlanGuard {
+  dafs_dd_plan* p = nullptr;
+  ~PlanGuard() { if (p) dafs_cuda_dd_plan_destroy(p); }
+};
+
+// a sub-alignment: member sequences in the reference's row order, gap pattern per row
+struct Aln {
+  int L = 0;
+  std::vector<int> seq;
+  std::vector<uint8_t> bits;   // [rows * L], 1 = residue
+  bool built = false;
+};
+
+const uint32_t kNone = 0xffffffffu;
+
+// project_alignment, src/dafs.cpp:766-826
+void merge(Aln& out, const Aln& a1, const Aln& a2, const uint32_t* z) {
+  const int L1 = a1.L, L2 = a2.L;
+  int matched = 0;
+  for (int i = 0; i < L1; ++i) matched += z[i] != kNone;
+  const int L = L1 + L2 - matched;
+  // column of the merged alignment for every column of a1 / a2
+  std::vector<int> c1(L1), c2(L2);
+  {
+    int r = 0, k = 0;
+    for (int i = 0; i < L1; ++i) {
+      if (z[i] != kNone) { while (k < (int)z[i]) c2[k++] = r++; c1[i] = r; c2[k++] = r++; }
+      else c1[i] = r++;
+    }
+    while (k < L2) c2[k++] = r++;
+  }
+  out.L = L;
+  out.seq = a1.seq;
+  out.seq.insert(out.seq.end(), a2.seq.begin(), a2.seq.end());
+  out.bits.assign(out.seq.size() * (size_t)L, 0);
+  for (size_t q = 0; q < a1.seq.size(); ++q)
+    for (int i = 0; i < L1; ++i) out.bits[q * L + c1[i]] = a1.bits[q * L1 + i];
+  for (size_t q = 0; q < a2.seq.size(); ++q)
+    for (int k = 0; k < L2; ++k) out.bits[(a1.seq.size() + q) * L + c2[k]] = a2.bits[q * L2 + k];
+  out.built = true;
+}
+
+// project_secondary_structure (:828-876) + the consensus of align_alignments (:941-945)
+void consensus(std::vector<uint32_t>& ss, int L, const uint32_t* x, int L1, const uint32_t* y, int L2, const uint32_t* z) {
+  std::vector<int> c1(L1), c2(L2);
+  int r = 0, k = 0;
+  for (int i = 0; i < L1; ++i) {
+    if (z[i] != kNone) { while (k < (int)z[i]) c2[k++] = r++; c1[i] = r; c2[k++] = r++; }
+    else c1[i] = r++;
+  }
+  while (k < L2) c2[k++] = r++;
+  std::vector<uint32_t> xx(L, kNone), yy(L, kNone);
+  for (int i = 0; i < L1; ++i) if (x[i] != kNone) xx[c1[i]] = (uint32_t)c1[x[i]];
+  for (int q = 0; q < L2; ++q) if (y[q] != kNone) yy[c2[q]] = (uint32_t)c2[y[q]];
+  ss.assign(L, kNone);
+  for (int i = 0; i < L; ++i) if (xx[i] == yy[i]) ss[i] = xx[i];
+}
+
+int grid_for(int64_t warps_wanted, int warps_per_block) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t blocks = (warps_wanted + warps_per_block - 1) / warps_per_block;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, (int64_t)sms * 8));
+}
+
+struct ResultOwner {
+  std::vector<int32_t> seq, node_iters, node_L;
+  std::vector<uint8_t> bits;
+  std::vector<uint32_t> ss, node_violated;
+  std::vector<float> node_score;
+};
+
+double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // namespace
+
+// build_tree, src/dafs.cpp:447-495.  The queue holds (value, (i, j)) ordered like std::pair;
+// popping the maximum whose two labels are both live merges their clusters into node n; the
+// merged cluster keeps matrix slot l, its distance to a live cluster ii is
+// (d[ii][l] + d[ii][r]) * value / 2 in float.
+extern "C" int dafs_cuda_guide_tree(int nseq, const float* sim, int32_t* left, int32_t* right, float* score) {
+  if (nseq < 1 || !sim || !left || !right) return fail(DAFS_CUDA_EINVAL, "NULL argument or nseq < 1");
+  typedef std::pair<float, std::pair<uint32_t, uint32_t>> Ent;
+  const uint32_t N = (uint32_t)nseq;
+  uint32_t n = N;
+  for (uint32_t k = 0; k < 2 * N - 1; ++k) { left[k] = right[k] = -1; if (score) score[k] = 0.0f; }
+  std::vector<float> d((size_t)N * N, 0.0f);
+  std::vector<uint32_t> slot(2 * N - 1, kNone);
+  for (uint32_t i = 0; i < N; ++i) slot[i] = i;
+  std::priority_queue<Ent> pq;
+  for (uint32_t i = 0; i + 1 < N; ++i)
+    for (uint32_t j = i + 1; j < N; ++j) {
+      d[(size_t)i * N + j] = d[(size_t)j * N + i] = sim[(size_t)i * N + j];
+      pq.push(Ent(sim[(size_t)i * N + j], std::make_pair(i, j)));
+    }
+  while (!pq.empty()) {
+    const Ent t = pq.top();
+    pq.pop();
+    const uint32_t a = t.second.first, b = t.second.second;
+    if (slot[a] == kNone || slot[b] == kNone) continue;
+    const uint32_t l = slot[a], r = slot[b];
+    slot[a] = slot[b] = kNone;
+    for (uint32_t i = 0; i < n; ++i) {
+      if (slot[i] == kNone) continue;
+      const uint32_t ii = slot[i];
+      const float v = (d[(size_t)ii * N + l] + d[(size_t)ii * N + r]) * t.first / 2;
+      d[(size_t)ii * N + l] = d[(size_t)l * N + ii] = v;
+      pq.push(Ent(v, std::make_pair(i, n)));
+    }
+    left[n] = (int32_t)a; right[n] = (int32_t)b;
+    if (score) score[n] = t.first;
+    slot[n++] = l;
+  }
+  if (n != 2 * N - 1) return fail(DAFS_CUDA_EINVAL, "similarity matrix did not yield a full tree (NaN?)");
+  return DAFS_CUDA_OK;
+}
+
+extern "C" void dafs_cuda_free_prog_result(dafs_prog_result* r) {
+  if (!r) return;
+  delete static_cast<ResultOwner*>(r->owner_);
+  *r = dafs_prog_result{};
+}
+
+extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
+                                     const int32_t* left, const int32_t* right, const dafs_prog_params* prm,
+                                     dafs_prog_result* out) {
+  using namespace dafs;
+  if (out) *out = dafs_prog_result{};
+  if (nseq < 1 || !len || !mp || !bp || !left || !right || !prm || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument or nseq < 1");
+  const int n = nseq, nn = 2 * n - 1;
+  const int64_t npairs = (int64_t)n * (n - 1) / 2;
+  if (mp->n_units != npairs) return fail(DAFS_CUDA_EINVAL, "mp holds %lld units, %lld pairs expected", (long long)mp->n_units, (long long)npairs);
+  if (bp->n_units != n) return fail(DAFS_CUDA_EINVAL, "bp holds %lld units, %d sequences expected", (long long)bp->n_units, n);
+  for (int i = 0; i < n; ++i)
+    if (len[i] < 1 || len[i] > 16384) return fail(DAFS_CUDA_EINVAL, "len[%d] = %d (1 .. 16384)", i, len[i]);
+  // the tree: leaves 0..n-1, internal nodes n..2n-2 whose children come earlier, root last
+  std::vector<int> level(nn, 0);
+  {
+    std::vector<char> used(nn, 0);
+    for (int k = 0; k < nn; ++k) {
+      if (k < n) { if (left[k] != -1 || right[k] != -1) return fail(DAFS_CUDA_EINVAL, "tree node %d is a leaf but has children", k); continue; }
+      const int a = left[k], b = right[k];
+      if (a < 0 || b < 0 || a >= k || b >= k || a == b || used[a] || used[b])
+        return fail(DAFS_CUDA_EINVAL, "tree node %d: children (%d, %d) are not two unused earlier nodes", k, a, b);
+      used[a] = used[b] = 1;
+      level[k] = 1 + std::max(level[a], level[b]);
+    }
+  }
+  // geometry of the CSR batches
+  std::vector<int2> pairs((size_t)npairs);
+  std::vector<int> ncols_mp((size_t)npairs);
+  std::vector<int64_t> u_row_off(npairs + 1), t_row_off(npairs + 1), b_row_off(n + 1);
+  {
+    int64_t u = 0, ru = 0, rt = 0;
+    for (int a = 0; a < n; ++a)
+      for (int b = a + 1; b < n; ++b, ++u) {
+        pairs[u] = make_int2(a, b); ncols_mp[u] = len[b];
+        u_row_off[u] = ru; t_row_off[u] = rt;
+        ru += len[a] + 1; rt += len[b] + 1;
+      }
+    u_row_off[npairs] = ru; t_row_off[npairs] = rt;
+    int64_t rb = 0;
+    for (int a = 0; a < n; ++a) { b_row_off[a] = rb; rb += len[a] + 1; }
+    b_row_off[n] = rb;
+  }
+  for (int64_t u = 0; u <= npairs; ++u)
+    if (mp->row_off[u] != u_row_off[u]) return fail(DAFS_CUDA_EINVAL, "mp->row_off[%lld] does not match the sequence lengths", (long long)u);
+  for (int a = 0; a <= n; ++a)
+    if (bp->row_off[a] != b_row_off[a]) return fail(DAFS_CUDA_EINVAL, "bp->row_off[%d] does not match the sequence lengths", a);
+  const int64_t mp_nnz = npairs ? mp->nz_off[npairs] : 0, bp_nnz = bp->nz_off[n];
+  if (mp_nnz < 0 || bp_nnz < 0 || mp_nnz != mp->nnz || bp_nnz != bp->nnz) return fail(DAFS_CUDA_EINVAL, "nnz does not match nz_off");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    cudaGetLastError();
+    return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)");
+  }
+
+  const double t_begin = now_ms();
+  StreamGuard G;
+  DAFS_CUDA_TRY(cudaStreamCreateWithFlags(&G.s, cudaStreamNonBlocking));
+  DAFS_CUDA_TRY(cudaEventCreate(&G.a));
+  DAFS_CUDA_TRY(cudaEventCreate(&G.b));
+  cudaStream_t st = G.s;
+  DevBufs B;
+  ProgArgs A{};
+  A.n = n;
+  int* d_len = nullptr; int2* d_pairs = nullptr; int* d_ncols = nullptr; int* d_bad = nullptr; int* d_fill = nullptr;
+  int64_t *d_u_row_off = nullptr, *d_t_row_off = nullptr, *d_nz_off = nullptr, *d_b_row_off = nullptr, *d_b_nz_off = nullptr;
+  int* d_rp = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
+  int* d_b_rp = nullptr; uint32_t* d_b_col = nullptr; float* d_b_val = nullptr;
+  ProgDesc* d_desc = nullptr;
+  const int64_t RU = u_row_off[npairs], RT = t_row_off[npairs];
+  DAFS_CUDA_TRY(B.get(&d_len, n));
+  DAFS_CUDA_TRY(B.get(&d_pairs, npairs));
+  DAFS_CUDA_TRY(B.get(&d_ncols, npairs));
+  DAFS_CUDA_TRY(B.get(&d_bad, 1));
+  DAFS_CUDA_TRY(B.get(&d_fill, RT));
+  DAFS_CUDA_TRY(B.get(&d_u_row_off, npairs + 1));
+  DAFS_CUDA_TRY(B.get(&d_t_row_off, npairs + 1));
+  DAFS_CUDA_TRY(B.get(&d_nz_off, npairs + 1));
+  DAFS_CUDA_TRY(B.get(&d_b_row_off, n + 1));
+  DAFS_CUDA_TRY(B.get(&d_b_nz_off, n + 1));
+  DAFS_CUDA_TRY(B.get(&d_rp, RU + RT));
+  DAFS_CUDA_TRY(B.get(&d_col, 2 * mp_nnz));
+  DAFS_CUDA_TRY(B.get(&d_val, 2 * mp_nnz));
+  DAFS_CUDA_TRY(B.get(&d_b_rp, b_row_off[n]));
+  DAFS_CUDA_TRY(B.get(&d_b_col, bp_nnz));
+  DAFS_CUDA_TRY(B.get(&d_b_val, bp_nnz));
+  DAFS_CUDA_TRY(B.get(&d_desc, (size_t)n * n));
+  auto h2d = [&](void* d, const void* h, size_t bytes) {
+    return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+  };
+  DAFS_CUDA_TRY(h2d(d_len, len, sizeof(int) * n));
+  DAFS_CUDA_TRY(h2d(d_pairs, pairs.data(), sizeof(int2) * npairs));
+  DAFS_CUDA_TRY(h2d(d_ncols, ncols_mp.data(), sizeof(int) * npairs));
+  DAFS_CUDA_TRY(h2d(d_u_row_off, u_row_off.data(), sizeof(int64_t) * (npairs + 1)));
+  DAFS_CUDA_TRY(h2d(d_t_row_off, t_row_off.data(), sizeof(int64_t) * (npairs + 1)));
+  DAFS_CUDA_TRY(h2d(d_nz_off, mp->nz_off, sizeof(int64_t) * (npairs + 1)));
+  DAFS_CUDA_TRY(h2d(d_b_row_off, b_row_off.data(), sizeof(int64_t) * (n + 1)));
+  DAFS_CUDA_TRY(h2d(d_b_nz_off, bp->nz_off, sizeof(int64_t) * (n + 1)));
+  DAFS_CUDA_TRY(h2d(d_rp, mp->row_ptr, sizeof(int) * RU));
+  DAFS_CUDA_TRY(h2d(d_col, mp->col, sizeof(uint32_t) * mp_nnz));
+  DAFS_CUDA_TRY(h2d(d_val, mp->val, sizeof(float) * mp_nnz));
+  DAFS_CUDA_TRY(h2d(d_b_rp, bp->row_ptr, sizeof(int) * b_row_off[n]));
+  DAFS_CUDA_TRY(h2d(d_b_col, bp->col, sizeof(uint32_t) * bp_nnz));
+  DAFS_CUDA_TRY(h2d(d_b_val, bp->val, sizeof(float) * bp_nnz));
+  DAFS_CUDA_TRY(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
+  if (npairs) prog_validate_kernel<<<grid_for(npairs, 4), 128, 0, st>>>(npairs, d_u_row_off, d_nz_off, d_rp, d_col, d_ncols, d_bad);
+  prog_validate_kernel<<<grid_for(n, 4), 128, 0, st>>>(n, d_b_row_off, d_b_nz_off, d_b_rp, d_b_col, d_len, d_bad);
+  int bad = 0;
+  DAFS_CUDA_TRY(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+  DAFS_CUDA_TRY(cudaStreamSynchronize(st));
+  if (bad) return fail(DAFS_CUDA_EINVAL, "mp / bp is not a well-formed row-sparse batch (row_ptr, ascending columns, column range)");
+  int launches = 2;
+  if (npairs) {
+    prog_transpose_kernel<<<grid_for(npairs, 4), 128, 0, st>>>(n, d_len, npairs, d_pairs, d_u_row_off, d_t_row_off, d_nz_off, d_rp,
+                                                               d_col, d_val, d_rp + RU, d_col + mp_nnz, d_val + mp_nnz, d_fill);
+    ++launches;
+  }
+  prog_desc_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(n, d_u_row_off, d_t_row_off, d_nz_off, RU, mp_nnz, d_desc);
+  ++launches;
+  DAFS_CUDA_TRY(cudaGetLastError());
+  A.len = d_len; A.rp_all = d_rp; A.col_all = d_col; A.val_all = d_val; A.desc = d_desc;
+  A.b_row_off = d_b_row_off; A.b_nz_off = d_b_nz_off; A.b_row_ptr = d_b_rp; A.b_col = d_b_col; A.b_val = d_b_val;
+
+  // ---- waves ----------------------------------------------------------------------
+  std::vector<Aln> aln(nn);
+  for (int s = 0; s < n; ++s) {             // leaves, :1520-1526
+    aln[s].L = len[s]; aln[s].seq.assign(1, s); aln[s].bits.assign(len[s], 1); aln[s].built = true;
+  }
+  ResultOwner* R = new ResultOwner();
+  struct OwnerGuard { ResultOwner*& r; ~OwnerGuard() { delete r; } } og{R};
+  R->node_iters.assign(nn, 0); R->node_L.assign(nn, 0); R->node_violated.assign(nn, 0); R->node_score.assign(nn, 0.0f);
+  for (int s = 0; s < n; ++s) R->node_L[s] = len[s];
+  const int max_level = level[nn - 1];
+  float ms_avg = 0.0f, ms_dd = 0.0f;
+  double ms_dd_host = 0.0;
+  int64_t total_iters = 0;
+  float root_score = 0.0f;
+  for (int lv = 1; lv <= max_level; ++lv) {
+    std::vector<int> wave;
+    for (int k = n; k < nn; ++k) if (level[k] == lv) wave.push_back(k);
+    const int W = (int)wave.size();
+    // sides, members and maps of the wave
+    std::vector<ProgSide> sides((size_t)2 * W);
+    std::vector<ProgNode> nodes(W);
+    std::vector<int> mem_seq;
+    std::vector<int64_t> mem_col, mem_inv;
+    std::vector<int> maps;
+    std::vector<int2> bp_tasks, mp_tasks;
+    int64_t dense = 0;
+    int accW = 32;
+    for (int q = 0; q < W; ++q) {
+      const int k = wave[q];
+      for (int sd = 0; sd < 2; ++sd) {
+        const Aln& a = aln[sd == 0 ? left[k] : right[k]];
+        ProgSide& S = sides[2 * q + sd];
+        S.L = a.L; S.rows = (int)a.seq.size(); S.mem0 = (int)mem_seq.size(); S.pad = 0; S.out = dense;
+        dense += (int64_t)a.L * a.L;
+        accW = std::max(accW, (a.L + 31) & ~31);
+        for (int r = 0; r < S.rows; ++r) {
+          const int s = a.seq[r];
+          mem_seq.push_back(s);
+          mem_col.push_back((int64_t)maps.size());
+          const uint8_t* g = a.bits.data() + (size_t)r * a.L;
+          for (int c = 0; c < a.L; ++c) if (g[c]) maps.push_back(c);
+          mem_inv.push_back((int64_t)maps.size());
+          int ii = 0;
+          for (int c = 0; c < a.L; ++c) maps.push_back(g[c] ? ii++ : -1);
+          if (ii != len[s]) return fail(DAFS_CUDA_ECUDA, "internal: alignment row of sequence %d holds %d residues", s, ii);
+        }
+        for (int c = 0; c < a.L; ++c) bp_tasks.push_back(make_int2(2 * q + sd, c));
+      }
+      nodes[q].side1 = 2 * q; nodes[q].side2 = 2 * q + 1; nodes[q].pad0 = nodes[q].pad1 = 0; nodes[q].out = dense;
+      dense += (int64_t)sides[2 * q].L * sides[2 * q + 1].L;
+      for (int c = 0; c < sides[2 * q].L; ++c) mp_tasks.push_back(make_int2(q, c));
+    }
+    int wpb = 8;
+    while (wpb > 1 && (size_t)wpb * accW * sizeof(float) > (size_t(96) << 10)) wpb /= 2;
+    const size_t smem = (size_t)wpb * accW * sizeof(float);
+    if (smem > (size_t(227) << 10)) return fail(DAFS_CUDA_EINVAL, "alignment of %d columns is too long for the averaging kernels", accW);
+    if (smem > (48 << 10)) {
+      DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    DevBufs WB;                                   // the wave's device buffers
+    ProgSide* d_sides = nullptr; ProgNode* d_nodes = nullptr; int* d_mem_seq = nullptr; int64_t* d_mem_col = nullptr;
+    int64_t* d_mem_inv = nullptr; int* d_maps = nullptr; int2* d_bp_tasks = nullptr; int2* d_mp_tasks = nullptr; float* d_dense = nullptr;
+    DAFS_CUDA_TRY(WB.get(&d_sides, sides.size()));
+    DAFS_CUDA_TRY(WB.get(&d_nodes, nodes.size()));
+    DAFS_CUDA_TRY(WB.get(&d_mem_seq, mem_seq.size()));
+    DAFS_CUDA_TRY(WB.get(&d_mem_col, mem_col.size()));
+    DAFS_CUDA_TRY(WB.get(&d_mem_inv, mem_inv.size()));
+    DAFS_CUDA_TRY(WB.get(&d_maps, maps.size()));
+    DAFS_CUDA_TRY(WB.get(&d_bp_tasks, bp_tasks.size()));
+    DAFS_CUDA_TRY(WB.get(&d_mp_tasks, mp_tasks.size()));
+    DAFS_CUDA_TRY(WB.get(&d_dense, (size_t)dense));
+    DAFS_CUDA_TRY(h2d(d_sides, sides.data(), sizeof(ProgSide) * sides.size()));
+    DAFS_CUDA_TRY(h2d(d_nodes, nodes.data(), sizeof(ProgNode) * nodes.size()));
+    DAFS_CUDA_TRY(h2d(d_mem_seq, mem_seq.data(), sizeof(int) * mem_seq.size()));
+    DAFS_CUDA_TRY(h2d(d_mem_col, mem_col.data(), sizeof(int64_t) * mem_col.size()));
+    DAFS_CUDA_TRY(h2d(d_mem_inv, mem_inv.data(), sizeof(int64_t) * mem_inv.size()));
+    DAFS_CUDA_TRY(h2d(d_maps, maps.data(), sizeof(int) * maps.size()));
+    DAFS_CUDA_TRY(h2d(d_bp_tasks, bp_tasks.data(), sizeof(int2) * bp_tasks.size()));
+    DAFS_CUDA_TRY(h2d(d_mp_tasks, mp_tasks.data(), sizeof(int2) * mp_tasks.size()));
+    A.sides = d_sides; A.nodes = d_nodes; A.mem_seq = d_mem_seq; A.mem_col = d_mem_col; A.mem_inv = d_mem_inv;
+    A.maps = d_maps; A.dense = d_dense;
+    DAFS_CUDA_TRY(cudaEventRecord(G.a, st));
+    prog_avg_bp_kernel<<<grid_for((int64_t)bp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)bp_tasks.size(), d_bp_tasks, accW);
+    prog_avg_mp_kernel<<<grid_for((int64_t)mp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)mp_tasks.size(), d_mp_tasks, accW);
+    launches += 2;
+    DAFS_CUDA_TRY(cudaGetLastError());
+    DAFS_CUDA_TRY(cudaEventRecord(G.b, st));
+    PinGuard H;
+    H.p = pinned_alloc(sizeof(float) * (size_t)dense);
+    if (!H.p) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %lld floats failed", (long long)dense);
+    float* h_dense = static_cast<float*>(H.p);
+    DAFS_CUDA_TRY(cudaMemcpyAsync(h_dense, d_dense, sizeof(float) * (size_t)dense, cudaMemcpyDeviceToHost, st));
+    DAFS_CUDA_TRY(cudaStreamSynchronize(st));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, G.a, G.b);
+    ms_avg += ms;
+
+    // the wave's DD problems, solved in one batch (solve_by_dd, :1006-1295)
+    const double t_dd0 = now_ms();
+    std::vector<dafs_dd_problem> prob(W);
+    std::vector<dafs_dd_result> res(W);
+    std::vector<std::vector<uint32_t>> xs(W), ys(W), zs(W);
+    for (int q = 0; q < W; ++q) {
+      const ProgSide& S1 = sides[2 * q];
+      const ProgSide& S2 = sides[2 * q + 1];
+      dafs_dd_problem& P = prob[q];
+      P.L1 = S1.L; P.L2 = S2.L; P.N1 = S1.rows; P.N2 = S2.rows;
+      P.p_x = h_dense + S1.out; P.p_y = h_dense + S2.out; P.p_z = h_dense + nodes[q].out;
+      P.w = prm->w; P.th_s = prm->th_s; P.min_th_s = prm->min_th_s; P.th_a = prm->th_a; P.eta0 = prm->eta0; P.t_max = prm->t_max;
+      xs[q].assign(S1.L, kNone); ys[q].assign(S2.L, kNone); zs[q].assign(S1.L, kNone);
+      res[q] = dafs_dd_result{};
+      res[q].x = xs[q].data(); res[q].y = ys[q].data(); res[q].z = zs[q].data();
+    }
+    {
+      PlanGuard PG;
+      int rc = dafs_cuda_dd_plan_create(W, prob.data(), 0, &PG.p);
+      if (!rc) rc = dafs_cuda_dd_plan_run(PG.p);
+      float dms = 0.0f;
+      if (!rc) rc = dafs_cuda_dd_plan_sync(PG.p, &dms);
+      if (!rc) rc = dafs_cuda_dd_plan_fetch(PG.p, res.data());
+      if (rc) return rc;
+      ms_dd += dms;
+      launches += 1;
+    }
+    ms_dd_host += now_ms() - t_dd0;
+    for (int q = 0; q < W; ++q) {
+      const int k = wave[q];
+      if (res[q].status != 0) return fail(DAFS_CUDA_ECUDA, "node %d: the alignment traceback left the envelope (the reference would not terminate)", k);
+      const Aln& a1 = aln[left[k]];
+      const Aln& a2 = aln[right[k]];
+      merge(aln[k], a1, a2, zs[q].data());
+      R->node_iters[k] = res[q].iters; R->node_violated[k] = res[q].violated; R->node_score[k] = res[q].score;
+      R->node_L[k] = aln[k].L;
+      total_iters += res[q].iters;
+      if (k == nn - 1) {
+        consensus(R->ss, aln[k].L, xs[q].data(), a1.L, ys[q].data(), a2.L, zs[q].data());
+        root_score = res[q].score;
+      }
+    }
+    for (int q = 0; q < W; ++q) {                 // children are no longer needed
+      Aln().bits.swap(aln[left[wave[q]]].bits);
+      Aln().bits.swap(aln[right[wave[q]]].bits);
+    }
+  }
+  const Aln& root = aln[nn - 1];
+  R->seq.assign(root.seq.begin(), root.seq.end());
+  R->bits = root.bits;
+  out->L = root.L; out->n_rows = n;
+  out->seq = R->seq.data(); out->bits = R->bits.data();
+  out->ss = R->ss.empty() ? nullptr : R->ss.data();
+  out->score = root_score;
+  out->n_nodes = nn;
+  out->node_iters = R->node_iters.data(); out->node_violated = R->node_violated.data();
+  out->node_score = R->node_score.data(); out->node_L = R->node_L.data();
+  out->waves = max_level; out->total_iters = total_iters; out->gpu_launches = launches;
+  out->ms_average = ms_avg; out->ms_dd = ms_dd; out->ms_dd_host = (float)ms_dd_host;
+  out->ms_total = (float)(now_ms() - t_begin);
+  out->owner_ = R;
+  R = nullptr;
+  return DAFS_CUDA_OK;
+}

@@ -11,6 +11,10 @@
  *         replaces DAFS::solve_by_dd                      src/dafs.cpp:1006-1295
  *         SparseNussinov::decode                          src/nussinov.cpp:207-392
  *         SparseNeedlemanWunsch::initialize/decode        src/needleman_wunsch.cpp:198-422
+ *   (4) the consistency transformation of DAFS::run()     src/dafs.cpp:1796-1827
+ *   (5) the progressive alignment along the guide tree
+ *         replaces DAFS::build_tree                       src/dafs.cpp:447-495
+ *         and DAFS::align(ss, aln, root)                  src/dafs.cpp:1518-1537
  *
  * Plain C types only.  Every entry point returns 0 on success or a negative
  * DAFS_CUDA_E* code; dafs_cuda_last_error() gives the message (thread-local).
@@ -253,6 +257,61 @@ int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp, const dafs
 /* Device time of the kernels of the last dafs_cuda_pct call on this thread, in ms:
  * {transpose, similarity, relax_bp, relax_mp, total incl. H2D/D2H}.              */
 void dafs_cuda_pct_last_ms(float out5[5]);
+
+/* ---- (5) progressive alignment along the guide tree ---------------------------
+ * dafs_cuda_guide_tree: DAFS::build_tree (src/dafs.cpp:447-495) from the similarity
+ * matrix sim[nseq*nseq] (what dafs_cuda_pct returns).  Nodes 0..nseq-1 are the leaves
+ * (left = right = -1), nodes nseq..2*nseq-2 the merges in the order they were made, the
+ * last one the root; score[k] = tree_[k].first (may be NULL).  Host arithmetic only.   */
+int dafs_cuda_guide_tree(int nseq, const float* sim, int32_t* left, int32_t* right, float* score);
+
+/* dafs_cuda_progressive: DAFS::align(ss, aln, root) (src/dafs.cpp:1518-1537), i.e. for
+ * every internal node align_alignments (:913-951): average_basepairing_probability of both
+ * children (:557-607), average_matching_probability (:513-555), solve_by_dd (:1006-1295),
+ * project_alignment (:766-826); for the root also project_secondary_structure (:828-876)
+ * and the consensus (:941-945).  Nodes whose children are finished are processed together
+ * (one averaging launch pair + one batched DD launch per wave); sibling subtrees share no
+ * state, so the results equal the reference's depth-first recursion bit for bit.
+ * Covers use_alifold_ == false (--no-alifold; RNAalifold needs ViennaRNA) and
+ * use_bp_update_ == false (the default).
+ *   mp, bp   what DAFS::run() holds at :1829: all i<j pairs / one unit per sequence,
+ *            e.g. the outputs of dafs_cuda_pct
+ *   left/right  the guide tree, 2*nseq-1 nodes as dafs_cuda_guide_tree returns them
+ *   prm      w = w_ (-w), th_s = th_s_[0] (-t), min_th_s = min(th_s_), th_a = th_a_ (-u),
+ *            eta0 = eta0_ (--eta), t_max = t_max_ (-m)                                  */
+typedef struct dafs_prog_params {
+  float w, th_s, min_th_s, th_a, eta0;
+  int32_t t_max;
+} dafs_prog_params;
+
+typedef struct dafs_prog_result {
+  int32_t L;                 /* columns of the root alignment                            */
+  int32_t n_rows;            /* = nseq                                                   */
+  const int32_t* seq;        /* [n_rows] ALN row r is sequence seq[r] (the reference's row
+                                order: rows of the left child, then of the right child)   */
+  const uint8_t* bits;       /* [n_rows * L] ALN[r].second: 1 = residue, 0 = gap          */
+  const uint32_t* ss;        /* [L] consensus structure of the root (partner column or
+                                0xffffffff); NULL when nseq == 1                          */
+  float score;               /* align()'s return value: the root's solve_by_dd score      */
+  int32_t n_nodes;           /* 2*nseq-1; the arrays below are indexed by tree node       */
+  const int32_t* node_iters; /* what solve_by_dd logs at :1292 (leaves: 0)                */
+  const uint32_t* node_violated;
+  const float* node_score;
+  const int32_t* node_L;     /* alignment columns of the node                             */
+  int32_t waves;             /* batched DD launches = height of the tree                  */
+  int64_t total_iters;
+  int32_t gpu_launches;
+  float ms_average;          /* device time of the averaging kernels, all waves           */
+  float ms_dd;               /* device time of the DD kernel, all waves                   */
+  float ms_dd_host;          /* wall time of the DD plans incl. host set-up and copies    */
+  float ms_total;            /* wall time of the call                                     */
+  void* owner_;              /* private                                                   */
+} dafs_prog_result;
+
+int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
+                          const int32_t* left, const int32_t* right, const dafs_prog_params* prm,
+                          dafs_prog_result* out);
+void dafs_cuda_free_prog_result(dafs_prog_result* r);
 
 #ifdef __cplusplus
 }
