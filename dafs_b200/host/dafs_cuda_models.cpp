@@ -238,4 +238,45 @@ void consistency_transform(const std::vector<Fasta>& fa, std::vector<std::vector
   dafs_cuda_free_batch(&ob);
 }
 
+void build_tree(const VVF& sim, std::vector<TreeNode>& tree) {
+  const uint N = sim.size();
+  std::vector<float> s = flatten(sim, N);
+  std::vector<int32_t> left(2 * N - 1), right(2 * N - 1);
+  std::vector<float> score(2 * N - 1);
+  if (dafs_cuda_guide_tree((int)N, s.data(), left.data(), right.data(), score.data()) != DAFS_CUDA_OK)
+    fail("dafs_cuda_guide_tree");
+  tree.resize(2 * N - 1);
+  for (uint k = 0; k != 2 * N - 1; ++k)      // leaves keep (0.0, (-1u, -1u)) like src/dafs.cpp:452
+    tree[k] = std::make_pair(score[k], std::make_pair((uint)left[k], (uint)right[k]));
+}
+
+float align_tree(const DDOptions& o, const std::vector<Fasta>& fa, const std::vector<std::vector<MP> >& mp,
+                 const std::vector<BP>& bp, const std::vector<TreeNode>& tree, VU& ss, ALN& aln) {
+  const uint N = fa.size();
+  std::vector<int> len(N);
+  PackedBatch pm, pb;
+  for (uint i = 0; i != N; ++i) {
+    len[i] = (int)fa[i].size();
+    pb.add(bp[i]);
+    for (uint j = i + 1; j != N; ++j) pm.add(mp[i][j]);
+  }
+  std::vector<int32_t> left(tree.size()), right(tree.size());
+  for (size_t k = 0; k != tree.size(); ++k) { left[k] = (int32_t)tree[k].second.first; right[k] = (int32_t)tree[k].second.second; }
+  dafs_prog_params prm;
+  prm.w = o.w; prm.th_s = o.th_s[0]; prm.min_th_s = *std::min_element(o.th_s.begin(), o.th_s.end());
+  prm.th_a = o.th_a; prm.eta0 = o.eta0; prm.t_max = (int32_t)o.t_max;
+  dafs_prog_result r;
+  if (dafs_cuda_progressive((int)N, len.data(), pm.finish(), pb.finish(), left.data(), right.data(), &prm, &r) != DAFS_CUDA_OK)
+    fail("dafs_cuda_progressive");
+  aln.resize(r.n_rows);
+  for (int q = 0; q < r.n_rows; ++q) {
+    aln[q].first = (uint)r.seq[q];
+    aln[q].second.assign(r.bits + (size_t)q * r.L, r.bits + (size_t)(q + 1) * r.L);
+  }
+  if (r.ss) ss.assign(r.ss, r.ss + r.L);      // a single sequence leaves ss untouched, like align()
+  const float s = r.score;
+  dafs_cuda_free_prog_result(&r);
+  return s;
+}
+
 }  // namespace dafs_cuda

@@ -5,6 +5,8 @@
 //   CudaNussinov          : Fold::Decoder   (src/fold.h:47-60)    replaces SparseNussinov (src/nussinov.cpp:207-413)
 //   CudaNeedlemanWunsch   : Align::Decoder  (src/align.h:57-65)   replaces SparseNeedlemanWunsch (src/needleman_wunsch.cpp:198-422)
 //   dafs_cuda::solve_by_dd, solve_by_dd_batch                     replace DAFS::solve_by_dd (src/dafs.cpp:1006-1295)
+//   dafs_cuda::consistency_transform                              replaces src/dafs.cpp:1797-1827 of DAFS::run()
+//   dafs_cuda::build_tree, align_tree                             replace DAFS::build_tree / DAFS::align (src/dafs.cpp:447-495, 1518-1537)
 // This header is compiled inside the reference tree (it includes align.h and
 // fold.h from there); see INTEGRATION.md for the three-line patch of
 // DAFS::parse_options / DAFS::solve_by_dd.  Errors from the C ABI are re-thrown
@@ -96,6 +98,16 @@ void solve_by_dd_batch(const DDOptions& o, const std::vector<DDInput>& in, std::
 // on return mp[i][j] is filled for all i, j, bp and sim as the reference leaves them.
 void consistency_transform(const std::vector<Fasta>& fa, std::vector<std::vector<MP> >& mp, std::vector<BP>& bp,
                            float w_pct_a, float w_pct_s, VVF& sim);
+
+// Drop-in for build_tree() + align(ss, aln, root) of DAFS::run() (src/dafs.cpp:1829-1838,
+// :447-495, :1518-1537) when use_alifold_ and use_bp_update_ are off (--no-alifold): all
+// guide-tree nodes whose children are finished are solved in one device wave.  tree is
+// DAFS::tree_ (vector<pair<float, pair<uint, uint>>>), filled like build_tree() fills it;
+// ss / aln / the return value are what align(ss, aln, tree_.size() - 1) yields.
+typedef std::pair<float, std::pair<uint, uint> > TreeNode;
+void build_tree(const VVF& sim, std::vector<TreeNode>& tree);
+float align_tree(const DDOptions& o, const std::vector<Fasta>& fa, const std::vector<std::vector<MP> >& mp,
+                 const std::vector<BP>& bp, const std::vector<TreeNode>& tree, VU& ss, ALN& aln);
 
 }  // namespace dafs_cuda
 

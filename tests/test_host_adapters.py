@@ -22,5 +22,6 @@ def test_adapters_cover_every_compute_entry_point():
     """Every compute call of the header is reachable from the C++ glue or documented as plan-level API."""
     src = open(os.path.join(ROOT, "dafs_b200", "host", "dafs_cuda_models.cpp")).read()
     for sym in ("dafs_cuda_pairhmm_all", "dafs_cuda_pairhmm_pairs", "dafs_cuda_mccaskill_all", "dafs_cuda_dd_solve_batch",
-                "dafs_cuda_nussinov_decode", "dafs_cuda_nw_decode", "dafs_cuda_pct"):
+                "dafs_cuda_nussinov_decode", "dafs_cuda_nw_decode", "dafs_cuda_pct", "dafs_cuda_guide_tree",
+                "dafs_cuda_progressive"):
         assert sym in src, sym
