@@ -158,6 +158,24 @@ void dev_trim() {
   cudaSetDevice(cur);
 }
 
+cudaError_t dev_info(int device, DevInfo* out) {
+  static std::mutex mu;
+  static DevInfo cache[64];
+  static bool have[64] = {false};
+  std::lock_guard<std::mutex> g(mu);
+  const int k = device & 63;
+  if (!have[k]) {
+    int sms = 0, smem = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e != cudaSuccess) return e;
+    cache[k].sms = sms; cache[k].smem_optin = (size_t)smem;
+    have[k] = true;
+  }
+  *out = cache[k];
+  return cudaSuccess;
+}
+
 // FP32 issue-rate probe: 8 independent chains per thread, 4 CTAs of 256 per SM.
 // FMA = true counts 2 flop per FFMA; false issues FMUL + FADD (what the bit-exact
 // pair-HMM arithmetic is restricted to, pairhmm_math.cuh) and counts 1 each.

@@ -39,6 +39,11 @@ template <class T> inline cudaError_t dev_malloc(T** out, size_t bytes) { return
 void dev_free(void* p);
 void dev_trim();
 
+// SM count and opt-in shared memory per block of a device, queried once
+// (cudaGetDeviceProperties costs about a millisecond per call, per-call plans pay it).
+struct DevInfo { int sms; size_t smem_optin; };
+cudaError_t dev_info(int device, DevInfo* out);
+
 // Symbol classes of the ProbCons alphabet "ACGUTN" (probconsRNA/Defaults.h:28,
 // wrapper.cpp:158-170).  U and T rows of the reference's tables are identical,
 // so they share class 3; 4 = N; 5 = every other byte (1e-10 / 1e-5 emissions).

@@ -87,7 +87,8 @@ static void pack_nus(NusHost& H, std::vector<char>& cst, int L, float w, std::ve
   for (int e = 0; e < nd; ++e) {
     const int a = rowmap[ents[e].i], b = (int)colmap[ents[e].j] - 1;
     ab[e] = (uint32_t)a | ((uint32_t)b << 16);
-    ent_c[e] = ents[e].i >= 1 ? (int)colmap[ents[e].i - 1] - 1 : -1;   // last live column <= i-1
+    // live row a in the high half; low half: 1 + (last live column <= i-1), 0 if none
+    ent_c[e] = (a << 16) | (ents[e].i >= 1 ? (int)colmap[ents[e].i - 1] : 0);
     col_ptr[b + 1]++; row_ptr[a + 1]++;
   }
   for (int b = 0; b < nJ; ++b) { max_col = std::max(max_col, col_ptr[b + 1]); col_ptr[b + 1] += col_ptr[b]; }
@@ -481,9 +482,9 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   PLAN_TRY(cudaMemcpy(p->d_order, order.data(), sizeof(int32_t) * nprob, cudaMemcpyHostToDevice));
 
   // geometry
-  cudaDeviceProp prop;
-  PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
-  const size_t budget = (size_t)prop.sharedMemPerBlockOptin - 2048;
+  dafs::DevInfo prop;
+  PLAN_TRY(dafs::dev_info(p->device, &prop));
+  const size_t budget = (size_t)prop.smem_optin - 2048;
   size_t ws_per = 0;
   plan_layout(p->lay, m, budget, &p->smem, &ws_per);
   p->all_smem = (p->lay.in_smem == (1u << DD_NITEMS) - 1u);
@@ -497,7 +498,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   }
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
   p->ctas_per_sm = blocks;
-  p->grid = std::max(1, std::min(nprob, prop.multiProcessorCount * blocks));
+  p->grid = std::max(1, std::min(nprob, prop.sms * blocks));
   p->lay.ws_stride = ws_per;
   PLAN_TRY(dev_malloc(&p->d_ws, ws_per * p->grid));
   p->lay.ws = p->d_ws;

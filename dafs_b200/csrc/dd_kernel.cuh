@@ -52,7 +52,7 @@ struct DDNusHdr {
   uint32_t row_ptr;            // int[nI+1]
   uint32_t row_ent;            // int[nd]     entry ids of live row a, ascending b
   uint32_t ent_ab;             // u32[nd]     a | b << 16 (live row / live column index)
-  uint32_t ent_c;              // i32[nd]     largest live column index with J <= i-1, or -1
+  uint32_t ent_c;              // i32[nd]     a << 16 | (1 + largest live column index with J <= i-1, 0 if none)
   uint32_t ent_ij;             // u32[n]      i | j << 16
   uint32_t ent_p;              // f32[n]
   uint32_t ent_flag;           // u8[n]       bit0: in c_x (dafs.cpp:1037)
@@ -242,14 +242,30 @@ __device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch&
           sc.es[e] = c;
         }
         // bifurcations: candidates of column j with k > i, in push order (:247-259)
+        // The list is in descending row order, so the candidates with k > i are a prefix.
+        // Four at a time: the packed (row, column) words and the candidate values are
+        // fetched first, the row lookups next, and only the compare chain is serial.
         const int cb = S.col_ptr[b], ce = S.col_ptr[b + 1];
-        for (int e = cb; e < ce; ++e) {
-          const int ka = (int)(S.ent_ab[e] & 0xffffu);
-          if (ka <= a) break;
-          const int cc = S.ent_c[e];
-          const float lv = (cc >= bs) ? myrow[cc] : 0.0f;    // dp[i][k-1]
-          const float c = __fadd_rn(lv, sc.es[e]);
-          if (v < c) { v = c; t = 4 + (e - cb); }
+        for (int e = cb; e < ce; e += 4) {
+          int w[4]; float sv[4], lv[4]; bool ok[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const bool in = e + u < ce;
+            w[u] = in ? S.ent_c[e + u] : 0;                  // row 0 is never below a live row
+            sv[u] = in ? sc.es[e + u] : 0.0f;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            ok[u] = (w[u] >> 16) > a;
+            const int cc = (w[u] & 0xffff) - 1;
+            lv[u] = (ok[u] && cc >= bs) ? myrow[cc] : 0.0f;  // dp[i][k-1]
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float c = __fadd_rn(lv[u], sv[u]);
+            if (ok[u] && v < c) { v = c; t = 4 + (e + u - cb); }
+          }
+          if (!ok[3]) break;
         }
         myrow[b] = v;
         nus_tr_store(sc, a * trs + b, t, !(below < v));

@@ -200,11 +200,11 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   for (int i = 0; i < nseq; ++i) order[i] = i;
   std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return len[a] > len[b]; });
 
-  cudaDeviceProp prop;
-  PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
+  dafs::DevInfo prop;
+  PLAN_TRY(dafs::dev_info(p->device, &prop));
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
   p->smem = (int)(tab_bytes + sizeof(double) * MC_CGEN_ROWS * 32 + 2 * sizeof(double) * (p->W + 2) + p->W + 16);
-  if ((size_t)p->smem > prop.sharedMemPerBlockOptin)
+  if ((size_t)p->smem > prop.smem_optin)
     return bail(fail(DAFS_CUDA_ENOTSUP, "sequence of %d nt needs %d bytes of shared memory", maxn, p->smem));
   PLAN_TRY(cudaFuncSetAttribute(mccaskill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   int blocks = 0;
@@ -218,7 +218,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   // CTAs per sequence: a lone CTA when there is at least one sequence per SM slot,
   // otherwise the largest portable cluster (2, 4, 8) that still gives every
   // sequence a team; DAFS_MCCASKILL_CLUSTER overrides (tuning knob).
-  const int slots = prop.multiProcessorCount * blocks;
+  const int slots = prop.sms * blocks;
   int nc = 1;
   while (nc < 8 && (int64_t)nseq * nc * 2 <= slots) nc *= 2;
   if (const char* e = getenv("DAFS_MCCASKILL_CLUSTER")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) nc = v; }

@@ -66,9 +66,12 @@ static float compute_xcut(float th) {
 
 // ---- small helper kernels ---------------------------------------------------
 // Exclusive scan of per-pair nnz -> nz_off[npairs+1]; one block.
-__global__ void scan_nnz_kernel(const int32_t* __restrict__ nnz, int n, int64_t* __restrict__ off) {
+// has_base: the range continues a scan, off[0] already holds its start (chunked runs).
+__global__ void scan_nnz_kernel(const int32_t* __restrict__ nnz, int n, int64_t* __restrict__ off, int has_base) {
   __shared__ long long part[1024];
   const int t = threadIdx.x, T = blockDim.x;
+  const long long base = has_base ? off[0] : 0;
+  __syncthreads();
   const int per = (n + T - 1) / T;
   const int b = min(n, t * per), e = min(n, b + per);
   long long s = 0;
@@ -76,7 +79,7 @@ __global__ void scan_nnz_kernel(const int32_t* __restrict__ nnz, int n, int64_t*
   part[t] = s;
   __syncthreads();
   if (t == 0) {
-    long long run = 0;
+    long long run = base;
     for (int k = 0; k < T; ++k) { const long long v = part[k]; part[k] = run; run += v; }
     off[n] = run;
   }
@@ -124,6 +127,15 @@ struct dafs_pairhmm_plan {
   uint32_t* d_pool_col = nullptr; float* d_pool_val = nullptr; int64_t pool_cap = 0;
   int64_t* d_pair_pool_off = nullptr; int32_t* d_pair_nnz = nullptr; float* d_pair_total = nullptr;
   int64_t* d_nz_off = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
+  // The pair list is run as up to kMaxChunks consecutive launches (whole rounds of the
+  // resident warps each), so that fetch() can copy the CSR of a finished chunk to the
+  // host while the next chunk computes.
+  int nchunks = 1;
+  int chunk_k0[5] = {0, 0, 0, 0, 0};
+  cudaEvent_t ev_chunk[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t evck0[4] = {nullptr, nullptr, nullptr, nullptr}, evck1[4] = {nullptr, nullptr, nullptr, nullptr};
+  int64_t* h_chunk_end = nullptr;   // pinned: nz_off at the end of each chunk
+  cudaStream_t copy_stream = nullptr;
   bool launched = false;
   int64_t nnz = -1;
   float last_ms = 0, last_kernel_ms = 0;
@@ -148,6 +160,13 @@ static void free_plan_buffers(dafs_pairhmm_plan* p) {
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->evk0) cudaEventDestroy(p->evk0);
   if (p->evk1) cudaEventDestroy(p->evk1);
+  for (int c = 0; c < 4; ++c) {
+    if (p->ev_chunk[c]) cudaEventDestroy(p->ev_chunk[c]);
+    if (p->evck0[c]) cudaEventDestroy(p->evck0[c]);
+    if (p->evck1[c]) cudaEventDestroy(p->evck1[c]);
+  }
+  if (p->h_chunk_end) pinned_free(p->h_chunk_end);
+  if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 
@@ -202,30 +221,37 @@ static int launch_all(dafs_pairhmm_plan* p) {
   a.pool_count = p->d_pool_count; a.pool_col = p->d_pool_col; a.pool_val = p->d_pool_val;
   a.pool_cap = p->pool_cap;
   a.pair_pool_off = p->d_pair_pool_off; a.pair_nnz = p->d_pair_nnz; a.pair_total = p->d_pair_total;
-  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_pool_count, 0, sizeof(unsigned long long), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  DAFS_CUDA_TRY(cudaEventRecord(p->evk0, p->stream));
-  cudaError_t e;
-  switch (p->C) {
-    case 2: e = launch_pairhmm<2>(a, p->grid, p->stream); break;
-    case 3: e = launch_pairhmm<3>(a, p->grid, p->stream); break;
-    case 4: e = launch_pairhmm<4>(a, p->grid, p->stream); break;
-    case 5: e = launch_pairhmm<5>(a, p->grid, p->stream); break;
-    case 6: e = launch_pairhmm<6>(a, p->grid, p->stream); break;
-    case 8: e = launch_pairhmm<8>(a, p->grid, p->stream); break;
-    case 10: e = launch_pairhmm<10>(a, p->grid, p->stream); break;
-    default: e = launch_pairhmm<12>(a, p->grid, p->stream); break;
+  for (int c = 0; c < p->nchunks; ++c) {
+    const int k0 = p->chunk_k0[c], kn = p->chunk_k0[c + 1] - k0;
+    a.order = p->d_order + k0; a.npairs = kn;
+    DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
+    DAFS_CUDA_TRY(cudaEventRecord(p->evck0[c], p->stream));
+    const int grid = (int)std::min<int64_t>(p->grid, (kn + kWarps - 1) / kWarps);
+    cudaError_t e;
+    switch (p->C) {
+      case 2: e = launch_pairhmm<2>(a, grid, p->stream); break;
+      case 3: e = launch_pairhmm<3>(a, grid, p->stream); break;
+      case 4: e = launch_pairhmm<4>(a, grid, p->stream); break;
+      case 5: e = launch_pairhmm<5>(a, grid, p->stream); break;
+      case 6: e = launch_pairhmm<6>(a, grid, p->stream); break;
+      case 8: e = launch_pairhmm<8>(a, grid, p->stream); break;
+      case 10: e = launch_pairhmm<10>(a, grid, p->stream); break;
+      default: e = launch_pairhmm<12>(a, grid, p->stream); break;
+    }
+    DAFS_CUDA_TRY(e);
+    DAFS_CUDA_TRY(cudaEventRecord(p->evck1[c], p->stream));
+    scan_nnz_kernel<<<1, 1024, 0, p->stream>>>(p->d_pair_nnz + k0, kn, p->d_nz_off + k0, c > 0);
+    DAFS_CUDA_TRY(cudaGetLastError());
+    const int gblocks = std::min(kn / 8 + 1, 148 * 8);
+    gather_csr_kernel<<<gblocks, 256, 0, p->stream>>>(kn, p->d_pair_pool_off + k0, p->d_pair_nnz + k0,
+                                                      p->d_nz_off + k0, p->d_pool_col, p->d_pool_val,
+                                                      p->d_col, p->d_val, p->pool_cap);
+    DAFS_CUDA_TRY(cudaGetLastError());
+    DAFS_CUDA_TRY(cudaMemcpyAsync(p->h_chunk_end + c, p->d_nz_off + k0 + kn, sizeof(int64_t), cudaMemcpyDeviceToHost, p->stream));
+    DAFS_CUDA_TRY(cudaEventRecord(p->ev_chunk[c], p->stream));
   }
-  DAFS_CUDA_TRY(e);
-  DAFS_CUDA_TRY(cudaEventRecord(p->evk1, p->stream));
-  scan_nnz_kernel<<<1, 1024, 0, p->stream>>>(p->d_pair_nnz, p->npairs, p->d_nz_off);
-  DAFS_CUDA_TRY(cudaGetLastError());
-  const int gblocks = std::min(p->npairs / 8 + 1, 148 * 8);
-  gather_csr_kernel<<<gblocks, 256, 0, p->stream>>>(p->npairs, p->d_pair_pool_off, p->d_pair_nnz,
-                                                    p->d_nz_off, p->d_pool_col, p->d_pool_val,
-                                                    p->d_col, p->d_val, p->pool_cap);
-  DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
   p->launched = true;
   p->nnz = -1;
@@ -278,6 +304,14 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   PLAN_TRY(cudaEventCreate(&p->ev1));
   PLAN_TRY(cudaEventCreate(&p->evk0));
   PLAN_TRY(cudaEventCreate(&p->evk1));
+  PLAN_TRY(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+  for (int c = 0; c < 4; ++c) {
+    PLAN_TRY(cudaEventCreateWithFlags(&p->ev_chunk[c], cudaEventDisableTiming));
+    PLAN_TRY(cudaEventCreate(&p->evck0[c]));
+    PLAN_TRY(cudaEventCreate(&p->evck1[c]));
+  }
+  p->h_chunk_end = static_cast<int64_t*>(pinned_alloc(64));
+  if (!p->h_chunk_end) return bail(fail(DAFS_CUDA_ENOMEM, "pinned allocation failed"));
   static bool tables_up[64] = {false};
   if (!tables_up[p->device & 63]) {
     PLAN_TRY(cudaMemcpyToSymbol(c_tab, &host_tables(), sizeof(PairHmmTables)));
@@ -306,17 +340,14 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
     est_nnz += (int64_t)l1 * std::min(l2, 10) + 64;
   }
   p->total_rows = p->row_off[npairs];
-  std::stable_sort(order.begin(), order.begin() + npairs, [&](int32_t a, int32_t b) {
-    return (int64_t)len[pi[a]] * len[pj[a]] > (int64_t)len[pi[b]] * len[pj[b]];
-  });
   p->C = choose_cols(max_l2);
   const int sw = 32 * p->C;
   const int64_t pw = (int64_t)((max_l2 + 1 + sw - 1) / sw) * sw;
   p->plane_stride = (int64_t)(max_l1 + 32) * pw;     // pipeline-order plane: L1 + 32 steps per stripe
   p->bnd_stride = max_l1 + 1;
-  cudaDeviceProp prop;
-  PLAN_TRY(cudaGetDeviceProperties(&prop, p->device));
-  const int max_grid = prop.multiProcessorCount * kMinBlocks;
+  dafs::DevInfo prop;
+  PLAN_TRY(dafs::dev_info(p->device, &prop));
+  const int max_grid = prop.sms * kMinBlocks;
   p->grid = (int)std::max<int64_t>(1, std::min<int64_t>(max_grid, (npairs + kWarps - 1) / kWarps));
   {
     // three planes per warp slot; long sequences get fewer resident CTAs rather
@@ -330,6 +361,27 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   }
   if (max_l1 > 65534 || max_l2 > 65534) return bail(fail(DAFS_CUDA_EINVAL, "sequences longer than 65534 are not supported"));
   const int64_t slots = (int64_t)p->grid * kWarps;
+  // chunks: whole rounds of the resident warps, the last (whose copy is not hidden) the smallest;
+  // inside a chunk the queue hands out the most expensive pairs first
+  {
+    const int64_t rounds = (npairs + slots - 1) / slots;
+    int want = rounds >= 6 ? 3 : 1;
+    if (const char* e = getenv("DAFS_PAIRHMM_CHUNKS")) want = std::max(1, std::min(4, atoi(e)));
+    if (rounds < want) want = 1;
+    p->nchunks = want;
+    int64_t k0 = 0, left_rounds = rounds;
+    for (int c = 0; c < want; ++c) {
+      p->chunk_k0[c] = (int)k0;
+      const int64_t r = (left_rounds + (want - c) - 1) / (want - c);   // ceil: larger chunks first
+      k0 = std::min<int64_t>(npairs, k0 + r * slots);
+      left_rounds -= r;
+    }
+    p->chunk_k0[want] = (int)npairs;
+    for (int c = 0; c < want; ++c)
+      std::stable_sort(order.begin() + p->chunk_k0[c], order.begin() + p->chunk_k0[c + 1], [&](int32_t a, int32_t b) {
+        return (int64_t)len[pi[a]] * len[pj[a]] > (int64_t)len[pi[b]] * len[pj[b]];
+      });
+  }
 
   PLAN_TRY(dev_malloc(&p->d_seq, enc.size()));
   PLAN_TRY(dev_malloc(&p->d_seq_off, sizeof(int64_t) * (nseq + 1)));
@@ -384,7 +436,12 @@ extern "C" int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* p, float* device_m
       if (rc2) return rc2;
     }
     DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
-    DAFS_CUDA_TRY(cudaEventElapsedTime(&p->last_kernel_ms, p->evk0, p->evk1));
+    p->last_kernel_ms = 0.0f;
+    for (int c = 0; c < p->nchunks; ++c) {
+      float ms = 0.0f;
+      DAFS_CUDA_TRY(cudaEventElapsedTime(&ms, p->evck0[c], p->evck1[c]));
+      p->last_kernel_ms += ms;
+    }
   }
   if (device_ms) *device_ms = p->last_ms;
   if (nnz) *nnz = p->nnz;
@@ -396,47 +453,86 @@ extern "C" int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* p, dafs_pairhmm_in
   info->cols_per_lane = p->C; info->grid = p->grid; info->warps_per_cta = dafs::kWarps;
   info->workspace_bytes = (int64_t)sizeof(float) * 3 * p->plane_stride * p->grid * dafs::kWarps;
   info->last_total_ms = p->last_ms; info->last_kernel_ms = p->last_kernel_ms;
-  info->launches_per_run = 3;
+  info->launches_per_run = 3 * p->nchunks;
   return DAFS_CUDA_OK;
 }
 
 extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch* out) {
   if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   *out = dafs_csr_batch{};
-  const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
-  if (rc) return rc;
-  const int64_t np = p->npairs, nnz = p->nnz, rows = p->total_rows;
-  // one pinned block: row_off | nz_off | row_ptr | col | val
-  const size_t b_row_off = sizeof(int64_t) * (np + 1), b_nz_off = sizeof(int64_t) * (np + 1);
-  const size_t b_row_ptr = sizeof(int32_t) * rows, b_col = sizeof(uint32_t) * nnz, b_val = sizeof(float) * nnz;
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  const int64_t np = p->npairs, rows = p->total_rows;
   auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
-  const size_t total = up(b_row_off) + up(b_nz_off) + up(b_row_ptr) + up(b_col) + up(b_val);
-  char* base = (char*)dafs::pinned_alloc(total);
-  if (!base) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %zu bytes failed", total);
-  int64_t* h_row_off = (int64_t*)base;
-  int64_t* h_nz_off = (int64_t*)(base + up(b_row_off));
-  int32_t* h_row_ptr = (int32_t*)((char*)h_nz_off + up(b_nz_off));
-  uint32_t* h_col = (uint32_t*)((char*)h_row_ptr + up(b_row_ptr));
-  float* h_val = (float*)((char*)h_col + up(b_col));
-  std::memcpy(h_row_off, p->row_off.data(), b_row_off);
-  cudaError_t e = cudaSuccess;
-  if (np > 0) {
-    e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->stream);
-    if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h_row_ptr, p->d_row_ptr, b_row_ptr, cudaMemcpyDeviceToHost, p->stream);
-    if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_col, p->d_col, b_col, cudaMemcpyDeviceToHost, p->stream);
-    if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_val, p->d_val, b_val, cudaMemcpyDeviceToHost, p->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
-  } else {
-    h_nz_off[0] = 0;
+  const size_t b_row_off = sizeof(int64_t) * (np + 1), b_nz_off = sizeof(int64_t) * (np + 1);
+  const size_t b_row_ptr = sizeof(int32_t) * rows;
+  // One pinned block: row_off | nz_off | row_ptr | col | val.  When the run is still in flight
+  // and chunked, col / val are laid out for the pool capacity (an upper bound of nnz) and every
+  // chunk is copied on a second stream as soon as its CSR is assembled, under the next chunk's
+  // kernel; otherwise (already synchronised, one chunk, or the pool overflowed and the run has
+  // to be repeated) one copy after the exact size is known.
+  for (int mode = (p->nnz < 0 && p->nchunks > 1 && np > 0) ? 0 : 1; mode < 2; ++mode) {
+    int64_t cap = 0;
+    if (mode == 0) cap = p->pool_cap;
+    else {
+      const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+      if (rc) return rc;
+      cap = p->nnz;
+    }
+    const size_t b_col = sizeof(uint32_t) * cap, b_val = sizeof(float) * cap;
+    const size_t total = up(b_row_off) + up(b_nz_off) + up(b_row_ptr) + up(b_col) + up(b_val);
+    char* base = (char*)dafs::pinned_alloc(total);
+    if (!base) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %zu bytes failed", total);
+    int64_t* h_row_off = (int64_t*)base;
+    int64_t* h_nz_off = (int64_t*)(base + up(b_row_off));
+    int32_t* h_row_ptr = (int32_t*)((char*)h_nz_off + up(b_nz_off));
+    uint32_t* h_col = (uint32_t*)((char*)h_row_ptr + up(b_row_ptr));
+    float* h_val = (float*)((char*)h_col + up(b_col));
+    std::memcpy(h_row_off, p->row_off.data(), b_row_off);
+    cudaError_t e = cudaSuccess;
+    bool overflow = false;
+    if (mode == 0) {
+      int64_t beg = 0;
+      for (int c = 0; c < p->nchunks && e == cudaSuccess; ++c) {
+        e = cudaEventSynchronize(p->ev_chunk[c]);
+        if (e != cudaSuccess) break;
+        const int64_t end = p->h_chunk_end[c];
+        if (end > cap) { overflow = true; break; }
+        const int64_t r0 = p->row_off[p->chunk_k0[c]], r1 = p->row_off[p->chunk_k0[c + 1]];
+        if (r1 > r0) e = cudaMemcpyAsync(h_row_ptr + r0, p->d_row_ptr + r0, sizeof(int32_t) * (r1 - r0), cudaMemcpyDeviceToHost, p->copy_stream);
+        if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h_col + beg, p->d_col + beg, sizeof(uint32_t) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
+        if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h_val + beg, p->d_val + beg, sizeof(float) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
+        beg = end;
+      }
+      if (e == cudaSuccess && !overflow) e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->copy_stream);
+      const cudaError_t e2 = cudaStreamSynchronize(p->copy_stream);
+      if (e == cudaSuccess) e = e2;
+      if (e == cudaSuccess && !overflow) {
+        const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);   // sets nnz and the timings; the stream is idle
+        if (rc) { dafs::pinned_free(base); return rc; }
+        if (p->nnz != beg) overflow = true;                                  // cannot happen: nz_off ends at the pool count
+      }
+      if (e == cudaSuccess && overflow) { dafs::pinned_free(base); continue; }   // regrow + rerun in sync(), then one copy
+    } else if (np > 0) {
+      const int64_t nnz = p->nnz;
+      e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->stream);
+      if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h_row_ptr, p->d_row_ptr, b_row_ptr, cudaMemcpyDeviceToHost, p->stream);
+      if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_col, p->d_col, sizeof(uint32_t) * nnz, cudaMemcpyDeviceToHost, p->stream);
+      if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_val, p->d_val, sizeof(float) * nnz, cudaMemcpyDeviceToHost, p->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    } else {
+      h_nz_off[0] = 0;
+    }
+    if (e != cudaSuccess) {
+      dafs::pinned_free(base);
+      return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
+    }
+    out->n_units = np; out->nnz = p->nnz;
+    out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
+    out->col = h_col; out->val = h_val; out->owner_ = base;
+    return DAFS_CUDA_OK;
   }
-  if (e != cudaSuccess) {
-    dafs::pinned_free(base);
-    return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
-  }
-  out->n_units = np; out->nnz = nnz;
-  out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
-  out->col = h_col; out->val = h_val; out->owner_ = base;
-  return DAFS_CUDA_OK;
+  return fail(DAFS_CUDA_ECUDA, "internal: fetch fell through");
 }
 
 // Device-to-device copy of the pair-ordered CSR into caller-owned device

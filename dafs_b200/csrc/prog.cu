@@ -6,6 +6,8 @@
 // reference's depth-first recursion.  Also dafs_cuda_guide_tree (build_tree, :447-495).
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <queue>
 #include <vector>
@@ -412,6 +414,19 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
       if (rc) return rc;
       ms_dd += dms;
       launches += 1;
+      if (getenv("DAFS_PROG_VERBOSE")) {           // per-wave diagnostics for tools/prof_prog.py
+        dafs_dd_info inf{};
+        dafs_cuda_dd_plan_info(PG.p, &inf);
+        int slow = 0;
+        for (int q = 1; q < W; ++q) if (res[q].iters > res[slow].iters) slow = q;
+        const float* cy = res[slow].cycles;
+        fprintf(stderr, "[prog] wave %d: %d problems, DD %.2f ms (plan wall %.2f ms), grid %d, smem %d B, in_smem %#x, cbp %lld; slowest: L1 %d L2 %d N %d+%d iters %d cbp %lld, "
+                        "cycles/iter x %.0f+%.0f y %.0f+%.0f z %.0f+%.0f\n",
+                lv, W, dms, now_ms() - t_dd0, inf.grid, inf.smem_bytes, inf.items_in_smem, (long long)inf.total_cbp, prob[slow].L1, prob[slow].L2,
+                prob[slow].N1, prob[slow].N2, res[slow].iters, (long long)res[slow].ncbp,
+                cy[0] / std::max(1, res[slow].iters + 1), cy[1] / std::max(1, res[slow].iters + 1), cy[2] / std::max(1, res[slow].iters + 1),
+                cy[3] / std::max(1, res[slow].iters + 1), cy[4] / std::max(1, res[slow].iters + 1), cy[5] / std::max(1, res[slow].iters + 1));
+      }
     }
     ms_dd_host += now_ms() - t_dd0;
     for (int q = 0; q < W; ++q) {

@@ -22,7 +22,11 @@ tmax = int(sys.argv[4]) if len(sys.argv) > 4 else 600
 cpu_n = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 reps = int(sys.argv[6]) if len(sys.argv) > 6 else 2
 
-seqs = db.homolog_family(nseq, L, config_id=4) if mode == "family" else db.random_rna(nseq, L, config_id=4)
+if mode.endswith(".fa"):                       # a FASTA file instead of synthetic input (nseq / len ignored)
+    seqs = db.fasta_read(mode)[1]
+    nseq, L = len(seqs), max(len(q) for q in seqs)
+else:
+    seqs = db.homolog_family(nseq, L, config_id=4) if mode == "family" else db.random_rna(nseq, L, config_id=4)
 lens = np.array([len(s) for s in seqs], np.int32)
 db.init(1)
 out = {"nseq": nseq, "len": L, "mode": mode, "t_max": tmax}
