@@ -275,6 +275,8 @@ extern "C" int dafs_cuda_pairhmm_tables(float* out54) {
   return DAFS_CUDA_OK;
 }
 
+namespace dafs { static thread_local bool g_chunked_fetch = false; }
+
 extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, const int* len,
                                              int64_t npairs, const int32_t* pi, const int32_t* pj,
                                              float th, dafs_pairhmm_plan** out) {
@@ -365,7 +367,10 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   // inside a chunk the queue hands out the most expensive pairs first
   {
     const int64_t rounds = (npairs + slots - 1) / slots;
-    int want = rounds >= 6 ? 3 : 1;
+    // Chunk boundaries cost about 4 % of device time (drain and refill of the resident
+    // warps), so only the one-call entry points, whose result always goes to the host, ask
+    // for them; a split-phase plan runs as one launch unless DAFS_PAIRHMM_CHUNKS says otherwise.
+    int want = (g_chunked_fetch && rounds >= 6) ? 3 : 1;
     if (const char* e = getenv("DAFS_PAIRHMM_CHUNKS")) want = std::max(1, std::min(4, atoi(e)));
     if (rounds < want) want = 1;
     p->nchunks = want;
@@ -567,7 +572,9 @@ extern "C" int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const i
   if (!out) return fail(DAFS_CUDA_EINVAL, "out is NULL");
   *out = dafs_csr_batch{};
   dafs_pairhmm_plan* p = nullptr;
+  dafs::g_chunked_fetch = true;     // the result goes to the host: copy chunk by chunk under the kernel
   int rc = dafs_cuda_pairhmm_plan_create(nseq, seq, len, npairs, pi, pj, th, &p);
+  dafs::g_chunked_fetch = false;
   if (rc) return rc;
   rc = dafs_cuda_pairhmm_plan_run(p);
   if (!rc) rc = dafs_cuda_pairhmm_plan_fetch(p, out);

@@ -137,3 +137,35 @@ def test_bad_arguments():
         dafs_b200.pairhmm_pairs([b"ACGU", b"AC"], [0], [2], 0.01)    # pair index out of range
     with dafs_b200.pairhmm_pairs([b"ACGU"], [], [], 0.01) as b:      # empty batch
         assert b.n_units == 0 and b.nnz == 0
+
+
+def _same_batch(a, b):
+    assert a.nnz == b.nnz
+    assert np.array_equal(np.asarray(a.row_off), np.asarray(b.row_off))
+    assert np.array_equal(np.asarray(a.nz_off), np.asarray(b.nz_off))
+    assert np.array_equal(np.asarray(a.row_ptr), np.asarray(b.row_ptr))
+    assert np.array_equal(np.asarray(a.col), np.asarray(b.col))
+    assert np.array_equal(np.asarray(a.val).view(np.uint32), np.asarray(b.val).view(np.uint32))
+
+
+@pytest.mark.parametrize("th", [0.01, 1e-5])
+def test_chunked_fetch_equals_single_launch(th):
+    """The one-call entry point runs the pair list as several launches and copies finished
+    chunks to the host under the next launch; the split-phase plan runs one launch.  Same
+    bits either way (th = 1e-5 overflows the first pool estimate: regrow + rerun path), and
+    equal to the oracle on a sample of pairs."""
+    import dafs_b200 as db
+    seqs = db.random_rna(180, 30, config_id=31)
+    pi, pj = db.all_pairs(len(seqs))
+    assert len(pi) >= 6 * 148 * 16                      # enough rounds of resident warps to be chunked
+    plan = db.PairHmmPlan(seqs, pi, pj, th)
+    plan.run()
+    with plan.fetch() as single, db.pairhmm_pairs(seqs, pi, pj, th) as chunked:
+        assert plan.info()["launches_per_run"] == 3
+        _same_batch(single, chunked)
+        for u in range(0, len(pi), 331):
+            rp, col, val = chunked.unit(u)
+            orp, ocol, oval, _ = ou.oracle_pair_csr(seqs[pi[u]], seqs[pj[u]], th)
+            assert np.array_equal(rp, orp) and np.array_equal(col, ocol)
+            assert np.array_equal(val.view(np.uint32), oval.view(np.uint32))
+    plan.close()

@@ -7,8 +7,16 @@ import torch
 torch.cuda.set_device(0); torch.cuda.synchronize()
 seqs = dafs_b200.random_rna(256, 300, config_id=4)
 pi, pj = dafs_b200.all_pairs(256)
-for it in range(8):
+one_call = len(sys.argv) > 1 and sys.argv[1] == "pairs"
+for it in range(16):
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
+    if one_call:
+        with dafs_b200.pairhmm_pairs(seqs, pi, pj, 0.01) as b:
+            n = int(b.nnz)
+        torch.cuda.synchronize()
+        print("pairhmm_pairs total %.1f ms  nnz %d" % ((time.perf_counter() - t0) * 1e3, n))
+        continue
     p = dafs_b200.PairHmmPlan(seqs, pi, pj, 0.01)
     t1 = time.perf_counter()
     p.run()
