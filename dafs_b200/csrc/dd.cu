@@ -30,7 +30,7 @@ struct NusHost {
 };
 struct ProbHost {
   NusHost sx, sy;
-  int L1 = 0, L2 = 0, nb = 0, bw = 0, ncz = 0, ncbp = 0, t_max = 0;
+  int L1 = 0, L2 = 0, nb = 0, bw = 0, ncz = 0, ncbp = 0, t_max = 0, stage = 0;
   size_t z_out = 0, result = 0, trace = 0;                     // result buffer
   std::vector<char> cst;                                       // the constant block
   size_t res_bytes = 0;
@@ -287,6 +287,9 @@ static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H)
   for (size_t u = 0; u < cbp.size(); ++u)
     cb[u] = make_int4(find_ent(H.sx, cbp[u].i, cbp[u].j), find_ent(H.sy, cbp[u].k, cbp[u].l),
                       zid(cbp[u].i, cbp[u].k), zid(cbp[u].j, cbp[u].l));
+  H.cst.resize(up16(H.cst.size()));
+  h.stage = (int)H.cst.size();                 // cbp stays in HBM (dd_kernel.cuh)
+  H.stage = h.stage;
   h.cbp = (uint32_t)put(H.cst, cb.data(), cb.size());
   H.cst.resize(up16(H.cst.size()));
   h.L1 = L1; h.L2 = L2; h.nb = H.nb; h.ncz = H.ncz; h.ncbp = H.ncbp; h.t_max = q.t_max;
@@ -323,6 +326,7 @@ struct dafs_dd_plan {
   dafs::DDLayout lay{};
   int grid = 0, smem = 0, ctas_per_sm = 0;
   bool all_smem = false;
+  int team = 1;                            // warps per Nussinov structure (dd_kernel<SMEM, T>)
   int64_t total_cbp = 0, total_entries = 0;
   bool launched = false;
   float last_ms = 0;
@@ -343,7 +347,7 @@ struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nb = 1, bw = 1, ncz = 1, n
 // Scratch layout from the batch maxima: items go to shared memory in priority
 // order (enum order in dd_kernel.cuh) while they fit, the rest to the per-CTA
 // global workspace.
-static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, int* smem_bytes, size_t* ws_bytes) {
+static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, int team, int* smem_bytes, size_t* ws_bytes) {
   lay.lp1 = (m.nJx + 2) & ~1;      // even stride: lane*lp + (B0 + s - lane) hits 32 distinct banks
   lay.lp2 = (m.nJy + 2) & ~1;
   lay.trs1 = m.nJx; lay.trs2 = m.nJy;
@@ -354,8 +358,8 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
   sz[DD_CST] = (size_t)m.cst;
   sz[DD_Q_X] = 4 * (size_t)m.nx; sz[DD_Q_Y] = 4 * (size_t)m.ny; sz[DD_Q_Z] = 4 * (size_t)m.nb; sz[DD_Q_CZ] = 4 * (size_t)m.ncz;
   sz[DD_ES_X] = 4 * (size_t)m.nx; sz[DD_ES_Y] = 4 * (size_t)m.ny;
-  sz[DD_ROW_X] = 4 * (size_t)32 * lay.lp1; sz[DD_ROW_Y] = 4 * (size_t)32 * lay.lp2;
-  sz[DD_BROW_X] = 4 * (size_t)lay.lp1; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2;
+  sz[DD_ROW_X] = 4 * (size_t)32 * lay.lp1 * team; sz[DD_ROW_Y] = 4 * (size_t)32 * lay.lp2 * team;   // one wave per team warp
+  sz[DD_BROW_X] = 4 * (size_t)lay.lp1 * team; sz[DD_BROW_Y] = 4 * (size_t)lay.lp2 * team;
   sz[DD_BROW_Z] = 4 * 2 * (size_t)(m.L2 + 2);
   sz[DD_TRZ] = 8 * (size_t)(m.L1 + 1) * lay.ts;
   sz[DD_TR_X] = trb * ((size_t)m.nIx * m.nJx + 1);
@@ -385,6 +389,16 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
 }  // namespace dafs
 
 using dafs::fail;
+
+namespace dafs {
+static const void* dd_kernel_fn(bool smem, int team) {
+  switch (team) {
+    case 3: return smem ? (const void*)dd_kernel<true, 3> : (const void*)dd_kernel<false, 3>;
+    case 2: return smem ? (const void*)dd_kernel<true, 2> : (const void*)dd_kernel<false, 2>;
+    default: return smem ? (const void*)dd_kernel<true, 1> : (const void*)dd_kernel<false, 1>;
+  }
+}
+}  // namespace dafs
 
 extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
                                         dafs_dd_plan** out) {
@@ -438,7 +452,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     m.nIy = std::max(m.nIy, H.sy.h.nI); m.nJy = std::max(m.nJy, H.sy.h.nJ);
     m.nb = std::max(m.nb, H.nb); m.bw = std::max(m.bw, H.bw); m.ncz = std::max(m.ncz, H.ncz); m.ncbp = std::max(m.ncbp, H.ncbp);
     m.col = std::max(m.col, std::max(H.sx.max_col, H.sy.max_col));
-    m.cst = std::max(m.cst, (int)H.cst.size());
+    m.cst = std::max(m.cst, H.stage);
     p->total_cbp += H.ncbp; p->total_entries += H.sx.h.n + H.sy.h.n + H.nb;
   }
   p->cst_bytes = cst; p->res_bytes = res;
@@ -486,15 +500,27 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   PLAN_TRY(dafs::dev_info(p->device, &prop));
   const size_t budget = (size_t)prop.smem_optin - 2048;
   size_t ws_per = 0;
-  plan_layout(p->lay, m, budget, &p->smem, &ws_per);
+  plan_layout(p->lay, m, budget, 1, &p->smem, &ws_per);
+  p->team = 1;
+  // Fewer problems than SMs (the upper waves of a guide tree): only the latency of one problem
+  // counts, so give each Nussinov structure a team of warps -- the largest team that does not
+  // push a scratch array out of shared memory.
+  {
+    int want = nprob <= prop.sms ? 3 : 1;
+    if (const char* e = getenv("DAFS_DD_TEAM")) want = std::max(1, std::min(3, atoi(e)));
+    const bool forced = getenv("DAFS_DD_TEAM") != nullptr;
+    for (int t = want; t > 1; --t) {
+      DDLayout lay2 = p->lay; int smem2 = 0; size_t ws2 = 0;
+      plan_layout(lay2, m, budget, t, &smem2, &ws2);
+      if (forced || lay2.in_smem == p->lay.in_smem) { p->lay = lay2; p->smem = smem2; ws_per = ws2; p->team = t; break; }
+    }
+  }
   p->all_smem = (p->lay.in_smem == (1u << DD_NITEMS) - 1u);
   int blocks = 0;
-  if (p->all_smem) {
-    PLAN_TRY(cudaFuncSetAttribute(dd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-    PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel<true>, DD_THREADS, p->smem));
-  } else {
-    PLAN_TRY(cudaFuncSetAttribute(dd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-    PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, dd_kernel<false>, DD_THREADS, p->smem));
+  {
+    const void* fn = dd_kernel_fn(p->all_smem, p->team);
+    PLAN_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, fn, 32 * (2 * p->team + 1), p->smem));
   }
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
   p->ctas_per_sm = blocks;
@@ -517,12 +543,11 @@ extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
   a.prob = p->d_prob; a.order = p->d_order; a.nprob = p->nprob; a.queue = p->d_queue; a.lay = p->lay;
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  if (p->all_smem) {
-    DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-    dd_kernel<true><<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
-  } else {
-    DAFS_CUDA_TRY(cudaFuncSetAttribute(dd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
-    dd_kernel<false><<<p->grid, DD_THREADS, p->smem, p->stream>>>(a);
+  {
+    const void* fn = dd_kernel_fn(p->all_smem, p->team);
+    DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    void* args[] = {(void*)&a};
+    DAFS_CUDA_TRY(cudaLaunchKernel(fn, dim3(p->grid), dim3(32 * (2 * p->team + 1)), args, (size_t)p->smem, p->stream));
   }
   DAFS_CUDA_TRY(cudaGetLastError());
   DAFS_CUDA_TRY(cudaEventRecord(p->ev1, p->stream));
@@ -574,7 +599,7 @@ extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
 
 extern "C" int dafs_cuda_dd_plan_info(dafs_dd_plan* p, dafs_dd_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
-  info->grid = p->grid; info->block = DD_THREADS; info->cols_per_lane = 0; info->smem_bytes = p->smem;
+  info->grid = p->grid; info->block = 32 * (2 * p->team + 1); info->cols_per_lane = 0; info->smem_bytes = p->smem;
   info->ctas_per_sm = p->ctas_per_sm; info->items_in_smem = p->lay.in_smem;
   info->workspace_bytes = (int64_t)p->lay.ws_stride * p->grid;
   info->arena_bytes = (int64_t)(p->cst_bytes + p->res_bytes);
@@ -608,7 +633,7 @@ __global__ void __launch_bounds__(32) nussinov_single_kernel(const char* blk, fl
   const DDNus S = dd_make_nus(blk, *reinterpret_cast<const DDNusHdr*>(blk), q);
   for (int e = threadIdx.x; e < S.nd; e += 32) sc.es[e] = -INFINITY;
   __syncwarp();
-  const float v = nussinov_warp(S, sc, th, threadIdx.x, nullptr);
+  const float v = nussinov_warp<1>(S, sc, th, threadIdx.x, 0, 1, nullptr);
   if (threadIdx.x == 0) *score = v;
   for (int i = threadIdx.x; i < S.L; i += 32) out[i] = sc.ss[i];
 }
@@ -662,6 +687,7 @@ extern "C" int dafs_cuda_nussinov_decode(int L, float th, float w, const float* 
   char* d_blk = B.take<char>(blk.size());
   float* d_q = B.take<float>(n);
   sc.es = B.take<float>(n); sc.row = B.take<float>(32 * (size_t)lp); sc.brow = B.take<float>(lp);
+  sc.prog = B.take<int>(4); sc.score_slot = B.take<float>(1);
   sc.ss = B.take<uint32_t>(L); sc.stk = B.take<uint32_t>(L / 2 + 4);
   uint32_t* d_out = B.take<uint32_t>(L); float* d_score = B.take<float>(1);
   sc.tr = tr16 ? (void*)B.take<uint16_t>(ntr) : (void*)B.take<uint8_t>(ntr);

@@ -64,7 +64,7 @@ struct DDNusHdr {
 };
 
 struct DDHdr {
-  int L1, L2, ncbp, t_max, bytes, pad1;
+  int L1, L2, ncbp, t_max, bytes, stage;   // stage: bytes staged to shared memory = everything before cbp
   float th_s, th_a, eta0;
   int pad0;
   DDNusHdr x, y;
@@ -76,7 +76,8 @@ struct DDHdr {
   uint32_t cz_row_ptr;         // int[L1+1]   c_z cells of row i (0-based), ascending k
   uint32_t cz_col;             // u16[ncz]
   uint32_t cz_bidx;            // i32[ncz]    band index of the cell, -1 outside the envelope
-  uint32_t cbp;                // int4 {entry in x, entry in y, c_z id of (i,k), c_z id of (j,l)}
+  uint32_t cbp;                // int4 {entry in x, entry in y, c_z id of (i,k), c_z id of (j,l)}; last in the
+                               // block and read from HBM: only the tally touches it, coalesced, once per iteration
 };
 
 struct DDProbRef {
@@ -145,8 +146,10 @@ __device__ __forceinline__ DDNus dd_make_nus(const char* blk, const DDNusHdr& h,
 
 struct NusScratch {
   float* es;        // [nd] value a candidate contributes: dp[i+1][j-1] + s, or -inf when inactive
-  float* row;       // [32*lp] dp rows (over live columns) of the current wave
-  float* brow;      // [lp] dp row of the live row just below the next wave
+  float* row;       // [T][32*lp] dp rows (over live columns) of the wave each team warp works on
+  float* brow;      // [T][lp] top row of that wave = the row below the next wave's lane 0
+  volatile int* prog;   // [T] progress of each team warp: wave << 16 | columns its top row has finished
+  float* score_slot;    // dp[0][L-1], written by the warp that owns the top wave
   void* tr;         // [nI*trs] traceback codes: t | down_ge << 7 (or << 15)
   uint32_t* ss;     // [L] result
   uint32_t* stk;    // traceback stack
@@ -195,33 +198,59 @@ __device__ __forceinline__ int nus_tr_load(const NusScratch& sc, int idx) {
 //   f(i+1, J[b]-1) = D[a+1][b-1]      ("diag")
 //   f(i, k-1)      = D[a][c(k)]       (c(k) = last live column <= k-1, ent_c)
 // Returns dp[0][L-1] in every lane.
-__device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch& sc, float th, int lane,
+template <int T>
+__device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch& sc, float th, int lane, int m, int bar_id,
                                                unsigned long long* prof) {
+  // T > 1: a TEAM of T warps fills the table.  Waves (32 live rows, bottom first) are dealt
+  // round-robin; wave v may work on live column b once wave v-1 has finished b in its top
+  // row (then every row below has: its own lanes are ahead of lane 31, and it waited for
+  // the wave below it in turn).  The top row of a wave is mirrored into brow[m] as it is
+  // produced; progress goes through prog[m] (shared memory, fence before the flag).  The
+  // waves overlap as a pipeline: nJ + 32 * waves steps instead of waves * (nJ + 31).
   const long long t0 = clock64();
   const int nI = S.nI, nJ = S.nJ, lp = sc.lp, trs = sc.trs;
-  float score = 0.0f;
-  float* myrow = sc.row + lane * lp;
-  for (int b = lane; b < nJ; b += 32) sc.brow[b] = 0.0f;     // nothing below the bottom live row
-  __syncwarp();
-  for (int ahi = nI - 1; ahi >= 0; ahi -= 32) {
+  float* myrow = sc.row + (size_t)m * 32 * lp + lane * lp;
+  float* mybrow = sc.brow + (size_t)m * lp;
+  const float* below_row = sc.brow + (size_t)((m + T - 1) % T) * lp;
+  volatile int* prog_mine = sc.prog + m;
+  volatile int* prog_prev = sc.prog + (m + T - 1) % T;
+  int seen = 0;
+  int wv = 0;
+  if (m == 0 && lane == 0) *sc.score_slot = 0.0f;            // before wave 0, which every later wave waits for
+  for (int ahi = nI - 1; ahi >= 0; ahi -= 32, ++wv) {
+    if (T > 1 && (wv % T) != m) continue;
     const int a = ahi - lane;
     const bool live = a >= 0;
     int i = 0, bs = 0x3fffffff, rcur = 0, rend = 0;
     if (live) { i = S.rowI[a]; bs = S.bstart[a]; rcur = S.row_ptr[a]; rend = S.row_ptr[a + 1]; }
     int next_b = (rcur < rend) ? (int)(S.ent_ab[S.row_ent[rcur]] >> 16) : 0x7fffffff;
+    // first column of the live row just below lane 0 (nothing below the bottom wave)
+    const int bsb = (wv > 0) ? (int)S.bstart[ahi + 1] : 0x3fffffff;
     // lane t works on live column B0 + s - t at step s; every lane must reach its
     // first valid column bs at some s >= 0
     int B0 = live ? bs + lane : 0x3fffffff;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) B0 = min(B0, __shfl_xor_sync(0xffffffffu, B0, o));
     const int nsteps = (nJ - B0) + 31;
+    const int prev_base = (wv - 1) << 16, my_base = wv << 16;
+    if (T > 1) {
+      if (lane == 0) *prog_mine = my_base;
+      if (wv > 0) {                                  // column B0 of the row below
+        const int tgt = prev_base + min(B0 + 1, nJ);
+        if (seen < tgt) { do { seen = *prog_prev; } while (seen < tgt); __threadfence_block(); }
+      }
+    }
     float cur = 0.0f;          // D[a][b-1] entering a step, D[a][b] leaving it
     float below_prev = 0.0f;   // D[a+1][b-1]
-    float brow_next = (lane == 0 && B0 >= 0 && B0 < nJ) ? sc.brow[B0] : 0.0f;
+    float brow_next = (lane == 0 && B0 >= bsb && B0 < nJ) ? below_row[B0] : 0.0f;
     for (int s = 0; s < nsteps; ++s) {
       const int b = B0 + s - lane;
+      if (T > 1 && wv > 0) {                         // lane 0 fetches column B0 + s + 1 of the row below now
+        const int tgt = prev_base + min(B0 + s + 2, nJ);
+        if (seen < tgt) { do { seen = *prog_prev; } while (seen < tgt); __threadfence_block(); }
+      }
       float below = __shfl_up_sync(0xffffffffu, cur, 1);
-      if (lane == 0) { below = brow_next; brow_next = (b + 1 < nJ) ? sc.brow[b + 1] : 0.0f; }
+      if (lane == 0) { below = brow_next; brow_next = (b + 1 >= bsb && b + 1 < nJ) ? below_row[b + 1] : 0.0f; }
       if (live && b >= bs && b < nJ) {
         const int j = S.colJ[b];
         const int span = j - i;
@@ -241,7 +270,7 @@ __device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch&
           }
           sc.es[e] = c;
         }
-        // bifurcations: candidates of column j with k > i, in push order (:247-259)
+        // bifurcations: candidates of column j with k > i, in push order (:247-259).
         // The list is in descending row order, so the candidates with k > i are a prefix.
         // Four at a time: the packed (row, column) words and the candidate values are
         // fetched first, the row lookups next, and only the compare chain is serial.
@@ -268,22 +297,31 @@ __device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch&
           if (!ok[3]) break;
         }
         myrow[b] = v;
+        if (lane == 31) mybrow[b] = v;                       // the row below the next wave's lane 0
         nus_tr_store(sc, a * trs + b, t, !(below < v));
         cur = v;
-        if (a == 0 && b == nJ - 1) score = v;
+        if (a == 0 && b == nJ - 1) *sc.score_slot = v;
       }
       below_prev = below;
       __syncwarp();
+      if (T > 1 && ((s & 3) == 3)) {                         // lane 31 has finished every column <= B0 + s - 31
+        __threadfence_block();
+        if (lane == 0) *prog_mine = my_base + max(0, min(B0 + s - 30, nJ));
+      }
     }
-    // the row of the last lane becomes the "row below" of the next wave
-    if (ahi - 32 >= 0) {
-      const int bs31 = __shfl_sync(0xffffffffu, bs, 31);
-      for (int b = lane; b < nJ; b += 32) sc.brow[b] = (b >= bs31) ? sc.row[31 * lp + b] : 0.0f;
+    if (T > 1) {
+      __threadfence_block();
+      if (lane == 0) *prog_mine = my_base + 0xffff;          // the whole wave is done
     }
     __syncwarp();
   }
-  score = __shfl_sync(0xffffffffu, score, (nI > 0) ? ((nI - 1) & 31) : 0);
+  if (T > 1) {                                               // team barrier: 1 = x team, 2 = y team
+    if (bar_id == 1) asm volatile("bar.sync 1, %0;" :: "r"(32 * T) : "memory");
+    else asm volatile("bar.sync 2, %0;" :: "r"(32 * T) : "memory");
+  } else __syncwarp();
+  const float score = (nI > 0) ? *sc.score_slot : 0.0f;
   const long long t1 = clock64();
+  if (T > 1 && m != 0) return score;                         // the team's first warp walks back
 
   // ---- traceback (:265-295) on full coordinates, all lanes in lock step.  The
   // order in which the reference's stack is served does not change ss.
@@ -449,6 +487,8 @@ struct DDShared {
   float s, s_prev, c, eta;
   unsigned violated;
   int done, bad, q;
+  int prog[8];                 // Nussinov team progress flags: x team [0..3], y team [4..7]
+  float nus_score[2];
   // cycles: 0 nussinov x fill, 1 x traceback, 2 y fill, 3 y traceback, 4 nw fill, 5 nw traceback,
   // 6 decode phase (CTA), 7 tally + update phase (CTA)
   unsigned long long prof[8];
@@ -471,26 +511,33 @@ __device__ __forceinline__ void dd_update_nus(const DDNus& S, const uint32_t* ss
   }
 }
 
-#define DD_THREADS 96
+#define DD_THREADS 96          // T = 1: one warp per decoder
+#define DD_MAX_TEAM 4
 
 // SMEM: every scratch item and the constant block are in shared memory (the host
 // says so), which lets the compiler address them as shared (LDS/STS, 32-bit
 // addresses); otherwise pointers are generic and items may sit in HBM.
-template <bool SMEM>
-__global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
+// T: warps per Nussinov structure.  T = 1 is the throughput configuration (three warps per
+// problem, several CTAs per SM); T > 1 is used when a launch has fewer problems than the GPU
+// has SMs (the upper waves of a guide tree), where only the latency of one problem counts.
+template <bool SMEM, int T>
+__global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
+  constexpr int NT = 32 * (2 * T + 1);
   extern __shared__ __align__(16) char smem[];
   __shared__ DDShared sh;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const DDLayout& lay = a.lay;
   char* const wsb = SMEM ? smem : lay.ws + (size_t)blockIdx.x * lay.ws_stride;
 #define DD_ITEM(T, item) reinterpret_cast<T*>((SMEM || ((lay.in_smem >> (item)) & 1u) ? smem : wsb) + lay.off[item])
-  // this warp's Nussinov structure: x for warp 0, y for warp 1 (warp 2 aligns)
-  const int wy = (warp == 1) ? 1 : 0;
+  // this warp's Nussinov structure: x for warps [0, T), y for warps [T, 2T); warp 2T aligns
+  const int wy = (warp >= T && warp < 2 * T) ? 1 : 0;
+  const int team_m = warp < T ? warp : warp - T;
   NusScratch ns;
   ns.es = DD_ITEM(float, DD_ES_X + wy); ns.row = DD_ITEM(float, DD_ROW_X + wy);
   ns.brow = DD_ITEM(float, DD_BROW_X + wy); ns.tr = DD_ITEM(void, DD_TR_X + wy);
   ns.ss = DD_ITEM(uint32_t, DD_SS_X + wy); ns.stk = DD_ITEM(uint32_t, DD_STK_X + wy);
   ns.lp = wy ? lay.lp2 : lay.lp1; ns.trs = wy ? lay.trs2 : lay.trs1; ns.tr16 = lay.tr16 != 0;
+  ns.prog = sh.prog + 4 * wy; ns.score_slot = sh.nus_score + wy;
   NwScratch nz;
   nz.rowbuf = DD_ITEM(float, DD_BROW_Z); nz.trz = DD_ITEM(uint2, DD_TRZ); nz.zres = DD_ITEM(uint32_t, DD_ZRES);
   nz.ts = lay.ts;
@@ -517,10 +564,10 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     const DDProbRef pr = a.prob[a.order[sh.q]];
     const char* blk = pr.cst;
     if (cst_in_smem) {            // stage the constant block: coalesced 16-byte copies
-      const int n16 = reinterpret_cast<const DDHdr*>(pr.cst)->bytes >> 4;
+      const int n16 = reinterpret_cast<const DDHdr*>(pr.cst)->stage >> 4;
       const uint4* src = reinterpret_cast<const uint4*>(pr.cst);
       uint4* dst = reinterpret_cast<uint4*>(cst_s);
-      for (int k = tid; k < n16; k += DD_THREADS) dst[k] = src[k];
+      for (int k = tid; k < n16; k += NT) dst[k] = src[k];
       blk = cst_s;
     }
     __syncthreads();
@@ -536,19 +583,20 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     const uint16_t* cz_col = reinterpret_cast<const uint16_t*>(blk + h.cz_col);
     const int* cz_bidx = reinterpret_cast<const int*>(blk + h.cz_bidx);
     const int nb = h.nb, ncz = h.ncz;
-    const int4* cbp = reinterpret_cast<const int4*>(blk + h.cbp);
+    const int4* cbp = reinterpret_cast<const int4*>(pr.cst + h.cbp);
     const int L1 = h.L1, L2 = h.L2, ncbp = h.ncbp, t_max = h.t_max;
     const float th_s = h.th_s, eta0 = h.eta0;
 
     // ---- q = 0 (dafs.cpp:1067-1069), scratch reset ----------------------------
-    for (int e = tid; e < X.n; e += DD_THREADS) { q_x[e] = 0.0f; tal_x[e] = 0; if (e < X.nd) es_x[e] = -INFINITY; }
-    for (int e = tid; e < Y.n; e += DD_THREADS) { q_y[e] = 0.0f; tal_y[e] = 0; if (e < Y.nd) es_y[e] = -INFINITY; }
-    for (int e = tid; e < nb; e += DD_THREADS) q_z[e] = 0.0f;
-    for (int e = tid; e < ncz; e += DD_THREADS) { q_cz[e] = 0.0f; tal_z[e] = 0; }
-    for (int k = tid; k < L1; k += DD_THREADS) { ss_x[k] = DD_NOPAIR; nz.zres[k] = DD_NOPAIR; }
-    for (int k = tid; k < L2; k += DD_THREADS) ss_y[k] = DD_NOPAIR;
+    for (int e = tid; e < X.n; e += NT) { q_x[e] = 0.0f; tal_x[e] = 0; if (e < X.nd) es_x[e] = -INFINITY; }
+    for (int e = tid; e < Y.n; e += NT) { q_y[e] = 0.0f; tal_y[e] = 0; if (e < Y.nd) es_y[e] = -INFINITY; }
+    for (int e = tid; e < nb; e += NT) q_z[e] = 0.0f;
+    for (int e = tid; e < ncz; e += NT) { q_cz[e] = 0.0f; tal_z[e] = 0; }
+    for (int k = tid; k < L1; k += NT) { ss_x[k] = DD_NOPAIR; nz.zres[k] = DD_NOPAIR; }
+    for (int k = tid; k < L2; k += NT) ss_y[k] = DD_NOPAIR;
     if (tid == 0) {
       sh.c = 0.0f; sh.eta = eta0; sh.s_prev = 0.0f; sh.violated = 0; sh.done = 0; sh.bad = 0;
+      for (int k = 0; k < 8; ++k) sh.prog[k] = 0;
       for (int k = 0; k < 8; ++k) sh.prof[k] = 0;
     }
     __syncthreads();
@@ -557,13 +605,16 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
     for (; t < t_max; ++t) {
       // ---- the three subproblems (dafs.cpp:1090-1093) -------------------------
       const long long tp0 = clock64();
-      if (warp < 2) { const float v = nussinov_warp(mine, ns, th_s, lane, sh.prof + 2 * wy); if (lane == 0) sh.part[wy] = v; }
-      else { const float v = nw_warp(Z, nz, lane, &sh.bad, sh.prof + 4); if (lane == 0) sh.part[2] = v; }
+      if (warp < 2 * T) {
+        const float v = nussinov_warp<T>(mine, ns, th_s, lane, team_m, 1 + wy, team_m == 0 ? sh.prof + 2 * wy : nullptr);
+        if (lane == 0 && team_m == 0) sh.part[wy] = v;
+      } else { const float v = nw_warp(Z, nz, lane, &sh.bad, sh.prof + 4); if (lane == 0) sh.part[2] = v; }
       if (tid == 0) sh.violated = 0;
       __syncthreads();
+      if (T > 1 && tid < 8) sh.prog[tid] = 0;                 // wave numbers restart with every decode
       const long long tp1 = clock64();
       // ---- tally (:1103-1117) ---------------------------------------------------
-      for (int u = tid; u < ncbp; u += DD_THREADS) {
+      for (int u = tid; u < ncbp; u += NT) {
         const int4 cb = cbp[u];
         const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_cz[cb.z]), q_cz[cb.w]);
         sw[u] = s_w;
@@ -574,7 +625,7 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       }
       __syncthreads();
       // ---- Lagrangian value, summed in CBP order by one thread (:1090-1111) ----
-      if (tid == DD_THREADS - 1) {
+      if (tid == NT - 1) {
         float s = __fadd_rn(0.0f, sh.part[0]);
         s = __fadd_rn(s, sh.part[1]);
         s = __fadd_rn(s, sh.part[2]);
@@ -584,12 +635,12 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       // ---- multiplier updates (:1121-1254) -----------------------------------------
       const float eta = sh.eta;
       unsigned viol = 0;
-      dd_update_nus(X, ss_x, tal_x, eta, viol, tid, DD_THREADS);
-      dd_update_nus(Y, ss_y, tal_y, eta, viol, tid, DD_THREADS);
+      dd_update_nus(X, ss_x, tal_x, eta, viol, tid, NT);
+      dd_update_nus(Y, ss_y, tal_y, eta, viol, tid, NT);
       // z (:1223-1254), one thread per row over its c_z cells.  Cells outside c_z
       // have t_z = 0 and q_z = 0, and stay there: max(0, 0 - eta*(1-0)) = 0 for
       // eta >= 0 or NaN (the host rejects eta0 < 0).
-      for (int i = tid; i < L1; i += DD_THREADS) {
+      for (int i = tid; i < L1; i += NT) {
         const uint32_t zi = nz.zres[i];
         for (int e = cz_row_ptr[i]; e < cz_row_ptr[i + 1]; ++e) {
           const int tz = tal_z[e];
@@ -629,8 +680,8 @@ __global__ void __launch_bounds__(DD_THREADS) dd_kernel(const DDArgs a) {
       if (sh.done) break;
     }
     // ---- results -------------------------------------------------------------------
-    for (int k = tid; k < L1; k += DD_THREADS) { pr.x_out[k] = ss_x[k]; pr.z_out[k] = nz.zres[k]; }
-    for (int k = tid; k < L2; k += DD_THREADS) pr.y_out[k] = ss_y[k];
+    for (int k = tid; k < L1; k += NT) { pr.x_out[k] = ss_x[k]; pr.z_out[k] = nz.zres[k]; }
+    for (int k = tid; k < L2; k += NT) pr.y_out[k] = ss_y[k];
     if (tid == 0) {
       pr.result[0] = sh.s_prev;
       reinterpret_cast<int*>(pr.result)[1] = t;
