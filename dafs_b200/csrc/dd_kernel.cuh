@@ -430,11 +430,10 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
       const bool c2 = m < up;                                                      // :284
       float x = in ? (c2 ? up : m) : -FLT_MAX;
       const float a = x;
+      // inclusive prefix maximum; a lane below the shuffle distance gets its own value
+      // back, which a maximum ignores, so no lane test is needed
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const float y = __shfl_up_sync(0xffffffffu, x, d);
-        if (lane >= d) x = fmaxf(x, y);
-      }
+      for (int d = 1; d < 32; d <<= 1) x = fmaxf(x, __shfl_up_sync(0xffffffffu, x, d));
       const float v = fmaxf(x, carry);                                             // dp[r][k]
       float left = __shfl_up_sync(0xffffffffu, v, 1);                              // dp[r][k-1]
       if (lane == 0) left = carry;
