@@ -44,16 +44,93 @@ def shard(npairs, rank, world):
     return np.arange(rank, npairs, world, dtype=np.int64)
 
 
-def gather_csr(dist, world, dev, col, val, nz_off, n_units, row_ptr=None):
+def exchange_sizes(dist, world, dev, nnz, n_units, nrows):
+    """(nnz, units, row_ptr entries) of every rank's fragment, as a [world, 3] CPU tensor."""
+    import torch
+    sizes = torch.tensor([nnz, n_units, nrows], dtype=torch.int64, device=dev)
+    all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(all_sizes, sizes)
+    return all_sizes.view(world, 3).cpu()
+
+
+class SharedHostBuffer:
+    """Host memory that every rank of the node maps (POSIX shared memory) and page-locks for
+    its own GPU: each rank copies its CSR fragment to the host over its own PCIe link, into
+    its own region, and rank 0 (which runs the host side of the pipeline) reads all of them in
+    place.  Region r holds, back to back: nz_off[units+1] (int64), row_ptr (int32), col (int32),
+    val (float32) of rank r's pairs, in that rank's pair order (bench.shard)."""
+
+    def __init__(self, dist, rank, world, all_sizes, pin=True):
+        import torch
+        from multiprocessing import resource_tracker, shared_memory
+        mx_nnz, mx_units, mx_rows = (int(all_sizes[:, k].max()) for k in range(3))
+        self.cap = (mx_nnz, mx_units, mx_rows)
+        up = lambda x: (x + 255) & ~255
+        self.off = [0, up(8 * (mx_units + 1))]
+        self.off.append(self.off[1] + up(4 * mx_rows))
+        self.off.append(self.off[2] + up(4 * mx_nnz))
+        self.stride = self.off[3] + up(4 * mx_nnz)
+        nbytes = self.stride * world
+        name = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            name[0] = self.shm.name
+        dist.broadcast_object_list(name, src=0)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=name[0])
+            try:                                   # only the creator unlinks it
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.rank, self.world = rank, world
+        self.bytes = torch.frombuffer(self.shm.buf, dtype=torch.uint8, count=nbytes)
+        self.pinned = False
+        if pin and torch.cuda.is_available():      # page-lock this rank's own region: the target of its copies
+            self.pin_ptr = self.bytes.data_ptr() + rank * self.stride
+            self.pinned = int(torch.cuda.cudart().cudaHostRegister(self.pin_ptr, self.stride, 0)) == 0
+
+    def fits(self, all_sizes):
+        return all(int(all_sizes[:, k].max()) <= self.cap[k] for k in range(3))
+
+    def region(self, r, sizes):
+        """(nz_off, row_ptr, col, val) views of rank r's region for the given (nnz, units, rows)."""
+        import torch
+        nn, nu, nr = (int(x) for x in sizes)
+        base = self.bytes[r * self.stride:(r + 1) * self.stride]
+        return (base[self.off[0]:self.off[0] + 8 * (nu + 1)].view(torch.int64),
+                base[self.off[1]:self.off[1] + 4 * nr].view(torch.int32),
+                base[self.off[2]:self.off[2] + 4 * nn].view(torch.int32),
+                base[self.off[3]:self.off[3] + 4 * nn].view(torch.float32))
+
+    def put(self, sizes, nz_off, row_ptr, col, val):
+        """This rank's fragment -> its region (device-to-host copies on the current stream)."""
+        dst = self.region(self.rank, sizes)
+        n = 0
+        for d, x in zip(dst, (nz_off, row_ptr, col, val)):
+            d.copy_(x[:d.numel()], non_blocking=True)
+            n += d.numel() * d.element_size()
+        return n
+
+    def close(self):
+        import torch
+        if self.pinned:
+            torch.cuda.cudart().cudaHostUnregister(self.pin_ptr)
+        del self.bytes
+        try:
+            self.shm.close()
+            if self.rank == 0:
+                self.shm.unlink()
+        except Exception:
+            pass
+
+
+def gather_csr(dist, world, dev, col, val, nz_off, n_units, row_ptr=None, all_sizes=None):
     """All-gather-v of per-rank CSR fragments: sizes first, then the max-padded
     payload.  Returns, on every rank, a list over ranks of (col, val, nz_off,
     n_units) views.  This is the only exchange step of the path."""
     import torch
-    nrows = 0 if row_ptr is None else row_ptr.numel()
-    sizes = torch.tensor([col.numel(), n_units, nrows], dtype=torch.int64, device=dev)
-    all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(all_sizes, sizes)
-    all_sizes = all_sizes.view(world, 3).cpu()
+    if all_sizes is None:
+        all_sizes = exchange_sizes(dist, world, dev, col.numel(), n_units, 0 if row_ptr is None else row_ptr.numel())
     mx_nnz, mx_units, mx_rows = (int(all_sizes[:, k].max()) for k in range(3))
 
     def pad(x, n):
@@ -444,7 +521,8 @@ def run_ours(args):
     # ---- e2e: host buffers in, host CSR out on rank 0 --------------------------
     h2d = NSEQ * LEN + 8 * (NSEQ + 1) + 4 * NSEQ + (8 + 4 + 8) * len(mine) + 8
     e2e_times, d2h = [], 0
-    pinned = {}
+    shared = None
+    copy_stream = torch.cuda.Stream(device=dev)
     for it in range(W + K):
         barrier()
         t0 = time.perf_counter()
@@ -458,29 +536,34 @@ def run_ours(args):
             if it >= W:
                 e2e_times.append(time.perf_counter() - t0)
             continue
+        # N > 1: every rank computes its pairs; the CSR fragments are all-gathered on the devices
+        # (NCCL over NVLink: the hand-over to the rank that runs the alignment stage on its GPU)
+        # and, at the same time, copied to host memory that rank 0 maps, each rank over its own
+        # PCIe link into its own region (SharedHostBuffer).
         p2 = dafs_b200.PairHmmPlan(seqs, mpi, mpj, TH)       # encode + H2D + workspace
         p2.run()
-        if True:
-            _, n_mine = p2.sync()
-            rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
-            col = torch.empty(max(n_mine, 1), dtype=torch.int32, device=dev)
-            val = torch.empty(max(n_mine, 1), dtype=torch.float32, device=dev)
-            rp = torch.empty(max(rows_mine, 1), dtype=torch.int32, device=dev)
-            nzo = torch.empty(len(mine) + 1, dtype=torch.int64, device=dev)
-            p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), max(n_mine, 1))
-            frags = gather_csr(dist, world, dev, col[:n_mine], val[:n_mine], nzo, len(mine), rp[:rows_mine])  # NCCL
-            if rank == 0:
-                d2h = 0
-                k = 0
-                for fr in frags:
-                    for x in (fr[0], fr[1], fr[2], fr[4]):
-                        if k not in pinned or pinned[k].numel() < x.numel() or pinned[k].dtype != x.dtype:
-                            pinned[k] = torch.empty(max(x.numel(), 1), dtype=x.dtype, pin_memory=True)
-                        pinned[k][:x.numel()].copy_(x, non_blocking=True)
-                        d2h += x.numel() * x.element_size()
-                        k += 1
-                torch.cuda.synchronize()
-                checksum = sum(int(fr[0].numel()) for fr in frags)
+        _, n_mine = p2.sync()
+        rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
+        col = torch.empty(max(n_mine, 1), dtype=torch.int32, device=dev)
+        val = torch.empty(max(n_mine, 1), dtype=torch.float32, device=dev)
+        rp = torch.empty(max(rows_mine, 1), dtype=torch.int32, device=dev)
+        nzo = torch.empty(len(mine) + 1, dtype=torch.int64, device=dev)
+        p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), max(n_mine, 1))
+        all_sizes = exchange_sizes(dist, world, dev, n_mine, len(mine), rows_mine)
+        if shared is None or not shared.fits(all_sizes):
+            if shared is not None:
+                shared.close()
+            shared = SharedHostBuffer(dist, rank, world, all_sizes)
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_stream(torch.cuda.current_stream())
+            d2h_mine = shared.put(all_sizes[rank], nzo, rp, col, val)
+        frags = gather_csr(dist, world, dev, col[:n_mine], val[:n_mine], nzo, len(mine), rp[:rows_mine], all_sizes=all_sizes)  # NCCL
+        copy_stream.synchronize()
+        barrier()                                             # every fragment is in host memory
+        if rank == 0:                                         # read-back of the step's result, from the host copy
+            checksum = sum(int(shared.region(r, all_sizes[r])[0][-1]) for r in range(world))
+            assert checksum == sum(int(fr[0].numel()) for fr in frags)
+        d2h = d2h_mine
         p2.close()
         barrier()
         if it >= W:
@@ -488,7 +571,12 @@ def run_ours(args):
     if rank == 0:
         print("e2e per step (ms):", " ".join("%.1f" % (x * 1e3) for x in e2e_times), file=sys.stderr)
     e2e_s = max_over_ranks(sum(e2e_times) / len(e2e_times))
-    d2h_max = int(max_over_ranks(float(d2h)))
+    if world > 1:                                             # bytes copied to the host by all ranks together
+        t = torch.tensor([d2h], dtype=torch.int64, device=dev); dist.all_reduce(t); d2h_max = int(t.item())
+        if shared is not None:
+            shared.close()
+    else:
+        d2h_max = int(d2h)
 
     if rank == 0:
         npairs = len(pi)

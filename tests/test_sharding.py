@@ -41,6 +41,21 @@ def _worker(rank, world, port, q):
     val = torch.tensor(np.concatenate([u + np.arange(n) / 10 for u, n in zip(mine, frag_nnz)]), dtype=torch.float32)
     nzo = torch.tensor(np.concatenate([[0], np.cumsum(frag_nnz)]), dtype=torch.int64)
     gathered = bench.gather_csr(dist, world, torch.device("cpu"), col, val, nzo, len(mine))
+    # the host-side hand-over: every rank writes its fragment into its region of one shared buffer
+    rp = torch.arange(3 * len(mine) + rank, dtype=torch.int32)
+    sizes = bench.exchange_sizes(dist, world, torch.device("cpu"), col.numel(), len(mine), rp.numel())
+    shared = bench.SharedHostBuffer(dist, rank, world, sizes, pin=False)
+    assert shared.fits(sizes)
+    shared.put(sizes[rank], nzo, rp, col, val)
+    dist.barrier()
+    if rank == 0:
+        for r in range(world):
+            o, p_, c, v = shared.region(r, sizes[r])
+            gc, gv, go, gn = gathered[r]
+            assert torch.equal(o, go) and torch.equal(c, gc) and torch.equal(v, gv)
+            assert torch.equal(p_, torch.arange(3 * gn + r, dtype=torch.int32))
+    dist.barrier()
+    shared.close()
     if rank == 0:
         out = {}
         for r, (c, v, o, n_units) in enumerate(gathered):
