@@ -6,6 +6,12 @@ C++ adapters in ``dafs_b200/host`` that plug it behind the reference's
 thin ctypes binding the tests and ``bench.py`` drive it through; there is no
 CPU fallback anywhere: if the library or a GPU is missing, calls raise.
 """
+import os as _os
+
+# Must be in the environment before the CUDA context exists (torch creates it lazily): the
+# progressive stage keeps many launches in flight on separate streams, see csrc/common.cu.
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 from .capi import (  # noqa: F401
     DafsCudaError,
     CsrBatch,

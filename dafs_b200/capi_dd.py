@@ -42,6 +42,7 @@ def _protos():
         L.dafs_cuda_dd_plan_run.argtypes = [C.c_void_p]
         L.dafs_cuda_dd_plan_sync.argtypes = [C.c_void_p, _FP]
         L.dafs_cuda_dd_plan_fetch.argtypes = [C.c_void_p, C.POINTER(_DDResult)]
+        L.dafs_cuda_dd_plan_poll.argtypes = [C.c_void_p, C.POINTER(_DDResult), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.dafs_cuda_dd_plan_info.argtypes = [C.c_void_p, C.POINTER(_DDInfo)]
         L.dafs_cuda_dd_plan_destroy.argtypes = [C.c_void_p]
         L.dafs_cuda_dd_plan_destroy.restype = None
@@ -140,6 +141,21 @@ class DDPlan:
         res, outs = self.batch.results(self.trace)
         _check(lib().dafs_cuda_dd_plan_fetch(self._h, res))
         return DDBatch.unpack(res, outs)
+
+    def poll(self, state=None):
+        """Non-blocking harvest (dafs_cuda_dd_plan_poll): returns (state, fresh) where fresh maps the
+        index of every problem that finished since the last poll to its result dict; pass the
+        returned state to the next call."""
+        if state is None:
+            res, outs = self.batch.results(self.trace)
+            state = {"res": res, "outs": outs, "done": (C.c_int32 * max(self.batch.n, 1))()}
+        before = list(state["done"])
+        n_new = C.c_int32()
+        _check(lib().dafs_cuda_dd_plan_poll(self._h, state["res"], state["done"], C.byref(n_new)))
+        allr = DDBatch.unpack(state["res"], state["outs"])
+        fresh = {k: allr[k] for k in range(self.batch.n) if state["done"][k] and not before[k]}
+        assert len(fresh) == n_new.value
+        return state, fresh
 
     def info(self):
         i = _DDInfo()

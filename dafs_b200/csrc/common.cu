@@ -4,11 +4,25 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <vector>
 
 namespace dafs {
+
+// dafs_cuda_progressive keeps many small launches in flight on their own streams next to
+// launches that run for tens of milliseconds.  With the default of 8 hardware work queues,
+// streams share queues and a short launch can sit behind a long one of another stream; ask
+// for the maximum (only effective if the CUDA context does not exist yet; never overrides
+// a value the user has set).
+namespace {
+struct MaxConnections {
+  MaxConnections() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+} g_max_connections;
+}  // namespace
+
+thread_local cudaStream_t g_dd_stream = nullptr, g_dd_poll_stream = nullptr;
 
 std::string& last_error() {
   static thread_local std::string e;
@@ -86,14 +100,15 @@ std::mutex g_dev_mu;
 std::vector<DevBlock> g_dev_free;
 std::map<void*, std::pair<size_t, int>> g_dev_cap;   // cached-class allocations in use
 size_t g_dev_cached = 0;
-const size_t kDevCacheMin = 256;                      // everything but the tiniest counters
+const size_t kDevCacheMin = 256;                      // smaller requests are rounded up: a cudaFree of even a 4-byte
+                                                      // counter waits for every kernel running on the device
 const size_t kDevSmall = size_t(1) << 20;
 const size_t kDevCacheLimit = size_t(32) << 30;
 }  // namespace
 
 cudaError_t dev_malloc(void** out, size_t bytes) {
   *out = nullptr;
-  if (bytes == 0) bytes = 1;
+  if (bytes < kDevCacheMin) bytes = kDevCacheMin;
   int dev = 0;
   cudaGetDevice(&dev);
   if (bytes >= kDevCacheMin) {

@@ -39,6 +39,11 @@ template <class T> inline cudaError_t dev_malloc(T** out, size_t bytes) { return
 void dev_free(void* p);
 void dev_trim();
 
+// Streams a caller inside the library lends to the next DD plans of this thread (a plan
+// normally makes its own): dafs_cuda_progressive keeps a small pool and reuses an idle stream
+// for every batch instead of creating two streams per batch.
+extern thread_local cudaStream_t g_dd_stream, g_dd_poll_stream;
+
 // SM count and opt-in shared memory per block of a device, queried once
 // (cudaGetDeviceProperties costs about a millisecond per call, per-call plans pay it).
 struct DevInfo { int sms; size_t smem_optin; };

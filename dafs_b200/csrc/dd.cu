@@ -327,6 +327,9 @@ struct dafs_dd_plan {
   int grid = 0, smem = 0, ctas_per_sm = 0;
   bool all_smem = false;
   int team = 1;                            // warps per Nussinov structure (dd_kernel<SMEM, T>)
+  cudaStream_t poll_stream = nullptr;      // dafs_cuda_dd_plan_poll: copies under the running kernel
+  bool own_stream = true, own_poll = true; // false: lent by the caller (common.cuh: g_dd_stream)
+  char* poll_stage = nullptr;              // pinned, res_bytes
   int64_t total_cbp = 0, total_entries = 0;
   bool launched = false;
   float last_ms = 0;
@@ -339,7 +342,9 @@ static void free_dd_plan(dafs_dd_plan* p) {
   dev_free(p->d_queue); dev_free(p->d_ws);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
-  if (p->stream) cudaStreamDestroy(p->stream);
+  if (p->poll_stream && p->own_poll) cudaStreamDestroy(p->poll_stream);
+  if (p->poll_stage) pinned_free(p->poll_stage);
+  if (p->stream && p->own_stream) cudaStreamDestroy(p->stream);
 }
 
 struct DDMaxima { int L1 = 1, L2 = 1, nx = 1, ny = 1, nb = 1, bw = 1, ncz = 1, ncbp = 1, col = 0, cst = 16, nIx = 1, nJx = 1, nIy = 1, nJy = 1; };
@@ -398,6 +403,17 @@ static const void* dd_kernel_fn(bool smem, int team) {
     default: return smem ? (const void*)dd_kernel<true, 1> : (const void*)dd_kernel<false, 1>;
   }
 }
+// The opt-in limit is raised to the device maximum once per kernel and device and then left
+// alone: launches of different sizes are in flight at the same time (dafs_cuda_progressive),
+// and changing the attribute of a function that is running makes the next launch wait for it.
+static cudaError_t dd_allow_smem(const void* fn, bool smem, int team, int device, size_t optin) {
+  static bool done[64][2][4] = {};
+  bool& d = done[device & 63][smem ? 1 : 0][team & 3];
+  if (d) return cudaSuccess;
+  const cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin - 1024);   // the kernel has some static shared memory too
+  if (e == cudaSuccess) d = true;
+  return e;
+}
 }  // namespace dafs
 
 extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
@@ -426,7 +442,9 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
 #define PLAN_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return bail(fail(e_ == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM : DAFS_CUDA_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_))); } while (0)
   PLAN_TRY(cudaGetDevice(&p->device));
   p->nprob = nprob; p->want_trace = want_trace != 0;
-  PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  if (g_dd_stream) { p->stream = g_dd_stream; p->own_stream = false; }
+  else PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  if (g_dd_poll_stream) { p->poll_stream = g_dd_poll_stream; p->own_poll = false; }
   PLAN_TRY(cudaEventCreate(&p->ev0));
   PLAN_TRY(cudaEventCreate(&p->ev1));
   PLAN_TRY(dev_malloc(&p->d_queue, sizeof(int)));
@@ -519,7 +537,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   int blocks = 0;
   {
     const void* fn = dd_kernel_fn(p->all_smem, p->team);
-    PLAN_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+    PLAN_TRY(dd_allow_smem(fn, p->all_smem, p->team, p->device, prop.smem_optin));
     PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, fn, 32 * (2 * p->team + 1), p->smem));
   }
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "dd_kernel does not fit on an SM (smem %d)", p->smem));
@@ -542,10 +560,10 @@ extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
   DDArgs a;
   a.prob = p->d_prob; a.order = p->d_order; a.nprob = p->nprob; a.queue = p->d_queue; a.lay = p->lay;
   DAFS_CUDA_TRY(cudaMemsetAsync(p->d_queue, 0, sizeof(int), p->stream));
+  DAFS_CUDA_TRY(cudaMemsetAsync(p->d_res, 0, p->res_bytes, p->stream));      // completion flags of the last run
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
   {
     const void* fn = dd_kernel_fn(p->all_smem, p->team);
-    DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
     void* args[] = {(void*)&a};
     DAFS_CUDA_TRY(cudaLaunchKernel(fn, dim3(p->grid), dim3(32 * (2 * p->team + 1)), args, (size_t)p->smem, p->stream));
   }
@@ -564,6 +582,59 @@ extern "C" int dafs_cuda_dd_plan_sync(dafs_dd_plan* p, float* device_ms) {
   return DAFS_CUDA_OK;
 }
 
+namespace dafs {
+// one problem's slice of the result block -> dafs_dd_result
+static void unpack_result(const dafs_dd_plan* p, const char* stage, int k, dafs_dd_result& r) {
+  const ProbHost& H = p->host[k];
+  const char* s = stage + H.res_base;
+  if (r.x) std::memcpy(r.x, s + H.sx.out, sizeof(uint32_t) * H.L1);
+  if (r.y) std::memcpy(r.y, s + H.sy.out, sizeof(uint32_t) * H.L2);
+  if (r.z) std::memcpy(r.z, s + H.z_out, sizeof(uint32_t) * H.L1);
+  const float* rf = reinterpret_cast<const float*>(s + H.result);
+  r.score = rf[0];
+  r.iters = reinterpret_cast<const int*>(rf)[1];
+  r.violated = reinterpret_cast<const unsigned*>(rf)[2];
+  r.status = reinterpret_cast<const int*>(rf)[3];
+  r.ncbp = H.ncbp;
+  for (int c = 0; c < 8; ++c) r.cycles[c] = rf[4 + c];
+  if (r.trace && p->want_trace)
+    std::memcpy(r.trace, s + H.trace, sizeof(float) * 3 * (size_t)std::min(H.t_max, r.iters + 1));
+}
+}  // namespace dafs
+
+// Non-blocking harvest: the result block is copied to the host on a second stream while the
+// kernel runs; a problem whose completion flag is set in one copy is read from the NEXT copy
+// (the flag is written after the results, but one copy reads them in no particular order).
+extern "C" int dafs_cuda_dd_plan_poll(dafs_dd_plan* p, dafs_dd_result* res, int32_t* done, int32_t* n_new) {
+  using namespace dafs;
+  if (!p || !done || !n_new || (p->nprob > 0 && !res)) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  *n_new = 0;
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  if (p->nprob == 0) return DAFS_CUDA_OK;
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  if (!p->poll_stream) DAFS_CUDA_TRY(cudaStreamCreateWithFlags(&p->poll_stream, cudaStreamNonBlocking));
+  if (!p->poll_stage) {
+    p->poll_stage = (char*)pinned_alloc(std::max<size_t>(p->res_bytes, 256));
+    if (!p->poll_stage) return fail(DAFS_CUDA_ENOMEM, "pinned staging of %zu bytes failed", p->res_bytes);
+  }
+  // the flags of an earlier run are cleared on the plan's stream just before ev0; a copy on the
+  // poll stream must not overtake that
+  DAFS_CUDA_TRY(cudaStreamWaitEvent(p->poll_stream, p->ev0, 0));
+  std::vector<int> fresh;
+  for (int pass = 0; pass < 2; ++pass) {
+    DAFS_CUDA_TRY(cudaMemcpyAsync(p->poll_stage, p->d_res, p->res_bytes, cudaMemcpyDeviceToHost, p->poll_stream));
+    DAFS_CUDA_TRY(cudaStreamSynchronize(p->poll_stream));
+    if (pass == 0) {
+      for (int k = 0; k < p->nprob; ++k)
+        if (!done[k] && reinterpret_cast<const int*>(p->poll_stage + p->host[k].res_base + p->host[k].result)[12] == 1) fresh.push_back(k);
+      if (fresh.empty()) return DAFS_CUDA_OK;
+    }
+  }
+  for (int k : fresh) { unpack_result(p, p->poll_stage, k, res[k]); done[k] = 1; }
+  *n_new = (int32_t)fresh.size();
+  return DAFS_CUDA_OK;
+}
+
 extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
   using namespace dafs;
   if (!p || (p->nprob > 0 && !res)) return fail(DAFS_CUDA_EINVAL, "NULL argument");
@@ -576,23 +647,7 @@ extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
   cudaError_t e = cudaMemcpyAsync(stage, p->d_res, p->res_bytes, cudaMemcpyDeviceToHost, p->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
   if (e != cudaSuccess) { pinned_free(stage); return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e)); }
-  for (int k = 0; k < p->nprob; ++k) {
-    const ProbHost& H = p->host[k];
-    const char* s = stage + H.res_base;
-    dafs_dd_result& r = res[k];
-    if (r.x) std::memcpy(r.x, s + H.sx.out, sizeof(uint32_t) * H.L1);
-    if (r.y) std::memcpy(r.y, s + H.sy.out, sizeof(uint32_t) * H.L2);
-    if (r.z) std::memcpy(r.z, s + H.z_out, sizeof(uint32_t) * H.L1);
-    const float* rf = reinterpret_cast<const float*>(s + H.result);
-    r.score = rf[0];
-    r.iters = reinterpret_cast<const int*>(rf)[1];
-    r.violated = reinterpret_cast<const unsigned*>(rf)[2];
-    r.status = reinterpret_cast<const int*>(rf)[3];
-    r.ncbp = H.ncbp;
-    for (int c = 0; c < 8; ++c) r.cycles[c] = rf[4 + c];
-    if (r.trace && p->want_trace)
-      std::memcpy(r.trace, s + H.trace, sizeof(float) * 3 * (size_t)std::min(H.t_max, r.iters + 1));
-  }
+  for (int k = 0; k < p->nprob; ++k) unpack_result(p, stage, k, res[k]);
   pinned_free(stage);
   return DAFS_CUDA_OK;
 }

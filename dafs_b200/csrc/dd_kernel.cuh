@@ -85,7 +85,8 @@ struct DDProbRef {
   uint32_t* x_out;             // [L1]
   uint32_t* y_out;             // [L2]
   uint32_t* z_out;             // [L1]
-  float* result;               // {score, iters, violated, status} as 4 x 32 bit, then 8 cycle counters (float)
+  float* result;               // {score, iters, violated, status} as 4 x 32 bit, then 8 cycle counters (float),
+                               // then the completion flag (word 12)
   float* trace;                // optional [t_max*3] {L, eta, violated} per iteration (-v 2, dafs.cpp:1273)
 };
 
@@ -486,6 +487,7 @@ struct DDShared {
   float s, s_prev, c, eta;
   unsigned violated;
   int done, bad, q;
+  unsigned long long g0;       // global timer when the problem was taken from the queue
   int prog[8];                 // Nussinov team progress flags: x team [0..3], y team [4..7]
   float nus_score[2];
   // cycles: 0 nussinov x fill, 1 x traceback, 2 y fill, 3 y traceback, 4 nw fill, 5 nw traceback,
@@ -557,7 +559,7 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) sh.q = atomicAdd(a.queue, 1);
+    if (tid == 0) { sh.q = atomicAdd(a.queue, 1); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(sh.g0)); }
     __syncthreads();
     if (sh.q >= a.nprob) break;
     const DDProbRef pr = a.prob[a.order[sh.q]];
@@ -687,7 +689,17 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
       reinterpret_cast<unsigned*>(pr.result)[2] = sh.violated;
       reinterpret_cast<int*>(pr.result)[3] = sh.bad;
       for (int k = 0; k < 8; ++k) pr.result[4 + k] = (float)sh.prof[k];
+      // slots 6 / 7 (phase counters, unused): when this problem started and ended on the device,
+      // milliseconds of the global timer modulo 10^5 (diagnostics of dafs_cuda_progressive)
+      unsigned long long g1;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1));
+      pr.result[10] = (float)((sh.g0 / 1000ull) % 100000000ull) * 1e-3f;
+      pr.result[11] = (float)((g1 / 1000ull) % 100000000ull) * 1e-3f;
     }
+    // completion flag for dafs_cuda_dd_plan_poll: set after everything above is visible
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) { __threadfence(); reinterpret_cast<volatile int*>(pr.result)[12] = 1; }
   }
 #undef DD_ITEM
 }

@@ -9,7 +9,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <queue>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
@@ -290,7 +292,11 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   A.len = d_len; A.rp_all = d_rp; A.col_all = d_col; A.val_all = d_val; A.desc = d_desc;
   A.b_row_off = d_b_row_off; A.b_nz_off = d_b_nz_off; A.b_row_ptr = d_b_rp; A.b_col = d_b_col; A.b_val = d_b_val;
 
-  // ---- waves ----------------------------------------------------------------------
+  // ---- batches -----------------------------------------------------------------------
+  // A node is ready when both children are built.  All nodes that are ready at the same time
+  // go out as one batch (two averaging launches + one DD launch on the batch's own stream);
+  // finished problems are harvested one by one with dafs_cuda_dd_plan_poll while their batch
+  // is still running, so a node that needs 600 iterations holds up its own ancestors only.
   std::vector<Aln> aln(nn);
   for (int s = 0; s < n; ++s) {             // leaves, :1520-1526
     aln[s].L = len[s]; aln[s].seq.assign(1, s); aln[s].bits.assign(len[s], 1); aln[s].built = true;
@@ -300,154 +306,265 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   R->node_iters.assign(nn, 0); R->node_L.assign(nn, 0); R->node_violated.assign(nn, 0); R->node_score.assign(nn, 0.0f);
   for (int s = 0; s < n; ++s) R->node_L[s] = len[s];
   const int max_level = level[nn - 1];
+  std::vector<int> parent(nn, -1);
+  for (int k = n; k < nn; ++k) { parent[left[k]] = k; parent[right[k]] = k; }
+  struct Batch {
+    std::vector<int> node;
+    std::vector<ProgSide> sides;
+    std::vector<dafs_dd_problem> prob;
+    std::vector<dafs_dd_result> res;
+    std::vector<std::vector<uint32_t>> xs, ys, zs;
+    std::vector<int32_t> done;
+    PlanGuard plan;
+    cudaStream_t stream = nullptr;
+    int remaining = 0;
+    double t0 = 0;
+  };
+  // a small pool of streams for the batches: an idle one is reused, so the number of streams
+  // (and of hardware queues they map to) stays at the number of batches in flight
+  struct StreamPool {
+    std::vector<cudaStream_t> all, idle;
+    cudaStream_t poll = nullptr;
+    ~StreamPool() { for (cudaStream_t s : all) cudaStreamDestroy(s); if (poll) cudaStreamDestroy(poll); g_dd_stream = nullptr; g_dd_poll_stream = nullptr; }
+  } pool;
+  DAFS_CUDA_TRY(cudaStreamCreateWithFlags(&pool.poll, cudaStreamNonBlocking));
+  std::vector<std::unique_ptr<Batch>> inflight;
+  std::vector<int> ready;
+  for (int k = n; k < nn; ++k) if (left[k] < n && right[k] < n) ready.push_back(k);
+  const bool serial = getenv("DAFS_PROG_WAVES") != nullptr;   // diagnostics: wait for a whole batch, like the first version
   float ms_avg = 0.0f, ms_dd = 0.0f;
   double ms_dd_host = 0.0;
   int64_t total_iters = 0;
   float root_score = 0.0f;
-  for (int lv = 1; lv <= max_level; ++lv) {
-    std::vector<int> wave;
-    for (int k = n; k < nn; ++k) if (level[k] == lv) wave.push_back(k);
-    const int W = (int)wave.size();
-    // sides, members and maps of the wave
-    std::vector<ProgSide> sides((size_t)2 * W);
-    std::vector<ProgNode> nodes(W);
-    std::vector<int> mem_seq;
-    std::vector<int64_t> mem_col, mem_inv;
-    std::vector<int> maps;
-    std::vector<int2> bp_tasks, mp_tasks;
-    int64_t dense = 0;
-    int accW = 32;
-    for (int q = 0; q < W; ++q) {
-      const int k = wave[q];
-      for (int sd = 0; sd < 2; ++sd) {
-        const Aln& a = aln[sd == 0 ? left[k] : right[k]];
-        ProgSide& S = sides[2 * q + sd];
-        S.L = a.L; S.rows = (int)a.seq.size(); S.mem0 = (int)mem_seq.size(); S.pad = 0; S.out = dense;
-        dense += (int64_t)a.L * a.L;
-        accW = std::max(accW, (a.L + 31) & ~31);
-        for (int r = 0; r < S.rows; ++r) {
-          const int s = a.seq[r];
-          mem_seq.push_back(s);
-          mem_col.push_back((int64_t)maps.size());
-          const uint8_t* g = a.bits.data() + (size_t)r * a.L;
-          for (int c = 0; c < a.L; ++c) if (g[c]) maps.push_back(c);
-          mem_inv.push_back((int64_t)maps.size());
-          int ii = 0;
-          for (int c = 0; c < a.L; ++c) maps.push_back(g[c] ? ii++ : -1);
-          if (ii != len[s]) return fail(DAFS_CUDA_ECUDA, "internal: alignment row of sequence %d holds %d residues", s, ii);
+  int batches = 0, built = 0;
+  const bool verbose = getenv("DAFS_PROG_VERBOSE") != nullptr;
+  double tm_sum[12] = {0}, tm_max[12] = {0};   // host phases: prep, averaging, plan create, plan run, poll, finish
+  auto lap = [&](int k, double t_from) { const double d = now_ms() - t_from; tm_sum[k] += d; tm_max[k] = std::max(tm_max[k], d); return now_ms(); };
+  // a solved node: merge the children (project_alignment), record, maybe release the parent
+  auto finish = [&](Batch& Bt, int q) -> int {
+    const int k = Bt.node[q];
+    const dafs_dd_result& r = Bt.res[q];
+    if (r.status != 0) return fail(DAFS_CUDA_ECUDA, "node %d: the alignment traceback left the envelope (the reference would not terminate)", k);
+    const Aln& a1 = aln[left[k]];
+    const Aln& a2 = aln[right[k]];
+    merge(aln[k], a1, a2, Bt.zs[q].data());
+    R->node_iters[k] = r.iters; R->node_violated[k] = r.violated; R->node_score[k] = r.score;
+    R->node_L[k] = aln[k].L;
+    total_iters += r.iters;
+    if (k == nn - 1) {
+      consensus(R->ss, aln[k].L, Bt.xs[q].data(), a1.L, Bt.ys[q].data(), a2.L, Bt.zs[q].data());
+      root_score = r.score;
+    }
+    std::vector<uint8_t>().swap(aln[left[k]].bits);       // children are no longer needed
+    std::vector<uint8_t>().swap(aln[right[k]].bits);
+    ++built;
+    const int pk = parent[k];
+    if (pk >= 0) {
+      const int sib = left[pk] == k ? right[pk] : left[pk];
+      if (aln[sib].built) ready.push_back(pk);
+    }
+    return DAFS_CUDA_OK;
+  };
+  PinGuard dense_pin;
+  size_t dense_cap = 0;
+  while (built < n - 1) {
+    if (!ready.empty()) {
+      double tl = now_ms();
+      std::unique_ptr<Batch> Bp(new Batch());
+      Batch& Bt = *Bp;
+      Bt.node.swap(ready);
+      std::sort(Bt.node.begin(), Bt.node.end());
+      const int W = (int)Bt.node.size();
+      // sides, members and maps of the batch
+      Bt.sides.resize((size_t)2 * W);
+      std::vector<ProgSide>& sides = Bt.sides;
+      std::vector<ProgNode> nodes(W);
+      std::vector<int> mem_seq;
+      std::vector<int64_t> mem_col, mem_inv;
+      std::vector<int> maps;
+      std::vector<int2> bp_tasks, mp_tasks;
+      int64_t dense = 0;
+      int accW = 32;
+      for (int q = 0; q < W; ++q) {
+        const int k = Bt.node[q];
+        for (int sd = 0; sd < 2; ++sd) {
+          const Aln& a = aln[sd == 0 ? left[k] : right[k]];
+          ProgSide& S = sides[2 * q + sd];
+          S.L = a.L; S.rows = (int)a.seq.size(); S.mem0 = (int)mem_seq.size(); S.pad = 0; S.out = dense;
+          dense += (int64_t)a.L * a.L;
+          accW = std::max(accW, (a.L + 31) & ~31);
+          for (int r = 0; r < S.rows; ++r) {
+            const int s = a.seq[r];
+            mem_seq.push_back(s);
+            mem_col.push_back((int64_t)maps.size());
+            const uint8_t* g = a.bits.data() + (size_t)r * a.L;
+            for (int c = 0; c < a.L; ++c) if (g[c]) maps.push_back(c);
+            mem_inv.push_back((int64_t)maps.size());
+            int ii = 0;
+            for (int c = 0; c < a.L; ++c) maps.push_back(g[c] ? ii++ : -1);
+            if (ii != len[s]) return fail(DAFS_CUDA_ECUDA, "internal: alignment row of sequence %d holds %d residues", s, ii);
+          }
+          for (int c = 0; c < a.L; ++c) bp_tasks.push_back(make_int2(2 * q + sd, c));
         }
-        for (int c = 0; c < a.L; ++c) bp_tasks.push_back(make_int2(2 * q + sd, c));
+        nodes[q].side1 = 2 * q; nodes[q].side2 = 2 * q + 1; nodes[q].pad0 = nodes[q].pad1 = 0; nodes[q].out = dense;
+        dense += (int64_t)sides[2 * q].L * sides[2 * q + 1].L;
+        for (int c = 0; c < sides[2 * q].L; ++c) mp_tasks.push_back(make_int2(q, c));
       }
-      nodes[q].side1 = 2 * q; nodes[q].side2 = 2 * q + 1; nodes[q].pad0 = nodes[q].pad1 = 0; nodes[q].out = dense;
-      dense += (int64_t)sides[2 * q].L * sides[2 * q + 1].L;
-      for (int c = 0; c < sides[2 * q].L; ++c) mp_tasks.push_back(make_int2(q, c));
-    }
-    int wpb = 8;
-    while (wpb > 1 && (size_t)wpb * accW * sizeof(float) > (size_t(96) << 10)) wpb /= 2;
-    const size_t smem = (size_t)wpb * accW * sizeof(float);
-    if (smem > (size_t(227) << 10)) return fail(DAFS_CUDA_EINVAL, "alignment of %d columns is too long for the averaging kernels", accW);
-    if (smem > (48 << 10)) {
-      DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    }
-    DevBufs WB;                                   // the wave's device buffers
-    ProgSide* d_sides = nullptr; ProgNode* d_nodes = nullptr; int* d_mem_seq = nullptr; int64_t* d_mem_col = nullptr;
-    int64_t* d_mem_inv = nullptr; int* d_maps = nullptr; int2* d_bp_tasks = nullptr; int2* d_mp_tasks = nullptr; float* d_dense = nullptr;
-    DAFS_CUDA_TRY(WB.get(&d_sides, sides.size()));
-    DAFS_CUDA_TRY(WB.get(&d_nodes, nodes.size()));
-    DAFS_CUDA_TRY(WB.get(&d_mem_seq, mem_seq.size()));
-    DAFS_CUDA_TRY(WB.get(&d_mem_col, mem_col.size()));
-    DAFS_CUDA_TRY(WB.get(&d_mem_inv, mem_inv.size()));
-    DAFS_CUDA_TRY(WB.get(&d_maps, maps.size()));
-    DAFS_CUDA_TRY(WB.get(&d_bp_tasks, bp_tasks.size()));
-    DAFS_CUDA_TRY(WB.get(&d_mp_tasks, mp_tasks.size()));
-    DAFS_CUDA_TRY(WB.get(&d_dense, (size_t)dense));
-    DAFS_CUDA_TRY(h2d(d_sides, sides.data(), sizeof(ProgSide) * sides.size()));
-    DAFS_CUDA_TRY(h2d(d_nodes, nodes.data(), sizeof(ProgNode) * nodes.size()));
-    DAFS_CUDA_TRY(h2d(d_mem_seq, mem_seq.data(), sizeof(int) * mem_seq.size()));
-    DAFS_CUDA_TRY(h2d(d_mem_col, mem_col.data(), sizeof(int64_t) * mem_col.size()));
-    DAFS_CUDA_TRY(h2d(d_mem_inv, mem_inv.data(), sizeof(int64_t) * mem_inv.size()));
-    DAFS_CUDA_TRY(h2d(d_maps, maps.data(), sizeof(int) * maps.size()));
-    DAFS_CUDA_TRY(h2d(d_bp_tasks, bp_tasks.data(), sizeof(int2) * bp_tasks.size()));
-    DAFS_CUDA_TRY(h2d(d_mp_tasks, mp_tasks.data(), sizeof(int2) * mp_tasks.size()));
-    A.sides = d_sides; A.nodes = d_nodes; A.mem_seq = d_mem_seq; A.mem_col = d_mem_col; A.mem_inv = d_mem_inv;
-    A.maps = d_maps; A.dense = d_dense;
-    DAFS_CUDA_TRY(cudaEventRecord(G.a, st));
-    prog_avg_bp_kernel<<<grid_for((int64_t)bp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)bp_tasks.size(), d_bp_tasks, accW);
-    prog_avg_mp_kernel<<<grid_for((int64_t)mp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)mp_tasks.size(), d_mp_tasks, accW);
-    launches += 2;
-    DAFS_CUDA_TRY(cudaGetLastError());
-    DAFS_CUDA_TRY(cudaEventRecord(G.b, st));
-    PinGuard H;
-    H.p = pinned_alloc(sizeof(float) * (size_t)dense);
-    if (!H.p) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %lld floats failed", (long long)dense);
-    float* h_dense = static_cast<float*>(H.p);
-    DAFS_CUDA_TRY(cudaMemcpyAsync(h_dense, d_dense, sizeof(float) * (size_t)dense, cudaMemcpyDeviceToHost, st));
-    DAFS_CUDA_TRY(cudaStreamSynchronize(st));
-    float ms = 0.0f;
-    cudaEventElapsedTime(&ms, G.a, G.b);
-    ms_avg += ms;
-
-    // the wave's DD problems, solved in one batch (solve_by_dd, :1006-1295)
-    const double t_dd0 = now_ms();
-    std::vector<dafs_dd_problem> prob(W);
-    std::vector<dafs_dd_result> res(W);
-    std::vector<std::vector<uint32_t>> xs(W), ys(W), zs(W);
-    for (int q = 0; q < W; ++q) {
-      const ProgSide& S1 = sides[2 * q];
-      const ProgSide& S2 = sides[2 * q + 1];
-      dafs_dd_problem& P = prob[q];
-      P.L1 = S1.L; P.L2 = S2.L; P.N1 = S1.rows; P.N2 = S2.rows;
-      P.p_x = h_dense + S1.out; P.p_y = h_dense + S2.out; P.p_z = h_dense + nodes[q].out;
-      P.w = prm->w; P.th_s = prm->th_s; P.min_th_s = prm->min_th_s; P.th_a = prm->th_a; P.eta0 = prm->eta0; P.t_max = prm->t_max;
-      xs[q].assign(S1.L, kNone); ys[q].assign(S2.L, kNone); zs[q].assign(S1.L, kNone);
-      res[q] = dafs_dd_result{};
-      res[q].x = xs[q].data(); res[q].y = ys[q].data(); res[q].z = zs[q].data();
-    }
-    {
-      PlanGuard PG;
-      int rc = dafs_cuda_dd_plan_create(W, prob.data(), 0, &PG.p);
-      if (!rc) rc = dafs_cuda_dd_plan_run(PG.p);
-      float dms = 0.0f;
-      if (!rc) rc = dafs_cuda_dd_plan_sync(PG.p, &dms);
-      if (!rc) rc = dafs_cuda_dd_plan_fetch(PG.p, res.data());
-      if (rc) return rc;
-      ms_dd += dms;
+      int wpb = 8;
+      while (wpb > 1 && (size_t)wpb * accW * sizeof(float) > (size_t(96) << 10)) wpb /= 2;
+      const size_t smem = (size_t)wpb * accW * sizeof(float);
+      if (smem > (size_t(227) << 10)) return fail(DAFS_CUDA_EINVAL, "alignment of %d columns is too long for the averaging kernels", accW);
+      if (smem > (48 << 10)) {
+        DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      }
+      tl = lap(0, tl);
+      DevBufs WB;                                   // the batch's device buffers (released after the copy below)
+      ProgSide* d_sides = nullptr; ProgNode* d_nodes = nullptr; int* d_mem_seq = nullptr; int64_t* d_mem_col = nullptr;
+      int64_t* d_mem_inv = nullptr; int* d_maps = nullptr; int2* d_bp_tasks = nullptr; int2* d_mp_tasks = nullptr; float* d_dense = nullptr;
+      DAFS_CUDA_TRY(WB.get(&d_sides, sides.size()));
+      DAFS_CUDA_TRY(WB.get(&d_nodes, nodes.size()));
+      DAFS_CUDA_TRY(WB.get(&d_mem_seq, mem_seq.size()));
+      DAFS_CUDA_TRY(WB.get(&d_mem_col, mem_col.size()));
+      DAFS_CUDA_TRY(WB.get(&d_mem_inv, mem_inv.size()));
+      DAFS_CUDA_TRY(WB.get(&d_maps, maps.size()));
+      DAFS_CUDA_TRY(WB.get(&d_bp_tasks, bp_tasks.size()));
+      DAFS_CUDA_TRY(WB.get(&d_mp_tasks, mp_tasks.size()));
+      DAFS_CUDA_TRY(WB.get(&d_dense, (size_t)dense));
+      tl = lap(6, tl);
+      DAFS_CUDA_TRY(h2d(d_sides, sides.data(), sizeof(ProgSide) * sides.size()));
+      DAFS_CUDA_TRY(h2d(d_nodes, nodes.data(), sizeof(ProgNode) * nodes.size()));
+      DAFS_CUDA_TRY(h2d(d_mem_seq, mem_seq.data(), sizeof(int) * mem_seq.size()));
+      DAFS_CUDA_TRY(h2d(d_mem_col, mem_col.data(), sizeof(int64_t) * mem_col.size()));
+      DAFS_CUDA_TRY(h2d(d_mem_inv, mem_inv.data(), sizeof(int64_t) * mem_inv.size()));
+      DAFS_CUDA_TRY(h2d(d_maps, maps.data(), sizeof(int) * maps.size()));
+      DAFS_CUDA_TRY(h2d(d_bp_tasks, bp_tasks.data(), sizeof(int2) * bp_tasks.size()));
+      DAFS_CUDA_TRY(h2d(d_mp_tasks, mp_tasks.data(), sizeof(int2) * mp_tasks.size()));
+      A.sides = d_sides; A.nodes = d_nodes; A.mem_seq = d_mem_seq; A.mem_col = d_mem_col; A.mem_inv = d_mem_inv;
+      A.maps = d_maps; A.dense = d_dense;
+      DAFS_CUDA_TRY(cudaEventRecord(G.a, st));
+      prog_avg_bp_kernel<<<grid_for((int64_t)bp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)bp_tasks.size(), d_bp_tasks, accW);
+      prog_avg_mp_kernel<<<grid_for((int64_t)mp_tasks.size(), wpb), 32 * wpb, smem, st>>>(A, (int64_t)mp_tasks.size(), d_mp_tasks, accW);
+      launches += 2;
+      DAFS_CUDA_TRY(cudaGetLastError());
+      DAFS_CUDA_TRY(cudaEventRecord(G.b, st));
+      tl = lap(7, tl);
+      // the dense averages are read once, by dafs_cuda_dd_plan_create below, so every batch lands in
+      // the same page-locked buffer; cudaHostAlloc waits for running kernels (51 ms behind a long DD
+      // batch), so it is sized generously by the first batch, which runs with nothing in flight
+      if (dense_cap < (size_t)dense) {
+        if (dense_pin.p) { dafs::pinned_free(dense_pin.p); dense_pin.p = nullptr; }
+        dense_cap = (size_t)dense + (size_t)dense / 2;
+        dense_pin.p = pinned_alloc(sizeof(float) * dense_cap);
+        if (!dense_pin.p) { dense_cap = 0; return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %lld floats failed", (long long)dense); }
+      }
+      tl = lap(8, tl);
+      float* h_dense = static_cast<float*>(dense_pin.p);
+      DAFS_CUDA_TRY(cudaMemcpyAsync(h_dense, d_dense, sizeof(float) * (size_t)dense, cudaMemcpyDeviceToHost, st));
+      DAFS_CUDA_TRY(cudaStreamSynchronize(st));
+      float ms = 0.0f;
+      cudaEventElapsedTime(&ms, G.a, G.b);
+      ms_avg += ms;
+      tl = lap(1, tl);
+      // the batch's DD problems, one asynchronous launch (solve_by_dd, :1006-1295)
+      Bt.t0 = now_ms();
+      Bt.prob.resize(W); Bt.res.resize(W); Bt.xs.resize(W); Bt.ys.resize(W); Bt.zs.resize(W);
+      Bt.done.assign(W, 0);
+      Bt.remaining = W;
+      for (int q = 0; q < W; ++q) {
+        const ProgSide& S1 = sides[2 * q];
+        const ProgSide& S2 = sides[2 * q + 1];
+        dafs_dd_problem& P = Bt.prob[q];
+        P.L1 = S1.L; P.L2 = S2.L; P.N1 = S1.rows; P.N2 = S2.rows;
+        P.p_x = h_dense + S1.out; P.p_y = h_dense + S2.out; P.p_z = h_dense + nodes[q].out;
+        P.w = prm->w; P.th_s = prm->th_s; P.min_th_s = prm->min_th_s; P.th_a = prm->th_a; P.eta0 = prm->eta0; P.t_max = prm->t_max;
+        Bt.xs[q].assign(S1.L, kNone); Bt.ys[q].assign(S2.L, kNone); Bt.zs[q].assign(S1.L, kNone);
+        Bt.res[q] = dafs_dd_result{};
+        Bt.res[q].x = Bt.xs[q].data(); Bt.res[q].y = Bt.ys[q].data(); Bt.res[q].z = Bt.zs[q].data();
+      }
+      {
+        if (pool.idle.empty()) {
+          cudaStream_t s = nullptr;
+          DAFS_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+          pool.all.push_back(s); pool.idle.push_back(s);
+        }
+        Bt.stream = pool.idle.back(); pool.idle.pop_back();
+        g_dd_stream = Bt.stream; g_dd_poll_stream = pool.poll;
+        int rc = dafs_cuda_dd_plan_create(W, Bt.prob.data(), 0, &Bt.plan.p);
+        g_dd_stream = nullptr; g_dd_poll_stream = nullptr;
+        tl = lap(2, tl);
+        if (!rc) rc = dafs_cuda_dd_plan_run(Bt.plan.p);
+        tl = lap(3, tl);
+        if (rc) return rc;
+      }
       launches += 1;
-      if (getenv("DAFS_PROG_VERBOSE")) {           // per-wave diagnostics for tools/prof_prog.py
-        dafs_dd_info inf{};
-        dafs_cuda_dd_plan_info(PG.p, &inf);
-        int slow = 0;
-        for (int q = 1; q < W; ++q) if (res[q].iters > res[slow].iters) slow = q;
-        const float* cy = res[slow].cycles;
-        fprintf(stderr, "[prog] wave %d: %d problems, DD %.2f ms (plan wall %.2f ms), grid %d, smem %d B, in_smem %#x, cbp %lld; slowest: L1 %d L2 %d N %d+%d iters %d cbp %lld, "
-                        "cycles/iter x %.0f+%.0f y %.0f+%.0f z %.0f+%.0f\n",
-                lv, W, dms, now_ms() - t_dd0, inf.grid, inf.smem_bytes, inf.items_in_smem, (long long)inf.total_cbp, prob[slow].L1, prob[slow].L2,
-                prob[slow].N1, prob[slow].N2, res[slow].iters, (long long)res[slow].ncbp,
-                cy[0] / std::max(1, res[slow].iters + 1), cy[1] / std::max(1, res[slow].iters + 1), cy[2] / std::max(1, res[slow].iters + 1),
-                cy[3] / std::max(1, res[slow].iters + 1), cy[4] / std::max(1, res[slow].iters + 1), cy[5] / std::max(1, res[slow].iters + 1));
+      ++batches;
+      inflight.push_back(std::move(Bp));
+      if (!serial) continue;
+    }
+    if (inflight.empty()) return fail(DAFS_CUDA_ECUDA, "internal: no node is ready and none is in flight");
+    // harvest
+    bool progress = false;
+    for (size_t bi = 0; bi < inflight.size();) {
+      Batch& Bt = *inflight[bi];
+      const int W = (int)Bt.node.size();
+      int32_t fresh = 0;
+      std::vector<int32_t> before;
+      if (serial) {
+        int rc = dafs_cuda_dd_plan_fetch(Bt.plan.p, Bt.res.data());
+        if (rc) return rc;
+        before.assign(W, 0);
+        Bt.done.assign(W, 1);
+        fresh = W;
+      } else {
+        before = Bt.done;
+        const double tp = now_ms();
+        const int rc = dafs_cuda_dd_plan_poll(Bt.plan.p, Bt.res.data(), Bt.done.data(), &fresh);
+        lap(4, tp);
+        if (rc) return rc;
+      }
+      if (fresh > 0) {
+        progress = true;
+        const double tf = now_ms();
+        for (int q = 0; q < W; ++q)
+          if (Bt.done[q] && !before[q]) { const int rc = finish(Bt, q); if (rc) return rc; }
+        lap(5, tf);
+        Bt.remaining -= fresh;
+      }
+      if (Bt.remaining == 0) {
+        float dms = 0.0f;
+        const double ts = now_ms();
+        const int rc = dafs_cuda_dd_plan_sync(Bt.plan.p, &dms);
+        lap(9, ts);
+        if (rc) return rc;
+        ms_dd += dms;
+        ms_dd_host += now_ms() - Bt.t0;
+        if (verbose) {                               // per-batch diagnostics for tools/bench_prog.py
+          dafs_dd_info inf{};
+          dafs_cuda_dd_plan_info(Bt.plan.p, &inf);
+          int slow = 0;
+          for (int q = 1; q < W; ++q) if (Bt.res[q].iters > Bt.res[slow].iters) slow = q;
+          const float* cy = Bt.res[slow].cycles;
+          const float it1 = (float)std::max(1, Bt.res[slow].iters + 1);
+          fprintf(stderr, "[prog] t = %.1f .. %.1f ms: batch of %d problems (first node %d, level %d): DD %.2f ms (wall %.2f ms), grid %d x %d threads, smem %d B, in_smem %#x, cbp %lld; "
+                          "slowest: on the device %.1f .. %.1f, L1 %d L2 %d N %d+%d iters %d cbp %lld, cycles/iter x %.0f+%.0f y %.0f+%.0f z %.0f+%.0f\n",
+                  Bt.t0 - t_begin, now_ms() - t_begin, W, Bt.node[0], level[Bt.node[0]], dms, now_ms() - Bt.t0, inf.grid, inf.block, inf.smem_bytes, inf.items_in_smem, (long long)inf.total_cbp,
+                  cy[6], cy[7], Bt.prob[slow].L1, Bt.prob[slow].L2, Bt.prob[slow].N1, Bt.prob[slow].N2, Bt.res[slow].iters, (long long)Bt.res[slow].ncbp,
+                  cy[0] / it1, cy[1] / it1, cy[2] / it1, cy[3] / it1, cy[4] / it1, cy[5] / it1);
+        }
+        pool.idle.push_back(Bt.stream);
+        const double te = now_ms();
+        inflight.erase(inflight.begin() + bi);
+        lap(10, te);
+      } else {
+        ++bi;
       }
     }
-    ms_dd_host += now_ms() - t_dd0;
-    for (int q = 0; q < W; ++q) {
-      const int k = wave[q];
-      if (res[q].status != 0) return fail(DAFS_CUDA_ECUDA, "node %d: the alignment traceback left the envelope (the reference would not terminate)", k);
-      const Aln& a1 = aln[left[k]];
-      const Aln& a2 = aln[right[k]];
-      merge(aln[k], a1, a2, zs[q].data());
-      R->node_iters[k] = res[q].iters; R->node_violated[k] = res[q].violated; R->node_score[k] = res[q].score;
-      R->node_L[k] = aln[k].L;
-      total_iters += res[q].iters;
-      if (k == nn - 1) {
-        consensus(R->ss, aln[k].L, xs[q].data(), a1.L, ys[q].data(), a2.L, zs[q].data());
-        root_score = res[q].score;
-      }
-    }
-    for (int q = 0; q < W; ++q) {                 // children are no longer needed
-      Aln().bits.swap(aln[left[wave[q]]].bits);
-      Aln().bits.swap(aln[right[wave[q]]].bits);
-    }
+    if (!progress && ready.empty()) std::this_thread::sleep_for(std::chrono::microseconds(50));
   }
+  if (verbose)
+    fprintf(stderr, "[prog] host phases, sum / longest single (ms): prep %.1f / %.1f, averaging %.1f / %.1f, plan create %.1f / %.1f, plan run %.1f / %.1f, poll %.1f / %.1f, merge %.1f / %.1f; device alloc %.1f / %.1f, upload + launch %.1f / %.1f, pinned alloc %.1f / %.1f, plan sync %.1f / %.1f, plan destroy %.1f / %.1f\n",
+            tm_sum[0], tm_max[0], tm_sum[1], tm_max[1], tm_sum[2], tm_max[2], tm_sum[3], tm_max[3], tm_sum[4], tm_max[4], tm_sum[5], tm_max[5], tm_sum[6], tm_max[6], tm_sum[7], tm_max[7], tm_sum[8], tm_max[8], tm_sum[9], tm_max[9], tm_sum[10], tm_max[10]);
   const Aln& root = aln[nn - 1];
   R->seq.assign(root.seq.begin(), root.seq.end());
   R->bits = root.bits;
@@ -458,7 +575,7 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   out->n_nodes = nn;
   out->node_iters = R->node_iters.data(); out->node_violated = R->node_violated.data();
   out->node_score = R->node_score.data(); out->node_L = R->node_L.data();
-  out->waves = max_level; out->total_iters = total_iters; out->gpu_launches = launches;
+  out->waves = batches; out->total_iters = total_iters; out->gpu_launches = launches;
   out->ms_average = ms_avg; out->ms_dd = ms_dd; out->ms_dd_host = (float)ms_dd_host;
   out->ms_total = (float)(now_ms() - t_begin);
   out->owner_ = R;

@@ -210,6 +210,11 @@ int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_tr
 int dafs_cuda_dd_plan_run(dafs_dd_plan* plan);
 int dafs_cuda_dd_plan_sync(dafs_dd_plan* plan, float* device_ms);
 int dafs_cuda_dd_plan_fetch(dafs_dd_plan* plan, dafs_dd_result* res);
+/* Non-blocking harvest while run() is in flight: every problem that has finished and whose
+ * done[k] is still 0 is written to res[k] (same fields as fetch) and done[k] set to 1;
+ * *n_new = how many.  The caller keeps done[] (nprob entries, zeroed before run).  This is what
+ * lets dafs_cuda_progressive start a guide-tree node as soon as its two children are solved. */
+int dafs_cuda_dd_plan_poll(dafs_dd_plan* plan, dafs_dd_result* res, int32_t* done, int32_t* n_new);
 void dafs_cuda_dd_plan_destroy(dafs_dd_plan* plan);
 
 typedef struct dafs_dd_info {
@@ -270,7 +275,8 @@ int dafs_cuda_guide_tree(int nseq, const float* sim, int32_t* left, int32_t* rig
  * children (:557-607), average_matching_probability (:513-555), solve_by_dd (:1006-1295),
  * project_alignment (:766-826); for the root also project_secondary_structure (:828-876)
  * and the consensus (:941-945).  Nodes whose children are finished are processed together
- * (one averaging launch pair + one batched DD launch per wave); sibling subtrees share no
+ * (one averaging launch pair + one batched DD launch per batch of ready nodes, harvested
+ * problem by problem while the launch is still running); sibling subtrees share no
  * state, so the results equal the reference's depth-first recursion bit for bit.
  * Covers use_alifold_ == false (--no-alifold; RNAalifold needs ViennaRNA) and
  * use_bp_update_ == false (the default).
@@ -298,7 +304,8 @@ typedef struct dafs_prog_result {
   const uint32_t* node_violated;
   const float* node_score;
   const int32_t* node_L;     /* alignment columns of the node                             */
-  int32_t waves;             /* batched DD launches = height of the tree                  */
+  int32_t waves;             /* batched DD launches (a node goes out as soon as both its
+                                children are solved; at least the height of the tree)      */
   int64_t total_iters;
   int32_t gpu_launches;
   float ms_average;          /* device time of the averaging kernels, all waves           */
