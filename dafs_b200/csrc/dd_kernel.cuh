@@ -450,28 +450,59 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
   const float score = mine[L2];                            // el(L1) = L2: dp[L1][L2] was written
   const long long t1 = clock64();
   // ---- traceback (:300-312) + alignment read-out (:317-335) ------------------
+  // A row is left through the cell the walk reaches after a run of 'Y' codes (3, leftwards,
+  // nothing recorded): code 1 records the pair and enters the row above one column to the
+  // left, code 2 enters it in the same column.  Alignments are mostly diagonal, so lane l
+  // decodes row i - l on the guess that the walk enters it at column k - l; the guesses are
+  // right up to the first lane whose predecessor left its row somewhere else, that prefix
+  // is committed (up to 32 rows per round) and the walk resumes from the first wrong guess.
   for (int i = lane; i < L1; i += 32) sc.zres[i] = DD_NOPAIR;
   __syncwarp();
-  if (lane == 0) {
+  {
     int i = L1, k = L2;
-    uint2 ev = A.env[L1];
     while (i > 0 && k > 0) {       // row 0 is all 'Y', column 0 all 'X': nothing more to record
-      const uint2 ev_up = A.env[i - 1];                            // wanted when the walk moves up: ask now
-      const int ef = max(1, (int)ev.x), c = k - ef;
-      if (c < 0 || k > (int)ev.y) { *bad = 1; break; }             // a cell that was never filled
-      const uint2 w = sc.trz[(size_t)i * ts + (c >> 5)];
-      // a run of 'Y' codes (3) only moves left and records nothing: jump to the nearest
-      // column at or left of k in this word whose code is not 3
-      const int b = c & 31;
-      const uint32_t stop = ~(w.x & w.y) & (0xffffffffu >> (31 - b));
-      if (stop == 0u) { k -= b + 1; continue; }                    // the run leaves the word
-      const int b2 = 31 - __clz(stop);
-      k -= b - b2;
-      const uint32_t code = ((w.x >> b2) & 1u) | (((w.y >> b2) & 1u) << 1);
-      if (code == 1u) { --i; --k; sc.zres[i] = (uint32_t)k; }
-      else if (code == 2u) --i;
-      else { *bad = 1; break; }
-      ev = ev_up;
+      const int ri = i - lane, kg = k - lane;
+      int status = 3;              // 0 left the row upwards, 1 reached column 0, 2 unfilled cell, 3 no guess
+      int kx = 0, rec = -1;
+      if (ri >= 1 && kg >= 1) {
+        const uint2 ev = A.env[ri];
+        const int ef = max(1, (int)ev.x);
+        int kk = kg, c = kk - ef;
+        if (c < 0 || kk > (int)ev.y) status = 2;                     // a cell that was never filled
+        else {
+          const uint2* trow = sc.trz + (size_t)ri * ts;
+          for (;;) {
+            const uint2 w = trow[c >> 5];
+            // jump to the nearest column at or left of kk in this word whose code is not 3
+            const int b = c & 31;
+            const uint32_t stop = ~(w.x & w.y) & (0xffffffffu >> (31 - b));
+            if (stop == 0u) {                                        // the run leaves the word
+              kk -= b + 1; c -= b + 1;
+              if (kk <= 0) { status = 1; break; }
+              if (c < 0) { status = 2; break; }
+              continue;
+            }
+            const int b2 = 31 - __clz(stop);
+            kk -= b - b2;
+            const uint32_t code = ((w.x >> b2) & 1u) | (((w.y >> b2) & 1u) << 1);
+            if (code == 1u) { rec = kk - 1; kx = kk - 1; status = 0; }
+            else if (code == 2u) { kx = kk; status = 0; }
+            else status = 2;
+            break;
+          }
+        }
+      }
+      const int pkx = __shfl_up_sync(0xffffffffu, kx, 1);
+      const int pst = __shfl_up_sync(0xffffffffu, status, 1);
+      const bool link = lane == 0 || (status != 3 && pst == 0 && pkx == kg);
+      const unsigned lm = __ballot_sync(0xffffffffu, link);
+      const int nacc = (lm == 0xffffffffu) ? 32 : __ffs(~lm) - 1;    // >= 1: lane 0 holds the true state
+      if (lane < nacc && rec >= 0) sc.zres[ri - 1] = (uint32_t)rec;
+      const int lst = __shfl_sync(0xffffffffu, status, nacc - 1);
+      const int lkx = __shfl_sync(0xffffffffu, kx, nacc - 1);
+      if (lst == 2) { if (lane == 0) *bad = 1; break; }
+      if (lst == 1) break;
+      i -= nacc; k = lkx;
     }
   }
   __syncwarp();
