@@ -357,6 +357,7 @@ static void plan_layout(DDLayout& lay, const DDMaxima& m, size_t smem_budget, in
   lay.lp2 = (m.nJy + 2) & ~1;
   lay.trs1 = m.nJx; lay.trs2 = m.nJy;
   lay.ts = (m.bw + 31) / 32;
+  { const char* e = getenv("DAFS_DD_NW_CHUNKED"); lay.nw_chunked = (e && atoi(e) > 0) ? 1 : 0; }
   lay.tr16 = (m.col > 120) ? 1u : 0u;
   const size_t trb = lay.tr16 ? 2 : 1;
   size_t sz[DD_NITEMS];
@@ -654,7 +655,7 @@ extern "C" int dafs_cuda_dd_plan_fetch(dafs_dd_plan* p, dafs_dd_result* res) {
 
 extern "C" int dafs_cuda_dd_plan_info(dafs_dd_plan* p, dafs_dd_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
-  info->grid = p->grid; info->block = 32 * (2 * p->team + 1); info->cols_per_lane = 0; info->smem_bytes = p->smem;
+  info->grid = p->grid; info->block = 32 * (2 * p->team + 1); info->cols_per_lane = p->lay.ts; info->smem_bytes = p->smem;
   info->ctas_per_sm = p->ctas_per_sm; info->items_in_smem = p->lay.in_smem;
   info->workspace_bytes = (int64_t)p->lay.ws_stride * p->grid;
   info->arena_bytes = (int64_t)(p->cst_bytes + p->res_bytes);
@@ -790,6 +791,7 @@ extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, con
   uint2* d_env = B.take<uint2>(L1 + 1);
   sc.rowbuf = B.take<float>(2 * (L2 + 2)); sc.trz = B.take<uint2>((size_t)(L1 + 1) * ts); sc.zres = B.take<uint32_t>(L1);
   sc.ts = ts;
+  { const char* e = getenv("DAFS_DD_NW_CHUNKED"); sc.chunked = (e && atoi(e) > 0) ? 1 : 0; }
   uint32_t* d_al = B.take<uint32_t>(L1); float* d_score = B.take<float>(1); int* d_bad = B.take<int>(1);
   DAFS_CUDA_TRY(cudaMemcpy(d_boff, boff.data(), sizeof(int) * (L1 + 2), cudaMemcpyHostToDevice));
   if (n) {

@@ -104,6 +104,7 @@ struct DDLayout {
   int lp1, lp2;                // row stride of the Nussinov row buffers (max live columns, odd)
   int trs1, trs2;              // row stride of the Nussinov traceback arrays (max live columns)
   int ts;                      // NW traceback words (uint2) per row: ceil(widest band / 32)
+  int nw_chunked;              // see NwScratch::chunked
   char* ws;                    // global workspace
   size_t ws_stride;            // per CTA
 };
@@ -174,6 +175,7 @@ struct NwScratch {
                     //               per 32 band columns
   uint32_t* zres;   // [L1] result
   int ts;           // words per row = ceil(widest band / 32)
+  int chunked;      // 1: 32 columns per scan even where one scan per row would do (DAFS_DD_NW_CHUNKED, A/B runs)
 };
 
 }  // namespace dafs
@@ -381,6 +383,144 @@ __device__ __forceinline__ float nussinov_warp(const DDNus& S, const NusScratch&
 
 namespace dafs {
 
+// NW fill when every band of the problem is at most 32 columns wide (alignments of close
+// homologs): lane l IS band column ef(r) + l, and the row above stays in registers -- its
+// cells dp[r-1][k] and dp[r-1][k-1] come by two independent shuffles from the lanes that
+// held them (the band moved right by ef(r) - ef(r-1) columns), not through a row buffer in
+// shared memory; the band data of row r+1 is requested before row r's scan.  Same
+// operands, compares and bits as the chunked row in nw_warp.
+__device__ __forceinline__ float nw_fill_narrow(const DDAln& A, const NwScratch& sc, int lane) {
+  const int L1 = A.L1, L2 = A.L2;
+  const float th = A.th;
+  uint2* trow = sc.trz;
+  float vprev = 0.0f, cprev = 0.0f, v = 0.0f;              // row above: dp[r-1][efp + lane], dp[r-1][efp - 1]
+  int efp = 1, wprev = 31;                                 // its first column and width - 1
+  uint2 ev = A.env[1];
+  int ef = max(1, (int)ev.x), el = (int)ev.y;
+  int bidx = A.boff[1] + min(lane, max(el - ef, 0));       // band index of (r, ef + lane), clamped into the row
+  float pv = A.pb[bidx], qv = A.qb[bidx];
+  for (int r = 1; r <= L1; ++r) {
+    // row r + 1: envelope and band data, nothing of it depends on the recursion
+    const int rn = min(r + 1, L1);
+    const uint2 evn = A.env[rn];
+    const int efn = max(1, (int)evn.x), eln = (int)evn.y;
+    const int bn = A.boff[rn] + min(lane, max(eln - efn, 0));
+    const float pvn = A.pb[bn], qvn = A.qb[bn];
+    const bool in = ef + lane <= el;
+    float up = 0.0f, dg = 0.0f;                            // row 0 is 0 everywhere (:270-274)
+    if (r > 1) {
+      const int ju = lane + (ef - efp), jd = ju - 1;       // lanes of the row above that hold columns k and k - 1
+      const float su = __shfl_sync(0xffffffffu, vprev, ju & 31);
+      const float sd = __shfl_sync(0xffffffffu, vprev, jd & 31);
+      up = (ju <= wprev) ? su : -FLT_MAX;                  // right of the band above: never filled
+      dg = (jd < 0) ? cprev : ((jd <= wprev) ? sd : -FLT_MAX);
+    }
+    const float m = __fadd_rn(__fsub_rn(__fadd_rn(dg, pv), th), qv);               // :282
+    const bool c2 = m < up;                                                        // :284
+    float x = in ? (c2 ? up : m) : -FLT_MAX;
+    const float a = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) x = fmaxf(x, __shfl_up_sync(0xffffffffu, x, d));
+    const float carry = (ef == 1) ? 0.0f : -FLT_MAX;       // dp[r][ef-1]
+    v = fmaxf(x, carry);                                                           // dp[r][k]
+    float left = __shfl_up_sync(0xffffffffu, v, 1);                                // dp[r][k-1]
+    if (lane == 0) left = carry;
+    const bool c3 = a < left;                                                      // :289
+    const unsigned lo = __ballot_sync(0xffffffffu, in && (c3 || !c2));             // codes 1 and 3
+    const unsigned hi = __ballot_sync(0xffffffffu, in && (c3 || c2));              // codes 2 and 3
+    if (lane == 0) trow[r] = make_uint2(lo, hi);           // ts == 1
+    vprev = v; cprev = carry; efp = ef; wprev = el - ef;
+    ef = efn; el = eln; pv = pvn; qv = qvn;
+  }
+  __syncwarp();
+  return __shfl_sync(0xffffffffu, v, (L2 - efp) & 31);     // el(L1) = L2: dp[L1][L2] sits in lane L2 - ef(L1)
+}
+
+// One row of the NW fill when every band of the problem is at most 32 CN columns wide:
+// lane l takes the CN consecutive band columns ef + CN l .. ef + CN l + CN - 1, so the
+// row's prefix maximum is ONE five-shuffle scan over the lanes' own maxima instead of one
+// scan per 32 columns (the scans of a row are a dependent chain through the carry; at
+// 33..64 columns this halves the row's latency).  Same operands, same compares, same
+// bits as the chunked row in nw_warp; the code bits are regrouped into the band-relative
+// words the traceback reads by a second round of ballots.
+template <int CN>
+__device__ __forceinline__ float nw_fill_blocked(const DDAln& A, const NwScratch& sc, int lane) {
+  const int L1 = A.L1, L2 = A.L2;
+  const float th = A.th;
+  for (int k = lane; k < 2 * (L2 + 2); k += 32) sc.rowbuf[k] = -FLT_MAX;
+  __syncwarp();
+  float* prev = sc.rowbuf + (L2 + 2);
+  float* mine = sc.rowbuf;
+  uint2* trow = sc.trz;
+  for (int r = 1; r <= L1; ++r) {
+    { float* t = prev; prev = mine; mine = t; }
+    trow += CN;                                            // ts == CN
+    const uint2 ev = A.env[r];
+    const int ef = max(1, (int)ev.x), el = (int)ev.y;
+    const float* pb = A.pb + (A.boff[r] - ef);             // band index of (r, k) = boff[r] - ef + k
+    const float* qb = A.qb + (A.boff[r] - ef);
+    const float carry = (ef == 1) ? 0.0f : -FLT_MAX;      // dp[r][ef-1]
+    if (lane == 0) mine[ef - 1] = carry;
+    const int kb = ef + CN * lane;
+    float pv[CN], qv[CN], upv[CN + 1], a[CN];
+#pragma unroll
+    for (int j = 0; j < CN; ++j) {                         // clamped into the band: no branch on a load
+      const int kc = min(kb + j, el);
+      pv[j] = pb[kc]; qv[j] = qb[kc];
+    }
+#pragma unroll
+    for (int j = 0; j <= CN; ++j) upv[j] = (r > 1) ? prev[min(kb + j, el + 1) - 1] : 0.0f;   // dp[r-1][kb-1+j]
+    unsigned c2m = 0u, inm = 0u;
+    float x = -FLT_MAX;
+#pragma unroll
+    for (int j = 0; j < CN; ++j) {
+      const bool in = kb + j <= el;
+      const float m = __fadd_rn(__fsub_rn(__fadd_rn(upv[j], pv[j]), th), qv[j]);   // :282
+      const bool c2 = m < upv[j + 1];                                             // :284
+      a[j] = in ? (c2 ? upv[j + 1] : m) : -FLT_MAX;
+      c2m |= (c2 ? 1u : 0u) << j;
+      inm |= (in ? 1u : 0u) << j;
+      x = fmaxf(x, a[j]);
+    }
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) x = fmaxf(x, __shfl_up_sync(0xffffffffu, x, d));
+    float left = __shfl_up_sync(0xffffffffu, x, 1);        // maximum over the lanes to the left
+    left = (lane == 0) ? carry : fmaxf(left, carry);       // dp[r][kb-1]
+    unsigned c3m = 0u;
+#pragma unroll
+    for (int j = 0; j < CN; ++j) {
+      const bool c3 = a[j] < left;                                                // :289
+      const float v = fmaxf(a[j], left);                                          // dp[r][kb+j]
+      c3m |= (c3 ? 1u : 0u) << j;
+      if ((inm >> j) & 1u) mine[kb + j] = v;
+      left = v;
+    }
+    const unsigned lom = inm & (c3m | ~c2m);               // codes 1 and 3
+    const unsigned him = inm & (c3m | c2m);                // codes 2 and 3
+    unsigned bl[CN], bh[CN];
+#pragma unroll
+    for (int j = 0; j < CN; ++j) {
+      bl[j] = __ballot_sync(0xffffffffu, (lom >> j) & 1u);
+      bh[j] = __ballot_sync(0xffffffffu, (him >> j) & 1u);
+    }
+    // band column c = CN l + j  ->  word c / 32, bit c % 32
+#pragma unroll
+    for (int w = 0; w < CN; ++w) {
+      const int c = 32 * w + lane, lsrc = c / CN, j = c - lsrc * CN;
+      unsigned sl = bl[0], sh = bh[0];
+#pragma unroll
+      for (int t = 1; t < CN; ++t) if (j == t) { sl = bl[t]; sh = bh[t]; }
+      const unsigned lo = __ballot_sync(0xffffffffu, (sl >> lsrc) & 1u);
+      const unsigned hi = __ballot_sync(0xffffffffu, (sh >> lsrc) & 1u);
+      if (lane == 0) trow[w] = make_uint2(lo, hi);
+    }
+    __syncwarp();
+  }
+  const float score = mine[L2];                            // el(L1) = L2: dp[L1][L2] was written
+  __syncwarp();
+  return score;
+}
+
 // SparseNeedlemanWunsch::decode(p, q, al) by one warp, one ROW per step.
 // The reference's cell update (needleman_wunsch.cpp:282-293)
 //   v = dp[i-1][k-1] + p - th + q;  if (v < dp[i-1][k]) v = dp[i-1][k];  if (v < dp[i][k-1]) v = dp[i][k-1];
@@ -400,6 +540,12 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
   const long long t0 = clock64();
   const int L1 = A.L1, L2 = A.L2, ts = sc.ts;
   const float th = A.th;
+  float score;
+  if (ts == 1 && !sc.chunked && L1 > 0 && L2 > 0) score = nw_fill_narrow(A, sc, lane);
+  else if (ts == 2 && !sc.chunked) score = nw_fill_blocked<2>(A, sc, lane);
+  else if (ts == 3 && !sc.chunked) score = nw_fill_blocked<3>(A, sc, lane);
+  else if (ts == 4 && !sc.chunked) score = nw_fill_blocked<4>(A, sc, lane);
+  else {
   // Both row buffers start at -FLT_MAX ("outside every band").  A row writes its band
   // and the cell just left of it (0 in column 0, :265-268, else -FLT_MAX, :262-264); the
   // bands only move right, so whatever the next row reads outside this row's band is
@@ -447,7 +593,9 @@ __device__ __forceinline__ float nw_warp(const DDAln& A, const NwScratch& sc, in
     }
     __syncwarp();
   }
-  const float score = mine[L2];                            // el(L1) = L2: dp[L1][L2] was written
+  score = mine[L2];                                        // el(L1) = L2: dp[L1][L2] was written
+  __syncwarp();
+  }
   const long long t1 = clock64();
   // ---- traceback (:300-312) + alignment read-out (:317-335) ------------------
   // A row is left through the cell the walk reaches after a run of 'Y' codes (3, leftwards,
@@ -573,6 +721,7 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
   NwScratch nz;
   nz.rowbuf = DD_ITEM(float, DD_BROW_Z); nz.trz = DD_ITEM(uint2, DD_TRZ); nz.zres = DD_ITEM(uint32_t, DD_ZRES);
   nz.ts = lay.ts;
+  nz.chunked = lay.nw_chunked;
   uint32_t* ss_x = DD_ITEM(uint32_t, DD_SS_X);
   uint32_t* ss_y = DD_ITEM(uint32_t, DD_SS_Y);
   float* es_x = DD_ITEM(float, DD_ES_X);
