@@ -218,7 +218,7 @@ int dafs_cuda_dd_plan_poll(dafs_dd_plan* plan, dafs_dd_result* res, int32_t* don
 void dafs_cuda_dd_plan_destroy(dafs_dd_plan* plan);
 
 typedef struct dafs_dd_info {
-  int grid, block, cols_per_lane;  /* persistent CTAs, threads, NW columns per lane */
+  int grid, block, cols_per_lane;  /* persistent CTAs, threads, 32-column words of the widest NW band */
   int smem_bytes;                  /* dynamic shared memory per CTA                 */
   int ctas_per_sm;
   unsigned items_in_smem;          /* bit per scratch array (dd_kernel.cuh)         */

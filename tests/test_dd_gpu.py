@@ -85,6 +85,50 @@ def test_nw_sparse_envelope(dafs, seed):
     assert bad == 0 and bits(so) == bits(sg) and np.array_equal(alo, alg)
 
 
+def banded_posterior(L1, L2, half, seed, gappy=False):
+    """A synthetic p_z whose envelope is about 2 * half + 1 columns wide around the (scaled)
+    diagonal; gappy: the ridge of strong matches jumps sideways every few rows, so the
+    walk back has many 'X' / 'Y' steps (insertions) instead of one long diagonal."""
+    r = np.random.default_rng(seed)
+    p = np.zeros((L1, L2), np.float32)
+    shift = 0
+    for i in range(L1):
+        if gappy and i % 7 == 3:
+            shift += int(r.integers(-min(3, half), min(3, half) + 1))
+        c = int(round(i * (L2 - 1) / max(L1 - 1, 1))) + shift
+        lo, hi = max(0, c - half), min(L2 - 1, c + half)
+        if lo > hi:
+            continue
+        p[i, lo:hi + 1] = (0.011 + 0.2 * r.random(hi - lo + 1)).astype(np.float32)
+        if 0 <= c < L2:
+            p[i, c] = np.float32(0.5 + 0.4 * r.random())
+    return p
+
+
+# band words 1 (register-resident rows), 2 / 3 / 4 (one scan per row), >= 5 (32 columns per scan)
+@pytest.mark.parametrize("half", [3, 12, 15, 16, 25, 40, 55, 70, 110])
+@pytest.mark.parametrize("gappy", [False, True])
+def test_nw_fill_variants_bit_exact(dafs, half, gappy):
+    for L1, L2 in ((200, 200), (131, 190), (190, 131)):
+        p = banded_posterior(L1, L2, half, 1000 + half, gappy)
+        q = rand_q((L1, L2), half, signed=True, density=0.2, scale=0.3)
+        for qq in (None, q):
+            so, alo, env, bad = ou.oracle_nw(p, qq, 0.01)
+            assert bad == 0
+            sg, alg = dafs.nw_decode(p, qq, 0.01)
+            assert bits(so) == bits(sg) and np.array_equal(alo, alg)
+            old = os.environ.get("DAFS_DD_NW_CHUNKED")
+            os.environ["DAFS_DD_NW_CHUNKED"] = "1"             # the 32-columns-per-scan fill
+            try:
+                sc, alc = dafs.nw_decode(p, qq, 0.01)
+            finally:
+                if old is None:
+                    del os.environ["DAFS_DD_NW_CHUNKED"]
+                else:
+                    os.environ["DAFS_DD_NW_CHUNKED"] = old
+            assert bits(sc) == bits(so) and np.array_equal(alc, alo)
+
+
 def check_dd(g, o, compare_xyz=True):
     assert bits(g["score"]) == bits(o["score"])
     assert g["iters"] == o["iters"] and g["violated"] == o["violated"] and g["ncbp"] == o["ncbp"]
