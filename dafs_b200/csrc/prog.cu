@@ -547,9 +547,9 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
           const float* cy = Bt.res[slow].cycles;
           const float it1 = (float)std::max(1, Bt.res[slow].iters + 1);
           fprintf(stderr, "[prog] t = %.1f .. %.1f ms: batch of %d problems (first node %d, level %d): DD %.2f ms (wall %.2f ms), grid %d x %d threads, smem %d B, in_smem %#x, band words %d, cbp %lld; "
-                          "slowest: on the device %.1f .. %.1f, L1 %d L2 %d N %d+%d iters %d cbp %lld, cycles/iter x %.0f+%.0f y %.0f+%.0f z %.0f+%.0f\n",
+                          "slowest: L1 %d L2 %d N %d+%d iters %d cbp %lld, cycles/iter decode %.0f update %.0f, x %.0f+%.0f y %.0f+%.0f z %.0f+%.0f\n",
                   Bt.t0 - t_begin, now_ms() - t_begin, W, Bt.node[0], level[Bt.node[0]], dms, now_ms() - Bt.t0, inf.grid, inf.block, inf.smem_bytes, inf.items_in_smem, inf.cols_per_lane, (long long)inf.total_cbp,
-                  cy[6], cy[7], Bt.prob[slow].L1, Bt.prob[slow].L2, Bt.prob[slow].N1, Bt.prob[slow].N2, Bt.res[slow].iters, (long long)Bt.res[slow].ncbp,
+                  Bt.prob[slow].L1, Bt.prob[slow].L2, Bt.prob[slow].N1, Bt.prob[slow].N2, Bt.res[slow].iters, (long long)Bt.res[slow].ncbp, cy[6] / it1, cy[7] / it1,
                   cy[0] / it1, cy[1] / it1, cy[2] / it1, cy[3] / it1, cy[4] / it1, cy[5] / it1);
         }
         pool.idle.push_back(Bt.stream);
