@@ -48,6 +48,27 @@ print("iterations total %d  mean %.1f  capped %d  converged %d  -> %.3f M iter/s
 cyc = np.sum([r["cycles"] for r in res], axis=0) / iters.sum()
 print("cycles/iter: x fill %.0f tb %.0f | y fill %.0f tb %.0f | z fill %.0f tb %.0f | decode phase %.0f | update phase %.0f" % tuple(cyc))
 print("ncbp mean %.1f max %d" % (np.mean([r["ncbp"] for r in res]), max(r["ncbp"] for r in res)))
+# how much of the batch time is the queue order?  list-schedule the measured per-problem times
+# (decode + update cycles) over the CTA slots in the plan's order (largest cells x min(t_max,
+# 1 + ncbp) first), in the ideal order (longest measured time first), and the work bound
+import heapq
+dur = np.array([r["cycles"][6] + r["cycles"][7] for r in res]) / 1.965e6          # ms at 1965 MHz
+ncbp = np.array([r["ncbp"] for r in res])
+def makespan(order):
+    slots = [0.0] * info["grid"]
+    heapq.heapify(slots)
+    for k in order:
+        heapq.heappush(slots, heapq.heappop(slots) + dur[k])
+    return max(slots)
+plan_order = sorted(range(len(res)), key=lambda k: -min(tmax, 1 + ncbp[k]))
+print("queue model (ms): plan order %.1f | longest-first %.1f | work / slots %.1f | longest problem %.1f | measured %.1f" % (
+    makespan(plan_order), makespan(np.argsort(-dur)), dur.sum() / info["grid"], dur.max(), ms))
+cap = iters >= tmax
+rank = {k: r for r, k in enumerate(plan_order)}
+print("capped problems: %d, queue positions min %d median %d max %d of %d (slots %d)" % (
+    cap.sum(), min(rank[k] for k in np.where(cap)[0]) if cap.any() else -1,
+    int(np.median([rank[k] for k in np.where(cap)[0]])) if cap.any() else -1,
+    max(rank[k] for k in np.where(cap)[0]) if cap.any() else -1, len(res), info["grid"]))
 if cpu_n:
     import oracle_util as ou
     t0 = time.perf_counter(); it = 0
