@@ -49,6 +49,30 @@ def test_family(n, length, seed):
     assert g["waves"] >= 1 and g["node_L"][-1] == g["L"]
 
 
+def test_schedules_agree():
+    """Dependency-driven scheduling (default: a node starts as soon as both children are solved,
+    single problems harvested with dafs_cuda_dd_plan_poll) and the level-synchronous order
+    (DAFS_PROG_WAVES=1) give the same alignment, structure, scores and per-node iterations."""
+    seqs = ou.stemloop_family(14, 80, 21, mutation=0.35)
+    lens, mp, bp, sim = inputs(seqs)
+    left, right, _ = db.guide_tree(sim)
+    a = check(lens, mp, bp, left, right, t_max=150)
+    old = os.environ.get("DAFS_PROG_WAVES")
+    os.environ["DAFS_PROG_WAVES"] = "1"
+    try:
+        b = check(lens, mp, bp, left, right, t_max=150)
+    finally:
+        if old is None:
+            del os.environ["DAFS_PROG_WAVES"]
+        else:
+            os.environ["DAFS_PROG_WAVES"] = old
+    for k in ("order", "bits", "ss", "node_iters", "node_violated", "node_L"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["node_score"].view(np.uint32), b["node_score"].view(np.uint32))
+    assert a["total_iters"] == b["total_iters"]
+    assert b["waves"] <= a["waves"]              # levels vs batches
+
+
 def test_chain_tree_unrelated():
     # a chain-shaped tree over unrelated sequences: mp_[a][b] with a > b (transposes), long runs
     seqs = random_rna(5, 48, config_id=77)

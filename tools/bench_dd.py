@@ -82,3 +82,5 @@ if cpu_n:
     print("oracle (1 core): %d iterations in %.2f s -> %.1f us/iter ; GPU speed-up per core %.0fx" % (
         it, dt, dt / it * 1e6, (iters.sum() / (ms * 1e-3)) / (it / dt)))
 plan.close()
+if os.environ.get("DAFS_BENCH_DD_DUMP"):
+    np.save(os.environ["DAFS_BENCH_DD_DUMP"], np.array([[r["ncbp"], min(r["iters"] + 1, tmax), r["violated"], dur[k] * 1e3] for k, r in enumerate(res)]))
