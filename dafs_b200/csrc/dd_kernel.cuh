@@ -675,32 +675,17 @@ struct DDShared {
 
 __device__ __forceinline__ void dd_update_nus(const DDNus& S, const uint32_t* ss, int* tal, float eta,
                                               unsigned& viol, int tid, int nthreads) {
-  // dafs.cpp:1121-1150 (x) and :1172-1201 (y), one thread per entry, four entries per pass: the
-  // loads of a pass (entry -> ss[i], flag) are issued together, so a thread waits for one load
-  // chain per four entries instead of one per entry (the root of a guide tree has ~10^4 entries)
-  for (int e0 = tid; e0 < S.n; e0 += 4 * nthreads) {
-    uint32_t ij[4], sv[4]; int t[4]; unsigned fl[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + u * nthreads;
-      const bool in = e < S.n;
-      ij[u] = in ? S.ent_ij[e] : 0u;
-      t[u] = in ? tal[e] : 0;
-      fl[u] = in ? (unsigned)S.ent_flag[e] : 0u;
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) sv[u] = ss[ij[u] & 0xffffu];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + u * nthreads;
-      if (e >= S.n) break;
-      if (t[u] != 0) tal[e] = 0;
-      if (sv[u] == (ij[u] >> 16)) {
-        if (t[u] != 1) { ++viol; S.ent_q[e] = __fsub_rn(S.ent_q[e], __fmul_rn(eta, (float)(t[u] - 1))); }
-      } else if ((fl[u] & 1u) && t[u] != 0) {
-        ++viol;
-        S.ent_q[e] = __fsub_rn(S.ent_q[e], __fmul_rn(eta, (float)t[u]));
-      }
+  // dafs.cpp:1121-1150 (x) and :1172-1201 (y), one thread per entry
+  for (int e = tid; e < S.n; e += nthreads) {
+    const uint32_t ij = S.ent_ij[e];
+    const int i = (int)(ij & 0xffffu), j = (int)(ij >> 16);
+    const int t = tal[e];
+    tal[e] = 0;
+    if (ss[i] == (uint32_t)j) {
+      if (t != 1) { ++viol; S.ent_q[e] = __fsub_rn(S.ent_q[e], __fmul_rn(eta, (float)(t - 1))); }
+    } else if ((S.ent_flag[e] & 1) && t != 0) {
+      ++viol;
+      S.ent_q[e] = __fsub_rn(S.ent_q[e], __fmul_rn(eta, (float)t));
     }
   }
 }
@@ -809,29 +794,13 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
       if (T > 1 && tid < 8) sh.prog[tid] = 0;                 // wave numbers restart with every decode
       const long long tp1 = clock64();
       // ---- tally (:1103-1117) ---------------------------------------------------
-      // Consecutive CBPs share their x entry and often a z cell (the enumeration runs over
-      // (i, j), then (k, l), :1016-1061): dealt round-robin, the 32 lanes of a warp would queue
-      // on the same shared-memory counters.  Each thread takes a contiguous slice instead, four
-      // quadruples (HBM) in flight.
-      {
-        const int per = (ncbp + NT - 1) / NT;
-        const int u_end = min(ncbp, (tid + 1) * per);
-        for (int u0 = tid * per; u0 < u_end; u0 += 4) {
-          int4 cbv[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) cbv[k] = (u0 + k < u_end) ? cbp[u0 + k] : make_int4(0, 0, 0, 0);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int u = u0 + k;
-            if (u >= u_end) break;
-            const int4 cb = cbv[k];
-            const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_cz[cb.z]), q_cz[cb.w]);
-            sw[u] = s_w;
-            if (s_w > 0.0f) {
-              atomicAdd(&tal_x[cb.x], 1); atomicAdd(&tal_y[cb.y], 1);
-              atomicAdd(&tal_z[cb.z], 1); atomicAdd(&tal_z[cb.w], 1);
-            }
-          }
+      for (int u = tid; u < ncbp; u += NT) {
+        const int4 cb = cbp[u];
+        const float s_w = __fsub_rn(__fsub_rn(__fadd_rn(q_x[cb.x], q_y[cb.y]), q_cz[cb.z]), q_cz[cb.w]);
+        sw[u] = s_w;
+        if (s_w > 0.0f) {
+          atomicAdd(&tal_x[cb.x], 1); atomicAdd(&tal_y[cb.y], 1);
+          atomicAdd(&tal_z[cb.z], 1); atomicAdd(&tal_z[cb.w], 1);
         }
       }
       __syncthreads();
@@ -840,17 +809,7 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
         float s = __fadd_rn(0.0f, sh.part[0]);
         s = __fadd_rn(s, sh.part[1]);
         s = __fadd_rn(s, sh.part[2]);
-        // s + 0.0f == s bit for bit here (s is never -0.0f: it starts as 0.0f + x), so the skipped
-        // terms are added as zeros and the chain is one add per term, loads eight ahead
-        int u = 0;
-        for (; u + 8 <= ncbp; u += 8) {
-          float v[8];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) v[k] = sw[u + k];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) s = __fadd_rn(s, dd_max0(v[k]));
-        }
-        for (; u < ncbp; ++u) s = __fadd_rn(s, dd_max0(sw[u]));
+        for (int u = 0; u < ncbp; ++u) { const float v = sw[u]; if (v > 0.0f) s = __fadd_rn(s, v); }
         sh.s = s;
       }
       // ---- multiplier updates (:1121-1254) -----------------------------------------
