@@ -33,6 +33,33 @@ struct DevBufs {
   }
 };
 
+// One grow-only device block per dafs_cuda_progressive call, carved anew for every batch: the
+// batch's tables and dense averages are dead once its averages are on the host, and a
+// cudaMalloc in the middle of the run waits for the DD batches in flight (19 ms measured).
+struct DevArena {
+  char* base = nullptr;
+  size_t cap = 0, used = 0;
+  ~DevArena() { if (base) dafs::dev_free(base); }
+  static size_t rounded(size_t bytes) { return (std::max<size_t>(bytes, 256) + 255) & ~size_t(255); }
+  cudaError_t reserve(size_t bytes) {
+    used = 0;
+    if (bytes <= cap) return cudaSuccess;
+    if (base) { dafs::dev_free(base); base = nullptr; cap = 0; }
+    const size_t want = bytes + bytes / 2;                   // the first batch is usually the largest
+    void* q = nullptr;
+    const cudaError_t e = dafs::dev_malloc(&q, want);
+    if (e == cudaSuccess) { base = static_cast<char*>(q); cap = want; }
+    return e;
+  }
+  template <class T> cudaError_t get(T** out, size_t count) {
+    const size_t b = rounded(count * sizeof(T));
+    if (used + b > cap) { *out = nullptr; return cudaErrorMemoryAllocation; }
+    *out = reinterpret_cast<T*>(base + used);
+    used += b;
+    return cudaSuccess;
+  }
+};
+
 struct StreamGuard {
   cudaStream_t s = nullptr;
   cudaEvent_t a = nullptr, b = nullptr;
@@ -367,6 +394,7 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   };
   PinGuard dense_pin;
   size_t dense_cap = 0;
+  DevArena arena;
   while (built < n - 1) {
     if (!ready.empty()) {
       double tl = now_ms();
@@ -419,7 +447,12 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
         DAFS_CUDA_TRY(cudaFuncSetAttribute(prog_avg_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       }
       tl = lap(0, tl);
-      DevBufs WB;                                   // the batch's device buffers (released after the copy below)
+      DevArena& WB = arena;                         // the batch's device buffers (dead after the copy below)
+      DAFS_CUDA_TRY(WB.reserve(DevArena::rounded(sizeof(ProgSide) * sides.size()) + DevArena::rounded(sizeof(ProgNode) * nodes.size()) +
+                               DevArena::rounded(sizeof(int) * mem_seq.size()) + DevArena::rounded(sizeof(int64_t) * mem_col.size()) +
+                               DevArena::rounded(sizeof(int64_t) * mem_inv.size()) + DevArena::rounded(sizeof(int) * maps.size()) +
+                               DevArena::rounded(sizeof(int2) * bp_tasks.size()) + DevArena::rounded(sizeof(int2) * mp_tasks.size()) +
+                               DevArena::rounded(sizeof(float) * (size_t)dense)));
       ProgSide* d_sides = nullptr; ProgNode* d_nodes = nullptr; int* d_mem_seq = nullptr; int64_t* d_mem_col = nullptr;
       int64_t* d_mem_inv = nullptr; int* d_maps = nullptr; int2* d_bp_tasks = nullptr; int2* d_mp_tasks = nullptr; float* d_dense = nullptr;
       DAFS_CUDA_TRY(WB.get(&d_sides, sides.size()));
