@@ -29,5 +29,5 @@ from .capi import (  # noqa: F401
 from .capi_mc import McCaskillPlan, mccaskill_all  # noqa: F401
 from .capi_pct import pct, pct_last_ms  # noqa: F401
 from .capi_prog import guide_tree, progressive  # noqa: F401
-from .capi_dd import DDPlan, dd_solve_batch, nussinov_decode, nw_decode  # noqa: F401
+from .capi_dd import DDPlan, dd_solve_batch, nussinov_decode, nw_decode, nw_decode_static  # noqa: F401
 from .synth import fasta_read, homolog_family, random_rna, splitmix64, synthetic_bpp  # noqa: F401

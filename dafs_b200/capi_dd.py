@@ -49,6 +49,7 @@ def _protos():
         L.dafs_cuda_dd_solve_batch.argtypes = [C.c_int, C.POINTER(_DDProblem), C.POINTER(_DDResult)]
         L.dafs_cuda_nussinov_decode.argtypes = [C.c_int, C.c_float, C.c_float, _FP, _FP, _UP, _FP]
         L.dafs_cuda_nw_decode.argtypes = [C.c_int, C.c_int, C.c_float, _FP, _FP, _UP, _FP]
+        L.dafs_cuda_nw_decode_static.argtypes = [C.c_int, C.c_int, C.c_float, _FP, _FP, _UP, _FP]
         _proto_done = True
     return L
 
@@ -197,4 +198,16 @@ def nw_decode(p, q=None, th=0.01):
     al = np.zeros(p.shape[0], np.uint32)
     s = C.c_float()
     _check(L.dafs_cuda_nw_decode(p.shape[0], p.shape[1], th, _fp(p), _fp(q), al.ctypes.data_as(_UP), C.byref(s)))
+    return np.float32(s.value), al
+
+
+def nw_decode_static(p, q=None, th=0.01):
+    """dafs_cuda_nw_decode_static: the same decode out of the library's static device scratch
+    (no cudaMalloc on the path)."""
+    L = _protos()
+    p = _f32(p); q = None if q is None else _f32(q)
+    al = np.zeros(p.shape[0], np.uint32)
+    s = C.c_float()
+    _check(L.dafs_cuda_nw_decode_static(p.shape[0], p.shape[1], th, _fp(p), _fp(q), al.ctypes.data_as(_UP),
+                                        C.byref(s)))
     return np.float32(s.value), al

@@ -5,6 +5,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <thread>
 #include <cstdlib>
 #include <cstdio>
@@ -809,6 +810,132 @@ extern "C" int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, con
   DAFS_CUDA_TRY(cudaMemcpy(&sv, d_score, sizeof(float), cudaMemcpyDeviceToHost));
   DAFS_CUDA_TRY(cudaMemcpy(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost));
   if (score) *score = sv;
+  if (bad) return fail(DAFS_CUDA_ECUDA, "NW traceback met an unfilled cell (the reference does not terminate on this input)");
+  return DAFS_CUDA_OK;
+}
+
+// ---- allocation-free single NW decode --------------------------------------------
+// dafs_cuda_nw_decode_static: same arguments and results as dafs_cuda_nw_decode, for
+// callers that may not call cudaMalloc (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  Every device byte it needs -- the band image of
+// p / q, the envelope, the row buffers, the traceback planes, the result -- lives in
+// ONE file-scope device array of DAFS_CUDA_NW_STATIC_BYTES; the host image of the
+// inputs is a file-scope host array of the same size.  No cudaMalloc / cudaFree /
+// cudaHostAlloc, no host heap, no allocating library routine on this path.
+//   * The array is shared by every call (and held by every device that loads the
+//     library until exit); it keeps the last call's contents.  What must start at zero
+//     (score, the bad-cell flag) is part of the image the call uploads; everything
+//     else is written before it is read.
+//   * Calls are serialised by a mutex on the host and run on the legacy default stream;
+//     two calls that overlap on the GPU (other processes share nothing) would race.
+namespace dafs {
+
+static __device__ __align__(256) unsigned char g_nw_static[DAFS_CUDA_NW_STATIC_BYTES];
+static unsigned char g_nw_static_host[DAFS_CUDA_NW_STATIC_BYTES];   // host image of the inputs
+static std::mutex g_nw_static_mu;
+static unsigned char* g_nw_static_addr[64] = {};                    // device address, per device
+
+// `g_nw_static` in host code is a host-side stand-in, not a device address: ask the
+// runtime once per device (with that device current) for the real one.
+static int nw_static_base(unsigned char** out) {
+  int dev = 0;
+  DAFS_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(DAFS_CUDA_ENODEV, "device index %d outside [0, 64)", dev);
+  if (!g_nw_static_addr[dev]) {
+    void* p = nullptr;
+    DAFS_CUDA_TRY(cudaGetSymbolAddress(&p, g_nw_static));
+    if (!p) return fail(DAFS_CUDA_ECUDA, "cudaGetSymbolAddress returned NULL");
+    g_nw_static_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_nw_static_addr[dev];
+  return DAFS_CUDA_OK;
+}
+
+// SparseNeedlemanWunsch::initialize, src/needleman_wunsch.cpp:198-253, into env[L1+1]
+static void envelope_into(int L1, int L2, float th, const float* p, uint2* env) {
+  for (int i = 0; i <= L1; ++i) env[i] = make_uint2(0, 0);
+  for (int i = 1; i <= L1; ++i) {
+    const float* row = p + (size_t)(i - 1) * L2;
+    int kf = 0, kl = 0;
+    for (int k = 1; k <= L2 && !kf; ++k) if (row[k - 1] - th >= 0.0) kf = k;
+    if (!kf) { env[i] = env[i - 1]; continue; }
+    for (int k = L2; k >= 1 && !kl; --k) if (row[k - 1] - th >= 0.0) kl = k;
+    env[i - 1].x = std::min(env[i - 1].x, (unsigned)(kf - 1)); env[i].x = (unsigned)kf;
+    env[i - 1].y = std::max(env[i - 1].y, (unsigned)(kl - 1)); env[i].y = (unsigned)kl;
+  }
+  env[L1].y = (unsigned)L2;
+  unsigned lo = (unsigned)L2, hi = 0;
+  for (int i = L1; i >= 1; --i) env[i].x = lo = std::min(lo, env[i].x);
+  for (int i = 0; i <= L1; ++i) env[i].y = hi = std::max(hi, env[i].y);
+  for (int i = 1; i <= L1; ++i) if (env[i - 1].y < env[i].x) env[i].x = env[i - 1].y;
+}
+
+}  // namespace dafs
+
+extern "C" int dafs_cuda_nw_decode_static(int L1, int L2, float th, const float* p, const float* q,
+                                          uint32_t* al, float* score) {
+  using namespace dafs;
+  if (L1 < 1 || L2 < 1 || !p || !al) return fail(DAFS_CUDA_EINVAL, "bad argument");
+  if (L1 > DAFS_CUDA_NW_STATIC_MAXL || L2 > DAFS_CUDA_NW_STATIC_MAXL)
+    return fail(DAFS_CUDA_EINVAL, "dafs_cuda_nw_decode_static: L1=%d L2=%d beyond the static limit of %d (use dafs_cuda_nw_decode)",
+                L1, L2, DAFS_CUDA_NW_STATIC_MAXL);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(DAFS_CUDA_ENODEV, "no CUDA device visible (libdafs_cuda has no CPU fallback)"); }
+  std::lock_guard<std::mutex> lock(g_nw_static_mu);
+  unsigned char* base = nullptr;
+  if (const int rc = nw_static_base(&base)) return rc;
+
+  // image = {score, bad, pad} | al[L1] | env[L1+1] | boff[L1+2] | p band | q band ; then scratch
+  unsigned char* h = g_nw_static_host;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { const size_t o = off; off = up16(off + std::max<size_t>(bytes, 16)); return o; };
+  const size_t o_hdr = take(16), o_al = take(sizeof(uint32_t) * L1), o_env = take(sizeof(uint2) * (L1 + 1)),
+               o_boff = take(sizeof(int) * (L1 + 2));
+  std::memset(h + o_hdr, 0, 16);
+  uint2* env = reinterpret_cast<uint2*>(h + o_env);
+  int* boff = reinterpret_cast<int*>(h + o_boff);
+  envelope_into(L1, L2, th, p, env);
+  size_t n = 0; int bw = 1;
+  boff[0] = 0;
+  for (int r = 1; r <= L1; ++r) {
+    boff[r] = (int)n;
+    const int ef = std::max(1, (int)env[r].x), el = (int)env[r].y;
+    if (el >= ef) { n += (size_t)(el - ef + 1); bw = std::max(bw, el - ef + 1); }
+  }
+  boff[L1 + 1] = (int)n;
+  const int ts = (bw + 31) / 32;
+  const size_t o_p = take(sizeof(float) * n), o_q = take(sizeof(float) * n);
+  const size_t image = off;
+  const size_t o_row = take(sizeof(float) * 2 * (size_t)(L2 + 2)), o_trz = take(sizeof(uint2) * (size_t)(L1 + 1) * ts),
+               o_zres = take(sizeof(uint32_t) * L1);
+  if (off > (size_t)DAFS_CUDA_NW_STATIC_BYTES)
+    return fail(DAFS_CUDA_EINVAL, "dafs_cuda_nw_decode_static: %d x %d with %zu envelope cells needs %zu bytes, the static scratch holds %d (use dafs_cuda_nw_decode)",
+                L1, L2, n, off, DAFS_CUDA_NW_STATIC_BYTES);
+  float* pb = reinterpret_cast<float*>(h + o_p);
+  float* qb = reinterpret_cast<float*>(h + o_q);
+  for (int r = 1; r <= L1; ++r) {
+    const int ef = std::max(1, (int)env[r].x), el = (int)env[r].y;
+    size_t w = (size_t)boff[r];
+    for (int k = ef; k <= el; ++k, ++w) {
+      pb[w] = p[(size_t)(r - 1) * L2 + (k - 1)];
+      qb[w] = q ? q[(size_t)(r - 1) * L2 + (k - 1)] : 0.0f;
+    }
+  }
+  DAFS_CUDA_TRY(cudaMemcpy(base, h, image, cudaMemcpyHostToDevice));      // also zeroes score / bad
+  DDAln A{}; NwScratch sc{};
+  A.L1 = L1; A.L2 = L2; A.th = th;
+  A.env = reinterpret_cast<const uint2*>(base + o_env); A.boff = reinterpret_cast<const int*>(base + o_boff);
+  A.pb = reinterpret_cast<const float*>(base + o_p); A.qb = reinterpret_cast<const float*>(base + o_q);
+  sc.rowbuf = reinterpret_cast<float*>(base + o_row); sc.trz = reinterpret_cast<uint2*>(base + o_trz);
+  sc.zres = reinterpret_cast<uint32_t*>(base + o_zres); sc.ts = ts;
+  { const char* e = getenv("DAFS_DD_NW_CHUNKED"); sc.chunked = (e && atoi(e) > 0) ? 1 : 0; }
+  nw_single_kernel<<<1, 32>>>(A, sc, reinterpret_cast<uint32_t*>(base + o_al), reinterpret_cast<float*>(base + o_hdr),
+                              reinterpret_cast<int*>(base + o_hdr + 4));
+  DAFS_CUDA_TRY(cudaGetLastError());
+  DAFS_CUDA_TRY(cudaMemcpy(h, base, o_env, cudaMemcpyDeviceToHost));      // {score, bad} | al
+  std::memcpy(al, h + o_al, sizeof(uint32_t) * L1);
+  if (score) std::memcpy(score, h + o_hdr, sizeof(float));
+  int bad = 0; std::memcpy(&bad, h + o_hdr + 4, sizeof(int));
   if (bad) return fail(DAFS_CUDA_ECUDA, "NW traceback met an unfilled cell (the reference does not terminate on this input)");
   return DAFS_CUDA_OK;
 }

@@ -239,6 +239,26 @@ int dafs_cuda_nussinov_decode(int L, float th, float w, const float* p, const fl
 int dafs_cuda_nw_decode(int L1, int L2, float th, const float* p, const float* q, uint32_t* al,
                         float* score);
 
+/* Allocation-free variant of dafs_cuda_nw_decode.  It has no counterpart in the
+ * reference; it was added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results (bit for bit).  All
+ * device memory it uses -- band image of p / q, envelope, DP rows, traceback
+ * planes, result -- is one file-scope device array of DAFS_CUDA_NW_STATIC_BYTES
+ * that every GPU loading the library holds until exit; the host image of the
+ * inputs is a static host array of the same size.  It calls no cudaMalloc,
+ * cudaFree, cudaHostAlloc or other allocating routine and uses no host heap.
+ * Limits: L1, L2 <= DAFS_CUDA_NW_STATIC_MAXL and a scratch need (about 8 bytes per
+ * envelope cell + 16 * (L1 + L2) + (L1 + 1) * ceil(widest band / 32) * 8) within the
+ * array; anything larger is rejected with DAFS_CUDA_EINVAL and a message naming the
+ * limit.  The array is shared by all calls and keeps the last call's contents
+ * (what must start at zero is re-uploaded by each call); calls are serialised by a
+ * host mutex and the legacy default stream -- calls that overlap on the GPU race. */
+#define DAFS_CUDA_NW_STATIC_BYTES (8 << 20)
+#define DAFS_CUDA_NW_STATIC_MAXL 2048
+int dafs_cuda_nw_decode_static(int L1, int L2, float th, const float* p, const float* q,
+                               uint32_t* al, float* score);
+
 /* ---- (4) probabilistic consistency transformation --------------------------
  * The stage DAFS::run() executes between the posteriors and the guide tree
  * (src/dafs.cpp:1796-1827): transpose_mp for every pair (:155-167, :1797-1799),
