@@ -409,7 +409,9 @@ static const void* dd_kernel_fn(bool smem, int team) {
 // alone: launches of different sizes are in flight at the same time (dafs_cuda_progressive),
 // and changing the attribute of a function that is running makes the next launch wait for it.
 static cudaError_t dd_allow_smem(const void* fn, bool smem, int team, int device, size_t optin) {
+  static std::mutex mu;
   static bool done[64][2][4] = {};
+  std::lock_guard<std::mutex> g(mu);
   bool& d = done[device & 63][smem ? 1 : 0][team & 3];
   if (d) return cudaSuccess;
   const cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)optin - 1024);   // the kernel has some static shared memory too

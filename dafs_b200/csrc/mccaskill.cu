@@ -80,11 +80,9 @@ static void build_mc_tables(McTables& T) {
   }
 }
 
-static const McTables& mc_host_tables() {
-  static McTables t;
-  static bool built = false;
-  if (!built) { build_mc_tables(t); built = true; }
-  return t;
+static const McTables& mc_host_tables() {   // built once, thread-safe (function-local static)
+  static const McTables* t = [] { McTables* x = new McTables(); build_mc_tables(*x); return x; }();
+  return *t;
 }
 
 // ViennaRNA's nucleotide encoding: A C G U -> 1..4, T counts as U, anything else 0

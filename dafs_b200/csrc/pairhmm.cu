@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include <numeric>
+#include <mutex>
 #include <thread>
 #include <cstdlib>
 #include <vector>
@@ -49,10 +50,10 @@ static void build_tables(PairHmmTables& t) {
   }
 }
 
+// built once, by whichever thread comes first (function-local static: the ngpu > 1 entry
+// points create plans from one host thread per device)
 static const PairHmmTables& host_tables() {
-  static PairHmmTables t;
-  static bool built = false;
-  if (!built) { build_tables(t); built = true; }
+  static const PairHmmTables t = [] { PairHmmTables x; build_tables(x); return x; }();
   return t;
 }
 
@@ -314,10 +315,14 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   }
   p->h_chunk_end = static_cast<int64_t*>(pinned_alloc(64));
   if (!p->h_chunk_end) return bail(fail(DAFS_CUDA_ENOMEM, "pinned allocation failed"));
-  static bool tables_up[64] = {false};
-  if (!tables_up[p->device & 63]) {
-    PLAN_TRY(cudaMemcpyToSymbol(c_tab, &host_tables(), sizeof(PairHmmTables)));
-    tables_up[p->device & 63] = true;
+  {
+    static std::mutex mu;
+    static bool tables_up[64] = {false};
+    std::lock_guard<std::mutex> g(mu);
+    if (!tables_up[p->device & 63]) {
+      PLAN_TRY(cudaMemcpyToSymbol(c_tab, &host_tables(), sizeof(PairHmmTables)));
+      tables_up[p->device & 63] = true;
+    }
   }
 
   // encode sequences

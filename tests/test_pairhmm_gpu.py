@@ -169,3 +169,22 @@ def test_chunked_fetch_equals_single_launch(th):
             assert np.array_equal(rp, orp) and np.array_equal(col, ocol)
             assert np.array_equal(val.view(np.uint32), oval.view(np.uint32))
     plan.close()
+
+
+def test_config_c5_length_pairs_bit_exact():
+    """Config C5 (L = 1500, 2.25 M cells per pair, 5 stripes): every pair of a 1500 / 1500 /
+    1499 triple in both orientations, plus a 40 x 1500 strip and its transpose."""
+    pool = random_rna(4, 1500, config_id=5)
+    seqs = [pool[0], pool[1], pool[2][:1499], pool[3][:40]]
+    pi = np.array([0, 0, 1, 1, 2, 2, 3, 0], np.int32)
+    pj = np.array([1, 2, 2, 0, 0, 1, 0, 3], np.int32)
+    with dafs_b200.pairhmm_pairs(seqs, pi, pj, 0.01) as b:
+        check_batch_against_oracle(seqs, pi, pj, 0.01, b)
+        assert b.nnz > 6 * 1499
+
+
+def test_config_c5_homologs_bit_exact():
+    fam = homolog_family(3, 1500, config_id=5)
+    pi, pj = dafs_b200.all_pairs(3)
+    with dafs_b200.pairhmm_pairs(fam, pi, pj, 0.01) as b:
+        check_batch_against_oracle(fam, pi, pj, 0.01, b)

@@ -4,7 +4,7 @@ flat little-endian int32 blob, dafs_b200/data/blstar37.i32, in the order the
 reference's copy_* functions consume them (boltzmann_param.c:5908-6026).  The
 blob is parameter data (the published parameters_BLstar_Vienna.txt set), not
 source; libdafs_cuda embeds it and oracle/mccaskill_oracle.c reads it.
-    python tools/extract_blstar.py [/root/reference/src/boltzmann_param.c]
+    python tools/extract_blstar.py [/root/reference/src/boltzmann_param.c [OUT]]
 Layout (int32 each): magic 0x424C5331, then
   stack[7][7]  mismatchH[7][5][5]  mismatchI[7][5][5]  dangle5[8][5]  dangle3[8][5]
   int11[7][7][5][5]  int21[7][7][5][5][5]  int22[7][7][4][4][4][4]
@@ -16,7 +16,7 @@ import struct
 import sys
 
 src = sys.argv[1] if len(sys.argv) > 1 else "/root/reference/src/boltzmann_param.c"
-out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "dafs_b200", "data", "blstar37.i32")
+out = sys.argv[2] if len(sys.argv) > 2 else os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "dafs_b200", "data", "blstar37.i32")
 txt = open(src).read()
 txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
 CONST = {"INF": 10000000, "DEF": -50, "NST": 0}
