@@ -4,7 +4,7 @@ ARCH := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := -O3 -std=c++17 -lineinfo $(ARCH) -Xcompiler -fPIC,-O2,-pthread,-ffp-contract=off -Xptxas -v --fmad=false
 CSRC := dafs_b200/csrc
 LIB := dafs_b200/libdafs_cuda.so
-OBJS := $(CSRC)/common.o $(CSRC)/pairhmm.o $(CSRC)/dd.o $(CSRC)/mccaskill.o $(CSRC)/pct.o $(CSRC)/prog.o
+OBJS := $(CSRC)/common.o $(CSRC)/pairhmm.o $(CSRC)/dd.o $(CSRC)/mccaskill.o $(CSRC)/pct.o $(CSRC)/prog.o $(CSRC)/comm.o
 
 all: $(LIB) oracle
 

@@ -8,8 +8,9 @@ BASELINE.json's config C4 (synthetic random RNA, N=256, L=300, 32 640 pairs).
 
 A "step" is one pass of the hot path over the whole pair list.  `value` is
 pairs/s with inputs resident in HBM (device time, CUDA events); `e2e` is the same
-metric through the C ABI with host buffers (H2D of the inputs, all kernels, the
-cross-rank NCCL all-gather of the CSR payload for N>1, D2H of the result)."""
+metric through the C ABI with host buffers (H2D of the inputs, all kernels, D2H of
+the result; for N>1 every rank delivers its fragment into host memory rank 0 maps).
+The device-resident NCCL gather of the fragments to rank 0 is timed under "handover"."""
 import argparse
 import json
 import os
@@ -44,32 +45,23 @@ def shard(npairs, rank, world):
     return np.arange(rank, npairs, world, dtype=np.int64)
 
 
-def exchange_sizes(dist, world, dev, nnz, n_units, nrows):
-    """(nnz, units, row_ptr entries) of every rank's fragment, as a [world, 3] CPU tensor."""
-    import torch
-    sizes = torch.tensor([nnz, n_units, nrows], dtype=torch.int64, device=dev)
-    all_sizes = torch.empty(world * 3, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(all_sizes, sizes)
-    return all_sizes.view(world, 3).cpu()
-
-
 class SharedHostBuffer:
     """Host memory that every rank of the node maps (POSIX shared memory) and page-locks for
-    its own GPU: each rank copies its CSR fragment to the host over its own PCIe link, into
-    its own region, and rank 0 (which runs the host side of the pipeline) reads all of them in
-    place.  Region r holds, back to back: nz_off[units+1] (int64), row_ptr (int32), col (int32),
-    val (float32) of rank r's pairs, in that rank's pair order (bench.shard)."""
+    its own GPU: each rank's dafs_cuda_pairhmm_pairs_into call delivers its CSR fragment over
+    its own PCIe link straight into its own region, and rank 0 (which runs the host side of the
+    pipeline) reads all of them in place.  Region r holds, back to back: nz_off[units+1] (int64),
+    row_ptr (int32), col (uint32), val (float32) of rank r's pairs, in that rank's pair order
+    (bench.shard).  caps = (nnz, units, rows) capacity of one region."""
 
-    def __init__(self, dist, rank, world, all_sizes, pin=True):
-        import torch
+    def __init__(self, dist, rank, world, caps, pin=True):
         from multiprocessing import resource_tracker, shared_memory
-        mx_nnz, mx_units, mx_rows = (int(all_sizes[:, k].max()) for k in range(3))
+        mx_nnz, mx_units, mx_rows = (int(x) for x in caps)
         self.cap = (mx_nnz, mx_units, mx_rows)
         up = lambda x: (x + 255) & ~255
         self.off = [0, up(8 * (mx_units + 1))]
         self.off.append(self.off[1] + up(4 * mx_rows))
         self.off.append(self.off[2] + up(4 * mx_nnz))
-        self.stride = self.off[3] + up(4 * mx_nnz)
+        self.stride = (self.off[3] + up(4 * mx_nnz) + 4095) & ~4095
         nbytes = self.stride * world
         name = [None]
         if rank == 0:
@@ -83,37 +75,27 @@ class SharedHostBuffer:
             except Exception:
                 pass
         self.rank, self.world = rank, world
-        self.bytes = torch.frombuffer(self.shm.buf, dtype=torch.uint8, count=nbytes)
+        self.bytes = np.frombuffer(self.shm.buf, dtype=np.uint8, count=nbytes)
         self.pinned = False
-        if pin and torch.cuda.is_available():      # page-lock this rank's own region: the target of its copies
-            self.pin_ptr = self.bytes.data_ptr() + rank * self.stride
-            self.pinned = int(torch.cuda.cudart().cudaHostRegister(self.pin_ptr, self.stride, 0)) == 0
+        if pin:                                    # page-lock this rank's own region: the target of its copies
+            import torch
+            if torch.cuda.is_available():
+                self.pin_ptr = self.bytes.ctypes.data + rank * self.stride
+                self.pinned = int(torch.cuda.cudart().cudaHostRegister(self.pin_ptr, self.stride, 0)) == 0
 
-    def fits(self, all_sizes):
-        return all(int(all_sizes[:, k].max()) <= self.cap[k] for k in range(3))
-
-    def region(self, r, sizes):
-        """(nz_off, row_ptr, col, val) views of rank r's region for the given (nnz, units, rows)."""
-        import torch
-        nn, nu, nr = (int(x) for x in sizes)
+    def region(self, r, sizes=None):
+        """(nz_off, row_ptr, col, val) views of rank r's region: whole capacity, or cut to
+        sizes = (nnz, units, rows)."""
+        nn, nu, nr = self.cap if sizes is None else (int(x) for x in sizes)
         base = self.bytes[r * self.stride:(r + 1) * self.stride]
-        return (base[self.off[0]:self.off[0] + 8 * (nu + 1)].view(torch.int64),
-                base[self.off[1]:self.off[1] + 4 * nr].view(torch.int32),
-                base[self.off[2]:self.off[2] + 4 * nn].view(torch.int32),
-                base[self.off[3]:self.off[3] + 4 * nn].view(torch.float32))
-
-    def put(self, sizes, nz_off, row_ptr, col, val):
-        """This rank's fragment -> its region (device-to-host copies on the current stream)."""
-        dst = self.region(self.rank, sizes)
-        n = 0
-        for d, x in zip(dst, (nz_off, row_ptr, col, val)):
-            d.copy_(x[:d.numel()], non_blocking=True)
-            n += d.numel() * d.element_size()
-        return n
+        return (base[self.off[0]:self.off[0] + 8 * (nu + 1)].view(np.int64),
+                base[self.off[1]:self.off[1] + 4 * nr].view(np.int32),
+                base[self.off[2]:self.off[2] + 4 * nn].view(np.uint32),
+                base[self.off[3]:self.off[3] + 4 * nn].view(np.float32))
 
     def close(self):
-        import torch
         if self.pinned:
+            import torch
             torch.cuda.cudart().cudaHostUnregister(self.pin_ptr)
         del self.bytes
         try:
@@ -122,39 +104,6 @@ class SharedHostBuffer:
                 self.shm.unlink()
         except Exception:
             pass
-
-
-def gather_csr(dist, world, dev, col, val, nz_off, n_units, row_ptr=None, all_sizes=None):
-    """All-gather-v of per-rank CSR fragments: sizes first, then the max-padded
-    payload.  Returns, on every rank, a list over ranks of (col, val, nz_off,
-    n_units) views.  This is the only exchange step of the path."""
-    import torch
-    if all_sizes is None:
-        all_sizes = exchange_sizes(dist, world, dev, col.numel(), n_units, 0 if row_ptr is None else row_ptr.numel())
-    mx_nnz, mx_units, mx_rows = (int(all_sizes[:, k].max()) for k in range(3))
-
-    def pad(x, n):
-        if x.numel() == n:
-            return x.contiguous()
-        y = torch.zeros(n, dtype=x.dtype, device=dev)
-        y[:x.numel()] = x
-        return y
-    outs = []
-    todo = [(col, mx_nnz), (val, mx_nnz), (nz_off, mx_units + 1)]
-    if row_ptr is not None:
-        todo.append((row_ptr, mx_rows))
-    for x, n in todo:
-        g = torch.empty(world * n, dtype=x.dtype, device=dev)
-        dist.all_gather_into_tensor(g, pad(x, n))
-        outs.append(g.view(world, n))
-    res = []
-    for r in range(world):
-        nn, nu, nr = (int(all_sizes[r, k]) for k in range(3))
-        item = (outs[0][r, :nn], outs[1][r, :nn], outs[2][r, :nu + 1], nu)
-        if row_ptr is not None:
-            item = item + (outs[3][r, :nr],)
-        res.append(item)
-    return res
 
 
 class ClockSampler:
@@ -273,7 +222,7 @@ def config_dict(ngpu):
     return {"workload": "C4: synthetic random RNA N=%d L=%d, all %d i<j pairs, ProbCons pair-HMM posteriors th=%g" % (
                 NSEQ, LEN, NSEQ * (NSEQ - 1) // 2, TH),
             "nseq": NSEQ, "seq_len": LEN, "pairs": NSEQ * (NSEQ - 1) // 2, "threshold": TH,
-            "parallelism": "pairs sharded round-robin over %d GPU(s), no data-path collective; CSR all-gather only in e2e" % ngpu,
+            "parallelism": "pairs sharded round-robin over %d GPU(s), no data-path collective; hand-over = NCCL gather-v to rank 0 (device) / per-rank D2H into shared host memory (e2e)" % ngpu,
             "l2": "per-step working set (per-warp F_M planes, ~0.9 GB) exceeds the 126 MB L2; no flush needed"}
 
 
@@ -323,21 +272,39 @@ def run_stages(rank, world, max_over_ranks, steps, with_cpu):
     plan.close()
     iters = float(sum(min(r["iters"] + 1, 600) for r in res))
     t = max_over_ranks(sum(ms) / len(ms)) * 1e-3
-    iters_all = max_over_ranks(iters) if world == 1 else None
+    # The bound of this stage is latency, not throughput: a problem is one
+    # sequential chain of <= 600 iterations, so a batch can end no earlier than its longest
+    # problem, nor earlier than all problems' time spread over the resident CTA slots.  Both from
+    # the kernel's own per-problem cycle counters (decode + update phases) at the measured SM clock.
+    sm_hz = 1.965e9
+    dur_ms = np.array([r["cycles"][6] + r["cycles"][7] for r in res]) / sm_hz * 1e3
+    longest_ms, spread_ms = float(dur_ms.max()), float(dur_ms.sum() / info["grid"])
+    rank_ms = sum(ms) / len(ms)
     out["dd_C3"] = {"workload": "C3: N=64 L=150, %d two-leaf problems, -m 600, reference stopping rule" % nprob,
                     "problems_per_s": nprob / t, "ms_per_step": t * 1e3,
-                    "iterations_per_s_rank0": iters / (sum(ms) / len(ms) * 1e-3), "iterations_rank0": iters,
+                    "iterations_per_s_rank0": iters / (rank_ms * 1e-3), "iterations_rank0": iters,
                     "plan_create_s_rank0": t_create, "grid": info["grid"], "smem_bytes": info["smem_bytes"],
-                    "gpu_launches_per_step": 1}
+                    "gpu_launches_per_step": 1,
+                    "latency_bound_rank0": {"longest_problem_ms": longest_ms, "work_over_cta_slots_ms": spread_ms,
+                                            "iterations_of_longest": int(res[int(dur_ms.argmax())]["iters"]) + 1,
+                                            "us_per_iteration_of_longest": longest_ms * 1e3 / (int(res[int(dur_ms.argmax())]["iters"]) + 1)},
+                    "frac_of_latency_bound": max(longest_ms, spread_ms) / rank_ms}
     if with_cpu and rank == 0:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_util as ou
         kind = "reference" if ou.have_ref() else "port"
         f = ou.ref_dd if ou.have_ref() else ou.oracle_dd
-        sample = probs[:: max(1, len(probs) // (4 * cores))][: 4 * cores]
+        idx = list(range(0, len(probs), max(1, len(probs) // (4 * cores))))[: 4 * cores]
+        sample = [probs[k] for k in idx]
         dt, o = cpu_threads(lambda p: f(p["p_x"], p["p_y"], p["p_z"], t_max=600), sample, cores)
+        # the CPU arm solved the same problems: iteration counts, score bits and x / y / z must be the GPU's
+        same = all(int(c["iters"]) == int(res[k]["iters"])
+                   and np.float32(c["score"]).view(np.uint32) == np.float32(res[k]["score"]).view(np.uint32)
+                   and all(np.array_equal(c[a], res[k][a]) for a in "xyz")
+                   for k, c in zip(idx, o))
         out["dd_C3"]["cpu_baseline"] = {"value": len(sample) / dt, "unit": "problems/s", "cores": cores, "kind": kind,
                                         "iterations_per_s": sum(min(r["iters"] + 1, 600) for r in o) / dt,
+                                        "identical_result": bool(same),
                                         "sample": "%d of the %d problems, %d host threads" % (len(sample), nprob, cores)}
     # ---- (2) McCaskill on C4's sequences and on C5 -------------------------------
     for name, n, L, cid in (("mccaskill_C4", NSEQ, LEN, CONFIG_ID), ("mccaskill_C5", 16, 1500, 5)):
@@ -518,54 +485,72 @@ def run_ours(args):
         t = torch.tensor([nnz], dtype=torch.int64, device=dev); dist.all_reduce(t); nnz_total = int(t.item())
     plan.close()
 
-    # ---- e2e: host buffers in, host CSR out on rank 0 --------------------------
+    # ---- N > 1: the device-resident hand-over (K6) ------------------------------
+    # Every rank's fragment is gathered to rank 0's GPU -- the rank that runs the alignment stage --
+    # by the library's own NCCL gather-v (exact sizes, send / recv to the root only).  Timed apart
+    # from `value` (wall clock around the collective, barrier on both sides, max over ranks).
+    handover = None
+    if world > 1:
+        uid = [dafs_b200.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = dafs_b200.Comm(uid[0], rank, world)
+        plan = dafs_b200.PairHmmPlan(seqs, mpi, mpj, TH)
+        plan.run(); plan.sync()
+        g_ms = []
+        for it in range(2 + min(K, 5)):
+            barrier()
+            t0 = time.perf_counter()
+            g = comm.gather(plan, 0)
+            barrier()
+            dt = time.perf_counter() - t0
+            if it >= 2:
+                g_ms.append(dt * 1e3)
+            if rank == 0:
+                assert int(g.nnz_off[-1]) == nnz_total and int(g.unit_off[-1]) == len(pi)
+                moved = 8 * (int(g.nnz_off[-1]) - int(g.nnz_off[1])) + 4 * (int(g.rows_off[-1]) - int(g.rows_off[1]))
+            g.close()
+        gather_ms = max_over_ranks(sum(g_ms) / len(g_ms))
+        if rank == 0:
+            handover = {"what": "dafs_cuda_pairhmm_plan_gather: NCCL %d gather-v of the CSR fragments to rank 0's GPU "
+                                "(ncclSend / ncclRecv in one group, exact sizes)" % comm.nccl_version(),
+                        "ms": gather_ms, "bytes_received_by_root": moved, "GB_per_s": moved / gather_ms * 1e-6,
+                        "pairs_per_s_kernels_plus_handover": len(pi) / ((step_ms + gather_ms) * 1e-3)}
+        plan.close()
+        comm.close()
+
+    # ---- e2e: host buffers in, host CSR out where rank 0 reads it ----------------
+    # The call the reference-facing adapter makes, once per step and rank: encode + H2D of the
+    # inputs + workspace, all kernels, D2H of the CSR.  N = 1: dafs_cuda_pairhmm_pairs (library-owned
+    # pinned batch).  N > 1: dafs_cuda_pairhmm_pairs_into, each rank delivering its fragment over its
+    # own PCIe link into its region of one host buffer that rank 0 maps (SharedHostBuffer); no
+    # device collective on this route -- the host copy is the product.
     h2d = NSEQ * LEN + 8 * (NSEQ + 1) + 4 * NSEQ + (8 + 4 + 8) * len(mine) + 8
     e2e_times, d2h = [], 0
     shared = None
-    copy_stream = torch.cuda.Stream(device=dev)
+    if world > 1:
+        rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
+        t = torch.tensor([nnz, len(mine), rows_mine], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        caps = t.cpu().numpy()
+        caps[0] = int(caps[0] * 1.02) + 4096                 # nnz of a shard is only known after it ran
+        shared = SharedHostBuffer(dist, rank, world, caps)
+        dst = dafs_b200.HostCsr(*shared.region(rank))
+        units_of = [len(shard(len(pi), r, world)) for r in range(world)]
     for it in range(W + K):
         barrier()
         t0 = time.perf_counter()
         if world == 1:
-            # the call the reference-facing adapter makes (CudaProbCons -> dafs_cuda_pairhmm_pairs):
-            # encode + H2D + workspace, all kernels, D2H of the CSR into pinned host memory
             with dafs_b200.pairhmm_pairs(seqs, mpi, mpj, TH) as b:
                 d2h = b.row_ptr.nbytes + b.nz_off.nbytes + b.col.nbytes + b.val.nbytes
                 checksum = int(b.nnz)
             barrier()
-            if it >= W:
-                e2e_times.append(time.perf_counter() - t0)
-            continue
-        # N > 1: every rank computes its pairs; the CSR fragments are all-gathered on the devices
-        # (NCCL over NVLink: the hand-over to the rank that runs the alignment stage on its GPU)
-        # and, at the same time, copied to host memory that rank 0 maps, each rank over its own
-        # PCIe link into its own region (SharedHostBuffer).
-        p2 = dafs_b200.PairHmmPlan(seqs, mpi, mpj, TH)       # encode + H2D + workspace
-        p2.run()
-        _, n_mine = p2.sync()
-        rows_mine = int((np.array([len(seqs[i]) for i in mpi]) + 1).sum())
-        col = torch.empty(max(n_mine, 1), dtype=torch.int32, device=dev)
-        val = torch.empty(max(n_mine, 1), dtype=torch.float32, device=dev)
-        rp = torch.empty(max(rows_mine, 1), dtype=torch.int32, device=dev)
-        nzo = torch.empty(len(mine) + 1, dtype=torch.int64, device=dev)
-        p2.export(rp.data_ptr(), nzo.data_ptr(), col.data_ptr(), val.data_ptr(), max(n_mine, 1))
-        all_sizes = exchange_sizes(dist, world, dev, n_mine, len(mine), rows_mine)
-        if shared is None or not shared.fits(all_sizes):
-            if shared is not None:
-                shared.close()
-            shared = SharedHostBuffer(dist, rank, world, all_sizes)
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_stream(torch.cuda.current_stream())
-            d2h_mine = shared.put(all_sizes[rank], nzo, rp, col, val)
-        frags = gather_csr(dist, world, dev, col[:n_mine], val[:n_mine], nzo, len(mine), rp[:rows_mine], all_sizes=all_sizes)  # NCCL
-        copy_stream.synchronize()
-        barrier()                                             # every fragment is in host memory
-        if rank == 0:                                         # read-back of the step's result, from the host copy
-            checksum = sum(int(shared.region(r, all_sizes[r])[0][-1]) for r in range(world))
-            assert checksum == sum(int(fr[0].numel()) for fr in frags)
-        d2h = d2h_mine
-        p2.close()
-        barrier()
+        else:
+            n_mine = dafs_b200.pairhmm_pairs_into(seqs, mpi, mpj, TH, dst)
+            d2h = 8 * (len(mine) + 1) + 4 * rows_mine + 8 * n_mine
+            barrier()                                         # every fragment is in host memory
+            if rank == 0:                                     # read-back of the step's result, from the host copy
+                checksum = sum(int(shared.region(r)[0][units_of[r]]) for r in range(world))
+                assert checksum == nnz_total, (checksum, nnz_total)
         if it >= W:
             e2e_times.append(time.perf_counter() - t0)
     if rank == 0:
@@ -573,8 +558,7 @@ def run_ours(args):
     e2e_s = max_over_ranks(sum(e2e_times) / len(e2e_times))
     if world > 1:                                             # bytes copied to the host by all ranks together
         t = torch.tensor([d2h], dtype=torch.int64, device=dev); dist.all_reduce(t); d2h_max = int(t.item())
-        if shared is not None:
-            shared.close()
+        shared.close()
     else:
         d2h_max = int(d2h)
 
@@ -605,6 +589,7 @@ def run_ours(args):
                     "ms_per_step_max": max(e2e_times) * 1e3},
             "gpu_launches": info["launches_per_run"] * K,
             "nnz": nnz_total,
+            "handover": handover,
             "kernel": {"name": "pairhmm_kernel<C=%d>" % info["cols_per_lane"], "grid": info["grid"],
                        "block": info["warps_per_cta"] * 32, "avg_ms": kernel_ms,
                        "workspace_bytes": info["workspace_bytes"]},

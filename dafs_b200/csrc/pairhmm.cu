@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "pairhmm_plan.cuh"
 #include "pairhmm_post.cuh"
 
 namespace dafs {
@@ -108,40 +109,7 @@ __global__ void gather_csr_kernel(int npairs, const int64_t* __restrict__ pool_o
 
 }  // namespace dafs
 
-// ---- plan -------------------------------------------------------------------
-struct dafs_pairhmm_plan {
-  int device = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
-  int nseq = 0, npairs = 0;
-  float th = 0, xcut = 0;
-  int C = 0, grid = 0;
-  int64_t total_rows = 0;          // sum over pairs of (L1+1)
-  std::vector<int64_t> row_off;    // host copy, [npairs+1]
-  // device
-  uint8_t* d_seq = nullptr; int64_t* d_seq_off = nullptr; int32_t* d_seq_len = nullptr;
-  int2* d_pairs = nullptr; int32_t* d_order = nullptr;
-  float* d_planes = nullptr; int64_t plane_stride = 0;
-  float4* d_bnd = nullptr; int64_t bnd_stride = 0;
-  int* d_queue = nullptr; unsigned long long* d_pool_count = nullptr;
-  int64_t* d_row_off = nullptr; int32_t* d_row_ptr = nullptr;
-  uint32_t* d_pool_col = nullptr; float* d_pool_val = nullptr; int64_t pool_cap = 0;
-  int64_t* d_pair_pool_off = nullptr; int32_t* d_pair_nnz = nullptr; float* d_pair_total = nullptr;
-  int64_t* d_nz_off = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
-  // The pair list is run as up to kMaxChunks consecutive launches (whole rounds of the
-  // resident warps each), so that fetch() can copy the CSR of a finished chunk to the
-  // host while the next chunk computes.
-  int nchunks = 1;
-  int chunk_k0[5] = {0, 0, 0, 0, 0};
-  cudaEvent_t ev_chunk[4] = {nullptr, nullptr, nullptr, nullptr};
-  cudaEvent_t evck0[4] = {nullptr, nullptr, nullptr, nullptr}, evck1[4] = {nullptr, nullptr, nullptr, nullptr};
-  int64_t* h_chunk_end = nullptr;   // pinned: nz_off at the end of each chunk
-  cudaStream_t copy_stream = nullptr;
-  bool launched = false;
-  int64_t nnz = -1;
-  float last_ms = 0, last_kernel_ms = 0;
-};
-
+// ---- plan (struct dafs_pairhmm_plan: pairhmm_plan.cuh) -------------------------
 namespace dafs {
 
 static const int kWarps = 4;     // warps per CTA
@@ -487,6 +455,47 @@ extern "C" int dafs_cuda_pairhmm_plan_info(dafs_pairhmm_plan* p, dafs_pairhmm_in
   return DAFS_CUDA_OK;
 }
 
+namespace dafs {
+struct HostCsr { int64_t* nz_off; int32_t* row_ptr; uint32_t* col; float* val; };
+
+// Copies the CSR of a run that is still in flight, chunk by chunk on the copy stream, each chunk
+// as soon as it is assembled (under the next chunk's kernel).  cap = entries col / val can take.
+// *overflow: a chunk ended past cap (pool too small, or the caller's buffers): nothing usable was
+// delivered, the caller synchronises (which regrows the pool and reruns if need be) and copies
+// once with the exact size.
+static cudaError_t copy_chunks(dafs_pairhmm_plan* p, const HostCsr& h, int64_t cap, bool* overflow, int64_t* copied) {
+  cudaError_t e = cudaSuccess;
+  int64_t beg = 0;
+  *overflow = false;
+  for (int c = 0; c < p->nchunks && e == cudaSuccess; ++c) {
+    e = cudaEventSynchronize(p->ev_chunk[c]);
+    if (e != cudaSuccess) break;
+    const int64_t end = p->h_chunk_end[c];
+    if (end > cap || end > p->pool_cap) { *overflow = true; break; }
+    const int64_t r0 = p->row_off[p->chunk_k0[c]], r1 = p->row_off[p->chunk_k0[c + 1]];
+    if (r1 > r0) e = cudaMemcpyAsync(h.row_ptr + r0, p->d_row_ptr + r0, sizeof(int32_t) * (r1 - r0), cudaMemcpyDeviceToHost, p->copy_stream);
+    if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h.col + beg, p->d_col + beg, sizeof(uint32_t) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
+    if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h.val + beg, p->d_val + beg, sizeof(float) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
+    beg = end;
+  }
+  if (e == cudaSuccess && !*overflow) e = cudaMemcpyAsync(h.nz_off, p->d_nz_off, sizeof(int64_t) * (p->npairs + 1), cudaMemcpyDeviceToHost, p->copy_stream);
+  const cudaError_t e2 = cudaStreamSynchronize(p->copy_stream);
+  *copied = beg;
+  return e == cudaSuccess ? e2 : e;
+}
+
+// One copy of a synchronised result (p->nnz known).
+static cudaError_t copy_whole(dafs_pairhmm_plan* p, const HostCsr& h) {
+  const int64_t nnz = p->nnz, rows = p->total_rows;
+  cudaError_t e = cudaMemcpyAsync(h.nz_off, p->d_nz_off, sizeof(int64_t) * (p->npairs + 1), cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h.row_ptr, p->d_row_ptr, sizeof(int32_t) * rows, cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h.col, p->d_col, sizeof(uint32_t) * nnz, cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h.val, p->d_val, sizeof(float) * nnz, cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  return e;
+}
+}  // namespace dafs
+
 extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch* out) {
   if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   *out = dafs_csr_batch{};
@@ -514,55 +523,72 @@ extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch
     char* base = (char*)dafs::pinned_alloc(total);
     if (!base) return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %zu bytes failed", total);
     int64_t* h_row_off = (int64_t*)base;
-    int64_t* h_nz_off = (int64_t*)(base + up(b_row_off));
-    int32_t* h_row_ptr = (int32_t*)((char*)h_nz_off + up(b_nz_off));
-    uint32_t* h_col = (uint32_t*)((char*)h_row_ptr + up(b_row_ptr));
-    float* h_val = (float*)((char*)h_col + up(b_col));
+    dafs::HostCsr h;
+    h.nz_off = (int64_t*)(base + up(b_row_off));
+    h.row_ptr = (int32_t*)((char*)h.nz_off + up(b_nz_off));
+    h.col = (uint32_t*)((char*)h.row_ptr + up(b_row_ptr));
+    h.val = (float*)((char*)h.col + up(b_col));
     std::memcpy(h_row_off, p->row_off.data(), b_row_off);
     cudaError_t e = cudaSuccess;
-    bool overflow = false;
     if (mode == 0) {
-      int64_t beg = 0;
-      for (int c = 0; c < p->nchunks && e == cudaSuccess; ++c) {
-        e = cudaEventSynchronize(p->ev_chunk[c]);
-        if (e != cudaSuccess) break;
-        const int64_t end = p->h_chunk_end[c];
-        if (end > cap) { overflow = true; break; }
-        const int64_t r0 = p->row_off[p->chunk_k0[c]], r1 = p->row_off[p->chunk_k0[c + 1]];
-        if (r1 > r0) e = cudaMemcpyAsync(h_row_ptr + r0, p->d_row_ptr + r0, sizeof(int32_t) * (r1 - r0), cudaMemcpyDeviceToHost, p->copy_stream);
-        if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h_col + beg, p->d_col + beg, sizeof(uint32_t) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
-        if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h_val + beg, p->d_val + beg, sizeof(float) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
-        beg = end;
-      }
-      if (e == cudaSuccess && !overflow) e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->copy_stream);
-      const cudaError_t e2 = cudaStreamSynchronize(p->copy_stream);
-      if (e == cudaSuccess) e = e2;
+      bool overflow = false; int64_t copied = 0;
+      e = dafs::copy_chunks(p, h, cap, &overflow, &copied);
       if (e == cudaSuccess && !overflow) {
         const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);   // sets nnz and the timings; the stream is idle
         if (rc) { dafs::pinned_free(base); return rc; }
-        if (p->nnz != beg) overflow = true;                                  // cannot happen: nz_off ends at the pool count
+        if (p->nnz != copied) overflow = true;                               // cannot happen: nz_off ends at the pool count
       }
       if (e == cudaSuccess && overflow) { dafs::pinned_free(base); continue; }   // regrow + rerun in sync(), then one copy
     } else if (np > 0) {
-      const int64_t nnz = p->nnz;
-      e = cudaMemcpyAsync(h_nz_off, p->d_nz_off, b_nz_off, cudaMemcpyDeviceToHost, p->stream);
-      if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h_row_ptr, p->d_row_ptr, b_row_ptr, cudaMemcpyDeviceToHost, p->stream);
-      if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_col, p->d_col, sizeof(uint32_t) * nnz, cudaMemcpyDeviceToHost, p->stream);
-      if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h_val, p->d_val, sizeof(float) * nnz, cudaMemcpyDeviceToHost, p->stream);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+      e = dafs::copy_whole(p, h);
     } else {
-      h_nz_off[0] = 0;
+      h.nz_off[0] = 0;
     }
     if (e != cudaSuccess) {
       dafs::pinned_free(base);
       return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
     }
     out->n_units = np; out->nnz = p->nnz;
-    out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
-    out->col = h_col; out->val = h_val; out->owner_ = base;
+    out->row_off = h_row_off; out->row_ptr = h.row_ptr; out->nz_off = h.nz_off;
+    out->col = h.col; out->val = h.val; out->owner_ = base;
     return DAFS_CUDA_OK;
   }
   return fail(DAFS_CUDA_ECUDA, "internal: fetch fell through");
+}
+
+// The same delivery into host arrays the CALLER owns (dafs_host_csr): what one rank of a
+// multi-process run calls with its region of a host buffer that the consuming process maps
+// (page-locked by the caller so that the chunk copies run under the kernels).
+extern "C" int dafs_cuda_pairhmm_plan_fetch_into(dafs_pairhmm_plan* p, dafs_host_csr* dst) {
+  if (!p || !dst) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  if (!dst->nz_off || !dst->row_ptr || (dst->cap_nnz > 0 && (!dst->col || !dst->val)))
+    return fail(DAFS_CUDA_EINVAL, "dafs_host_csr: NULL array");
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  dst->n_units = p->npairs; dst->rows = p->total_rows; dst->nnz = 0;
+  if (dst->cap_units < p->npairs || dst->cap_rows < p->total_rows)
+    return fail(DAFS_CUDA_ENOMEM, "dafs_host_csr holds %lld units / %lld rows, the result has %lld / %lld",
+                (long long)dst->cap_units, (long long)dst->cap_rows, (long long)p->npairs, (long long)p->total_rows);
+  if (p->npairs == 0) { dst->nz_off[0] = 0; return DAFS_CUDA_OK; }
+  dafs::HostCsr h{dst->nz_off, dst->row_ptr, dst->col, dst->val};
+  if (p->nnz < 0 && p->nchunks > 1) {
+    bool overflow = false; int64_t copied = 0;
+    const cudaError_t e = dafs::copy_chunks(p, h, dst->cap_nnz, &overflow, &copied);
+    if (e != cudaSuccess) return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
+    const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+    if (rc) return rc;
+    if (!overflow && p->nnz == copied) { dst->nnz = p->nnz; return DAFS_CUDA_OK; }
+  } else {
+    const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  dst->nnz = p->nnz;
+  if (p->nnz > dst->cap_nnz)
+    return fail(DAFS_CUDA_ENOMEM, "dafs_host_csr holds %lld entries, the result has %lld (nnz is set: regrow and call again)",
+                (long long)dst->cap_nnz, (long long)p->nnz);
+  const cudaError_t e = dafs::copy_whole(p, h);
+  if (e != cudaSuccess) return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e));
+  return DAFS_CUDA_OK;
 }
 
 // Device-to-device copy of the pair-ordered CSR into caller-owned device
@@ -603,6 +629,21 @@ extern "C" int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const i
   if (rc) return rc;
   rc = dafs_cuda_pairhmm_plan_run(p);
   if (!rc) rc = dafs_cuda_pairhmm_plan_fetch(p, out);
+  dafs_cuda_pairhmm_plan_destroy(p);
+  return rc;
+}
+
+extern "C" int dafs_cuda_pairhmm_pairs_into(int nseq, const char* const* seq, const int* len,
+                                            int64_t npairs, const int32_t* pi, const int32_t* pj,
+                                            float th, dafs_host_csr* dst) {
+  if (!dst) return fail(DAFS_CUDA_EINVAL, "dst is NULL");
+  dafs_pairhmm_plan* p = nullptr;
+  dafs::g_chunked_fetch = true;
+  int rc = dafs_cuda_pairhmm_plan_create(nseq, seq, len, npairs, pi, pj, th, &p);
+  dafs::g_chunked_fetch = false;
+  if (rc) return rc;
+  rc = dafs_cuda_pairhmm_plan_run(p);
+  if (!rc) rc = dafs_cuda_pairhmm_plan_fetch_into(p, dst);
   dafs_cuda_pairhmm_plan_destroy(p);
   return rc;
 }

@@ -109,6 +109,29 @@ int dafs_cuda_pairhmm_plan_sync(dafs_pairhmm_plan* plan, float* device_ms, int64
 int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* plan, dafs_csr_batch* out);
 void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* plan);
 
+/* The same result delivered into HOST arrays the caller owns -- what one rank of a
+ * multi-process run (one process per GPU, pairs sharded with dafs_cuda_pairhmm_pairs'
+ * explicit list) calls with its region of a host buffer that the consuming process maps,
+ * e.g. POSIX shared memory registered with cudaHostRegister; replaces the per-pair
+ * push_back into mp[i][j] of src/align.cpp:69-78 for that rank's pairs.  The caller sets
+ * the cap_* fields and the four pointers; the call fills n_units, rows, nnz and the arrays
+ * (same meaning as in dafs_csr_batch; the row_ptr block of unit u starts at the sum of
+ * len[pi[k]] + 1 over k < u).  Too small: DAFS_CUDA_ENOMEM with n_units / rows / nnz set
+ * to what is needed.  Page-locked arrays let the copy of a finished part of the pair list
+ * run under the kernel of the next part.                                              */
+typedef struct dafs_host_csr {
+  int64_t cap_units, cap_rows, cap_nnz;   /* in: capacity of nz_off (- 1), row_ptr, col / val */
+  int64_t* nz_off;                        /* [cap_units + 1]                                   */
+  int32_t* row_ptr;                       /* [cap_rows]                                        */
+  uint32_t* col;                          /* [cap_nnz]                                         */
+  float* val;                             /* [cap_nnz]                                         */
+  int64_t n_units, rows, nnz;             /* out                                               */
+} dafs_host_csr;
+int dafs_cuda_pairhmm_pairs_into(int nseq, const char* const* seq, const int* len,
+                                 int64_t npairs, const int32_t* pi, const int32_t* pj,
+                                 float th, dafs_host_csr* dst);
+int dafs_cuda_pairhmm_plan_fetch_into(dafs_pairhmm_plan* plan, dafs_host_csr* dst);
+
 /* Device-resident hand-over: copies the pair-ordered CSR (row_ptr blocks,
  * nz_off[npairs+1], col, val) into caller-owned DEVICE buffers, e.g. the
  * tensors a rank feeds to an NCCL all-gather.  cap_nnz = capacity of d_col/d_val
@@ -116,6 +139,45 @@ void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* plan);
 int dafs_cuda_pairhmm_plan_export(dafs_pairhmm_plan* plan, int32_t* d_row_ptr,
                                   int64_t* d_nz_off, uint32_t* d_col, float* d_val,
                                   int64_t cap_nnz);
+
+/* ---- K6: hand-over between ranks (one process per GPU, NCCL over NVLink) ---------
+ * No counterpart in the single-process reference; this is the "sparse posterior matrices
+ * are gathered to the rank that runs progressive alignment" step, i.e.
+ * what stands between the per-rank loops over pairs (src/align.cpp:41-51) and the code
+ * that reads all of mp_ (src/dafs.cpp:1797-1838).  NCCL is bound at run time
+ * (libnccl.so.2); without it these calls return DAFS_CUDA_ENOTSUP.
+ *   unique_id  rank 0 makes the 128-byte id and hands it to the others (any channel)
+ *   create     collective over all ranks; binds the communicator to the current device
+ *   gather     collective: every rank's fragment (the result of its plan, pairs in that
+ *              rank's own order) lands on `root`, device-resident, exact sizes, as the
+ *              concatenation over ranks r of
+ *                d_nz_off  [units_r + 1] entries at unit_off[r] + r, relative to nnz_off[r]
+ *                d_row_ptr [rows_r] at rows_off[r];  d_col / d_val [nnz_r] at nnz_off[r]
+ *              (unit_off / nnz_off / rows_off are host arrays of nranks + 1 prefix sums).
+ *              On the other ranks *out stays empty.                                     */
+#define DAFS_CUDA_COMM_ID_BYTES 128
+typedef struct dafs_comm dafs_comm;
+int dafs_cuda_comm_unique_id(void* id128);
+int dafs_cuda_comm_create(const void* id128, int rank, int nranks, dafs_comm** comm);
+int dafs_cuda_comm_info(const dafs_comm* comm, int* rank, int* nranks, int* nccl_version);
+void dafs_cuda_comm_destroy(dafs_comm* comm);
+typedef struct dafs_gathered_csr {
+  int32_t nranks;
+  const int64_t* unit_off;   /* host [nranks+1] */
+  const int64_t* nnz_off;    /* host [nranks+1] */
+  const int64_t* rows_off;   /* host [nranks+1] */
+  const int64_t* d_nz_off;   /* device */
+  const int32_t* d_row_ptr;  /* device */
+  const uint32_t* d_col;     /* device */
+  const float* d_val;        /* device */
+  void* owner_;              /* private */
+} dafs_gathered_csr;
+int dafs_cuda_pairhmm_plan_gather(dafs_pairhmm_plan* plan, dafs_comm* comm, int root,
+                                  dafs_gathered_csr* out);
+/* D2H of a gathered result into caller arrays sized from the offsets (any may be NULL). */
+int dafs_cuda_gathered_to_host(const dafs_gathered_csr* g, int64_t* nz_off, int32_t* row_ptr,
+                               uint32_t* col, float* val);
+void dafs_cuda_free_gathered(dafs_gathered_csr* g);
 
 /* Geometry and timings of a plan (for benchmarks and profiles). */
 typedef struct dafs_pairhmm_info {

@@ -48,8 +48,9 @@ template <class... A> inline void info(const char*, A&&...) {}
 }  // namespace spdlog
 
 namespace {
-int g_last_iters = 0;
-unsigned g_last_violated = 0;
+// per thread: bench.py's CPU arm runs independent problems on all host cores
+thread_local int g_last_iters = 0;
+thread_local unsigned g_last_violated = 0;
 }
 
 // Stub with exactly the members DAFS::solve_by_dd touches (dafs.cpp:126-152).
@@ -116,7 +117,7 @@ struct Alifold {
 };
 namespace {
 struct SolveLog { int L1, L2, iters; unsigned violated; float score; };
-std::vector<SolveLog> g_solve_log;
+thread_local std::vector<SolveLog> g_solve_log;
 }
 float DAFS::solve(VU& x, VU& y, VU& z, const VVF& p_x, const VVF& p_y, const VVF& p_z, const ALN& aln1,
                   const ALN& aln2) const {
