@@ -121,6 +121,7 @@ struct dafs_mccaskill_plan {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int nseq = 0, W = 0, grid = 0, smem = 0, cluster = 1;
+  int gl = 8, threads = MC_THREADS;    // lanes per DP cell, threads per CTA (mccaskill_kernel<GL>)
   float th = 0;
   int64_t total_rows = 0, pool_cap = 0;
   std::vector<int64_t> row_off;
@@ -147,6 +148,9 @@ static void free_mc_plan(dafs_mccaskill_plan* p) {
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 static const int kMcMaxLen = 6000;
+static const void* mc_kernel_fn(int gl) {
+  return gl == 8 ? (const void*)mccaskill_kernel<8> : gl == 16 ? (const void*)mccaskill_kernel<16> : (const void*)mccaskill_kernel<32>;
+}
 }  // namespace dafs
 
 using dafs::fail;
@@ -201,14 +205,25 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   dafs::DevInfo prop;
   PLAN_TRY(dafs::dev_info(p->device, &prop));
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  p->smem = (int)(tab_bytes + sizeof(double) * MC_CGEN_ROWS * 32 + 2 * sizeof(double) * (p->W + 2) + p->W + 16);
+  p->smem = (int)(tab_bytes + sizeof(McCoef) + 2 * sizeof(double) * (p->W + 2) + 2 * sizeof(uint16_t) * p->W + p->W + 16);
   if ((size_t)p->smem > prop.smem_optin)
     return bail(fail(DAFS_CUDA_ENOTSUP, "sequence of %d nt needs %d bytes of shared memory", maxn, p->smem));
-  PLAN_TRY(cudaFuncSetAttribute(mccaskill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+  // Lanes per DP cell: the sums of a cell are as long as its span, so short sequences (whose
+  // diagonals hold fewer cells than the CTA has lanes) get 8-lane groups and long ones whole warps.
+  p->gl = maxn <= 480 ? 8 : maxn <= 1100 ? 16 : 32;
+  if (const char* e = getenv("DAFS_MCCASKILL_LANES")) { const int v = atoi(e); if (v == 8 || v == 16 || v == 32) p->gl = v; }
+  // Throughput form (at least one sequence per SM): two CTAs of 384 threads per SM, each with a
+  // sequence of its own, so that one sequence's per-diagonal barrier and serial cell tails are
+  // covered by the other's work.  Latency form (fewer sequences than SMs): one CTA of 768 threads,
+  // in a thread-block cluster per sequence.
+  p->threads = (nseq >= prop.sms && 2 * (size_t)p->smem + 2048 <= prop.smem_optin) ? MC_THREADS / 2 : MC_THREADS;
+  if (const char* e = getenv("DAFS_MCCASKILL_THREADS")) { const int v = atoi(e); if (v >= 64 && v <= MC_THREADS && v % 32 == 0) p->threads = v; }
+  const void* fn = mc_kernel_fn(p->gl);
+  PLAN_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   int blocks = 0;
-  PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, mccaskill_kernel, MC_THREADS, p->smem));
+  PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, fn, p->threads, p->smem));
   if (blocks < 1) return bail(fail(DAFS_CUDA_ECUDA, "mccaskill_kernel does not fit on an SM"));
-  p->ws_stride = (size_t)MC_NARRAYS * p->W * p->W;
+  p->ws_stride = (size_t)MC_NARRAYS * p->W * p->W + (size_t)MC_NROWS * p->W;
   size_t free_b = 0, total_b = 0;
   PLAN_TRY(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cta = p->ws_stride * sizeof(double);
@@ -265,16 +280,18 @@ extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   a.row_off = p->d_row_off; a.row_ptr = p->d_row_ptr; a.pool_off = p->d_pool_off; a.pool_col = p->d_pool_col;
   a.pool_val = p->d_pool_val; a.seq_nnz = p->d_seq_nnz; a.seq_lnz = p->d_seq_lnz;
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  DAFS_CUDA_TRY(cudaFuncSetAttribute(mccaskill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+  const void* fn = mc_kernel_fn(p->gl);
+  DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p->grid); cfg.blockDim = dim3(MC_THREADS);
+    cfg.gridDim = dim3(p->grid); cfg.blockDim = dim3(p->threads);
     cfg.dynamicSmemBytes = p->smem; cfg.stream = p->stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = p->cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    DAFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, mccaskill_kernel, a));
+    void* kargs[] = {(void*)&a};
+    DAFS_CUDA_TRY(cudaLaunchKernelExC(&cfg, fn, kargs));
   }
   mc_scan_kernel<<<1, 32, 0, p->stream>>>(p->d_seq_nnz, p->nseq, p->d_nz_off);
   DAFS_CUDA_TRY(cudaGetLastError());
@@ -338,7 +355,7 @@ extern "C" int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* p, dafs_csr_b
 
 extern "C" int dafs_cuda_mccaskill_plan_info(dafs_mccaskill_plan* p, dafs_mccaskill_info* info) {
   if (!p || !info) return fail(DAFS_CUDA_EINVAL, "NULL argument");
-  info->grid = p->grid; info->block = MC_THREADS; info->smem_bytes = p->smem; info->row_stride = p->W;
+  info->grid = p->grid; info->block = p->threads; info->smem_bytes = p->smem; info->row_stride = p->W;
   info->workspace_bytes = (int64_t)(p->ws_stride * sizeof(double)) * (p->grid / p->cluster);
   info->table_bytes = (int)sizeof(dafs::McTables);
   info->last_ms = p->last_ms;

@@ -11,17 +11,32 @@
 //   qm(i,j)  = sum_{k=i..j} (mlb^(k-i) + qm(i,k-1)) * qm1(k,j)  =  A(i,j) + R(i,j)  with
 //              A(i,j) = sum_{k=i+1..j} qm(i,k-1)*qm1(k,j)   and   R(i,j) = qm1(i,j) + mlb*R(i+1,j);
 //              the multiloop closing sum of qb(i,j) is then just A(i+1,j-1)
-//   qq(i,j)  = qq(i,j-1)*sc + qb(i,j)*Ext(i,j)                (ViennaRNA's rolling qq)
-//   q(i,j)   = sc^(j-i+1) + qq(i,j) + sum_{k=i..j-1} q(i,k) * qq(k+1,j)
-//   O(i,j)   = q(1,i-1)*q(j+1,n)*Ext(i,j) + sum_{interior (p,q)} O(p,q)*wI*sc^(..)
-//            + MLstem(i,j) * sum_{p<i} [ prm_l(p,j)*qm(p+1,i-1) + prml(p,j)*(mlb^(i-p-1) + qm(p+1,i-1)) ]
-//            = ... MLstem(i,j) * [ sum_{p<i-1} PL(p,j)*qm(p+1,i-1) + tB(i,j) ],  PL = prm_l + prml,
+//   exterior: only q(1,j) =: q5[j] and q(i,n) =: q3[i] are ever used (Z = q5[n] and the
+//              first term of O), so instead of ViennaRNA's O(n^3) q(i,j) table
+//              q5[j] = q5[j-1]*sc + sum_k q5[k-1] * qb(k,j)*Ext(k,j)     (j unpaired | j pairs with k)
+//              q3[i] = q3[i+1]*sc + sum_k qb(i,k)*Ext(i,k) * q3[k+1]     (i unpaired | i pairs with k)
+//              -- the same sums over structures, O(n^2) in total, evaluated by the cell (1,j) /
+//              (i,n) of the diagonal that completes column j / row i of qb
+//   O(i,j)   = q5[i-1]*q3[j+1]*Ext(i,j) + sum_{interior (p,q)} O(p,q)*wI*sc^(..)
+//            + MLstem(i,j) * [ sum_{p<i-1} PL(p,j)*qm(p+1,i-1) + tB(i,j) ],  PL = prm_l + prml,
 //              tB(i,j) = prml(i-1,j) + mlb*tB(i-1,j)
 //   prm_l(p,j) = prm_l(p,j+1)*mlb + OM(p,j+1),  prml(p,j) = sum_{q>j+1} OM(p,q)*qm(j+1,q-1),
-//   OM = O*MLclose*sc^2,   P(i,j) = qb*O / q(1,n).
-// Every O(span) inner sum runs over one index with a warp striding it; arrays
-// that are read along their first index are kept transposed (qm1T, qqT, qmT,
-// prmlT, prm_lT) so that all of those reads are coalesced.
+//   OM = O*MLclose*sc^2,   P(i,j) = qb*O / Z.
+//
+// Work layout: a cell of the diagonal belongs to a GROUP of GL lanes (GL = 8 for sequences up to
+// 480 nt: four cells per warp; 16 up to 1100 nt; whole warps beyond): the sums of a cell run over
+// one index with the group striding it, the serial parts (hairpin, the seven small interior loops,
+// the epilogue with its table look-ups) occupy one lane of eight instead of one of thirty-two, and
+// four times as many cells are in flight per SM.  Cells are handed out from a per-diagonal list
+// that holds the cells whose ends can pair first, so the groups of a warp mostly do the same work.
+// Arrays that are read along their first index are kept transposed (qm1T, qmT, E5T, GT, PLT, HT)
+// so that every stream is contiguous; quantities that are only read one or two diagonals later
+// (A, R, prm_l, prml, tB, the V rows of the interior-loop recurrence) live in rolling per-diagonal
+// rows instead of W x W arrays.  Eight W x W FP64 arrays per team remain (was thirteen): qb qm qmT
+// O, and qm1T / E5T / G / GT whose storage the outside pass reuses for OM / PLT / H / HT.
+// Launch forms (mccaskill.cu): at least one sequence per SM -> two CTAs of 384 threads per SM, each
+// with its own sequence (one sequence's diagonal barrier is covered by the other's work); fewer ->
+// one CTA of 768 threads, in a thread-block cluster per sequence.
 #pragma once
 #include <cooperative_groups.h>
 
@@ -39,7 +54,7 @@ struct McArgs {
   int W;                       // row stride of the DP arrays = max n + 2
   float th;
   const McTables* tab;         // in HBM; staged to shared memory by every CTA
-  double* ws;                  // per-team workspace: MC_NARRAYS arrays of W*W doubles
+  double* ws;                  // per-team workspace: MC_NARRAYS arrays of W*W doubles + MC_NROWS rows of W
   size_t ws_stride;            // doubles per team
   // outputs
   const int64_t* row_off;      // [nseq+1] start of each sequence's row_ptr block (n+1 entries)
@@ -54,16 +69,25 @@ struct McArgs {
 #ifndef MC_THREADS
 #define MC_THREADS 768      // 80 registers per thread: one CTA of 24 warps per SM
 #endif
-#define MC_WARPS (MC_THREADS / 32)
+#ifndef MC_UNR
+#define MC_UNR 4            // pairs of stream loads a lane has in flight in the O(span) sums
+#endif
+#define MC_WARPS (MC_THREADS / 32)   // most warps a CTA can have; the launch may use fewer (blockDim.x)
 
 __device__ __forceinline__ double mc_warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+template <int GL>
+__device__ __forceinline__ double mc_group_sum(double v) {
+#pragma unroll
+  for (int o = GL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
 
-// The CTAs of one thread-block cluster share a sequence: cell c of a diagonal
-// belongs to CTA c % nc, the per-diagonal barrier is the cluster barrier (release /
+// The CTAs of one thread-block cluster share a sequence: entry e of a diagonal's cell list
+// belongs to CTA e % nc, the per-diagonal barrier is the cluster barrier (release /
 // acquire at cluster scope, so the global-memory DP arrays written by one CTA are
 // visible to the others), a lone CTA uses the block barrier.
 struct McTeam {
@@ -75,258 +99,411 @@ __device__ __forceinline__ void mc_sync(const McTeam& tm) {
 }
 
 struct McWs {
-  double *q, *qb, *qm, *qmT, *qm1T, *qqT, *O, *OM, *prmlT, *prm_lT;
-  double *G, *A, *R;       // inside only
-  double *H, *PLT, *tB;    // outside only: they reuse the storage of G, A, R
+  double *qb, *qm, *qmT, *O;
+  double *qm1T, *E5T, *G, *GT; // inside only
+  double *OM, *PLT, *H, *HT;   // outside only: they reuse the storage of qm1T, E5T, G, GT
+  double *Vroll;               // V rows of the last three diagonals: [3][W][32]
+  // rows of W doubles
+  double *q5, *q3;             // exterior partition functions of prefixes / suffixes
+  double *Aroll, *Rroll;       // inside: A of the last three diagonals, R of the last two (indexed by i)
+  double *plroll, *prroll, *tbroll;   // outside: prm_l, prml, tB of the last two diagonals (indexed by i)
 };
-#define MC_NARRAYS 13
+#define MC_NARRAYS 8
+#define MC_NROWS (14 + 96)   // q5 q3 | Aroll x3 Rroll x2 | plroll x2 prroll x2 tbroll x2 (+1 spare) | Vroll 3 x 32
+
+// Per-CTA scheduling state in static shared memory.
+struct McSched {
+  int next[2];                 // hand-out counter of the diagonal (double-buffered)
+  int wcnt[MC_WARPS];          // per-warp counts of the cell list being built
+};
 
 // Interior loops.  A loop with u1, u2 unpaired bases is "generic" when ViennaRNA's
 // exp_E_IntLoop takes its last branch, internal[u1+u2] * mismatchI(outer) *
 // mismatchI(inner) * ninio[|u1-u2|]: every (u1,u2) with min >= 1 except 1x1, 1x2,
-// 2x1, 2x2.  For those the weight factorises into a part of the outer pair, a part
-// of the inner pair and a part of (u1,u2) alone, so with
+// 2x1, 2x2.  With
 //   G(k,l) = qb(k,l) * mismatchI[rtype(k,l)][S[l+1]][S[k-1]]      (inside)
 //   H(p,q) = O(p,q)  * mismatchI[type(p,q)][S[p+1]][S[q-1]]       (outside)
-//   cgen[u1][u2] = internal[u1+u2] * ninio[|u1-u2|] * scale[u1+u2+2]   (0 for the rest)
-// the generic part of a cell is one masked dot product of a 30x30 triangle of G
-// (or H) with cgen, and only the 65 special loops (stack, bulges, 1x1, 1x2, 2x1,
-// 2x2) are evaluated through mc_interior.
-#define MC_GEN_BATCH 10      // loads of G / H in flight per lane
-#define MC_CGEN_ROWS 41      // u1 = 0..40 (rows past 30 are zero: the u1 loop runs in batches)
+// the generic part of a cell is mismatchI(outer) * sum_s internal[s]*scale[s+2] * V(i,j,s),
+//   V(i,j,s) = sum_{u1+u2=s, u1,u2>=1} ninio[|u1-u2|] * G(i+1+u1, j-1-u2),
+// and growing a loop by one unpaired base on EACH side keeps |u1-u2|, so
+//   V(i,j,s) = V(i+1,j-1,s-2) + ninio[s-2] * ( G(i+2, j-s) + G(i+s, j-2) )      (one term for s = 2)
+// -- O(30) per cell from the row kept two diagonals ago instead of a 435-term sum per cell (the
+// idea of the O(n^3) interior-loop evaluation of Lyngso et al.).  Every cell maintains its V row
+// (an enclosing pair needs it whether or not the cell's own ends pair).  The four small loops the
+// generic formula does not cover sit at s = 2 (1x1), s = 3 (1x2, 2x1) and in V(i+1,j-1,2) of s = 4
+// (2x2), so the combination takes nothing from s = 2, 3 and only the two new terms at s = 4.
+// Outside: Vo(i,j,s) = Vo(i-1,j+1,s-2) + ninio[s-2] * ( H(i-2, j+s) + H(i-s, j+2) ) likewise.
+// Bulges of 2..30 bases are bulge[u]*scale[u+2] * tAU(outer) * tAU(inner) along one row and one
+// column of qb (O outside); the remaining seven loops (stack, 1-bulges, 1x1, 1x2, 2x1, 2x2) go
+// through mc_interior on seven lanes.
+struct McCoef {              // per-scale coefficient tables in shared memory
+  double fgen[32];           // internal[s] * scale[s+2]
+  double gnin[32];           // ninio[k]
+  double cbul[32];           // bulge[u] * scale[u+2]
+};
 
-// sum over u1 >= 1, 1 <= u2 = lane of A[u1*row_step + u2*col_step] * cgen[u1][u2]
-// subject to u1 <= u1max, u2 <= u2max, u1 + u2 <= usum (<= MC_MAXLOOP).  Lane-partial.
-__device__ __forceinline__ double mc_generic_sum(const double* __restrict__ A, ptrdiff_t row_step, int col_step,
-                                                 const double* __restrict__ cgen, int u1max, int u2max, int usum,
-                                                 int lane) {
-  double s = 0.0;
-  const int u2 = lane;
-  const bool lane_ok = u2 >= 1 && u2 <= u2max;
-  const double* a = A + (ptrdiff_t)u2 * col_step;
-  const int top = min(u1max, usum - 1);
-  for (int u0 = 1; u0 <= top; u0 += MC_GEN_BATCH) {
-    double v[MC_GEN_BATCH];
+// The cell list of diagonal d (cells i = 1 .. n-d, j = i+d): cells for which `front(i)` holds are
+// packed at the head in ascending i, the others at the tail in descending i.  Built by the whole
+// CTA before the barrier that ends the previous diagonal; the order is a pure function of the
+// predicate, so every CTA of a cluster builds the same list and takes entries e = rank (mod nc).
+template <class F>
+__device__ __forceinline__ void mc_build_list(uint16_t* list, int ncell, McSched& sc, F front) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x;
+  int base = 0;                                  // front cells among those of earlier passes
+  for (int b = 0; b < ncell; b += NT) {
+    const int c = b + tid;                       // cell i = c + 1
+    const bool in = c < ncell;
+    const bool f = in && front(c + 1);
+    const unsigned mf = __ballot_sync(0xffffffffu, f);
+    if (lane == 0) sc.wcnt[warp] = __popc(mf);
+    __syncthreads();
+    int before = 0, total = 0;
 #pragma unroll
-    for (int t = 0; t < MC_GEN_BATCH; ++t) {
-      const int u1 = u0 + t;
-      v[t] = (lane_ok && u1 <= u1max && u1 + u2 <= usum) ? a[(ptrdiff_t)u1 * row_step] : 0.0;
-    }
-#pragma unroll
-    for (int t = 0; t < MC_GEN_BATCH; ++t) s += v[t] * cgen[(u0 + t) * 32 + u2];
+    for (int k = 0; k < MC_WARPS; ++k) { const int x = k < (NT >> 5) ? sc.wcnt[k] : 0; total += x; if (k < warp) before += x; }
+    const int nf = base + before + __popc(mf & ((1u << lane) - 1u));    // front cells with a smaller index
+    if (f) list[nf] = (uint16_t)(c + 1);
+    else if (in) list[ncell - 1 - (c - nf)] = (uint16_t)(c + 1);
+    base += total;
+    if (b + NT < ncell) __syncthreads();          // wcnt is rewritten by the next pass
   }
-  return s;
 }
 
-// Inside recursion over all spans for the current scale.  Returns nothing; q(1,n) is in ws.q.
+// Inside recursion over all spans for the current scale.  Z = q5[n] afterwards.
+template <int GL>
 __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                          const double* mlb, const double* cgen, int* next_cell, const McWs& w, const McTeam& tm,
-                          int lane) {
+                          const double* mlb, const McCoef& cf, McSched& sc, uint16_t* lists, const McWs& w,
+                          const McTeam& tm, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
-  for (int i = 1 + tm.rank * MC_THREADS + threadIdx.x; i <= n + 1; i += tm.nc * MC_THREADS) w.q[IX(i, i - 1)] = 1.0;
-  if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
+  constexpr int WG = 32 / GL;         // cells per warp
+  const int gl = lane & (GL - 1), grp = lane / GL, NT = blockDim.x;
+  if (threadIdx.x < 2) sc.next[threadIdx.x] = 0;
+  if (tm.rank == 0 && threadIdx.x == 0) { w.q5[0] = 1.0; w.q3[n + 1] = 1.0; }
+  __syncthreads();
+  mc_build_list(lists, n, sc, [&](int) { return true; });
   mc_sync(tm);
   for (int d = 0; d < n; ++d) {
-    // cells of the diagonal are handed out dynamically: a cell whose ends can pair
-    // costs several times one whose ends cannot
+    const int ncell = n - d;
+    const uint16_t* list = lists + (d & 1) * W;
+    const int usum = min(MC_MAXLOOP, d - MC_TURN - 3);          // u1 + u2 <= usum keeps l - k > TURN
+    double* Ad = w.Aroll + (d % 3) * W;
+    const double* Ad2 = w.Aroll + ((d + 1) % 3) * W;            // diagonal d - 2
+    double* Rd = w.Rroll + (d & 1) * W;
+    const double* Rd1 = w.Rroll + ((d + 1) & 1) * W;            // diagonal d - 1
+    double* Vd = w.Vroll + (size_t)(d % 3) * W * 32;
+    const double* Vd2 = w.Vroll + (size_t)((d + 1) % 3) * W * 32;   // diagonal d - 2
     for (;;) {
-      int i = 0;
-      if (lane == 0) i = 1 + tm.rank + tm.nc * atomicAdd(&next_cell[d & 1], 1);
-      i = __shfl_sync(0xffffffffu, i, 0);
-      if (i + d > n) break;
+      int h = 0;
+      if (lane == 0) h = atomicAdd(&sc.next[d & 1], WG);
+      h = __shfl_sync(0xffffffffu, h, 0);
+      if (h * tm.nc + tm.rank >= ncell) break;
+      const int e = (h + grp) * tm.nc + tm.rank;
+      const bool valid = e < ncell;
+      const int i = valid ? (int)list[e] : 1;
       const int j = i + d;
-      const int si = S[i], sj = S[j];
-      const int type = mc_pair(si, sj);
+      const int type = valid ? mc_pair(S[i], S[j]) : 0;
       const bool closes = (d > MC_TURN) && type != 0;
-      // operands of the lane-0 epilogue, requested now so that their latency hides
-      // behind the sums (uniform addresses: one broadcast transaction each)
-      const double pre_A = (closes && d > 2) ? w.A[IX(i + 1, j - 1)] : 0.0;
-      const double pre_m1 = d > 0 ? w.qm1T[IX(j - 1, i)] : 0.0;
-      const double pre_e1 = d > 0 ? w.qqT[IX(j - 1, i)] : 0.0;
-      const double pre_R = d > 0 ? w.R[IX(i + 1, j)] : 0.0;
+      const bool lead = valid && gl == 0;
+      // operands of the group's epilogue, requested now so that their latency hides behind the sums
+      double pre_A = 0.0, pre_m1 = 0.0, pre_R = 0.0;
+      if (lead && d > 0) {
+        pre_m1 = w.qm1T[IX(j - 1, i)];
+        pre_R = Rd1[i + 1];
+        if (closes && d > 2) pre_A = Ad2[i + 1];
+      }
+      // V row of this cell (every cell), and the generic interior-loop part of a closing one
       double vb = 0.0;          // hairpin + interior part of qb, lane-partial
-      if (closes) {
-        if (lane == 0) {
-          const int u = d - 1;
-          int s6 = 0;
-          if (u == 4) { for (int c = 0; c < 6; ++c) s6 = s6 * 5 + S[i + c]; }
-          vb = mc_hairpin(T, u, type, S[i + 1], S[j - 1], s6) * scale[u + 2];
-        }
-        const int si1 = S[i + 1], sj1 = S[j - 1];
-        const int usum = min(MC_MAXLOOP, d - MC_TURN - 3);       // u1 + u2 <= usum keeps l - k > TURN
-        if (usum >= 0) {
-          // generic loops
-          if (usum >= 2)
-            vb += (double)T.mmI[type - 1][si1][sj1] *
-                  mc_generic_sum(w.G + IX(i + 1, j - 1), (ptrdiff_t)W, -1, cgen, MC_MAXLOOP, MC_MAXLOOP, usum, lane);
-          // special loops: round 0 = stack and right bulges (u1 = 0, u2 = lane), round 1 = left
-          // bulges (u1 = lane, u2 = 0), round 2 = 1x1, 1x2, 2x1, 2x2 on lanes 0..3
+      if (usum >= 2) {
+        constexpr int NC = 32 / GL;
+        const double* Vold = Vd2 + (size_t)(i + 1) * 32;
+        double* Vnew = Vd + (size_t)i * 32;
+        const double* Grow = w.G + IX(i + 2, j);          // G(i+2, j-s) = Grow[-s]
+        const double* GTrow = w.GT + IX(j - 2, i);        // G(i+s, j-2) = GT[j-2][i+s] = GTrow[s]
+        double gen = 0.0;
 #pragma unroll
-          for (int round = 0; round < 3; ++round) {
-            int u1, u2;
-            bool ok;
-            if (round == 0) { u1 = 0; u2 = lane; ok = lane <= usum; }
-            else if (round == 1) { u1 = lane; u2 = 0; ok = lane >= 1 && lane <= usum; }
-            else { u1 = 1 + (lane >> 1); u2 = 1 + (lane & 1); ok = lane < 4 && u1 + u2 <= usum; }
-            if (ok) {
-              const int k = i + 1 + u1, l = j - 1 - u2;
-              const double v = w.qb[IX(k, l)];
-              if (v != 0.0)
-                vb += v * mc_interior(T, u1, u2, type, mc_rtype(mc_pair(S[k], S[l])), si1, sj1, S[k - 1], S[l + 1]) *
-                      scale[u1 + u2 + 2];
+        for (int c = 0; c < NC; ++c) {
+          const int sz = 2 + gl + GL * c;
+          if (valid && sz <= usum) {
+            double bnd = Grow[-sz];
+            if (sz > 2) bnd += GTrow[sz];
+            bnd *= cf.gnin[sz - 2];
+            double v = bnd;
+            if (sz >= 4) v += Vold[sz - 2];
+            Vnew[sz] = v;
+            gen += cf.fgen[sz] * (sz >= 5 ? v : (sz == 4 ? bnd : 0.0));
+          }
+        }
+        if (closes) vb = (double)T.mmI[type - 1][S[i + 1]][S[j - 1]] * gen;
+      }
+      if (__any_sync(0xffffffffu, closes)) {
+        if (closes) {
+          const int si1 = S[i + 1], sj1 = S[j - 1];
+          if (gl == GL - 1) {
+            const int u = d - 1;
+            int s6 = 0;
+            if (u == 4) { for (int c = 0; c < 6; ++c) s6 = s6 * 5 + S[i + c]; }
+            vb += mc_hairpin(T, u, type, si1, sj1, s6) * scale[u + 2];
+          }
+          if (usum >= 0) {
+            // bulges of 2 .. usum bases: row i+1 and column j-1 of qb
+            double bs = 0.0;
+            const double* qb_r = w.qb + IX(i + 1, j - 1);
+            const double tA = (double)T.termAU;
+            for (int u = 2 + gl; u <= usum; u += GL) {
+              double r = qb_r[-u];
+              if (r != 0.0 && (int)S[i + 1] * (int)S[j - 1 - u] != 6) r *= tA;
+              double c = qb_r[(ptrdiff_t)u * W];
+              if (c != 0.0 && (int)S[i + 1 + u] * (int)S[j - 1] != 6) c *= tA;
+              bs += cf.cbul[u] * (r + c);
+            }
+            vb += (type > 2 ? tA : 1.0) * bs;
+            // stack, 1-bulges, 1x1, 1x2, 2x1, 2x2 on lanes 0..6
+            if (gl < 7) {
+              const int u1 = (0x2211100 >> (4 * gl)) & 15, u2 = (0x2121010 >> (4 * gl)) & 15;
+              if (u1 + u2 <= usum) {
+                const int k = i + 1 + u1, l = j - 1 - u2;
+                const double v = w.qb[IX(k, l)];
+                if (v != 0.0)
+                  vb += v * mc_interior(T, u1, u2, type, mc_rtype(mc_pair(S[k], S[l])), si1, sj1, S[k - 1], S[l + 1]) *
+                        scale[u1 + u2 + 2];
+              }
             }
           }
         }
       }
-      // the two O(d) sums share one pass over k = i+1 .. j; four strides of 32 per
-      // round keep up to 16 independent loads in flight per lane
-      double sm = 0.0, sq = 0.0;
-      const double* qm_i = w.qm + IX(i, 0);
-      const double* q_i = w.q + IX(i, 0);
-      const double* qm1T_j = w.qm1T + IX(j, 0);
-      const double* qqT_j = w.qqT + IX(j, 0);
-      for (int kb = i + 1 + lane; kb <= j; kb += 128) {
-        double a0[4], a1[4], b0[4], b1[4];
+      // A(i,j): one pass over k = i+1 .. j, four strides of 8 per round
+      double sm = 0.0;
+      {
+        const double* qm_i = w.qm + IX(i, 0);
+        const double* qm1T_j = w.qm1T + IX(j, 0);
+        for (int kb = i + 1 + gl; kb <= j; kb += MC_UNR * GL) {
+          double a0[MC_UNR], a1[MC_UNR];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int k = kb + 32 * u;
-          const bool ok = k <= j;
-          a0[u] = ok ? qm_i[k - 1] : 0.0;  a1[u] = ok ? qm1T_j[k] : 0.0;
-          b0[u] = ok ? q_i[k - 1] : 0.0;   b1[u] = ok ? qqT_j[k] : 0.0;
+          for (int u = 0; u < MC_UNR; ++u) {
+            const int k = kb + GL * u;
+            const bool ok = valid && k <= j;
+            a0[u] = ok ? qm_i[k - 1] : 0.0;  a1[u] = ok ? qm1T_j[k] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < MC_UNR; ++u) sm += a0[u] * a1[u];
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { sm += a0[u] * a1[u]; sq += b0[u] * b1[u]; }
       }
-      vb = mc_warp_sum(vb); sm = mc_warp_sum(sm); sq = mc_warp_sum(sq);
-      if (lane == 0) {
+      vb = mc_group_sum<GL>(vb); sm = mc_group_sum<GL>(sm);
+      double e_cur = 0.0;        // qb(i,j) * Ext(i,j)
+      if (lead) {
         if (closes)
           vb += pre_A * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
         w.qb[IX(i, j)] = vb;
-        w.G[IX(i, j)] = (vb != 0.0) ? vb * (double)T.mmI[mc_rtype(type) - 1][S[j + 1]][S[i - 1]] : 0.0;
-        const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
+        const double gij = (vb != 0.0) ? vb * (double)T.mmI[mc_rtype(type) - 1][S[j + 1]][S[i - 1]] : 0.0;
+        w.G[IX(i, j)] = gij;
+        w.GT[IX(j, i)] = gij;
+        const int sl = i > 1 ? (int)S[i - 1] : -1, sr = j < n ? (int)S[j + 1] : -1;
         double m1 = pre_m1 * mlb[1];
-        double e1 = pre_e1 * scale[1];
-        if (vb != 0.0) { m1 += vb * mc_stem(T, type, si1, sj1, true); e1 += vb * mc_stem(T, type, si1, sj1, false); }
+        if (vb != 0.0) { m1 += vb * mc_stem(T, type, sl, sr, true); e_cur = vb * mc_stem(T, type, sl, sr, false); }
         w.qm1T[IX(j, i)] = m1;
-        w.qqT[IX(j, i)] = e1;
+        w.E5T[IX(j, i)] = e_cur;
         const double r = m1 + pre_R * mlb[1];
-        w.A[IX(i, j)] = sm;
-        w.R[IX(i, j)] = r;
+        Ad[i] = sm;
+        Rd[i] = r;
         const double vqm = sm + r;
         w.qm[IX(i, j)] = vqm;
         w.qmT[IX(j, i)] = vqm;
-        w.q[IX(i, j)] = scale[d + 1] + e1 + sq;
+      }
+      // exterior: the cell that completes column j of qb extends q5, the one that completes row i extends q3
+      const bool ext5 = valid && i == 1, ext3 = valid && j == n;
+      if (__any_sync(0xffffffffu, ext5 || ext3)) {
+        double s5 = 0.0, s3 = 0.0;
+        if (ext5) {                                    // k = 2 .. j - TURN - 1 (k = 1 is this cell)
+          const double* e5 = w.E5T + IX(j, 0);
+          for (int k = 2 + gl; k < j - MC_TURN; k += GL) s5 += w.q5[k - 1] * e5[k];
+        }
+        if (ext3) {                                    // k = i + TURN + 1 .. n - 1 (k = n is this cell)
+          const double* qb_i = w.qb + IX(i, 0);
+          const int sl = i > 1 ? (int)S[i - 1] : -1;
+          const int si = S[i];
+          for (int k = i + MC_TURN + 1 + gl; k < n; k += GL) {
+            const double v = qb_i[k];
+            if (v != 0.0) s3 += v * mc_stem(T, mc_pair(si, S[k]), sl, (int)S[k + 1], false) * w.q3[k + 1];
+          }
+        }
+        s5 = mc_group_sum<GL>(s5); s3 = mc_group_sum<GL>(s3);
+        if (lead && ext5) w.q5[j] = w.q5[j - 1] * scale[1] + e_cur + s5;
+        if (lead && ext3) w.q3[i] = w.q3[i + 1] * scale[1] + e_cur + s3;
       }
     }
-    if (threadIdx.x == 0) next_cell[(d + 1) & 1] = 0;
+    // next diagonal: reset its counters, build its list (cells that close first)
+    if (threadIdx.x == 0) { sc.next[(d + 1) & 1] = 0; }
+    if (d + 1 < n) {
+      const int dn = d + 1;
+      mc_build_list(lists + (dn & 1) * W, n - dn, sc,
+                    [&](int i) { return dn <= MC_TURN || mc_pair(S[i], S[i + dn]) != 0; });
+    }
     mc_sync(tm);
   }
 #undef IX
 }
 
 // Outside recursion; needs the inside arrays of the same scale.
+template <int GL>
 __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
-                           const double* mlb, const double* cgen, int* next_cell, const McWs& w, const McTeam& tm,
-                           int lane) {
+                           const double* mlb, const McCoef& cf, McSched& sc, uint16_t* lists, const McWs& w,
+                           const McTeam& tm, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
-  // O, H, OM, prmlT, prm_lT, PLT, tB start at zero: entries that are never written
-  // (pairs that cannot form, q > n) are read as 0.
-  for (size_t c = (size_t)tm.rank * MC_THREADS + threadIdx.x; c < (size_t)(n + 2) * W; c += (size_t)tm.nc * MC_THREADS) {
-    w.O[c] = 0.0; w.H[c] = 0.0; w.OM[c] = 0.0; w.prmlT[c] = 0.0; w.prm_lT[c] = 0.0; w.PLT[c] = 0.0; w.tB[c] = 0.0;
+  constexpr int WG = 32 / GL;         // cells per warp
+  const int gl = lane & (GL - 1), grp = lane / GL, NT = blockDim.x;
+  // O, H, OM, PLT start at zero: entries that are never written (pairs that cannot form, q > n) are
+  // read as 0; so do the rolling rows.
+  for (size_t c = (size_t)tm.rank * NT + threadIdx.x; c < (size_t)(n + 2) * W; c += (size_t)tm.nc * NT) {
+    w.O[c] = 0.0; w.H[c] = 0.0; w.HT[c] = 0.0; w.OM[c] = 0.0; w.PLT[c] = 0.0;
   }
-  if (threadIdx.x < 2) next_cell[threadIdx.x] = 0;
+  for (int c = tm.rank * NT + threadIdx.x; c < 6 * W; c += tm.nc * NT) w.plroll[c] = 0.0;   // plroll | prroll | tbroll are contiguous
+  if (threadIdx.x < 2) sc.next[threadIdx.x] = 0;
+  __syncthreads();
+  {
+    const int d0 = n - 1;
+    if (d0 > MC_TURN)
+      mc_build_list(lists + (d0 & 1) * W, n - d0, sc,
+                    [&](int i) { return mc_pair(S[i], S[i + d0]) != 0 && w.qb[IX(i, i + d0)] != 0.0; });
+  }
   mc_sync(tm);
   for (int d = n - 1; d > MC_TURN; --d) {
+    const int ncell = n - d;
+    const uint16_t* list = lists + (d & 1) * W;
+    double* pl_d = w.plroll + (d & 1) * W;   const double* pl_d1 = w.plroll + ((d + 1) & 1) * W;   // diagonal d + 1
+    double* pr_d = w.prroll + (d & 1) * W;   const double* pr_d1 = w.prroll + ((d + 1) & 1) * W;
+    double* tb_d = w.tbroll + (d & 1) * W;   const double* tb_d1 = w.tbroll + ((d + 1) & 1) * W;
+    double* Vd = w.Vroll + (size_t)(d % 3) * W * 32;
+    const double* Vd2 = w.Vroll + (size_t)((d + 2) % 3) * W * 32;   // diagonal d + 2
     for (;;) {
-      int i = 0;
-      if (lane == 0) i = 1 + tm.rank + tm.nc * atomicAdd(&next_cell[d & 1], 1);
-      i = __shfl_sync(0xffffffffu, i, 0);
-      if (i + d > n) break;
+      int h = 0;
+      if (lane == 0) h = atomicAdd(&sc.next[d & 1], WG);
+      h = __shfl_sync(0xffffffffu, h, 0);
+      if (h * tm.nc + tm.rank >= ncell) break;
+      const int e = (h + grp) * tm.nc + tm.rank;
+      const bool valid = e < ncell;
+      const int i = valid ? (int)list[e] : 1;
       const int j = i + d;
-      const double pre_pl = j + 1 <= n ? w.prm_lT[IX(j + 1, i)] : 0.0;
-      const double pre_om = j + 1 <= n ? w.OM[IX(i, j + 1)] : 0.0;
-      const double pre_prml = i > 1 ? w.prmlT[IX(j, i - 1)] : 0.0;
-      const double pre_tB = i > 1 ? w.tB[IX(i - 1, j)] : 0.0;
-      const double pre_q1 = w.q[IX(1, i - 1)], pre_q2 = w.q[IX(j + 1, n)];
-      // (a) prm_l(i,j), prml(i,j): OM of spans >= d+1 only
-      if (j + 1 <= n) {
-        double t = 0.0;
-        const double* OM_i = w.OM + IX(i, 0);
-        const double* qm_j1 = w.qm + IX(j + 1, 0);
-        for (int qb0 = j + 2 + lane; qb0 <= n; qb0 += 128) {
-          double x0[4], x1[4];
+      const bool lead = valid && gl == 0;
+      const int type = valid ? mc_pair(S[i], S[j]) : 0;
+      const double qbij = type ? w.qb[IX(i, j)] : 0.0;
+      const bool pairs = type != 0 && qbij != 0.0;
+      double pre_pl = 0.0, pre_om = 0.0, pre_prml = 0.0, pre_tB = 0.0, pre_q1 = 0.0, pre_q2 = 0.0;
+      if (lead) {
+        if (j + 1 <= n) { pre_pl = pl_d1[i]; pre_om = w.OM[IX(i, j + 1)]; }
+        if (i > 1) { pre_prml = pr_d1[i - 1]; pre_tB = tb_d1[i - 1]; }
+        if (pairs) { pre_q1 = w.q5[i - 1]; pre_q2 = w.q3[j + 1]; }
+      }
+      // (a) prml(i,j) = sum_{q = j+2 .. n} OM(i,q) * qm(j+1,q-1)            [every cell]
+      // (c) sum_{p = 1 .. i-2} PL(p,j) * qm(p+1,i-1)                        [cells that pair]
+      // fused into one loop of na + nc steps: both operands of a step are contiguous in their stream
+      const int na = valid ? max(0, n - j - 1) : 0, ncc = pairs ? max(0, i - 2) : 0;
+      double ta = 0.0, tc = 0.0;
+      {
+        const double* OM_i = w.OM + IX(i, 0) + (j + 2);          // OM(i, j+2+t)
+        const double* qm_j1 = w.qm + IX(min(j + 1, n), 0) + (j + 1);   // qm(j+1, j+1+t)
+        const double* pl_j = w.PLT + IX(j, 0) + 1;               // PL(1+t, j)
+        const double* qmT_i1 = w.qmT + IX(i - 1, 0) + 2;         // qm(2+t, i-1) = qmT[i-1][2+t]
+        const int tot = na + ncc;
+        const int wtot = __reduce_max_sync(0xffffffffu, tot);
+        for (int tb0 = gl; tb0 < wtot; tb0 += MC_UNR * GL) {
+          double x0[MC_UNR], x1[MC_UNR];
+          bool first[MC_UNR];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int qx = qb0 + 32 * u;
-            x0[u] = qx <= n ? OM_i[qx] : 0.0; x1[u] = qx <= n ? qm_j1[qx - 1] : 0.0;
+          for (int u = 0; u < MC_UNR; ++u) {
+            const int t = tb0 + GL * u;
+            first[u] = t < na;
+            const bool ok = t < tot;
+            const int t2 = t - na;
+            x0[u] = ok ? (first[u] ? OM_i[t] : pl_j[t2]) : 0.0;
+            x1[u] = ok ? (first[u] ? qm_j1[t] : qmT_i1[t2]) : 0.0;
           }
 #pragma unroll
-          for (int u = 0; u < 4; ++u) t += x0[u] * x1[u];
-        }
-        t = mc_warp_sum(t);
-        if (lane == 0) {
-          const double pl = pre_pl * mlb[1] + pre_om;
-          w.prmlT[IX(j, i)] = t;
-          w.prm_lT[IX(j, i)] = pl;
-          w.PLT[IX(j, i)] = t + pl;
+          for (int u = 0; u < MC_UNR; ++u) { const double pr = x0[u] * x1[u]; if (first[u]) ta += pr; else tc += pr; }
         }
       }
-      const double tb = pre_prml + mlb[1] * pre_tB;
-      if (lane == 0 && i > 1) w.tB[IX(i, j)] = tb;
-      // (b) O(i,j)
-      const int type = mc_pair(S[i], S[j]);
-      if (!type) continue;
-      const double qbij = w.qb[IX(i, j)];
-      if (qbij == 0.0) continue;
-      const int si1 = i > 1 ? (int)S[i - 1] : -1, sj1 = j < n ? (int)S[j + 1] : -1;
-      const int t2 = mc_rtype(type);
+      // (b) O(i,j): the Vo row of this cell (every cell) and the generic enclosing loops of a pairing one
       double o = 0.0;
-      if (lane == 0) o = pre_q1 * pre_q2 * mc_stem(T, type, si1, sj1, false);
-      if (i > 1 && j < n) {
-        // (p,q) = (i-1-u1, j+1+u2) encloses (i,j)
-        const int sp1 = S[i - 1], sq1 = S[j + 1];
-        const int u1max = min(MC_MAXLOOP, i - 2), u2max = min(MC_MAXLOOP, n - j - 1);
-        if (u1max >= 1 && u2max >= 1)
-          o += (double)T.mmI[t2 - 1][sq1][sp1] *
-               mc_generic_sum(w.H + IX(i - 1, j + 1), -(ptrdiff_t)W, 1, cgen, u1max, u2max, MC_MAXLOOP, lane);
+      {
+        constexpr int NC = 32 / GL;
+        const bool has_old = valid && i >= 2 && j + 1 <= n;        // cell (i-1, j+1) of diagonal d + 2 exists
+        const double* Vold = Vd2 + (size_t)(i - 1) * 32;
+        double* Vnew = Vd + (size_t)i * 32;
+        const double* Hrow = w.H + IX(i - 2, j);                   // H(i-2, j+s) = Hrow[s]
+        const double* HTrow = w.HT + IX(j + 2, i);                 // H(i-s, j+2) = HT[j+2][i-s] = HTrow[-s]
+        double gen = 0.0;
 #pragma unroll
-        for (int round = 0; round < 3; ++round) {
-          int u1, u2;
-          bool ok;
-          if (round == 0) { u1 = 0; u2 = lane; ok = lane <= MC_MAXLOOP; }
-          else if (round == 1) { u1 = lane; u2 = 0; ok = lane >= 1 && lane <= MC_MAXLOOP; }
-          else { u1 = 1 + (lane >> 1); u2 = 1 + (lane & 1); ok = lane < 4; }
-          if (ok && u1 <= u1max && u2 <= u2max) {
-            const int p = i - 1 - u1, qx = j + 1 + u2;
-            const double v = w.O[IX(p, qx)];
-            if (v != 0.0)
-              o += v * mc_interior(T, u1, u2, mc_pair(S[p], S[qx]), t2, S[p + 1], S[qx - 1], sp1, sq1) *
-                   scale[u1 + u2 + 2];
+        for (int c = 0; c < NC; ++c) {
+          const int sz = 2 + gl + GL * c;
+          if (valid && sz <= MC_MAXLOOP) {
+            double bnd = 0.0;
+            if (i >= 3 && j + sz <= n) bnd = Hrow[sz];
+            if (sz > 2 && i - sz >= 1 && j + 2 <= n) bnd += HTrow[-sz];
+            bnd *= cf.gnin[sz - 2];
+            double v = bnd;
+            if (sz >= 4 && has_old) v += Vold[sz - 2];
+            Vnew[sz] = v;
+            gen += cf.fgen[sz] * (sz >= 5 ? v : (sz == 4 ? bnd : 0.0));
+          }
+        }
+        if (pairs) o = (double)T.mmI[mc_rtype(type) - 1][S[j + 1]][S[i - 1]] * gen;
+      }
+      if (__any_sync(0xffffffffu, pairs)) {
+        if (pairs && i > 1 && j < n) {
+          // (p,q) = (i-1-u1, j+1+u2) encloses (i,j)
+          const int t2 = mc_rtype(type);
+          const int sp1 = S[i - 1], sq1 = S[j + 1];
+          const int u1max = min(MC_MAXLOOP, i - 2), u2max = min(MC_MAXLOOP, n - j - 1);
+          // bulges of 2 .. 30 bases: row i-1 and column j+1 of O
+          double bs = 0.0;
+          const double* O_r = w.O + IX(i - 1, j + 1);
+          const double tA = (double)T.termAU;
+          for (int u = 2 + gl; u <= MC_MAXLOOP; u += GL) {
+            double r = u <= u2max ? O_r[u] : 0.0;
+            if (r != 0.0 && sp1 * (int)S[j + 1 + u] != 6) r *= tA;
+            double c = u <= u1max ? O_r[-(ptrdiff_t)u * W] : 0.0;
+            if (c != 0.0 && (int)S[i - 1 - u] * sq1 != 6) c *= tA;
+            bs += cf.cbul[u] * (r + c);
+          }
+          o += (type > 2 ? tA : 1.0) * bs;
+          if (gl < 7) {
+            const int u1 = (0x2211100 >> (4 * gl)) & 15, u2 = (0x2121010 >> (4 * gl)) & 15;
+            if (u1 <= u1max && u2 <= u2max) {
+              const int p = i - 1 - u1, qx = j + 1 + u2;
+              const double v = w.O[IX(p, qx)];
+              if (v != 0.0)
+                o += v * mc_interior(T, u1, u2, mc_pair(S[p], S[qx]), t2, S[p + 1], S[qx - 1], sp1, sq1) *
+                     scale[u1 + u2 + 2];
+            }
           }
         }
       }
-      double t = 0.0;
-      const double* pl_j = w.PLT + IX(j, 0);
-      const double* qmT_i1 = w.qmT + IX(i - 1, 0);       // qm(p+1, i-1) = qmT[i-1][p+1]
-      for (int pb = 1 + lane; pb < i - 1; pb += 128) {
-        double x0[4], x1[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int p = pb + 32 * u;
-          x0[u] = p < i - 1 ? pl_j[p] : 0.0; x1[u] = p < i - 1 ? qmT_i1[p + 1] : 0.0;
+      ta = mc_group_sum<GL>(ta); tc = mc_group_sum<GL>(tc); o = mc_group_sum<GL>(o);
+      if (lead) {
+        if (j + 1 <= n) {
+          const double pl = pre_pl * mlb[1] + pre_om;
+          pr_d[i] = ta;
+          pl_d[i] = pl;
+          w.PLT[IX(j, i)] = ta + pl;
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) t += x0[u] * x1[u];
-      }
-      o = mc_warp_sum(o); t = mc_warp_sum(t);
-      if (lane == 0) {
-        o += (t + tb) * mc_stem(T, type, si1, sj1, true);
-        w.O[IX(i, j)] = o;
-        w.H[IX(i, j)] = o * (double)T.mmI[type - 1][S[i + 1]][S[j - 1]];
-        w.OM[IX(i, j)] = o * ((double)T.ml_closing * mc_stem(T, t2, S[j - 1], S[i + 1], true)) * scale[2];
+        const double tb = pre_prml + mlb[1] * pre_tB;
+        if (i > 1) tb_d[i] = tb;
+        if (pairs) {
+          const int sl = i > 1 ? (int)S[i - 1] : -1, sr = j < n ? (int)S[j + 1] : -1;
+          o += pre_q1 * pre_q2 * mc_stem(T, type, sl, sr, false);
+          o += (tc + tb) * mc_stem(T, type, sl, sr, true);
+          w.O[IX(i, j)] = o;
+          const double hij = o * (double)T.mmI[type - 1][S[i + 1]][S[j - 1]];
+          w.H[IX(i, j)] = hij;
+          w.HT[IX(j, i)] = hij;
+          w.OM[IX(i, j)] = o * ((double)T.ml_closing * mc_stem(T, mc_rtype(type), S[j - 1], S[i + 1], true)) * scale[2];
+        }
       }
     }
-    if (threadIdx.x == 0) next_cell[(d - 1) & 1] = 0;
+    if (threadIdx.x == 0) { sc.next[(d - 1) & 1] = 0; }
+    if (d - 1 > MC_TURN) {
+      const int dn = d - 1;
+      mc_build_list(lists + (dn & 1) * W, n - dn, sc,
+                    [&](int i) { return mc_pair(S[i], S[i + dn]) != 0 && w.qb[IX(i, i + dn)] != 0.0; });
+    }
     mc_sync(tm);
   }
 #undef IX
@@ -336,37 +513,42 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
 
 namespace dafs {
 
-// Dynamic shared memory: McTables | cgen[37][32] | scale[W+2] | mlb[W+2] | codes[W+8]
+// Dynamic shared memory: McTables | McCoef | scale[W+2] | mlb[W+2] | lists[2][W] (uint16) | codes[W+8]
+template <int GL>
 __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   extern __shared__ __align__(16) char smem[];
   __shared__ int s_total;
-  __shared__ int s_next[2];
+  __shared__ McSched s_sched;
   McTables& T = *reinterpret_cast<McTables*>(smem);
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  double* cgen = reinterpret_cast<double*>(smem + tab_bytes);
-  double* scale = cgen + MC_CGEN_ROWS * 32;
+  McCoef& cf = *reinterpret_cast<McCoef*>(smem + tab_bytes);
+  double* scale = reinterpret_cast<double*>(smem + tab_bytes + sizeof(McCoef));
   double* mlb = scale + (a.W + 2);
-  uint8_t* S = reinterpret_cast<uint8_t*>(mlb + (a.W + 2));
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint16_t* lists = reinterpret_cast<uint16_t*>(mlb + (a.W + 2));
+  uint8_t* S = reinterpret_cast<uint8_t*>(lists + 2 * a.W);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x;
   McTeam tm;
   tm.nc = a.cluster;
   tm.rank = tm.nc > 1 ? (int)cooperative_groups::this_cluster().block_rank() : 0;
   const int team = blockIdx.x / tm.nc, nteams = gridDim.x / tm.nc;
-  const int gwarp = tm.rank * MC_WARPS + warp, nwarps = tm.nc * MC_WARPS;
+  const int gwarp = tm.rank * (NT >> 5) + warp, nwarps = tm.nc * (NT >> 5);
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.tab);
     uint32_t* dst = reinterpret_cast<uint32_t*>(&T);
-    for (int k = tid; k < (int)(sizeof(McTables) / 4); k += MC_THREADS) dst[k] = src[k];
+    for (int k = tid; k < (int)(sizeof(McTables) / 4); k += NT) dst[k] = src[k];
   }
   const int W = a.W;
   McWs w;
   {
     double* base = a.ws + (size_t)team * a.ws_stride;
     const size_t A = (size_t)W * W;
-    w.q = base; w.qb = base + A; w.qm = base + 2 * A; w.qmT = base + 3 * A; w.qm1T = base + 4 * A;
-    w.qqT = base + 5 * A; w.O = base + 6 * A; w.OM = base + 7 * A; w.prmlT = base + 8 * A; w.prm_lT = base + 9 * A;
-    w.G = base + 10 * A; w.A = base + 11 * A; w.R = base + 12 * A;
-    w.H = w.G; w.PLT = w.A; w.tB = w.R;
+    w.qb = base; w.qm = base + A; w.qmT = base + 2 * A; w.O = base + 3 * A;
+    w.qm1T = base + 4 * A; w.E5T = base + 5 * A; w.G = base + 6 * A; w.GT = base + 7 * A;
+    w.OM = w.qm1T; w.PLT = w.E5T; w.H = w.G; w.HT = w.GT;
+    double* rows = base + (size_t)MC_NARRAYS * A;
+    w.q5 = rows; w.q3 = rows + W; w.Aroll = rows + 2 * W; w.Rroll = rows + 5 * W;
+    w.plroll = rows + 7 * W; w.prroll = rows + 9 * W; w.tbroll = rows + 11 * W;
+    w.Vroll = rows + 14 * W;
   }
 #define IX(i, j) ((size_t)(i) * W + (j))
   // sequences are dealt to the teams round-robin in length order (longest first)
@@ -375,7 +557,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     const int s = a.order[sq];
     const int n = a.seq_len[s];
     const uint8_t* gs = a.seq + a.seq_off[s];
-    for (int k = tid; k <= n + 1; k += MC_THREADS) S[k] = (k >= 1 && k <= n) ? gs[k - 1] : (uint8_t)0;
+    for (int k = tid; k <= n + 1; k += NT) S[k] = (k >= 1 && k <= n) ? gs[k - 1] : (uint8_t)0;
     // ---- scale: start from ViennaRNA's default per-nucleotide guess and move to
     // exp(lnZ/n) when the first inside pass ends far from 1 (the reference takes
     // its pf_scale from an MFE run instead, fold.cpp:86-95; p does not depend on it)
@@ -384,22 +566,23 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     double Z = 0.0, lnZ = 0.0;
     for (int attempt = 0; attempt < 8; ++attempt) {
       __syncthreads();
-      for (int k = tid; k <= n + 2; k += MC_THREADS) { scale[k] = exp(-(double)k * lns); mlb[k] = exp((double)k * (ln_mlbase - lns)); }
-      for (int k = tid; k < MC_CGEN_ROWS * 32; k += MC_THREADS) {
-        const int u1 = k >> 5, u2 = k & 31, ul = max(u1, u2), us = min(u1, u2);
-        const bool generic = us >= 1 && u1 + u2 <= MC_MAXLOOP && !(us == 1 && ul <= 2) && !(us == 2 && ul == 2);
-        cgen[k] = generic ? (double)T.internal[u1 + u2] * (double)T.ninio[ul - us] * exp(-(double)(u1 + u2 + 2) * lns) : 0.0;
+      for (int k = tid; k <= n + 2; k += NT) { scale[k] = exp(-(double)k * lns); mlb[k] = exp((double)k * (ln_mlbase - lns)); }
+      if (tid < 32) {
+        const int k = tid;
+        cf.fgen[k] = k <= MC_MAXLOOP ? (double)T.internal[k] * exp(-(double)(k + 2) * lns) : 0.0;
+        cf.gnin[k] = k <= MC_MAXLOOP ? (double)T.ninio[k] : 0.0;
+        cf.cbul[k] = k <= MC_MAXLOOP ? (double)T.bulge[k] * exp(-(double)(k + 2) * lns) : 0.0;
       }
       __syncthreads();
-      mc_inside(T, S, n, W, scale, mlb, cgen, s_next, w, tm, lane);
-      Z = w.q[IX(1, n)];
+      mc_inside<GL>(T, S, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
+      Z = w.q5[n];
       if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
       if (!(Z > 0.0)) { lns -= 0.25; continue; }
       lnZ = log(Z) + (double)n * lns;
       if (fabs(log(Z)) <= 150.0) break;
       lns = lnZ / (double)n;                            // rerun with the ensemble's own scale
     }
-    mc_outside(T, S, n, W, scale, mlb, cgen, s_next, w, tm, lane);
+    mc_outside<GL>(T, S, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
     // ---- read-out: p = float(qb*O/Z) > th, rows ascending, columns ascending ----
     int32_t* row_ptr = a.row_ptr + a.row_off[s];
     const float th = a.th;
