@@ -48,3 +48,33 @@ def test_team_equals_single_warp_and_oracle(length, family, mutation):
     o = ou.oracle_dd(probs[0]["p_x"], probs[0]["p_y"], probs[0]["p_z"], t_max=120)
     assert base[0]["iters"] == o["iters"] and base[0]["score"].view(np.uint32) == o["score"].view(np.uint32)
     assert all(np.array_equal(base[0][k], o[k]) for k in "xyz")
+
+
+def test_team_mode_is_repeatable():
+    """compute-sanitizer is closed on the B200 pool (profiles/r02_sanitizer.txt), so the race check
+    of the team pipeline (progress flags in shared memory) is run-to-run identity: 40 runs per team
+    size of the same batch, every bit of every result equal to the first run and to one warp."""
+    probs = []
+    for k in range(6):
+        p_x, p_y, p_z = ou.dd_problem(100 + 20 * k, family=5 + k, mutation=0.5, mix=True)
+        probs.append(dict(p_x=p_x, p_y=p_y, p_z=p_z, t_max=60))
+    base, _ = solve(probs, 1)
+    for team in (2, 3):
+        old = os.environ.get("DAFS_DD_TEAM")
+        os.environ["DAFS_DD_TEAM"] = str(team)
+        try:
+            plan = db.DDPlan(probs, trace=True)
+            for rep in range(40):
+                plan.run(); plan.sync()
+                got = plan.fetch()
+                for g, b in zip(got, base):
+                    assert g["iters"] == b["iters"] and g["violated"] == b["violated"], (team, rep)
+                    assert g["score"].view(np.uint32) == b["score"].view(np.uint32), (team, rep)
+                    assert all(np.array_equal(g[k], b[k]) for k in "xyz"), (team, rep)
+                    assert np.array_equal(g["trace"].view(np.uint32), b["trace"].view(np.uint32)), (team, rep)
+            plan.close()
+        finally:
+            if old is None:
+                del os.environ["DAFS_DD_TEAM"]
+            else:
+                os.environ["DAFS_DD_TEAM"] = old

@@ -105,3 +105,20 @@ def test_config_c5_length(dafs):
         oracle_results = list(ex.map(ou.oracle_mccaskill, seqs))
     assert oracle_results[2][1] / 1500 > 0.8          # ln Z per nucleotide far above the first-pass scale
     assert check_batch(dafs, seqs, 0.01, oracle_results) <= TOL
+
+
+def test_repeatable(dafs):
+    """Run-to-run identity of the kernel (dynamic cell hand-out, rolling rows, 8-lane groups): the
+    order in which groups pick up cells varies between runs, the bits of the result must not."""
+    seqs = random_rna(6, 120, config_id=13) + random_rna(3, 520, config_id=14)
+    with dafs.McCaskillPlan(seqs, 0.01) as plan:
+        first = None
+        for rep in range(12):
+            plan.run()
+            b, lnz = plan.fetch()
+            with b:
+                cur = (b.row_ptr.copy(), b.col.copy(), b.val.view(np.uint32).copy(), np.array(lnz))
+            if first is None:
+                first = cur
+            else:
+                assert all(np.array_equal(x, y) for x, y in zip(first, cur)), rep
