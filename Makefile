@@ -19,7 +19,7 @@ $(CSRC)/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh) include/dafs_cuda.h
 $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart_static -lpthread -ldl -lrt
 
-oracle:
+oracle: $(LIB)
 	$(MAKE) -C oracle
 
 clean:

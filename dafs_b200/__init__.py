@@ -27,7 +27,7 @@ from .capi import (  # noqa: F401
     pairhmm_tables,
 )
 from .capi_comm import Comm, HostCsr, comm_unique_id, pairhmm_pairs_into, plan_fetch_into  # noqa: F401
-from .capi_mc import McCaskillPlan, mccaskill_all  # noqa: F401
+from .capi_mc import McCaskillPlan, mccaskill_all, mccaskill_constrained  # noqa: F401
 from .capi_pct import pct, pct_last_ms  # noqa: F401
 from .capi_prog import guide_tree, progressive  # noqa: F401
 from .capi_dd import DDPlan, dd_solve_batch, nussinov_decode, nw_decode, nw_decode_static  # noqa: F401

@@ -22,6 +22,10 @@ def _protos():
                                               C.c_int, C.POINTER(_CsrBatch)]
         L.dafs_cuda_mccaskill_plan_create.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
                                                       C.c_float, C.POINTER(C.c_void_p)]
+        L.dafs_cuda_mccaskill_plan_create_constrained.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
+                                                                  C.POINTER(C.c_char_p), C.c_float, C.POINTER(C.c_void_p)]
+        L.dafs_cuda_mccaskill_constrained.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
+                                                      C.POINTER(C.c_char_p), C.c_float, C.POINTER(_CsrBatch)]
         L.dafs_cuda_mccaskill_plan_run.argtypes = [C.c_void_p]
         L.dafs_cuda_mccaskill_plan_sync.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64)]
         L.dafs_cuda_mccaskill_plan_fetch.argtypes = [C.c_void_p, C.POINTER(_CsrBatch), C.c_void_p]
@@ -41,13 +45,39 @@ def mccaskill_all(seqs, th=0.01, ngpu=1):
     return CsrBatch(raw, None)
 
 
+def _cons_args(cons, n):
+    """constraint strings (bytes / str / None per sequence) -> char*[n]"""
+    arr = (C.c_char_p * max(n, 1))()
+    keep = []
+    for k, c in enumerate(cons):
+        if c is not None:
+            keep.append(c.encode("ascii") if isinstance(c, str) else bytes(c))
+            arr[k] = keep[-1]
+    return arr, keep
+
+
+def mccaskill_constrained(seqs, cons, th=0.01):
+    """RNAfold::calculate(seq, str, bp) for a batch: cons[k] in the reference's alphabet ('?' free,
+    '.' unpaired, '(' ')' a given pair) or None."""
+    L = _protos()
+    b, n, arr, lens = _seq_args(seqs)
+    carr, keep = _cons_args(cons, n)
+    raw = _CsrBatch()
+    _check(L.dafs_cuda_mccaskill_constrained(n, arr, lens, carr, C.c_float(th), C.byref(raw)))
+    return CsrBatch(raw, None)
+
+
 class McCaskillPlan:
-    def __init__(self, seqs, th=0.01):
+    def __init__(self, seqs, th=0.01, cons=None):
         L = _protos()
         b, n, arr, lens = _seq_args(seqs)
         self.nseq = n
         self._h = C.c_void_p()
-        _check(L.dafs_cuda_mccaskill_plan_create(n, arr, lens, C.c_float(th), C.byref(self._h)))
+        if cons is None:
+            _check(L.dafs_cuda_mccaskill_plan_create(n, arr, lens, C.c_float(th), C.byref(self._h)))
+        else:
+            carr, keep = _cons_args(cons, n)
+            _check(L.dafs_cuda_mccaskill_plan_create_constrained(n, arr, lens, carr, C.c_float(th), C.byref(self._h)))
 
     def run(self):
         _check(lib().dafs_cuda_mccaskill_plan_run(self._h))

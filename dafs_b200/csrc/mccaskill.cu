@@ -123,8 +123,9 @@ struct dafs_mccaskill_plan {
   int nseq = 0, W = 0, grid = 0, smem = 0, cluster = 1;
   int gl = 8, threads = MC_THREADS;    // lanes per DP cell, threads per CTA (mccaskill_kernel<GL>)
   float th = 0;
-  int64_t total_rows = 0, pool_cap = 0;
+  int64_t total_rows = 0, pool_cap = 0, seq_bytes = 0;
   std::vector<int64_t> row_off;
+  uint16_t* d_cons = nullptr;      // constraint classes | partners, each as long as d_seq (NULL: unconstrained)
   uint8_t* d_seq = nullptr; int64_t* d_seq_off = nullptr; int32_t* d_seq_len = nullptr; int32_t* d_order = nullptr;
   dafs::McTables* d_tab = nullptr;
   double* d_ws = nullptr; size_t ws_stride = 0;
@@ -139,6 +140,7 @@ struct dafs_mccaskill_plan {
 
 namespace dafs {
 static void free_mc_plan(dafs_mccaskill_plan* p) {
+  dev_free(p->d_cons);
   dev_free(p->d_seq); dev_free(p->d_seq_off); dev_free(p->d_seq_len); dev_free(p->d_order); dev_free(p->d_tab);
   dev_free(p->d_ws); dev_free(p->d_row_off); dev_free(p->d_row_ptr); dev_free(p->d_pool_off);
   dev_free(p->d_pool_col); dev_free(p->d_pool_val); dev_free(p->d_seq_nnz); dev_free(p->d_seq_lnz);
@@ -155,8 +157,41 @@ static const void* mc_kernel_fn(int gl) {
 
 using dafs::fail;
 
+namespace dafs {
+// Constraint string of one sequence (the reference's alphabet: '?' free, '.' stays unpaired, '(' ')'
+// a given pair; anything else is treated as free) -> per-position class and partner (mc_allowed).
+static int encode_constraint(const char* str, int n, uint16_t* cls, uint16_t* prt) {
+  std::vector<int> open, open_loop;
+  int next_loop = 1, cur = 0;
+  for (int k = 0; k < n; ++k) {
+    cls[k] = (uint16_t)cur; prt[k] = 0;
+    const char c = str[k];
+    if (c == '.') cls[k] = (uint16_t)(cur | 0x8000);
+    else if (c == '(') {
+      cls[k] = (uint16_t)(cur | 0x4000);
+      open.push_back(k); open_loop.push_back(cur);
+      if (next_loop >= 0x3fff) return -1;
+      cur = next_loop++;
+    } else if (c == ')') {
+      if (open.empty()) return -1;
+      const int a = open.back(); open.pop_back();
+      cur = open_loop.back(); open_loop.pop_back();
+      cls[k] = (uint16_t)(cur | 0x4000);
+      prt[k] = (uint16_t)(a + 1); prt[a] = (uint16_t)(k + 1);
+    }
+  }
+  return open.empty() ? 0 : -1;
+}
+}  // namespace dafs
+
 extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq, const int* len, float th,
                                                dafs_mccaskill_plan** out) {
+  return dafs_cuda_mccaskill_plan_create_constrained(nseq, seq, len, nullptr, th, out);
+}
+
+extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char* const* seq, const int* len,
+                                                           const char* const* str, float th,
+                                                           dafs_mccaskill_plan** out) {
   using namespace dafs;
   if (!out) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
   *out = nullptr;
@@ -196,6 +231,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   }
   p->total_rows = p->row_off[nseq]; p->pool_cap = pool_off[nseq];
   std::vector<uint8_t> enc(seq_off[nseq]);
+  p->seq_bytes = seq_off[nseq];
   for (int i = 0; i < nseq; ++i)
     for (int k = 0; k < len[i]; ++k) enc[seq_off[i] + k] = mc_code((unsigned char)seq[i][k]);
   std::vector<int32_t> order(nseq);
@@ -205,7 +241,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   dafs::DevInfo prop;
   PLAN_TRY(dafs::dev_info(p->device, &prop));
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  p->smem = (int)(tab_bytes + sizeof(McCoef) + 2 * sizeof(double) * (p->W + 2) + 2 * sizeof(uint16_t) * p->W + p->W + 16);
+  p->smem = (int)(tab_bytes + sizeof(McCoef) + 2 * sizeof(double) * (p->W + 2) + 2 * sizeof(uint16_t) * p->W + p->W + 16 + 2 * sizeof(uint16_t) * (p->W + 2));
   if ((size_t)p->smem > prop.smem_optin)
     return bail(fail(DAFS_CUDA_ENOTSUP, "sequence of %d nt needs %d bytes of shared memory", maxn, p->smem));
   // Lanes per DP cell: the sums of a cell are as long as its span, so short sequences (whose
@@ -255,6 +291,18 @@ extern "C" int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq,
   PLAN_TRY(dev_malloc(&p->d_nz_off, sizeof(int64_t) * (nseq + 1)));
   PLAN_TRY(dev_malloc(&p->d_col, sizeof(uint32_t) * p->pool_cap));
   PLAN_TRY(dev_malloc(&p->d_val, sizeof(float) * p->pool_cap));
+  if (str) {
+    const size_t tot = enc.size();
+    std::vector<uint16_t> cons(2 * tot, 0);
+    for (int i = 0; i < nseq; ++i) {
+      if (!str[i]) { continue; }       // this sequence is unconstrained: class 0 (one loop), no partners
+      if (encode_constraint(str[i], len[i], cons.data() + seq_off[i], cons.data() + tot + seq_off[i]))
+        return bail(fail(DAFS_CUDA_EINVAL, "sequence %d: unbalanced brackets in the constraint", i));
+    }
+    PLAN_TRY(dev_malloc(&p->d_cons, sizeof(uint16_t) * 2 * std::max<size_t>(tot, 1)));
+    PLAN_TRY(cudaMemcpyAsync(p->d_cons, cons.data(), sizeof(uint16_t) * 2 * tot, cudaMemcpyHostToDevice, p->stream));
+    PLAN_TRY(cudaStreamSynchronize(p->stream));
+  }
   PLAN_TRY(cudaMemcpyAsync(p->d_seq, enc.data(), enc.size(), cudaMemcpyHostToDevice, p->stream));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq_off, seq_off.data(), sizeof(int64_t) * (nseq + 1), cudaMemcpyHostToDevice, p->stream));
   PLAN_TRY(cudaMemcpyAsync(p->d_seq_len, len, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, p->stream));
@@ -276,6 +324,7 @@ extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   if (p->nseq == 0) { p->nnz = 0; return DAFS_CUDA_OK; }
   McArgs a;
   a.seq = p->d_seq; a.seq_off = p->d_seq_off; a.seq_len = p->d_seq_len; a.order = p->d_order; a.nseq = p->nseq;
+  a.cons_cls = p->d_cons; a.cons_prt = p->d_cons ? p->d_cons + p->seq_bytes : nullptr;
   a.W = p->W; a.th = p->th; a.tab = p->d_tab; a.ws = p->d_ws; a.ws_stride = p->ws_stride; a.cluster = p->cluster;
   a.row_off = p->d_row_off; a.row_ptr = p->d_row_ptr; a.pool_off = p->d_pool_off; a.pool_col = p->d_pool_col;
   a.pool_val = p->d_pool_val; a.seq_nnz = p->d_seq_nnz; a.seq_lnz = p->d_seq_lnz;
@@ -368,6 +417,20 @@ extern "C" void dafs_cuda_mccaskill_plan_destroy(dafs_mccaskill_plan* p) {
   if (p->stream) cudaStreamSynchronize(p->stream);
   dafs::free_mc_plan(p);
   delete p;
+}
+
+// RNAfold::calculate(seq, str, bp) for a batch (src/fold.cpp:118-166): one device, one call.
+extern "C" int dafs_cuda_mccaskill_constrained(int nseq, const char* const* seq, const int* len,
+                                               const char* const* str, float th, dafs_csr_batch* out) {
+  if (!out) return fail(DAFS_CUDA_EINVAL, "out is NULL");
+  *out = dafs_csr_batch{};
+  dafs_mccaskill_plan* p = nullptr;
+  int rc = dafs_cuda_mccaskill_plan_create_constrained(nseq, seq, len, str, th, &p);
+  if (rc) return rc;
+  rc = dafs_cuda_mccaskill_plan_run(p);
+  if (!rc) rc = dafs_cuda_mccaskill_plan_fetch(p, out, nullptr);
+  dafs_cuda_mccaskill_plan_destroy(p);
+  return rc;
 }
 
 // All sequences (src/fold.cpp:60-68).  ngpu > 1: sequences dealt round-robin by

@@ -53,6 +53,10 @@ struct McArgs {
   int cluster;                 // CTAs per sequence (= the launch's cluster size)
   int W;                       // row stride of the DP arrays = max n + 2
   float th;
+  const uint16_t* cons_cls;    // hard constraints (NULL: none), per nucleotide like seq: bit 15 = must stay
+                               // unpaired, bit 14 = has a given partner, low 14 bits = id of the loop of the
+                               // given pairs the position lies in; see mc_allowed
+  const uint16_t* cons_prt;    // 1-based partner of a position with a given pair, else 0
   const McTables* tab;         // in HBM; staged to shared memory by every CTA
   double* ws;                  // per-team workspace: MC_NARRAYS arrays of W*W doubles + MC_NROWS rows of W
   size_t ws_stride;            // doubles per team
@@ -110,6 +114,21 @@ struct McWs {
 };
 #define MC_NARRAYS 8
 #define MC_NROWS (14 + 96)   // q5 q3 | Aroll x3 Rroll x2 | plroll x2 prroll x2 tbroll x2 (+1 spare) | Vroll 3 x 32
+
+// Hard constraints (RNAfold::calculate(seq, str, bp), src/fold.cpp:118-166): ViennaRNA applies the
+// dot-bracket constraint by removing every pair that conflicts with it.  Pair (i,j) survives when it
+// is a given pair, or when both ends are unconstrained and lie in the same loop of the given pairs
+// (then no given pair separates them, i.e. none is crossed).
+struct McCons {
+  const uint16_t* cls;         // shared memory, 1-based; NULL = unconstrained
+  const uint16_t* prt;
+};
+__device__ __forceinline__ bool mc_allowed(const McCons& c, int i, int j) {
+  if (!c.cls) return true;
+  const unsigned ci = c.cls[i], cj = c.cls[j];
+  if (c.prt[i] == (uint16_t)j) return true;
+  return ((ci | cj) >> 14) == 0 && ci == cj;
+}
 
 // Per-CTA scheduling state in static shared memory.
 struct McSched {
@@ -170,7 +189,7 @@ __device__ __forceinline__ void mc_build_list(uint16_t* list, int ncell, McSched
 
 // Inside recursion over all spans for the current scale.  Z = q5[n] afterwards.
 template <int GL>
-__device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
+__device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& cons, int n, int W, const double* scale,
                           const double* mlb, const McCoef& cf, McSched& sc, uint16_t* lists, const McWs& w,
                           const McTeam& tm, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
@@ -200,7 +219,7 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
       const bool valid = e < ncell;
       const int i = valid ? (int)list[e] : 1;
       const int j = i + d;
-      const int type = valid ? mc_pair(S[i], S[j]) : 0;
+      const int type = (valid && mc_allowed(cons, i, j)) ? mc_pair(S[i], S[j]) : 0;
       const bool closes = (d > MC_TURN) && type != 0;
       const bool lead = valid && gl == 0;
       // operands of the group's epilogue, requested now so that their latency hides behind the sums
@@ -335,7 +354,7 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, int n, int W, con
     if (d + 1 < n) {
       const int dn = d + 1;
       mc_build_list(lists + (dn & 1) * W, n - dn, sc,
-                    [&](int i) { return dn <= MC_TURN || mc_pair(S[i], S[i + dn]) != 0; });
+                    [&](int i) { return dn <= MC_TURN || (mc_pair(S[i], S[i + dn]) != 0 && mc_allowed(cons, i, i + dn)); });
     }
     mc_sync(tm);
   }
@@ -513,7 +532,8 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
 
 namespace dafs {
 
-// Dynamic shared memory: McTables | McCoef | scale[W+2] | mlb[W+2] | lists[2][W] (uint16) | codes[W+8]
+// Dynamic shared memory: McTables | McCoef | scale[W+2] | mlb[W+2] | lists[2][W] (uint16) | codes[W+8] |
+// constraint classes[W+2], partners[W+2] (uint16)
 template <int GL>
 __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   extern __shared__ __align__(16) char smem[];
@@ -526,6 +546,8 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   double* mlb = scale + (a.W + 2);
   uint16_t* lists = reinterpret_cast<uint16_t*>(mlb + (a.W + 2));
   uint8_t* S = reinterpret_cast<uint8_t*>(lists + 2 * a.W);
+  uint16_t* s_cls = reinterpret_cast<uint16_t*>(S + ((a.W + 8 + 1) & ~1));
+  uint16_t* s_prt = s_cls + (a.W + 2);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x;
   McTeam tm;
   tm.nc = a.cluster;
@@ -558,6 +580,16 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     const int n = a.seq_len[s];
     const uint8_t* gs = a.seq + a.seq_off[s];
     for (int k = tid; k <= n + 1; k += NT) S[k] = (k >= 1 && k <= n) ? gs[k - 1] : (uint8_t)0;
+    McCons cons{nullptr, nullptr};
+    if (a.cons_cls) {
+      const uint16_t* gc = a.cons_cls + a.seq_off[s];
+      const uint16_t* gp = a.cons_prt + a.seq_off[s];
+      for (int k = tid; k <= n + 1; k += NT) {
+        const bool in = k >= 1 && k <= n;
+        s_cls[k] = in ? gc[k - 1] : (uint16_t)0; s_prt[k] = in ? gp[k - 1] : (uint16_t)0;
+      }
+      cons.cls = s_cls; cons.prt = s_prt;
+    }
     // ---- scale: start from ViennaRNA's default per-nucleotide guess and move to
     // exp(lnZ/n) when the first inside pass ends far from 1 (the reference takes
     // its pf_scale from an MFE run instead, fold.cpp:86-95; p does not depend on it)
@@ -574,7 +606,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
         cf.cbul[k] = k <= MC_MAXLOOP ? (double)T.bulge[k] * exp(-(double)(k + 2) * lns) : 0.0;
       }
       __syncthreads();
-      mc_inside<GL>(T, S, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
+      mc_inside<GL>(T, S, cons, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
       Z = w.q5[n];
       if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
       if (!(Z > 0.0)) { lns -= 0.25; continue; }

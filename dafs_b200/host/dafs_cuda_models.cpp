@@ -108,7 +108,18 @@ void CudaBoltzmann::calculate(const std::string& seq, BP& bp) {
   dafs_cuda_free_batch(&b);
 }
 
-void CudaBoltzmann::calculate(const std::string&, const std::string&, BP&) { throw "not supported"; }
+// RNAfold::calculate(seq, str, bp) (src/fold.cpp:118-166): the constraint goes to the device in the
+// reference's own alphabet ('?' free, '.' unpaired, '(' ')' a given pair)
+void CudaBoltzmann::calculate(const std::string& seq, const std::string& str, BP& bp) {
+  if (seq.size() != str.size()) throw std::string("constraint and sequence differ in length");
+  const char* s[1] = {seq.data()};
+  const char* c[1] = {str.data()};
+  const int len[1] = {(int)seq.size()};
+  dafs_csr_batch b;
+  if (dafs_cuda_mccaskill_constrained(1, s, len, c, threshold(), &b) != DAFS_CUDA_OK) fail("dafs_cuda_mccaskill_constrained");
+  unpack_unit(b, 0, bp);
+  dafs_cuda_free_batch(&b);
+}
 
 void CudaBoltzmann::calculate(const std::vector<Fasta>& fa, std::vector<BP>& bp) {
   const uint N = fa.size();

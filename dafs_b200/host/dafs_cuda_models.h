@@ -38,8 +38,7 @@ class CudaBoltzmann : public Fold::Model {
  public:
   explicit CudaBoltzmann(float th, int ngpu = 0);
   void calculate(const std::string& seq, BP& bp) override;
-  // constrained folding (--bp-update, --ipknot) is not offered on the device:
-  // throws "not supported" like AUXFold does (src/fold.cpp:220)
+  // constrained folding (--bp-update, --bp-update1, --ipknot): src/fold.cpp:118-166
   void calculate(const std::string& seq, const std::string& str, BP& bp) override;
   void calculate(const std::vector<Fasta>& fa, std::vector<BP>& bp) override;
 

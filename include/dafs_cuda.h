@@ -212,6 +212,19 @@ int dafs_cuda_mccaskill_all(int nseq, const char* const* seq, const int* len, fl
 typedef struct dafs_mccaskill_plan dafs_mccaskill_plan;
 int dafs_cuda_mccaskill_plan_create(int nseq, const char* const* seq, const int* len, float th,
                                     dafs_mccaskill_plan** plan);
+/* Constrained folding: RNAfold::calculate(seq, str, bp), src/fold.cpp:118-166 (what
+ * --bp-update / --bp-update1 / --ipknot reach through update_basepairing_probability,
+ * src/dafs.cpp:609-711).  str[i] is the constraint of sequence i in the reference's alphabet
+ * ('?' no constraint, '.' stays unpaired, '(' ')' a given pair; the reference rewrites it to
+ * ViennaRNA's '.', 'x', '(' ')' at :124-125), as long as the sequence; str == NULL or
+ * str[i] == NULL = unconstrained.  ViennaRNA's pf_fold applies such a constraint by removing
+ * the conflicting pairs: a '.' base pairs with nobody, the ends of a given pair pair with
+ * nobody else, and no pair crosses a given pair.                                        */
+int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char* const* seq, const int* len,
+                                                const char* const* str, float th,
+                                                dafs_mccaskill_plan** plan);
+int dafs_cuda_mccaskill_constrained(int nseq, const char* const* seq, const int* len,
+                                    const char* const* str, float th, dafs_csr_batch* out);
 int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* plan);
 int dafs_cuda_mccaskill_plan_sync(dafs_mccaskill_plan* plan, float* device_ms, int64_t* nnz);
 int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* plan, dafs_csr_batch* out, double* lnz);

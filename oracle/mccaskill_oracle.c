@@ -208,6 +208,43 @@ static double w_stem(const boltz_t* B, int type, int si1, int sj1, int multi) {
   return e;
 }
 
+/* ---- hard constraints (RNAfold::calculate(seq, str, bp), src/fold.cpp:118-166) --------------
+ * The reference maps its constraint string ('?' free, '.' must stay unpaired, '(' ')' a given
+ * pair) to ViennaRNA's ('.' free, 'x', '(' ')') and calls pf_fold with fold_constrained = 1.
+ * ViennaRNA applies such a dot-bracket constraint by REMOVING the pairs that conflict with it
+ * (x: the base pairs with nobody; '(' ')': the two bases pair with nobody else and no pair may
+ * cross theirs) -- it does not force the given pair to be present (no ENFORCE_BP in the legacy
+ * wrapper).  allow[(i-1)*n + (j-1)] = 1 when pair (i,j), i < j, survives.  Like the rest of this
+ * file this is a restatement without ViennaRNA at hand: parity unpinned. */
+static __thread const unsigned char* g_allow = NULL;
+static __thread int g_allow_n = 0;
+#define PAIR_TYPE(i, j) ((g_allow && !g_allow[(size_t)((i) - 1) * g_allow_n + ((j) - 1)]) ? 0 : k_pair[S[i]][S[j]])
+
+int oracle_mccaskill_mask(const char* str, int n, unsigned char* allow) {
+  int* partner = (int*)calloc(n + 2, sizeof(int));
+  int* stack = (int*)calloc(n + 2, sizeof(int));
+  int sp = 0;
+  for (int i = 1; i <= n; i++) {
+    if (str[i - 1] == '(') stack[sp++] = i;
+    else if (str[i - 1] == ')') { if (!sp) { free(partner); free(stack); return -1; } const int a = stack[--sp]; partner[a] = i; partner[i] = a; }
+  }
+  if (sp) { free(partner); free(stack); return -1; }
+  for (int i = 1; i <= n; i++)
+    for (int j = i + 1; j <= n; j++) {
+      int ok = str[i - 1] != '.' && str[j - 1] != '.';
+      if (partner[i] && partner[i] != j) ok = 0;
+      if (partner[j] && partner[j] != i) ok = 0;
+      for (int a = 1; a <= n && ok; a++) {
+        const int b = partner[a];
+        if (b <= a) continue;
+        if ((a < i && i < b && b < j) || (i < a && a < j && j < b)) ok = 0;
+      }
+      allow[(size_t)(i - 1) * n + (j - 1)] = (unsigned char)ok;
+    }
+  free(partner); free(stack);
+  return 0;
+}
+
 /* ---- exhaustive enumeration (short sequences) ------------------------------------
  * Sums the Boltzmann weights of every secondary structure (hairpins >= TURN,
  * interior loops <= MAXLOOP) by recursing over loops, independent of the DP
@@ -266,6 +303,7 @@ static void bf_rec(bf_t* b, int pos) {
   b->pt[pos] = 0;
   for (int j = pos + TURN + 1; j <= n; j++) {
     if (b->pt[j] != 0 || !k_pair[b->S[pos]][b->S[j]]) continue;
+    if (g_allow && !g_allow[(size_t)(pos - 1) * n + (j - 1)]) continue;
     /* non-crossing: positions < pos are all decided, so a decided position q in
      * (pos, j) is the right end of a pair opened before pos -- it would cross. */
     int ok = 1;
@@ -347,4 +385,27 @@ int oracle_mccaskill_csr(const char* seq, int n, float th, int32_t* row_ptr, uin
   row_ptr[n] = nnz;
   free(P);
   return nnz;
+}
+
+/* constrained variants: str as RNAfold::calculate(seq, str, bp) receives it */
+double oracle_mccaskill_constrained(const char* seq, const char* str, int n, double* P) {
+  if (!g_loaded) return NAN;
+  unsigned char* allow = (unsigned char*)calloc((size_t)n * n, 1);
+  if (oracle_mccaskill_mask(str, n, allow)) { free(allow); return NAN; }
+  g_allow = allow; g_allow_n = n;
+  const double lnz = n > 400 ? mccaskill_ld(seq, n, 1.35, NULL) : mccaskill_d(seq, n, 1.35, NULL);
+  const double r = mccaskill_d(seq, n, exp(lnz / n), P);
+  g_allow = NULL;
+  free(allow);
+  return r;
+}
+
+double oracle_mccaskill_bruteforce_constrained(const char* seq, const char* str, int n, double* P) {
+  unsigned char* allow = (unsigned char*)calloc((size_t)n * n, 1);
+  if (oracle_mccaskill_mask(str, n, allow)) { free(allow); return -1.0; }
+  g_allow = allow; g_allow_n = n;
+  const double z = oracle_mccaskill_bruteforce(seq, n, P);
+  g_allow = NULL;
+  free(allow);
+  return z;
 }

@@ -105,9 +105,12 @@ int main(int argc, char** argv) {
     BP bp0;
     gpu_s.calculate(fa[0].seq(), bp0);
     CHECK(same_sv(bp0, bp[0]), "CudaBoltzmann single != batch");
-    bool threw = false;
-    try { BP t; gpu_s.calculate(fa[0].seq(), std::string(fa[0].size(), '.'), t); } catch (...) { threw = true; }
-    CHECK(threw, "constrained overload must throw");
+    // the constrained overload (src/fold.cpp:118-166): '?' everywhere = unconstrained, '.' everywhere = no pair
+    BP bpq, bpx;
+    gpu_s.calculate(fa[0].seq(), std::string(fa[0].size(), '?'), bpq);
+    CHECK(same_sv(bpq, bp[0]), "CudaBoltzmann constrained with '?' only != unconstrained");
+    gpu_s.calculate(fa[0].seq(), std::string(fa[0].size(), '.'), bpx);
+    for (const auto& r : bpx) CHECK(r.empty(), "CudaBoltzmann constrained with '.' only kept a pair");
 
     // (3) decoders on the matrices DAFS would hand them
     const uint L1 = fa[0].size(), L2 = fa[1].size();

@@ -213,8 +213,28 @@ def _mc():
         L.oracle_mccaskill_bruteforce.restype = C.c_double
         L.oracle_mccaskill_bruteforce.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
         L.oracle_mccaskill_csr.argtypes = [C.c_char_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_mccaskill_constrained.restype = C.c_double
+        L.oracle_mccaskill_constrained.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_void_p]
+        L.oracle_mccaskill_bruteforce_constrained.restype = C.c_double
+        L.oracle_mccaskill_bruteforce_constrained.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_void_p]
         _mc_loaded = True
     return L
+
+
+def oracle_mccaskill_constrained(seq, con):
+    """Constrained variant (RNAfold::calculate(seq, str, bp)): con uses the reference's alphabet,
+    '?' free, '.' unpaired, '(' ')' a given pair."""
+    n = len(seq)
+    P = np.zeros((n, n), np.float64)
+    lnz = _mc().oracle_mccaskill_constrained(seq, con, n, P.ctypes.data)
+    return P, float(lnz)
+
+
+def oracle_mccaskill_bruteforce_constrained(seq, con):
+    n = len(seq)
+    P = np.zeros((n, n), np.float64)
+    Z = _mc().oracle_mccaskill_bruteforce_constrained(seq, con, n, P.ctypes.data)
+    return P, float(Z)
 
 
 def oracle_mccaskill(seq):

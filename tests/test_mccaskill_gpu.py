@@ -122,3 +122,73 @@ def test_repeatable(dafs):
                 first = cur
             else:
                 assert all(np.array_equal(x, y) for x, y in zip(first, cur)), rep
+
+
+def constrained_case(seq, frac_pairs=0.5, seed=0):
+    """A constraint in the reference's alphabet derived from the sequence's own likely structure:
+    some pairs of the unconstrained ensemble become '(' ')', a few other bases '.', the rest '?'
+    -- what update_basepairing_probability builds from a predicted structure (dafs.cpp:633-652)."""
+    r = np.random.default_rng(seed)
+    P, _ = ou.oracle_mccaskill(seq)
+    n = len(seq)
+    con = [b"?"] * n
+    used = np.zeros(n, bool)
+    order = np.dstack(np.unravel_index(np.argsort(-P, axis=None), P.shape))[0]
+    chosen = []
+    for i, j in order[:4 * n]:
+        if P[i, j] < 0.3:
+            break
+        if used[i] or used[j] or any((a < i < b < j) or (i < a < j < b) for a, b in chosen):
+            continue
+        if r.random() < frac_pairs:
+            chosen.append((i, j)); used[i] = used[j] = True
+            con[i], con[j] = b"(", b")"
+    for k in range(n):
+        if not used[k] and r.random() < 0.1:
+            con[k] = b"."
+    return b"".join(con)
+
+
+def check_constrained(dafs, seqs, cons, th=0.01):
+    worst = 0.0
+    with dafs.mccaskill_constrained(seqs, cons, th) as b:
+        for u, (s, c) in enumerate(zip(seqs, cons)):
+            n = len(s)
+            P, _ = ou.oracle_mccaskill(s) if c is None else ou.oracle_mccaskill_constrained(s, c)
+            rp, col, val = b.unit(u)
+            rows = np.repeat(np.arange(n), np.diff(rp))
+            G = np.zeros((n, n)); G[rows, col] = val
+            keep_o = P.astype(np.float32) > th
+            diff = np.abs(G - np.where(keep_o, P, 0.0))
+            near = np.abs(P - th) <= TOL
+            assert diff[~near].max(initial=0.0) <= TOL, (u, diff[~near].max())
+            worst = max(worst, np.abs(G - P)[G > 0].max(initial=0.0))
+    return worst
+
+
+def test_constrained_short_cases(dafs):
+    """Row f4 (src/fold.cpp:118-166): the cases of tests/test_oracle_mccaskill.py, where the restatement
+    equals exhaustive enumeration under the same constraint."""
+    cases = [(b"GGCGAAAGCCGCGAAAGCGCC", b"?????????????????????"), (b"GGCGAAAGCCGCGAAAGCGCC", b"((?????))????????????"),
+             (b"GGCGAAAGCCGCGAAAGCGCC", b"..???????????????????"), (b"GGCGAAAGCCGCGAAAGCGCC", b"(???????????????????)"),
+             (b"GCGGCAAAAGCCGCUUUUGCGC", b"??(????.?)??(?..??)???"), (b"GGGGACGGGGACGGGGACGG", b"?(??????????????)???"),
+             (b"GGGAAAUCCC", b"(((????)))"), (b"GGGAAAUCCC", None)]
+    seqs, cons = [c[0] for c in cases], [c[1] for c in cases]
+    assert check_constrained(dafs, seqs, cons, 0.001) <= TOL
+
+
+def test_constrained_rfam_and_random(dafs):
+    seqs = fasta_read(os.path.join(ROOT, "tests", "golden", "RF00005_0.fa"))[1][:5] + \
+        fasta_read(os.path.join(ROOT, "tests", "golden", "RF00017_4.fa"))[1][:3] + random_rna(2, 400, config_id=17)
+    seqs = [q if isinstance(q, bytes) else q.encode() for q in seqs]
+    cons = [constrained_case(q, seed=k) for k, q in enumerate(seqs)]
+    assert sum(c.count(b"(") for c in cons) >= 20
+    assert check_constrained(dafs, seqs, cons) <= TOL
+    # constraints change the answer: the same batch without them differs somewhere
+    with dafs.mccaskill_constrained(seqs, cons) as a, dafs.mccaskill_all(seqs) as b:
+        assert a.nnz != b.nnz or not np.array_equal(a.val, b.val)
+
+
+def test_constraint_rejected_when_unbalanced(dafs):
+    with pytest.raises(dafs.DafsCudaError):
+        dafs.mccaskill_constrained([b"GGGAAAUCCC"], [b"((??????)?"])

@@ -55,3 +55,33 @@ def test_self_golden():
         assert abs(lnz - c["lnz"]) < 1e-7 * max(1.0, abs(c["lnz"]))
         for i, j, p in c["top"]:
             assert abs(P[i, j] - p) < 1e-9
+
+
+CONSTRAINED = [
+    (b"GGCGAAAGCCGCGAAAGCGCC", b"?????????????????????"),      # no constraint at all
+    (b"GGCGAAAGCCGCGAAAGCGCC", b"((?????))????????????"),      # two given pairs
+    (b"GGCGAAAGCCGCGAAAGCGCC", b"..???????????????????"),      # two bases kept unpaired
+    (b"GGCGAAAGCCGCGAAAGCGCC", b"(???????????????????)"),      # one pair around everything
+    (b"GCGGCAAAAGCCGCUUUUGCGC", b"??(????.?)??(?..??)???"),    # pairs and unpaired bases
+    (b"GGGGACGGGGACGGGGACGG", b"?(??????????????)???"),        # a pair whose ends cannot pair (G-G): it still blocks crossings
+    (b"GGGAAAUCCC", b"(((????)))"),
+]
+
+
+@pytest.mark.parametrize("seq,con", CONSTRAINED)
+def test_constrained_dp_equals_constrained_enumeration(seq, con):
+    Pb, Z = ou.oracle_mccaskill_bruteforce_constrained(seq, con)
+    Pd, lnz = ou.oracle_mccaskill_constrained(seq, con)
+    assert abs(math.log(Z) - lnz) < 1e-9
+    assert np.abs(Pb - Pd).max() < 1e-12
+    n = len(seq)
+    for i in range(n):
+        if con[i:i + 1] == b".":
+            assert Pd[i, :].max() == 0 and Pd[:, i].max() == 0
+
+
+def test_free_constraint_is_the_unconstrained_ensemble():
+    s = random_rna(1, 80, config_id=21)[0]
+    P0, z0 = ou.oracle_mccaskill(s)
+    P1, z1 = ou.oracle_mccaskill_constrained(s, b"?" * len(s))
+    assert z0 == z1 and np.array_equal(P0, P1)
