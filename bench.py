@@ -197,7 +197,11 @@ def time_cpu(seqs, npairs, target_s, steps=1, warmup=0):
         first = (k * count) % max(1, npairs - count + 1)
         t0 = time.perf_counter(); run(seqs, first, count, cores); times.append(time.perf_counter() - t0)
     dt = sum(times) / len(times)
+    # what the reference itself does (src/align.cpp:41-51): one thread
+    n1 = int(min(npairs, 64))
+    t0 = time.perf_counter(); run(seqs, 0, n1, 1); t1 = time.perf_counter() - t0
     return {"value": count / dt, "unit": "pairs/s", "cores": cores, "kind": kind,
+            "single_thread_value": n1 / t1, "single_thread_sample": "%d pairs" % n1,
             "sample": "%d of %d pairs of the same N=%d L=%d list per step, %d host threads" % (count, npairs, NSEQ, LEN, cores)}, dt
 
 
@@ -327,9 +331,29 @@ def run_stages(rank, world, max_over_ranks, steps, with_cpu):
         if with_cpu and rank == 0:
             import oracle_util as ou
             k = min(cores, n) if L < 1000 else min(cores, n, 4)
-            dt, _ = cpu_threads(lambda q: ou.oracle_mccaskill(q)[1], seqs[:k], k)
+            dt, cnt = cpu_threads(ou.oracle_mccaskill_counted, seqs[:k], k)
             out[name]["cpu_baseline"] = {"value": k / dt, "unit": "sequences/s", "cores": k, "kind": "port",
                                          "sample": "%d sequences, one per host thread (FP64 restatement, parity unpinned)" % k}
+            # Roofline: algorithmic work = the FP64 multiplications and additions the
+            # reference algorithm (ViennaRNA's recursions as restated in oracle/) executes in its O(span)
+            # sums and interior-loop terms, COUNTED by the instrumented restatement on the sampled
+            # sequences; the kernel reaches the same numbers with fewer operations (O(n^2) exterior
+            # sums, O(30)-per-cell interior-loop recurrence), so this is work delivered, not issued.
+            flops_seq = float(np.mean([c[1] for c in cnt]))
+            peak64 = dafs_b200.fp64_probe()
+            ach = flops_seq * n / t / 1e12
+            traffic = None
+            try:
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "mccaskill_traffic.json"))).get(name)
+            except Exception:
+                pass
+            out[name]["roofline"] = {"bound": "fp64", "achieved": ach, "peak": peak64, "unit": "TFLOP/s", "frac": ach / peak64,
+                                     "flops_per_sequence_counted": flops_seq,
+                                     "flops_per_sequence_survey_estimate": 3.5 * L ** 3 + 1100.0 * L ** 2,
+                                     "traffic": traffic,
+                                     "note": "peak = DFMA rate measured by dafs_cuda_fp64_probe in this run; the stage is bound by "
+                                             "dependent-load latency and HBM traffic of the per-sequence DP arrays, not by the FP64 pipe "
+                                             "(profiles/r02_mccaskill_kernel_ncu.txt); traffic = dram bytes per launch from that ncu capture"}
     # ---- (4) consistency transformation on C4's sequences (next row) ----------
     # All pairs feed every relaxed pair, so this stage does not shard: rank 0 runs it (N = 1 only).
     if world == 1:
@@ -426,6 +450,9 @@ def run_stages(rank, world, max_over_ranks, steps, with_cpu):
                             and o["score"].view(np.uint32) == gd["score"].view(np.uint32))
                 out[name]["cpu_baseline"] = {"stage": "progressive (DAFS::align)", "value": t_cpu, "unit": "s", "cores": 1, "kind": kind,
                                              "device_s": t_dev, "identical_result": same,
+                                             "dd_iterations_sample": int(gd["total_iters"]),
+                                             # the reference's recursion on ALL sequences, scaled from the sample by DD iterations
+                                             "extrapolated_full_s": t_cpu * g["total_iters"] / max(1, int(gd["total_iters"])),
                                              "sample": "%d of the %d sequences, the reference's depth-first recursion on one core" % (ns, len(seqs))}
             data[1].close(); data[2].close()
     return out
@@ -618,6 +645,21 @@ def run_ours(args):
     if rank == 0:
         if stages:
             line["stages"] = stages
+            fam = stages.get("dafs_C4_family")
+            if fam and "cpu_baseline" in fam and "cpu_baseline" in line:
+                # BASELINE.json's acceptance figure: all-pairs posteriors + the DD (progressive alignment) stage
+                # at N=256, L=300 against the reference on the host cores.  Posteriors: this line's e2e against
+                # ProbCons::calculate on all cores; DD stage: dafs_cuda_progressive on the 256-sequence family
+                # (one GPU: the guide-tree recursion does not shard) against the reference's own recursion,
+                # measured on a 24-sequence sample and scaled to all sequences by DD iterations.
+                gpu_post, gpu_dd = line["e2e"]["ms_per_step"] * 1e-3, fam["stages_ms"]["progressive"] * 1e-3
+                cpu_post = len(pi) / line["cpu_baseline"]["value"]
+                cpu_dd = fam["cpu_baseline"]["extrapolated_full_s"]
+                line["north_star"] = {"what": "all-pairs posteriors + DD stage, N=256 L=300, %d GPU(s) vs %d host cores" % (world, line["cpu_baseline"]["cores"]),
+                                      "gpu_s": {"posteriors_e2e": gpu_post, "dd_stage": gpu_dd},
+                                      "cpu_s": {"posteriors_all_cores": cpu_post, "dd_stage_one_core_extrapolated": cpu_dd},
+                                      "ratio": (cpu_post + cpu_dd) / (gpu_post + gpu_dd),
+                                      "ratio_posteriors_only": cpu_post / gpu_post, "target": 50.0}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -19,6 +19,7 @@ from .capi import (  # noqa: F401
     all_pairs,
     device_count,
     fp32_probe,
+    fp64_probe,
     init,
     lib,
     library_path,

@@ -97,6 +97,15 @@ def fp32_probe():
     return a.value, b.value
 
 
+def fp64_probe():
+    """DFMA TFLOP/s measured on the current device."""
+    a = C.c_double(0)
+    L = lib()
+    L.dafs_cuda_fp64_probe.argtypes = [C.POINTER(C.c_double)]
+    _check(L.dafs_cuda_fp64_probe(C.byref(a)))
+    return a.value
+
+
 def _as_bytes(seqs):
     return [s.encode("ascii") if isinstance(s, str) else bytes(s) for s in seqs]
 

@@ -209,9 +209,51 @@ __global__ void __launch_bounds__(256) fp32_probe_kernel(float* out, float a, fl
   if (s == 12345.678f) out[0] = s;
 }
 
+// FP64 issue-rate probe (DFMA, 2 flop each), same shape: the denominator of the McCaskill roofline.
+__global__ void __launch_bounds__(256) fp64_probe_kernel(double* out, double a, double b, int iters) {
+  double v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = (double)(threadIdx.x + k) * 1e-3;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __fma_rn(v[k], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += v[k];
+  if (s == 12345.678) out[0] = s;
+}
+
 }  // namespace dafs
 
 extern "C" {
+
+int dafs_cuda_fp64_probe(double* fma_tflops) {
+  int dev = 0, sms = 0;
+  DAFS_CUDA_TRY(cudaGetDevice(&dev));
+  DAFS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  double* out = nullptr;
+  DAFS_CUDA_TRY(cudaMalloc(&out, 8));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int iters = 1 << 13, grid = sms * 8;
+  double best = 0;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(e0);
+    dafs::fp64_probe_kernel<<<grid, 256>>>(out, 0.999, 1e-3, iters);
+    cudaEventRecord(e1);
+    DAFS_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double tf = 2.0 * 8 * iters * 256.0 * grid / (ms * 1e-3) / 1e12;
+    if (rep && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(out);
+  DAFS_CUDA_TRY(cudaGetLastError());
+  if (fma_tflops) *fma_tflops = best;
+  return DAFS_CUDA_OK;
+}
 
 int dafs_cuda_fp32_probe(double* fma_tflops, double* muladd_tflops) {
   int dev = 0, sms = 0;

@@ -49,6 +49,8 @@ int dafs_cuda_device_count(void);
  * FFMA (2 flop each) and FMUL+FADD (the unfused arithmetic bit-exact parity
  * allows).  TFLOP/s, best of 3 after a warm-up launch.                          */
 int dafs_cuda_fp32_probe(double* fma_tflops, double* muladd_tflops);
+/* Same for FP64 (DFMA): the denominator of the McCaskill stage's roofline.        */
+int dafs_cuda_fp64_probe(double* fma_tflops);
 
 /* ---- sparse results ------------------------------------------------------
  * A batch of row-sparse matrices, one per unit (a sequence pair for (1), a

@@ -216,6 +216,10 @@ static double w_stem(const boltz_t* B, int type, int si1, int sj1, int multi) {
  * cross theirs) -- it does not force the given pair to be present (no ENFORCE_BP in the legacy
  * wrapper).  allow[(i-1)*n + (j-1)] = 1 when pair (i,j), i < j, survives.  Like the rest of this
  * file this is a restatement without ViennaRNA at hand: parity unpinned. */
+/* FP64 multiplications and additions of the O(span) sums and interior-loop terms executed by the
+ * last DP call of this thread (the instrumented count SURVEY.md 8(d) asks for; table look-ups,
+ * the O(1) epilogues and the read-out are not counted). */
+static __thread uint64_t g_flops = 0;
 static __thread const unsigned char* g_allow = NULL;
 static __thread int g_allow_n = 0;
 #define PAIR_TYPE(i, j) ((g_allow && !g_allow[(size_t)((i) - 1) * g_allow_n + ((j) - 1)]) ? 0 : k_pair[S[i]][S[j]])
@@ -368,8 +372,12 @@ double oracle_mccaskill_lnz(const char* seq, int n) {
 double oracle_mccaskill(const char* seq, int n, double* P) {
   if (!g_loaded) return NAN;
   const double lnz = n > 400 ? mccaskill_ld(seq, n, 1.35, NULL) : mccaskill_d(seq, n, 1.35, NULL);
+  g_flops = 0;
   return mccaskill_d(seq, n, exp(lnz / n), P);
 }
+
+/* counted flops of this thread's last oracle_mccaskill call (its final inside + outside pass) */
+double oracle_mccaskill_last_flops(void) { return (double)g_flops; }
 
 int oracle_mccaskill_csr(const char* seq, int n, float th, int32_t* row_ptr, uint32_t* col, float* val) {
   double* P = (double*)malloc(sizeof(double) * (size_t)n * n);
@@ -408,4 +416,15 @@ double oracle_mccaskill_bruteforce_constrained(const char* seq, const char* str,
   g_allow = NULL;
   free(allow);
   return z;
+}
+
+/* Inside + outside in double at the given sequence's own scale, returns the counted flops. */
+double oracle_mccaskill_count_flops(const char* seq, int n) {
+  if (!g_loaded) return NAN;
+  double* P = (double*)malloc(sizeof(double) * (size_t)n * n);
+  const double lnz = n > 400 ? mccaskill_ld(seq, n, 1.35, NULL) : mccaskill_d(seq, n, 1.35, NULL);
+  g_flops = 0;
+  mccaskill_d(seq, n, exp(lnz / n), P);
+  free(P);
+  return (double)g_flops;
 }

@@ -221,6 +221,24 @@ def _mc():
     return L
 
 
+def oracle_mccaskill_flops(seq):
+    """FP64 flops of the reference algorithm's sums on this sequence (instrumented restatement)."""
+    L = _mc()
+    L.oracle_mccaskill_count_flops.restype = C.c_double
+    L.oracle_mccaskill_count_flops.argtypes = [C.c_char_p, C.c_int]
+    return float(L.oracle_mccaskill_count_flops(seq, len(seq)))
+
+
+def oracle_mccaskill_counted(seq):
+    """(ln Z, counted flops) of one oracle_mccaskill call; safe in a thread pool (thread-local counter)."""
+    L = _mc()
+    L.oracle_mccaskill_last_flops.restype = C.c_double
+    n = len(seq)
+    P = np.zeros((n, n), np.float64)
+    lnz = L.oracle_mccaskill(seq, n, P.ctypes.data)
+    return float(lnz), float(L.oracle_mccaskill_last_flops())
+
+
 def oracle_mccaskill_constrained(seq, con):
     """Constrained variant (RNAfold::calculate(seq, str, bp)): con uses the reference's alphabet,
     '?' free, '.' unpaired, '(' ')' a given pair."""
