@@ -28,7 +28,7 @@ class _DDInfo(C.Structure):
     _fields_ = [("grid", C.c_int), ("block", C.c_int), ("cols_per_lane", C.c_int), ("smem_bytes", C.c_int),
                 ("ctas_per_sm", C.c_int), ("items_in_smem", C.c_uint), ("workspace_bytes", C.c_int64),
                 ("arena_bytes", C.c_int64), ("total_cbp", C.c_int64), ("total_entries", C.c_int64),
-                ("last_ms", C.c_float)]
+                ("last_ms", C.c_float), ("packed_on_device", C.c_int)]
 
 
 _proto_done = False

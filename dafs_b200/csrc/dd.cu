@@ -13,6 +13,7 @@
 
 #include "common.cuh"
 #include "dd_kernel.cuh"
+#include "dd_pack.cuh"
 
 namespace dafs {
 
@@ -36,6 +37,7 @@ struct ProbHost {
   std::vector<char> cst;                                       // the constant block
   size_t res_bytes = 0;
   size_t cst_base = 0, res_base = 0;                           // position in the plan's buffers
+  size_t cst_bytes_dev = 0;                                    // block size when the block is built on the device (cst stays empty)
 };
 
 static size_t up16(size_t x) { return (x + 15) & ~size_t(15); }
@@ -308,6 +310,48 @@ static int build_problem(const dafs_dd_problem& q, bool want_trace, ProbHost& H)
   return DAFS_CUDA_OK;
 }
 
+// Offsets of every section of a problem's constant block from its counts alone: the same sequence of
+// put() calls as pack_nus() / build_problem() above (16-byte alignment, at least one element each).
+static void layout_nus(size_t& cur, DDNusHdr& h, int L, int n, int nd, int nI, int nJ, float w) {
+  auto sect = [&](size_t elem, size_t cnt) { const size_t off = up16(cur); cur = off + elem * std::max<size_t>(cnt, 1); return (uint32_t)off; };
+  h = DDNusHdr{};
+  h.L = L; h.n = n; h.nd = nd; h.nI = nI; h.nJ = nJ; h.w = w;
+  h.col_ptr = sect(4, (size_t)nJ + 1); h.row_ptr = sect(4, (size_t)nI + 1); h.row_ent = sect(4, nd);
+  h.ent_ab = sect(4, nd); h.ent_c = sect(4, nd); h.ent_ij = sect(4, n); h.ent_p = sect(4, n); h.ent_flag = sect(1, n);
+  h.rowI = sect(2, nI); h.colJ = sect(2, nJ); h.bstart = sect(2, nI); h.rowmap = sect(2, (size_t)L + 1); h.colmap = sect(2, (size_t)L + 1);
+}
+
+static void layout_problem(const dafs_dd_problem& q, const PackCounts& c, bool want_trace, ProbHost& H, DDHdr& h) {
+  const int L1 = q.L1, L2 = q.L2;
+  const unsigned N1 = (unsigned)q.N1, N2 = (unsigned)q.N2;
+  const float wx = q.w * 2 * N1 / (N1 + N2), wy = q.w * 2 * N2 / (N1 + N2);   // dafs.cpp:1091-1092
+  H = ProbHost();
+  H.L1 = L1; H.L2 = L2; H.t_max = q.t_max; H.ncbp = c.ncbp; H.nb = c.nb; H.bw = c.bw; H.ncz = c.ncz;
+  h = DDHdr{};
+  size_t cur = sizeof(DDHdr), res = 0;
+  layout_nus(cur, H.sx.h, L1, c.n_x, c.nd_x, c.nI_x, c.nJ_x, wx);
+  H.sx.max_col = c.maxcol_x; H.sx.out = up16(res); res = H.sx.out + sizeof(uint32_t) * L1;
+  layout_nus(cur, H.sy.h, L2, c.n_y, c.nd_y, c.nI_y, c.nJ_y, wy);
+  H.sy.max_col = c.maxcol_y; H.sy.out = up16(res); res = H.sy.out + sizeof(uint32_t) * L2;
+  auto sect = [&](size_t elem, size_t cnt) { const size_t off = up16(cur); cur = off + elem * std::max<size_t>(cnt, 1); return (uint32_t)off; };
+  h.z_env = sect(8, (size_t)L1 + 1); h.z_boff = sect(4, (size_t)L1 + 2); h.z_pb = sect(4, c.nb);
+  h.cz_row_ptr = sect(4, (size_t)L1 + 1); h.cz_col = sect(2, c.ncz); h.cz_bidx = sect(4, c.ncz);
+  cur = up16(cur);
+  h.stage = (int)cur; H.stage = h.stage;
+  h.cbp = sect(16, c.ncbp);
+  cur = up16(cur);
+  h.L1 = L1; h.L2 = L2; h.nb = c.nb; h.ncz = c.ncz; h.ncbp = c.ncbp; h.t_max = q.t_max;
+  h.bytes = (int)cur;
+  h.th_s = q.th_s; h.th_a = q.th_a; h.eta0 = q.eta0;
+  h.x = H.sx.h; h.y = H.sy.h;
+  H.cst_bytes_dev = cur;
+  H.z_out = up16(res); res = H.z_out + sizeof(uint32_t) * L1;
+  H.result = up16(res); res = H.result + 64;
+  H.trace = up16(res);
+  if (want_trace) res = H.trace + sizeof(float) * 3 * (size_t)std::max(q.t_max, 0);
+  H.res_bytes = up16(res);
+}
+
 }  // namespace dafs
 
 // ---- plan ---------------------------------------------------------------------
@@ -333,6 +377,7 @@ struct dafs_dd_plan {
   char* poll_stage = nullptr;              // pinned, res_bytes
   int64_t total_cbp = 0, total_entries = 0;
   bool launched = false;
+  bool packed_on_device = false;
   float last_ms = 0;
 };
 
@@ -420,8 +465,10 @@ static cudaError_t dd_allow_smem(const void* fn, bool smem, int team, int device
 }
 }  // namespace dafs
 
-extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
-                                        dafs_dd_plan** out) {
+// device_inputs: p_x / p_y / p_z of every problem are DEVICE pointers and the constant blocks are
+// built by dd_pack_count / dd_pack_fill (dd_pack.cuh) instead of build_problem() on the host cores.
+static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_trace, bool device_inputs,
+                               dafs_dd_plan** out) {
   using namespace dafs;
   if (!out) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
   *out = nullptr;
@@ -454,9 +501,53 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   PLAN_TRY(dev_malloc(&p->d_queue, sizeof(int)));
   if (nprob == 0) { *out = p; return DAFS_CUDA_OK; }
 
-  // per-problem setup on the host cores (independent problems)
   p->host.resize(nprob);
-  {
+  p->packed_on_device = device_inputs;
+  // device path: scratch + problem descriptors, count kernel, totals back (64 bytes per problem)
+  char* d_scratch = nullptr; PackProb* d_pp = nullptr; PackCounts* d_counts = nullptr; DDHdr* d_hdr = nullptr;
+  std::vector<PackProb> pp;
+  std::vector<DDHdr> hdr;
+  auto pack_free = [&]() { dev_free(d_scratch); dev_free(d_pp); dev_free(d_counts); dev_free(d_hdr); d_scratch = nullptr; d_pp = nullptr; d_counts = nullptr; d_hdr = nullptr; };
+  auto bail_pack = [&](int rc) { pack_free(); return bail(rc); };
+#define PACK_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return bail_pack(fail(e_ == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM : DAFS_CUDA_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_))); } while (0)
+  if (device_inputs) {
+    pp.resize(nprob); hdr.resize(nprob);
+    size_t sc = 0;
+    std::vector<size_t> sc_off(nprob);
+    for (int k = 0; k < nprob; ++k) { sc_off[k] = sc; sc += pack_scratch_bytes(prob[k].L1, prob[k].L2); }
+    PACK_TRY(dev_malloc(&d_scratch, std::max<size_t>(sc, 256)));
+    PACK_TRY(dev_malloc(&d_pp, sizeof(PackProb) * nprob));
+    PACK_TRY(dev_malloc(&d_counts, sizeof(PackCounts) * nprob));
+    PACK_TRY(dev_malloc(&d_hdr, sizeof(DDHdr) * nprob));
+    for (int k = 0; k < nprob; ++k) {
+      const dafs_dd_problem& q = prob[k];
+      PackProb& P = pp[k];
+      const unsigned N1 = (unsigned)q.N1, N2 = (unsigned)q.N2;
+      P.L1 = q.L1; P.L2 = q.L2; P.N1 = N1; P.N2 = N2; P.p_x = q.p_x; P.p_y = q.p_y; P.p_z = q.p_z;
+      P.w = q.w; P.wx = q.w * 2 * N1 / (N1 + N2); P.wy = q.w * 2 * N2 / (N1 + N2);
+      P.th_s = q.th_s; P.min_th_s = q.min_th_s; P.th_a = q.th_a;
+      P.scratch = d_scratch + sc_off[k]; P.block = nullptr; P.hdr = nullptr;
+    }
+    std::vector<PackCounts> counts(nprob);
+    PACK_TRY(cudaMemcpyAsync(d_pp, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
+    int maxL = 1;
+    for (int k = 0; k < nprob; ++k) maxL = std::max(maxL, std::max(prob[k].L1, prob[k].L2));
+    const dim3 rgrid((maxL + DD_PACK_ROWS - 1) / DD_PACK_ROWS, nprob);
+    const size_t env_smem = (size_t)(maxL + 1) * sizeof(uint2) <= 96 * 1024 ? (size_t)(maxL + 1) * sizeof(uint2) : 0;
+    if (env_smem > 48 * 1024) PACK_TRY(cudaFuncSetAttribute(dd_pack_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)env_smem));
+    dd_pack_gates<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+    dd_pack_cbp<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+    dd_pack_classify<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+    dd_pack_scan<<<nprob, DD_PACK_THREADS, env_smem, p->stream>>>(d_pp, d_counts);
+    PACK_TRY(cudaGetLastError());
+    PACK_TRY(cudaMemcpyAsync(counts.data(), d_counts, sizeof(PackCounts) * nprob, cudaMemcpyDeviceToHost, p->stream));
+    PACK_TRY(cudaStreamSynchronize(p->stream));
+    for (int k = 0; k < nprob; ++k) {
+      if (counts[k].n_x > 65535 * 8 || counts[k].ncz > (1 << 28)) return bail_pack(fail(DAFS_CUDA_EINVAL, "problem %d is too dense", k));
+      layout_problem(prob[k], counts[k], p->want_trace, p->host[k], hdr[k]);
+    }
+  } else {
+    // per-problem setup on the host cores (independent problems)
     std::atomic<int> next(0);
     const int nt = (int)std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)nprob));
     auto work = [&]() { for (;;) { const int k = next.fetch_add(1); if (k >= nprob) break; build_problem(prob[k], p->want_trace, p->host[k]); } };
@@ -466,7 +557,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   DDMaxima m;
   size_t cst = 0, res = 0;
   for (auto& H : p->host) {
-    H.cst_base = cst; cst += H.cst.size(); cst = (cst + 255) & ~size_t(255);
+    H.cst_base = cst; cst += device_inputs ? H.cst_bytes_dev : H.cst.size(); cst = (cst + 255) & ~size_t(255);
     H.res_base = res; res += H.res_bytes;
     m.L1 = std::max(m.L1, H.L1); m.L2 = std::max(m.L2, H.L2);
     m.nx = std::max(m.nx, H.sx.h.n); m.ny = std::max(m.ny, H.sy.h.n);
@@ -482,7 +573,49 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
   PLAN_TRY(dev_malloc(&p->d_res, std::max<size_t>(res, 256)));
   PLAN_TRY(dev_malloc(&p->d_prob, sizeof(DDProbRef) * nprob));
   PLAN_TRY(dev_malloc(&p->d_order, sizeof(int32_t) * nprob));
-  {
+  if (device_inputs) {
+    // blocks start as zeros (the host packer's padding bytes are zeros), then every section is written in place
+    PACK_TRY(cudaMemsetAsync(p->d_cst, 0, std::max<size_t>(cst, 256), p->stream));
+    for (int k = 0; k < nprob; ++k) { pp[k].block = p->d_cst + p->host[k].cst_base; pp[k].hdr = d_hdr + k; }
+    PACK_TRY(cudaMemcpyAsync(d_pp, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
+    PACK_TRY(cudaMemcpyAsync(d_hdr, hdr.data(), sizeof(DDHdr) * nprob, cudaMemcpyHostToDevice, p->stream));
+    {
+      int maxL = 1;
+      for (int k = 0; k < nprob; ++k) maxL = std::max(maxL, std::max(prob[k].L1, prob[k].L2));
+      const dim3 rgrid((maxL + DD_PACK_ROWS - 1) / DD_PACK_ROWS, nprob);
+      dd_pack_head<<<nprob, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+      dd_pack_entries<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+      dd_pack_rows<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+    }
+    PACK_TRY(cudaGetLastError());
+    PACK_TRY(cudaStreamSynchronize(p->stream));       // pp / hdr go out of scope; the caller may reuse the matrices
+    if (const char* e = getenv("DAFS_DD_PACK_VERIFY")) {
+      if (atoi(e) > 0) {
+        // test hook: the device-built blocks must equal the host packer's, byte for byte
+        std::vector<char> dev(cst);
+        PACK_TRY(cudaMemcpy(dev.data(), p->d_cst, cst, cudaMemcpyDeviceToHost));
+        for (int k = 0; k < nprob; ++k) {
+          const dafs_dd_problem& q = prob[k];
+          std::vector<float> hx((size_t)q.L1 * q.L1), hy((size_t)q.L2 * q.L2), hz((size_t)q.L1 * q.L2);
+          PACK_TRY(cudaMemcpy(hx.data(), q.p_x, sizeof(float) * hx.size(), cudaMemcpyDeviceToHost));
+          PACK_TRY(cudaMemcpy(hy.data(), q.p_y, sizeof(float) * hy.size(), cudaMemcpyDeviceToHost));
+          PACK_TRY(cudaMemcpy(hz.data(), q.p_z, sizeof(float) * hz.size(), cudaMemcpyDeviceToHost));
+          dafs_dd_problem hq = q;
+          hq.p_x = hx.data(); hq.p_y = hy.data(); hq.p_z = hz.data();
+          ProbHost ref;
+          build_problem(hq, p->want_trace, ref);
+          const ProbHost& H = p->host[k];
+          if (ref.cst.size() != H.cst_bytes_dev || ref.res_bytes != H.res_bytes)
+            return bail_pack(fail(DAFS_CUDA_ECUDA, "pack verify: problem %d: block %zu bytes on the device, %zu on the host", k, H.cst_bytes_dev, ref.cst.size()));
+          for (size_t c = 0; c < ref.cst.size(); ++c)
+            if (ref.cst[c] != dev[H.cst_base + c])
+              return bail_pack(fail(DAFS_CUDA_ECUDA, "pack verify: problem %d: block byte %zu differs (device %d, host %d; stage %d, bytes %zu)", k, c,
+                                    (int)(unsigned char)dev[H.cst_base + c], (int)(unsigned char)ref.cst[c], H.stage, ref.cst.size()));
+        }
+      }
+    }
+    pack_free();
+  } else {
     // one pinned staging buffer -> one H2D copy
     char* stage = (char*)pinned_alloc(std::max<size_t>(cst, 256));
     if (!stage) return bail(fail(DAFS_CUDA_ENOMEM, "pinned staging of %zu bytes failed", cst));
@@ -492,6 +625,7 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
     pinned_free(stage);
     PLAN_TRY(e);
   }
+#undef PACK_TRY
   std::vector<DDProbRef> dp(nprob);
   std::vector<int32_t> order(nprob);
   for (int k = 0; k < nprob; ++k) {
@@ -553,6 +687,46 @@ extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, 
 #undef PLAN_TRY
   *out = p;
   return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_dd_plan_create_device(int nprob, const dafs_dd_problem* prob, int want_trace,
+                                               dafs_dd_plan** out) {
+  return dd_plan_create_impl(nprob, prob, want_trace, true, out);
+}
+
+extern "C" int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
+                                        dafs_dd_plan** out) {
+  const char* e = getenv("DAFS_DD_DEVICE_PACK");
+  if (!(e && atoi(e) > 0) || nprob <= 0 || !prob || !out) return dd_plan_create_impl(nprob, prob, want_trace, false, out);
+  // test hook: the same call with the set-up on the device -- the matrices are uploaded as they are and
+  // the constant blocks built by the pack kernels
+  using namespace dafs;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return dd_plan_create_impl(nprob, prob, want_trace, false, out); }
+  size_t tot = 0;
+  for (int k = 0; k < nprob; ++k) {
+    const dafs_dd_problem& q = prob[k];
+    if (q.L1 < 1 || q.L2 < 1 || q.L1 > kMaxL || q.L2 > kMaxL || !q.p_x || !q.p_y || !q.p_z) return dd_plan_create_impl(nprob, prob, want_trace, false, out);
+    tot += (size_t)q.L1 * q.L1 + (size_t)q.L2 * q.L2 + (size_t)q.L1 * q.L2;
+  }
+  float* d = nullptr;
+  DAFS_CUDA_TRY(dev_malloc(&d, sizeof(float) * std::max<size_t>(tot, 1)));
+  std::vector<dafs_dd_problem> dq(prob, prob + nprob);
+  size_t off = 0;
+  cudaError_t err = cudaSuccess;
+  for (int k = 0; k < nprob && err == cudaSuccess; ++k) {
+    const dafs_dd_problem& q = prob[k];
+    const size_t nx = (size_t)q.L1 * q.L1, ny = (size_t)q.L2 * q.L2, nz = (size_t)q.L1 * q.L2;
+    err = cudaMemcpy(d + off, q.p_x, sizeof(float) * nx, cudaMemcpyHostToDevice); dq[k].p_x = d + off; off += nx;
+    if (err == cudaSuccess) err = cudaMemcpy(d + off, q.p_y, sizeof(float) * ny, cudaMemcpyHostToDevice);
+    dq[k].p_y = d + off; off += ny;
+    if (err == cudaSuccess) err = cudaMemcpy(d + off, q.p_z, sizeof(float) * nz, cudaMemcpyHostToDevice);
+    dq[k].p_z = d + off; off += nz;
+  }
+  int rc = err == cudaSuccess ? dd_plan_create_impl(nprob, dq.data(), want_trace, true, out)
+                              : fail(DAFS_CUDA_ECUDA, "upload of the dense matrices failed: %s", cudaGetErrorString(err));
+  dev_free(d);
+  return rc;
 }
 
 extern "C" int dafs_cuda_dd_plan_run(dafs_dd_plan* p) {
@@ -663,6 +837,7 @@ extern "C" int dafs_cuda_dd_plan_info(dafs_dd_plan* p, dafs_dd_info* info) {
   info->workspace_bytes = (int64_t)p->lay.ws_stride * p->grid;
   info->arena_bytes = (int64_t)(p->cst_bytes + p->res_bytes);
   info->total_cbp = p->total_cbp; info->total_entries = p->total_entries; info->last_ms = p->last_ms;
+  info->packed_on_device = p->packed_on_device ? 1 : 0;
   return DAFS_CUDA_OK;
 }
 

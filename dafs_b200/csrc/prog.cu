@@ -365,6 +365,7 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   float root_score = 0.0f;
   int batches = 0, built = 0;
   const bool verbose = getenv("DAFS_PROG_VERBOSE") != nullptr;
+  const bool host_pack = [] { const char* e = getenv("DAFS_PROG_HOST_PACK"); return e && atoi(e) > 0; }();
   double tm_sum[12] = {0}, tm_max[12] = {0};   // host phases: prep, averaging, plan create, plan run, poll, finish
   auto lap = [&](int k, double t_from) { const double d = now_ms() - t_from; tm_sum[k] += d; tm_max[k] = std::max(tm_max[k], d); return now_ms(); };
   // a solved node: merge the children (project_alignment), record, maybe release the parent
@@ -482,22 +483,27 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
       DAFS_CUDA_TRY(cudaGetLastError());
       DAFS_CUDA_TRY(cudaEventRecord(G.b, st));
       tl = lap(7, tl);
-      // the dense averages are read once, by dafs_cuda_dd_plan_create below, so every batch lands in
-      // the same page-locked buffer; cudaHostAlloc waits for running kernels (51 ms behind a long DD
-      // batch), so it is sized generously by the first batch, which runs with nothing in flight
-      if (dense_cap < (size_t)dense) {
-        if (dense_pin.p) { dafs::pinned_free(dense_pin.p); dense_pin.p = nullptr; }
-        dense_cap = (size_t)dense + (size_t)dense / 2;
-        dense_pin.p = pinned_alloc(sizeof(float) * dense_cap);
-        if (!dense_pin.p) { dense_cap = 0; return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %lld floats failed", (long long)dense); }
+      // The dense averages stay in HBM: the batch's DD plan is built from them by the pack kernels
+      // (dafs_cuda_dd_plan_create_device: CBP enumeration, envelope, packing).  DAFS_PROG_HOST_PACK=1 keeps
+      // the earlier route for A/B runs: one D2H of the batch's matrices into a page-locked buffer that every
+      // batch shares (cudaHostAlloc waits for running kernels, so it is sized generously by the first batch,
+      // which runs with nothing in flight), set-up on the host cores.
+      float* h_dense = nullptr;
+      if (host_pack) {
+        if (dense_cap < (size_t)dense) {
+          if (dense_pin.p) { dafs::pinned_free(dense_pin.p); dense_pin.p = nullptr; }
+          dense_cap = (size_t)dense + (size_t)dense / 2;
+          dense_pin.p = pinned_alloc(sizeof(float) * dense_cap);
+          if (!dense_pin.p) { dense_cap = 0; return fail(DAFS_CUDA_ENOMEM, "pinned allocation of %lld floats failed", (long long)dense); }
+        }
+        tl = lap(8, tl);
+        h_dense = static_cast<float*>(dense_pin.p);
+        DAFS_CUDA_TRY(cudaMemcpyAsync(h_dense, d_dense, sizeof(float) * (size_t)dense, cudaMemcpyDeviceToHost, st));
+        DAFS_CUDA_TRY(cudaStreamSynchronize(st));
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, G.a, G.b);
+        ms_avg += ms;
       }
-      tl = lap(8, tl);
-      float* h_dense = static_cast<float*>(dense_pin.p);
-      DAFS_CUDA_TRY(cudaMemcpyAsync(h_dense, d_dense, sizeof(float) * (size_t)dense, cudaMemcpyDeviceToHost, st));
-      DAFS_CUDA_TRY(cudaStreamSynchronize(st));
-      float ms = 0.0f;
-      cudaEventElapsedTime(&ms, G.a, G.b);
-      ms_avg += ms;
       tl = lap(1, tl);
       // the batch's DD problems, one asynchronous launch (solve_by_dd, :1006-1295)
       Bt.t0 = now_ms();
@@ -509,7 +515,8 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
         const ProgSide& S2 = sides[2 * q + 1];
         dafs_dd_problem& P = Bt.prob[q];
         P.L1 = S1.L; P.L2 = S2.L; P.N1 = S1.rows; P.N2 = S2.rows;
-        P.p_x = h_dense + S1.out; P.p_y = h_dense + S2.out; P.p_z = h_dense + nodes[q].out;
+        const float* base = host_pack ? h_dense : d_dense;
+        P.p_x = base + S1.out; P.p_y = base + S2.out; P.p_z = base + nodes[q].out;
         P.w = prm->w; P.th_s = prm->th_s; P.min_th_s = prm->min_th_s; P.th_a = prm->th_a; P.eta0 = prm->eta0; P.t_max = prm->t_max;
         Bt.xs[q].assign(S1.L, kNone); Bt.ys[q].assign(S2.L, kNone); Bt.zs[q].assign(S1.L, kNone);
         Bt.res[q] = dafs_dd_result{};
@@ -523,7 +530,15 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
         }
         Bt.stream = pool.idle.back(); pool.idle.pop_back();
         g_dd_stream = Bt.stream; g_dd_poll_stream = pool.poll;
-        int rc = dafs_cuda_dd_plan_create(W, Bt.prob.data(), 0, &Bt.plan.p);
+        int rc;
+        if (host_pack) rc = dafs_cuda_dd_plan_create(W, Bt.prob.data(), 0, &Bt.plan.p);
+        else {
+          // the pack kernels run on the batch's stream, behind the averaging kernels; the call returns when
+          // the blocks are built, so the arena that holds the matrices is free for the next batch
+          DAFS_CUDA_TRY(cudaStreamWaitEvent(Bt.stream, G.b, 0));
+          rc = dafs_cuda_dd_plan_create_device(W, Bt.prob.data(), 0, &Bt.plan.p);
+          if (!rc) { float ms = 0.0f; cudaEventElapsedTime(&ms, G.a, G.b); ms_avg += ms; }
+        }
         g_dd_stream = nullptr; g_dd_poll_stream = nullptr;
         tl = lap(2, tl);
         if (!rc) rc = dafs_cuda_dd_plan_run(Bt.plan.p);

@@ -284,6 +284,13 @@ int dafs_cuda_dd_solve_batch(int nprob, const dafs_dd_problem* prob, dafs_dd_res
 typedef struct dafs_dd_plan dafs_dd_plan;
 int dafs_cuda_dd_plan_create(int nprob, const dafs_dd_problem* prob, int want_trace,
                              dafs_dd_plan** plan);
+/* The same plan from matrices that are already in HBM: p_x / p_y / p_z of every problem are DEVICE
+ * pointers (e.g. the averaged matrices of guide-tree nodes, which dafs_cuda_progressive builds on
+ * the device).  CBP enumeration (:1016-1061), the NW envelope and all packing run in two kernels;
+ * the host sees 64 bytes of counts per problem.  The matrices may be reused once the call returns.
+ * The resulting plan is byte-identical to the one dafs_cuda_dd_plan_create builds.            */
+int dafs_cuda_dd_plan_create_device(int nprob, const dafs_dd_problem* prob, int want_trace,
+                                    dafs_dd_plan** plan);
 int dafs_cuda_dd_plan_run(dafs_dd_plan* plan);
 int dafs_cuda_dd_plan_sync(dafs_dd_plan* plan, float* device_ms);
 int dafs_cuda_dd_plan_fetch(dafs_dd_plan* plan, dafs_dd_result* res);
@@ -303,6 +310,7 @@ typedef struct dafs_dd_info {
   int64_t arena_bytes;             /* per-problem device data                       */
   int64_t total_cbp, total_entries;
   float last_ms;
+  int packed_on_device;            /* 1: the constant blocks were built by the pack kernels */
 } dafs_dd_info;
 int dafs_cuda_dd_plan_info(dafs_dd_plan* plan, dafs_dd_info* info);
 
