@@ -804,13 +804,27 @@ __global__ void __launch_bounds__(32 * (2 * T + 1)) dd_kernel(const DDArgs a) {
         }
       }
       __syncthreads();
-      // ---- Lagrangian value, summed in CBP order by one thread (:1090-1111) ----
-      if (tid == NT - 1) {
+      // ---- Lagrangian value, summed in CBP order (:1090-1111) ----
+      // The reference adds only the positive s_w, one after the other.  The last warp walks the list 32
+      // entries at a time and chains an addition per POSITIVE entry (in order, broadcast by shuffle):
+      // the serial part is as long as the number of violated candidates, not as the list (2 112 CBPs at
+      // the root of RF00017 cost 100 k cycles per iteration with one thread reading every entry).
+      if (tid >= NT - 32) {
+        const int ln = tid & 31;
         float s = __fadd_rn(0.0f, sh.part[0]);
         s = __fadd_rn(s, sh.part[1]);
         s = __fadd_rn(s, sh.part[2]);
-        for (int u = 0; u < ncbp; ++u) { const float v = sw[u]; if (v > 0.0f) s = __fadd_rn(s, v); }
-        sh.s = s;
+        for (int base = 0; base < ncbp; base += 32) {
+          const int u = base + ln;
+          const float v = u < ncbp ? sw[u] : 0.0f;
+          unsigned m = __ballot_sync(0xffffffffu, v > 0.0f);
+          while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            s = __fadd_rn(s, __shfl_sync(0xffffffffu, v, b));
+          }
+        }
+        if (ln == 31) sh.s = s;
       }
       // ---- multiplier updates (:1121-1254) -----------------------------------------
       const float eta = sh.eta;
