@@ -192,3 +192,25 @@ def test_constrained_rfam_and_random(dafs):
 def test_constraint_rejected_when_unbalanced(dafs):
     with pytest.raises(dafs.DafsCudaError):
         dafs.mccaskill_constrained([b"GGGAAAUCCC"], [b"((??????)?"])
+
+
+VIENNA_GOLD = os.path.join(ROOT, "tests", "golden", "mccaskill_golden.json")
+
+
+@pytest.mark.skipif(not os.path.exists(VIENNA_GOLD), reason="no ViennaRNA-generated golden file (tools/pin_mccaskill.sh makes it where RNAlib2 2.4.18 exists)")
+def test_vienna_golden(dafs):
+    """The pin of path (2): RNAfold(bl = true)::calculate of the reference itself, where somebody could run it."""
+    import json
+    cases = json.load(open(VIENNA_GOLD))["cases"]
+    seqs = [c["seq"].encode() for c in cases]
+    cons = [None if c["con"] is None else c["con"].encode() for c in cases]
+    with dafs.mccaskill_constrained(seqs, cons, 0.01) as b:
+        for u, c in enumerate(cases):
+            n = len(c["seq"])
+            rp, col, val = b.unit(u)
+            G = np.zeros((n, n)); G[np.repeat(np.arange(n), np.diff(rp)), col] = val
+            R = np.zeros((n, n))
+            for i, j, p in c["bp"]:
+                R[i, j] = p
+            near = (np.abs(G - 0.01) <= TOL) | (np.abs(R - 0.01) <= TOL)
+            assert np.abs(G - R)[~near].max(initial=0.0) <= TOL, (u, np.abs(G - R).max())
