@@ -14,7 +14,8 @@ namespace {
 
 struct DevBufs {                       // everything dev_malloc'ed by one call
   std::vector<void*> p;
-  ~DevBufs() { for (void* q : p) dafs::dev_free(q); }
+  cudaStream_t stream = nullptr;        // kernels of the call run here: wait for them before the buffers go back to the cache (error returns)
+  ~DevBufs() { if (stream) cudaStreamSynchronize(stream); for (void* q : p) dafs::dev_free(q); }
   template <class T> cudaError_t get(T** out, size_t count) {
     void* q = nullptr;
     const cudaError_t e = dafs::dev_malloc(&q, std::max<size_t>(count * sizeof(T), 256));
@@ -187,11 +188,17 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   const int64_t mp_nnz = npairs ? mp->nz_off[npairs] : 0, bp_nnz = bp->nz_off[n];
   if (mp_nnz < 0 || bp_nnz < 0 || mp_nnz != mp->nnz || bp_nnz != bp->nnz) return fail(DAFS_CUDA_EINVAL, "nnz does not match nz_off");
 
+  // the outputs are handed over only by a successful return: any error path frees what was filled so far
+  struct OutGuard {
+    dafs_csr_batch *a, *b; bool ok = false;
+    ~OutGuard() { if (!ok) { dafs_cuda_free_batch(a); dafs_cuda_free_batch(b); } }
+  } outs{mp_out, bp_out};
   StreamGuard G;
   DAFS_CUDA_TRY(cudaStreamCreateWithFlags(&G.s, cudaStreamNonBlocking));
   for (auto& e : G.ev) DAFS_CUDA_TRY(cudaEventCreate(&e));
   cudaStream_t st = G.s;
   DevBufs B;
+  B.stream = st;
   PctArgs A{};
   A.n = n;
   int* d_len = nullptr; int2* d_pairs = nullptr; int* d_ncols_mp = nullptr; int* d_bad = nullptr; int* d_cursor = nullptr;
@@ -392,7 +399,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
     DAFS_CUDA_TRY(B.get(&d_acc, acc_warps * acc_floats_per_warp));
     Pool P;
     const int64_t rows = orow_mp[npairs];
-    if ((rc = P.alloc(B, rows, std::max<int64_t>(2 * mp_nnz, 1024)))) { dafs_cuda_free_batch(bp_out); return rc; }
+    if ((rc = P.alloc(B, rows, std::max<int64_t>(2 * mp_nnz, 1024)))) return rc;
     int64_t need = 0;
     for (int attempt = 0; attempt < 2; ++attempt) {
       cudaError_t e = cudaMemsetAsync(P.O.pool_count, 0, sizeof(unsigned long long), st);
@@ -417,20 +424,19 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
       }
       if (e == cudaSuccess) e = cudaMemcpyAsync(&need, P.O.pool_count, sizeof need, cudaMemcpyDeviceToHost, st);
       if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-      if (e != cudaSuccess) { dafs_cuda_free_batch(bp_out); return fail(DAFS_CUDA_ECUDA, "relax_mp: %s", cudaGetErrorString(e)); }
+      if (e != cudaSuccess) { return fail(DAFS_CUDA_ECUDA, "relax_mp: %s", cudaGetErrorString(e)); }
       if (need <= P.O.pool_cap) break;
-      if (attempt == 1) { dafs_cuda_free_batch(bp_out); return fail(DAFS_CUDA_ECUDA, "relax_mp pool overflow after regrow"); }
-      if ((rc = P.grow(B, need))) { dafs_cuda_free_batch(bp_out); return rc; }
+      if (attempt == 1) { return fail(DAFS_CUDA_ECUDA, "relax_mp pool overflow after regrow"); }
+      if ((rc = P.grow(B, need))) return rc;
     }
     cudaEventRecord(ev_mp1, st);
-    if ((rc = pct_finish(B, st, npairs, rows, d_orow_mp, P.O, need, u_row_off.data(), mp_out))) { dafs_cuda_free_batch(bp_out); return rc; }
+    if ((rc = pct_finish(B, st, npairs, rows, d_orow_mp, P.O, need, u_row_off.data(), mp_out))) return rc;
   } else {
     cudaEventRecord(ev_mp1, st);
-    if ((rc = copy_batch(mp, mp_out))) { dafs_cuda_free_batch(bp_out); return rc; }
+    if ((rc = copy_batch(mp, mp_out))) return rc;
   }
   cudaEventRecord(G.ev[5], st);
   if (cudaStreamSynchronize(st) != cudaSuccess) {
-    dafs_cuda_free_batch(bp_out); dafs_cuda_free_batch(mp_out);
     return fail(DAFS_CUDA_ECUDA, "consistency transformation failed: %s", cudaGetErrorString(cudaGetLastError()));
   }
   cudaEventElapsedTime(&g_ms[0], G.ev[1], G.ev[2]);
@@ -438,6 +444,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   cudaEventElapsedTime(&g_ms[2], G.ev[3], G.ev[4]);
   cudaEventElapsedTime(&g_ms[3], ev_mp0, ev_mp1);
   cudaEventElapsedTime(&g_ms[4], G.ev[0], G.ev[5]);
+  outs.ok = true;
   return DAFS_CUDA_OK;
 }
 

@@ -23,7 +23,8 @@ namespace {
 
 struct DevBufs {
   std::vector<void*> p;
-  ~DevBufs() { for (void* q : p) dafs::dev_free(q); }
+  cudaStream_t stream = nullptr;        // kernels of the call run here: wait for them before the buffers go back to the cache (error returns)
+  ~DevBufs() { if (stream) cudaStreamSynchronize(stream); for (void* q : p) dafs::dev_free(q); }
   template <class T> cudaError_t get(T** out, size_t count) {
     void* q = nullptr;
     const cudaError_t e = dafs::dev_malloc(&q, std::max<size_t>(count * sizeof(T), 256));
@@ -39,7 +40,7 @@ struct DevBufs {
 struct DevArena {
   char* base = nullptr;
   size_t cap = 0, used = 0;
-  ~DevArena() { if (base) dafs::dev_free(base); }
+  ~DevArena() { if (base) { cudaDeviceSynchronize(); dafs::dev_free(base); } }   // batches on other streams may still read it on an error return
   static size_t rounded(size_t bytes) { return (std::max<size_t>(bytes, 256) + 255) & ~size_t(255); }
   cudaError_t reserve(size_t bytes) {
     used = 0;
@@ -258,6 +259,7 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   DAFS_CUDA_TRY(cudaEventCreate(&G.b));
   cudaStream_t st = G.s;
   DevBufs B;
+  B.stream = st;
   ProgArgs A{};
   A.n = n;
   int* d_len = nullptr; int2* d_pairs = nullptr; int* d_ncols = nullptr; int* d_bad = nullptr; int* d_fill = nullptr;
