@@ -15,6 +15,7 @@ _os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 from .capi import (  # noqa: F401
     DafsCudaError,
     CsrBatch,
+    DeviceCsrBatch,
     PairHmmPlan,
     all_pairs,
     device_count,

@@ -124,6 +124,42 @@ def all_pairs(n):
     return pi.astype(np.int32), pj.astype(np.int32)
 
 
+class DeviceCsrBatch:
+    """Owns a device-resident dafs_csr_batch (row_off / nz_off on the host, row_ptr / col / val in
+    HBM): pass it to pct / progressive, or make a host copy with to_host()."""
+
+    def __init__(self, raw):
+        self._raw = raw
+        n = int(raw.n_units)
+        self.n_units, self.nnz = n, int(raw.nnz)
+        self.row_off = np.ctypeslib.as_array(raw.row_off, shape=(n + 1,))
+        self.nz_off = np.ctypeslib.as_array(raw.nz_off, shape=(n + 1,))
+
+    def to_host(self):
+        L = lib()
+        L.dafs_cuda_batch_to_host.argtypes = [C.POINTER(_CsrBatch), C.POINTER(_CsrBatch)]
+        out = _CsrBatch()
+        _check(L.dafs_cuda_batch_to_host(C.byref(self._raw), C.byref(out)))
+        return CsrBatch(out, None)
+
+    def close(self):
+        if self._raw is not None:
+            lib().dafs_cuda_free_batch(C.byref(self._raw))
+            self._raw = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class CsrBatch:
     """Owns a dafs_csr_batch; numpy views are valid until close()."""
 
@@ -232,6 +268,14 @@ class PairHmmPlan:
         raw = _CsrBatch()
         _check(lib().dafs_cuda_pairhmm_plan_fetch(self._h, C.byref(raw)))
         return CsrBatch(raw, None)
+
+    def fetch_device(self):
+        """The result as a device-resident batch (the plan cannot be run again)."""
+        L = lib()
+        L.dafs_cuda_pairhmm_plan_fetch_device.argtypes = [C.c_void_p, C.POINTER(_CsrBatch)]
+        raw = _CsrBatch()
+        _check(L.dafs_cuda_pairhmm_plan_fetch_device(self._h, C.byref(raw)))
+        return DeviceCsrBatch(raw)
 
     def close(self):
         if self._h:

@@ -3,7 +3,7 @@ import ctypes as C
 
 import numpy as np
 
-from .capi import CsrBatch, _CsrBatch, _check, _seq_args, lib
+from .capi import CsrBatch, DeviceCsrBatch, _CsrBatch, _check, _seq_args, lib
 
 
 class _McInfo(C.Structure):
@@ -92,6 +92,13 @@ class McCaskillPlan:
         lnz = np.zeros(max(self.nseq, 1), np.float64)
         _check(lib().dafs_cuda_mccaskill_plan_fetch(self._h, C.byref(raw), lnz.ctypes.data_as(C.c_void_p)))
         return CsrBatch(raw, None), lnz[:self.nseq]
+
+    def fetch_device(self):
+        L = lib()
+        L.dafs_cuda_mccaskill_plan_fetch_device.argtypes = [C.c_void_p, C.POINTER(_CsrBatch)]
+        raw = _CsrBatch()
+        _check(L.dafs_cuda_mccaskill_plan_fetch_device(self._h, C.byref(raw)))
+        return DeviceCsrBatch(raw)
 
     def info(self):
         i = _McInfo()

@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-from .capi import CsrBatch, _CsrBatch, _check, lib
+from .capi import CsrBatch, DeviceCsrBatch, _CsrBatch, _check, lib
 
 _done = False
 
@@ -15,6 +15,7 @@ def _protos():
     if not _done:
         L.dafs_cuda_pct.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(_CsrBatch), C.POINTER(_CsrBatch),
                                     C.c_float, C.c_float, C.c_void_p, C.POINTER(_CsrBatch), C.POINTER(_CsrBatch)]
+        L.dafs_cuda_pct_device.argtypes = L.dafs_cuda_pct.argtypes
         L.dafs_cuda_pct_last_ms.argtypes = [C.POINTER(C.c_float)]
         L.dafs_cuda_pct_last_ms.restype = None
         _done = True
@@ -23,7 +24,7 @@ def _protos():
 
 def _as_raw(b, keep):
     """A dafs_csr_batch over numpy arrays (or a CsrBatch the library returned)."""
-    if isinstance(b, CsrBatch):
+    if isinstance(b, (CsrBatch, DeviceCsrBatch)):
         return b._raw
     arrs = (np.ascontiguousarray(b.row_off, np.int64), np.ascontiguousarray(b.row_ptr, np.int32),
             np.ascontiguousarray(b.nz_off, np.int64), np.ascontiguousarray(b.col, np.uint32),
@@ -40,9 +41,10 @@ def _as_raw(b, keep):
     return raw
 
 
-def pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
-    """-> (sim[n, n], relaxed mp CsrBatch, relaxed bp CsrBatch).  mp / bp: a CsrBatch or any
-    object with row_off / row_ptr / nz_off / col / val arrays in the dafs_csr_batch layout."""
+def pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25, device_out=False):
+    """-> (sim[n, n], relaxed mp, relaxed bp).  mp / bp: a CsrBatch, a DeviceCsrBatch or any
+    object with row_off / row_ptr / nz_off / col / val arrays in the dafs_csr_batch layout.
+    device_out: the relaxed batches stay in HBM (DeviceCsrBatch)."""
     L = _protos()
     lens = np.ascontiguousarray(lens, np.int32)
     n = len(lens)
@@ -50,9 +52,12 @@ def pct(lens, mp, bp, w_pct_a=0.25, w_pct_s=0.25):
     rmp, rbp = _as_raw(mp, keep), _as_raw(bp, keep)
     sim = np.zeros((n, n), np.float32)
     omp, obp = _CsrBatch(), _CsrBatch()
-    _check(L.dafs_cuda_pct(n, lens.ctypes.data_as(C.POINTER(C.c_int)), C.byref(rmp), C.byref(rbp),
-                           C.c_float(w_pct_a), C.c_float(w_pct_s), sim.ctypes.data_as(C.c_void_p),
-                           C.byref(omp), C.byref(obp)))
+    fn = L.dafs_cuda_pct_device if device_out else L.dafs_cuda_pct
+    _check(fn(n, lens.ctypes.data_as(C.POINTER(C.c_int)), C.byref(rmp), C.byref(rbp),
+              C.c_float(w_pct_a), C.c_float(w_pct_s), sim.ctypes.data_as(C.c_void_p),
+              C.byref(omp), C.byref(obp)))
+    if device_out:
+        return sim, DeviceCsrBatch(omp), DeviceCsrBatch(obp)
     return sim, CsrBatch(omp, None), CsrBatch(obp, None)
 
 

@@ -141,6 +141,7 @@ extern "C" int dafs_cuda_pairhmm_plan_gather(dafs_pairhmm_plan* p, dafs_comm* c,
   *out = dafs_gathered_csr{};
   if (root < 0 || root >= c->nranks) return fail(DAFS_CUDA_EINVAL, "root %d outside [0, %d)", root, c->nranks);
   if (p->device != c->device) return fail(DAFS_CUDA_EINVAL, "plan and communicator live on different devices");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was handed over to a device batch");
   const NcclApi* api = nccl_api();
   if (!api) return fail(DAFS_CUDA_ENOTSUP, "libnccl.so.2 could not be loaded");
   const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);

@@ -6,7 +6,9 @@
 #include <algorithm>
 #include <cstdlib>
 #include <map>
+#include <cstring>
 #include <mutex>
+#include <unordered_set>
 #include <vector>
 
 namespace dafs {
@@ -22,6 +24,7 @@ struct MaxConnections {
 } g_max_connections;
 }  // namespace
 
+thread_local DDPackLend g_dd_pack_lend = {nullptr, 0};
 thread_local cudaStream_t g_dd_stream = nullptr, g_dd_poll_stream = nullptr;
 
 std::string& last_error() {
@@ -191,6 +194,60 @@ cudaError_t dev_info(int device, DevInfo* out) {
   return cudaSuccess;
 }
 
+// ---- device-resident batches ------------------------------------------------------------
+namespace {
+struct DeviceBatchOwner { int device; void* pinned; void* d_row_ptr; void* d_col; void* d_val; };
+std::mutex g_devbatch_mu;
+std::unordered_set<void*> g_devbatch;
+}  // namespace
+
+int make_device_batch(int64_t units, int64_t nnz, const int64_t* h_row_off, const int64_t* d_nz_off,
+                      int32_t* d_row_ptr, uint32_t* d_col, float* d_val, cudaStream_t st, dafs_csr_batch* out) {
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t b_off = sizeof(int64_t) * (units + 1);
+  char* pin = (char*)pinned_alloc(2 * up(b_off) + 256);
+  if (!pin) return fail(DAFS_CUDA_ENOMEM, "pinned allocation failed");
+  int64_t* row_off = (int64_t*)pin;
+  int64_t* nz_off = (int64_t*)(pin + up(b_off));
+  std::memcpy(row_off, h_row_off, b_off);
+  cudaError_t e = cudaMemcpyAsync(nz_off, d_nz_off, b_off, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { pinned_free(pin); return fail(DAFS_CUDA_ECUDA, "copy of nz_off failed: %s", cudaGetErrorString(e)); }
+  DeviceBatchOwner* o = new DeviceBatchOwner();
+  cudaGetDevice(&o->device);
+  o->pinned = pin; o->d_row_ptr = d_row_ptr; o->d_col = d_col; o->d_val = d_val;
+  { std::lock_guard<std::mutex> g(g_devbatch_mu); g_devbatch.insert(o); }
+  out->n_units = units; out->nnz = nnz; out->row_off = row_off; out->nz_off = nz_off;
+  out->row_ptr = d_row_ptr; out->col = d_col; out->val = d_val; out->owner_ = o;
+  return DAFS_CUDA_OK;
+}
+
+bool is_device_batch(const dafs_csr_batch* b) {
+  if (!b || !b->owner_) return false;
+  std::lock_guard<std::mutex> g(g_devbatch_mu);
+  return g_devbatch.count(b->owner_) != 0;
+}
+
+bool free_device_batch(dafs_csr_batch* b) {
+  if (!b || !b->owner_) return false;
+  DeviceBatchOwner* o = nullptr;
+  {
+    std::lock_guard<std::mutex> g(g_devbatch_mu);
+    auto it = g_devbatch.find(b->owner_);
+    if (it == g_devbatch.end()) return false;
+    o = static_cast<DeviceBatchOwner*>(*it);
+    g_devbatch.erase(it);
+  }
+  int cur = 0;
+  cudaGetDevice(&cur);
+  if (cur != o->device) cudaSetDevice(o->device);
+  dev_free(o->d_row_ptr); dev_free(o->d_col); dev_free(o->d_val);
+  if (cur != o->device) cudaSetDevice(cur);
+  pinned_free(o->pinned);
+  delete o;
+  return true;
+}
+
 // FP32 issue-rate probe: 8 independent chains per thread, 4 CTAs of 256 per SM.
 // FMA = true counts 2 flop per FFMA; false issues FMUL + FADD (what the bit-exact
 // pair-HMM arithmetic is restricted to, pairhmm_math.cuh) and counts 1 each.
@@ -316,8 +373,34 @@ void dafs_cuda_shutdown(void) { dafs::pinned_trim(); dafs::dev_trim(); }
 
 void dafs_cuda_free_batch(dafs_csr_batch* b) {
   if (!b) return;
-  dafs::pinned_free((void*)b->owner_);
+  if (!dafs::free_device_batch(b)) dafs::pinned_free((void*)b->owner_);
   *b = dafs_csr_batch{};
+}
+
+int dafs_cuda_batch_is_device(const dafs_csr_batch* b) { return b && dafs::is_device_batch(b) ? 1 : 0; }
+
+int dafs_cuda_batch_to_host(const dafs_csr_batch* b, dafs_csr_batch* out) {
+  if (!b || !out) return dafs::fail(DAFS_CUDA_EINVAL, "NULL argument");
+  *out = dafs_csr_batch{};
+  const int64_t units = b->n_units, rows = units >= 0 && b->row_off ? b->row_off[units] : 0, nnz = b->nnz;
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t b_off = sizeof(int64_t) * (units + 1);
+  char* base = (char*)dafs::pinned_alloc(2 * up(b_off) + up(sizeof(int32_t) * rows) + up(sizeof(uint32_t) * nnz) + up(sizeof(float) * nnz) + 256);
+  if (!base) return dafs::fail(DAFS_CUDA_ENOMEM, "pinned allocation failed");
+  int64_t* row_off = (int64_t*)base;
+  int64_t* nz_off = (int64_t*)(base + up(b_off));
+  int32_t* row_ptr = (int32_t*)((char*)nz_off + up(b_off));
+  uint32_t* col = (uint32_t*)((char*)row_ptr + up(sizeof(int32_t) * rows));
+  float* val = (float*)((char*)col + up(sizeof(uint32_t) * nnz));
+  std::memcpy(row_off, b->row_off, b_off);
+  std::memcpy(nz_off, b->nz_off, b_off);
+  cudaError_t e = rows ? cudaMemcpy(row_ptr, b->row_ptr, sizeof(int32_t) * rows, cudaMemcpyDefault) : cudaSuccess;
+  if (e == cudaSuccess && nnz) e = cudaMemcpy(col, b->col, sizeof(uint32_t) * nnz, cudaMemcpyDefault);
+  if (e == cudaSuccess && nnz) e = cudaMemcpy(val, b->val, sizeof(float) * nnz, cudaMemcpyDefault);
+  if (e != cudaSuccess) { dafs::pinned_free(base); return dafs::fail(DAFS_CUDA_ECUDA, "copy of the batch failed: %s", cudaGetErrorString(e)); }
+  out->n_units = units; out->nnz = nnz; out->row_off = row_off; out->nz_off = nz_off; out->row_ptr = row_ptr; out->col = col; out->val = val;
+  out->owner_ = base;
+  return DAFS_CUDA_OK;
 }
 
 }  // extern "C"

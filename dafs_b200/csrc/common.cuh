@@ -39,10 +39,24 @@ template <class T> inline cudaError_t dev_malloc(T** out, size_t bytes) { return
 void dev_free(void* p);
 void dev_trim();
 
+// Device-resident batches: a dafs_csr_batch whose row_off / nz_off are host arrays (pinned) and whose
+// row_ptr / col / val live in HBM.  make_device_batch takes ownership of the three device arrays
+// (dev_malloc'ed) and copies nz_off from the device; dafs_cuda_free_batch releases either kind.
+int make_device_batch(int64_t units, int64_t nnz, const int64_t* h_row_off, const int64_t* d_nz_off,
+                      int32_t* d_row_ptr, uint32_t* d_col, float* d_val, cudaStream_t st, dafs_csr_batch* out);
+bool is_device_batch(const dafs_csr_batch* b);
+bool free_device_batch(dafs_csr_batch* b);   // false: not a device batch
+
 // Streams a caller inside the library lends to the next DD plans of this thread (a plan
 // normally makes its own): dafs_cuda_progressive keeps a small pool and reuses an idle stream
 // for every batch instead of creating two streams per batch.
 extern thread_local cudaStream_t g_dd_stream, g_dd_poll_stream;
+// Likewise a device block for the scratch of the pack kernels of dafs_cuda_dd_plan_create_device (dd_pack.cuh):
+// the progressive stage owns one grow-only block for all its batches, so that no cudaMalloc / cudaFree (both wait
+// for the DD batches in flight) happens per batch.  dd_pack_bytes: what a batch needs.
+struct DDPackLend { char* base; size_t cap; };
+extern thread_local DDPackLend g_dd_pack_lend;
+size_t dd_pack_bytes(int nprob, const dafs_dd_problem* prob);
 
 // SM count and opt-in shared memory per block of a device, queried once
 // (cudaGetDeviceProperties costs about a millisecond per call, per-call plans pay it).

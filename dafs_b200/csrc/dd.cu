@@ -465,6 +465,14 @@ static cudaError_t dd_allow_smem(const void* fn, bool smem, int team, int device
 }
 }  // namespace dafs
 
+namespace dafs {
+size_t dd_pack_bytes(int nprob, const dafs_dd_problem* prob) {
+  size_t sc = 0;
+  for (int k = 0; k < nprob; ++k) sc += pack_scratch_bytes(prob[k].L1, prob[k].L2);
+  return sc + pack_up(sizeof(PackProb) * nprob) + pack_up(sizeof(PackCounts) * nprob) + pack_up(sizeof(DDHdr) * nprob);
+}
+}  // namespace dafs
+
 // device_inputs: p_x / p_y / p_z of every problem are DEVICE pointers and the constant blocks are
 // built by dd_pack_count / dd_pack_fill (dd_pack.cuh) instead of build_problem() on the host cores.
 static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_trace, bool device_inputs,
@@ -505,6 +513,7 @@ static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_
   p->packed_on_device = device_inputs;
   // device path: scratch + problem descriptors, count kernel, totals back (64 bytes per problem)
   char* d_scratch = nullptr; PackProb* d_pp = nullptr; PackCounts* d_counts = nullptr; DDHdr* d_hdr = nullptr;
+  PackProb* c_pp_ = nullptr; PackCounts* c_counts_ = nullptr; DDHdr* c_hdr_ = nullptr;   // carved from the scratch block
   std::vector<PackProb> pp;
   std::vector<DDHdr> hdr;
   auto pack_free = [&]() { dev_free(d_scratch); dev_free(d_pp); dev_free(d_counts); dev_free(d_hdr); d_scratch = nullptr; d_pp = nullptr; d_counts = nullptr; d_hdr = nullptr; };
@@ -515,10 +524,17 @@ static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_
     size_t sc = 0;
     std::vector<size_t> sc_off(nprob);
     for (int k = 0; k < nprob; ++k) { sc_off[k] = sc; sc += pack_scratch_bytes(prob[k].L1, prob[k].L2); }
-    PACK_TRY(dev_malloc(&d_scratch, std::max<size_t>(sc, 256)));
-    PACK_TRY(dev_malloc(&d_pp, sizeof(PackProb) * nprob));
-    PACK_TRY(dev_malloc(&d_counts, sizeof(PackCounts) * nprob));
-    PACK_TRY(dev_malloc(&d_hdr, sizeof(DDHdr) * nprob));
+    const size_t o_pp = sc, o_counts = o_pp + pack_up(sizeof(PackProb) * nprob), o_hdr = o_counts + pack_up(sizeof(PackCounts) * nprob);
+    const size_t need = o_hdr + pack_up(sizeof(DDHdr) * nprob);
+    char* blockp = nullptr;
+    if (g_dd_pack_lend.base && g_dd_pack_lend.cap >= need) blockp = g_dd_pack_lend.base;      // lent by the progressive stage
+    else { PACK_TRY(dev_malloc(&d_scratch, need)); blockp = d_scratch; }
+    char* const scratch0 = blockp;
+    d_pp = nullptr; d_counts = nullptr; d_hdr = nullptr;                                         // carved, not owned
+    PackProb* const c_pp = reinterpret_cast<PackProb*>(blockp + o_pp);
+    PackCounts* const c_counts = reinterpret_cast<PackCounts*>(blockp + o_counts);
+    DDHdr* const c_hdr = reinterpret_cast<DDHdr*>(blockp + o_hdr);
+    c_pp_ = c_pp; c_counts_ = c_counts; c_hdr_ = c_hdr;
     for (int k = 0; k < nprob; ++k) {
       const dafs_dd_problem& q = prob[k];
       PackProb& P = pp[k];
@@ -526,21 +542,21 @@ static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_
       P.L1 = q.L1; P.L2 = q.L2; P.N1 = N1; P.N2 = N2; P.p_x = q.p_x; P.p_y = q.p_y; P.p_z = q.p_z;
       P.w = q.w; P.wx = q.w * 2 * N1 / (N1 + N2); P.wy = q.w * 2 * N2 / (N1 + N2);
       P.th_s = q.th_s; P.min_th_s = q.min_th_s; P.th_a = q.th_a;
-      P.scratch = d_scratch + sc_off[k]; P.block = nullptr; P.hdr = nullptr;
+      P.scratch = scratch0 + sc_off[k]; P.block = nullptr; P.hdr = nullptr;
     }
     std::vector<PackCounts> counts(nprob);
-    PACK_TRY(cudaMemcpyAsync(d_pp, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
+    PACK_TRY(cudaMemcpyAsync(c_pp_, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
     int maxL = 1;
     for (int k = 0; k < nprob; ++k) maxL = std::max(maxL, std::max(prob[k].L1, prob[k].L2));
     const dim3 rgrid((maxL + DD_PACK_ROWS - 1) / DD_PACK_ROWS, nprob);
     const size_t env_smem = (size_t)(maxL + 1) * sizeof(uint2) <= 96 * 1024 ? (size_t)(maxL + 1) * sizeof(uint2) : 0;
     if (env_smem > 48 * 1024) PACK_TRY(cudaFuncSetAttribute(dd_pack_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)env_smem));
-    dd_pack_gates<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
-    dd_pack_cbp<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
-    dd_pack_classify<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
-    dd_pack_scan<<<nprob, DD_PACK_THREADS, env_smem, p->stream>>>(d_pp, d_counts);
+    dd_pack_gates<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
+    dd_pack_cbp<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
+    dd_pack_classify<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
+    dd_pack_scan<<<nprob, DD_PACK_THREADS, env_smem, p->stream>>>(c_pp_, c_counts_);
     PACK_TRY(cudaGetLastError());
-    PACK_TRY(cudaMemcpyAsync(counts.data(), d_counts, sizeof(PackCounts) * nprob, cudaMemcpyDeviceToHost, p->stream));
+    PACK_TRY(cudaMemcpyAsync(counts.data(), c_counts_, sizeof(PackCounts) * nprob, cudaMemcpyDeviceToHost, p->stream));
     PACK_TRY(cudaStreamSynchronize(p->stream));
     for (int k = 0; k < nprob; ++k) {
       if (counts[k].n_x > 65535 * 8 || counts[k].ncz > (1 << 28)) return bail_pack(fail(DAFS_CUDA_EINVAL, "problem %d is too dense", k));
@@ -576,16 +592,16 @@ static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_
   if (device_inputs) {
     // blocks start as zeros (the host packer's padding bytes are zeros), then every section is written in place
     PACK_TRY(cudaMemsetAsync(p->d_cst, 0, std::max<size_t>(cst, 256), p->stream));
-    for (int k = 0; k < nprob; ++k) { pp[k].block = p->d_cst + p->host[k].cst_base; pp[k].hdr = d_hdr + k; }
-    PACK_TRY(cudaMemcpyAsync(d_pp, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
-    PACK_TRY(cudaMemcpyAsync(d_hdr, hdr.data(), sizeof(DDHdr) * nprob, cudaMemcpyHostToDevice, p->stream));
+    for (int k = 0; k < nprob; ++k) { pp[k].block = p->d_cst + p->host[k].cst_base; pp[k].hdr = c_hdr_ + k; }
+    PACK_TRY(cudaMemcpyAsync(c_pp_, pp.data(), sizeof(PackProb) * nprob, cudaMemcpyHostToDevice, p->stream));
+    PACK_TRY(cudaMemcpyAsync(c_hdr_, hdr.data(), sizeof(DDHdr) * nprob, cudaMemcpyHostToDevice, p->stream));
     {
       int maxL = 1;
       for (int k = 0; k < nprob; ++k) maxL = std::max(maxL, std::max(prob[k].L1, prob[k].L2));
       const dim3 rgrid((maxL + DD_PACK_ROWS - 1) / DD_PACK_ROWS, nprob);
-      dd_pack_head<<<nprob, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
-      dd_pack_entries<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
-      dd_pack_rows<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(d_pp);
+      dd_pack_head<<<nprob, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
+      dd_pack_entries<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
+      dd_pack_rows<<<rgrid, DD_PACK_THREADS, 0, p->stream>>>(c_pp_);
     }
     PACK_TRY(cudaGetLastError());
     PACK_TRY(cudaStreamSynchronize(p->stream));       // pp / hdr go out of scope; the caller may reuse the matrices

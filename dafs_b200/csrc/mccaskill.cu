@@ -134,6 +134,7 @@ struct dafs_mccaskill_plan {
   int32_t* d_seq_nnz = nullptr; double* d_seq_lnz = nullptr;
   int64_t* d_nz_off = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr;
   bool launched = false;
+  bool consumed = false;
   int64_t nnz = -1;
   float last_ms = 0;
 };
@@ -319,6 +320,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char*
 extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   using namespace dafs;
   if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result arrays were handed over (dafs_cuda_mccaskill_plan_fetch_device): create a new plan");
   DAFS_CUDA_TRY(cudaSetDevice(p->device));
   p->launched = true; p->nnz = -1;
   if (p->nseq == 0) { p->nnz = 0; return DAFS_CUDA_OK; }
@@ -370,6 +372,7 @@ extern "C" int dafs_cuda_mccaskill_plan_sync(dafs_mccaskill_plan* p, float* devi
 extern "C" int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* p, dafs_csr_batch* out, double* lnz) {
   if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   *out = dafs_csr_batch{};
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was handed over to a device batch");
   const int rc = dafs_cuda_mccaskill_plan_sync(p, nullptr, nullptr);
   if (rc) return rc;
   const int64_t ns = p->nseq, nnz = p->nnz, rows = p->total_rows;
@@ -399,6 +402,22 @@ extern "C" int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* p, dafs_csr_b
   if (e != cudaSuccess) { dafs::pinned_free(base); return fail(DAFS_CUDA_ECUDA, "result copy failed: %s", cudaGetErrorString(e)); }
   out->n_units = ns; out->nnz = nnz; out->row_off = h_row_off; out->row_ptr = h_row_ptr; out->nz_off = h_nz_off;
   out->col = h_col; out->val = h_val; out->owner_ = base;
+  return DAFS_CUDA_OK;
+}
+
+// The result stays in HBM (see dafs_cuda_pairhmm_plan_fetch_device): the plan gives up its row_ptr /
+// col / val arrays and cannot be run again.
+extern "C" int dafs_cuda_mccaskill_plan_fetch_device(dafs_mccaskill_plan* p, dafs_csr_batch* out) {
+  if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  *out = dafs_csr_batch{};
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was already handed over");
+  const int rc = dafs_cuda_mccaskill_plan_sync(p, nullptr, nullptr);
+  if (rc) return rc;
+  if (p->nseq == 0) return fail(DAFS_CUDA_EINVAL, "empty plan");
+  const int rc2 = dafs::make_device_batch(p->nseq, p->nnz, p->row_off.data(), p->d_nz_off, p->d_row_ptr, p->d_col, p->d_val, p->stream, out);
+  if (rc2) return rc2;
+  p->d_row_ptr = nullptr; p->d_col = nullptr; p->d_val = nullptr;
+  p->consumed = true;
   return DAFS_CUDA_OK;
 }
 

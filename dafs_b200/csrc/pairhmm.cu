@@ -411,6 +411,7 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
 
 extern "C" int dafs_cuda_pairhmm_plan_run(dafs_pairhmm_plan* p) {
   if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result arrays were handed over (dafs_cuda_pairhmm_plan_fetch_device): create a new plan");
   DAFS_CUDA_TRY(cudaSetDevice(p->device));
   if (p->npairs == 0) { p->launched = true; p->nnz = 0; return DAFS_CUDA_OK; }
   return dafs::launch_all(p);
@@ -499,6 +500,7 @@ static cudaError_t copy_whole(dafs_pairhmm_plan* p, const HostCsr& h) {
 extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch* out) {
   if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
   *out = dafs_csr_batch{};
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was handed over to a device batch");
   if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
   DAFS_CUDA_TRY(cudaSetDevice(p->device));
   const int64_t np = p->npairs, rows = p->total_rows;
@@ -561,6 +563,7 @@ extern "C" int dafs_cuda_pairhmm_plan_fetch(dafs_pairhmm_plan* p, dafs_csr_batch
 // (page-locked by the caller so that the chunk copies run under the kernels).
 extern "C" int dafs_cuda_pairhmm_plan_fetch_into(dafs_pairhmm_plan* p, dafs_host_csr* dst) {
   if (!p || !dst) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was handed over to a device batch");
   if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
   if (!dst->nz_off || !dst->row_ptr || (dst->cap_nnz > 0 && (!dst->col || !dst->val)))
     return fail(DAFS_CUDA_EINVAL, "dafs_host_csr: NULL array");
@@ -591,12 +594,32 @@ extern "C" int dafs_cuda_pairhmm_plan_fetch_into(dafs_pairhmm_plan* p, dafs_host
   return DAFS_CUDA_OK;
 }
 
+// The result stays in HBM: row_ptr / col / val of the batch are the plan's own arrays (the plan gives
+// them up and cannot be run again), row_off / nz_off are host copies.  What a device consumer
+// (dafs_cuda_pct, dafs_cuda_progressive) takes instead of a host batch.
+extern "C" int dafs_cuda_pairhmm_plan_fetch_device(dafs_pairhmm_plan* p, dafs_csr_batch* out) {
+  if (!p || !out) return fail(DAFS_CUDA_EINVAL, "NULL argument");
+  *out = dafs_csr_batch{};
+  if (!p->launched) return fail(DAFS_CUDA_EINVAL, "plan was not run");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was already handed over");
+  const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
+  if (rc) return rc;
+  DAFS_CUDA_TRY(cudaSetDevice(p->device));
+  if (p->npairs == 0) DAFS_CUDA_TRY(cudaMemsetAsync(p->d_nz_off, 0, sizeof(int64_t), p->stream));
+  const int rc2 = dafs::make_device_batch(p->npairs, p->nnz, p->row_off.data(), p->d_nz_off, p->d_row_ptr, p->d_col, p->d_val, p->stream, out);
+  if (rc2) return rc2;
+  p->d_row_ptr = nullptr; p->d_col = nullptr; p->d_val = nullptr;
+  p->consumed = true;
+  return DAFS_CUDA_OK;
+}
+
 // Device-to-device copy of the pair-ordered CSR into caller-owned device
 // buffers (e.g. tensors of the process that will run an NCCL all-gather on them).
 extern "C" int dafs_cuda_pairhmm_plan_export(dafs_pairhmm_plan* p, int32_t* d_row_ptr,
                                              int64_t* d_nz_off, uint32_t* d_col, float* d_val,
                                              int64_t cap_nnz) {
   if (!p) return fail(DAFS_CUDA_EINVAL, "plan is NULL");
+  if (p->consumed) return fail(DAFS_CUDA_EINVAL, "the plan's result was handed over to a device batch");
   const int rc = dafs_cuda_pairhmm_plan_sync(p, nullptr, nullptr);
   if (rc) return rc;
   if (p->nnz > cap_nnz) return fail(DAFS_CUDA_EINVAL, "export buffers hold %lld entries, result has %lld", (long long)cap_nnz, (long long)p->nnz);

@@ -37,6 +37,7 @@ struct dafs_pairhmm_plan {
   int64_t* h_chunk_end = nullptr;   // pinned: nz_off at the end of each chunk
   cudaStream_t copy_stream = nullptr;
   bool launched = false;
+  bool consumed = false;            // the result arrays were given to a device batch
   int64_t nnz = -1;
   float last_ms = 0, last_kernel_ms = 0;
 };

@@ -23,6 +23,9 @@ struct DevBufs {                       // everything dev_malloc'ed by one call
     *out = static_cast<T*>(q);
     return e;
   }
+  void release(void* q) {              // the caller takes the buffer over
+    for (size_t k = 0; k < p.size(); ++k) if (p[k] == q) { p.erase(p.begin() + k); break; }
+  }
   void drop(void* q) {
     for (size_t k = 0; k < p.size(); ++k) if (p[k] == q) { p.erase(p.begin() + k); break; }
     dafs::dev_free(q);
@@ -30,6 +33,7 @@ struct DevBufs {                       // everything dev_malloc'ed by one call
 };
 
 thread_local float g_ms[5] = {0, 0, 0, 0, 0};
+thread_local bool g_device_out = false;   // dafs_cuda_pct_device: the outputs stay in HBM
 
 size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
 
@@ -60,12 +64,31 @@ struct HostBatch {
 
 int copy_batch(const dafs_csr_batch* in, dafs_csr_batch* out) {
   const int64_t units = in->n_units, re = in->row_off[units], nnz = in->nz_off[units];
+  if (g_device_out) {
+    int32_t* d_rp = nullptr; uint32_t* d_col = nullptr; float* d_val = nullptr; int64_t* d_nz = nullptr;
+    auto bail = [&](int rc) { dafs::dev_free(d_rp); dafs::dev_free(d_col); dafs::dev_free(d_val); dafs::dev_free(d_nz); return rc; };
+    cudaError_t e = dafs::dev_malloc(&d_rp, std::max<size_t>(sizeof(int32_t) * re, 256));
+    if (e == cudaSuccess) e = dafs::dev_malloc(&d_col, std::max<size_t>(sizeof(uint32_t) * nnz, 256));
+    if (e == cudaSuccess) e = dafs::dev_malloc(&d_val, std::max<size_t>(sizeof(float) * nnz, 256));
+    if (e == cudaSuccess) e = dafs::dev_malloc(&d_nz, sizeof(int64_t) * (units + 1));
+    if (e == cudaSuccess) e = cudaMemcpy(d_nz, in->nz_off, sizeof(int64_t) * (units + 1), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && re) e = cudaMemcpy(d_rp, in->row_ptr, sizeof(int32_t) * re, cudaMemcpyDefault);
+    if (e == cudaSuccess && nnz) e = cudaMemcpy(d_col, in->col, sizeof(uint32_t) * nnz, cudaMemcpyDefault);
+    if (e == cudaSuccess && nnz) e = cudaMemcpy(d_val, in->val, sizeof(float) * nnz, cudaMemcpyDefault);
+    if (e != cudaSuccess) return bail(fail(e == cudaErrorMemoryAllocation ? DAFS_CUDA_ENOMEM : DAFS_CUDA_ECUDA, "copy of the batch failed: %s", cudaGetErrorString(e)));
+    const int rc = dafs::make_device_batch(units, nnz, in->row_off, d_nz, d_rp, d_col, d_val, nullptr, out);
+    if (rc) return bail(rc);
+    dafs::dev_free(d_nz);
+    return DAFS_CUDA_OK;
+  }
   HostBatch h;
   if (!h.alloc(units, re, nnz)) return fail(DAFS_CUDA_ENOMEM, "pinned allocation failed");
   std::memcpy(h.row_off, in->row_off, h.b_off);
   std::memcpy(h.nz_off, in->nz_off, h.b_off);
-  std::memcpy(h.row_ptr, in->row_ptr, h.b_row_ptr);
-  if (nnz) { std::memcpy(h.col, in->col, h.b_col); std::memcpy(h.val, in->val, h.b_val); }
+  cudaError_t e = re ? cudaMemcpy(h.row_ptr, in->row_ptr, h.b_row_ptr, cudaMemcpyDefault) : cudaSuccess;   // the input may be device-resident
+  if (e == cudaSuccess && nnz) e = cudaMemcpy(h.col, in->col, h.b_col, cudaMemcpyDefault);
+  if (e == cudaSuccess && nnz) e = cudaMemcpy(h.val, in->val, h.b_val, cudaMemcpyDefault);
+  if (e != cudaSuccess) return fail(DAFS_CUDA_ECUDA, "copy of the batch failed: %s", cudaGetErrorString(e));
   h.give(out, units, nnz);
   return DAFS_CUDA_OK;
 }
@@ -99,6 +122,13 @@ static int pct_finish(DevBufs& B, cudaStream_t st, int64_t units, int64_t rows, 
   pct_scan_kernel<<<1, 1024, 0, st>>>(d_unit_nnz, units, C.nz_off);
   pct_gather_kernel<<<grid_for(units, 4), 128, 0, st>>>(units, d_out_row_off, O, C.nz_off, C.row_ptr, C.col, C.val);
   DAFS_CUDA_TRY(cudaGetLastError());
+  if (g_device_out) {
+    // the three arrays leave the call's buffer list and become the batch's
+    const int rc = make_device_batch(units, nnz, h_row_off, C.nz_off, C.row_ptr, C.col, C.val, st, out);
+    if (rc) return rc;
+    B.release(C.row_ptr); B.release(C.col); B.release(C.val);
+    return DAFS_CUDA_OK;
+  }
   HostBatch h;
   if (!h.alloc(units, rows + units, nnz)) return fail(DAFS_CUDA_ENOMEM, "pinned allocation failed");
   std::memcpy(h.row_off, h_row_off, h.b_off);
@@ -238,7 +268,7 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
 
   DAFS_CUDA_TRY(cudaEventRecord(G.ev[0], st));
   auto h2d = [&](void* d, const void* h, size_t bytes) {
-    return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyDefault, st) : cudaSuccess;   // inputs may be device-resident batches
   };
   DAFS_CUDA_TRY(h2d(d_len, len, sizeof(int) * n));
   DAFS_CUDA_TRY(h2d(d_pairs, pairs.data(), sizeof(int2) * npairs));
@@ -446,6 +476,15 @@ extern "C" int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp,
   cudaEventElapsedTime(&g_ms[4], G.ev[0], G.ev[5]);
   outs.ok = true;
   return DAFS_CUDA_OK;
+}
+
+extern "C" int dafs_cuda_pct_device(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
+                                    float w_pct_a, float w_pct_s, float* sim, dafs_csr_batch* mp_out,
+                                    dafs_csr_batch* bp_out) {
+  g_device_out = true;
+  const int rc = dafs_cuda_pct(nseq, len, mp, bp, w_pct_a, w_pct_s, sim, mp_out, bp_out);
+  g_device_out = false;
+  return rc;
 }
 
 extern "C" void dafs_cuda_pct_last_ms(float out5[5]) {

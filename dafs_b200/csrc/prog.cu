@@ -286,7 +286,7 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   DAFS_CUDA_TRY(B.get(&d_b_val, bp_nnz));
   DAFS_CUDA_TRY(B.get(&d_desc, (size_t)n * n));
   auto h2d = [&](void* d, const void* h, size_t bytes) {
-    return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyDefault, st) : cudaSuccess;   // mp / bp may be device-resident batches
   };
   DAFS_CUDA_TRY(h2d(d_len, len, sizeof(int) * n));
   DAFS_CUDA_TRY(h2d(d_pairs, pairs.data(), sizeof(int2) * npairs));
@@ -398,6 +398,8 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
   PinGuard dense_pin;
   size_t dense_cap = 0;
   DevArena arena;
+  struct DevOne { void* p = nullptr; ~DevOne() { if (p) { cudaDeviceSynchronize(); dafs::dev_free(p); } } } pack_buf;   // scratch of the pack kernels, lent to every batch's plan
+  size_t pack_cap = 0;
   while (built < n - 1) {
     if (!ready.empty()) {
       double tl = now_ms();
@@ -538,7 +540,16 @@ extern "C" int dafs_cuda_progressive(int nseq, const int* len, const dafs_csr_ba
           // the pack kernels run on the batch's stream, behind the averaging kernels; the call returns when
           // the blocks are built, so the arena that holds the matrices is free for the next batch
           DAFS_CUDA_TRY(cudaStreamWaitEvent(Bt.stream, G.b, 0));
+          const size_t pack_need = dd_pack_bytes(W, Bt.prob.data());
+          if (pack_need > pack_cap) {               // grow-only; the first batch is usually the largest and runs with nothing in flight
+            dafs::dev_free(pack_buf.p); pack_buf.p = nullptr; pack_cap = 0;
+            void* q = nullptr;
+            DAFS_CUDA_TRY(dafs::dev_malloc(&q, pack_need + pack_need / 4));
+            pack_buf.p = q; pack_cap = pack_need + pack_need / 4;
+          }
+          g_dd_pack_lend.base = static_cast<char*>(pack_buf.p); g_dd_pack_lend.cap = pack_cap;
           rc = dafs_cuda_dd_plan_create_device(W, Bt.prob.data(), 0, &Bt.plan.p);
+          g_dd_pack_lend.base = nullptr; g_dd_pack_lend.cap = 0;
           if (!rc) { float ms = 0.0f; cudaEventElapsedTime(&ms, G.a, G.b); ms_avg += ms; }
         }
         g_dd_stream = nullptr; g_dd_poll_stream = nullptr;

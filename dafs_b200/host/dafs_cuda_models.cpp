@@ -290,4 +290,51 @@ float align_tree(const DDOptions& o, const std::vector<Fasta>& fa, const std::ve
   return s;
 }
 
+// Everything between :1787 and :1838 of DAFS::run() in one call, with the posteriors resident in HBM
+// from the models to the alignment: McCaskill and pair-HMM plans hand their results over as device
+// batches, the consistency transformation reads and writes device batches, the progressive stage reads
+// them.  Only sim (N x N floats), the tree and the alignment reach the host.
+float align_from_sequences(const DDOptions& o, const std::vector<Fasta>& fa, float th_bp, float w_pct_a, float w_pct_s,
+                           VVF& sim, std::vector<TreeNode>& tree, VU& ss, ALN& aln) {
+  const uint N = fa.size();
+  std::vector<const char*> seq(N);
+  std::vector<int> len(N);
+  for (uint i = 0; i != N; ++i) { seq[i] = fa[i].seq().data(); len[i] = (int)fa[i].size(); }
+  std::vector<int32_t> pi, pj;
+  for (uint i = 0; i != N; ++i) for (uint j = i + 1; j != N; ++j) { pi.push_back((int32_t)i); pj.push_back((int32_t)j); }
+  struct Batches {
+    dafs_csr_batch b[4] = {};
+    dafs_mccaskill_plan* pm = nullptr; dafs_pairhmm_plan* pp = nullptr;
+    ~Batches() { for (auto& x : b) dafs_cuda_free_batch(&x); dafs_cuda_mccaskill_plan_destroy(pm); dafs_cuda_pairhmm_plan_destroy(pp); }
+  } B;
+  if (dafs_cuda_mccaskill_plan_create((int)N, seq.data(), len.data(), th_bp, &B.pm) != DAFS_CUDA_OK) fail("dafs_cuda_mccaskill_plan_create");
+  if (dafs_cuda_pairhmm_plan_create((int)N, seq.data(), len.data(), (int64_t)pi.size(), pi.data(), pj.data(), o.th_a, &B.pp) != DAFS_CUDA_OK)
+    fail("dafs_cuda_pairhmm_plan_create");
+  if (dafs_cuda_mccaskill_plan_run(B.pm) != DAFS_CUDA_OK || dafs_cuda_pairhmm_plan_run(B.pp) != DAFS_CUDA_OK) fail("plan_run");   // the two stages overlap on the device
+  if (dafs_cuda_mccaskill_plan_fetch_device(B.pm, &B.b[0]) != DAFS_CUDA_OK) fail("dafs_cuda_mccaskill_plan_fetch_device");
+  if (dafs_cuda_pairhmm_plan_fetch_device(B.pp, &B.b[1]) != DAFS_CUDA_OK) fail("dafs_cuda_pairhmm_plan_fetch_device");
+  std::vector<float> s((size_t)N * N);
+  if (dafs_cuda_pct_device((int)N, len.data(), &B.b[1], &B.b[0], w_pct_a, w_pct_s, s.data(), &B.b[2], &B.b[3]) != DAFS_CUDA_OK) fail("dafs_cuda_pct_device");
+  sim.assign(N, VF(N));
+  for (uint i = 0; i != N; ++i) std::copy(s.begin() + (size_t)i * N, s.begin() + (size_t)(i + 1) * N, sim[i].begin());
+  build_tree(sim, tree);
+  std::vector<int32_t> left(tree.size()), right(tree.size());
+  for (size_t k = 0; k != tree.size(); ++k) { left[k] = (int32_t)tree[k].second.first; right[k] = (int32_t)tree[k].second.second; }
+  dafs_prog_params prm;
+  prm.w = o.w; prm.th_s = o.th_s[0]; prm.min_th_s = *std::min_element(o.th_s.begin(), o.th_s.end());
+  prm.th_a = o.th_a; prm.eta0 = o.eta0; prm.t_max = (int32_t)o.t_max;
+  dafs_prog_result r;
+  if (dafs_cuda_progressive((int)N, len.data(), &B.b[2], &B.b[3], left.data(), right.data(), &prm, &r) != DAFS_CUDA_OK)
+    fail("dafs_cuda_progressive");
+  aln.resize(r.n_rows);
+  for (int q = 0; q < r.n_rows; ++q) {
+    aln[q].first = (uint)r.seq[q];
+    aln[q].second.assign(r.bits + (size_t)q * r.L, r.bits + (size_t)(q + 1) * r.L);
+  }
+  if (r.ss) ss.assign(r.ss, r.ss + r.L);
+  const float sc = r.score;
+  dafs_cuda_free_prog_result(&r);
+  return sc;
+}
+
 }  // namespace dafs_cuda

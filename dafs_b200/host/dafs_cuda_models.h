@@ -108,6 +108,13 @@ void build_tree(const VVF& sim, std::vector<TreeNode>& tree);
 float align_tree(const DDOptions& o, const std::vector<Fasta>& fa, const std::vector<std::vector<MP> >& mp,
                  const std::vector<BP>& bp, const std::vector<TreeNode>& tree, VU& ss, ALN& aln);
 
+// One call for DAFS::run() :1787-1838 when alifold and --bp-update are off and -f is 0: fold model, align
+// model, consistency transformation, guide tree and progressive alignment with the posteriors kept in
+// HBM between the stages (device batches).  th_bp = CUTOFF (:65), w_pct_a / w_pct_s = -p / -q; sim and
+// tree are filled as the reference fills sim_ and tree_; ss / aln / the return value are align()'s.
+float align_from_sequences(const DDOptions& o, const std::vector<Fasta>& fa, float th_bp, float w_pct_a, float w_pct_s,
+                           VVF& sim, std::vector<TreeNode>& tree, VU& ss, ALN& aln);
+
 }  // namespace dafs_cuda
 
 #endif  // DAFS_CUDA_MODELS_H_

@@ -134,6 +134,16 @@ int dafs_cuda_pairhmm_pairs_into(int nseq, const char* const* seq, const int* le
                                  float th, dafs_host_csr* dst);
 int dafs_cuda_pairhmm_plan_fetch_into(dafs_pairhmm_plan* plan, dafs_host_csr* dst);
 
+/* Device-resident batches.  fetch_device returns a dafs_csr_batch whose row_off / nz_off are host
+ * arrays and whose row_ptr / col / val are DEVICE pointers (the plan's own arrays: the plan gives them
+ * up and cannot be run again); dafs_cuda_pct, dafs_cuda_pct_device and dafs_cuda_progressive accept
+ * such batches wherever they accept host ones, so the posteriors stay in HBM between the stages of
+ * DAFS::run() (src/dafs.cpp:1787-1838) instead of crossing PCIe twice.  dafs_cuda_free_batch releases
+ * either kind; dafs_cuda_batch_to_host makes a host copy (tests, output).                          */
+int dafs_cuda_pairhmm_plan_fetch_device(dafs_pairhmm_plan* plan, dafs_csr_batch* out);
+int dafs_cuda_batch_is_device(const dafs_csr_batch* b);
+int dafs_cuda_batch_to_host(const dafs_csr_batch* b, dafs_csr_batch* out);
+
 /* Device-resident hand-over: copies the pair-ordered CSR (row_ptr blocks,
  * nz_off[npairs+1], col, val) into caller-owned DEVICE buffers, e.g. the
  * tensors a rank feeds to an NCCL all-gather.  cap_nnz = capacity of d_col/d_val
@@ -230,6 +240,7 @@ int dafs_cuda_mccaskill_constrained(int nseq, const char* const* seq, const int*
 int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* plan);
 int dafs_cuda_mccaskill_plan_sync(dafs_mccaskill_plan* plan, float* device_ms, int64_t* nnz);
 int dafs_cuda_mccaskill_plan_fetch(dafs_mccaskill_plan* plan, dafs_csr_batch* out, double* lnz);
+int dafs_cuda_mccaskill_plan_fetch_device(dafs_mccaskill_plan* plan, dafs_csr_batch* out);
 void dafs_cuda_mccaskill_plan_destroy(dafs_mccaskill_plan* plan);
 typedef struct dafs_mccaskill_info {
   int grid, block, smem_bytes, row_stride, table_bytes;
@@ -363,6 +374,11 @@ int dafs_cuda_nw_decode_static(int L1, int L2, float th, const float* p, const f
 int dafs_cuda_pct(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
                   float w_pct_a, float w_pct_s, float* sim, dafs_csr_batch* mp_out,
                   dafs_csr_batch* bp_out);
+
+/* The same with device-resident outputs (see dafs_cuda_pairhmm_plan_fetch_device). */
+int dafs_cuda_pct_device(int nseq, const int* len, const dafs_csr_batch* mp, const dafs_csr_batch* bp,
+                         float w_pct_a, float w_pct_s, float* sim, dafs_csr_batch* mp_out,
+                         dafs_csr_batch* bp_out);
 
 /* Device time of the kernels of the last dafs_cuda_pct call on this thread, in ms:
  * {transpose, similarity, relax_bp, relax_mp, total incl. H2D/D2H}.              */

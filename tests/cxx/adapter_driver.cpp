@@ -147,6 +147,19 @@ int main(int argc, char** argv) {
                                   rx.data(), ry.data(), rz.data(), &it, &vi);
     CHECK(same_bits(rs, r.score) && (unsigned)it == r.iters && vi == r.violated, "solve_by_dd: score %g/%g iters %d/%u violated %u/%u", rs, r.score, it, r.iters, vi, r.violated);
     CHECK(VU(rx.begin(), rx.end()) == x && VU(ry.begin(), ry.end()) == y && VU(rz.begin(), rz.end()) == z, "solve_by_dd: x / y / z differ");
+    // (5) the whole pipeline, stage by stage through host containers vs in one call with device batches
+    {
+      std::vector<std::vector<MP> > mp2 = mp_g;
+      std::vector<BP> bp2 = bp;
+      VVF sim_a, sim_b;
+      dafs_cuda::consistency_transform(fa, mp2, bp2, 0.25f, 0.25f, sim_a);
+      std::vector<dafs_cuda::TreeNode> tree_a, tree_b;
+      dafs_cuda::build_tree(sim_a, tree_a);
+      VU ss_a, ss_b; ALN aln_a, aln_b;
+      const float sa = dafs_cuda::align_tree(o, fa, mp2, bp2, tree_a, ss_a, aln_a);
+      const float sb = dafs_cuda::align_from_sequences(o, fa, 0.01f, 0.25f, 0.25f, sim_b, tree_b, ss_b, aln_b);
+      CHECK(same_bits(sa, sb) && ss_a == ss_b && aln_a == aln_b && tree_a == tree_b, "align_from_sequences differs from the stage-by-stage adapters: %g vs %g", sa, sb);
+    }
     if (g_fail == 0)
       std::printf("adapters ok: %u sequences, %llu posteriors identical (ProbCons), Nussinov %.6f, NW %.6f, DD %u iterations score %.6f\n",
                   N, (unsigned long long)entries, sn_g, sw_g, r.iters, r.score);

@@ -137,3 +137,39 @@ def test_rejects_bad_tree():
         db.progressive(lens, mp, bp, [-1, -1, -1, 0, 0], [-1, -1, -1, 1, 3])     # node 0 used twice
     with pytest.raises(db.DafsCudaError):
         db.progressive(lens, mp, bp, [-1, -1, -1, 0, 4], [-1, -1, -1, 1, 2])     # child not earlier
+
+
+def test_device_resident_pipeline_equals_host_pipeline():
+    """Posteriors kept in HBM between the stages (fetch_device -> dafs_cuda_pct_device ->
+    dafs_cuda_progressive) give the bits of the pipeline that passes host batches."""
+    import dafs_b200 as db
+    seqs = db.homolog_family(14, 110, config_id=31)
+    lens = np.array([len(q) for q in seqs], np.int32)
+    pi, pj = db.all_pairs(len(seqs))
+    # host route
+    bp_h = db.mccaskill_all(seqs, 0.01); mp_h = db.pairhmm_all(seqs, 0.01)
+    sim_h, mp2_h, bp2_h = db.pct(lens, mp_h, bp_h, 0.25, 0.25)
+    left, right, _ = db.guide_tree(sim_h)
+    g_h = db.progressive(lens, mp2_h, bp2_h, left, right)
+    # device route
+    with db.McCaskillPlan(seqs, 0.01) as pm, db.PairHmmPlan(seqs, pi, pj, 0.01) as pp:
+        pm.run(); pp.run()
+        bp_d = pm.fetch_device(); mp_d = pp.fetch_device()
+        with pytest.raises(db.DafsCudaError):
+            pp.run()                                   # the plan gave its result arrays away
+    assert mp_d.nnz == mp_h.nnz and np.array_equal(mp_d.nz_off, mp_h.nz_off)
+    sim_d, mp2_d, bp2_d = db.pct(lens, mp_d, bp_d, 0.25, 0.25, device_out=True)
+    assert np.array_equal(sim_d.view(np.uint32), sim_h.view(np.uint32))
+    for dev, host in ((mp2_d, mp2_h), (bp2_d, bp2_h), (mp_d, mp_h)):
+        with dev.to_host() as c:
+            assert np.array_equal(c.row_ptr, host.row_ptr) and np.array_equal(c.col, host.col)
+            assert np.array_equal(c.val.view(np.uint32), host.val.view(np.uint32))
+    g_d = db.progressive(lens, mp2_d, bp2_d, left, right)
+    assert g_d["L"] == g_h["L"] and np.array_equal(g_d["bits"], g_h["bits"]) and np.array_equal(g_d["ss"], g_h["ss"])
+    assert g_d["score"].view(np.uint32) == g_h["score"].view(np.uint32)
+    # zero weights: the outputs are copies of the (device) inputs
+    _, c_mp, c_bp = db.pct(lens, mp_d, bp_d, 0.0, 0.0, device_out=True)
+    with c_mp.to_host() as c:
+        assert np.array_equal(c.val.view(np.uint32), mp_h.val.view(np.uint32))
+    for b in (bp_d, mp_d, mp2_d, bp2_d, c_mp, c_bp, bp_h, mp_h, mp2_h, bp2_h):
+        b.close()
