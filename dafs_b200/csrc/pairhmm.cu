@@ -157,7 +157,7 @@ static int alloc_pool(dafs_pairhmm_plan* p, int64_t cap) {
 // amortise the per-step shuffles, narrow ones keep the unrolled row body inside
 // the instruction cache.
 static const int kColsPerLane[] = {2, 3, 4, 5, 6, 8, 10, 12};
-static const float kColsCost[] = {1.30f, 1.14f, 1.00f, 1.00f, 0.94f, 0.92f, 1.01f, 1.08f};
+static const float kColsCost[] = {1.35f, 1.15f, 1.10f, 1.00f, 0.975f, 1.10f, 1.25f, 1.03f};   // time per padded column, B200, round 2
 static int choose_cols(int max_l2) {
   if (const char* e = getenv("DAFS_PAIRHMM_COLS")) {          // tuning knob
     const int want = atoi(e);

@@ -4,6 +4,7 @@
 // evaluation order follow probconsRNA/ScoreType.h exactly.
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdint>
 
 namespace dafs {
 
@@ -20,8 +21,11 @@ namespace dafs {
 // rounded once).  The coefficient rows {c3,c2,c1,c0} live in shared memory as a
 // 17-entry float4 table indexed by n, fetched with one LDS.128 -- this replaces
 // three compares and three selects per LOOKUP and moves the work from the ALU
-// pipe to the FMA pipe.  d is clamped to 8 first (n <= 16); for d >= 7.5 the
-// caller discards the value anyway.
+// pipe to the FMA pipe.  For d >= 7.5 the value is not needed and the fetch is skipped.
+// The shared-memory data pipe is the unit this kernel loads most (an LDS.128 is four
+// quarter-warp wavefronts of 128 bytes): every row is stored EIGHT times, copy (lane & 7) of row n
+// at float4 index 8 n + (lane & 7), so the eight lanes of a wavefront always read eight different
+// 16-byte bank groups whatever rows they want -- no bank conflict is possible.
 #define DAFS_LOOKUP_ROWS                                                                   \
   {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f},      \
   {-0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f},      \
@@ -30,13 +34,19 @@ namespace dafs {
 #define DAFS_LOOKUP_SLOTS 17
 __host__ __device__ __forceinline__ int pairhmm_lookup_piece(int n) { return n >= 10 ? 3 : n >= 6 ? 2 : n >= 3 ? 1 : 0; }
 
-__device__ __forceinline__ float pairhmm_lookup(const float4* __restrict__ tab, float d) {
-  const float t = __fmaf_ru(fminf(d, 8.0f), 2.0f, 12582912.0f);
-  const float4 k = tab[__float_as_int(t) - 0x4b400000];
-  float r = __fadd_rn(__fmul_rn(k.x, d), k.y);
-  r = __fadd_rn(__fmul_rn(r, d), k.z);
-  r = __fadd_rn(__fmul_rn(r, d), k.w);
-  return r;
+#define DAFS_LOOKUP_COPIES 8
+// Shared-window address of this lane's copy of row 0 plus the constant that cancels the exponent bits
+// of the magic sum below: bits(t) = 0x4b400000 + n, (bits << 7) mod 2^32 = 0xa0000000 + 128 n.
+// The sum is kept in shared memory and read back (PairHmmSmem::lut_addr[lane]): ptxas folds a value it can
+// trace to the cvta into "base register + immediate" again and spends a second integer add per call.
+__device__ __forceinline__ uint32_t pairhmm_lut_addr(const float4* tab, int lane) {
+  return (uint32_t)__cvta_generic_to_shared(tab) + (uint32_t)(lane & 7) * 16u + 0x60000000u;
+}
+
+__device__ __forceinline__ float pairhmm_lds(uint32_t addr) {
+  float v;
+  asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
 }
 
 // LOG_ADD / LOG_PLUS_EQUALS (ScoreType.h:233-238, :259-262), branch-free.
@@ -45,11 +55,44 @@ __device__ __forceinline__ float pairhmm_lookup(const float4* __restrict__ tab, 
 // or hi == LOG_ZERO too (then LOOKUP(0)+LOG_ZERO rounds to LOG_ZERO, the same
 // answer).  The same holds for the even more negative values that padded DP
 // cells carry, so "zero" never leaks into a finite cell.
-__device__ __forceinline__ float pairhmm_lse(const float4* __restrict__ tab, float x, float y) {
-  const float hi = fmaxf(x, y), lo = fminf(x, y);
-  const float d = __fsub_rn(hi, lo);
-  const float r = __fadd_rn(pairhmm_lookup(tab, d), lo);
-  return d >= 7.5f ? hi : r;
+// 14 instructions: max, min, sub, setp, fma.rp, lea, lds (skipped, like the final add, when
+// d >= 7.5: no clamp of the index is needed), 3 x (mul, add), add.  Every mul / add carries .rn,
+// which PTX never contracts.  The four coefficient registers are the caller's (PairHmmCoef, set
+// to anything once): a predicated load leaves them partly defined, and registers that every call
+// site declared for itself would be live across the whole DP loop.  Calls that share a set run
+// one after the other, so a caller keeps one set per independent chain.
+#ifndef DAFS_PAIRHMM_MSETS
+#define DAFS_PAIRHMM_MSETS 2     // sets for the M state (two calls per cell): cells alternate
+#endif
+struct PairHmmCoef { float k0 = 0.f, k1 = 0.f, k2 = 0.f, k3 = 0.f; };
+
+__device__ __forceinline__ float pairhmm_lse(uint32_t lut, PairHmmCoef& K, float x, float y) {
+  float r;
+  asm("{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .f32 hi, lo, d, t, q;\n\t"
+      ".reg .b32 a;\n\t"
+      "max.f32 hi, %5, %6;\n\t"
+      "min.f32 lo, %5, %6;\n\t"
+      "sub.rn.f32 d, hi, lo;\n\t"
+      "setp.ge.f32 p, d, 0f40F00000;\n\t"             // 7.5
+      "fma.rp.f32 t, d, 0f40000000, 0f4B400000;\n\t"  // ceil(2 d) in the low mantissa bits
+      "mov.b32 a, t;\n\t"
+      "shl.b32 a, a, 7;\n\t"
+      "add.u32 a, a, %7;\n\t"
+      "@!p ld.shared.v4.f32 {%1, %2, %3, %4}, [a];\n\t"
+      "mul.rn.f32 q, %1, d;\n\t"
+      "add.rn.f32 q, q, %2;\n\t"
+      "mul.rn.f32 q, q, d;\n\t"
+      "add.rn.f32 q, q, %3;\n\t"
+      "mul.rn.f32 q, q, d;\n\t"
+      "add.rn.f32 q, q, %4;\n\t"
+      "mov.f32 %0, hi;\n\t"
+      "@!p add.rn.f32 %0, q, lo;\n\t"
+      "}"
+      : "=&f"(r), "+f"(K.k0), "+f"(K.k1), "+f"(K.k2), "+f"(K.k3)
+      : "f"(x), "f"(y), "r"(lut));
+  return r;
 }
 
 // EXP (ScoreType.h:37-57) for x <= 0: quartic pieces with double literals, so

@@ -188,3 +188,29 @@ def test_config_c5_homologs_bit_exact():
     pi, pj = dafs_b200.all_pairs(3)
     with dafs_b200.pairhmm_pairs(fam, pi, pj, 0.01) as b:
         check_batch_against_oracle(fam, pi, pj, 0.01, b)
+
+
+def test_rows_beyond_shared_counters_bit_exact():
+    """More than 2048 rows: the per-row counters of the CSR emission leave shared memory for the forward plane
+    (DAFS_PAIRHMM_CNT_ROWS); 2100 x 300 and 300 x 2100 also put eight chained stripes behind two short ones."""
+    fam = homolog_family(2, 2100, config_id=7)
+    seqs = [fam[0], fam[1][:2047], fam[1][:300]]
+    pi = np.array([0, 1, 0, 2, 1], np.int32)
+    pj = np.array([1, 0, 2, 0, 2], np.int32)
+    with dafs_b200.pairhmm_pairs(seqs, pi, pj, 0.01) as b:
+        check_batch_against_oracle(seqs, pi, pj, 0.01, b)
+
+
+@pytest.mark.parametrize("cols", [2, 3, 4, 5, 6, 8, 10, 12])
+def test_every_stripe_width_bit_exact(cols, monkeypatch):
+    """Each compiled columns-per-lane variant (stripes of 64..384 columns), lengths around the stripe width and
+    around the minimum period of the chained stripes (short rows are spaced by idle steps)."""
+    monkeypatch.setenv("DAFS_PAIRHMM_COLS", str(cols))
+    sw = 32 * cols
+    pool = random_rna(6, 2 * sw + 40, config_id=cols)
+    seqs = [pool[0][:sw - 1], pool[1][:sw], pool[2][:sw + 1], pool[3], pool[4][:97], pool[5][:1]]
+    pi, pj = dafs_b200.all_pairs(len(seqs))
+    pi = np.concatenate([pi, pj]).astype(np.int32)
+    pj = np.concatenate([pj, pi[:len(pj)]]).astype(np.int32)
+    with dafs_b200.pairhmm_pairs(seqs, pi, pj, 0.01) as b:
+        check_batch_against_oracle(seqs, pi, pj, 0.01, b)
