@@ -45,6 +45,39 @@ def shard(npairs, rank, world):
     return np.arange(rank, npairs, world, dtype=np.int64)
 
 
+def gpu_numa_node(index):
+    """(NUMA node of GPU `index`, its CPUs) from sysfs, or (None, None) where the platform does not say."""
+    try:
+        import torch
+        props = torch.cuda.get_device_properties(index)
+        bus = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return None, None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        return node, (cpus or None)
+    except Exception:
+        return None, None
+
+
+def bind_to_gpu_node(index):
+    """Run this process on the CPUs next to its GPU, so that the pages it touches first (its region of the
+    shared result buffer, the library's page-locked staging) are in the memory its PCIe link reaches without
+    crossing the socket interconnect."""
+    node, cpus = gpu_numa_node(index)
+    if not cpus:
+        return False
+    try:
+        os.sched_setaffinity(0, cpus)
+        return True
+    except OSError:
+        return False
+
+
 class SharedHostBuffer:
     """Host memory that every rank of the node maps (POSIX shared memory) and page-locks for
     its own GPU: each rank's dafs_cuda_pairhmm_pairs_into call delivers its CSR fragment over
@@ -53,7 +86,7 @@ class SharedHostBuffer:
     row_ptr (int32), col (uint32), val (float32) of rank r's pairs, in that rank's pair order
     (bench.shard).  caps = (nnz, units, rows) capacity of one region."""
 
-    def __init__(self, dist, rank, world, caps, pin=True):
+    def __init__(self, dist, rank, world, caps, pin=True, numa_local=True, gpu=None, touch_all_by_rank0=False):
         from multiprocessing import resource_tracker, shared_memory
         mx_nnz, mx_units, mx_rows = (int(x) for x in caps)
         self.cap = (mx_nnz, mx_units, mx_rows)
@@ -77,6 +110,15 @@ class SharedHostBuffer:
         self.rank, self.world = rank, world
         self.bytes = np.frombuffer(self.shm.buf, dtype=np.uint8, count=nbytes)
         self.pinned = False
+        # first touch decides which memory node holds a page: every rank touches its own region, from the CPUs
+        # next to its GPU when the platform tells which they are
+        self.numa_bound = bool(numa_local and gpu is not None and bind_to_gpu_node(gpu))
+        if touch_all_by_rank0:                     # (profiling only: the placement this class had before)
+            if rank == 0:
+                self.bytes[:] = 0
+            dist.barrier()
+        else:
+            self.bytes[rank * self.stride:(rank + 1) * self.stride] = 0
         if pin:                                    # page-lock this rank's own region: the target of its copies
             import torch
             if torch.cuda.is_available():
@@ -603,7 +645,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         caps = t.cpu().numpy()
         caps[0] = int(caps[0] * 1.02) + 4096                 # nnz of a shard is only known after it ran
-        shared = SharedHostBuffer(dist, rank, world, caps)
+        shared = SharedHostBuffer(dist, rank, world, caps, gpu=local)
         dst = dafs_b200.HostCsr(*shared.region(rank))
         units_of = [len(shard(len(pi), r, world)) for r in range(world)]
     for it in range(W + K):

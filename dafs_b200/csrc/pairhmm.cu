@@ -1,6 +1,7 @@
 // Host side of (1): plan management, launch, CSR assembly and the C-ABI entry
 // points declared in include/dafs_cuda.h.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <numeric>
@@ -129,6 +130,8 @@ static void free_plan_buffers(dafs_pairhmm_plan* p) {
   if (p->ev1) cudaEventDestroy(p->ev1);
   if (p->evk0) cudaEventDestroy(p->evk0);
   if (p->evk1) cudaEventDestroy(p->evk1);
+  if (p->ev_cp0) cudaEventDestroy(p->ev_cp0);
+  if (p->ev_cp1) cudaEventDestroy(p->ev_cp1);
   for (int c = 0; c < 4; ++c) {
     if (p->ev_chunk[c]) cudaEventDestroy(p->ev_chunk[c]);
     if (p->evck0[c]) cudaEventDestroy(p->evck0[c]);
@@ -244,7 +247,14 @@ extern "C" int dafs_cuda_pairhmm_tables(float* out54) {
   return DAFS_CUDA_OK;
 }
 
-namespace dafs { static thread_local bool g_chunked_fetch = false; }
+namespace dafs {
+static thread_local bool g_chunked_fetch = false;
+// Copy time of a result over kernel time of the run that produced it, as the one-call entry points of this
+// process last saw it (0.47 for one B200 on a PCIe 5 link; near 1 when several ranks share the host's ingest
+// bandwidth and each runs an N-th of the pairs).  Decides how a pair list is cut into launches: the copy of
+// launch c runs under launch c + 1, so launch c + 1 should take about ratio x as long as launch c.
+static std::atomic<float> g_copy_ratio{0.4f};
+}
 
 extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, const int* len,
                                              int64_t npairs, const int32_t* pi, const int32_t* pj,
@@ -272,6 +282,7 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
   p->nseq = nseq; p->npairs = (int)npairs; p->th = th; p->xcut = compute_xcut(th);
   PLAN_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
   PLAN_TRY(cudaEventCreate(&p->ev0));
+  if (g_chunked_fetch) { PLAN_TRY(cudaEventCreate(&p->ev_cp0)); PLAN_TRY(cudaEventCreate(&p->ev_cp1)); }
   PLAN_TRY(cudaEventCreate(&p->ev1));
   PLAN_TRY(cudaEventCreate(&p->evk0));
   PLAN_TRY(cudaEventCreate(&p->evk1));
@@ -343,28 +354,31 @@ extern "C" int dafs_cuda_pairhmm_plan_create(int nseq, const char* const* seq, c
     // Chunk boundaries cost about 4 % of device time (drain and refill of the resident
     // warps), so only the one-call entry points, whose result always goes to the host, ask
     // for them; a split-phase plan runs as one launch unless DAFS_PAIRHMM_CHUNKS says otherwise.
-    int want = (g_chunked_fetch && rounds >= 6) ? 3 : 1;
+    const double ratio = std::min(1.0, std::max(0.25, (double)g_copy_ratio.load()));
+    int want = 1;
+    if (g_chunked_fetch) {
+      if (rounds >= 6) want = ratio > 0.6 ? 4 : 3;
+      else if (rounds >= 2 && ratio >= 0.6) want = (int)std::min<int64_t>(rounds, 4);   // the copy is as long as the kernels
+    }
     if (const char* e = getenv("DAFS_PAIRHMM_CHUNKS")) want = std::max(1, std::min(4, atoi(e)));
     if (rounds < want) want = 1;
     p->nchunks = want;
-    // Sizes fall geometrically (x 0.4): the copy of chunk c runs under the kernel of chunk
-    // c + 1, which only has to be 0.4 x as long (558 MB leave at 57 GB/s = 9.8 ms, the kernels
-    // take 24.6 ms), and the copy of the last chunk, which nothing hides, is a tenth of the
-    // result instead of a third.
+    // Sizes fall geometrically (x ratio): the copy of chunk c runs under the kernel of chunk
+    // c + 1, which only has to be ratio x as long (one GPU: 558 MB leave at 57 GB/s = 9.8 ms, the kernels
+    // take 21 ms), and the copy of the last chunk, which nothing hides, is the smallest.
     int64_t rc[4] = {0, 0, 0, 0};
     {
       double wsum = 0.0, w = 1.0;
-      for (int c = 0; c < want; ++c) { wsum += w; w *= 0.4; }
+      for (int c = 0; c < want; ++c) { wsum += w; w *= ratio; }
       int64_t used = 0;
-      w = 1.0;
       for (int c = want - 1; c >= 1; --c) {                 // smallest first, the first chunk takes the rest
         double wc = 1.0;
-        for (int k = 0; k < c; ++k) wc *= 0.4;
+        for (int k = 0; k < c; ++k) wc *= ratio;
         rc[c] = std::max<int64_t>(1, (int64_t)((double)rounds * wc / wsum + 0.5));
         used += rc[c];
       }
       rc[0] = rounds - used;
-      if (rc[0] < rc[1]) {                                   // few rounds: fall back to an even split
+      if (want > 1 && rc[0] < rc[1]) {                       // few rounds: fall back to an even split
         int64_t left_rounds = rounds;
         for (int c = 0; c < want; ++c) { rc[c] = (left_rounds + (want - c) - 1) / (want - c); left_rounds -= rc[c]; }
       }
@@ -468,19 +482,31 @@ static cudaError_t copy_chunks(dafs_pairhmm_plan* p, const HostCsr& h, int64_t c
   cudaError_t e = cudaSuccess;
   int64_t beg = 0;
   *overflow = false;
+  float copy_ms = 0.f;
   for (int c = 0; c < p->nchunks && e == cudaSuccess; ++c) {
     e = cudaEventSynchronize(p->ev_chunk[c]);
     if (e != cudaSuccess) break;
+    if (c > 0 && p->ev_cp0) {                          // the previous chunk's copy is over or still running: either way
+      float ms = 0.f;                                  // its own duration is what the events give
+      if (cudaEventSynchronize(p->ev_cp1) == cudaSuccess && cudaEventElapsedTime(&ms, p->ev_cp0, p->ev_cp1) == cudaSuccess) copy_ms += ms;
+    }
+    if (p->ev_cp0) cudaEventRecord(p->ev_cp0, p->copy_stream);
     const int64_t end = p->h_chunk_end[c];
     if (end > cap || end > p->pool_cap) { *overflow = true; break; }
     const int64_t r0 = p->row_off[p->chunk_k0[c]], r1 = p->row_off[p->chunk_k0[c + 1]];
     if (r1 > r0) e = cudaMemcpyAsync(h.row_ptr + r0, p->d_row_ptr + r0, sizeof(int32_t) * (r1 - r0), cudaMemcpyDeviceToHost, p->copy_stream);
     if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h.col + beg, p->d_col + beg, sizeof(uint32_t) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
     if (e == cudaSuccess && end > beg) e = cudaMemcpyAsync(h.val + beg, p->d_val + beg, sizeof(float) * (end - beg), cudaMemcpyDeviceToHost, p->copy_stream);
+    if (p->ev_cp1) cudaEventRecord(p->ev_cp1, p->copy_stream);
     beg = end;
   }
   if (e == cudaSuccess && !*overflow) e = cudaMemcpyAsync(h.nz_off, p->d_nz_off, sizeof(int64_t) * (p->npairs + 1), cudaMemcpyDeviceToHost, p->copy_stream);
   const cudaError_t e2 = cudaStreamSynchronize(p->copy_stream);
+  if (e == cudaSuccess && e2 == cudaSuccess && !*overflow && p->ev_cp0) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev_cp0, p->ev_cp1) == cudaSuccess) copy_ms += ms;
+    p->last_copy_ms = copy_ms;
+  }
   *copied = beg;
   return e == cudaSuccess ? e2 : e;
 }
@@ -488,11 +514,17 @@ static cudaError_t copy_chunks(dafs_pairhmm_plan* p, const HostCsr& h, int64_t c
 // One copy of a synchronised result (p->nnz known).
 static cudaError_t copy_whole(dafs_pairhmm_plan* p, const HostCsr& h) {
   const int64_t nnz = p->nnz, rows = p->total_rows;
+  if (p->ev_cp0) cudaEventRecord(p->ev_cp0, p->stream);
   cudaError_t e = cudaMemcpyAsync(h.nz_off, p->d_nz_off, sizeof(int64_t) * (p->npairs + 1), cudaMemcpyDeviceToHost, p->stream);
   if (e == cudaSuccess && rows) e = cudaMemcpyAsync(h.row_ptr, p->d_row_ptr, sizeof(int32_t) * rows, cudaMemcpyDeviceToHost, p->stream);
   if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h.col, p->d_col, sizeof(uint32_t) * nnz, cudaMemcpyDeviceToHost, p->stream);
   if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(h.val, p->d_val, sizeof(float) * nnz, cudaMemcpyDeviceToHost, p->stream);
+  if (p->ev_cp1) cudaEventRecord(p->ev_cp1, p->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (e == cudaSuccess && p->ev_cp0) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev_cp0, p->ev_cp1) == cudaSuccess) p->last_copy_ms = ms;
+  }
   return e;
 }
 }  // namespace dafs
@@ -640,6 +672,16 @@ extern "C" void dafs_cuda_pairhmm_plan_destroy(dafs_pairhmm_plan* p) {
   delete p;
 }
 
+namespace dafs {
+// after a one-call run: remember how long its result took to copy relative to its kernels
+static void note_copy_ratio(const dafs_pairhmm_plan* p) {
+  if (p->last_copy_ms > 0.f && p->last_kernel_ms > 0.05f && p->nnz > (1 << 20)) {
+    const float r = p->last_copy_ms / p->last_kernel_ms;
+    g_copy_ratio.store(0.5f * g_copy_ratio.load() + 0.5f * std::min(4.0f, r));
+  }
+}
+}  // namespace dafs
+
 extern "C" int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const int* len,
                                        int64_t npairs, const int32_t* pi, const int32_t* pj,
                                        float th, dafs_csr_batch* out) {
@@ -652,6 +694,7 @@ extern "C" int dafs_cuda_pairhmm_pairs(int nseq, const char* const* seq, const i
   if (rc) return rc;
   rc = dafs_cuda_pairhmm_plan_run(p);
   if (!rc) rc = dafs_cuda_pairhmm_plan_fetch(p, out);
+  if (!rc) dafs::note_copy_ratio(p);
   dafs_cuda_pairhmm_plan_destroy(p);
   return rc;
 }
@@ -667,6 +710,7 @@ extern "C" int dafs_cuda_pairhmm_pairs_into(int nseq, const char* const* seq, co
   if (rc) return rc;
   rc = dafs_cuda_pairhmm_plan_run(p);
   if (!rc) rc = dafs_cuda_pairhmm_plan_fetch_into(p, dst);
+  if (!rc) dafs::note_copy_ratio(p);
   dafs_cuda_pairhmm_plan_destroy(p);
   return rc;
 }

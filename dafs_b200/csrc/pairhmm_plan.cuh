@@ -36,9 +36,10 @@ struct dafs_pairhmm_plan {
   cudaEvent_t evck0[4] = {nullptr, nullptr, nullptr, nullptr}, evck1[4] = {nullptr, nullptr, nullptr, nullptr};
   int64_t* h_chunk_end = nullptr;   // pinned: nz_off at the end of each chunk
   cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_cp0 = nullptr, ev_cp1 = nullptr;   // around the result copies of a one-call run (copy rate, see g_copy_ratio)
   bool launched = false;
   bool consumed = false;            // the result arrays were given to a device batch
   int64_t nnz = -1;
-  float last_ms = 0, last_kernel_ms = 0;
+  float last_ms = 0, last_kernel_ms = 0, last_copy_ms = 0;
 };
 
