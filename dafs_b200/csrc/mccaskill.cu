@@ -122,6 +122,7 @@ struct dafs_mccaskill_plan {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int nseq = 0, W = 0, grid = 0, smem = 0, cluster = 1;
   int gl = 8, threads = MC_THREADS;    // lanes per DP cell, threads per CTA (mccaskill_kernel<GL>)
+  bool banded = false;                 // mccaskill_kernel<GL, true>
   float th = 0;
   int64_t total_rows = 0, pool_cap = 0, seq_bytes = 0;
   std::vector<int64_t> row_off;
@@ -151,8 +152,11 @@ static void free_mc_plan(dafs_mccaskill_plan* p) {
   if (p->stream) cudaStreamDestroy(p->stream);
 }
 static const int kMcMaxLen = 6000;
-static const void* mc_kernel_fn(int gl) {
-  return gl == 8 ? (const void*)mccaskill_kernel<8> : gl == 16 ? (const void*)mccaskill_kernel<16> : (const void*)mccaskill_kernel<32>;
+// banded: the O(span) sums in bands of diagonals with a tiled far pass (mc_far_tile): for a sequence that one CTA
+// of at least 256 threads owns; a cluster that shares a sequence keeps the cell-by-cell streams
+static const void* mc_kernel_fn(int gl, bool banded) {
+  if (banded) return gl == 8 ? (const void*)mccaskill_kernel<8, true> : gl == 16 ? (const void*)mccaskill_kernel<16, true> : (const void*)mccaskill_kernel<32, true>;
+  return gl == 8 ? (const void*)mccaskill_kernel<8, false> : gl == 16 ? (const void*)mccaskill_kernel<16, false> : (const void*)mccaskill_kernel<32, false>;
 }
 }  // namespace dafs
 
@@ -242,7 +246,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char*
   dafs::DevInfo prop;
   PLAN_TRY(dafs::dev_info(p->device, &prop));
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
-  p->smem = (int)(tab_bytes + sizeof(McCoef) + 2 * sizeof(double) * (p->W + 2) + 2 * sizeof(uint16_t) * p->W + p->W + 16 + 2 * sizeof(uint16_t) * (p->W + 2));
+  p->smem = (int)(tab_bytes + sizeof(McCoef) + sizeof(double) * MC_FAR_STAGE + 2 * sizeof(double) * (p->W + 2) + 2 * sizeof(uint16_t) * p->W + p->W + 16 + 2 * sizeof(uint16_t) * (p->W + 2));
   if ((size_t)p->smem > prop.smem_optin)
     return bail(fail(DAFS_CUDA_ENOTSUP, "sequence of %d nt needs %d bytes of shared memory", maxn, p->smem));
   // Lanes per DP cell: the sums of a cell are as long as its span, so short sequences (whose
@@ -255,7 +259,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char*
   // in a thread-block cluster per sequence.
   p->threads = (nseq >= prop.sms && 2 * (size_t)p->smem + 2048 <= prop.smem_optin) ? MC_THREADS / 2 : MC_THREADS;
   if (const char* e = getenv("DAFS_MCCASKILL_THREADS")) { const int v = atoi(e); if (v >= 64 && v <= MC_THREADS && v % 32 == 0) p->threads = v; }
-  const void* fn = mc_kernel_fn(p->gl);
+  const void* fn = mc_kernel_fn(p->gl, true);        // (both forms: same shared memory, same register bound)
   PLAN_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   int blocks = 0;
   PLAN_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, fn, p->threads, p->smem));
@@ -273,6 +277,7 @@ extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char*
   while (nc < 8 && (int64_t)nseq * nc * 2 <= slots) nc *= 2;
   if (const char* e = getenv("DAFS_MCCASKILL_CLUSTER")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) nc = v; }
   p->cluster = nc;
+  p->banded = nc == 1 && p->threads >= 256;
   const int teams = std::max(1, std::min(std::min(nseq, slots / nc), by_mem));
   p->grid = teams * nc;
 
@@ -331,7 +336,7 @@ extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   a.row_off = p->d_row_off; a.row_ptr = p->d_row_ptr; a.pool_off = p->d_pool_off; a.pool_col = p->d_pool_col;
   a.pool_val = p->d_pool_val; a.seq_nnz = p->d_seq_nnz; a.seq_lnz = p->d_seq_lnz;
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
-  const void* fn = mc_kernel_fn(p->gl);
+  const void* fn = mc_kernel_fn(p->gl, p->banded);
   DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
   {
     cudaLaunchConfig_t cfg = {};

@@ -111,9 +111,15 @@ struct McWs {
   double *q5, *q3;             // exterior partition functions of prefixes / suffixes
   double *Aroll, *Rroll;       // inside: A of the last three diagonals, R of the last two (indexed by i)
   double *plroll, *prroll, *tbroll;   // outside: prm_l, prml, tB of the last two diagonals (indexed by i)
+  double *far0, *far1;         // far parts of the O(span) sums of the current band of diagonals: [MC_NB][W] each
 };
 #define MC_NARRAYS 8
-#define MC_NROWS (14 + 96)   // q5 q3 | Aroll x3 Rroll x2 | plroll x2 prroll x2 tbroll x2 (+1 spare) | Vroll 3 x 32
+#define MC_NB 16             // diagonals per band (see mc_far_tile)
+#define MC_TI 32             // cells per diagonal in a tile of the far pass
+#define MC_KC 32             // terms staged per round of the far pass
+#define MC_FAR_ROWS (MC_TI + MC_TI + MC_NB - 1)                         // staged rows: P | D
+#define MC_FAR_STAGE (MC_KC * (MC_TI + 1) + MC_KC * (MC_TI + MC_NB))   // doubles of shared memory (also holds 5 x 512 partial sums)
+#define MC_NROWS (14 + 96 + 2 * MC_NB)   // q5 q3 | Aroll x3 Rroll x2 | plroll x2 prroll x2 tbroll x2 (+1 spare) | Vroll 3 x 32 | far0, far1
 
 // Hard constraints (RNAfold::calculate(seq, str, bp), src/fold.cpp:118-166): ViennaRNA applies the
 // dot-bracket constraint by removing every pair that conflicts with it.  Pair (i,j) survives when it
@@ -165,8 +171,10 @@ struct McCoef {              // per-scale coefficient tables in shared memory
 // packed at the head in ascending i, the others at the tail in descending i.  Built by the whole
 // CTA before the barrier that ends the previous diagonal; the order is a pure function of the
 // predicate, so every CTA of a cluster builds the same list and takes entries e = rank (mod nc).
+// promote_last: the front cell with the largest i moves to the second place (inside pass: cells i = 1 and
+// j = n are front cells and carry the exterior sums, so they start first).
 template <class F>
-__device__ __forceinline__ void mc_build_list(uint16_t* list, int ncell, McSched& sc, F front) {
+__device__ __forceinline__ void mc_build_list(uint16_t* list, int ncell, McSched& sc, F front, bool promote_last = false) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x;
   int base = 0;                                  // front cells among those of earlier passes
   for (int b = 0; b < ncell; b += NT) {
@@ -185,16 +193,153 @@ __device__ __forceinline__ void mc_build_list(uint16_t* list, int ncell, McSched
     base += total;
     if (b + NT < ncell) __syncthreads();          // wcnt is rewritten by the next pass
   }
+  if (promote_last && base >= 3) {
+    __syncthreads();
+    if (tid == 0) { const uint16_t t = list[1]; list[1] = list[base - 1]; list[base - 1] = t; }
+  }
+}
+
+// ---- the O(span) sums, banded -------------------------------------------------------------------
+// A(i,j) = sum_k qm(i,k-1) qm1(k,j) and the two outside sums are dot products of a row that belongs to
+// one end of the cell with a row that belongs to the other end.  Evaluated cell by cell they are chains of
+// dependent HBM round trips (span / lanes / MC_UNR of them per cell) that stream 2 x span doubles per cell.
+// Here the diagonals are taken in bands of MC_NB: the terms whose two factors were complete before the
+// band began -- all but fewer than MC_NB at either end of the range -- are summed for the whole band in one
+// pass over tiles of MC_TI cells x MC_NB diagonals.  In a tile one factor depends on a (the cell's position
+// in the diagonal: MC_TI rows, "P") and the other on a +- b (b = diagonal within the band: MC_TI + MC_NB - 1
+// rows, "D"); both are staged in shared memory MC_KC terms at a time, k fastest (coalesced), the next round's
+// values being fetched into registers while this round's are used, and every staged value feeds up to MC_NB
+// (P) or MC_TI (D) products.  The bounds of a cell's range are a property of ITS P row on one side and of ITS
+// D row on the other, so entries outside a row's bounds are staged as zeros and the inner loop has no tests.
+// The near terms are left to the cell-by-cell pass (mc_inside / mc_outside), which adds far + near.
+//   P entry: MP[(rp0 + a) * W + k + cp]  for k in prange(a),  D entry: MD[r * W + k + cd] for k in drange(r),
+//   r = rd0 + a + sgn * b.
+template <class FP, class FD, class FS>
+__device__ __forceinline__ void mc_far_tile(int W, int nmax, double* stage, const double* __restrict__ MP, int rp0, int cp,
+                                            const double* __restrict__ MD, int rd0, int sgn, int cd, int k0, int k1,
+                                            FP prange, FD drange, FS store) {
+  constexpr int PP = MC_TI + 1, PD = MC_TI + MC_NB, MB = 4;
+  constexpr int QM = 10;                               // staged rows per thread: warp, warp + nwp, ... (CTAs of >= 256 threads)
+  static_assert(MC_KC == 32, "a lane stages term kk = lane of its rows");
+  double* sP = stage;
+  double* sD = stage + MC_KC * PP;
+  const int tid = threadIdx.x, NT = blockDim.x, nwp = NT >> 5;
+  const int a = tid & 31, bw = tid >> 5, uoff = sgn < 0 ? MC_NB - 1 : 0;
+  // products: warp (bw & 3) owns diagonals 4 (bw & 3) .. + 3 of the band for all 32 cells of the tile (one P value,
+  // four D values, four FMAs per term); the nwp / 4 groups of four warps take the terms of a round in turn and
+  // their partial sums meet in shared memory at the end
+  static_assert(MC_NB == 16, "four warps x four diagonals");
+  const int G = max(nwp >> 2, 1), g = bw >> 2, b4 = (bw & 3) * 4;
+  const bool works = g < G;
+  double acc[MB];
+#pragma unroll
+  for (int m = 0; m < MB; ++m) acc[m] = 0.0;
+  double nxt[QM];
+  auto fetch = [&](int kc) {
+    const int k = kc + a;
+#pragma unroll
+    for (int q = 0; q < QM; ++q) {
+      const int row = bw + q * nwp;
+      double v = 0.0;
+      if (row < MC_FAR_ROWS && k <= k1) {
+        int lo, hi;
+        if (row < MC_TI) {
+          const int r = rp0 + row;
+          prange(row, lo, hi);
+          if (r >= 0 && r <= nmax + 1 && k >= lo && k <= hi) v = MP[(size_t)r * W + k + cp];
+        } else {
+          const int r = rd0 + (row - MC_TI) - uoff;
+          drange(r, lo, hi);
+          if (r >= 0 && r <= nmax + 1 && k >= lo && k <= hi) v = MD[(size_t)r * W + k + cd];
+        }
+      }
+      nxt[q] = v;
+    }
+  };
+  fetch(k0);
+  const double* dcol = sD + a + sgn * b4 + uoff;       // + sgn * m per diagonal, + kk * PD per term
+  for (int kc = k0; kc <= k1; kc += MC_KC) {
+#pragma unroll
+    for (int q = 0; q < QM; ++q) {
+      const int row = bw + q * nwp;
+      if (row < MC_TI) sP[a * PP + row] = nxt[q];
+      else if (row < MC_FAR_ROWS) sD[a * PD + (row - MC_TI)] = nxt[q];
+    }
+    __syncthreads();
+    if (kc + MC_KC <= k1) fetch(kc + MC_KC);
+    if (works) {
+      for (int kk = g; kk < MC_KC; kk += G) {
+        const double pv = sP[kk * PP + a];
+#pragma unroll
+        for (int m = 0; m < MB; ++m) acc[m] += pv * dcol[kk * PD + sgn * m];
+      }
+    }
+    __syncthreads();
+  }
+  if (G > 1) {                                         // (the last barrier above freed the staging tiles)
+    if (works && g > 0) {
+#pragma unroll
+      for (int m = 0; m < MB; ++m) stage[(g - 1) * (MC_TI * MC_NB) + (b4 + m) * MC_TI + a] = acc[m];
+    }
+    __syncthreads();
+    if (g == 0) {
+      for (int h = 1; h < G; ++h) {
+#pragma unroll
+        for (int m = 0; m < MB; ++m) acc[m] += stage[(h - 1) * (MC_TI * MC_NB) + (b4 + m) * MC_TI + a];
+      }
+    }
+  }
+  if (g == 0) {
+#pragma unroll
+    for (int m = 0; m < MB; ++m) store(a, b4 + m, acc[m]);
+  }
+  if (G > 1) __syncthreads();                          // the next tile stages into the same memory
+}
+
+// near terms of a banded sum: up to 2 * (MC_NB - 1) products x[t] * y[t], t = gl, gl + GL, ..., all loads first
+template <int GL, class FX>
+__device__ __forceinline__ double mc_near(int nterms, int gl, FX term) {
+  constexpr int NI = (2 * MC_NB + GL - 1) / GL;
+  double x[NI], y[NI];
+#pragma unroll
+  for (int u = 0; u < NI; ++u) {
+    const int t = gl + GL * u;
+    x[u] = 0.0; y[u] = 0.0;
+    if (t < nterms) term(t, x[u], y[u]);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int u = 0; u < NI; ++u) s += x[u] * y[u];
+  return s;
+}
+
+// two such sums in one round of loads: terms t < n1 go to s1, the others to s2
+template <int GL, class FX>
+__device__ __forceinline__ void mc_near2(int n1, int nterms, int gl, FX term, double& s1, double& s2) {
+  constexpr int NI = (2 * MC_NB + GL - 1) / GL;
+  double x[NI], y[NI];
+#pragma unroll
+  for (int u = 0; u < NI; ++u) {
+    const int t = gl + GL * u;
+    x[u] = 0.0; y[u] = 0.0;
+    if (t < nterms) term(t, x[u], y[u]);
+  }
+  s1 = 0.0; s2 = 0.0;
+#pragma unroll
+  for (int u = 0; u < NI; ++u) { const double pr = x[u] * y[u]; if (gl + GL * u < n1) s1 += pr; else s2 += pr; }
 }
 
 // Inside recursion over all spans for the current scale.  Z = q5[n] afterwards.
-template <int GL>
+template <int GL, bool BANDED>
 __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& cons, int n, int W, const double* scale,
                           const double* mlb, const McCoef& cf, McSched& sc, uint16_t* lists, const McWs& w,
-                          const McTeam& tm, int lane) {
+                          double* stage, const McTeam& tm, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
   constexpr int WG = 32 / GL;         // cells per warp
   const int gl = lane & (GL - 1), grp = lane / GL, NT = blockDim.x;
+  // The banded evaluation (mc_far_tile) pays when one CTA owns the sequence; a cluster that shares one has few
+  // tiles per CTA and band, and its whole-warp groups already keep many loads in flight per cell.
+  constexpr bool banded = BANDED;                            // chosen by the host: one CTA of >= 256 threads per sequence
   if (threadIdx.x < 2) sc.next[threadIdx.x] = 0;
   if (tm.rank == 0 && threadIdx.x == 0) { w.q5[0] = 1.0; w.q3[n + 1] = 1.0; }
   __syncthreads();
@@ -202,6 +347,19 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
   mc_sync(tm);
   for (int d = 0; d < n; ++d) {
     const int ncell = n - d;
+    const int d0 = banded ? (d & ~(MC_NB - 1)) : 0;             // first diagonal of the band (0: no far part)
+    if (banded && d == d0 && d0 > 0) {
+      // far part of A for the cells of diagonals d0 .. d0 + MC_NB - 1: k in [j - d0 + 1, i + d0]
+      // (both qm(i,k-1) and qm1(k,j) span less than d0)
+      for (int t = tm.rank; t * MC_TI < n - d0; t += tm.nc) {
+        const int i0 = 1 + t * MC_TI;
+        mc_far_tile(W, n, stage, w.qm, i0, -1, w.qm1T, i0 + d0, +1, 0, i0 + 1, min(i0 + MC_TI - 1 + d0, n),
+                    [&](int a, int& lo, int& hi) { lo = i0 + a + 1; hi = i0 + a + d0; },      // never the unwritten lower triangle: 0 x garbage
+                    [&](int r, int& lo, int& hi) { lo = r - d0 + 1; hi = r; },                 // k <= j
+                    [&](int a, int b, double v) { if (i0 + a + d0 + b <= n) w.far0[b * W + i0 + a] = v; });
+      }
+      mc_sync(tm);
+    }
     const uint16_t* list = lists + (d & 1) * W;
     const int usum = min(MC_MAXLOOP, d - MC_TURN - 3);          // u1 + u2 <= usum keeps l - k > TURN
     double* Ad = w.Aroll + (d % 3) * W;
@@ -223,7 +381,8 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
       const bool closes = (d > MC_TURN) && type != 0;
       const bool lead = valid && gl == 0;
       // operands of the group's epilogue, requested now so that their latency hides behind the sums
-      double pre_A = 0.0, pre_m1 = 0.0, pre_R = 0.0;
+      double pre_A = 0.0, pre_m1 = 0.0, pre_R = 0.0, pre_far = 0.0;
+      if (lead && d0 > 0) pre_far = w.far0[(d - d0) * W + i];
       if (lead && d > 0) {
         pre_m1 = w.qm1T[IX(j - 1, i)];
         pre_R = Rd1[i + 1];
@@ -238,15 +397,21 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
         const double* Grow = w.G + IX(i + 2, j);          // G(i+2, j-s) = Grow[-s]
         const double* GTrow = w.GT + IX(j - 2, i);        // G(i+s, j-2) = GT[j-2][i+s] = GTrow[s]
         double gen = 0.0;
+        double g1[NC], g2[NC], vo[NC];           // every load before the first store (the rows may alias for the compiler)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const int sz = 2 + gl + GL * c;
+          const bool on = valid && sz <= usum;
+          g1[c] = on ? Grow[-sz] : 0.0;
+          g2[c] = (on && sz > 2) ? GTrow[sz] : 0.0;
+          vo[c] = (on && sz >= 4) ? Vold[sz - 2] : 0.0;
+        }
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           const int sz = 2 + gl + GL * c;
           if (valid && sz <= usum) {
-            double bnd = Grow[-sz];
-            if (sz > 2) bnd += GTrow[sz];
-            bnd *= cf.gnin[sz - 2];
-            double v = bnd;
-            if (sz >= 4) v += Vold[sz - 2];
+            const double bnd = (g1[c] + g2[c]) * cf.gnin[sz - 2];
+            const double v = bnd + vo[c];
             Vnew[sz] = v;
             gen += cf.fgen[sz] * (sz >= 5 ? v : (sz == 4 ? bnd : 0.0));
           }
@@ -289,21 +454,30 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
           }
         }
       }
-      // A(i,j): one pass over k = i+1 .. j, four strides of 8 per round
+      // A(i,j): in the first band every k = i+1 .. j; later the d - d0 terms at either end of the range
+      // (the far part comes from mc_far_tile)
       double sm = 0.0;
       {
         const double* qm_i = w.qm + IX(i, 0);
         const double* qm1T_j = w.qm1T + IX(j, 0);
-        for (int kb = i + 1 + gl; kb <= j; kb += MC_UNR * GL) {
-          double a0[MC_UNR], a1[MC_UNR];
+        if (d0 == 0) {
+          for (int kb = i + 1 + gl; kb <= j; kb += MC_UNR * GL) {
+            double a0[MC_UNR], a1[MC_UNR];
 #pragma unroll
-          for (int u = 0; u < MC_UNR; ++u) {
-            const int k = kb + GL * u;
-            const bool ok = valid && k <= j;
-            a0[u] = ok ? qm_i[k - 1] : 0.0;  a1[u] = ok ? qm1T_j[k] : 0.0;
+            for (int u = 0; u < MC_UNR; ++u) {
+              const int k = kb + GL * u;
+              const bool ok = valid && k <= j;
+              a0[u] = ok ? qm_i[k - 1] : 0.0;  a1[u] = ok ? qm1T_j[k] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < MC_UNR; ++u) sm += a0[u] * a1[u];
           }
-#pragma unroll
-          for (int u = 0; u < MC_UNR; ++u) sm += a0[u] * a1[u];
+        } else {
+          const int nb = d - d0;                                 // k = i+1 .. j-d0  and  k = i+d0+1 .. j
+          sm = mc_near<GL>(valid ? 2 * nb : 0, gl, [&](int t, double& x, double& y) {
+            const int k = t < nb ? i + 1 + t : i + d0 + 1 + (t - nb);
+            x = qm_i[k - 1]; y = qm1T_j[k];
+          });
         }
       }
       vb = mc_group_sum<GL>(vb); sm = mc_group_sum<GL>(sm);
@@ -321,30 +495,57 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
         w.qm1T[IX(j, i)] = m1;
         w.E5T[IX(j, i)] = e_cur;
         const double r = m1 + pre_R * mlb[1];
+        sm += pre_far;
         Ad[i] = sm;
         Rd[i] = r;
         const double vqm = sm + r;
         w.qm[IX(i, j)] = vqm;
         w.qmT[IX(j, i)] = vqm;
       }
-      // exterior: the cell that completes column j of qb extends q5, the one that completes row i extends q3
+      // exterior: the cell that completes column j of qb extends q5, the one that completes row i extends q3.
+      // These two cells of every diagonal carry an O(n) sum each; the whole warp takes it (32 lanes, MC_UNR pairs
+      // of loads in flight per lane) instead of the cell's own group, or they would be what the barrier waits for.
       const bool ext5 = valid && i == 1, ext3 = valid && j == n;
-      if (__any_sync(0xffffffffu, ext5 || ext3)) {
+      const unsigned m5 = __ballot_sync(0xffffffffu, ext5 && gl == 0), m3 = __ballot_sync(0xffffffffu, ext3 && gl == 0);
+      if (m5 | m3) {
         double s5 = 0.0, s3 = 0.0;
-        if (ext5) {                                    // k = 2 .. j - TURN - 1 (k = 1 is this cell)
-          const double* e5 = w.E5T + IX(j, 0);
-          for (int k = 2 + gl; k < j - MC_TURN; k += GL) s5 += w.q5[k - 1] * e5[k];
-        }
-        if (ext3) {                                    // k = i + TURN + 1 .. n - 1 (k = n is this cell)
-          const double* qb_i = w.qb + IX(i, 0);
-          const int sl = i > 1 ? (int)S[i - 1] : -1;
-          const int si = S[i];
-          for (int k = i + MC_TURN + 1 + gl; k < n; k += GL) {
-            const double v = qb_i[k];
-            if (v != 0.0) s3 += v * mc_stem(T, mc_pair(si, S[k]), sl, (int)S[k + 1], false) * w.q3[k + 1];
+        if (m5) {                                      // k = 2 .. j - TURN - 1 (k = 1 is this cell)
+          const int jj = __shfl_sync(0xffffffffu, j, __ffs(m5) - 1);
+          const double* e5 = w.E5T + IX(jj, 0);
+          for (int kb = 2 + lane; kb < jj - MC_TURN; kb += 32 * MC_UNR) {
+            double x[MC_UNR], y[MC_UNR];
+#pragma unroll
+            for (int u = 0; u < MC_UNR; ++u) {
+              const int k = kb + 32 * u;
+              const bool ok = k < jj - MC_TURN;
+              x[u] = ok ? w.q5[k - 1] : 0.0; y[u] = ok ? e5[k] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < MC_UNR; ++u) s5 += x[u] * y[u];
           }
+          s5 = mc_warp_sum(s5);
         }
-        s5 = mc_group_sum<GL>(s5); s3 = mc_group_sum<GL>(s3);
+        if (m3) {                                      // k = i + TURN + 1 .. n - 1 (k = n is this cell)
+          const int ii = __shfl_sync(0xffffffffu, i, __ffs(m3) - 1);
+          const double* qb_i = w.qb + IX(ii, 0);
+          const int sl = ii > 1 ? (int)S[ii - 1] : -1;
+          const int si = S[ii];
+          for (int kb = ii + MC_TURN + 1 + lane; kb < n; kb += 32 * MC_UNR) {
+            double x[MC_UNR], y[MC_UNR];
+#pragma unroll
+            for (int u = 0; u < MC_UNR; ++u) {
+              const int k = kb + 32 * u;
+              const bool ok = k < n;
+              x[u] = ok ? qb_i[k] : 0.0; y[u] = ok ? w.q3[k + 1] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < MC_UNR; ++u) {
+              const int k = kb + 32 * u;
+              if (x[u] != 0.0) s3 += x[u] * mc_stem(T, mc_pair(si, S[k]), sl, (int)S[k + 1], false) * y[u];
+            }
+          }
+          s3 = mc_warp_sum(s3);
+        }
         if (lead && ext5) w.q5[j] = w.q5[j - 1] * scale[1] + e_cur + s5;
         if (lead && ext3) w.q3[i] = w.q3[i + 1] * scale[1] + e_cur + s3;
       }
@@ -354,7 +555,8 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
     if (d + 1 < n) {
       const int dn = d + 1;
       mc_build_list(lists + (dn & 1) * W, n - dn, sc,
-                    [&](int i) { return dn <= MC_TURN || (mc_pair(S[i], S[i + dn]) != 0 && mc_allowed(cons, i, i + dn)); });
+                    [&](int i) { return dn <= MC_TURN || i == 1 || i == n - dn || (mc_pair(S[i], S[i + dn]) != 0 && mc_allowed(cons, i, i + dn)); },
+                    dn > MC_TURN);
     }
     mc_sync(tm);
   }
@@ -362,10 +564,10 @@ __device__ void mc_inside(const McTables& T, const uint8_t* S, const McCons& con
 }
 
 // Outside recursion; needs the inside arrays of the same scale.
-template <int GL>
+template <int GL, bool BANDED>
 __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, const double* scale,
                            const double* mlb, const McCoef& cf, McSched& sc, uint16_t* lists, const McWs& w,
-                           const McTeam& tm, int lane) {
+                           double* stage, const McTeam& tm, int lane) {
 #define IX(i, j) ((size_t)(i) * W + (j))
   constexpr int WG = 32 / GL;         // cells per warp
   const int gl = lane & (GL - 1), grp = lane / GL, NT = blockDim.x;
@@ -384,8 +586,31 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
                     [&](int i) { return mc_pair(S[i], S[i + d0]) != 0 && w.qb[IX(i, i + d0)] != 0.0; });
   }
   mc_sync(tm);
+  constexpr bool banded = BANDED;                               // see mc_inside
+  int dtop = n - 1;                                             // top diagonal of the current band
   for (int d = n - 1; d > MC_TURN; --d) {
     const int ncell = n - d;
+    if (banded && (d == n - 1 || (d & (MC_NB - 1)) == MC_NB - 1)) {
+      // Band d .. d - (d mod MC_NB): the terms of the two O(span) sums whose outside factor belongs to a cell of
+      // span > dtop (complete):  (a) q >= i + dtop + 1,  (c) p <= j - dtop - 1 (and p <= i - 2).
+      dtop = d;
+      const int dbot = max(d & ~(MC_NB - 1), MC_TURN + 1);
+      for (int t = tm.rank; t * MC_TI < n - dbot; t += tm.nc) {
+        const int i0 = 1 + t * MC_TI;
+        // (a): P = OM(i, q), D = qm(j+1, q-1), j + 1 = i0 + dtop + 1 + a - b
+        mc_far_tile(W, n, stage, w.OM, i0, 0, w.qm, i0 + dtop + 1, -1, -1, i0 + dtop + 1, n,
+                    [&](int a, int& lo, int& hi) { lo = i0 + a + dtop + 1; hi = n; },
+                    [&](int r, int& lo, int& hi) { lo = r + 1; hi = r <= n ? n : -1; },         // q - 1 >= j + 1
+                    [&](int a, int b, double v) { if (dtop - b > MC_TURN && i0 + a + dtop - b <= n) w.far0[b * W + i0 + a] = v; });
+        // (c): P = qm(p+1, i-1) = qmT[i-1][p+1], D = PL(p, j) = PLT[j][p], j = i0 + dtop + a - b
+        mc_far_tile(W, n, stage, w.qmT, i0 - 1, +1, w.PLT, i0 + dtop, -1, 0, 1, min(i0 + MC_TI - 3, n),
+                    [&](int a, int& lo, int& hi) { lo = 1; hi = i0 + a - 2; },
+                    [&](int r, int& lo, int& hi) { lo = 1; hi = r <= n ? r - dtop - 1 : -1; },
+                    [&](int a, int b, double v) { if (dtop - b > MC_TURN && i0 + a + dtop - b <= n) w.far1[b * W + i0 + a] = v; });
+      }
+      mc_sync(tm);
+    }
+    const int bnd_b = dtop - d;                                 // diagonal within the band
     const uint16_t* list = lists + (d & 1) * W;
     double* pl_d = w.plroll + (d & 1) * W;   const double* pl_d1 = w.plroll + ((d + 1) & 1) * W;   // diagonal d + 1
     double* pr_d = w.prroll + (d & 1) * W;   const double* pr_d1 = w.prroll + ((d + 1) & 1) * W;
@@ -405,18 +630,35 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       const int type = valid ? mc_pair(S[i], S[j]) : 0;
       const double qbij = type ? w.qb[IX(i, j)] : 0.0;
       const bool pairs = type != 0 && qbij != 0.0;
-      double pre_pl = 0.0, pre_om = 0.0, pre_prml = 0.0, pre_tB = 0.0, pre_q1 = 0.0, pre_q2 = 0.0;
+      double pre_pl = 0.0, pre_om = 0.0, pre_prml = 0.0, pre_tB = 0.0, pre_q1 = 0.0, pre_q2 = 0.0, pre_fa = 0.0, pre_fc = 0.0;
       if (lead) {
+        if (banded) {
+          pre_fa = w.far0[bnd_b * W + i];
+          if (pairs) pre_fc = w.far1[bnd_b * W + i];
+        }
         if (j + 1 <= n) { pre_pl = pl_d1[i]; pre_om = w.OM[IX(i, j + 1)]; }
         if (i > 1) { pre_prml = pr_d1[i - 1]; pre_tB = tb_d1[i - 1]; }
         if (pairs) { pre_q1 = w.q5[i - 1]; pre_q2 = w.q3[j + 1]; }
       }
       // (a) prml(i,j) = sum_{q = j+2 .. n} OM(i,q) * qm(j+1,q-1)            [every cell]
       // (c) sum_{p = 1 .. i-2} PL(p,j) * qm(p+1,i-1)                        [cells that pair]
-      // fused into one loop of na + nc steps: both operands of a step are contiguous in their stream
-      const int na = valid ? max(0, n - j - 1) : 0, ncc = pairs ? max(0, i - 2) : 0;
+      // here only the terms next to the cell (fewer than MC_NB each, one round of loads); the rest is in far0 / far1
       double ta = 0.0, tc = 0.0;
-      {
+      if (banded) {
+        const int na = valid ? max(0, min(i + dtop, n) - (j + 2) + 1) : 0;
+        const int p0 = max(1, i - bnd_b);
+        const int ncc = pairs ? max(0, (i - 2) - p0 + 1) : 0;
+        const double* OM_i = w.OM + IX(i, 0) + (j + 2);          // OM(i, j+2+t)
+        const double* qm_j1 = w.qm + IX(min(j + 1, n), 0) + (j + 1);   // qm(j+1, j+1+t)
+        const double* pl_j = w.PLT + IX(j, 0) + p0;              // PL(p0+t, j)
+        const double* qmT_i1 = w.qmT + IX(i - 1, 0) + p0 + 1;    // qm(p0+1+t, i-1) = qmT[i-1][p0+1+t]
+        mc_near2<GL>(na, na + ncc, gl, [&](int t, double& x, double& y) {
+          if (t < na) { x = OM_i[t]; y = qm_j1[t]; }
+          else { x = pl_j[t - na]; y = qmT_i1[t - na]; }
+        }, ta, tc);
+      } else {
+        // the whole of both sums, fused into one loop of na + nc steps: both operands of a step are contiguous
+        const int na = valid ? max(0, n - j - 1) : 0, ncc = pairs ? max(0, i - 2) : 0;
         const double* OM_i = w.OM + IX(i, 0) + (j + 2);          // OM(i, j+2+t)
         const double* qm_j1 = w.qm + IX(min(j + 1, n), 0) + (j + 1);   // qm(j+1, j+1+t)
         const double* pl_j = w.PLT + IX(j, 0) + 1;               // PL(1+t, j)
@@ -449,16 +691,21 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
         const double* Hrow = w.H + IX(i - 2, j);                   // H(i-2, j+s) = Hrow[s]
         const double* HTrow = w.HT + IX(j + 2, i);                 // H(i-s, j+2) = HT[j+2][i-s] = HTrow[-s]
         double gen = 0.0;
+        double g1[NC], g2[NC], vo[NC];           // every load before the first store
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const int sz = 2 + gl + GL * c;
+          const bool on = valid && sz <= MC_MAXLOOP;
+          g1[c] = (on && i >= 3 && j + sz <= n) ? Hrow[sz] : 0.0;
+          g2[c] = (on && sz > 2 && i - sz >= 1 && j + 2 <= n) ? HTrow[-sz] : 0.0;
+          vo[c] = (on && sz >= 4 && has_old) ? Vold[sz - 2] : 0.0;
+        }
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           const int sz = 2 + gl + GL * c;
           if (valid && sz <= MC_MAXLOOP) {
-            double bnd = 0.0;
-            if (i >= 3 && j + sz <= n) bnd = Hrow[sz];
-            if (sz > 2 && i - sz >= 1 && j + 2 <= n) bnd += HTrow[-sz];
-            bnd *= cf.gnin[sz - 2];
-            double v = bnd;
-            if (sz >= 4 && has_old) v += Vold[sz - 2];
+            const double bnd = (g1[c] + g2[c]) * cf.gnin[sz - 2];
+            const double v = bnd + vo[c];
             Vnew[sz] = v;
             gen += cf.fgen[sz] * (sz >= 5 ? v : (sz == 4 ? bnd : 0.0));
           }
@@ -499,6 +746,7 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
       if (lead) {
         if (j + 1 <= n) {
           const double pl = pre_pl * mlb[1] + pre_om;
+          ta += pre_fa;
           pr_d[i] = ta;
           pl_d[i] = pl;
           w.PLT[IX(j, i)] = ta + pl;
@@ -508,7 +756,7 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
         if (pairs) {
           const int sl = i > 1 ? (int)S[i - 1] : -1, sr = j < n ? (int)S[j + 1] : -1;
           o += pre_q1 * pre_q2 * mc_stem(T, type, sl, sr, false);
-          o += (tc + tb) * mc_stem(T, type, sl, sr, true);
+          o += (tc + pre_fc + tb) * mc_stem(T, type, sl, sr, true);
           w.O[IX(i, j)] = o;
           const double hij = o * (double)T.mmI[type - 1][S[i + 1]][S[j - 1]];
           w.H[IX(i, j)] = hij;
@@ -532,9 +780,9 @@ __device__ void mc_outside(const McTables& T, const uint8_t* S, int n, int W, co
 
 namespace dafs {
 
-// Dynamic shared memory: McTables | McCoef | scale[W+2] | mlb[W+2] | lists[2][W] (uint16) | codes[W+8] |
-// constraint classes[W+2], partners[W+2] (uint16)
-template <int GL>
+// Dynamic shared memory: McTables | McCoef | staging tiles of the far pass | scale[W+2] | mlb[W+2] |
+// lists[2][W] (uint16) | codes[W+8] | constraint classes[W+2], partners[W+2] (uint16)
+template <int GL, bool BANDED>
 __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   extern __shared__ __align__(16) char smem[];
   __shared__ int s_total;
@@ -542,7 +790,8 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
   McTables& T = *reinterpret_cast<McTables*>(smem);
   const size_t tab_bytes = (sizeof(McTables) + 15) & ~size_t(15);
   McCoef& cf = *reinterpret_cast<McCoef*>(smem + tab_bytes);
-  double* scale = reinterpret_cast<double*>(smem + tab_bytes + sizeof(McCoef));
+  double* stage = reinterpret_cast<double*>(smem + tab_bytes + sizeof(McCoef));
+  double* scale = stage + MC_FAR_STAGE;
   double* mlb = scale + (a.W + 2);
   uint16_t* lists = reinterpret_cast<uint16_t*>(mlb + (a.W + 2));
   uint8_t* S = reinterpret_cast<uint8_t*>(lists + 2 * a.W);
@@ -571,6 +820,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
     w.q5 = rows; w.q3 = rows + W; w.Aroll = rows + 2 * W; w.Rroll = rows + 5 * W;
     w.plroll = rows + 7 * W; w.prroll = rows + 9 * W; w.tbroll = rows + 11 * W;
     w.Vroll = rows + 14 * W;
+    w.far0 = rows + (14 + 96) * W; w.far1 = w.far0 + MC_NB * W;
   }
 #define IX(i, j) ((size_t)(i) * W + (j))
   // sequences are dealt to the teams round-robin in length order (longest first)
@@ -606,7 +856,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
         cf.cbul[k] = k <= MC_MAXLOOP ? (double)T.bulge[k] * exp(-(double)(k + 2) * lns) : 0.0;
       }
       __syncthreads();
-      mc_inside<GL>(T, S, cons, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
+      mc_inside<GL, BANDED>(T, S, cons, n, W, scale, mlb, cf, s_sched, lists, w, stage, tm, lane);
       Z = w.q5[n];
       if (isnan(Z) || isinf(Z)) { lns += 0.35; continue; }
       if (!(Z > 0.0)) { lns -= 0.25; continue; }
@@ -614,7 +864,7 @@ __global__ void __launch_bounds__(MC_THREADS) mccaskill_kernel(const McArgs a) {
       if (fabs(log(Z)) <= 150.0) break;
       lns = lnZ / (double)n;                            // rerun with the ensemble's own scale
     }
-    mc_outside<GL>(T, S, n, W, scale, mlb, cf, s_sched, lists, w, tm, lane);
+    mc_outside<GL, BANDED>(T, S, n, W, scale, mlb, cf, s_sched, lists, w, stage, tm, lane);
     // ---- read-out: p = float(qb*O/Z) > th, rows ascending, columns ascending ----
     int32_t* row_ptr = a.row_ptr + a.row_off[s];
     const float th = a.th;
