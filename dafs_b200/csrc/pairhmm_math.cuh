@@ -81,12 +81,18 @@ __device__ __forceinline__ float pairhmm_lse(uint32_t lut, PairHmmCoef& K, float
       "shl.b32 a, a, 7;\n\t"
       "add.u32 a, a, %7;\n\t"
       "@!p ld.shared.v4.f32 {%1, %2, %3, %4}, [a];\n\t"
+#ifdef DAFS_PAIRHMM_FMA   /* A/B build only (tools/ab_pairhmm_fma.sh): fused polynomial, NOT bit-exact with the reference */
+      "fma.rn.f32 q, %1, d, %2;\n\t"
+      "fma.rn.f32 q, q, d, %3;\n\t"
+      "fma.rn.f32 q, q, d, %4;\n\t"
+#else
       "mul.rn.f32 q, %1, d;\n\t"
       "add.rn.f32 q, q, %2;\n\t"
       "mul.rn.f32 q, q, d;\n\t"
       "add.rn.f32 q, q, %3;\n\t"
       "mul.rn.f32 q, q, d;\n\t"
       "add.rn.f32 q, q, %4;\n\t"
+#endif
       "mov.f32 %0, hi;\n\t"
       "@!p add.rn.f32 %0, q, lo;\n\t"
       "}"
