@@ -194,6 +194,53 @@ def test_constraint_rejected_when_unbalanced(dafs):
         dafs.mccaskill_constrained([b"GGGAAAUCCC"], [b"((??????)?"])
 
 
+# ---- the banded kernel (mccaskill_kernel<GL, true>): one CTA per sequence --------------------------------
+# Small batches get a thread-block cluster per sequence and the streaming kernel, so the cases above never
+# reach the band pass; these do: DAFS_MCCASKILL_CLUSTER=1 gives every sequence one CTA whatever the batch, and
+# the last case is the throughput form itself (more sequences than SMs: two CTAs of 384 threads per SM).
+
+@pytest.mark.parametrize("lanes", [8, 16, 32])
+@pytest.mark.parametrize("n,count", [(47, 3), (150, 3), (300, 3), (601, 2)])
+def test_banded_kernel_random_lengths(dafs, monkeypatch, n, count, lanes):
+    """Lengths below, at and above a few bands of 16 diagonals and tiles of 32 cells, every group size."""
+    monkeypatch.setenv("DAFS_MCCASKILL_CLUSTER", "1")
+    monkeypatch.setenv("DAFS_MCCASKILL_LANES", str(lanes))
+    seqs = random_rna(count, n, config_id=21)
+    with dafs.McCaskillPlan(seqs, 0.01) as plan:
+        assert plan.info()["grid"] == count                      # one CTA per sequence
+    assert check_batch(dafs, seqs) <= TOL
+
+
+def test_banded_kernel_ragged_rescale_and_constraints(dafs, monkeypatch):
+    monkeypatch.setenv("DAFS_MCCASKILL_CLUSTER", "1")
+    r = random_rna(8, 200, config_id=9)
+    seqs = [r[k][:20 + 25 * k] for k in range(8)] + [(b"GGGGCCCCGGGGAAAACCCCGGGGCCCC" * 20)[:500]]
+    for th in (0.01, 0.001):
+        assert check_batch(dafs, seqs, th) <= TOL
+    cseqs = fasta_read(os.path.join(ROOT, "tests", "golden", "RF00017_4.fa"))[1][:3] + random_rna(2, 400, config_id=17)
+    cseqs = [q if isinstance(q, bytes) else q.encode() for q in cseqs]
+    cons = [constrained_case(q, seed=k) for k, q in enumerate(cseqs)]
+    assert check_constrained(dafs, cseqs, cons) <= TOL
+
+
+def test_banded_kernel_throughput_form_and_repeatable(dafs):
+    """160 sequences of 40..120 nt: more sequences than SMs, so the plan takes two CTAs of 384 threads per SM and the
+    banded kernel by itself; every sequence against the restatement, and twice the same bits."""
+    pool = random_rna(160, 120, config_id=23)
+    seqs = [s[:40 + (k % 81)] for k, s in enumerate(pool)]
+    with dafs.McCaskillPlan(seqs, 0.01) as plan:
+        info = plan.info()
+        assert info["block"] == 384 and info["grid"] >= 148
+        runs = []
+        for rep in range(2):
+            plan.run()
+            b, lnz = plan.fetch()
+            with b:
+                runs.append((b.row_ptr.copy(), b.col.copy(), b.val.view(np.uint32).copy(), np.array(lnz)))
+        assert all(np.array_equal(x, y) for x, y in zip(*runs))
+    assert check_batch(dafs, seqs) <= TOL
+
+
 VIENNA_GOLD = os.path.join(ROOT, "tests", "golden", "mccaskill_golden.json")
 
 
