@@ -709,6 +709,11 @@ def run_ours(args):
                          "frac": achieved / fma_tf, "traffic": traffic,
                          "peak_nominal": FP32_NOMINAL_TFLOPS, "peak_unfused_muladd": muladd_tf,
                          "frac_of_unfused": achieved / muladd_tf,
+                         # the survey's 120 flop/cell counts three LOG_PLUS_EQUALS per cell that take the reference's
+                         # LOG_ZERO shortcut and do no arithmetic; printed for comparison with SURVEY.md 8(d)
+                         "flop_per_cell": FLOP_PER_CELL, "frac_at_120_flop_per_cell": achieved * 120.0 / FLOP_PER_CELL / fma_tf,
+                         "traffic_source": "profiles/pairhmm_traffic.json: dram bytes of one launch from the committed ncu "
+                                           "capture of this kernel, not measured in this run",
                          "note": "FP32 CUDA-core bound (SURVEY.md 8(d): neither the HBM nor the tensor roofline applies; "
                                  "the HBM view is in roofline_hbm); peak = FFMA rate measured by dafs_cuda_fp32_probe in "
                                  "this run (MEASURED_PEAKS.json has no FP32 entry; nominal 148 SM x 128 x 2 x 1.965 GHz "
