@@ -275,7 +275,29 @@ extern "C" int dafs_cuda_mccaskill_plan_create_constrained(int nseq, const char*
   const int slots = prop.sms * blocks;
   int nc = 1;
   while (nc < 8 && (int64_t)nseq * nc * 2 <= slots) nc *= 2;
-  if (const char* e = getenv("DAFS_MCCASKILL_CLUSTER")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) nc = v; }
+  // Very few sequences (a C5 shard of an 8-GPU run holds two): a non-portable cluster of 16 CTAs per sequence, when
+  // the device can co-schedule one per sequence (a cluster lives inside one GPC)
+  bool allow16 = false;
+  if (nc == 8 && (int64_t)nseq * 16 * 2 <= slots) {
+    const void* fs = mc_kernel_fn(p->gl, false);
+    if (cudaFuncSetAttribute(fs, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+        cudaFuncSetAttribute(fs, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem) == cudaSuccess) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(16 * nseq); cfg.blockDim = dim3(p->threads); cfg.dynamicSmemBytes = p->smem;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 16; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      int ncl = 0;
+      if (cudaOccupancyMaxActiveClusters(&ncl, fs, &cfg) == cudaSuccess && ncl >= nseq) { nc = 16; allow16 = true; }
+    }
+    (void)cudaGetLastError();
+  }
+  if (const char* e = getenv("DAFS_MCCASKILL_CLUSTER")) {
+    const int v = atoi(e);
+    if (v == 1 || v == 2 || v == 4 || v == 8) nc = v;
+    else if (v == 16 && allow16) nc = 16;
+  }
   p->cluster = nc;
   p->banded = nc == 1 && p->threads >= 256;
   const int teams = std::max(1, std::min(std::min(nseq, slots / nc), by_mem));
@@ -338,6 +360,7 @@ extern "C" int dafs_cuda_mccaskill_plan_run(dafs_mccaskill_plan* p) {
   DAFS_CUDA_TRY(cudaEventRecord(p->ev0, p->stream));
   const void* fn = mc_kernel_fn(p->gl, p->banded);
   DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem));
+  if (p->cluster > 8) DAFS_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p->grid); cfg.blockDim = dim3(p->threads);
