@@ -678,13 +678,27 @@ static int dd_plan_create_impl(int nprob, const dafs_dd_problem* prob, int want_
   // counts, so give each Nussinov structure a team of warps -- the largest team that does not
   // push a scratch array out of shared memory.
   {
-    int want = nprob <= prop.sms ? 3 : 1;
-    if (const char* e = getenv("DAFS_DD_TEAM")) want = std::max(1, std::min(3, atoi(e)));
+    // (also when the batch is larger than the SM count but every problem still gets a CTA of its own with the
+    // team's shared memory and threads: small problems, several CTAs per SM)
     const bool forced = getenv("DAFS_DD_TEAM") != nullptr;
+    int want = 3;
+    if (forced) want = std::max(1, std::min(3, atoi(getenv("DAFS_DD_TEAM"))));
     for (int t = want; t > 1; --t) {
       DDLayout lay2 = p->lay; int smem2 = 0; size_t ws2 = 0;
       plan_layout(lay2, m, budget, t, &smem2, &ws2);
-      if (forced || lay2.in_smem == p->lay.in_smem) { p->lay = lay2; p->smem = smem2; ws_per = ws2; p->team = t; break; }
+      if (!forced) {
+        if (lay2.in_smem != p->lay.in_smem) continue;
+        if (nprob > prop.sms) {                      // does every problem get its own CTA?
+          const bool all2 = (lay2.in_smem == (1u << DD_NITEMS) - 1u);
+          const void* fn2 = dd_kernel_fn(all2, t);
+          int b2 = 0;
+          if (dd_allow_smem(fn2, all2, t, p->device, prop.smem_optin) != cudaSuccess ||
+              cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, fn2, 32 * (2 * t + 1), smem2) != cudaSuccess ||
+              (int64_t)nprob > (int64_t)prop.sms * b2) { (void)cudaGetLastError(); continue; }
+        }
+      }
+      p->lay = lay2; p->smem = smem2; ws_per = ws2; p->team = t;
+      break;
     }
   }
   p->all_smem = (p->lay.in_smem == (1u << DD_NITEMS) - 1u);
